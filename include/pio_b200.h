@@ -1,0 +1,258 @@
+/* pio_b200 — C ABI of the B200-native Perceiver IO hot path (libpio_b200.so).
+ *
+ * The reference (felixyu7/perceiver-io-1) is pure Python and has no FFI of its own: its
+ * boundary for this path is the Python class API of perceiver/model.py + perceiver/adapter.py
+ * (SURVEY.md §8b).  Each entry point below names the reference code whose arithmetic it
+ * replaces; the drop-in Python classes in perceiver-io-1_b200/perceiver/ bind these through
+ * ctypes.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless stated otherwise; tensors are dense row-major
+ *     fp32 (int64 for token ids / labels, uint8 for boolean masks) unless a stride is given;
+ *   - nothing here allocates device memory: scratch comes from the caller (`ws`, `ws_bytes`),
+ *     saved-for-backward state lives in an opaque caller-owned buffer (`saved`) whose size is
+ *     given by the matching pio_*_saved_bytes();
+ *   - every launch goes to the caller's stream (`cudaStream_t` passed as void*); calls are
+ *     asynchronous, re-entrant, and may come from any host thread (autograd's worker thread);
+ *   - return value: PIO_OK or a PIO_ERR_* code; pio_last_error() gives the text (thread-local).
+ *     No C++ exception crosses this boundary.  There is no CPU fallback anywhere.
+ *   - `mode`: PIO_MODE_FP32 = fp32 FFMA arithmetic end to end (parity mode, rel 1e-4);
+ *             PIO_MODE_BF16 = bf16 tcgen05 tensor-core contractions, fp32 accumulate/residual
+ *             stream (performance mode, rel 1e-2).
+ */
+#ifndef PIO_B200_H
+#define PIO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PIO_OK 0
+#define PIO_ERR_ARG 1
+#define PIO_ERR_CUDA 2
+#define PIO_ERR_WORKSPACE 3
+#define PIO_ERR_UNSUPPORTED 4
+
+#define PIO_MODE_FP32 0
+#define PIO_MODE_BF16 1
+
+typedef void* pio_stream_t; /* cudaStream_t */
+
+const char* pio_last_error(void);
+int pio_version(void);
+/* number of CUDA kernels this library has launched in this process (bench.py's gpu_launches) */
+long long pio_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Input adapters
+ * ---------------------------------------------------------------------------------------- */
+
+/* ImageInputAdapter.forward, adapter.py:99-109: out[b,m,:] = concat(x[b,m,0:c_img], pos[m,0:c_pos]).
+ * x (batch, m, c_img) is the image with its spatial dims flattened; out (batch, m, c_img+c_pos). */
+int pio_image_encode(const float* x, const float* pos_enc, float* out, int64_t batch, int64_t m,
+                     int c_img, int c_pos, pio_stream_t stream);
+
+/* ImageInputAdapter._positions/_position_encodings, adapter.py:53-94, generated on the device:
+ * out (prod(shape), ndim*(2*bands+1)); `shape` is a HOST pointer to ndim ints (ndim <= 4). */
+int pio_fourier_table(float* out, const int* shape, int ndim, int bands, pio_stream_t stream);
+
+/* TextInputAdapter.forward, adapter.py:127-133: out[b,i,:] = emb[ids[b,i],:]*scale + pos[i,:]. */
+int pio_text_embed_fwd(const int64_t* ids, const float* emb, const float* pos, float* out,
+                       int64_t batch, int64_t l, int c, int64_t vocab, float scale, pio_stream_t stream);
+/* its backward: demb (vocab,c) must be zero-filled by the caller (rows are accumulated with
+ * atomics); dpos (l,c) is overwritten with the sum over the batch. */
+int pio_text_embed_bwd(const int64_t* ids, const float* dout, float* demb, float* dpos,
+                       int64_t batch, int64_t l, int c, int64_t vocab, float scale, pio_stream_t stream);
+
+/* TextMasking.forward, model.py:265-293, split at its one data-dependent point (the size of the
+ * randint draw).  Elements are processed in blocks of PIO_MASK_BLOCK.
+ *   select: flags[i] bit0 = selected (label kept), bit1 = replace by [MASK], bit2 = replace by a
+ *           random token; block_counts[j] = number of bit2 elements in block j.
+ *   apply : ids[i] <- mask_token_id / random_ids[rank of i among bit2 elements] ; labels[i] <-
+ *           original id if selected else -100.  In place on ids like the reference. */
+#define PIO_MASK_BLOCK 1024
+int pio_text_mask_select(const int64_t* ids, const uint8_t* pad, const float* r0, const float* r1,
+                         const float* r2, uint8_t* flags, int32_t* block_counts, int64_t n,
+                         int64_t unk_token_id, float mask_p, pio_stream_t stream);
+int pio_text_mask_apply(int64_t* ids, int64_t* labels, const uint8_t* flags, const int32_t* block_counts,
+                        const int64_t* random_ids, int64_t n_random, int64_t n, int64_t mask_token_id,
+                        pio_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Primitives (torch ops the reference delegates to; exported for the parity tests)
+ * ---------------------------------------------------------------------------------------- */
+
+/* nn.LayerNorm (model.py:22,89,90,108), eps 1e-5 in the reference. stats (rows,2) = mean, rstd. */
+int pio_layernorm_fwd(const float* x, const float* w, const float* b, float* y, float* stats,
+                      int64_t rows, int c, float eps, pio_stream_t stream);
+/* dx = LN'(dy) (+ dres if non-null; dx itself may be null when the input needs no gradient);
+ * dw/db overwritten (accumulate=0) or added to (1). */
+int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const float* w,
+                      const float* dres, float* dx, float* dw, float* db, int accumulate,
+                      int64_t rows, int c, void* ws, size_t ws_bytes, pio_stream_t stream);
+size_t pio_layernorm_bwd_ws_bytes(int64_t rows, int c);
+
+/* C[m,n] = sum_k A(m,k) B(n,k) with a fused epilogue — nn.Linear forward / backward
+ * (model.py:23,25; adapter.py:146-149) and the MHA projections (model.py:66-74).
+ *   a_kmajor: A(m,k) = a[m*lda+k] else a[k*lda+m];  b_kmajor: B(n,k) = b[n*ldb+k] else b[k*ldb+n].
+ *   act: 0 none | 1 GELU(erf) (pre-activation stored to aux if non-null) | 2 multiply by GELU'(aux).
+ *   rowsum_a (m) optional: sum_k A(m,k) (bias gradient riding on a weight-gradient GEMM). */
+typedef struct {
+    const float* a;
+    const float* b;
+    float* c;
+    int64_t m, n, k;
+    int64_t lda, ldb, ldc;
+    int a_kmajor, b_kmajor;
+    const float* bias;
+    const float* residual;
+    int64_t ldr;
+    float* aux;
+    int64_t ldaux;
+    int act;
+    int accumulate;
+    float* rowsum_a;
+} pio_gemm_desc;
+int pio_gemm_f32(const pio_gemm_desc* d, void* ws, size_t ws_bytes, pio_stream_t stream);
+size_t pio_gemm_f32_ws_bytes(int64_t m, int64_t n, int64_t k);
+
+/* Attention core of nn.MultiheadAttention as called at model.py:74 (dropout 0):
+ * S = (q dh^-1/2) k^T, padded keys -> -inf, P = softmax(S), O = P v.  Flash-style: P is never
+ * stored; lse (batch,heads,n) = logsumexp of the scaled scores, saved for the backward, which
+ * recomputes P.  Head h is columns [h*dh,(h+1)*dh) of each row; *_bs / *_rs are batch / row
+ * strides in elements (so a packed (rows,3E) qkv buffer is addressed without a copy).
+ * A query whose keys are all padded yields NaN, like the reference. */
+typedef struct {
+    const float* q;
+    const float* k;
+    const float* v;
+    const uint8_t* pad; /* (batch, m) 1 = ignore key; nullable */
+    float* o;
+    float* lse;
+    int64_t q_bs, q_rs, k_bs, k_rs, v_bs, v_rs, o_bs, o_rs;
+    int batch, heads, n, m, dh;
+    float scale;
+} pio_attn_desc;
+int pio_attn_fwd(const pio_attn_desc* d, int mode, pio_stream_t stream);
+
+typedef struct {
+    pio_attn_desc fwd;  /* q,k,v,pad,o(read),lse(read) as in the forward */
+    const float* d_o;   /* same strides as o */
+    float* dq;          /* strides as q */
+    float* dk;          /* strides as k */
+    float* dv;          /* strides as v */
+    float* delta;       /* scratch (batch,heads,n) */
+} pio_attn_bwd_desc;
+int pio_attn_bwd(const pio_attn_bwd_desc* d, int mode, pio_stream_t stream);
+
+/* nn.CrossEntropyLoss (lightning.py:61,184,225-226): mean over targets != ignore_index of
+ * logsumexp(logits) - logits[target].  out3 = {loss, n_valid, loss_sum}; row_lse holds 2*rows floats: the per-row
+ * logsumexp (saved for the backward) followed by per-row losses (scratch). */
+int pio_cross_entropy_fwd(const float* logits, const int64_t* labels, float* out3, float* row_lse,
+                          int64_t rows, int64_t classes, int64_t ld, int64_t ignore_index,
+                          pio_stream_t stream);
+int pio_cross_entropy_bwd(const float* logits, const int64_t* labels, const float* out3,
+                          const float* row_lse, const float* dloss, float* dlogits, int64_t rows,
+                          int64_t classes, int64_t ld, int64_t ignore_index, pio_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused operators (one call per reference module)
+ * ---------------------------------------------------------------------------------------- */
+
+/* Residual(mlp(C)), model.py:20-26,47-56: y = Linear2(GELU(Linear1(LN(x)))) + x.
+ * `residual` = 0 gives the bare module (mlp / CrossAttention / SelfAttention .forward) without
+ * the `+ x` of Residual.forward (model.py:54-56); same flag on the attention operators below. */
+typedef struct {
+    const float *ln_w, *ln_b, *w1, *b1, *w2, *b2;
+} pio_mlp_weights;
+typedef struct {
+    float *ln_w, *ln_b, *w1, *b1, *w2, *b2;
+} pio_mlp_grads;
+size_t pio_mlp_saved_bytes(int64_t rows, int c, int mode);
+size_t pio_mlp_ws_bytes(int64_t rows, int c, int mode);
+int pio_mlp_fwd(const float* x, float* y, const pio_mlp_weights* w, void* saved, int64_t rows, int c,
+                int residual, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+int pio_mlp_bwd(const float* dy, const float* x, float* dx, const pio_mlp_weights* w, const void* saved,
+                const pio_mlp_grads* g, int accumulate, int64_t rows, int c, int residual, int mode,
+                void* ws, size_t ws_bytes, pio_stream_t stream);
+
+/* Attention weights as torch.nn.MultiheadAttention stores them (model.py:66-71): wq (E,E),
+ * wk / wv (E,C_kv); they may alias one packed (3E,E) in_proj_weight.  Biases likewise. */
+typedef struct {
+    const float *ln_w, *ln_b;       /* q_norm (cross) or norm (self) */
+    const float *wq, *wk, *wv;
+    const float *bq, *bk, *bv;
+    const float *wo, *bo;
+    const float *kv_ln_w, *kv_ln_b; /* kv_norm (cross-attention only) */
+} pio_attn_weights;
+typedef struct {
+    float *ln_w, *ln_b;
+    float *wq, *wk, *wv;
+    float *bq, *bk, *bv;
+    float *wo, *bo;
+    float *kv_ln_w, *kv_ln_b;
+} pio_attn_grads;
+
+/* The key/value side of CrossAttention, model.py:90,98 + the k/v in-projection of :74:
+ * kv[b,j,0:E] = LN_kv(x_kv[b,j]) Wk^T + bk,  kv[b,j,E:2E] = ... Wv^T + bv.
+ * Computed once per distinct layer and shared by the repeats of layer_n (model.py:186-187). */
+size_t pio_kv_project_saved_bytes(int64_t rows, int c_kv, int e, int mode);
+size_t pio_kv_project_ws_bytes(int64_t rows, int c_kv, int e, int mode);
+int pio_kv_project_fwd(const float* x_kv, float* kv, const pio_attn_weights* w, void* saved,
+                       int64_t rows, int c_kv, int e, int mode, void* ws, size_t ws_bytes,
+                       pio_stream_t stream);
+/* dx_kv may be null (input needs no gradient, e.g. images). */
+int pio_kv_project_bwd(const float* dkv, const float* x_kv, float* dx_kv, const pio_attn_weights* w,
+                       const void* saved, const pio_attn_grads* g, int accumulate, int64_t rows,
+                       int c_kv, int e, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+
+/* The query side of Residual(CrossAttention), model.py:77-99 + :54-56:
+ * y = out_proj(attn(LN_q(x_q) Wq^T + bq, K, V, pad)) + x_q  with kv from pio_kv_project_fwd. */
+size_t pio_cross_attend_saved_bytes(int batch, int n, int m, int e, int heads, int mode);
+size_t pio_cross_attend_ws_bytes(int batch, int n, int m, int e, int heads, int mode);
+int pio_cross_attend_fwd(const float* x_q, const float* kv, const uint8_t* pad, float* y,
+                         const pio_attn_weights* w, void* saved, int batch, int n, int m, int e,
+                         int heads, int residual, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+int pio_cross_attend_bwd(const float* dy, const float* x_q, const float* kv, const uint8_t* pad,
+                         float* dx_q, float* dkv, const pio_attn_weights* w, const void* saved,
+                         const pio_attn_grads* g, int accumulate, int batch, int n, int m, int e,
+                         int heads, int residual, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+
+/* Residual(SelfAttention), model.py:102-116 + :54-56, one layer: y = out_proj(attn(qkv(LN(x)))) + x. */
+size_t pio_self_attn_saved_bytes(int batch, int n, int c, int heads, int mode);
+size_t pio_self_attn_ws_bytes(int batch, int n, int c, int heads, int mode);
+int pio_self_attn_fwd(const float* x, float* y, const pio_attn_weights* w, void* saved, int batch, int n,
+                      int c, int heads, int residual, int mode, void* ws, size_t ws_bytes,
+                      pio_stream_t stream);
+int pio_self_attn_bwd(const float* dy, const float* x, float* dx, const pio_attn_weights* w,
+                      const void* saved, const pio_attn_grads* g, int accumulate, int batch, int n, int c,
+                      int heads, int residual, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+
+/* self_attention_block, model.py:36-44,102-116: `layers` x [Residual(SelfAttention) ->
+ * Residual(mlp)] applied to x (batch,n,c).  `attn`/`mlp` are arrays of `layers` structs. */
+size_t pio_latent_block_saved_bytes(int layers, int batch, int n, int c, int heads, int mode);
+size_t pio_latent_block_ws_bytes(int layers, int batch, int n, int c, int heads, int mode);
+int pio_latent_block_fwd(const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp,
+                         void* saved, int layers, int batch, int n, int c, int heads, int mode,
+                         void* ws, size_t ws_bytes, pio_stream_t stream);
+int pio_latent_block_bwd(const float* dy, const float* x, float* dx, const pio_attn_weights* attn,
+                         const pio_mlp_weights* mlp, const void* saved, const pio_attn_grads* attn_g,
+                         const pio_mlp_grads* mlp_g, int accumulate, int layers, int batch, int n, int c,
+                         int heads, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+
+/* nn.Linear of Classification/TextOutputAdapter, adapter.py:146-149: y = x W^T + b. */
+size_t pio_linear_ws_bytes(int64_t rows, int c_in, int64_t c_out, int mode);
+int pio_linear_fwd(const float* x, const float* w, const float* b, float* y, int64_t rows, int c_in,
+                   int64_t c_out, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+/* dx nullable. dw/db overwritten or accumulated. */
+int pio_linear_bwd(const float* dy, const float* x, const float* w, float* dx, float* dw, float* db,
+                   int accumulate, int64_t rows, int c_in, int64_t c_out, int mode, void* ws,
+                   size_t ws_bytes, pio_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PIO_B200_H */

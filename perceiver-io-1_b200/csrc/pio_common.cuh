@@ -1,0 +1,95 @@
+// Shared helpers for the pio_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <math.h>
+#include <algorithm>
+
+#include "../../include/pio_b200.h"
+
+namespace pio {
+
+// thread-local last error text, readable through pio_last_error()
+void set_error(const char* fmt, ...);
+
+#define PIO_CHECK_ARG(cond, ...)                    \
+    do {                                            \
+        if (!(cond)) {                              \
+            pio::set_error(__VA_ARGS__);            \
+            return PIO_ERR_ARG;                     \
+        }                                           \
+    } while (0)
+
+#define PIO_CUDA(call)                                                                   \
+    do {                                                                                 \
+        cudaError_t _e = (call);                                                         \
+        if (_e != cudaSuccess) {                                                         \
+            pio::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e),      \
+                           __FILE__, __LINE__);                                          \
+            return PIO_ERR_CUDA;                                                         \
+        }                                                                                \
+    } while (0)
+
+// every kernel launch is followed by this: counts the launch (pio_launch_count) and surfaces
+// launch-configuration errors
+void count_launch();
+#define PIO_LAUNCH_CHECK()           \
+    do {                             \
+        pio::count_launch();         \
+        PIO_CUDA(cudaGetLastError()); \
+    } while (0)
+
+#define PIO_TRY(expr)                  \
+    do {                               \
+        int _s = (expr);               \
+        if (_s != PIO_OK) return _s;   \
+    } while (0)
+
+static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+int num_sms();
+
+// out1[i] (+)= sum_s part[s*stride+i] (i<n1); out2[i] (+)= sum_s part[s*stride+n1+i] (i<n2)
+int reduce_partials(const float* part, int splits, int64_t stride, float* out1, int64_t n1, float* out2,
+                    int64_t n2, int accumulate, cudaStream_t st);
+
+// bump allocator over a caller-provided workspace
+struct Workspace {
+    char* base;
+    size_t size;
+    size_t off;
+    Workspace(void* p, size_t n) : base((char*)p), size(n), off(0) {}
+    void* take(size_t bytes) {
+        size_t o = align_up(off, 256);
+        if (o + bytes > size || base == nullptr) return nullptr;
+        off = o + bytes;
+        return base + o;
+    }
+    float* takef(size_t n) { return (float*)take(n * sizeof(float)); }
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+__device__ __forceinline__ float gelu_erf(float x) {
+    return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+    // d/dx [x Phi(x)] = Phi(x) + x phi(x)
+    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+    const float pdf = 0.39894228040143267794f * expf(-0.5f * x * x);
+    return cdf + x * pdf;
+}
+
+}  // namespace pio

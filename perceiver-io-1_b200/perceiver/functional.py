@@ -1,0 +1,477 @@
+"""torch.autograd glue over the C ABI: one Function per fused operator of libpio_b200.so.
+
+Everything numerical happens in the CUDA kernels; torch provides storage, streams and the
+autograd graph.  Saved-for-backward state is an opaque byte buffer whose layout only the
+library knows (pio_*_saved_bytes).
+"""
+import ctypes
+from ctypes import byref
+
+import torch
+from torch.autograd.function import once_differentiable
+
+from . import _native as N
+
+_MODE = {"mode": N.MODE_FP32}
+
+
+def set_compute_mode(mode):
+    """'fp32' (FFMA kernels, rel 1e-4 parity mode) or 'bf16' (tcgen05 tensor cores, rel 1e-2)."""
+    m = {"fp32": N.MODE_FP32, "bf16": N.MODE_BF16, N.MODE_FP32: N.MODE_FP32, N.MODE_BF16: N.MODE_BF16}.get(mode)
+    if m is None:
+        raise ValueError(f"unknown compute mode {mode!r}")
+    _MODE["mode"] = m
+
+
+def get_compute_mode():
+    return _MODE["mode"]
+
+
+def _c(t, dtype=torch.float32):
+    """contiguous CUDA tensor of the expected dtype (no silent device moves)."""
+    N.require_cuda(t)
+    if t.dtype != dtype:
+        raise TypeError(f"expected {dtype}, got {t.dtype}")
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _saved(nbytes, device):
+    return torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+
+
+def _mha_ptrs(w_packed, w_q, w_k, w_v, bias, e):
+    """Device addresses of (wq, wk, wv, bq, bk, bv) for packed (3E,E) or split storage."""
+    if w_packed is not None:
+        base = w_packed.data_ptr()
+        wq, wk, wv = base, base + 4 * e * e, base + 8 * e * e
+    else:
+        wq = w_q.data_ptr() if w_q is not None else None
+        wk = w_k.data_ptr() if w_k is not None else None
+        wv = w_v.data_ptr() if w_v is not None else None
+    b = bias.data_ptr()
+    return wq, wk, wv, b, b + 4 * e, b + 8 * e
+
+
+# ------------------------------------------------------------------------------------------
+# adapters
+# ------------------------------------------------------------------------------------------
+
+class ImageEncodeFn(torch.autograd.Function):
+    """ImageInputAdapter.forward (reference adapter.py:99-109)."""
+
+    @staticmethod
+    def forward(ctx, x, pos_enc):
+        x = _c(x)
+        pos_enc = _c(pos_enc)
+        b = x.shape[0]
+        c_img = x.shape[-1]
+        m, c_pos = pos_enc.shape
+        out = torch.empty(b, m, c_img + c_pos, dtype=torch.float32, device=x.device)
+        N.check(N.lib().pio_image_encode(x.data_ptr(), pos_enc.data_ptr(), out.data_ptr(), b, m, c_img, c_pos,
+                                         N.stream_ptr(x.device)), "pio_image_encode")
+        ctx.x_shape = x.shape
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dout):
+        dx = dout[..., :ctx.x_shape[-1]].reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        return dx, None
+
+
+class TextEmbedFn(torch.autograd.Function):
+    """TextInputAdapter.forward (reference adapter.py:127-133)."""
+
+    @staticmethod
+    def forward(ctx, ids, emb, pos, scale):
+        ids = _c(ids, torch.int64)
+        emb = _c(emb)
+        pos = _c(pos)
+        b, l = ids.shape
+        vocab, c = emb.shape
+        out = torch.empty(b, l, c, dtype=torch.float32, device=emb.device)
+        N.check(N.lib().pio_text_embed_fwd(ids.data_ptr(), emb.data_ptr(), pos.data_ptr(), out.data_ptr(), b, l, c, vocab,
+                                           float(scale), N.stream_ptr(emb.device)), "pio_text_embed_fwd")
+        ctx.save_for_backward(ids)
+        ctx.meta = (vocab, c, pos.shape[0], float(scale))
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dout):
+        (ids,) = ctx.saved_tensors
+        vocab, c, max_len, scale = ctx.meta
+        dout = _c(dout)
+        b, l = ids.shape
+        demb = torch.zeros(vocab, c, dtype=torch.float32, device=dout.device) if ctx.needs_input_grad[1] else None
+        dpos = torch.zeros(max_len, c, dtype=torch.float32, device=dout.device) if ctx.needs_input_grad[2] else None
+        N.check(N.lib().pio_text_embed_bwd(ids.data_ptr(), dout.data_ptr(), N.ptr(demb), N.ptr(dpos), b, l, c, vocab, scale,
+                                           N.stream_ptr(dout.device)), "pio_text_embed_bwd")
+        return None, demb, dpos, None
+
+
+def text_mask(ids, pad_mask, vocab_size, unk_token_id, mask_token_id, num_special_tokens, mask_p, generator=None):
+    """TextMasking.forward (reference model.py:265-293), in place on ``ids``; returns labels.
+
+    The four RNG draws stay torch calls in the reference's order (three float32 uniforms, then a
+    randint whose length is the number of random-replacement positions), so the same device and
+    generator state give bit-identical results; the select / scatter logic is two kernels."""
+    N.require_cuda(ids, pad_mask)
+    if ids.dtype != torch.int64 or not ids.is_contiguous():
+        raise TypeError("ids must be a contiguous int64 tensor (masked in place)")
+    dev = ids.device
+    n = ids.numel()
+    pad = None
+    if pad_mask is not None:
+        if pad_mask.dtype != torch.bool:
+            raise TypeError("pad_mask must be a bool tensor")
+        pad = pad_mask.expand_as(ids).contiguous()
+    r0 = torch.rand(ids.shape, dtype=torch.float, device=dev, generator=generator)
+    r1 = torch.rand(ids.shape, dtype=torch.float, device=dev, generator=generator)
+    r2 = torch.rand(ids.shape, dtype=torch.float, device=dev, generator=generator)
+    nblk = max(1, (n + 1023) // 1024)
+    flags = torch.empty(max(n, 1), dtype=torch.uint8, device=dev)
+    counts = torch.zeros(nblk, dtype=torch.int32, device=dev)
+    st = N.stream_ptr(dev)
+    N.check(N.lib().pio_text_mask_select(ids.data_ptr(), N.ptr(pad), r0.data_ptr(), r1.data_ptr(), r2.data_ptr(),
+                                         flags.data_ptr(), counts.data_ptr(), n, int(unk_token_id), float(mask_p), st),
+            "pio_text_mask_select")
+    n_random = int(counts.sum().item())  # the reference's own host sync: is_selected_2.sum() (model.py:288)
+    rnd = torch.randint(num_special_tokens, vocab_size, size=(n_random,), device=dev, generator=generator)
+    labels = torch.empty_like(ids)
+    N.check(N.lib().pio_text_mask_apply(ids.data_ptr(), labels.data_ptr(), flags.data_ptr(), counts.data_ptr(),
+                                        rnd.data_ptr() if n_random else None, n_random, n, int(mask_token_id), st),
+            "pio_text_mask_apply")
+    return labels
+
+
+# ------------------------------------------------------------------------------------------
+# fused operators
+# ------------------------------------------------------------------------------------------
+
+class MlpFn(torch.autograd.Function):
+    """Residual(mlp(C)) (reference model.py:20-26,47-56)."""
+
+    @staticmethod
+    def forward(ctx, x, ln_w, ln_b, w1, b1, w2, b2, residual):
+        x = _c(x)
+        params = [_c(p) for p in (ln_w, ln_b, w1, b1, w2, b2)]
+        c = x.shape[-1]
+        rows = x.numel() // c
+        mode = get_compute_mode()
+        L = N.lib()
+        saved = _saved(L.pio_mlp_saved_bytes(rows, c, mode), x.device)
+        ws = N.workspace(L.pio_mlp_ws_bytes(rows, c, mode), x.device)
+        y = torch.empty_like(x)
+        w = N.mlp_struct(**dict(zip(N.MlpWeights._names, params)))
+        N.check(L.pio_mlp_fwd(x.data_ptr(), y.data_ptr(), byref(w), saved.data_ptr(), rows, c, int(residual), mode,
+                              ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_mlp_fwd")
+        ctx.save_for_backward(x, *params)
+        ctx.saved_buf = saved
+        ctx.meta = (rows, c, int(residual), mode)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x, *params = ctx.saved_tensors
+        rows, c, residual, mode = ctx.meta
+        dy = _c(dy)
+        L = N.lib()
+        grads = [torch.empty_like(p) for p in params]
+        dx = torch.empty_like(x)
+        ws = N.workspace(L.pio_mlp_ws_bytes(rows, c, mode), x.device)
+        w = N.mlp_struct(**dict(zip(N.MlpWeights._names, params)))
+        g = N.mlp_struct(**dict(zip(N.MlpWeights._names, grads)))
+        N.check(L.pio_mlp_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g), 0,
+                              rows, c, residual, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_mlp_bwd")
+        ctx.saved_buf = None
+        return (dx, *grads, None)
+
+
+class KVProjectFn(torch.autograd.Function):
+    """kv_norm + key/value in-projection of CrossAttention (reference model.py:90,98 and the k/v
+    half of nn.MultiheadAttention's in-projection, :74).  Output kv (B, M, 2E) = [K | V]."""
+
+    @staticmethod
+    def forward(ctx, x_kv, ln_w, ln_b, bias, w_packed, w_k, w_v, e):
+        x_kv = _c(x_kv)
+        ln_w, ln_b, bias = _c(ln_w), _c(ln_b), _c(bias)
+        w_packed = _c(w_packed) if w_packed is not None else None
+        w_k = _c(w_k) if w_k is not None else None
+        w_v = _c(w_v) if w_v is not None else None
+        b, m, ckv = x_kv.shape
+        rows = b * m
+        mode = get_compute_mode()
+        L = N.lib()
+        _, wk, wv, _, bk, bv = _mha_ptrs(w_packed, None, w_k, w_v, bias, e)
+        w = N.attn_struct(wk=wk, wv=wv, bk=bk, bv=bv, kv_ln_w=ln_w, kv_ln_b=ln_b)
+        saved = _saved(L.pio_kv_project_saved_bytes(rows, ckv, e, mode), x_kv.device)
+        ws = N.workspace(L.pio_kv_project_ws_bytes(rows, ckv, e, mode), x_kv.device)
+        kv = torch.empty(b, m, 2 * e, dtype=torch.float32, device=x_kv.device)
+        N.check(L.pio_kv_project_fwd(x_kv.data_ptr(), kv.data_ptr(), byref(w), saved.data_ptr(), rows, ckv, e, mode,
+                                     ws.data_ptr(), ws.numel(), N.stream_ptr(x_kv.device)), "pio_kv_project_fwd")
+        ctx.save_for_backward(x_kv, ln_w, ln_b, bias, w_packed, w_k, w_v)
+        ctx.saved_buf = saved
+        ctx.meta = (rows, ckv, e, mode)
+        return kv
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dkv):
+        x_kv, ln_w, ln_b, bias, w_packed, w_k, w_v = ctx.saved_tensors
+        rows, ckv, e, mode = ctx.meta
+        dkv = _c(dkv)
+        L = N.lib()
+        dev = x_kv.device
+        dln_w, dln_b = torch.empty_like(ln_w), torch.empty_like(ln_b)
+        dbias = torch.zeros_like(bias)
+        dwp = torch.zeros_like(w_packed) if w_packed is not None else None
+        dwk = torch.empty_like(w_k) if w_k is not None else None
+        dwv = torch.empty_like(w_v) if w_v is not None else None
+        dx = torch.empty_like(x_kv) if ctx.needs_input_grad[0] else None
+        _, wk, wv, _, bk, bv = _mha_ptrs(w_packed, None, w_k, w_v, bias, e)
+        _, gwk, gwv, _, gbk, gbv = _mha_ptrs(dwp, None, dwk, dwv, dbias, e)
+        w = N.attn_struct(wk=wk, wv=wv, bk=bk, bv=bv, kv_ln_w=ln_w, kv_ln_b=ln_b)
+        g = N.attn_struct(wk=gwk, wv=gwv, bk=gbk, bv=gbv, kv_ln_w=dln_w, kv_ln_b=dln_b)
+        ws = N.workspace(L.pio_kv_project_ws_bytes(rows, ckv, e, mode), dev)
+        N.check(L.pio_kv_project_bwd(dkv.data_ptr(), x_kv.data_ptr(), N.ptr(dx), byref(w), ctx.saved_buf.data_ptr(),
+                                     byref(g), 0, rows, ckv, e, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
+                "pio_kv_project_bwd")
+        ctx.saved_buf = None
+        return dx, dln_w, dln_b, dbias, dwp, dwk, dwv, None
+
+
+class CrossAttendFn(torch.autograd.Function):
+    """Query side of Residual(CrossAttention) (reference model.py:77-99, :54-56): q_norm,
+    q in-projection, attention over the projected kv, out-projection, + x_q."""
+
+    @staticmethod
+    def forward(ctx, x_q, kv, pad, ln_w, ln_b, bias, w_packed, w_q, wo, bo, heads, residual):
+        x_q, kv = _c(x_q), _c(kv)
+        ln_w, ln_b, bias, wo, bo = _c(ln_w), _c(ln_b), _c(bias), _c(wo), _c(bo)
+        w_packed = _c(w_packed) if w_packed is not None else None
+        w_q = _c(w_q) if w_q is not None else None
+        if pad is not None:
+            pad = _c(pad, torch.bool)
+        b, n, e = x_q.shape
+        m = kv.shape[1]
+        mode = get_compute_mode()
+        L = N.lib()
+        wq, _, _, bq, _, _ = _mha_ptrs(w_packed, w_q, None, None, bias, e)
+        w = N.attn_struct(ln_w=ln_w, ln_b=ln_b, wq=wq, bq=bq, wo=wo, bo=bo)
+        saved = _saved(L.pio_cross_attend_saved_bytes(b, n, m, e, heads, mode), x_q.device)
+        ws = N.workspace(L.pio_cross_attend_ws_bytes(b, n, m, e, heads, mode), x_q.device)
+        y = torch.empty_like(x_q)
+        N.check(L.pio_cross_attend_fwd(x_q.data_ptr(), kv.data_ptr(), N.ptr(pad), y.data_ptr(), byref(w), saved.data_ptr(),
+                                       b, n, m, e, heads, int(residual), mode, ws.data_ptr(), ws.numel(),
+                                       N.stream_ptr(x_q.device)), "pio_cross_attend_fwd")
+        ctx.save_for_backward(x_q, kv, pad, ln_w, ln_b, bias, w_packed, w_q, wo, bo)
+        ctx.saved_buf = saved
+        ctx.meta = (b, n, m, e, heads, int(residual), mode)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x_q, kv, pad, ln_w, ln_b, bias, w_packed, w_q, wo, bo = ctx.saved_tensors
+        b, n, m, e, heads, residual, mode = ctx.meta
+        dy = _c(dy)
+        L = N.lib()
+        dev = x_q.device
+        dln_w, dln_b = torch.empty_like(ln_w), torch.empty_like(ln_b)
+        dbias = torch.zeros_like(bias)
+        dwp = torch.zeros_like(w_packed) if w_packed is not None else None
+        dwq = torch.empty_like(w_q) if w_q is not None else None
+        dwo, dbo = torch.empty_like(wo), torch.empty_like(bo)
+        dx = torch.empty_like(x_q)
+        dkv = torch.empty_like(kv)
+        wq, _, _, bq, _, _ = _mha_ptrs(w_packed, w_q, None, None, bias, e)
+        gwq, _, _, gbq, _, _ = _mha_ptrs(dwp, dwq, None, None, dbias, e)
+        w = N.attn_struct(ln_w=ln_w, ln_b=ln_b, wq=wq, bq=bq, wo=wo, bo=bo)
+        g = N.attn_struct(ln_w=dln_w, ln_b=dln_b, wq=gwq, bq=gbq, wo=dwo, bo=dbo)
+        ws = N.workspace(L.pio_cross_attend_ws_bytes(b, n, m, e, heads, mode), dev)
+        N.check(L.pio_cross_attend_bwd(dy.data_ptr(), x_q.data_ptr(), kv.data_ptr(), N.ptr(pad), dx.data_ptr(),
+                                       dkv.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g), 0, b, n, m, e, heads,
+                                       residual, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
+                "pio_cross_attend_bwd")
+        ctx.saved_buf = None
+        return dx, dkv, None, dln_w, dln_b, dbias, dwp, dwq, dwo, dbo, None, None
+
+
+_SA_NAMES = ("ln_w", "ln_b", "in_w", "in_b", "wo", "bo")
+_LAYER_PARAMS = 12  # 6 attention + 6 mlp tensors per latent layer
+
+
+def _sa_struct(ln_w, ln_b, in_w, in_b, wo, bo, e):
+    wq, wk, wv, bq, bk, bv = _mha_ptrs(in_w, None, None, None, in_b, e)
+    return dict(ln_w=ln_w, ln_b=ln_b, wq=wq, wk=wk, wv=wv, bq=bq, bk=bk, bv=bv, wo=wo, bo=bo)
+
+
+class SelfAttnFn(torch.autograd.Function):
+    """Residual(SelfAttention) (reference model.py:102-116, :54-56), one layer."""
+
+    @staticmethod
+    def forward(ctx, x, ln_w, ln_b, in_w, in_b, wo, bo, heads, residual):
+        x = _c(x)
+        params = [_c(p) for p in (ln_w, ln_b, in_w, in_b, wo, bo)]
+        b, n, c = x.shape
+        mode = get_compute_mode()
+        L = N.lib()
+        w = N.attn_struct(**_sa_struct(*params, c))
+        saved = _saved(L.pio_self_attn_saved_bytes(b, n, c, heads, mode), x.device)
+        ws = N.workspace(L.pio_self_attn_ws_bytes(b, n, c, heads, mode), x.device)
+        y = torch.empty_like(x)
+        N.check(L.pio_self_attn_fwd(x.data_ptr(), y.data_ptr(), byref(w), saved.data_ptr(), b, n, c, heads, int(residual),
+                                    mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_self_attn_fwd")
+        ctx.save_for_backward(x, *params)
+        ctx.saved_buf = saved
+        ctx.meta = (b, n, c, heads, int(residual), mode)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x, *params = ctx.saved_tensors
+        b, n, c, heads, residual, mode = ctx.meta
+        dy = _c(dy)
+        L = N.lib()
+        grads = [torch.empty_like(p) for p in params]
+        dx = torch.empty_like(x)
+        w = N.attn_struct(**_sa_struct(*params, c))
+        g = N.attn_struct(**_sa_struct(*grads, c))
+        ws = N.workspace(L.pio_self_attn_ws_bytes(b, n, c, heads, mode), x.device)
+        N.check(L.pio_self_attn_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g),
+                                    0, b, n, c, heads, residual, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)),
+                "pio_self_attn_bwd")
+        ctx.saved_buf = None
+        return (dx, *grads, None, None)
+
+
+class LatentBlockFn(torch.autograd.Function):
+    """self_attention_block (reference model.py:36-44): S x [Residual(SelfAttention),
+    Residual(mlp)] in one call.  ``params`` = 12 tensors per layer: ln_w, ln_b, in_proj_weight,
+    in_proj_bias, out_proj.weight, out_proj.bias, then the mlp's ln_w, ln_b, w1, b1, w2, b2."""
+
+    @staticmethod
+    def _structs(params, layers, c):
+        attn = (N.AttnWeights * layers)()
+        mlp = (N.MlpWeights * layers)()
+        for s in range(layers):
+            p = params[s * _LAYER_PARAMS:(s + 1) * _LAYER_PARAMS]
+            for k, v in _sa_struct(*p[:6], c).items():
+                setattr(attn[s], k, v if isinstance(v, int) or v is None else v.data_ptr())
+            for k, v in zip(N.MlpWeights._names, p[6:]):
+                setattr(mlp[s], k, v.data_ptr())
+        return attn, mlp
+
+    @staticmethod
+    def forward(ctx, x, heads, *params):
+        x = _c(x)
+        params = [_c(p) for p in params]
+        layers = len(params) // _LAYER_PARAMS
+        assert layers * _LAYER_PARAMS == len(params) and layers >= 1
+        b, n, c = x.shape
+        mode = get_compute_mode()
+        L = N.lib()
+        attn, mlp = LatentBlockFn._structs(params, layers, c)
+        saved = _saved(L.pio_latent_block_saved_bytes(layers, b, n, c, heads, mode), x.device)
+        ws = N.workspace(L.pio_latent_block_ws_bytes(layers, b, n, c, heads, mode), x.device)
+        y = torch.empty_like(x)
+        N.check(L.pio_latent_block_fwd(x.data_ptr(), y.data_ptr(), attn, mlp, saved.data_ptr(), layers, b, n, c, heads, mode,
+                                       ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_latent_block_fwd")
+        ctx.save_for_backward(x, *params)
+        ctx.saved_buf = saved
+        ctx.meta = (layers, b, n, c, heads, mode)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x, *params = ctx.saved_tensors
+        layers, b, n, c, heads, mode = ctx.meta
+        dy = _c(dy)
+        L = N.lib()
+        grads = [torch.empty_like(p) for p in params]
+        dx = torch.empty_like(x)
+        attn, mlp = LatentBlockFn._structs(params, layers, c)
+        attn_g, mlp_g = LatentBlockFn._structs(grads, layers, c)
+        ws = N.workspace(L.pio_latent_block_ws_bytes(layers, b, n, c, heads, mode), x.device)
+        N.check(L.pio_latent_block_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), attn, mlp, ctx.saved_buf.data_ptr(), attn_g,
+                                       mlp_g, 0, layers, b, n, c, heads, mode, ws.data_ptr(), ws.numel(),
+                                       N.stream_ptr(x.device)), "pio_latent_block_bwd")
+        ctx.saved_buf = None
+        return (dx, None, *grads)
+
+
+class LinearFn(torch.autograd.Function):
+    """nn.Linear of the output adapters (reference adapter.py:146-149)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        x, w, b = _c(x), _c(w), _c(b)
+        c_out, c_in = w.shape
+        rows = x.numel() // c_in
+        mode = get_compute_mode()
+        L = N.lib()
+        ws = N.workspace(L.pio_linear_ws_bytes(rows, c_in, c_out, mode), x.device)
+        y = torch.empty(*x.shape[:-1], c_out, dtype=torch.float32, device=x.device)
+        N.check(L.pio_linear_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), rows, c_in, c_out, mode,
+                                 ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_linear_fwd")
+        ctx.save_for_backward(x, w)
+        ctx.meta = (rows, c_in, c_out, mode)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        rows, c_in, c_out, mode = ctx.meta
+        dy = _c(dy)
+        L = N.lib()
+        dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        dw = torch.empty_like(w)
+        db = torch.empty(c_out, dtype=torch.float32, device=x.device)
+        ws = N.workspace(L.pio_linear_ws_bytes(rows, c_in, c_out, mode), x.device)
+        N.check(L.pio_linear_bwd(dy.data_ptr(), x.data_ptr(), w.data_ptr(), N.ptr(dx), dw.data_ptr(), db.data_ptr(), 0, rows,
+                                 c_in, c_out, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_linear_bwd")
+        return dx, dw, db
+
+
+class CrossEntropyFn(torch.autograd.Function):
+    """nn.CrossEntropyLoss(ignore_index=-100), mean reduction (reference lightning.py:61,184,
+    225-226).  logits (..., classes) with the class dim LAST (no 'b m c -> b c m' transpose)."""
+
+    @staticmethod
+    def forward(ctx, logits, labels, ignore_index):
+        logits = _c(logits)
+        labels = _c(labels, torch.int64)
+        classes = logits.shape[-1]
+        rows = logits.numel() // classes
+        if labels.numel() != rows:
+            raise ValueError(f"labels shape {tuple(labels.shape)} does not match logits {tuple(logits.shape)}")
+        dev = logits.device
+        out3 = torch.empty(3, dtype=torch.float32, device=dev)
+        row_lse = torch.empty(2 * max(rows, 1), dtype=torch.float32, device=dev)
+        N.check(N.lib().pio_cross_entropy_fwd(logits.data_ptr(), labels.data_ptr(), out3.data_ptr(), row_lse.data_ptr(), rows,
+                                              classes, classes, int(ignore_index), N.stream_ptr(dev)),
+                "pio_cross_entropy_fwd")
+        ctx.save_for_backward(logits, labels, out3, row_lse)
+        ctx.meta = (rows, classes, int(ignore_index))
+        return out3[0].clone()
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dloss):
+        logits, labels, out3, row_lse = ctx.saved_tensors
+        rows, classes, ignore = ctx.meta
+        dloss = dloss.to(torch.float32).reshape(1).contiguous()
+        dlogits = torch.empty_like(logits)
+        N.check(N.lib().pio_cross_entropy_bwd(logits.data_ptr(), labels.data_ptr(), out3.data_ptr(), row_lse.data_ptr(),
+                                              dloss.data_ptr(), dlogits.data_ptr(), rows, classes, classes, ignore,
+                                              N.stream_ptr(logits.device)), "pio_cross_entropy_bwd")
+        return dlogits, None, None
+
+
+def cross_entropy(logits, labels, ignore_index=-100):
+    return CrossEntropyFn.apply(logits, labels, ignore_index)

@@ -1,0 +1,272 @@
+"""Perceiver IO encoder / decoder — drop-in for the reference's perceiver/model.py.
+
+Same class names, constructor signatures, forward conventions, exceptions and state_dict keys;
+every forward runs the fused sm_100a operators of libpio_b200.so (functional.py).  Differences
+that are deliberate and documented in DESIGN.md:
+  * the key/value projection of the shared ``layer_n`` is computed once per forward and reused
+    by its (num_layers-1) applications (same weights, same input — reference model.py:186-187);
+  * ``PerceiverMLM.forward`` uses the wiring the reference evidently intends (its own raises a
+    TypeError) and only decodes the ``l`` queries it returns;
+  * dropout > 0 is only supported in eval mode (identity) for now; ``attn_mask`` is rejected
+    (no caller of the reference ever passes one).
+"""
+from typing import Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import functional as F
+from .adapter import InputAdapter, OutputAdapter
+from .layers import LayerNorm, Linear, MultiheadAttentionParams
+from .tokenizer import MASK_TOKEN, SPECIAL_TOKENS, UNK_TOKEN
+from .utils import Sequential
+
+
+def _no_dropout(module: nn.Module, p: float):
+    if p > 0.0 and module.training:
+        raise NotImplementedError('dropout > 0 in training mode is not implemented by the B200 kernels yet')
+
+
+def _no_attn_mask(attn_mask):
+    if attn_mask is not None:
+        raise NotImplementedError('attn_mask is not supported (no caller of the reference passes one)')
+
+
+class MLP(Sequential):
+    """LN -> Linear -> GELU(erf) -> Linear with the reference's child indices 0,1,(2),3."""
+
+    def __init__(self, num_channels: int):
+        super().__init__(LayerNorm(num_channels), Linear(num_channels, num_channels), nn.GELU(),
+                         Linear(num_channels, num_channels))
+
+    def _params(self):
+        return (self[0].weight, self[0].bias, self[1].weight, self[1].bias, self[3].weight, self[3].bias)
+
+    def forward(self, x, residual: bool = False):
+        return F.MlpFn.apply(x, *self._params(), residual)
+
+
+def mlp(num_channels: int):
+    return MLP(num_channels)
+
+
+class MultiHeadAttention(nn.Module):
+    def __init__(self, num_q_channels: int, num_kv_channels: int, num_heads: int, dropout: float):
+        super().__init__()
+        self.attention = MultiheadAttentionParams(embed_dim=num_q_channels, num_heads=num_heads,
+                                                  kdim=num_kv_channels, vdim=num_kv_channels, dropout=dropout)
+
+
+class CrossAttention(nn.Module):
+    def __init__(self, num_q_channels: int, num_kv_channels: int, num_heads: int, dropout: float):
+        super().__init__()
+        self.q_norm = LayerNorm(num_q_channels)
+        self.kv_norm = LayerNorm(num_kv_channels)
+        self.attention = MultiHeadAttention(num_q_channels=num_q_channels, num_kv_channels=num_kv_channels,
+                                            num_heads=num_heads, dropout=dropout)
+        self.dropout_p = dropout
+
+    def project_kv(self, x_kv):
+        """kv_norm + K/V in-projection -> (B, M, 2E); reusable across applications of this layer."""
+        a = self.attention.attention
+        w_packed, _, w_k, w_v = a.packed()
+        return F.KVProjectFn.apply(x_kv, self.kv_norm.weight, self.kv_norm.bias, a.in_proj_bias, w_packed, w_k, w_v,
+                                   a.embed_dim)
+
+    def forward(self, x_q, x_kv, pad_mask=None, attn_mask=None, kv=None, residual: bool = False):
+        _no_attn_mask(attn_mask)
+        _no_dropout(self, self.dropout_p)
+        a = self.attention.attention
+        if kv is None:
+            kv = self.project_kv(x_kv)
+        w_packed, w_q, _, _ = a.packed()
+        return F.CrossAttendFn.apply(x_q, kv, pad_mask, self.q_norm.weight, self.q_norm.bias, a.in_proj_bias, w_packed,
+                                     w_q, a.out_proj.weight, a.out_proj.bias, a.num_heads, residual)
+
+
+class SelfAttention(nn.Module):
+    def __init__(self, num_channels: int, num_heads: int, dropout: float):
+        super().__init__()
+        self.norm = LayerNorm(num_channels)
+        self.attention = MultiHeadAttention(num_q_channels=num_channels, num_kv_channels=num_channels,
+                                            num_heads=num_heads, dropout=dropout)
+        self.dropout_p = dropout
+
+    def _params(self):
+        a = self.attention.attention
+        return (self.norm.weight, self.norm.bias, a.in_proj_weight, a.in_proj_bias, a.out_proj.weight, a.out_proj.bias)
+
+    def forward(self, x, pad_mask=None, attn_mask=None, residual: bool = False):
+        _no_attn_mask(attn_mask)
+        _no_dropout(self, self.dropout_p)
+        if pad_mask is not None:
+            raise NotImplementedError('SelfAttention with a pad mask is never reached in the reference model')
+        return F.SelfAttnFn.apply(x, *self._params(), self.attention.attention.num_heads, residual)
+
+
+class Residual(nn.Module):
+    """``dropout(module(*args)) + args[0]``; for the three module kinds of the model the add is
+    fused into the operator's last GEMM epilogue."""
+
+    def __init__(self, module: nn.Module, dropout: float):
+        super().__init__()
+        self.module = module
+        self.dropout = nn.Dropout(p=dropout)
+        self.dropout_p = dropout
+
+    def forward(self, *args, **kwargs):
+        _no_dropout(self, self.dropout_p)
+        if isinstance(self.module, (CrossAttention, SelfAttention, MLP)):
+            return self.module(*args, residual=True, **kwargs)
+        return self.dropout(self.module(*args, **kwargs)) + args[0]
+
+
+def cross_attention_layer(num_q_channels: int, num_kv_channels: int, num_heads: int, dropout: float):
+    return Sequential(Residual(CrossAttention(num_q_channels, num_kv_channels, num_heads, dropout), dropout),
+                      Residual(mlp(num_q_channels), dropout))
+
+
+def self_attention_layer(num_channels: int, num_heads: int, dropout: float):
+    return Sequential(Residual(SelfAttention(num_channels, num_heads, dropout), dropout),
+                      Residual(mlp(num_channels), dropout))
+
+
+class SelfAttentionBlock(Sequential):
+    """S self-attention layers; forward hands all of them to one fused call."""
+
+    def forward(self, x):
+        params = []
+        for layer in self:
+            sa, ff = layer[0], layer[1]
+            _no_dropout(sa, sa.dropout_p)
+            params.extend(sa.module._params())
+            params.extend(ff.module._params())
+        heads = self[0][0].module.attention.attention.num_heads
+        return F.LatentBlockFn.apply(x, heads, *params)
+
+
+def self_attention_block(num_layers: int, num_channels: int, num_heads: int, dropout: float):
+    return SelfAttentionBlock(*[self_attention_layer(num_channels, num_heads, dropout) for _ in range(num_layers)])
+
+
+class PerceiverEncoder(nn.Module):
+    def __init__(self,
+                 input_adapter: InputAdapter,
+                 latent_shape: Tuple[int, int],
+                 num_layers: int,
+                 num_cross_attention_heads: int = 4,
+                 num_self_attention_heads: int = 4,
+                 num_self_attention_layers_per_block: int = 2,
+                 dropout: float = 0.0):
+        """Generic Perceiver IO encoder: input adapter -> (B, M, C_in); latent array (N, C) cross-attends
+        to it once per layer, each followed by a block of latent self-attention layers.  Layers 2..L
+        share one set of weights (``layer_n``)."""
+        super().__init__()
+        self.input_adapter = input_adapter
+        self.num_layers = num_layers
+        c = latent_shape[1]
+
+        def perceiver_layer():
+            return Sequential(
+                cross_attention_layer(c, input_adapter.num_input_channels, num_cross_attention_heads, dropout),
+                self_attention_block(num_self_attention_layers_per_block, c, num_self_attention_heads, dropout))
+
+        self.layer_1 = perceiver_layer()
+        if num_layers > 1:
+            self.layer_n = perceiver_layer()
+        self.latent = nn.Parameter(torch.empty(*latent_shape))
+        with torch.no_grad():
+            self.latent.normal_(0.0, 0.02).clamp_(-2.0, 2.0)
+
+    @staticmethod
+    def _apply_layer(layer, x_latent, x, pad_mask, attn_mask, kv=None):
+        cross, block = layer[0], layer[1]
+        x_latent = cross[0](x_latent, x, pad_mask, attn_mask, kv=kv)
+        x_latent = cross[1](x_latent)
+        return block(x_latent)
+
+    def forward(self, x, pad_mask=None, attn_mask=None):
+        b = x.shape[0]
+        x = self.input_adapter(x)
+        x_latent = self.latent.unsqueeze(0).expand(b, -1, -1).contiguous()
+        x_latent = self._apply_layer(self.layer_1, x_latent, x, pad_mask, attn_mask)
+        if self.num_layers > 1:
+            kv_n = self.layer_n[0][0].module.project_kv(x)  # once for all repeats of the shared layer
+            for _ in range(self.num_layers - 1):
+                x_latent = self._apply_layer(self.layer_n, x_latent, x, pad_mask, attn_mask, kv=kv_n)
+        return x_latent, pad_mask
+
+
+class PerceiverDecoder(nn.Module):
+    def __init__(self,
+                 output_adapter: OutputAdapter,
+                 latent_shape: Tuple[int, int],
+                 num_cross_attention_heads: int = 4,
+                 dropout: float = 0.0):
+        """Generic Perceiver IO decoder: a learned (K, C_out) query array cross-attends to the latents;
+        the output adapter maps (B, K, C_out) to the task output."""
+        super().__init__()
+        c_out = output_adapter.output_shape[-1]
+        self.output_adapter = output_adapter
+        self.latent_shape = latent_shape
+        self.cross_attention = cross_attention_layer(num_q_channels=c_out, num_kv_channels=latent_shape[1],
+                                                     num_heads=num_cross_attention_heads, dropout=dropout)
+        self.output = nn.Parameter(torch.empty(*output_adapter.output_shape))
+        with torch.no_grad():
+            self.output.normal_(0.0, 0.02).clamp_(-2.0, 2.0)
+
+    def forward(self, x, pad_mask=None, num_queries: Optional[int] = None):
+        b, *d = x.shape
+        if tuple(d) != tuple(self.latent_shape):
+            raise ValueError(f'Latent shape {tuple(d)} different from required shape {self.latent_shape}')
+        q = self.output if num_queries is None else self.output[:num_queries]
+        q = q.unsqueeze(0).expand(b, -1, -1).contiguous()
+        out = self.cross_attention(q, x)  # pad_mask is accepted and unused, as in the reference
+        return self.output_adapter(out)
+
+
+class TextMasking(nn.Module):
+    def __init__(self, vocab_size: int, unk_token_id: int, mask_token_id: int, num_special_tokens: int,
+                 mask_p: float = 0.15):
+        """BERT-style 80/10/10 masking (https://arxiv.org/abs/1810.04805)."""
+        super().__init__()
+        self.vocab_size = vocab_size
+        self.unk_token_id = unk_token_id
+        self.mask_token_id = mask_token_id
+        self.num_special_tokens = num_special_tokens
+        self.mask_p = mask_p
+
+    @staticmethod
+    def create(tokenizer, **kwargs):
+        return TextMasking(vocab_size=tokenizer.get_vocab_size(),
+                           unk_token_id=tokenizer.token_to_id(UNK_TOKEN),
+                           mask_token_id=tokenizer.token_to_id(MASK_TOKEN),
+                           num_special_tokens=len(SPECIAL_TOKENS), **kwargs)
+
+    def forward(self, x, pad_mask, generator=None):
+        labels = F.text_mask(x, pad_mask, self.vocab_size, self.unk_token_id, self.mask_token_id,
+                             self.num_special_tokens, self.mask_p, generator=generator)
+        return x, labels
+
+
+class PerceiverMLM(nn.Module):
+    def __init__(self, encoder: PerceiverEncoder, decoder: PerceiverDecoder, masking: TextMasking):
+        super().__init__()
+        self.encoder = encoder
+        self.decoder = decoder
+        self.masking = masking
+
+    def forward(self, x_input, pad_mask=None, masking=True):
+        _, l = x_input.shape
+        if masking:
+            x_masked, x_labels = self.masking(x_input, pad_mask)
+        else:
+            x_masked, x_labels = x_input, None
+        x_latent, _ = self.encoder(x_masked, pad_mask)
+        x_logits = self.decoder(x_latent, pad_mask, num_queries=l)
+        return x_logits, x_labels
+
+
+class PerceiverIO(Sequential):
+    def __init__(self, encoder: PerceiverEncoder, decoder: PerceiverDecoder):
+        super().__init__(encoder, decoder)
