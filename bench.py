@@ -120,7 +120,12 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
+
+    def mark(self):
+        """start of the timed region: earlier samples (warm-up, same load) are only used if the
+        timed region is too short to hold two samples of its own"""
+        self.t_mark = time.time()
 
     def stop(self):
         if self.proc is None:
@@ -132,7 +137,13 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], None, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        t_mark = getattr(self, "t_mark", 0.0)
+        inside = [ln for t, ln in self.lines if t >= t_mark]
+        window = "timed region"
+        if len(inside) < 2:
+            inside = [ln for _, ln in self.lines]
+            window = "warm-up + timed region (timed region shorter than two 100 ms samples)"
+        for ln in inside:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 6:
                 continue
@@ -146,7 +157,7 @@ class ClockSampler:
                     reasons.add(n)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "window": window}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -280,15 +291,23 @@ def gpu_arm(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return ms.item()
 
-    for _ in range(max(args.warmup, 3)):
-        step(ids_d, pad_d)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        step(ids_d, pad_d)
+    torch.cuda.synchronize()
+    sampler.mark()
     launches0 = N.lib().pio_launch_count()
     total_ms = timed(lambda: step(ids_d, pad_d), args.steps)
     launches = N.lib().pio_launch_count() - launches0
     clocks = sampler.stop() if rank == 0 else None
+    if args.profile_only:
+        if rank == 0:
+            print(json.dumps({"profile_only": True, "ms_per_step": total_ms / args.steps, "gpu_launches": int(launches)}))
+        if distributed:
+            dist.destroy_process_group()
+        return None
 
     # end to end through the public API with HOST buffers: H2D of the batch and D2H of the loss each step
     def e2e_step():
@@ -361,6 +380,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--profile-only", action="store_true", help="timed steps only (for ncu launch lists)")
     ap.add_argument("--mode", default=os.environ.get("PIO_MODE", "fp32"), choices=["fp32", "bf16"])
     args = ap.parse_args()
     if args.impl == "reference":

@@ -80,7 +80,7 @@ class ImageInputAdapter(InputAdapter):
         b, *d = x.shape
         if tuple(d) != tuple(self.image_shape):
             raise ValueError(f'Input image shape {tuple(d)} different from required shape {self.image_shape}')
-        return F.ImageEncodeFn.apply(x.reshape(b, -1, d[-1]), self.position_encoding)
+        return F.ImageEncodeFn.apply(x.reshape(b, self.position_encoding.shape[0], d[-1]), self.position_encoding)
 
 
 class TextInputAdapter(InputAdapter):
