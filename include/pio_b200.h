@@ -119,6 +119,34 @@ typedef struct {
 int pio_gemm_f32(const pio_gemm_desc* d, void* ws, size_t ws_bytes, pio_stream_t stream);
 size_t pio_gemm_f32_ws_bytes(int64_t m, int64_t n, int64_t k);
 
+/* The same product on the bf16 tensor cores (tcgen05.mma, TMA-staged operands, fp32 accumulator in
+ * TMEM) for PIO_MODE_BF16.  a / b are bf16; leading dimensions must be multiples of 8 elements and
+ * bases 16-byte aligned (TMA).  Outputs: fp32 (c32) and/or bf16 (c16).  aux16 (bf16) plays the role
+ * of `aux` above.  No rowsum: bias gradients are reduced by pio_colsum_bf16. */
+typedef struct {
+    const void* a;
+    const void* b;
+    int64_t m, n, k;
+    int64_t lda, ldb;
+    int a_kmajor, b_kmajor;
+    float* c32;
+    int64_t ldc32;
+    void* c16;
+    int64_t ldc16;
+    const float* bias;
+    const float* residual;
+    int64_t ldr;
+    void* aux16;
+    int64_t ldaux;
+    int act;
+    int accumulate;
+} pio_gemm_bf16_desc;
+int pio_gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, pio_stream_t stream);
+size_t pio_gemm_bf16_ws_bytes(int64_t m, int64_t n, int64_t k);
+/* fp32 (rows, cols; pitch ld_src) -> bf16 with pitch ld_dst >= cols (pad columns zero-filled). */
+int pio_cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_src, int64_t ld_dst,
+                  pio_stream_t stream);
+
 /* Attention core of nn.MultiheadAttention as called at model.py:74 (dropout 0):
  * S = (q dh^-1/2) k^T, padded keys -> -inf, P = softmax(S), O = P v.  Flash-style: P is never
  * stored; lse (batch,heads,n) = logsumexp of the scaled scores, saved for the backward, which

@@ -1,0 +1,490 @@
+// bf16 tensor-core GEMM for PIO_MODE_BF16: C[m,n] = sum_k A(m,k) B(n,k), fp32 accumulation.
+//
+//   * operands arrive by TMA (cp.async.bulk.tensor.2d, 128-byte swizzle) into a 4-stage
+//     shared-memory ring guarded by full/empty mbarriers;
+//   * one elected thread issues tcgen05.mma (kind::f16, M=128, N=BN, K=16) with the fp32
+//     accumulator tile in TMEM; tcgen05.commit releases ring slots and signals the epilogue;
+//   * four epilogue warps read the accumulator with tcgen05.ld (lane = row), apply
+//     bias / GELU / GELU' / residual and store fp32 and/or bf16.
+//
+// Either operand may be K-major (row = m|n, contiguous k: activations X, weights W for X W^T) or
+// MN-major (row = k, contiguous m|n: W for dY W, and dY / X for the weight gradient dY^T X), so
+// every product of the forward and backward pass reads its operands where they already lie.
+// Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..5 = epilogue.
+#include <cuda.h>
+
+#include <mutex>
+
+#include "pio_common.cuh"
+
+namespace pio {
+
+constexpr int TC_BM = 128;
+constexpr int TC_BK = 64;  // 64 bf16 = one 128-byte swizzle row
+constexpr int TC_STAGES = 4;
+constexpr int TC_THREADS = 192;
+
+struct TcParams {
+    int M, N, K;
+    int num_kb, kb_per_split, splits;
+    float* c32;
+    int64_t ldc32;
+    __nv_bfloat16* c16;
+    int64_t ldc16;
+    const float* bias;
+    const float* residual;
+    int64_t ldr;
+    __nv_bfloat16* aux16;
+    int64_t ldaux;
+    int act;
+    int accumulate;
+    float* partial;
+    int64_t partial_stride;
+};
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P1;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+        "@P1 bra DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "DONE:\n\t"
+        "}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"((uint64_t)map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)map) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_c, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_c),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// shared-memory matrix descriptor, 128-byte swizzle (layout_type 2), descriptor version 1
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFFu);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+// instruction descriptor, kind::f16: fp32 accumulate, bf16 x bf16, M = 128, N = bn
+__device__ __forceinline__ uint32_t make_idesc(int bn, bool a_mn, bool b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) |
+           ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+}
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+    gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
+    constexpr int A_STAGE = TC_BM * TC_BK * 2;  // 16 KB
+    constexpr int B_STAGE = BN * TC_BK * 2;
+    constexpr uint32_t STAGE_BYTES = A_STAGE + B_STAGE;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + TC_STAGES * A_STAGE;
+    uint64_t* full_bar = (uint64_t*)(sB + TC_STAGES * B_STAGE);
+    uint64_t* empty_bar = full_bar + TC_STAGES;
+    uint64_t* tmem_full = empty_bar + TC_STAGES;
+    uint32_t* tmem_slot = (uint32_t*)(tmem_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.y * TC_BM, n0 = blockIdx.x * BN;
+    const int kb_begin = blockIdx.z * p.kb_per_split;
+    const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+    const int nkb = kb_end - kb_begin;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmA);
+        prefetch_tmap(&tmB);
+        for (int s = 0; s < TC_STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(tmem_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % TC_STAGES;
+                const uint32_t ph = (uint32_t)(i / TC_STAGES) & 1u;
+                mbar_wait(&empty_bar[s], ph ^ 1u);
+                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                const int k0 = (kb_begin + i) * TC_BK;
+                uint8_t* a_dst = sA + s * A_STAGE;
+                uint8_t* b_dst = sB + s * B_STAGE;
+                if (!A_MN) {
+                    tma_load_2d(a_dst, &tmA, k0, m0, &full_bar[s]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < TC_BM / 64; ++j) tma_load_2d(a_dst + j * 8192, &tmA, m0 + j * 64, k0, &full_bar[s]);
+                }
+                if (!B_MN) {
+                    tma_load_2d(b_dst, &tmB, k0, n0, &full_bar[s]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < BN / 64; ++j) tma_load_2d(b_dst + j * 8192, &tmB, n0 + j * 64, k0, &full_bar[s]);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(BN, A_MN, B_MN);
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % TC_STAGES;
+                const uint32_t ph = (uint32_t)(i / TC_STAGES) & 1u;
+                mbar_wait(&full_bar[s], ph);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(sA + s * A_STAGE);
+                const uint32_t b_addr = smem_u32(sB + s * B_STAGE);
+#pragma unroll
+                for (int k = 0; k < TC_BK / 16; ++k) {
+                    // K-major: step 16 elements (32 B) inside the 128-byte swizzle row;
+                    // MN-major: step 16 k-rows of 128 B (two 8-row swizzle atoms)
+                    const uint64_t da = A_MN ? make_smem_desc(a_addr + k * 2048, 8192, 1024) : make_smem_desc(a_addr + k * 32, 16, 1024);
+                    const uint64_t db = B_MN ? make_smem_desc(b_addr + k * 2048, 8192, 1024) : make_smem_desc(b_addr + k * 32, 16, 1024);
+                    umma_bf16(tmem_base, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[s]);  // frees the ring slot once these MMAs have read it
+            }
+            umma_commit(tmem_full);  // accumulator complete
+        }
+        __syncwarp();
+    } else {
+        // ---------------- epilogue: TMEM lane quadrant = warp id mod 4
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const int64_t gm = (int64_t)m0 + row;
+        mbar_wait(tmem_full, 0);
+        tc_fence_after();
+        const bool row_ok = gm < p.M;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+            uint32_t r[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+            tmem_ld_wait();
+            if (!row_ok) continue;
+            const int nb = n0 + c0;
+            if (nb >= p.N) continue;
+            if (p.splits > 1) {
+                float* out = p.partial + (int64_t)blockIdx.z * p.partial_stride + gm * p.N + nb;
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (nb + j < p.N) out[j] = __uint_as_float(r[j]);
+                continue;
+            }
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+            const bool full = (nb + 32 <= p.N);
+            if (p.bias) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (full || nb + j < p.N) v[j] += __ldg(p.bias + nb + j);
+            }
+            if (p.act == 1) {
+                if (p.aux16) {
+                    __nv_bfloat16* a = p.aux16 + gm * p.ldaux + nb;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (full || nb + j < p.N) a[j] = __float2bfloat16(v[j]);
+                }
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+            } else if (p.act == 2) {
+                const __nv_bfloat16* a = p.aux16 + gm * p.ldaux + nb;
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (full || nb + j < p.N) v[j] *= gelu_erf_grad(__bfloat162float(a[j]));
+            }
+            if (p.residual) {
+                const float* rr = p.residual + gm * p.ldr + nb;
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (full || nb + j < p.N) v[j] += rr[j];
+            }
+            if (p.c32) {
+                float* o = p.c32 + gm * p.ldc32 + nb;
+                if (p.accumulate) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (full || nb + j < p.N) o[j] += v[j];
+                } else if (full && ((((uintptr_t)o) & 15) == 0)) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (full || nb + j < p.N) o[j] = v[j];
+                }
+            }
+            if (p.c16) {
+                __nv_bfloat16* o = p.c16 + gm * p.ldc16 + nb;
+                if (full && ((((uintptr_t)o) & 15) == 0)) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 8) {
+                        __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j], v[j + 1]);
+                        __nv_bfloat162 h1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+                        __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
+                        __nv_bfloat162 h3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
+                        uint4 u;
+                        u.x = *reinterpret_cast<uint32_t*>(&h0);
+                        u.y = *reinterpret_cast<uint32_t*>(&h1);
+                        u.z = *reinterpret_cast<uint32_t*>(&h2);
+                        u.w = *reinterpret_cast<uint32_t*>(&h3);
+                        *reinterpret_cast<uint4*>(o + j) = u;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (full || nb + j < p.N) o[j] = __float2bfloat16(v[j]);
+                }
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, BN);
+    }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)ptr;
+    });
+    return fn;
+}
+
+// 2-D bf16 tensor map over a row-major (rows, cols) matrix with leading dimension ld (elements);
+// box = box_rows x 64 columns, 128-byte swizzle, zero fill out of bounds.
+int make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) {
+        set_error("cuTensorMapEncodeTiled entry point not available from the driver");
+        return PIO_ERR_CUDA;
+    }
+    PIO_CHECK_ARG((((uintptr_t)base) & 15) == 0, "bf16 GEMM operand base %p is not 16-byte aligned", base);
+    PIO_CHECK_ARG(ld % 8 == 0, "bf16 GEMM operand leading dimension %lld is not a multiple of 8 elements", (long long)ld);
+    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows %lld cols %lld ld %lld)", (int)r, (long long)rows,
+                  (long long)cols, (long long)ld);
+        return PIO_ERR_CUDA;
+    }
+    return PIO_OK;
+}
+
+static void tc_choose(int64_t m, int64_t n, int64_t k, bool splittable, int* bn, int* splits, int* kb_per) {
+    const int sms = num_sms();
+    *bn = (n <= 64) ? 64 : 128;
+    const int64_t tiles = cdiv(m, TC_BM) * cdiv(n, *bn);
+    const int num_kb = (int)cdiv(k, TC_BK);
+    int s = 1;
+    if (splittable && num_kb >= 16 && tiles < sms) {
+        s = (int)std::min<int64_t>(cdiv(sms, tiles), num_kb / 4);
+        s = std::max(s, 1);
+    }
+    int per = (int)cdiv(num_kb, s);
+    s = (int)cdiv(num_kb, per);
+    *splits = s;
+    *kb_per = per;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, dim3 grid, cudaStream_t st) {
+    const size_t smem = (size_t)TC_STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + 1024 + 256;
+    static bool configured = false;  // per instantiation; attribute is sticky per function
+    if (!configured) {
+        PIO_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    gemm_tc_kernel<BN, A_MN, B_MN><<<grid, TC_THREADS, smem, st>>>(ta, tb, p);
+    PIO_LAUNCH_CHECK();
+    return PIO_OK;
+}
+
+int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream_t st) {
+    PIO_CHECK_ARG(d && d->a && d->b && (d->c32 || d->c16), "pio_gemm_bf16: null pointer");
+    PIO_CHECK_ARG(d->m >= 0 && d->n >= 0 && d->k >= 1, "pio_gemm_bf16: bad dims");
+    PIO_CHECK_ARG(d->act >= 0 && d->act <= 2 && (d->act != 2 || d->aux16), "pio_gemm_bf16: bad act/aux");
+    PIO_CHECK_ARG(d->m < (1ll << 31) && d->n < (1ll << 31) && d->k < (1ll << 31), "pio_gemm_bf16: dims exceed 2^31");
+    if (d->m == 0 || d->n == 0) return PIO_OK;
+    const bool a_mn = !d->a_kmajor, b_mn = !d->b_kmajor;
+    const bool splittable = !d->bias && !d->residual && d->act == 0 && d->c32 && !d->c16 && d->ldc32 == d->n;
+    int bn, splits, kb_per;
+    tc_choose(d->m, d->n, d->k, splittable, &bn, &splits, &kb_per);
+
+    TcParams p{};
+    p.M = (int)d->m; p.N = (int)d->n; p.K = (int)d->k;
+    p.num_kb = (int)cdiv(d->k, TC_BK);
+    p.c32 = d->c32; p.ldc32 = d->ldc32;
+    p.c16 = (__nv_bfloat16*)d->c16; p.ldc16 = d->ldc16;
+    p.bias = d->bias; p.residual = d->residual; p.ldr = d->ldr;
+    p.aux16 = (__nv_bfloat16*)d->aux16; p.ldaux = d->ldaux;
+    p.act = d->act; p.accumulate = d->accumulate;
+    p.partial_stride = d->m * d->n;
+    if (splits > 1) {
+        Workspace W(ws, ws_bytes);
+        p.partial = W.takef((size_t)splits * (size_t)p.partial_stride);
+        if (!p.partial) {
+            splits = 1;
+            kb_per = p.num_kb;
+        }
+    }
+    p.splits = splits;
+    p.kb_per_split = kb_per;
+
+    // tensor maps: K-major operand = (rows = m|n, cols = k); MN-major operand = (rows = k, cols = m|n)
+    CUtensorMap ta, tb;
+    if (!a_mn) PIO_TRY(make_tmap_bf16(&ta, d->a, d->m, d->k, d->lda, TC_BM));
+    else PIO_TRY(make_tmap_bf16(&ta, d->a, d->k, d->m, d->lda, TC_BK));
+    if (!b_mn) PIO_TRY(make_tmap_bf16(&tb, d->b, d->n, d->k, d->ldb, bn));
+    else PIO_TRY(make_tmap_bf16(&tb, d->b, d->k, d->n, d->ldb, TC_BK));
+
+    dim3 grid((unsigned)cdiv(d->n, bn), (unsigned)cdiv(d->m, TC_BM), (unsigned)splits);
+    PIO_CHECK_ARG(grid.y <= 65535 && grid.z <= 65535, "pio_gemm_bf16: grid too large");
+    int rc;
+#define PIO_TC(BNV)                                                        \
+    do {                                                                   \
+        if (!a_mn && !b_mn) rc = launch_tc<BNV, false, false>(ta, tb, p, grid, st);      \
+        else if (!a_mn && b_mn) rc = launch_tc<BNV, false, true>(ta, tb, p, grid, st);   \
+        else if (a_mn && !b_mn) rc = launch_tc<BNV, true, false>(ta, tb, p, grid, st);   \
+        else rc = launch_tc<BNV, true, true>(ta, tb, p, grid, st);                        \
+    } while (0)
+    if (bn == 64) PIO_TC(64);
+    else PIO_TC(128);
+#undef PIO_TC
+    PIO_TRY(rc);
+    if (splits > 1) PIO_TRY(reduce_partials(p.partial, splits, p.partial_stride, d->c32, d->m * d->n, nullptr, 0, d->accumulate, st));
+    return PIO_OK;
+}
+
+// fp32 -> bf16 with a (possibly padded) destination pitch; pad columns are zero-filled
+__global__ void cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t rows, int cols,
+                                 int64_t ld_src, int64_t ld_dst) {
+    const int64_t total = rows * ld_dst;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / ld_dst;
+        const int c = (int)(i - r * ld_dst);
+        dst[i] = __float2bfloat16(c < cols ? src[r * ld_src + c] : 0.f);
+    }
+}
+
+int cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_src, int64_t ld_dst, cudaStream_t st) {
+    PIO_CHECK_ARG(src && dst && rows >= 0 && cols > 0 && ld_dst >= cols && ld_src >= cols, "pio_cast_bf16: bad arguments");
+    if (rows == 0) return PIO_OK;
+    const int64_t total = rows * ld_dst;
+    const int blocks = (int)std::min<int64_t>(cdiv(total, 256 * 4), (int64_t)num_sms() * 16);
+    cast_bf16_kernel<<<std::max(blocks, 1), 256, 0, st>>>(src, (__nv_bfloat16*)dst, rows, cols, ld_src, ld_dst);
+    PIO_LAUNCH_CHECK();
+    return PIO_OK;
+}
+
+}  // namespace pio
+
+using namespace pio;
+
+extern "C" {
+
+size_t pio_gemm_bf16_ws_bytes(int64_t m, int64_t n, int64_t k) {
+    int bn, splits, kb_per;
+    tc_choose(m, n, k, true, &bn, &splits, &kb_per);
+    if (splits <= 1) return 256;
+    return align_up((size_t)splits * (size_t)(m * n) * sizeof(float), 256) + 256;
+}
+
+int pio_gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, pio_stream_t stream) {
+    return gemm_bf16(d, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+int pio_cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_src, int64_t ld_dst, pio_stream_t stream) {
+    return cast_bf16(src, dst, rows, cols, ld_src, ld_dst, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -41,6 +41,15 @@ class GemmDesc(Structure):
                 ("act", c_int), ("accumulate", c_int), ("rowsum_a", c_void_p)]
 
 
+class GemmBf16Desc(Structure):
+    _fields_ = [("a", c_void_p), ("b", c_void_p),
+                ("m", c_int64), ("n", c_int64), ("k", c_int64), ("lda", c_int64), ("ldb", c_int64),
+                ("a_kmajor", c_int), ("b_kmajor", c_int),
+                ("c32", c_void_p), ("ldc32", c_int64), ("c16", c_void_p), ("ldc16", c_int64),
+                ("bias", c_void_p), ("residual", c_void_p), ("ldr", c_int64),
+                ("aux16", c_void_p), ("ldaux", c_int64), ("act", c_int), ("accumulate", c_int)]
+
+
 class AttnDesc(Structure):
     _fields_ = [("q", c_void_p), ("k", c_void_p), ("v", c_void_p), ("pad", c_void_p), ("o", c_void_p), ("lse", c_void_p),
                 ("q_bs", c_int64), ("q_rs", c_int64), ("k_bs", c_int64), ("k_rs", c_int64),
@@ -71,6 +80,9 @@ _SIGNATURES = {
     "pio_layernorm_bwd_ws_bytes": (c_size_t, [c_int64, c_int]),
     "pio_gemm_f32": (c_int, [POINTER(GemmDesc), P, c_size_t, P]),
     "pio_gemm_f32_ws_bytes": (c_size_t, [c_int64, c_int64, c_int64]),
+    "pio_gemm_bf16": (c_int, [POINTER(GemmBf16Desc), P, c_size_t, P]),
+    "pio_gemm_bf16_ws_bytes": (c_size_t, [c_int64, c_int64, c_int64]),
+    "pio_cast_bf16": (c_int, [P, P, c_int64, c_int, c_int64, c_int64, P]),
     "pio_attn_fwd": (c_int, [POINTER(AttnDesc), c_int, P]),
     "pio_attn_bwd": (c_int, [POINTER(AttnBwdDesc), c_int, P]),
     "pio_cross_entropy_fwd": (c_int, [P, P, P, P, c_int64, c_int64, c_int64, c_int64, P]),
