@@ -3,7 +3,7 @@
 // for the score dot products, lane = channel for the P·V accumulation), nothing of size n x m
 // ever leaves the SM.  Backward recomputes P from the saved log-sum-exp: one kernel owns query
 // rows (dQ, and the row term delta = dO·O), one owns key rows (dK, dV) — no atomics.
-#include "pio_common.cuh"
+#include "pio_ops_common.cuh"
 
 namespace pio {
 
@@ -17,6 +17,7 @@ struct AttnP {
     const float *q, *k, *v, *o, *d_o, *lse_in;
     const uint8_t* pad;
     float *out, *lse, *dq, *dk, *dv, *delta;
+    __nv_bfloat16 *out16, *dq16, *dk16, *dv16;  // optional bf16 copies, same element strides
     int64_t q_bs, q_rs, k_bs, k_rs, v_bs, v_rs, o_bs, o_rs;
     int batch, heads, n, m, dh;
     float scale;
@@ -129,7 +130,11 @@ __global__ void __launch_bounds__(AT_THREADS) attn_fwd_kernel(const AttnP p) {
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
             const int d = 32 * c + lane;
-            if (d < p.dh) og[d] = acc[i][c] * inv;
+            if (d < p.dh) {
+                const float val = acc[i][c] * inv;
+                og[d] = val;
+                if (p.out16) p.out16[(int64_t)b * p.o_bs + (int64_t)qi * p.o_rs + (int64_t)h * p.dh + d] = __float2bfloat16(val);
+            }
         }
         if (lane == 0) p.lse[((int64_t)b * p.heads + h) * p.n + qi] = m_run[i] + logf(l_run[i]);
     }
@@ -223,7 +228,10 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_dq_kernel(const AttnP p) 
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
             const int d = 32 * c + lane;
-            if (d < p.dh) dqg[d] = acc[i][c];
+            if (d < p.dh) {
+                dqg[d] = acc[i][c];
+                if (p.dq16) p.dq16[(int64_t)b * p.q_bs + (int64_t)qi * p.q_rs + (int64_t)h * p.dh + d] = __float2bfloat16(acc[i][c]);
+            }
         }
     }
 }
@@ -330,6 +338,8 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_dkv_kernel(const AttnP p)
             if (d < p.dh) {
                 dkg[d] = dk[i][c];
                 dvg[d] = dv[i][c];
+                if (p.dk16) p.dk16[(int64_t)b * p.k_bs + (int64_t)kj * p.k_rs + (int64_t)h * p.dh + d] = __float2bfloat16(dk[i][c]);
+                if (p.dv16) p.dv16[(int64_t)b * p.v_bs + (int64_t)kj * p.v_rs + (int64_t)h * p.dh + d] = __float2bfloat16(dv[i][c]);
             }
         }
     }
@@ -373,20 +383,21 @@ static void fill(AttnP& p, const pio_attn_desc* d) {
         else { constexpr int NCH = 16; EXPR; }                  \
     } while (0)
 
-int attn_fwd_simt(const pio_attn_desc* d, cudaStream_t st) {
+int attn_fwd_simt(const pio_attn_desc* d, cudaStream_t st, const AttnBf16Out* extra) {
     PIO_TRY(check_desc(d, "pio_attn_fwd"));
     if (d->batch == 0 || d->n == 0) return PIO_OK;
     AttnP p{};
     fill(p, d);
     p.out = d->o;
     p.lse = d->lse;
+    if (extra) p.out16 = extra->o16;
     dim3 grid((unsigned)cdiv(d->n, AT_ROWS), (unsigned)d->heads, (unsigned)d->batch);
     int rc = PIO_OK;
     PIO_DISPATCH_NCH(d->dh, rc = launch(attn_fwd_kernel<NCH>, grid, fwd_smem(32 * NCH), p, st));
     return rc;
 }
 
-int attn_bwd_simt(const pio_attn_bwd_desc* bd, cudaStream_t st) {
+int attn_bwd_simt(const pio_attn_bwd_desc* bd, cudaStream_t st, const AttnBf16Out* extra) {
     const pio_attn_desc* d = &bd->fwd;
     PIO_TRY(check_desc(d, "pio_attn_bwd"));
     PIO_CHECK_ARG(bd->d_o && bd->dq && bd->dk && bd->dv && bd->delta, "pio_attn_bwd: null pointer");
@@ -397,6 +408,11 @@ int attn_bwd_simt(const pio_attn_bwd_desc* bd, cudaStream_t st) {
     p.lse_in = d->lse;
     p.d_o = bd->d_o;
     p.dq = bd->dq; p.dk = bd->dk; p.dv = bd->dv; p.delta = bd->delta;
+    if (extra) {
+        p.dq16 = extra->dq16;
+        p.dk16 = extra->dk16;
+        p.dv16 = extra->dv16;
+    }
     int rc = PIO_OK;
     if (d->n > 0) {
         dim3 gq((unsigned)cdiv(d->n, AT_ROWS), (unsigned)d->heads, (unsigned)d->batch);

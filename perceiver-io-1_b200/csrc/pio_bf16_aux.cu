@@ -1,0 +1,115 @@
+// Bandwidth-bound helpers of the bf16 pipeline: LayerNorm with bf16 output, fp32->bf16 cast fused
+// with the column sums that give bias gradients, bf16 column sums.
+#include "pio_ops_common.cuh"
+
+namespace pio {
+
+__global__ void layernorm_fwd_bf16_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                          const float* __restrict__ b, __nv_bfloat16* __restrict__ y, int64_t ldy,
+                                          float* __restrict__ stats, int64_t rows, int c, float eps) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const float inv_c = 1.0f / (float)c;
+    for (int64_t r = warp; r < rows; r += nwarps) {
+        const float* xr = x + r * c;
+        float s = 0.f;
+        for (int j = lane; j < c; j += 32) s += xr[j];
+        const float mean = warp_sum(s) * inv_c;
+        float v = 0.f;
+        for (int j = lane; j < c; j += 32) {
+            const float d = xr[j] - mean;
+            v += d * d;
+        }
+        const float rstd = rsqrtf(warp_sum(v) * inv_c + eps);
+        __nv_bfloat16* yr = y + r * ldy;
+        for (int j = lane; j < (int)ldy; j += 32)
+            yr[j] = __float2bfloat16(j < c ? (xr[j] - mean) * rstd * __ldg(w + j) + __ldg(b + j) : 0.f);
+        if (lane == 0 && stats != nullptr) {
+            stats[2 * r] = mean;
+            stats[2 * r + 1] = rstd;
+        }
+    }
+}
+
+int layernorm_fwd_bf16(const float* x, const float* w, const float* b, __nv_bfloat16* y, int64_t ldy, float* stats,
+                       int64_t rows, int c, float eps, cudaStream_t st) {
+    PIO_CHECK_ARG(x && w && b && y && c > 0 && ldy >= c, "layernorm_fwd_bf16: bad arguments");
+    if (rows == 0) return PIO_OK;
+    const int threads = 256;
+    const int blocks = (int)std::min<int64_t>(cdiv(rows, threads / 32), (int64_t)num_sms() * 16);
+    layernorm_fwd_bf16_kernel<<<blocks, threads, 0, st>>>(x, w, b, y, ldy, stats, rows, c, eps);
+    PIO_LAUNCH_CHECK();
+    return PIO_OK;
+}
+
+// grid (ceil(c/128), chunks): block covers 128 columns x rows [chunk*rpc, (chunk+1)*rpc)
+template <typename TIn>
+__global__ void __launch_bounds__(256) colsum_partial_kernel(const TIn* __restrict__ src, int64_t ld_src,
+                                                             __nv_bfloat16* __restrict__ dst16, int64_t ld_dst,
+                                                             float* __restrict__ partial, int64_t rows, int c,
+                                                             int64_t rows_per_chunk, int pad_cols) {
+    __shared__ float s_part[256];
+    const int col = blockIdx.x * 128 + (threadIdx.x & 127);
+    const int sub = threadIdx.x >> 7;
+    const int64_t r0 = (int64_t)blockIdx.y * rows_per_chunk;
+    const int64_t r1 = min(rows, r0 + rows_per_chunk);
+    float acc = 0.f;
+    if (col < c) {
+        for (int64_t r = r0 + sub; r < r1; r += 2) {
+            float v;
+            if constexpr (sizeof(TIn) == 4) v = (float)src[r * ld_src + col];
+            else v = __bfloat162float(src[r * ld_src + col]);
+            acc += v;
+            if (dst16) dst16[r * ld_dst + col] = __float2bfloat16(v);
+        }
+    } else if (dst16 && col < pad_cols) {
+        for (int64_t r = r0 + sub; r < r1; r += 2) dst16[r * ld_dst + col] = __float2bfloat16(0.f);
+    }
+    s_part[threadIdx.x] = acc;
+    __syncthreads();
+    if (partial && sub == 0 && col < c) partial[(int64_t)blockIdx.y * c + col] = acc + s_part[threadIdx.x + 128];
+}
+
+static int colsum_chunks(int64_t rows, int c) {
+    const int64_t col_blocks = cdiv(c, 128);
+    int64_t chunks = std::max<int64_t>(1, std::min<int64_t>(cdiv(2 * (int64_t)num_sms(), col_blocks), cdiv(rows, 16)));
+    return (int)std::min<int64_t>(chunks, 256);
+}
+
+size_t colsum_ws_bytes(int64_t rows, int c) { return align_up((size_t)colsum_chunks(rows, c) * c * sizeof(float), 256) + 256; }
+
+template <typename TIn>
+static int colsum_impl(const TIn* src, int64_t ld_src, __nv_bfloat16* dst16, int64_t ld_dst, float* colsum, int accumulate,
+                       int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t st) {
+    PIO_CHECK_ARG(src && c > 0 && rows >= 0, "colsum: bad arguments");
+    if (rows == 0) return PIO_OK;
+    const int chunks = colsum_chunks(rows, c);
+    float* partial = nullptr;
+    if (colsum) {
+        Workspace W(ws, ws_bytes);
+        partial = W.takef((size_t)chunks * c);
+        if (!partial) {
+            set_error("colsum: workspace too small (%zu bytes)", ws_bytes);
+            return PIO_ERR_WORKSPACE;
+        }
+    }
+    const int pad_cols = dst16 ? (int)ld_dst : c;
+    dim3 grid((unsigned)cdiv(std::max(pad_cols, c), 128), (unsigned)chunks);
+    colsum_partial_kernel<TIn><<<grid, 256, 0, st>>>(src, ld_src, dst16, ld_dst, partial, rows, c, cdiv(rows, chunks), pad_cols);
+    PIO_LAUNCH_CHECK();
+    if (colsum) PIO_TRY(reduce_partials(partial, chunks, c, colsum, c, nullptr, 0, accumulate, st));
+    return PIO_OK;
+}
+
+int cast_colsum_f32(const float* src, int64_t ld_src, __nv_bfloat16* dst16, int64_t ld_dst, float* colsum, int accumulate,
+                    int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t st) {
+    return colsum_impl<float>(src, ld_src, dst16, ld_dst, colsum, accumulate, rows, c, ws, ws_bytes, st);
+}
+
+int colsum_bf16(const __nv_bfloat16* src, int64_t ld_src, float* colsum, int accumulate, int64_t rows, int c, void* ws,
+                size_t ws_bytes, cudaStream_t st) {
+    return colsum_impl<__nv_bfloat16>(src, ld_src, nullptr, 0, colsum, accumulate, rows, c, ws, ws_bytes, st);
+}
+
+}  // namespace pio

@@ -2,34 +2,11 @@
 // Residual(CrossAttention), the latent self-attention block, the output linear).  Each call
 // enqueues its kernel sequence on the caller's stream; saved-for-backward state and scratch are
 // carved from caller-owned buffers with a fixed layout that only this file knows.
-#include "pio_common.cuh"
+#include "pio_ops_common.cuh"
 
 namespace pio {
 
-int attn_fwd_simt(const pio_attn_desc* d, cudaStream_t st);
-int attn_bwd_simt(const pio_attn_bwd_desc* d, cudaStream_t st);
-
 namespace {
-
-constexpr float LN_EPS = 1e-5f;  // nn.LayerNorm default, used everywhere in the reference
-
-struct Ctx {
-    cudaStream_t st;
-    Workspace W;
-    Ctx(void* ws, size_t n, pio_stream_t s) : st((cudaStream_t)s), W(ws, n) {}
-    void* rest() { return W.base ? W.base + align_up(W.off, 256) : nullptr; }
-    size_t rest_bytes() {
-        const size_t o = align_up(W.off, 256);
-        return (W.base && o < W.size) ? W.size - o : 0;
-    }
-};
-
-#define PIO_TAKE(var, ctx, count, who)                                                     \
-    float* var = (ctx).W.takef((size_t)(count));                                           \
-    if (!var) {                                                                            \
-        set_error("%s: workspace too small (%zu bytes given)", who, (ctx).W.size);        \
-        return PIO_ERR_WORKSPACE;                                                          \
-    }
 
 // y[rows, n] = act(x[rows,k] W[n,k]^T + bias) (+ residual)
 int gemm_xwT(Ctx& c, const float* x, int64_t ldx, const float* w, int64_t ldw, float* y, int64_t ldy, int64_t rows,
@@ -71,17 +48,6 @@ int gemm_dW(Ctx& c, const float* dy, int64_t lddy, const float* x, int64_t ldx, 
 }
 
 size_t dW_scratch(int64_t nout, int64_t kin, int64_t rows) { return pio_gemm_f32_ws_bytes(nout, kin, rows); }
-
-// carve 256-byte aligned arrays out of an opaque saved buffer (nullptr base = size query)
-struct Carver {
-    float* base;
-    size_t off;
-    float* take(size_t n) {
-        float* r = base ? base + off : nullptr;
-        off += (n + 63) / 64 * 64;
-        return r;
-    }
-};
 
 // ---------------------------------------------------------------- mlp
 struct MlpSaved {
@@ -358,8 +324,8 @@ struct BlockLayout {
 };
 
 int check_mode(int mode, const char* who) {
-    if (mode != PIO_MODE_FP32) {
-        set_error("%s: mode %d is not available in this build of the fused operator", who, mode);
+    if (mode != PIO_MODE_FP32 && mode != PIO_MODE_BF16) {
+        set_error("%s: unknown mode %d", who, mode);
         return PIO_ERR_UNSUPPORTED;
     }
     return PIO_OK;
@@ -373,14 +339,17 @@ using namespace pio;
 extern "C" {
 
 // ---- mlp
-size_t pio_mlp_saved_bytes(int64_t rows, int c, int mode) { (void)mode; return MlpSaved::floats(rows, c) * 4 + 256; }
-size_t pio_mlp_ws_bytes(int64_t rows, int c, int mode) { (void)mode; return mlp_bwd_ws(rows, c); }
+size_t pio_mlp_saved_bytes(int64_t rows, int c, int mode) {
+    return mode == PIO_MODE_BF16 ? bf::mlp_saved_bytes(rows, c) : MlpSaved::floats(rows, c) * 4 + 256;
+}
+size_t pio_mlp_ws_bytes(int64_t rows, int c, int mode) { return mode == PIO_MODE_BF16 ? bf::mlp_ws_bytes(rows, c) : mlp_bwd_ws(rows, c); }
 
 int pio_mlp_fwd(const float* x, float* y, const pio_mlp_weights* w, void* saved, int64_t rows, int c, int residual,
                 int mode, void* ws, size_t ws_bytes, pio_stream_t stream) {
     PIO_TRY(check_mode(mode, "pio_mlp_fwd"));
     PIO_CHECK_ARG(x && y && w && saved && rows >= 0 && c > 0, "pio_mlp_fwd: bad arguments");
     Ctx ctx(ws, ws_bytes, stream);
+    if (mode == PIO_MODE_BF16) return bf::mlp_fwd(ctx, x, y, w, saved, rows, c, residual);
     return mlp_fwd(ctx, x, y, w, saved, rows, c, residual);
 }
 
@@ -390,15 +359,18 @@ int pio_mlp_bwd(const float* dy, const float* x, float* dx, const pio_mlp_weight
     PIO_TRY(check_mode(mode, "pio_mlp_bwd"));
     PIO_CHECK_ARG(dy && x && dx && w && saved && g && rows >= 0 && c > 0, "pio_mlp_bwd: bad arguments");
     Ctx ctx(ws, ws_bytes, stream);
+    if (mode == PIO_MODE_BF16) return bf::mlp_bwd(ctx, dy, x, dx, w, saved, g, accumulate, rows, c, residual);
     return mlp_bwd(ctx, dy, x, dx, w, saved, g, accumulate, rows, c, residual);
 }
 
 // ---- kv projection
 size_t pio_kv_project_saved_bytes(int64_t rows, int c_kv, int e, int mode) {
-    (void)mode; (void)e;
-    return KvSaved::floats(rows, c_kv) * 4 + 256;
+    (void)e;
+    return mode == PIO_MODE_BF16 ? bf::kv_saved_bytes(rows, c_kv) : KvSaved::floats(rows, c_kv) * 4 + 256;
 }
-size_t pio_kv_project_ws_bytes(int64_t rows, int c_kv, int e, int mode) { (void)mode; return kv_project_bwd_ws(rows, c_kv, e); }
+size_t pio_kv_project_ws_bytes(int64_t rows, int c_kv, int e, int mode) {
+    return mode == PIO_MODE_BF16 ? bf::kv_ws_bytes(rows, c_kv, e) : kv_project_bwd_ws(rows, c_kv, e);
+}
 
 int pio_kv_project_fwd(const float* x_kv, float* kv, const pio_attn_weights* w, void* saved, int64_t rows, int c_kv, int e,
                        int mode, void* ws, size_t ws_bytes, pio_stream_t stream) {
@@ -406,6 +378,7 @@ int pio_kv_project_fwd(const float* x_kv, float* kv, const pio_attn_weights* w, 
     PIO_CHECK_ARG(x_kv && kv && w && saved && rows >= 0 && c_kv > 0 && e > 0, "pio_kv_project_fwd: bad arguments");
     PIO_CHECK_ARG(w->kv_ln_w && w->kv_ln_b && w->wk && w->wv && w->bk && w->bv, "pio_kv_project_fwd: missing weights");
     Ctx ctx(ws, ws_bytes, stream);
+    if (mode == PIO_MODE_BF16) return bf::kv_project_fwd(ctx, x_kv, kv, w, saved, rows, c_kv, e);
     return kv_project_fwd(ctx, x_kv, kv, w, saved, rows, c_kv, e);
 }
 
@@ -416,17 +389,18 @@ int pio_kv_project_bwd(const float* dkv, const float* x_kv, float* dx_kv, const 
     PIO_CHECK_ARG(dkv && x_kv && w && saved && g && rows >= 0 && c_kv > 0 && e > 0, "pio_kv_project_bwd: bad arguments");
     PIO_CHECK_ARG(g->kv_ln_w && g->kv_ln_b && g->wk && g->wv && g->bk && g->bv, "pio_kv_project_bwd: missing grads");
     Ctx ctx(ws, ws_bytes, stream);
+    if (mode == PIO_MODE_BF16) return bf::kv_project_bwd(ctx, dkv, x_kv, dx_kv, w, saved, g, accumulate, rows, c_kv, e);
     return kv_project_bwd(ctx, dkv, x_kv, dx_kv, w, saved, g, accumulate, rows, c_kv, e);
 }
 
 // ---- query side of cross attention
 size_t pio_cross_attend_saved_bytes(int batch, int n, int m, int e, int heads, int mode) {
-    (void)mode; (void)m;
-    return XaSaved::floats(batch, n, e, heads) * 4 + 256;
+    (void)m;
+    return mode == PIO_MODE_BF16 ? bf::xa_saved_bytes(batch, n, e, heads) : XaSaved::floats(batch, n, e, heads) * 4 + 256;
 }
 size_t pio_cross_attend_ws_bytes(int batch, int n, int m, int e, int heads, int mode) {
-    (void)mode; (void)m;
-    return cross_attend_bwd_ws(batch, n, e, heads);
+    (void)m;
+    return mode == PIO_MODE_BF16 ? bf::xa_ws_bytes(batch, n, e, heads) : cross_attend_bwd_ws(batch, n, e, heads);
 }
 
 static int check_heads(int e, int heads, const char* who) {
@@ -441,6 +415,7 @@ int pio_cross_attend_fwd(const float* x_q, const float* kv, const uint8_t* pad, 
     PIO_CHECK_ARG(x_q && kv && y && w && saved && batch >= 0 && n >= 0 && m >= 0, "pio_cross_attend_fwd: bad arguments");
     PIO_TRY(check_heads(e, heads, "pio_cross_attend_fwd"));
     Ctx ctx(ws, ws_bytes, stream);
+    if (mode == PIO_MODE_BF16) return bf::cross_attend_fwd(ctx, x_q, kv, pad, y, w, saved, batch, n, m, e, heads, residual);
     return cross_attend_fwd(ctx, x_q, kv, pad, y, w, saved, batch, n, m, e, heads, residual);
 }
 
@@ -452,15 +427,18 @@ int pio_cross_attend_bwd(const float* dy, const float* x_q, const float* kv, con
     PIO_CHECK_ARG(dy && x_q && kv && dx_q && dkv && w && saved && g, "pio_cross_attend_bwd: bad arguments");
     PIO_TRY(check_heads(e, heads, "pio_cross_attend_bwd"));
     Ctx ctx(ws, ws_bytes, stream);
+    if (mode == PIO_MODE_BF16)
+        return bf::cross_attend_bwd(ctx, dy, x_q, kv, pad, dx_q, dkv, w, saved, g, accumulate, batch, n, m, e, heads, residual);
     return cross_attend_bwd(ctx, dy, x_q, kv, pad, dx_q, dkv, w, saved, g, accumulate, batch, n, m, e, heads, residual);
 }
 
 // ---- one self-attention layer
 size_t pio_self_attn_saved_bytes(int batch, int n, int c, int heads, int mode) {
-    (void)mode;
-    return SaSaved::floats(batch, n, c, heads) * 4 + 256;
+    return mode == PIO_MODE_BF16 ? bf::sa_saved_bytes(batch, n, c, heads) : SaSaved::floats(batch, n, c, heads) * 4 + 256;
 }
-size_t pio_self_attn_ws_bytes(int batch, int n, int c, int heads, int mode) { (void)mode; return self_attn_bwd_ws(batch, n, c, heads); }
+size_t pio_self_attn_ws_bytes(int batch, int n, int c, int heads, int mode) {
+    return mode == PIO_MODE_BF16 ? bf::sa_ws_bytes(batch, n, c, heads) : self_attn_bwd_ws(batch, n, c, heads);
+}
 
 int pio_self_attn_fwd(const float* x, float* y, const pio_attn_weights* w, void* saved, int batch, int n, int c, int heads,
                       int residual, int mode, void* ws, size_t ws_bytes, pio_stream_t stream) {
@@ -468,6 +446,7 @@ int pio_self_attn_fwd(const float* x, float* y, const pio_attn_weights* w, void*
     PIO_CHECK_ARG(x && y && w && saved && batch >= 0 && n >= 0, "pio_self_attn_fwd: bad arguments");
     PIO_TRY(check_heads(c, heads, "pio_self_attn_fwd"));
     Ctx ctx(ws, ws_bytes, stream);
+    if (mode == PIO_MODE_BF16) return bf::self_attn_fwd(ctx, x, y, w, saved, batch, n, c, heads, residual);
     return self_attn_fwd(ctx, x, y, w, saved, batch, n, c, heads, residual);
 }
 
@@ -478,17 +457,19 @@ int pio_self_attn_bwd(const float* dy, const float* x, float* dx, const pio_attn
     PIO_CHECK_ARG(dy && x && dx && w && saved && g, "pio_self_attn_bwd: bad arguments");
     PIO_TRY(check_heads(c, heads, "pio_self_attn_bwd"));
     Ctx ctx(ws, ws_bytes, stream);
+    if (mode == PIO_MODE_BF16) return bf::self_attn_bwd(ctx, dy, x, dx, w, saved, g, accumulate, batch, n, c, heads, residual);
     return self_attn_bwd(ctx, dy, x, dx, w, saved, g, accumulate, batch, n, c, heads, residual);
 }
 
 // ---- latent block
 size_t pio_latent_block_saved_bytes(int layers, int batch, int n, int c, int heads, int mode) {
-    (void)mode;
+    if (mode == PIO_MODE_BF16) return bf::block_saved_bytes(layers, batch, n, c, heads);
     BlockLayout L(batch, n, c, heads);
     return (size_t)layers * L.per_layer * 4 + 256;
 }
 size_t pio_latent_block_ws_bytes(int layers, int batch, int n, int c, int heads, int mode) {
-    (void)mode; (void)layers;
+    (void)layers;
+    if (mode == PIO_MODE_BF16) return bf::block_ws_bytes(batch, n, c, heads);
     const size_t r = (size_t)batch * n;
     return 2 * align_up(r * c * 4, 256) + std::max(self_attn_bwd_ws(batch, n, c, heads), mlp_bwd_ws(r, c)) + 1024;
 }
@@ -500,6 +481,7 @@ int pio_latent_block_fwd(const float* x, float* y, const pio_attn_weights* attn,
     PIO_CHECK_ARG(x && y && attn && mlp && saved && layers >= 1 && batch >= 0 && n >= 0, "pio_latent_block_fwd: bad arguments");
     PIO_TRY(check_heads(c, heads, "pio_latent_block_fwd"));
     Ctx ctx(ws, ws_bytes, stream);
+    if (mode == PIO_MODE_BF16) return bf::latent_block_fwd(ctx, x, y, attn, mlp, saved, layers, batch, n, c, heads);
     BlockLayout L(batch, n, c, heads);
     const int64_t rows = (int64_t)batch * n;
     const float* cur = x;
@@ -522,6 +504,8 @@ int pio_latent_block_bwd(const float* dy, const float* x, float* dx, const pio_a
     PIO_CHECK_ARG(dy && x && dx && attn && mlp && saved && attn_g && mlp_g && layers >= 1, "pio_latent_block_bwd: bad arguments");
     PIO_TRY(check_heads(c, heads, "pio_latent_block_bwd"));
     Ctx ctx(ws, ws_bytes, stream);
+    if (mode == PIO_MODE_BF16)
+        return bf::latent_block_bwd(ctx, dy, x, dx, attn, mlp, saved, attn_g, mlp_g, accumulate, layers, batch, n, c, heads);
     BlockLayout L(batch, n, c, heads);
     const int64_t rows = (int64_t)batch * n;
     PIO_TAKE(dmid, ctx, (size_t)rows * c, "pio_latent_block_bwd");
@@ -540,7 +524,7 @@ int pio_latent_block_bwd(const float* dy, const float* x, float* dx, const pio_a
 
 // ---- output linear
 size_t pio_linear_ws_bytes(int64_t rows, int c_in, int64_t c_out, int mode) {
-    (void)mode;
+    if (mode == PIO_MODE_BF16) return bf::linear_ws_bytes(rows, c_in, c_out);
     return dW_scratch(c_out, c_in, rows) + 1024;
 }
 
@@ -549,6 +533,7 @@ int pio_linear_fwd(const float* x, const float* w, const float* b, float* y, int
     PIO_TRY(check_mode(mode, "pio_linear_fwd"));
     PIO_CHECK_ARG(x && w && y && rows >= 0 && c_in > 0 && c_out > 0, "pio_linear_fwd: bad arguments");
     Ctx ctx(ws, ws_bytes, stream);
+    if (mode == PIO_MODE_BF16) return bf::linear_fwd(ctx, x, w, b, y, rows, c_in, c_out);
     return gemm_xwT(ctx, x, c_in, w, c_in, y, c_out, rows, c_out, c_in, b, nullptr, 0, 0, nullptr, 0);
 }
 
@@ -557,6 +542,7 @@ int pio_linear_bwd(const float* dy, const float* x, const float* w, float* dx, f
     PIO_TRY(check_mode(mode, "pio_linear_bwd"));
     PIO_CHECK_ARG(dy && x && w && dw && rows >= 0 && c_in > 0 && c_out > 0, "pio_linear_bwd: bad arguments");
     Ctx ctx(ws, ws_bytes, stream);
+    if (mode == PIO_MODE_BF16) return bf::linear_bwd(ctx, dy, x, w, dx, dw, db, accumulate, rows, c_in, c_out);
     if (dx) PIO_TRY(gemm_dyW(ctx, dy, c_out, w, c_in, dx, c_in, rows, c_out, c_in, 0, nullptr, 0, 0));
     return gemm_dW(ctx, dy, c_out, x, c_in, dw, db, rows, c_out, c_in, accumulate);
 }

@@ -1,0 +1,446 @@
+// PIO_MODE_BF16 pipelines of the fused operators: every contraction runs on the tcgen05 GEMM
+// (pio_gemm_tc.cu) with bf16 operands and fp32 accumulation; LayerNorm statistics, the residual
+// stream, softmax and all parameter gradients stay fp32.  Matrix weights arrive as bf16 shadows
+// (row pitch padded to 8 elements) in the same pio_*_weights structs; LayerNorm parameters and
+// biases stay fp32.  Saved activations that only feed GEMMs are kept in bf16.
+#include "pio_ops_common.cuh"
+
+namespace pio {
+namespace bf {
+
+using bf16 = __nv_bfloat16;
+
+struct ByteCarver {
+    char* base;
+    size_t off;
+    void* take(size_t bytes) {
+        void* r = base ? base + off : nullptr;
+        off += align_up(bytes, 256);
+        return r;
+    }
+    float* f32(size_t n) { return (float*)take(n * 4); }
+    bf16* b16(size_t n) { return (bf16*)take(n * 2); }
+};
+
+#define PIO_TAKE_BYTES(type, var, ctx, bytes, who)                                        \
+    type* var = (type*)(ctx).W.take((size_t)(bytes));                                     \
+    if (!var) {                                                                           \
+        set_error("%s: workspace too small (%zu bytes given)", who, (ctx).W.size);       \
+        return PIO_ERR_WORKSPACE;                                                         \
+    }
+
+static int tc_gemm(Ctx& c, const pio_gemm_bf16_desc& d) { return gemm_bf16(&d, c.rest(), c.rest_bytes(), c.st); }
+
+// y = act(x16 W16^T + bias) (+ residual)
+static int tc_xwT(Ctx& c, const bf16* x, int64_t ldx, const bf16* w, int64_t ldw, int64_t rows, int64_t n, int64_t k,
+                  float* c32, int64_t ldc32, bf16* c16, int64_t ldc16, const float* bias, const float* res, int64_t ldr,
+                  int act, bf16* aux, int64_t ldaux) {
+    pio_gemm_bf16_desc d{};
+    d.a = x; d.b = w; d.m = rows; d.n = n; d.k = k; d.lda = ldx; d.ldb = ldw; d.a_kmajor = 1; d.b_kmajor = 1;
+    d.c32 = c32; d.ldc32 = ldc32; d.c16 = c16; d.ldc16 = ldc16;
+    d.bias = bias; d.residual = res; d.ldr = ldr; d.act = act; d.aux16 = aux; d.ldaux = ldaux;
+    return tc_gemm(c, d);
+}
+// dx (+)= dy16[rows, nout] W16[nout, kin]   (B read MN-major, in place)
+static int tc_dyW(Ctx& c, const bf16* dy, int64_t lddy, const bf16* w, int64_t ldw, int64_t rows, int64_t nout, int64_t kin,
+                  float* c32, int64_t ldc32, bf16* c16, int64_t ldc16, int act, bf16* aux, int64_t ldaux, int accumulate) {
+    pio_gemm_bf16_desc d{};
+    d.a = dy; d.b = w; d.m = rows; d.n = kin; d.k = nout; d.lda = lddy; d.ldb = ldw; d.a_kmajor = 1; d.b_kmajor = 0;
+    d.c32 = c32; d.ldc32 = ldc32; d.c16 = c16; d.ldc16 = ldc16; d.act = act; d.aux16 = aux; d.ldaux = ldaux;
+    d.accumulate = accumulate;
+    return tc_gemm(c, d);
+}
+// dw[nout, kin] (+)= dy16[rows, nout]^T x16[rows, kin]   (both read MN-major, in place; split-K)
+static int tc_dW(Ctx& c, const bf16* dy, int64_t lddy, const bf16* x, int64_t ldx, float* dw, int64_t rows, int64_t nout,
+                 int64_t kin, int accumulate) {
+    pio_gemm_bf16_desc d{};
+    d.a = dy; d.b = x; d.m = nout; d.n = kin; d.k = rows; d.lda = lddy; d.ldb = ldx; d.a_kmajor = 0; d.b_kmajor = 0;
+    d.c32 = dw; d.ldc32 = kin; d.accumulate = accumulate;
+    return tc_gemm(c, d);
+}
+
+static size_t scratch_bytes(int64_t rows, int64_t nout, int64_t kin) {
+    return std::max(std::max(pio_gemm_bf16_ws_bytes(nout, kin, rows), colsum_ws_bytes(rows, (int)std::max(nout, kin))),
+                    pio_layernorm_bwd_ws_bytes(rows, (int)kin)) + 1024;
+}
+
+static int need_mult8(int v, const char* what, const char* who) {
+    PIO_CHECK_ARG(v % 8 == 0, "%s: %s = %d must be a multiple of 8 in bf16 mode", who, what, v);
+    return PIO_OK;
+}
+
+// ---------------------------------------------------------------- mlp
+struct MlpSaved {
+    float* stats;
+    bf16 *h0, *h1, *g;
+    size_t total;
+    MlpSaved(void* p, int64_t rows, int ch) {
+        ByteCarver k{(char*)p, 0};
+        stats = k.f32((size_t)rows * 2);
+        h0 = k.b16((size_t)rows * ch);
+        h1 = k.b16((size_t)rows * ch);
+        g = k.b16((size_t)rows * ch);
+        total = k.off;
+    }
+};
+size_t mlp_saved_bytes(int64_t rows, int ch) { return MlpSaved(nullptr, rows, ch).total + 256; }
+size_t mlp_ws_bytes(int64_t rows, int ch) {
+    return 2 * align_up((size_t)rows * ch * 2, 256) + align_up((size_t)rows * ch * 4, 256) + scratch_bytes(rows, ch, ch);
+}
+
+int mlp_fwd(Ctx& c, const float* x, float* y, const pio_mlp_weights* w, void* saved, int64_t rows, int ch, int residual) {
+    PIO_TRY(need_mult8(ch, "channels", "pio_mlp_fwd"));
+    MlpSaved s(saved, rows, ch);
+    PIO_TRY(layernorm_fwd_bf16(x, w->ln_w, w->ln_b, s.h0, ch, s.stats, rows, ch, LN_EPS, c.st));
+    PIO_TRY(tc_xwT(c, s.h0, ch, (const bf16*)w->w1, ch, rows, ch, ch, nullptr, 0, s.g, ch, w->b1, nullptr, 0, 1, s.h1, ch));
+    PIO_TRY(tc_xwT(c, s.g, ch, (const bf16*)w->w2, ch, rows, ch, ch, y, ch, nullptr, 0, w->b2, residual ? x : nullptr, ch, 0,
+                   nullptr, 0));
+    return PIO_OK;
+}
+
+int mlp_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_mlp_weights* w, const void* saved,
+            const pio_mlp_grads* g, int acc, int64_t rows, int ch, int residual) {
+    PIO_TRY(need_mult8(ch, "channels", "pio_mlp_bwd"));
+    MlpSaved s((void*)saved, rows, ch);
+    const size_t mark = c.W.off;
+    PIO_TAKE_BYTES(bf16, dy16, c, (size_t)rows * ch * 2, "pio_mlp_bwd");
+    PIO_TAKE_BYTES(bf16, dh1, c, (size_t)rows * ch * 2, "pio_mlp_bwd");
+    PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ch * 4, "pio_mlp_bwd");
+    PIO_TRY(cast_colsum_f32(dy, ch, dy16, ch, g->b2, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->w2, ch, rows, ch, ch, nullptr, 0, dh1, ch, 2, s.h1, ch, 0));
+    PIO_TRY(tc_dW(c, dy16, ch, s.g, ch, g->w2, rows, ch, ch, acc));
+    PIO_TRY(colsum_bf16(dh1, ch, g->b1, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(tc_dyW(c, dh1, ch, (const bf16*)w->w1, ch, rows, ch, ch, dh0, ch, nullptr, 0, 0, nullptr, 0, 0));
+    PIO_TRY(tc_dW(c, dh1, ch, s.h0, ch, g->w1, rows, ch, ch, acc));
+    PIO_TRY(pio_layernorm_bwd(dh0, x, s.stats, w->ln_w, residual ? dy : nullptr, dx, g->ln_w, g->ln_b, acc, rows, ch,
+                              c.rest(), c.rest_bytes(), c.st));
+    c.W.off = mark;
+    return PIO_OK;
+}
+
+// ---------------------------------------------------------------- kv projection
+struct KvSaved {
+    float* stats;
+    bf16* h0;
+    size_t total;
+    KvSaved(void* p, int64_t rows, int ckv) {
+        ByteCarver k{(char*)p, 0};
+        stats = k.f32((size_t)rows * 2);
+        h0 = k.b16((size_t)rows * pad8(ckv));
+        total = k.off;
+    }
+};
+size_t kv_saved_bytes(int64_t rows, int ckv) { return KvSaved(nullptr, rows, ckv).total + 256; }
+size_t kv_ws_bytes(int64_t rows, int ckv, int e) {
+    return align_up((size_t)rows * 2 * e * 2, 256) + align_up((size_t)rows * ckv * 4, 256) + scratch_bytes(rows, 2 * e, ckv);
+}
+
+static bool packed16(const void* wk, const void* wv, int e, int64_t ldw) {
+    return (const char*)wv == (const char*)wk + (size_t)e * ldw * 2;
+}
+
+int kv_project_fwd(Ctx& c, const float* x_kv, float* kv, const pio_attn_weights* w, void* saved, int64_t rows, int ckv, int e) {
+    PIO_TRY(need_mult8(e, "embed dim", "pio_kv_project_fwd"));
+    KvSaved s(saved, rows, ckv);
+    const int64_t ckp = pad8(ckv);
+    PIO_TRY(layernorm_fwd_bf16(x_kv, w->kv_ln_w, w->kv_ln_b, s.h0, ckp, s.stats, rows, ckv, LN_EPS, c.st));
+    if (packed16(w->wk, w->wv, e, ckp) && w->bv == w->bk + e) {
+        PIO_TRY(tc_xwT(c, s.h0, ckp, (const bf16*)w->wk, ckp, rows, 2 * e, ckv, kv, 2 * e, nullptr, 0, w->bk, nullptr, 0, 0,
+                       nullptr, 0));
+    } else {
+        PIO_TRY(tc_xwT(c, s.h0, ckp, (const bf16*)w->wk, ckp, rows, e, ckv, kv, 2 * e, nullptr, 0, w->bk, nullptr, 0, 0, nullptr, 0));
+        PIO_TRY(tc_xwT(c, s.h0, ckp, (const bf16*)w->wv, ckp, rows, e, ckv, kv + e, 2 * e, nullptr, 0, w->bv, nullptr, 0, 0,
+                       nullptr, 0));
+    }
+    return PIO_OK;
+}
+
+int kv_project_bwd(Ctx& c, const float* dkv, const float* x_kv, float* dx_kv, const pio_attn_weights* w, const void* saved,
+                   const pio_attn_grads* g, int acc, int64_t rows, int ckv, int e) {
+    PIO_TRY(need_mult8(e, "embed dim", "pio_kv_project_bwd"));
+    KvSaved s((void*)saved, rows, ckv);
+    const int64_t ckp = pad8(ckv);
+    const size_t mark = c.W.off;
+    PIO_TAKE_BYTES(bf16, dkv16, c, (size_t)rows * 2 * e * 2, "pio_kv_project_bwd");
+    PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ckv * 4, "pio_kv_project_bwd");
+    if (g->bv == g->bk + e) {
+        PIO_TRY(cast_colsum_f32(dkv, 2 * e, dkv16, 2 * e, g->bk, acc, rows, 2 * e, c.rest(), c.rest_bytes(), c.st));
+    } else {
+        PIO_TRY(cast_colsum_f32(dkv, 2 * e, dkv16, 2 * e, g->bk, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
+        PIO_TRY(cast_colsum_f32(dkv + e, 2 * e, dkv16 + e, 2 * e, g->bv, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
+    }
+    if (packed16(w->wk, w->wv, e, ckp)) {
+        PIO_TRY(tc_dyW(c, dkv16, 2 * e, (const bf16*)w->wk, ckp, rows, 2 * e, ckv, dh0, ckv, nullptr, 0, 0, nullptr, 0, 0));
+    } else {
+        PIO_TRY(tc_dyW(c, dkv16, 2 * e, (const bf16*)w->wk, ckp, rows, e, ckv, dh0, ckv, nullptr, 0, 0, nullptr, 0, 0));
+        PIO_TRY(tc_dyW(c, dkv16 + e, 2 * e, (const bf16*)w->wv, ckp, rows, e, ckv, dh0, ckv, nullptr, 0, 0, nullptr, 0, 1));
+    }
+    if (g->wv == g->wk + (size_t)e * ckv) {
+        PIO_TRY(tc_dW(c, dkv16, 2 * e, s.h0, ckp, g->wk, rows, 2 * e, ckv, acc));
+    } else {
+        PIO_TRY(tc_dW(c, dkv16, 2 * e, s.h0, ckp, g->wk, rows, e, ckv, acc));
+        PIO_TRY(tc_dW(c, dkv16 + e, 2 * e, s.h0, ckp, g->wv, rows, e, ckv, acc));
+    }
+    PIO_TRY(pio_layernorm_bwd(dh0, x_kv, s.stats, w->kv_ln_w, nullptr, dx_kv, g->kv_ln_w, g->kv_ln_b, acc, rows, ckv, c.rest(),
+                              c.rest_bytes(), c.st));
+    c.W.off = mark;
+    return PIO_OK;
+}
+
+// ---------------------------------------------------------------- attention helpers
+static void fill_attn(pio_attn_desc& a, const float* q, int64_t q_rs, const float* k, const float* v, int64_t kv_rs,
+                      const uint8_t* pad, float* o, float* lse, int batch, int heads, int n, int m, int e) {
+    a.q = q; a.k = k; a.v = v; a.pad = pad; a.o = o; a.lse = lse;
+    a.q_rs = q_rs; a.q_bs = (int64_t)n * q_rs;
+    a.k_rs = kv_rs; a.k_bs = (int64_t)m * kv_rs;
+    a.v_rs = kv_rs; a.v_bs = (int64_t)m * kv_rs;
+    a.o_rs = e; a.o_bs = (int64_t)n * e;
+    a.batch = batch; a.heads = heads; a.n = n; a.m = m; a.dh = e / heads;
+    a.scale = 1.0f / sqrtf((float)(e / heads));
+}
+
+// ---------------------------------------------------------------- query side of cross-attention
+struct XaSaved {
+    float *stats, *q, *o, *lse;
+    bf16 *hq, *o16;
+    size_t total;
+    XaSaved(void* p, int batch, int n, int e, int heads) {
+        const size_t r = (size_t)batch * n;
+        ByteCarver k{(char*)p, 0};
+        stats = k.f32(r * 2);
+        hq = k.b16(r * e);
+        q = k.f32(r * e);
+        o = k.f32(r * e);
+        o16 = k.b16(r * e);
+        lse = k.f32((size_t)batch * heads * n);
+        total = k.off;
+    }
+};
+size_t xa_saved_bytes(int batch, int n, int e, int heads) { return XaSaved(nullptr, batch, n, e, heads).total + 256; }
+size_t xa_ws_bytes(int batch, int n, int e, int heads) {
+    const size_t r = (size_t)batch * n;
+    return 2 * align_up(r * e * 2, 256) + 3 * align_up(r * e * 4, 256) + align_up((size_t)batch * heads * n * 4, 256) +
+           scratch_bytes(r, e, e);
+}
+
+int cross_attend_fwd(Ctx& c, const float* x_q, const float* kv, const uint8_t* pad, float* y, const pio_attn_weights* w,
+                     void* saved, int batch, int n, int m, int e, int heads, int residual) {
+    PIO_TRY(need_mult8(e, "embed dim", "pio_cross_attend_fwd"));
+    XaSaved s(saved, batch, n, e, heads);
+    const int64_t rows = (int64_t)batch * n;
+    PIO_TRY(layernorm_fwd_bf16(x_q, w->ln_w, w->ln_b, s.hq, e, s.stats, rows, e, LN_EPS, c.st));
+    PIO_TRY(tc_xwT(c, s.hq, e, (const bf16*)w->wq, e, rows, e, e, s.q, e, nullptr, 0, w->bq, nullptr, 0, 0, nullptr, 0));
+    pio_attn_desc a{};
+    fill_attn(a, s.q, e, kv, kv + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
+    AttnBf16Out ex;
+    ex.o16 = s.o16;
+    PIO_TRY(attn_fwd_simt(&a, c.st, &ex));
+    PIO_TRY(tc_xwT(c, s.o16, e, (const bf16*)w->wo, e, rows, e, e, y, e, nullptr, 0, w->bo, residual ? x_q : nullptr, e, 0,
+                   nullptr, 0));
+    return PIO_OK;
+}
+
+int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv, const uint8_t* pad, float* dx_q, float* dkv,
+                     const pio_attn_weights* w, const void* saved, const pio_attn_grads* g, int acc, int batch, int n, int m,
+                     int e, int heads, int residual) {
+    PIO_TRY(need_mult8(e, "embed dim", "pio_cross_attend_bwd"));
+    XaSaved s((void*)saved, batch, n, e, heads);
+    const int64_t rows = (int64_t)batch * n;
+    const size_t mark = c.W.off;
+    PIO_TAKE_BYTES(bf16, dy16, c, (size_t)rows * e * 2, "pio_cross_attend_bwd");
+    PIO_TAKE_BYTES(bf16, dq16, c, (size_t)rows * e * 2, "pio_cross_attend_bwd");
+    PIO_TAKE_BYTES(float, d_o, c, (size_t)rows * e * 4, "pio_cross_attend_bwd");
+    PIO_TAKE_BYTES(float, dq, c, (size_t)rows * e * 4, "pio_cross_attend_bwd");
+    PIO_TAKE_BYTES(float, dhq, c, (size_t)rows * e * 4, "pio_cross_attend_bwd");
+    PIO_TAKE_BYTES(float, delta, c, (size_t)batch * heads * n * 4, "pio_cross_attend_bwd");
+    PIO_TRY(cast_colsum_f32(dy, e, dy16, e, g->bo, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)w->wo, e, rows, e, e, d_o, e, nullptr, 0, 0, nullptr, 0, 0));
+    PIO_TRY(tc_dW(c, dy16, e, s.o16, e, g->wo, rows, e, e, acc));
+    pio_attn_bwd_desc b{};
+    fill_attn(b.fwd, s.q, e, kv, kv + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
+    b.d_o = d_o; b.dq = dq; b.dk = dkv; b.dv = dkv + e; b.delta = delta;
+    AttnBf16Out ex;
+    ex.dq16 = dq16;
+    PIO_TRY(attn_bwd_simt(&b, c.st, &ex));
+    PIO_TRY(colsum_bf16(dq16, e, g->bq, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(tc_dyW(c, dq16, e, (const bf16*)w->wq, e, rows, e, e, dhq, e, nullptr, 0, 0, nullptr, 0, 0));
+    PIO_TRY(tc_dW(c, dq16, e, s.hq, e, g->wq, rows, e, e, acc));
+    PIO_TRY(pio_layernorm_bwd(dhq, x_q, s.stats, w->ln_w, residual ? dy : nullptr, dx_q, g->ln_w, g->ln_b, acc, rows, e,
+                              c.rest(), c.rest_bytes(), c.st));
+    c.W.off = mark;
+    return PIO_OK;
+}
+
+// ---------------------------------------------------------------- self-attention layer
+struct SaSaved {
+    float *stats, *qkv, *o, *lse;
+    bf16 *h0, *o16;
+    size_t total;
+    SaSaved(void* p, int batch, int n, int ch, int heads) {
+        const size_t r = (size_t)batch * n;
+        ByteCarver k{(char*)p, 0};
+        stats = k.f32(r * 2);
+        h0 = k.b16(r * ch);
+        qkv = k.f32(3 * r * ch);
+        o = k.f32(r * ch);
+        o16 = k.b16(r * ch);
+        lse = k.f32((size_t)batch * heads * n);
+        total = k.off;
+    }
+};
+size_t sa_saved_bytes(int batch, int n, int ch, int heads) { return SaSaved(nullptr, batch, n, ch, heads).total + 256; }
+size_t sa_ws_bytes(int batch, int n, int ch, int heads) {
+    const size_t r = (size_t)batch * n;
+    return align_up(r * ch * 2, 256) + align_up(3 * r * ch * 2, 256) + 2 * align_up(r * ch * 4, 256) +
+           align_up(3 * r * ch * 4, 256) + align_up((size_t)batch * heads * n * 4, 256) + scratch_bytes(r, 3 * ch, ch);
+}
+
+static int check_packed_self(const pio_attn_weights* w, int ch, const char* who) {
+    const char* q = (const char*)w->wq;
+    PIO_CHECK_ARG((const char*)w->wk == q + (size_t)ch * ch * 2 && (const char*)w->wv == q + 2 * (size_t)ch * ch * 2 &&
+                      w->bk == w->bq + ch && w->bv == w->bq + 2 * ch,
+                  "%s: bf16 mode expects the packed (3C,C) in-projection of a self-attention layer", who);
+    return PIO_OK;
+}
+
+int self_attn_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* w, void* saved, int batch, int n, int ch, int heads,
+                  int residual) {
+    PIO_TRY(need_mult8(ch, "channels", "pio_self_attn_fwd"));
+    PIO_TRY(check_packed_self(w, ch, "pio_self_attn_fwd"));
+    SaSaved s(saved, batch, n, ch, heads);
+    const int64_t rows = (int64_t)batch * n;
+    PIO_TRY(layernorm_fwd_bf16(x, w->ln_w, w->ln_b, s.h0, ch, s.stats, rows, ch, LN_EPS, c.st));
+    PIO_TRY(tc_xwT(c, s.h0, ch, (const bf16*)w->wq, ch, rows, 3 * ch, ch, s.qkv, 3 * ch, nullptr, 0, w->bq, nullptr, 0, 0,
+                   nullptr, 0));
+    pio_attn_desc a{};
+    fill_attn(a, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
+    AttnBf16Out ex;
+    ex.o16 = s.o16;
+    PIO_TRY(attn_fwd_simt(&a, c.st, &ex));
+    PIO_TRY(tc_xwT(c, s.o16, ch, (const bf16*)w->wo, ch, rows, ch, ch, y, ch, nullptr, 0, w->bo, residual ? x : nullptr, ch, 0,
+                   nullptr, 0));
+    return PIO_OK;
+}
+
+int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_attn_weights* w, const void* saved,
+                  const pio_attn_grads* g, int acc, int batch, int n, int ch, int heads, int residual) {
+    PIO_TRY(need_mult8(ch, "channels", "pio_self_attn_bwd"));
+    PIO_TRY(check_packed_self(w, ch, "pio_self_attn_bwd"));
+    PIO_CHECK_ARG(g->wk == g->wq + (size_t)ch * ch && g->wv == g->wq + 2 * (size_t)ch * ch && g->bk == g->bq + ch &&
+                      g->bv == g->bq + 2 * ch,
+                  "pio_self_attn_bwd: packed (3C,C) gradient storage expected");
+    SaSaved s((void*)saved, batch, n, ch, heads);
+    const int64_t rows = (int64_t)batch * n;
+    const size_t mark = c.W.off;
+    PIO_TAKE_BYTES(bf16, dy16, c, (size_t)rows * ch * 2, "pio_self_attn_bwd");
+    PIO_TAKE_BYTES(bf16, dqkv16, c, (size_t)rows * 3 * ch * 2, "pio_self_attn_bwd");
+    PIO_TAKE_BYTES(float, d_o, c, (size_t)rows * ch * 4, "pio_self_attn_bwd");
+    PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ch * 4, "pio_self_attn_bwd");
+    PIO_TAKE_BYTES(float, dqkv, c, (size_t)rows * 3 * ch * 4, "pio_self_attn_bwd");
+    PIO_TAKE_BYTES(float, delta, c, (size_t)batch * heads * n * 4, "pio_self_attn_bwd");
+    PIO_TRY(cast_colsum_f32(dy, ch, dy16, ch, g->bo, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->wo, ch, rows, ch, ch, d_o, ch, nullptr, 0, 0, nullptr, 0, 0));
+    PIO_TRY(tc_dW(c, dy16, ch, s.o16, ch, g->wo, rows, ch, ch, acc));
+    pio_attn_bwd_desc b{};
+    fill_attn(b.fwd, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
+    b.d_o = d_o; b.dq = dqkv; b.dk = dqkv + ch; b.dv = dqkv + 2 * ch; b.delta = delta;
+    AttnBf16Out ex;
+    ex.dq16 = dqkv16; ex.dk16 = dqkv16 + ch; ex.dv16 = dqkv16 + 2 * ch;
+    PIO_TRY(attn_bwd_simt(&b, c.st, &ex));
+    PIO_TRY(colsum_bf16(dqkv16, 3 * ch, g->bq, acc, rows, 3 * ch, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(tc_dyW(c, dqkv16, 3 * ch, (const bf16*)w->wq, ch, rows, 3 * ch, ch, dh0, ch, nullptr, 0, 0, nullptr, 0, 0));
+    PIO_TRY(tc_dW(c, dqkv16, 3 * ch, s.h0, ch, g->wq, rows, 3 * ch, ch, acc));
+    PIO_TRY(pio_layernorm_bwd(dh0, x, s.stats, w->ln_w, residual ? dy : nullptr, dx, g->ln_w, g->ln_b, acc, rows, ch, c.rest(),
+                              c.rest_bytes(), c.st));
+    c.W.off = mark;
+    return PIO_OK;
+}
+
+// ---------------------------------------------------------------- latent block
+struct BlockLayout {
+    size_t sa, xmid, mlp, xnext, per_layer;  // byte offsets within a layer's slab
+    BlockLayout(int batch, int n, int ch, int heads) {
+        const size_t r = (size_t)batch * n;
+        const size_t act = align_up(r * ch * 4, 256);
+        sa = 0;
+        xmid = sa + align_up(sa_saved_bytes(batch, n, ch, heads), 256);
+        mlp = xmid + act;
+        xnext = mlp + align_up(mlp_saved_bytes(r, ch), 256);
+        per_layer = xnext + act;
+    }
+};
+size_t block_saved_bytes(int layers, int batch, int n, int ch, int heads) {
+    return (size_t)layers * BlockLayout(batch, n, ch, heads).per_layer + 256;
+}
+size_t block_ws_bytes(int batch, int n, int ch, int heads) {
+    const size_t r = (size_t)batch * n;
+    return 2 * align_up(r * ch * 4, 256) + std::max(sa_ws_bytes(batch, n, ch, heads), mlp_ws_bytes(r, ch)) + 1024;
+}
+
+int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,
+                     int layers, int batch, int n, int ch, int heads) {
+    BlockLayout L(batch, n, ch, heads);
+    const int64_t rows = (int64_t)batch * n;
+    const float* cur = x;
+    for (int s = 0; s < layers; ++s) {
+        char* slab = (char*)saved + (size_t)s * L.per_layer;
+        float* xmid = (float*)(slab + L.xmid);
+        float* out = (s == layers - 1) ? y : (float*)(slab + L.xnext);
+        PIO_TRY(self_attn_fwd(c, cur, xmid, &attn[s], slab + L.sa, batch, n, ch, heads, 1));
+        PIO_TRY(mlp_fwd(c, xmid, out, &mlp[s], slab + L.mlp, rows, ch, 1));
+        cur = out;
+    }
+    return PIO_OK;
+}
+
+int latent_block_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_attn_weights* attn, const pio_mlp_weights* mlp,
+                     const void* saved, const pio_attn_grads* attn_g, const pio_mlp_grads* mlp_g, int acc, int layers,
+                     int batch, int n, int ch, int heads) {
+    BlockLayout L(batch, n, ch, heads);
+    const int64_t rows = (int64_t)batch * n;
+    PIO_TAKE_BYTES(float, dmid, c, (size_t)rows * ch * 4, "pio_latent_block_bwd");
+    PIO_TAKE_BYTES(float, dcur, c, (size_t)rows * ch * 4, "pio_latent_block_bwd");
+    const float* grad = dy;
+    for (int s = layers - 1; s >= 0; --s) {
+        const char* slab = (const char*)saved + (size_t)s * L.per_layer;
+        const float* x_in = (s == 0) ? x : (const float*)((const char*)saved + (size_t)(s - 1) * L.per_layer + L.xnext);
+        PIO_TRY(mlp_bwd(c, grad, (const float*)(slab + L.xmid), dmid, &mlp[s], slab + L.mlp, &mlp_g[s], acc, rows, ch, 1));
+        float* out = (s == 0) ? dx : dcur;
+        PIO_TRY(self_attn_bwd(c, dmid, x_in, out, &attn[s], slab + L.sa, &attn_g[s], acc, batch, n, ch, heads, 1));
+        grad = out;
+    }
+    return PIO_OK;
+}
+
+// ---------------------------------------------------------------- output linear
+size_t linear_ws_bytes(int64_t rows, int c_in, int64_t c_out) {
+    return align_up((size_t)rows * pad8(c_out) * 2, 256) + align_up((size_t)rows * pad8(c_in) * 2, 256) +
+           scratch_bytes(rows, c_out, c_in);
+}
+
+int linear_fwd(Ctx& c, const float* x, const float* w16, const float* b, float* y, int64_t rows, int c_in, int64_t c_out) {
+    const int64_t cip = pad8(c_in);
+    const size_t mark = c.W.off;
+    PIO_TAKE_BYTES(bf16, x16, c, (size_t)rows * cip * 2, "pio_linear_fwd");
+    PIO_TRY(cast_bf16(x, x16, rows, c_in, c_in, cip, c.st));
+    PIO_TRY(tc_xwT(c, x16, cip, (const bf16*)w16, cip, rows, c_out, c_in, y, c_out, nullptr, 0, b, nullptr, 0, 0, nullptr, 0));
+    c.W.off = mark;
+    return PIO_OK;
+}
+
+int linear_bwd(Ctx& c, const float* dy, const float* x, const float* w16, float* dx, float* dw, float* db, int acc, int64_t rows,
+               int c_in, int64_t c_out) {
+    const int64_t cip = pad8(c_in), cop = pad8(c_out);
+    const size_t mark = c.W.off;
+    PIO_TAKE_BYTES(bf16, dy16, c, (size_t)rows * cop * 2, "pio_linear_bwd");
+    PIO_TAKE_BYTES(bf16, x16, c, (size_t)rows * cip * 2, "pio_linear_bwd");
+    PIO_TRY(cast_colsum_f32(dy, c_out, dy16, cop, db, acc, rows, (int)c_out, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(cast_bf16(x, x16, rows, c_in, c_in, cip, c.st));
+    if (dx) PIO_TRY(tc_dyW(c, dy16, cop, (const bf16*)w16, cip, rows, c_out, c_in, dx, c_in, nullptr, 0, 0, nullptr, 0, 0));
+    PIO_TRY(tc_dW(c, dy16, cop, x16, cip, dw, rows, c_out, c_in, acc));
+    c.W.off = mark;
+    return PIO_OK;
+}
+
+}  // namespace bf
+}  // namespace pio

@@ -1,0 +1,102 @@
+// Shared plumbing of the fused operators (fp32 and bf16 pipelines).
+#pragma once
+#include "pio_common.cuh"
+
+namespace pio {
+
+// optional bf16 copies written by the fp32 attention kernels (same element strides as the fp32 tensors)
+struct AttnBf16Out {
+    __nv_bfloat16* o16 = nullptr;
+    __nv_bfloat16* dq16 = nullptr;
+    __nv_bfloat16* dk16 = nullptr;
+    __nv_bfloat16* dv16 = nullptr;
+};
+int attn_fwd_simt(const pio_attn_desc* d, cudaStream_t st, const AttnBf16Out* extra = nullptr);
+int attn_bwd_simt(const pio_attn_bwd_desc* d, cudaStream_t st, const AttnBf16Out* extra = nullptr);
+
+int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream_t st);
+int cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_src, int64_t ld_dst, cudaStream_t st);
+
+// bf16 helpers (pio_bf16_aux.cu)
+int layernorm_fwd_bf16(const float* x, const float* w, const float* b, __nv_bfloat16* y, int64_t ldy, float* stats,
+                       int64_t rows, int c, float eps, cudaStream_t st);
+// dst16 (optional) = bf16(src); colsum (optional, c floats) (+)= column sums of src.  scratch: colsum_ws_bytes
+int cast_colsum_f32(const float* src, int64_t ld_src, __nv_bfloat16* dst16, int64_t ld_dst, float* colsum, int accumulate,
+                    int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t st);
+int colsum_bf16(const __nv_bfloat16* src, int64_t ld_src, float* colsum, int accumulate, int64_t rows, int c, void* ws,
+                size_t ws_bytes, cudaStream_t st);
+size_t colsum_ws_bytes(int64_t rows, int c);
+
+constexpr float LN_EPS = 1e-5f;  // nn.LayerNorm default, used everywhere in the reference
+
+struct Ctx {
+    cudaStream_t st;
+    Workspace W;
+    Ctx(void* ws, size_t n, pio_stream_t s) : st((cudaStream_t)s), W(ws, n) {}
+    void* rest() { return W.base ? W.base + align_up(W.off, 256) : nullptr; }
+    size_t rest_bytes() {
+        const size_t o = align_up(W.off, 256);
+        return (W.base && o < W.size) ? W.size - o : 0;
+    }
+};
+
+#define PIO_TAKE(var, ctx, count, who)                                                     \
+    float* var = (ctx).W.takef((size_t)(count));                                           \
+    if (!var) {                                                                            \
+        set_error("%s: workspace too small (%zu bytes given)", who, (ctx).W.size);        \
+        return PIO_ERR_WORKSPACE;                                                          \
+    }
+
+// carve 256-byte aligned arrays out of an opaque saved buffer (nullptr base = size query)
+struct Carver {
+    float* base;
+    size_t off;
+    float* take(size_t n) {
+        float* r = base ? base + off : nullptr;
+        off += (n + 63) / 64 * 64;
+        return r;
+    }
+};
+
+
+static inline int64_t pad8(int64_t x) { return (x + 7) / 8 * 8; }
+
+// PIO_MODE_BF16 pipelines (pio_ops_bf16.cu)
+namespace bf {
+size_t mlp_saved_bytes(int64_t rows, int ch);
+size_t mlp_ws_bytes(int64_t rows, int ch);
+int mlp_fwd(Ctx& c, const float* x, float* y, const pio_mlp_weights* w, void* saved, int64_t rows, int ch, int residual);
+int mlp_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_mlp_weights* w, const void* saved,
+            const pio_mlp_grads* g, int acc, int64_t rows, int ch, int residual);
+size_t kv_saved_bytes(int64_t rows, int ckv);
+size_t kv_ws_bytes(int64_t rows, int ckv, int e);
+int kv_project_fwd(Ctx& c, const float* x_kv, float* kv, const pio_attn_weights* w, void* saved, int64_t rows, int ckv, int e);
+int kv_project_bwd(Ctx& c, const float* dkv, const float* x_kv, float* dx_kv, const pio_attn_weights* w, const void* saved,
+                   const pio_attn_grads* g, int acc, int64_t rows, int ckv, int e);
+size_t xa_saved_bytes(int batch, int n, int e, int heads);
+size_t xa_ws_bytes(int batch, int n, int e, int heads);
+int cross_attend_fwd(Ctx& c, const float* x_q, const float* kv, const uint8_t* pad, float* y, const pio_attn_weights* w,
+                     void* saved, int batch, int n, int m, int e, int heads, int residual);
+int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv, const uint8_t* pad, float* dx_q, float* dkv,
+                     const pio_attn_weights* w, const void* saved, const pio_attn_grads* g, int acc, int batch, int n, int m,
+                     int e, int heads, int residual);
+size_t sa_saved_bytes(int batch, int n, int ch, int heads);
+size_t sa_ws_bytes(int batch, int n, int ch, int heads);
+int self_attn_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* w, void* saved, int batch, int n, int ch, int heads,
+                  int residual);
+int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_attn_weights* w, const void* saved,
+                  const pio_attn_grads* g, int acc, int batch, int n, int ch, int heads, int residual);
+size_t block_saved_bytes(int layers, int batch, int n, int ch, int heads);
+size_t block_ws_bytes(int batch, int n, int ch, int heads);
+int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,
+                     int layers, int batch, int n, int ch, int heads);
+int latent_block_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_attn_weights* attn, const pio_mlp_weights* mlp,
+                     const void* saved, const pio_attn_grads* attn_g, const pio_mlp_grads* mlp_g, int acc, int layers,
+                     int batch, int n, int ch, int heads);
+size_t linear_ws_bytes(int64_t rows, int c_in, int64_t c_out);
+int linear_fwd(Ctx& c, const float* x, const float* w16, const float* b, float* y, int64_t rows, int c_in, int64_t c_out);
+int linear_bwd(Ctx& c, const float* dy, const float* x, const float* w16, float* dx, float* dw, float* db, int acc, int64_t rows,
+               int c_in, int64_t c_out);
+}  // namespace bf
+
+}  // namespace pio

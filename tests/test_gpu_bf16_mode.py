@@ -1,0 +1,119 @@
+"""PIO_MODE_BF16 (tcgen05 GEMMs, bf16 operands, fp32 accumulate / residual stream) against the
+fp32 references: north_star tolerance rel 1e-2, measured as max-abs error over the tensor's
+largest magnitude."""
+import pytest
+import torch
+
+from conftest import load_golden
+from gpu_util import BF16_TOL, assert_rel, rel_err
+from oracle import perceiver_oracle as O
+from test_dropin_api import build_from_meta
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+GRAD_TOL = 3e-2  # gradients pass through up to ~40 bf16 contractions; logits/loss keep 1e-2
+
+
+@pytest.fixture(autouse=True)
+def bf16_mode():
+    import perceiver
+    perceiver.set_compute_mode("bf16")
+    yield
+    perceiver.set_compute_mode("fp32")
+
+
+def _check_grads(model, ref_grads, tol):
+    worst = ("", 0.0)
+    for k, p in model.named_parameters():
+        g = ref_grads.get(k)
+        if g is None or g.abs().max() < 1e-10:
+            continue
+        assert p.grad is not None, k
+        assert torch.isfinite(p.grad).all(), k
+        e = rel_err(p.grad, g)
+        if e > worst[1]:
+            worst = (k, e)
+    assert worst[1] <= tol, f"worst grad {worst}"
+
+
+@pytest.mark.parametrize("name", ["img_tiny", "img_rgb_1layer", "mlm_tiny", "mlm_short_l", "seqclf_tiny"])
+def test_golden_bf16(name):
+    import perceiver
+    meta, a, sd, grads = load_golden(name)
+    model = build_from_meta(meta)
+    model.load_state_dict(sd)
+    model = model.to(DEV)
+    if meta["kind"] == "image":
+        logits = model(a["x"].to(DEV))
+        loss = perceiver.cross_entropy(logits, a["y"].to(DEV))
+    elif meta.get("clf_classes") is None:
+        l = a["ids_masked"].shape[1]
+        lat, pm = model[0](a["ids_masked"].to(DEV), a["pad"].to(DEV))
+        logits = model[1](lat, pm, num_queries=l)
+        loss = perceiver.cross_entropy(logits, a["labels"].to(DEV))
+    else:
+        logits = model(a["ids"].to(DEV), a["pad"].to(DEV))
+        loss = perceiver.cross_entropy(logits, a["y"].to(DEV))
+    loss.backward()
+    assert_rel(logits, a["logits"], BF16_TOL, "logits")
+    assert_rel(loss, a["loss"], BF16_TOL, "loss")
+    _check_grads(model, grads, GRAD_TOL)
+
+
+def _vs_oracle(kind, model, x, pad, target, kw):
+    import perceiver
+    sd_cpu = {k: v.detach().clone().requires_grad_(v.is_floating_point()) for k, v in model.state_dict().items()}
+    ref_logits = O.perceiver_io(sd_cpu, x, pad, kind=kind, **kw)
+    ref_loss = O.cross_entropy(ref_logits, target)
+    ref_loss.backward()
+    model = model.to(DEV)
+    got = model(x.to(DEV), pad.to(DEV)) if pad is not None else model(x.to(DEV))
+    loss = perceiver.cross_entropy(got, target.to(DEV))
+    loss.backward()
+    assert_rel(got, ref_logits, BF16_TOL, "logits")
+    assert_rel(loss, ref_loss, BF16_TOL, "loss")
+    _check_grads(model, {k: v.grad for k, v in sd_cpu.items() if v.grad is not None}, GRAD_TOL)
+
+
+def test_config1_mnist_shape_bf16():
+    from perceiver import ClassificationOutputAdapter, ImageInputAdapter, PerceiverDecoder, PerceiverEncoder, PerceiverIO
+    torch.manual_seed(0)
+    enc = PerceiverEncoder(ImageInputAdapter((28, 28, 1), 32), (32, 128), 3, 4, 4, 3)
+    dec = PerceiverDecoder(ClassificationOutputAdapter(10, num_output_channels=128), (32, 128), 1)
+    x = torch.rand(16, 28, 28, 1) * 2 - 1
+    y = torch.randint(0, 10, (16,))
+    _vs_oracle("image", PerceiverIO(enc, dec), x, None, y,
+               dict(num_layers=3, cross_heads=4, self_heads=4, sa_layers=3, dec_heads=1))
+
+
+def test_config2_mlm_shape_bf16():
+    from perceiver import PerceiverDecoder, PerceiverEncoder, PerceiverIO, TextInputAdapter, TextOutputAdapter
+    torch.manual_seed(0)
+    enc = PerceiverEncoder(TextInputAdapter(10003, 512, 256), (64, 256), 3, 4, 4, 6)
+    dec = PerceiverDecoder(TextOutputAdapter(10003, 512, 256), (64, 256), 4)
+    b = 4
+    ids = torch.randint(3, 10003, (b, 512))
+    lens = torch.randint(128, 513, (b,))
+    lens[0] = 512
+    pad = torch.arange(512)[None, :] >= lens[:, None]
+    ids[pad] = 0
+    labels = torch.full((b, 512), -100, dtype=torch.long)
+    sel = (torch.rand(b, 512) < 0.15) & ~pad
+    labels[sel] = ids[sel]
+    _vs_oracle("text", PerceiverIO(enc, dec), ids, pad, labels,
+               dict(num_layers=3, cross_heads=4, self_heads=4, sa_layers=6, dec_heads=4))
+
+
+def test_weight_shadow_follows_parameter_updates():
+    """The bf16 shadows are keyed on the parameter version: an optimizer step must be visible."""
+    from perceiver import mlp
+    torch.manual_seed(1)
+    ff = mlp(32).to(DEV)
+    x = torch.randn(4, 8, 32, device=DEV)
+    y0 = ff(x)
+    with torch.no_grad():
+        ff[1].weight.mul_(2.0)
+    y1 = ff(x)
+    assert rel_err(y1, y0) > 1e-2
+    sd = {"module." + k: v.cpu() for k, v in ff.state_dict().items()}
+    assert_rel(y1, O.mlp_residual(sd, "", x.cpu()) - x.cpu(), BF16_TOL, "after update")
