@@ -39,27 +39,30 @@ def _saved(nbytes, device):
     return torch.empty(int(nbytes), dtype=torch.uint8, device=device)
 
 
-_shadow = {}
-
-
-def invalidate_weight_cache():
-    """Drop the bf16 weight shadows (only needed after writing to ``param.data`` directly, which
-    does not bump the version counter the cache keys on)."""
-    _shadow.clear()
+def invalidate_weight_cache(module=None):
+    """Drop bf16 weight shadows (only needed after writing through ``param.data``, which does not
+    bump the version counter the shadows are keyed on)."""
+    if module is not None:
+        for p in module.parameters():
+            if hasattr(p, "_pio_w16"):
+                del p._pio_w16
 
 
 def _w16(w):
-    """bf16 shadow of a 2-D fp32 weight, row pitch padded to 8 elements (TMA), refreshed whenever the
-    parameter's version counter moves (optimizer step, load_state_dict)."""
-    key = (w._version, tuple(w.shape), w.device)
-    hit = _shadow.get(w.data_ptr())
-    if hit is not None and hit[0] == key:
-        return hit[1]
+    """bf16 shadow of a 2-D fp32 weight, row pitch padded to 8 elements (TMA).  The shadow lives on
+    the parameter object itself and is rebuilt whenever the parameter's version counter moves
+    (optimizer step, load_state_dict, .to())."""
+    hit = getattr(w, "_pio_w16", None)
+    if hit is not None and hit[0] == w._version and hit[1] == w.data_ptr():
+        return hit[2]
     rows, cols = w.shape
     ld = (cols + 7) // 8 * 8
     out = torch.empty(rows, ld, dtype=torch.bfloat16, device=w.device)
     N.check(N.lib().pio_cast_bf16(w.data_ptr(), out.data_ptr(), rows, cols, cols, ld, N.stream_ptr(w.device)), "pio_cast_bf16")
-    _shadow[w.data_ptr()] = (key, out)
+    try:
+        w._pio_w16 = (w._version, w.data_ptr(), out)
+    except Exception:
+        pass
     return out
 
 
@@ -67,7 +70,7 @@ def _mat(w, mode):
     """the matrix operand the kernels read in this mode: the fp32 parameter or its bf16 shadow"""
     if w is None or mode == N.MODE_FP32:
         return w
-    return _w16(w.detach())
+    return _w16(w)
 
 
 def _mha_ptrs(w_packed, w_q, w_k, w_v, bias, e):
@@ -201,10 +204,12 @@ class MlpFn(torch.autograd.Function):
         saved = _saved(L.pio_mlp_saved_bytes(rows, c, mode), x.device)
         ws = N.workspace(L.pio_mlp_ws_bytes(rows, c, mode), x.device)
         y = torch.empty_like(x)
-        w = N.mlp_struct(**dict(zip(N.MlpWeights._names, _mlp_operands(params, mode))))
+        ops = _mlp_operands(params, mode)
+        w = N.mlp_struct(**dict(zip(N.MlpWeights._names, ops)))
         N.check(L.pio_mlp_fwd(x.data_ptr(), y.data_ptr(), byref(w), saved.data_ptr(), rows, c, int(residual), mode,
                               ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_mlp_fwd")
         ctx.save_for_backward(x, *params)
+        ctx.wstruct, ctx.keep = w, ops
         ctx.saved_buf = saved
         ctx.meta = (rows, c, int(residual), mode)
         return y
@@ -219,7 +224,7 @@ class MlpFn(torch.autograd.Function):
         grads = [torch.empty_like(p) for p in params]
         dx = torch.empty_like(x)
         ws = N.workspace(L.pio_mlp_ws_bytes(rows, c, mode), x.device)
-        w = N.mlp_struct(**dict(zip(N.MlpWeights._names, _mlp_operands(params, mode))))
+        w = ctx.wstruct
         g = N.mlp_struct(**dict(zip(N.MlpWeights._names, grads)))
         N.check(L.pio_mlp_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g), 0,
                               rows, c, residual, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_mlp_bwd")
@@ -242,8 +247,10 @@ class KVProjectFn(torch.autograd.Function):
         rows = b * m
         mode = get_compute_mode()
         L = N.lib()
-        _, wk, wv, _, bk, bv = _mha_ptrs(_mat(w_packed, mode), None, _mat(w_k, mode), _mat(w_v, mode), bias, e)
+        mats = (_mat(w_packed, mode), _mat(w_k, mode), _mat(w_v, mode))
+        _, wk, wv, _, bk, bv = _mha_ptrs(mats[0], None, mats[1], mats[2], bias, e)
         w = N.attn_struct(wk=wk, wv=wv, bk=bk, bv=bv, kv_ln_w=ln_w, kv_ln_b=ln_b)
+        ctx.wstruct, ctx.keep = w, mats
         saved = _saved(L.pio_kv_project_saved_bytes(rows, ckv, e, mode), x_kv.device)
         ws = N.workspace(L.pio_kv_project_ws_bytes(rows, ckv, e, mode), x_kv.device)
         kv = torch.empty(b, m, 2 * e, dtype=torch.float32, device=x_kv.device)
@@ -268,9 +275,8 @@ class KVProjectFn(torch.autograd.Function):
         dwk = torch.empty_like(w_k) if w_k is not None else None
         dwv = torch.empty_like(w_v) if w_v is not None else None
         dx = torch.empty_like(x_kv) if ctx.needs_input_grad[0] else None
-        _, wk, wv, _, bk, bv = _mha_ptrs(_mat(w_packed, mode), None, _mat(w_k, mode), _mat(w_v, mode), bias, e)
         _, gwk, gwv, _, gbk, gbv = _mha_ptrs(dwp, None, dwk, dwv, dbias, e)
-        w = N.attn_struct(wk=wk, wv=wv, bk=bk, bv=bv, kv_ln_w=ln_w, kv_ln_b=ln_b)
+        w = ctx.wstruct
         g = N.attn_struct(wk=gwk, wv=gwv, bk=gbk, bv=gbv, kv_ln_w=dln_w, kv_ln_b=dln_b)
         ws = N.workspace(L.pio_kv_project_ws_bytes(rows, ckv, e, mode), dev)
         N.check(L.pio_kv_project_bwd(dkv.data_ptr(), x_kv.data_ptr(), N.ptr(dx), byref(w), ctx.saved_buf.data_ptr(),
@@ -296,8 +302,10 @@ class CrossAttendFn(torch.autograd.Function):
         m = kv.shape[1]
         mode = get_compute_mode()
         L = N.lib()
-        wq, _, _, bq, _, _ = _mha_ptrs(_mat(w_packed, mode), _mat(w_q, mode), None, None, bias, e)
-        w = N.attn_struct(ln_w=ln_w, ln_b=ln_b, wq=wq, bq=bq, wo=_mat(wo, mode), bo=bo)
+        mats = (_mat(w_packed, mode), _mat(w_q, mode), _mat(wo, mode))
+        wq, _, _, bq, _, _ = _mha_ptrs(mats[0], mats[1], None, None, bias, e)
+        w = N.attn_struct(ln_w=ln_w, ln_b=ln_b, wq=wq, bq=bq, wo=mats[2], bo=bo)
+        ctx.wstruct, ctx.keep = w, mats
         saved = _saved(L.pio_cross_attend_saved_bytes(b, n, m, e, heads, mode), x_q.device)
         ws = N.workspace(L.pio_cross_attend_ws_bytes(b, n, m, e, heads, mode), x_q.device)
         y = torch.empty_like(x_q)
@@ -324,9 +332,8 @@ class CrossAttendFn(torch.autograd.Function):
         dwo, dbo = torch.empty_like(wo), torch.empty_like(bo)
         dx = torch.empty_like(x_q)
         dkv = torch.empty_like(kv)
-        wq, _, _, bq, _, _ = _mha_ptrs(_mat(w_packed, mode), _mat(w_q, mode), None, None, bias, e)
         gwq, _, _, gbq, _, _ = _mha_ptrs(dwp, dwq, None, None, dbias, e)
-        w = N.attn_struct(ln_w=ln_w, ln_b=ln_b, wq=wq, bq=bq, wo=_mat(wo, mode), bo=bo)
+        w = ctx.wstruct
         g = N.attn_struct(ln_w=dln_w, ln_b=dln_b, wq=gwq, bq=gbq, wo=dwo, bo=dbo)
         ws = N.workspace(L.pio_cross_attend_ws_bytes(b, n, m, e, heads, mode), dev)
         N.check(L.pio_cross_attend_bwd(dy.data_ptr(), x_q.data_ptr(), kv.data_ptr(), N.ptr(pad), dx.data_ptr(),
@@ -344,8 +351,9 @@ _LAYER_PARAMS = 12  # 6 attention + 6 mlp tensors per latent layer
 def _sa_struct(ln_w, ln_b, in_w, in_b, wo, bo, e, mode=N.MODE_FP32):
     """``mode`` selects fp32 parameters or their bf16 shadows for the two matrices (gradient structs
     always pass MODE_FP32)."""
-    wq, wk, wv, bq, bk, bv = _mha_ptrs(_mat(in_w, mode), None, None, None, in_b, e)
-    return dict(ln_w=ln_w, ln_b=ln_b, wq=wq, wk=wk, wv=wv, bq=bq, bk=bk, bv=bv, wo=_mat(wo, mode), bo=bo)
+    in_m, wo_m = _mat(in_w, mode), _mat(wo, mode)
+    wq, wk, wv, bq, bk, bv = _mha_ptrs(in_m, None, None, None, in_b, e)
+    return dict(ln_w=ln_w, ln_b=ln_b, wq=wq, wk=wk, wv=wv, bq=bq, bk=bk, bv=bv, wo=wo_m, bo=bo, _keep=(in_m, wo_m))
 
 
 class SelfAttnFn(torch.autograd.Function):
@@ -358,7 +366,10 @@ class SelfAttnFn(torch.autograd.Function):
         b, n, c = x.shape
         mode = get_compute_mode()
         L = N.lib()
-        w = N.attn_struct(**_sa_struct(*params, c, mode))
+        fields = _sa_struct(*params, c, mode)
+        ctx.keep = fields.pop("_keep")
+        w = N.attn_struct(**fields)
+        ctx.wstruct = w
         saved = _saved(L.pio_self_attn_saved_bytes(b, n, c, heads, mode), x.device)
         ws = N.workspace(L.pio_self_attn_ws_bytes(b, n, c, heads, mode), x.device)
         y = torch.empty_like(x)
@@ -378,8 +389,10 @@ class SelfAttnFn(torch.autograd.Function):
         L = N.lib()
         grads = [torch.empty_like(p) for p in params]
         dx = torch.empty_like(x)
-        w = N.attn_struct(**_sa_struct(*params, c, mode))
-        g = N.attn_struct(**_sa_struct(*grads, c))
+        w = ctx.wstruct
+        gfields = _sa_struct(*grads, c)
+        gfields.pop("_keep")
+        g = N.attn_struct(**gfields)
         ws = N.workspace(L.pio_self_attn_ws_bytes(b, n, c, heads, mode), x.device)
         N.check(L.pio_self_attn_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g),
                                     0, b, n, c, heads, residual, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)),
@@ -397,13 +410,18 @@ class LatentBlockFn(torch.autograd.Function):
     def _structs(params, layers, c, mode=N.MODE_FP32):
         attn = (N.AttnWeights * layers)()
         mlp = (N.MlpWeights * layers)()
+        keep = []
         for s in range(layers):
             p = params[s * _LAYER_PARAMS:(s + 1) * _LAYER_PARAMS]
-            for k, v in _sa_struct(*p[:6], c, mode).items():
+            fields = _sa_struct(*p[:6], c, mode)
+            keep.append(fields.pop("_keep"))
+            for k, v in fields.items():
                 setattr(attn[s], k, v if isinstance(v, int) or v is None else v.data_ptr())
-            for k, v in zip(N.MlpWeights._names, _mlp_operands(p[6:], mode)):
+            ops = _mlp_operands(p[6:], mode)
+            keep.append(ops)
+            for k, v in zip(N.MlpWeights._names, ops):
                 setattr(mlp[s], k, v.data_ptr())
-        return attn, mlp
+        return attn, mlp, keep
 
     @staticmethod
     def forward(ctx, x, heads, *params):
@@ -414,7 +432,8 @@ class LatentBlockFn(torch.autograd.Function):
         b, n, c = x.shape
         mode = get_compute_mode()
         L = N.lib()
-        attn, mlp = LatentBlockFn._structs(params, layers, c, mode)
+        attn, mlp, keep = LatentBlockFn._structs(params, layers, c, mode)
+        ctx.wstructs, ctx.keep = (attn, mlp), keep
         saved = _saved(L.pio_latent_block_saved_bytes(layers, b, n, c, heads, mode), x.device)
         ws = N.workspace(L.pio_latent_block_ws_bytes(layers, b, n, c, heads, mode), x.device)
         y = torch.empty_like(x)
@@ -434,8 +453,8 @@ class LatentBlockFn(torch.autograd.Function):
         L = N.lib()
         grads = [torch.empty_like(p) for p in params]
         dx = torch.empty_like(x)
-        attn, mlp = LatentBlockFn._structs(params, layers, c, mode)
-        attn_g, mlp_g = LatentBlockFn._structs(grads, layers, c)
+        attn, mlp = ctx.wstructs
+        attn_g, mlp_g, _ = LatentBlockFn._structs(grads, layers, c)
         ws = N.workspace(L.pio_latent_block_ws_bytes(layers, b, n, c, heads, mode), x.device)
         N.check(L.pio_latent_block_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), attn, mlp, ctx.saved_buf.data_ptr(), attn_g,
                                        mlp_g, 0, layers, b, n, c, heads, mode, ws.data_ptr(), ws.numel(),
@@ -456,7 +475,9 @@ class LinearFn(torch.autograd.Function):
         L = N.lib()
         ws = N.workspace(L.pio_linear_ws_bytes(rows, c_in, c_out, mode), x.device)
         y = torch.empty(*x.shape[:-1], c_out, dtype=torch.float32, device=x.device)
-        N.check(L.pio_linear_fwd(x.data_ptr(), _mat(w, mode).data_ptr(), b.data_ptr(), y.data_ptr(), rows, c_in, c_out, mode,
+        wm = _mat(w, mode)
+        ctx.wm = wm
+        N.check(L.pio_linear_fwd(x.data_ptr(), wm.data_ptr(), b.data_ptr(), y.data_ptr(), rows, c_in, c_out, mode,
                                  ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_linear_fwd")
         ctx.save_for_backward(x, w)
         ctx.meta = (rows, c_in, c_out, mode)
@@ -473,7 +494,7 @@ class LinearFn(torch.autograd.Function):
         dw = torch.empty_like(w)
         db = torch.empty(c_out, dtype=torch.float32, device=x.device)
         ws = N.workspace(L.pio_linear_ws_bytes(rows, c_in, c_out, mode), x.device)
-        N.check(L.pio_linear_bwd(dy.data_ptr(), x.data_ptr(), _mat(w, mode).data_ptr(), N.ptr(dx), dw.data_ptr(), db.data_ptr(), 0, rows,
+        N.check(L.pio_linear_bwd(dy.data_ptr(), x.data_ptr(), ctx.wm.data_ptr(), N.ptr(dx), dw.data_ptr(), db.data_ptr(), 0, rows,
                                  c_in, c_out, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_linear_bwd")
         return dx, dw, db
 
