@@ -485,10 +485,10 @@ long long pio_launch_count(void) { return pio::g_launches.load(std::memory_order
 
 int pio_image_encode(const float* x, const float* pos_enc, float* out, int64_t batch, int64_t m, int c_img,
                      int c_pos, pio_stream_t stream) {
-    PIO_CHECK_ARG(x && pos_enc && out, "pio_image_encode: null pointer");
     PIO_CHECK_ARG(batch >= 0 && m >= 0 && c_img > 0 && c_pos >= 0, "pio_image_encode: bad dims");
     const int64_t total = batch * m * (c_img + c_pos);
-    if (total == 0) return PIO_OK;
+    if (total == 0) return PIO_OK;  // empty batch: torch hands out null data pointers
+    PIO_CHECK_ARG(x && pos_enc && out, "pio_image_encode: null pointer");
     const int threads = 256;
     const int blocks = (int)std::min<int64_t>(cdiv(total, threads * 4), (int64_t)num_sms() * 16);
     image_encode_kernel<<<std::max(blocks, 1), threads, 0, (cudaStream_t)stream>>>(x, pos_enc, out, total, m, c_img, c_pos);

@@ -1,6 +1,6 @@
 // bf16 tensor-core GEMM for PIO_MODE_BF16: C[m,n] = sum_k A(m,k) B(n,k), fp32 accumulation.
 //
-//   * operands arrive by TMA (cp.async.bulk.tensor.2d, 128-byte swizzle) into a 4-stage
+//   * operands arrive by TMA (cp.async.bulk.tensor.2d, 128-byte swizzle) into a 3-stage
 //     shared-memory ring guarded by full/empty mbarriers;
 //   * one elected thread issues tcgen05.mma (kind::f16, M=128, N=BN, K=16) with the fp32
 //     accumulator tile in TMEM; tcgen05.commit releases ring slots and signals the epilogue;
@@ -21,7 +21,7 @@ namespace pio {
 
 constexpr int TC_BM = 128;
 constexpr int TC_BK = 64;  // 64 bf16 = one 128-byte swizzle row
-constexpr int TC_STAGES = 4;
+constexpr int TC_STAGES = 3;  // 3 x 32 KB + barriers: two CTAs per SM, so one tile's epilogue overlaps another's mainloop
 constexpr int TC_THREADS = 192;
 
 struct TcParams {
@@ -133,7 +133,7 @@ __device__ __forceinline__ uint32_t make_idesc(int bn, bool a_mn, bool b_mn) {
 }
 
 template <int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(TC_THREADS, 2)
     gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
     constexpr int A_STAGE = TC_BM * TC_BK * 2;  // 16 KB
     constexpr int B_STAGE = BN * TC_BK * 2;
@@ -219,94 +219,52 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
         __syncwarp();
     } else {
         // ---------------- epilogue: TMEM lane quadrant = warp id mod 4
+        // tcgen05.ld hands each thread one accumulator ROW (32 columns at a time); a padded
+        // shared-memory transpose (aliasing the now idle operand ring) turns that into lane = column,
+        // so bias / residual / aux reads and every output row are 128-byte coalesced accesses.
         const int q = warp & 3;
-        const int row = q * 32 + lane;
-        const int64_t gm = (int64_t)m0 + row;
         mbar_wait(tmem_full, 0);
         tc_fence_after();
-        const bool row_ok = gm < p.M;
+        float* stile = reinterpret_cast<float*>(smem) + q * (32 * 33);
 #pragma unroll 1
         for (int c0 = 0; c0 < BN; c0 += 32) {
             uint32_t r[32];
             tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
             tmem_ld_wait();
-            if (!row_ok) continue;
-            const int nb = n0 + c0;
-            if (nb >= p.N) continue;
-            if (p.splits > 1) {
-                float* out = p.partial + (int64_t)blockIdx.z * p.partial_stride + gm * p.N + nb;
+            const int n = n0 + c0 + lane;
+            if (n0 + c0 >= p.N) continue;  // warp-uniform
 #pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (nb + j < p.N) out[j] = __uint_as_float(r[j]);
-                continue;
-            }
-            float v[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-            const bool full = (nb + 32 <= p.N);
-            if (p.bias) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (full || nb + j < p.N) v[j] += __ldg(p.bias + nb + j);
-            }
-            if (p.act == 1) {
-                if (p.aux16) {
-                    __nv_bfloat16* a = p.aux16 + gm * p.ldaux + nb;
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (full || nb + j < p.N) a[j] = __float2bfloat16(v[j]);
+            for (int j = 0; j < 32; ++j) stile[lane * 33 + j] = __uint_as_float(r[j]);
+            __syncwarp();
+            const bool n_ok = n < p.N;
+            const float bias = (p.bias && n_ok) ? __ldg(p.bias + n) : 0.f;
+            const int64_t gm0 = (int64_t)m0 + q * 32;
+            const int rows_here = (int)min((int64_t)32, (int64_t)p.M - gm0);  // may be <= 0
+#pragma unroll 4
+            for (int rr = 0; rr < 32; ++rr) {
+                if (rr >= rows_here) break;  // warp-uniform
+                if (!n_ok) continue;
+                const int64_t gm = gm0 + rr;
+                float v = stile[rr * 33 + lane];
+                if (p.splits > 1) {
+                    p.partial[(int64_t)blockIdx.z * p.partial_stride + gm * p.N + n] = v;
+                    continue;
                 }
-#pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-            } else if (p.act == 2) {
-                const __nv_bfloat16* a = p.aux16 + gm * p.ldaux + nb;
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (full || nb + j < p.N) v[j] *= gelu_erf_grad(__bfloat162float(a[j]));
-            }
-            if (p.residual) {
-                const float* rr = p.residual + gm * p.ldr + nb;
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (full || nb + j < p.N) v[j] += rr[j];
-            }
-            if (p.c32) {
-                float* o = p.c32 + gm * p.ldc32 + nb;
-                if (p.accumulate) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (full || nb + j < p.N) o[j] += v[j];
-                } else if (full && ((((uintptr_t)o) & 15) == 0)) {
-#pragma unroll
-                    for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (full || nb + j < p.N) o[j] = v[j];
+                v += bias;
+                if (p.act == 1) {
+                    if (p.aux16) p.aux16[gm * p.ldaux + n] = __float2bfloat16(v);
+                    v = gelu_erf(v);
+                } else if (p.act == 2) {
+                    v *= gelu_erf_grad(__bfloat162float(p.aux16[gm * p.ldaux + n]));
                 }
-            }
-            if (p.c16) {
-                __nv_bfloat16* o = p.c16 + gm * p.ldc16 + nb;
-                if (full && ((((uintptr_t)o) & 15) == 0)) {
-#pragma unroll
-                    for (int j = 0; j < 32; j += 8) {
-                        __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j], v[j + 1]);
-                        __nv_bfloat162 h1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
-                        __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
-                        __nv_bfloat162 h3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
-                        uint4 u;
-                        u.x = *reinterpret_cast<uint32_t*>(&h0);
-                        u.y = *reinterpret_cast<uint32_t*>(&h1);
-                        u.z = *reinterpret_cast<uint32_t*>(&h2);
-                        u.w = *reinterpret_cast<uint32_t*>(&h3);
-                        *reinterpret_cast<uint4*>(o + j) = u;
-                    }
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (full || nb + j < p.N) o[j] = __float2bfloat16(v[j]);
+                if (p.residual) v += p.residual[gm * p.ldr + n];
+                if (p.c32) {
+                    float* o = p.c32 + gm * p.ldc32 + n;
+                    *o = p.accumulate ? (*o + v) : v;
                 }
+                if (p.c16) p.c16[gm * p.ldc16 + n] = __float2bfloat16(v);
             }
+            __syncwarp();
         }
         tc_fence_before();
     }

@@ -313,6 +313,7 @@ def test_cross_entropy_fwd_bwd(N, rows, classes):
 def test_bad_arguments_return_errors_not_crashes(N):
     L = N.lib()
     assert L.pio_image_encode(None, None, None, 1, 1, 1, 1, None) == 1
+    assert L.pio_image_encode(None, None, None, 0, 1, 1, 1, None) == 0  # empty batch is a no-op
     assert b"null" in L.pio_last_error()
     d = N.AttnDesc()
     assert L.pio_attn_fwd(ctypes.byref(d), 0, None) == 1
