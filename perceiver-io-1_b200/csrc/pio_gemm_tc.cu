@@ -40,6 +40,7 @@ struct TcParams {
     int accumulate;
     float* partial;
     int64_t partial_stride;
+    int epi_kind;
 };
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -132,6 +133,154 @@ __device__ __forceinline__ uint32_t make_idesc(int bn, bool a_mn, bool b_mn) {
            ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
 }
 
+// Epilogue flavours, resolved on the host so the row loop below carries no run-time flag tests
+// (with four epilogue warps per CTA there is nothing to hide a branchy, latency-bound loop behind).
+enum EpiKind : int {
+    EPI_F32 = 0,        // c32 = acc + bias
+    EPI_F32_RES = 1,    // c32 = acc + bias + residual
+    EPI_F32_ACC = 2,    // c32 += acc + bias
+    EPI_B16 = 3,        // c16 = acc + bias
+    EPI_B16_GELU = 4,   // aux16 = acc + bias ; c16 = gelu(aux)
+    EPI_B16_DGELU = 5,  // c16 = acc * gelu'(aux16)
+    EPI_PARTIAL = 6,    // split-K partial sums
+    EPI_GENERIC = 7     // any other combination of outputs / flags
+};
+
+__device__ __forceinline__ void store4_f32(float* o, const float (&v)[4], bool vec, int valid) {
+    if (vec && valid == 4) {
+        *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (j < valid) o[j] = v[j];
+    }
+}
+__device__ __forceinline__ void store4_b16(__nv_bfloat16* o, const float (&v)[4], bool vec, int valid) {
+    if (vec && valid == 4) {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]);
+        __nv_bfloat162 hi = __floats2bfloat162_rn(v[2], v[3]);
+        uint2 u;
+        u.x = *reinterpret_cast<uint32_t*>(&lo);
+        u.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(o) = u;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (j < valid) o[j] = __float2bfloat16(v[j]);
+    }
+}
+__device__ __forceinline__ void load4_b16(const __nv_bfloat16* a, float (&v)[4], bool vec, int valid) {
+    if (vec && valid == 4) {
+        const uint2 u = *reinterpret_cast<const uint2*>(a);
+        const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162*>(&u.x);
+        const __nv_bfloat162 hi = *reinterpret_cast<const __nv_bfloat162*>(&u.y);
+        v[0] = __low2float(lo); v[1] = __high2float(lo); v[2] = __low2float(hi); v[3] = __high2float(hi);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = (j < valid) ? __bfloat162float(a[j]) : 0.f;
+    }
+}
+__device__ __forceinline__ void load4_f32(const float* a, float (&v)[4], bool vec, int valid) {
+    if (vec && valid == 4) {
+        const float4 t = *reinterpret_cast<const float4*>(a);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = (j < valid) ? a[j] : 0.f;
+    }
+}
+
+// One warp's 32 accumulator rows x BN columns, staged in shared memory (row pitch BN+4 floats).
+// Each lane owns 4 consecutive columns of a row, so every global access is a coalesced row
+// segment (16 B per lane when the leading dimensions allow it).
+template <int BN, int KIND>
+__device__ __forceinline__ void epilogue_rows(const TcParams& p, const float* stile, int lane, int n0, int64_t gm0,
+                                              int rows_here, int zsplit) {
+    constexpr int PITCH = BN + 4;
+    constexpr int LANES_PER_ROW = BN / 4;            // 32 (BN=128) or 16 (BN=64)
+    constexpr int ROWS_PER_IT = 32 / LANES_PER_ROW;  // 1 or 2
+    const int col = (lane % LANES_PER_ROW) * 4;
+    const int rsub = lane / LANES_PER_ROW;
+    const int n = n0 + col;
+    const int valid = min(4, p.N - n);  // <= 0: this lane has no columns
+    float bias[4] = {0.f, 0.f, 0.f, 0.f};
+    if (p.bias && KIND != EPI_PARTIAL && KIND != EPI_B16_DGELU) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (j < valid) bias[j] = __ldg(p.bias + n + j);
+    }
+    const bool v32 = ((p.ldc32 & 3) == 0) && ((n & 3) == 0) && ((((uintptr_t)p.c32) & 15) == 0);
+    const bool v16 = ((p.ldc16 & 3) == 0) && ((((uintptr_t)p.c16) & 7) == 0);
+    const bool vaux = ((p.ldaux & 3) == 0) && ((((uintptr_t)p.aux16) & 7) == 0);
+    const bool vres = ((p.ldr & 3) == 0) && ((((uintptr_t)p.residual) & 15) == 0);
+    const bool vpart = ((p.N & 3) == 0);
+#pragma unroll 4
+    for (int it = 0; it < 32 / ROWS_PER_IT; ++it) {
+        const int rr = it * ROWS_PER_IT + rsub;
+        if (rr >= rows_here || valid <= 0) continue;
+        const int64_t gm = gm0 + rr;
+        const float4 t = *reinterpret_cast<const float4*>(stile + rr * PITCH + col);
+        float v[4] = {t.x + bias[0], t.y + bias[1], t.z + bias[2], t.w + bias[3]};
+        if (KIND == EPI_PARTIAL) {
+            store4_f32(p.partial + (int64_t)zsplit * p.partial_stride + gm * p.N + n, v, vpart, valid);
+        } else if (KIND == EPI_F32) {
+            store4_f32(p.c32 + gm * p.ldc32 + n, v, v32, valid);
+        } else if (KIND == EPI_F32_RES) {
+            float r[4];
+            load4_f32(p.residual + gm * p.ldr + n, r, vres, valid);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] += r[j];
+            store4_f32(p.c32 + gm * p.ldc32 + n, v, v32, valid);
+        } else if (KIND == EPI_F32_ACC) {
+            float r[4];
+            load4_f32(p.c32 + gm * p.ldc32 + n, r, v32, valid);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] += r[j];
+            store4_f32(p.c32 + gm * p.ldc32 + n, v, v32, valid);
+        } else if (KIND == EPI_B16) {
+            store4_b16(p.c16 + gm * p.ldc16 + n, v, v16, valid);
+        } else if (KIND == EPI_B16_GELU) {
+            if (p.aux16) store4_b16(p.aux16 + gm * p.ldaux + n, v, vaux, valid);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = gelu_erf(v[j]);
+            store4_b16(p.c16 + gm * p.ldc16 + n, v, v16, valid);
+        } else if (KIND == EPI_B16_DGELU) {
+            float a[4];
+            load4_b16(p.aux16 + gm * p.ldaux + n, a, vaux, valid);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] *= gelu_erf_grad(a[j]);
+            store4_b16(p.c16 + gm * p.ldc16 + n, v, v16, valid);
+        } else {  // EPI_GENERIC
+            if (p.act == 1) {
+                if (p.aux16) store4_b16(p.aux16 + gm * p.ldaux + n, v, vaux, valid);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) v[j] = gelu_erf(v[j]);
+            } else if (p.act == 2) {
+                float a[4];
+                load4_b16(p.aux16 + gm * p.ldaux + n, a, vaux, valid);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) v[j] *= gelu_erf_grad(a[j]);
+            }
+            if (p.residual) {
+                float r[4];
+                load4_f32(p.residual + gm * p.ldr + n, r, vres, valid);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) v[j] += r[j];
+            }
+            if (p.c32) {
+                if (p.accumulate) {
+                    float r[4];
+                    load4_f32(p.c32 + gm * p.ldc32 + n, r, v32, valid);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) v[j] += r[j];
+                }
+                store4_f32(p.c32 + gm * p.ldc32 + n, v, v32, valid);
+            }
+            if (p.c16) store4_b16(p.c16 + gm * p.ldc16 + n, v, v16, valid);
+        }
+    }
+}
+
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(TC_THREADS, 2)
     gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
@@ -219,52 +368,35 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
         __syncwarp();
     } else {
         // ---------------- epilogue: TMEM lane quadrant = warp id mod 4
-        // tcgen05.ld hands each thread one accumulator ROW (32 columns at a time); a padded
-        // shared-memory transpose (aliasing the now idle operand ring) turns that into lane = column,
-        // so bias / residual / aux reads and every output row are 128-byte coalesced accesses.
+        // tcgen05.ld hands each thread one accumulator ROW; the rows are staged in shared memory
+        // (aliasing the now idle operand ring) and read back with lane = 4 consecutive columns.
         const int q = warp & 3;
+        constexpr int PITCH = BN + 4;
         mbar_wait(tmem_full, 0);
         tc_fence_after();
-        float* stile = reinterpret_cast<float*>(smem) + q * (32 * 33);
-#pragma unroll 1
+        float* stile = reinterpret_cast<float*>(smem) + q * (32 * PITCH);
+#pragma unroll
         for (int c0 = 0; c0 < BN; c0 += 32) {
             uint32_t r[32];
             tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
             tmem_ld_wait();
-            const int n = n0 + c0 + lane;
-            if (n0 + c0 >= p.N) continue;  // warp-uniform
 #pragma unroll
-            for (int j = 0; j < 32; ++j) stile[lane * 33 + j] = __uint_as_float(r[j]);
-            __syncwarp();
-            const bool n_ok = n < p.N;
-            const float bias = (p.bias && n_ok) ? __ldg(p.bias + n) : 0.f;
-            const int64_t gm0 = (int64_t)m0 + q * 32;
-            const int rows_here = (int)min((int64_t)32, (int64_t)p.M - gm0);  // may be <= 0
-#pragma unroll 4
-            for (int rr = 0; rr < 32; ++rr) {
-                if (rr >= rows_here) break;  // warp-uniform
-                if (!n_ok) continue;
-                const int64_t gm = gm0 + rr;
-                float v = stile[rr * 33 + lane];
-                if (p.splits > 1) {
-                    p.partial[(int64_t)blockIdx.z * p.partial_stride + gm * p.N + n] = v;
-                    continue;
-                }
-                v += bias;
-                if (p.act == 1) {
-                    if (p.aux16) p.aux16[gm * p.ldaux + n] = __float2bfloat16(v);
-                    v = gelu_erf(v);
-                } else if (p.act == 2) {
-                    v *= gelu_erf_grad(__bfloat162float(p.aux16[gm * p.ldaux + n]));
-                }
-                if (p.residual) v += p.residual[gm * p.ldr + n];
-                if (p.c32) {
-                    float* o = p.c32 + gm * p.ldc32 + n;
-                    *o = p.accumulate ? (*o + v) : v;
-                }
-                if (p.c16) p.c16[gm * p.ldc16 + n] = __float2bfloat16(v);
-            }
-            __syncwarp();
+            for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<float4*>(stile + lane * PITCH + c0 + j) =
+                    make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+        }
+        __syncwarp();
+        const int64_t gm0 = (int64_t)m0 + q * 32;
+        const int rows_here = (int)min((int64_t)32, (int64_t)p.M - gm0);  // may be <= 0
+        switch (p.epi_kind) {
+            case EPI_F32: epilogue_rows<BN, EPI_F32>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
+            case EPI_F32_RES: epilogue_rows<BN, EPI_F32_RES>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
+            case EPI_F32_ACC: epilogue_rows<BN, EPI_F32_ACC>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
+            case EPI_B16: epilogue_rows<BN, EPI_B16>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
+            case EPI_B16_GELU: epilogue_rows<BN, EPI_B16_GELU>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
+            case EPI_B16_DGELU: epilogue_rows<BN, EPI_B16_DGELU>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
+            case EPI_PARTIAL: epilogue_rows<BN, EPI_PARTIAL>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
+            default: epilogue_rows<BN, EPI_GENERIC>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
         }
         tc_fence_before();
     }
@@ -377,6 +509,18 @@ int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream
     }
     p.splits = splits;
     p.kb_per_split = kb_per;
+    {
+        const bool o32 = d->c32 != nullptr, o16 = d->c16 != nullptr;
+        int kind = EPI_GENERIC;
+        if (splits > 1) kind = EPI_PARTIAL;
+        else if (o32 && !o16 && d->act == 0 && !d->residual && !d->accumulate) kind = EPI_F32;
+        else if (o32 && !o16 && d->act == 0 && d->residual && !d->accumulate) kind = EPI_F32_RES;
+        else if (o32 && !o16 && d->act == 0 && !d->residual && d->accumulate) kind = EPI_F32_ACC;
+        else if (!o32 && o16 && d->act == 0 && !d->residual) kind = EPI_B16;
+        else if (!o32 && o16 && d->act == 1 && !d->residual) kind = EPI_B16_GELU;
+        else if (!o32 && o16 && d->act == 2 && !d->residual && !d->bias) kind = EPI_B16_DGELU;
+        p.epi_kind = kind;
+    }
 
     // tensor maps: K-major operand = (rows = m|n, cols = k); MN-major operand = (rows = k, cols = m|n)
     CUtensorMap ta, tb;
