@@ -226,7 +226,9 @@ typedef struct {
 
 /* The key/value side of CrossAttention, model.py:90,98 + the k/v in-projection of :74:
  * kv[b,j,0:E] = LN_kv(x_kv[b,j]) Wk^T + bk,  kv[b,j,E:2E] = ... Wv^T + bv.
- * Computed once per distinct layer and shared by the repeats of layer_n (model.py:186-187). */
+ * Computed once per distinct layer and shared by the repeats of layer_n (model.py:186-187).
+ * In PIO_MODE_BF16 the kv tensor and its gradient dkv are bf16 (B, M, 2E) behind the float* type,
+ * here and in pio_cross_attend_*. */
 size_t pio_kv_project_saved_bytes(int64_t rows, int c_kv, int e, int mode);
 size_t pio_kv_project_ws_bytes(int64_t rows, int c_kv, int e, int mode);
 int pio_kv_project_fwd(const float* x_kv, float* kv, const pio_attn_weights* w, void* saved,

@@ -14,14 +14,21 @@ constexpr int AT_TILE = 32;               // streamed rows per tile (one per lan
 constexpr int AT_THREADS = AT_WARPS * 32;
 
 struct AttnP {
-    const float *q, *k, *v, *o, *d_o, *lse_in;
+    const void *q, *k, *v;  // fp32, or bf16 when in16
+    const float *o, *d_o, *lse_in;
     const uint8_t* pad;
     float *out, *lse, *dq, *dk, *dv, *delta;
     __nv_bfloat16 *out16, *dq16, *dk16, *dv16;  // optional bf16 copies, same element strides
     int64_t q_bs, q_rs, k_bs, k_rs, v_bs, v_rs, o_bs, o_rs;
     int batch, heads, n, m, dh;
     float scale;
+    int in16;  // q, k, v are bf16 (same element strides) instead of fp32
 };
+
+__device__ __forceinline__ float load_in(const void* base, int64_t idx, bool in16) {
+    return in16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[idx])
+                : __ldg(reinterpret_cast<const float*>(base) + idx);
+}
 
 // rows [r0, r0+nrows) of a (rows, dh) head slice -> smem transposed [DHP][AT_ROWS], zero padded
 template <int DHP>
@@ -31,6 +38,27 @@ __device__ __forceinline__ void load_rows_T(float* sT, const float* __restrict__
         float v = 0.f;
         if (r0 + r < rlim && d < dh) v = __ldg(g + (int64_t)(r0 + r) * rs + d);
         sT[d * AT_ROWS + r] = v;
+    }
+}
+// same, source fp32 or bf16 at element offset `off` of `base`
+template <int DHP>
+__device__ __forceinline__ void load_rows_T(float* sT, const void* base, int64_t off, bool in16, int64_t rs, int r0, int rlim,
+                                            int dh) {
+    for (int idx = threadIdx.x; idx < AT_ROWS * DHP; idx += AT_THREADS) {
+        const int r = idx / DHP, d = idx - r * DHP;
+        float v = 0.f;
+        if (r0 + r < rlim && d < dh) v = load_in(base, off + (int64_t)(r0 + r) * rs + d, in16);
+        sT[d * AT_ROWS + r] = v;
+    }
+}
+template <int DHP>
+__device__ __forceinline__ void load_tile_rows(float* s, const void* base, int64_t off, bool in16, int64_t rs, int r0, int rlim,
+                                               int dh) {
+    for (int idx = threadIdx.x; idx < AT_TILE * DHP; idx += AT_THREADS) {
+        const int r = idx / DHP, d = idx - r * DHP;
+        float v = 0.f;
+        if (r0 + r < rlim && d < dh) v = load_in(base, off + (int64_t)(r0 + r) * rs + d, in16);
+        s[r * (DHP + 1) + d] = v;
     }
 }
 // rows [r0, r0+32) -> smem [32][DHP+1], zero padded
@@ -54,12 +82,13 @@ __global__ void __launch_bounds__(AT_THREADS) attn_fwd_kernel(const AttnP p) {
     float* Ps = Vs + AT_TILE * (DHP + 1);      // [warps][32][4]
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * AT_ROWS;
-    const float* qg = p.q + (int64_t)b * p.q_bs + (int64_t)h * p.dh;
-    const float* kg = p.k + (int64_t)b * p.k_bs + (int64_t)h * p.dh;
-    const float* vg = p.v + (int64_t)b * p.v_bs + (int64_t)h * p.dh;
+    const int64_t qoff = (int64_t)b * p.q_bs + (int64_t)h * p.dh;
+    const int64_t koff = (int64_t)b * p.k_bs + (int64_t)h * p.dh;
+    const int64_t voff = (int64_t)b * p.v_bs + (int64_t)h * p.dh;
+    const bool in16 = p.in16 != 0;
     const uint8_t* padb = p.pad ? p.pad + (int64_t)b * p.m : nullptr;
 
-    load_rows_T<DHP>(QsT, qg, p.q_rs, q0, p.n, p.dh);
+    load_rows_T<DHP>(QsT, p.q, qoff, in16, p.q_rs, q0, p.n, p.dh);
     float m_run[AT_RPW], l_run[AT_RPW], acc[AT_RPW][NCH];
 #pragma unroll
     for (int i = 0; i < AT_RPW; ++i) {
@@ -71,8 +100,8 @@ __global__ void __launch_bounds__(AT_THREADS) attn_fwd_kernel(const AttnP p) {
     float* Pw = Ps + wid * AT_TILE * 4;
     for (int j0 = 0; j0 < p.m; j0 += AT_TILE) {
         __syncthreads();  // previous tile fully consumed (also orders the Q load on the first pass)
-        load_tile_rows<DHP>(Ks, kg, p.k_rs, j0, p.m, p.dh);
-        load_tile_rows<DHP>(Vs, vg, p.v_rs, j0, p.m, p.dh);
+        load_tile_rows<DHP>(Ks, p.k, koff, in16, p.k_rs, j0, p.m, p.dh);
+        load_tile_rows<DHP>(Vs, p.v, voff, in16, p.v_rs, j0, p.m, p.dh);
         __syncthreads();
         float s[AT_RPW] = {0.f, 0.f, 0.f, 0.f};
         const float* krow = Ks + lane * (DHP + 1);
@@ -152,14 +181,15 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_dq_kernel(const AttnP p) 
     float* dSs = Vs + AT_TILE * (DHP + 1);      // [warps][32][4]
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * AT_ROWS;
-    const float* qg = p.q + (int64_t)b * p.q_bs + (int64_t)h * p.dh;
-    const float* kg = p.k + (int64_t)b * p.k_bs + (int64_t)h * p.dh;
-    const float* vg = p.v + (int64_t)b * p.v_bs + (int64_t)h * p.dh;
+    const int64_t qoff = (int64_t)b * p.q_bs + (int64_t)h * p.dh;
+    const int64_t koff = (int64_t)b * p.k_bs + (int64_t)h * p.dh;
+    const int64_t voff = (int64_t)b * p.v_bs + (int64_t)h * p.dh;
+    const bool in16 = p.in16 != 0;
     const float* og = p.o + (int64_t)b * p.o_bs + (int64_t)h * p.dh;
     const float* dog = p.d_o + (int64_t)b * p.o_bs + (int64_t)h * p.dh;
     const uint8_t* padb = p.pad ? p.pad + (int64_t)b * p.m : nullptr;
 
-    load_rows_T<DHP>(QsT, qg, p.q_rs, q0, p.n, p.dh);
+    load_rows_T<DHP>(QsT, p.q, qoff, in16, p.q_rs, q0, p.n, p.dh);
     load_rows_T<DHP>(dOsT, dog, p.o_rs, q0, p.n, p.dh);
     float delta[AT_RPW], lse[AT_RPW], acc[AT_RPW][NCH];
 #pragma unroll
@@ -179,8 +209,8 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_dq_kernel(const AttnP p) 
     float* dSw = dSs + wid * AT_TILE * 4;
     for (int j0 = 0; j0 < p.m; j0 += AT_TILE) {
         __syncthreads();
-        load_tile_rows<DHP>(Ks, kg, p.k_rs, j0, p.m, p.dh);
-        load_tile_rows<DHP>(Vs, vg, p.v_rs, j0, p.m, p.dh);
+        load_tile_rows<DHP>(Ks, p.k, koff, in16, p.k_rs, j0, p.m, p.dh);
+        load_tile_rows<DHP>(Vs, p.v, voff, in16, p.v_rs, j0, p.m, p.dh);
         __syncthreads();
         float s[AT_RPW] = {0.f, 0.f, 0.f, 0.f}, dp[AT_RPW] = {0.f, 0.f, 0.f, 0.f};
         const float* krow = Ks + lane * (DHP + 1);
@@ -224,12 +254,12 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_dq_kernel(const AttnP p) 
     for (int i = 0; i < AT_RPW; ++i) {
         const int qi = q0 + wid * AT_RPW + i;
         if (qi >= p.n) continue;
-        float* dqg = p.dq + (int64_t)b * p.q_bs + (int64_t)qi * p.q_rs + (int64_t)h * p.dh;
+        const int64_t dqo = (int64_t)b * p.q_bs + (int64_t)qi * p.q_rs + (int64_t)h * p.dh;
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
             const int d = 32 * c + lane;
             if (d < p.dh) {
-                dqg[d] = acc[i][c];
+                if (p.dq) p.dq[dqo + d] = acc[i][c];
                 if (p.dq16) p.dq16[(int64_t)b * p.q_bs + (int64_t)qi * p.q_rs + (int64_t)h * p.dh + d] = __float2bfloat16(acc[i][c]);
             }
         }
@@ -251,14 +281,15 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_dkv_kernel(const AttnP p)
     float* del_s = lse_s + AT_TILE;               // [32]
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int b = blockIdx.z, h = blockIdx.y, k0 = blockIdx.x * AT_ROWS;
-    const float* qg = p.q + (int64_t)b * p.q_bs + (int64_t)h * p.dh;
-    const float* kg = p.k + (int64_t)b * p.k_bs + (int64_t)h * p.dh;
-    const float* vg = p.v + (int64_t)b * p.v_bs + (int64_t)h * p.dh;
+    const int64_t qoff = (int64_t)b * p.q_bs + (int64_t)h * p.dh;
+    const int64_t koff = (int64_t)b * p.k_bs + (int64_t)h * p.dh;
+    const int64_t voff = (int64_t)b * p.v_bs + (int64_t)h * p.dh;
+    const bool in16 = p.in16 != 0;
     const float* dog = p.d_o + (int64_t)b * p.o_bs + (int64_t)h * p.dh;
     const uint8_t* padb = p.pad ? p.pad + (int64_t)b * p.m : nullptr;
 
-    load_rows_T<DHP>(KsT, kg, p.k_rs, k0, p.m, p.dh);
-    load_rows_T<DHP>(VsT, vg, p.v_rs, k0, p.m, p.dh);
+    load_rows_T<DHP>(KsT, p.k, koff, in16, p.k_rs, k0, p.m, p.dh);
+    load_rows_T<DHP>(VsT, p.v, voff, in16, p.v_rs, k0, p.m, p.dh);
     bool kdead[AT_RPW];
     float dk[AT_RPW][NCH], dv[AT_RPW][NCH];
 #pragma unroll
@@ -276,7 +307,7 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_dkv_kernel(const AttnP p)
     const int64_t stat_base = ((int64_t)b * p.heads + h) * p.n;
     for (int i0 = 0; i0 < p.n; i0 += AT_TILE) {
         __syncthreads();
-        load_tile_rows<DHP>(Qs, qg, p.q_rs, i0, p.n, p.dh);
+        load_tile_rows<DHP>(Qs, p.q, qoff, in16, p.q_rs, i0, p.n, p.dh);
         load_tile_rows<DHP>(dOs, dog, p.o_rs, i0, p.n, p.dh);
         if (threadIdx.x < AT_TILE) {
             const int qi = i0 + threadIdx.x;
@@ -330,14 +361,14 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_dkv_kernel(const AttnP p)
     for (int i = 0; i < AT_RPW; ++i) {
         const int kj = k0 + wid * AT_RPW + i;
         if (kj >= p.m) continue;
-        float* dkg = p.dk + (int64_t)b * p.k_bs + (int64_t)kj * p.k_rs + (int64_t)h * p.dh;
-        float* dvg = p.dv + (int64_t)b * p.v_bs + (int64_t)kj * p.v_rs + (int64_t)h * p.dh;
+        const int64_t dko = (int64_t)b * p.k_bs + (int64_t)kj * p.k_rs + (int64_t)h * p.dh;
+        const int64_t dvo = (int64_t)b * p.v_bs + (int64_t)kj * p.v_rs + (int64_t)h * p.dh;
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
             const int d = 32 * c + lane;
             if (d < p.dh) {
-                dkg[d] = dk[i][c];
-                dvg[d] = dv[i][c];
+                if (p.dk) p.dk[dko + d] = dk[i][c];
+                if (p.dv) p.dv[dvo + d] = dv[i][c];
                 if (p.dk16) p.dk16[(int64_t)b * p.k_bs + (int64_t)kj * p.k_rs + (int64_t)h * p.dh + d] = __float2bfloat16(dk[i][c]);
                 if (p.dv16) p.dv16[(int64_t)b * p.v_bs + (int64_t)kj * p.v_rs + (int64_t)h * p.dh + d] = __float2bfloat16(dv[i][c]);
             }
@@ -390,7 +421,10 @@ int attn_fwd_simt(const pio_attn_desc* d, cudaStream_t st, const AttnBf16Out* ex
     fill(p, d);
     p.out = d->o;
     p.lse = d->lse;
-    if (extra) p.out16 = extra->o16;
+    if (extra) {
+        p.out16 = extra->o16;
+        p.in16 = extra->in16;
+    }
     dim3 grid((unsigned)cdiv(d->n, AT_ROWS), (unsigned)d->heads, (unsigned)d->batch);
     int rc = PIO_OK;
     PIO_DISPATCH_NCH(d->dh, rc = launch(attn_fwd_kernel<NCH>, grid, fwd_smem(32 * NCH), p, st));
@@ -400,7 +434,9 @@ int attn_fwd_simt(const pio_attn_desc* d, cudaStream_t st, const AttnBf16Out* ex
 int attn_bwd_simt(const pio_attn_bwd_desc* bd, cudaStream_t st, const AttnBf16Out* extra) {
     const pio_attn_desc* d = &bd->fwd;
     PIO_TRY(check_desc(d, "pio_attn_bwd"));
-    PIO_CHECK_ARG(bd->d_o && bd->dq && bd->dk && bd->dv && bd->delta, "pio_attn_bwd: null pointer");
+    PIO_CHECK_ARG(bd->d_o && bd->delta, "pio_attn_bwd: null pointer");
+    PIO_CHECK_ARG((bd->dq || (extra && extra->dq16)) && (bd->dk || (extra && extra->dk16)) && (bd->dv || (extra && extra->dv16)),
+                  "pio_attn_bwd: every gradient needs an fp32 or a bf16 destination");
     if (d->batch == 0) return PIO_OK;
     AttnP p{};
     fill(p, d);
@@ -409,6 +445,7 @@ int attn_bwd_simt(const pio_attn_bwd_desc* bd, cudaStream_t st, const AttnBf16Ou
     p.d_o = bd->d_o;
     p.dq = bd->dq; p.dk = bd->dk; p.dv = bd->dv; p.delta = bd->delta;
     if (extra) {
+        p.in16 = extra->in16;
         p.dq16 = extra->dq16;
         p.dk16 = extra->dk16;
         p.dv16 = extra->dv16;

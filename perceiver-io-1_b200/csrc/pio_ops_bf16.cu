@@ -144,12 +144,13 @@ int kv_project_fwd(Ctx& c, const float* x_kv, float* kv, const pio_attn_weights*
     KvSaved s(saved, rows, ckv);
     const int64_t ckp = pad8(ckv);
     PIO_TRY(layernorm_fwd_bf16(x_kv, w->kv_ln_w, w->kv_ln_b, s.h0, ckp, s.stats, rows, ckv, LN_EPS, c.st));
+    bf16* kv16 = reinterpret_cast<bf16*>(kv);  // bf16 mode: the kv tensor is bf16 (B, M, 2E)
     if (packed16(w->wk, w->wv, e, ckp) && w->bv == w->bk + e) {
-        PIO_TRY(tc_xwT(c, s.h0, ckp, (const bf16*)w->wk, ckp, rows, 2 * e, ckv, kv, 2 * e, nullptr, 0, w->bk, nullptr, 0, 0,
+        PIO_TRY(tc_xwT(c, s.h0, ckp, (const bf16*)w->wk, ckp, rows, 2 * e, ckv, nullptr, 0, kv16, 2 * e, w->bk, nullptr, 0, 0,
                        nullptr, 0));
     } else {
-        PIO_TRY(tc_xwT(c, s.h0, ckp, (const bf16*)w->wk, ckp, rows, e, ckv, kv, 2 * e, nullptr, 0, w->bk, nullptr, 0, 0, nullptr, 0));
-        PIO_TRY(tc_xwT(c, s.h0, ckp, (const bf16*)w->wv, ckp, rows, e, ckv, kv + e, 2 * e, nullptr, 0, w->bv, nullptr, 0, 0,
+        PIO_TRY(tc_xwT(c, s.h0, ckp, (const bf16*)w->wk, ckp, rows, e, ckv, nullptr, 0, kv16, 2 * e, w->bk, nullptr, 0, 0, nullptr, 0));
+        PIO_TRY(tc_xwT(c, s.h0, ckp, (const bf16*)w->wv, ckp, rows, e, ckv, nullptr, 0, kv16 + e, 2 * e, w->bv, nullptr, 0, 0,
                        nullptr, 0));
     }
     return PIO_OK;
@@ -161,13 +162,13 @@ int kv_project_bwd(Ctx& c, const float* dkv, const float* x_kv, float* dx_kv, co
     KvSaved s((void*)saved, rows, ckv);
     const int64_t ckp = pad8(ckv);
     const size_t mark = c.W.off;
-    PIO_TAKE_BYTES(bf16, dkv16, c, (size_t)rows * 2 * e * 2, "pio_kv_project_bwd");
+    const bf16* dkv16 = reinterpret_cast<const bf16*>(dkv);  // bf16 mode: the kv gradient is bf16
     PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ckv * 4, "pio_kv_project_bwd");
     if (g->bv == g->bk + e) {
-        PIO_TRY(cast_colsum_f32(dkv, 2 * e, dkv16, 2 * e, g->bk, acc, rows, 2 * e, c.rest(), c.rest_bytes(), c.st));
+        PIO_TRY(colsum_bf16(dkv16, 2 * e, g->bk, acc, rows, 2 * e, c.rest(), c.rest_bytes(), c.st));
     } else {
-        PIO_TRY(cast_colsum_f32(dkv, 2 * e, dkv16, 2 * e, g->bk, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
-        PIO_TRY(cast_colsum_f32(dkv + e, 2 * e, dkv16 + e, 2 * e, g->bv, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
+        PIO_TRY(colsum_bf16(dkv16, 2 * e, g->bk, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
+        PIO_TRY(colsum_bf16(dkv16 + e, 2 * e, g->bv, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
     }
     if (packed16(w->wk, w->wv, e, ckp)) {
         PIO_TRY(tc_dyW(c, dkv16, 2 * e, (const bf16*)w->wk, ckp, rows, 2 * e, ckv, dh0, ckv, nullptr, 0, 0, nullptr, 0, 0));
@@ -188,9 +189,11 @@ int kv_project_bwd(Ctx& c, const float* dkv, const float* x_kv, float* dx_kv, co
 }
 
 // ---------------------------------------------------------------- attention helpers
-static void fill_attn(pio_attn_desc& a, const float* q, int64_t q_rs, const float* k, const float* v, int64_t kv_rs,
+static void fill_attn(pio_attn_desc& a, const bf16* q, int64_t q_rs, const bf16* k, const bf16* v, int64_t kv_rs,
                       const uint8_t* pad, float* o, float* lse, int batch, int heads, int n, int m, int e) {
-    a.q = q; a.k = k; a.v = v; a.pad = pad; a.o = o; a.lse = lse;
+    // the descriptor's q/k/v are typed float*; AttnBf16Out::in16 tells the kernels they are bf16
+    a.q = reinterpret_cast<const float*>(q); a.k = reinterpret_cast<const float*>(k); a.v = reinterpret_cast<const float*>(v);
+    a.pad = pad; a.o = o; a.lse = lse;
     a.q_rs = q_rs; a.q_bs = (int64_t)n * q_rs;
     a.k_rs = kv_rs; a.k_bs = (int64_t)m * kv_rs;
     a.v_rs = kv_rs; a.v_bs = (int64_t)m * kv_rs;
@@ -201,15 +204,15 @@ static void fill_attn(pio_attn_desc& a, const float* q, int64_t q_rs, const floa
 
 // ---------------------------------------------------------------- query side of cross-attention
 struct XaSaved {
-    float *stats, *q, *o, *lse;
-    bf16 *hq, *o16;
+    float *stats, *o, *lse;
+    bf16 *hq, *q, *o16;
     size_t total;
     XaSaved(void* p, int batch, int n, int e, int heads) {
         const size_t r = (size_t)batch * n;
         ByteCarver k{(char*)p, 0};
         stats = k.f32(r * 2);
         hq = k.b16(r * e);
-        q = k.f32(r * e);
+        q = k.b16(r * e);
         o = k.f32(r * e);
         o16 = k.b16(r * e);
         lse = k.f32((size_t)batch * heads * n);
@@ -229,11 +232,13 @@ int cross_attend_fwd(Ctx& c, const float* x_q, const float* kv, const uint8_t* p
     XaSaved s(saved, batch, n, e, heads);
     const int64_t rows = (int64_t)batch * n;
     PIO_TRY(layernorm_fwd_bf16(x_q, w->ln_w, w->ln_b, s.hq, e, s.stats, rows, e, LN_EPS, c.st));
-    PIO_TRY(tc_xwT(c, s.hq, e, (const bf16*)w->wq, e, rows, e, e, s.q, e, nullptr, 0, w->bq, nullptr, 0, 0, nullptr, 0));
+    PIO_TRY(tc_xwT(c, s.hq, e, (const bf16*)w->wq, e, rows, e, e, nullptr, 0, s.q, e, w->bq, nullptr, 0, 0, nullptr, 0));
+    const bf16* kv16 = reinterpret_cast<const bf16*>(kv);
     pio_attn_desc a{};
-    fill_attn(a, s.q, e, kv, kv + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
+    fill_attn(a, s.q, e, kv16, kv16 + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
     AttnBf16Out ex;
     ex.o16 = s.o16;
+    ex.in16 = 1;
     PIO_TRY(attn_fwd_simt(&a, c.st, &ex));
     PIO_TRY(tc_xwT(c, s.o16, e, (const bf16*)w->wo, e, rows, e, e, y, e, nullptr, 0, w->bo, residual ? x_q : nullptr, e, 0,
                    nullptr, 0));
@@ -250,17 +255,19 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
     PIO_TAKE_BYTES(bf16, dy16, c, (size_t)rows * e * 2, "pio_cross_attend_bwd");
     PIO_TAKE_BYTES(bf16, dq16, c, (size_t)rows * e * 2, "pio_cross_attend_bwd");
     PIO_TAKE_BYTES(float, d_o, c, (size_t)rows * e * 4, "pio_cross_attend_bwd");
-    PIO_TAKE_BYTES(float, dq, c, (size_t)rows * e * 4, "pio_cross_attend_bwd");
     PIO_TAKE_BYTES(float, dhq, c, (size_t)rows * e * 4, "pio_cross_attend_bwd");
     PIO_TAKE_BYTES(float, delta, c, (size_t)batch * heads * n * 4, "pio_cross_attend_bwd");
     PIO_TRY(cast_colsum_f32(dy, e, dy16, e, g->bo, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
     PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)w->wo, e, rows, e, e, d_o, e, nullptr, 0, 0, nullptr, 0, 0));
     PIO_TRY(tc_dW(c, dy16, e, s.o16, e, g->wo, rows, e, e, acc));
+    const bf16* kv16 = reinterpret_cast<const bf16*>(kv);
+    bf16* dkv16 = reinterpret_cast<bf16*>(dkv);
     pio_attn_bwd_desc b{};
-    fill_attn(b.fwd, s.q, e, kv, kv + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
-    b.d_o = d_o; b.dq = dq; b.dk = dkv; b.dv = dkv + e; b.delta = delta;
+    fill_attn(b.fwd, s.q, e, kv16, kv16 + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
+    b.d_o = d_o; b.delta = delta;
     AttnBf16Out ex;
-    ex.dq16 = dq16;
+    ex.in16 = 1;
+    ex.dq16 = dq16; ex.dk16 = dkv16; ex.dv16 = dkv16 + e;
     PIO_TRY(attn_bwd_simt(&b, c.st, &ex));
     PIO_TRY(colsum_bf16(dq16, e, g->bq, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
     PIO_TRY(tc_dyW(c, dq16, e, (const bf16*)w->wq, e, rows, e, e, dhq, e, nullptr, 0, 0, nullptr, 0, 0));
@@ -273,15 +280,15 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
 
 // ---------------------------------------------------------------- self-attention layer
 struct SaSaved {
-    float *stats, *qkv, *o, *lse;
-    bf16 *h0, *o16;
+    float *stats, *o, *lse;
+    bf16 *h0, *qkv, *o16;
     size_t total;
     SaSaved(void* p, int batch, int n, int ch, int heads) {
         const size_t r = (size_t)batch * n;
         ByteCarver k{(char*)p, 0};
         stats = k.f32(r * 2);
         h0 = k.b16(r * ch);
-        qkv = k.f32(3 * r * ch);
+        qkv = k.b16(3 * r * ch);
         o = k.f32(r * ch);
         o16 = k.b16(r * ch);
         lse = k.f32((size_t)batch * heads * n);
@@ -310,12 +317,13 @@ int self_attn_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* w, v
     SaSaved s(saved, batch, n, ch, heads);
     const int64_t rows = (int64_t)batch * n;
     PIO_TRY(layernorm_fwd_bf16(x, w->ln_w, w->ln_b, s.h0, ch, s.stats, rows, ch, LN_EPS, c.st));
-    PIO_TRY(tc_xwT(c, s.h0, ch, (const bf16*)w->wq, ch, rows, 3 * ch, ch, s.qkv, 3 * ch, nullptr, 0, w->bq, nullptr, 0, 0,
+    PIO_TRY(tc_xwT(c, s.h0, ch, (const bf16*)w->wq, ch, rows, 3 * ch, ch, nullptr, 0, s.qkv, 3 * ch, w->bq, nullptr, 0, 0,
                    nullptr, 0));
     pio_attn_desc a{};
     fill_attn(a, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
     AttnBf16Out ex;
     ex.o16 = s.o16;
+    ex.in16 = 1;
     PIO_TRY(attn_fwd_simt(&a, c.st, &ex));
     PIO_TRY(tc_xwT(c, s.o16, ch, (const bf16*)w->wo, ch, rows, ch, ch, y, ch, nullptr, 0, w->bo, residual ? x : nullptr, ch, 0,
                    nullptr, 0));
@@ -336,15 +344,15 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
     PIO_TAKE_BYTES(bf16, dqkv16, c, (size_t)rows * 3 * ch * 2, "pio_self_attn_bwd");
     PIO_TAKE_BYTES(float, d_o, c, (size_t)rows * ch * 4, "pio_self_attn_bwd");
     PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ch * 4, "pio_self_attn_bwd");
-    PIO_TAKE_BYTES(float, dqkv, c, (size_t)rows * 3 * ch * 4, "pio_self_attn_bwd");
     PIO_TAKE_BYTES(float, delta, c, (size_t)batch * heads * n * 4, "pio_self_attn_bwd");
     PIO_TRY(cast_colsum_f32(dy, ch, dy16, ch, g->bo, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
     PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->wo, ch, rows, ch, ch, d_o, ch, nullptr, 0, 0, nullptr, 0, 0));
     PIO_TRY(tc_dW(c, dy16, ch, s.o16, ch, g->wo, rows, ch, ch, acc));
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
-    b.d_o = d_o; b.dq = dqkv; b.dk = dqkv + ch; b.dv = dqkv + 2 * ch; b.delta = delta;
+    b.d_o = d_o; b.delta = delta;
     AttnBf16Out ex;
+    ex.in16 = 1;
     ex.dq16 = dqkv16; ex.dk16 = dqkv16 + ch; ex.dv16 = dqkv16 + 2 * ch;
     PIO_TRY(attn_bwd_simt(&b, c.st, &ex));
     PIO_TRY(colsum_bf16(dqkv16, 3 * ch, g->bq, acc, rows, 3 * ch, c.rest(), c.rest_bytes(), c.st));

@@ -10,6 +10,7 @@ struct AttnBf16Out {
     __nv_bfloat16* dq16 = nullptr;
     __nv_bfloat16* dk16 = nullptr;
     __nv_bfloat16* dv16 = nullptr;
+    int in16 = 0;  // q, k, v of the descriptor point at bf16 data (same element strides)
 };
 int attn_fwd_simt(const pio_attn_desc* d, cudaStream_t st, const AttnBf16Out* extra = nullptr);
 int attn_bwd_simt(const pio_attn_bwd_desc* d, cudaStream_t st, const AttnBf16Out* extra = nullptr);

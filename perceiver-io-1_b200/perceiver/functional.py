@@ -253,7 +253,7 @@ class KVProjectFn(torch.autograd.Function):
         ctx.wstruct, ctx.keep = w, mats
         saved = _saved(L.pio_kv_project_saved_bytes(rows, ckv, e, mode), x_kv.device)
         ws = N.workspace(L.pio_kv_project_ws_bytes(rows, ckv, e, mode), x_kv.device)
-        kv = torch.empty(b, m, 2 * e, dtype=torch.float32, device=x_kv.device)
+        kv = torch.empty(b, m, 2 * e, dtype=torch.float32 if mode == N.MODE_FP32 else torch.bfloat16, device=x_kv.device)
         N.check(L.pio_kv_project_fwd(x_kv.data_ptr(), kv.data_ptr(), byref(w), saved.data_ptr(), rows, ckv, e, mode,
                                      ws.data_ptr(), ws.numel(), N.stream_ptr(x_kv.device)), "pio_kv_project_fwd")
         ctx.save_for_backward(x_kv, ln_w, ln_b, bias, w_packed, w_k, w_v)
@@ -266,7 +266,7 @@ class KVProjectFn(torch.autograd.Function):
     def backward(ctx, dkv):
         x_kv, ln_w, ln_b, bias, w_packed, w_k, w_v = ctx.saved_tensors
         rows, ckv, e, mode = ctx.meta
-        dkv = _c(dkv)
+        dkv = _c(dkv, torch.float32 if mode == N.MODE_FP32 else torch.bfloat16)
         L = N.lib()
         dev = x_kv.device
         dln_w, dln_b = torch.empty_like(ln_w), torch.empty_like(ln_b)
@@ -292,7 +292,8 @@ class CrossAttendFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x_q, kv, pad, ln_w, ln_b, bias, w_packed, w_q, wo, bo, heads, residual):
-        x_q, kv = _c(x_q), _c(kv)
+        mode = get_compute_mode()
+        x_q, kv = _c(x_q), _c(kv, torch.float32 if mode == N.MODE_FP32 else torch.bfloat16)
         ln_w, ln_b, bias, wo, bo = _c(ln_w), _c(ln_b), _c(bias), _c(wo), _c(bo)
         w_packed = _c(w_packed) if w_packed is not None else None
         w_q = _c(w_q) if w_q is not None else None
