@@ -152,7 +152,10 @@ int pio_cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t l
  * stored; lse (batch,heads,n) = logsumexp of the scaled scores, saved for the backward, which
  * recomputes P.  Head h is columns [h*dh,(h+1)*dh) of each row; *_bs / *_rs are batch / row
  * strides in elements (so a packed (rows,3E) qkv buffer is addressed without a copy).
- * A query whose keys are all padded yields NaN, like the reference. */
+ * A query whose keys are all padded yields NaN, like the reference.
+ * mode = PIO_MODE_BF16: q, k, v point at bf16 data (same element strides); the forward then runs the
+ * tcgen05 flash kernel (TMA-staged K/V tiles, QK^T and PV on the tensor cores, accumulators in TMEM)
+ * when dh == 64 and the fp32-arithmetic kernel otherwise; o, lse and the gradients stay fp32. */
 typedef struct {
     const float* q;
     const float* k;

@@ -468,12 +468,22 @@ int attn_bwd_simt(const pio_attn_bwd_desc* bd, cudaStream_t st, const AttnBf16Ou
 extern "C" {
 
 int pio_attn_fwd(const pio_attn_desc* d, int mode, pio_stream_t stream) {
-    (void)mode;
+    if (mode == PIO_MODE_BF16) {  // q, k, v are bf16 behind the float* type
+        PIO_CHECK_ARG(d != nullptr, "pio_attn_fwd: null descriptor");
+        if (pio::attn_fwd_tc_supported(d)) return pio::attn_fwd_tc(d, nullptr, (cudaStream_t)stream);
+        pio::AttnBf16Out ex;
+        ex.in16 = 1;
+        return pio::attn_fwd_simt(d, (cudaStream_t)stream, &ex);
+    }
     return pio::attn_fwd_simt(d, (cudaStream_t)stream);
 }
 
 int pio_attn_bwd(const pio_attn_bwd_desc* d, int mode, pio_stream_t stream) {
-    (void)mode;
+    if (mode == PIO_MODE_BF16) {
+        pio::AttnBf16Out ex;
+        ex.in16 = 1;
+        return pio::attn_bwd_simt(d, (cudaStream_t)stream, &ex);
+    }
     return pio::attn_bwd_simt(d, (cudaStream_t)stream);
 }
 

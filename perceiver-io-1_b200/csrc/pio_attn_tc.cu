@@ -1,0 +1,330 @@
+// Flash-style attention forward on the 5th-gen tensor cores (PIO_MODE_BF16, head dim 64).
+//
+// One CTA owns 128 query rows of one (batch, head) and streams the key/value axis in tiles of BKV keys:
+//   * Q, K and V tiles arrive by 3-D TMA (cp.async.bulk.tensor, 128-byte swizzle; the batch and row
+//     axes are separate tensor dimensions so rows past the end of a sample are zero-filled);
+//   * S = Q K^T is a tcgen05.mma (M=128, N=BKV, K=64) into TMEM; four softmax warps read it with
+//     tcgen05.ld (one query row per thread), apply scale, padding mask and the online-softmax update,
+//     and write P as bf16 straight into the swizzled K-major shared-memory layout the next MMA reads;
+//   * O_tile = P V is a second tcgen05.mma (V is consumed MN-major, exactly as TMA delivered it) into
+//     its own TMEM columns; the softmax threads fold it into their fp32 register accumulator with the
+//     running-max correction, so no N x M quantity ever exists outside the SM.
+// Small tiles (BKV = 64, 64 KB of shared memory, 128 TMEM columns) keep three CTAs resident per SM;
+// their phases interleave, which is what hides the TMA / MMA / MUFU latencies of this simple,
+// non-pipelined per-CTA schedule.
+// Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..5 = softmax.
+#include <cuda.h>
+
+#include "pio_ops_common.cuh"
+#include "pio_tc_common.cuh"
+
+namespace pio {
+
+constexpr int FA_BQ = 128;
+constexpr int FA_THREADS = 192;
+
+struct FaParams {
+    const uint8_t* pad;  // (batch, m) or null
+    float* o32;          // optional
+    __nv_bfloat16* o16;  // optional
+    float* lse;          // (batch, heads, n)
+    int64_t o_bs, o_rs;
+    int batch, heads, n, m;
+    float scale_log2e;
+};
+
+__device__ __forceinline__ float fast_exp2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"((uint64_t)map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <int BKV>
+__global__ void __launch_bounds__(FA_THREADS, 2)
+    attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                       const __grid_constant__ CUtensorMap tmV, const FaParams p) {
+    constexpr int DH = 64;
+    constexpr int Q_BYTES = FA_BQ * DH * 2;   // 16 KB
+    constexpr int KV_BYTES = BKV * DH * 2;    // 8 KB at BKV = 64
+    constexpr int P_BYTES = FA_BQ * BKV * 2;  // 16 KB at BKV = 64
+    constexpr int TMEM_COLS = (BKV + DH <= 128) ? 128 : 256;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* sQ = smem;
+    uint8_t* sK = sQ + Q_BYTES;           // [2][KV_BYTES]
+    uint8_t* sV = sK + 2 * KV_BYTES;      // [2][KV_BYTES]
+    uint8_t* sP = sV + 2 * KV_BYTES;      // BKV/64 regions of 128 rows x 128 B
+    float* sBias = (float*)(sP + P_BYTES);  // [2][BKV]
+    uint64_t* bars = (uint64_t*)(sBias + 2 * BKV);
+    uint64_t* q_full = bars;
+    uint64_t* kv_full = bars + 1;   // [2]
+    uint64_t* kv_empty = bars + 3;  // [2]
+    uint64_t* s_full = bars + 5;
+    uint64_t* p_full = bars + 6;
+    uint64_t* o_full = bars + 7;
+    uint32_t* tmem_slot = (uint32_t*)(bars + 8);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q0 = blockIdx.x * FA_BQ, h = blockIdx.y, b = blockIdx.z;
+    const int T = (p.m + BKV - 1) / BKV;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmQ);
+        prefetch_tmap(&tmK);
+        prefetch_tmap(&tmV);
+        mbar_init(q_full, 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&kv_full[s], 1);
+            mbar_init(&kv_empty[s], 1);
+        }
+        mbar_init(s_full, 1);
+        mbar_init(p_full, 4);
+        mbar_init(o_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_s = tmem_base;
+    const uint32_t tmem_o = tmem_base + BKV;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(q_full, Q_BYTES);
+            tma_load_3d(sQ, &tmQ, h * DH, q0, b, q_full);
+            for (int j = 0; j < T; ++j) {
+                const int s = j & 1;
+                const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+                mbar_wait(&kv_empty[s], ph ^ 1u);
+                mbar_expect_tx(&kv_full[s], 2 * KV_BYTES);
+                tma_load_3d(sK + s * KV_BYTES, &tmK, h * DH, j * BKV, b, &kv_full[s]);
+                tma_load_3d(sV + s * KV_BYTES, &tmV, h * DH, j * BKV, b, &kv_full[s]);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc_s = make_idesc(BKV, false, false);
+            const uint32_t idesc_o = make_idesc(DH, false, true);
+            mbar_wait(q_full, 0);
+            for (int j = 0; j < T; ++j) {
+                const int s = j & 1;
+                const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+                mbar_wait(&kv_full[s], ph);
+                tc_fence_after();
+                const uint32_t q_addr = smem_u32(sQ), k_addr = smem_u32(sK + s * KV_BYTES), v_addr = smem_u32(sV + s * KV_BYTES);
+#pragma unroll
+                for (int t = 0; t < DH / 16; ++t)
+                    umma_bf16(tmem_s, make_smem_desc(q_addr + t * 32, 16, 1024), make_smem_desc(k_addr + t * 32, 16, 1024), idesc_s,
+                              t > 0 ? 1u : 0u);
+                umma_commit(s_full);
+                mbar_wait(p_full, (uint32_t)j & 1u);
+                tc_fence_after();
+                const uint32_t p_addr = smem_u32(sP);
+#pragma unroll
+                for (int t = 0; t < BKV / 16; ++t)
+                    umma_bf16(tmem_o, make_smem_desc(p_addr + (t / 4) * 16384 + (t % 4) * 32, 16, 1024),
+                              make_smem_desc(v_addr + t * 2048, BKV * 128, 1024), idesc_o, t > 0 ? 1u : 0u);
+                umma_commit(o_full);
+                umma_commit(&kv_empty[s]);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ---------------- softmax warps: thread = query row, TMEM lane quadrant = warp id mod 4
+        const int qd = warp & 3;
+        const int row = qd * 32 + lane;      // 0..127 within the tile
+        const int tid = (warp - 2) * 32 + lane;  // 0..127 for cooperative loads
+        const uint32_t lane_off = (uint32_t)(qd * 32) << 16;
+        const uint8_t* padb = p.pad ? p.pad + (int64_t)b * p.m : nullptr;
+        float m_run = -INFINITY, l_run = 0.f;
+        float acc[DH];
+#pragma unroll
+        for (int d = 0; d < DH; ++d) acc[d] = 0.f;
+        for (int j = 0; j < T; ++j) {
+            const int j0 = j * BKV;
+            const bool masked = (padb != nullptr) || (j0 + BKV > p.m);  // CTA-uniform
+            float* bias = sBias + (j & 1) * BKV;
+            if (masked) {
+                if (tid < BKV) {
+                    const int key = j0 + tid;
+                    const bool dead = (key >= p.m) || (padb != nullptr && padb[key] != 0);
+                    bias[tid] = dead ? -INFINITY : 0.f;
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            }
+            mbar_wait(s_full, (uint32_t)j & 1u);
+            tc_fence_after();
+            // pass 1: row maximum of the scaled scores
+            float mx = -INFINITY;
+#pragma unroll
+            for (int c0 = 0; c0 < BKV; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld32(tmem_s + lane_off + (uint32_t)c0, r);
+                tmem_ld_wait();
+                if (masked) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]) * p.scale_log2e + bias[c0 + i]);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]) * p.scale_log2e);
+                }
+            }
+            const float m_new = fmaxf(m_run, mx);
+            const float m_use = (m_new == -INFINITY) ? 0.f : m_new;  // fully masked so far: every p below is 0
+            const float alpha = fast_exp2(m_run - m_use);            // exp2(-inf) = 0 on the first live tile
+            // pass 2: p = exp2(s - m), row sum, bf16 P into the swizzled K-major layout
+            float l_tile = 0.f;
+#pragma unroll
+            for (int c0 = 0; c0 < BKV; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld32(tmem_s + lane_off + (uint32_t)c0, r);
+                tmem_ld_wait();
+                float pv[32];
+                if (masked) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) pv[i] = fast_exp2(__uint_as_float(r[i]) * p.scale_log2e + bias[c0 + i] - m_use);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) pv[i] = fast_exp2(__uint_as_float(r[i]) * p.scale_log2e - m_use);
+                }
+#pragma unroll
+                for (int i = 0; i < 32; ++i) l_tile += pv[i];
+                uint8_t* prow = sP + (c0 / 64) * 16384 + row * 128;
+#pragma unroll
+                for (int piece = 0; piece < 4; ++piece) {
+                    uint32_t w[4];
+#pragma unroll
+                    for (int e2 = 0; e2 < 4; ++e2) {
+                        __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[piece * 8 + 2 * e2], pv[piece * 8 + 2 * e2 + 1]);
+                        w[e2] = *reinterpret_cast<uint32_t*>(&h2);
+                    }
+                    const int ci = ((c0 % 64) / 32) * 4 + piece;  // 16-byte chunk index within the 128-byte row
+                    *reinterpret_cast<uint4*>(prow + ((ci ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+            }
+            l_run = l_run * alpha + l_tile;
+            m_run = m_new;
+            tc_fence_before();     // TMEM reads of S are done before the next MMA may overwrite it
+            fence_proxy_async();   // P stores visible to the tensor-core (async) proxy
+            __syncwarp();
+            if (lane == 0) mbar_arrive(p_full);
+            // fold O_tile = P V into the register accumulator
+            mbar_wait(o_full, (uint32_t)j & 1u);
+            tc_fence_after();
+#pragma unroll
+            for (int c0 = 0; c0 < DH; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld32(tmem_o + lane_off + (uint32_t)c0, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[c0 + i] = fmaf(acc[c0 + i], alpha, __uint_as_float(r[i]));
+            }
+        }
+        tc_fence_before();
+        const int qi = q0 + row;
+        if (qi < p.n) {
+            const float inv = 1.0f / l_run;  // l = 0 (every key padded): inf * 0 = NaN, like the reference
+            const int64_t off = (int64_t)b * p.o_bs + (int64_t)qi * p.o_rs + (int64_t)h * DH;
+            if (p.o32) {
+                float* o = p.o32 + off;
+#pragma unroll
+                for (int d = 0; d < DH; d += 4)
+                    *reinterpret_cast<float4*>(o + d) = make_float4(acc[d] * inv, acc[d + 1] * inv, acc[d + 2] * inv, acc[d + 3] * inv);
+            }
+            if (p.o16) {
+                __nv_bfloat16* o = p.o16 + off;
+#pragma unroll
+                for (int d = 0; d < DH; d += 8) {
+                    uint32_t w[4];
+#pragma unroll
+                    for (int e2 = 0; e2 < 4; ++e2) {
+                        __nv_bfloat162 h2 = __floats2bfloat162_rn(acc[d + 2 * e2] * inv, acc[d + 2 * e2 + 1] * inv);
+                        w[e2] = *reinterpret_cast<uint32_t*>(&h2);
+                    }
+                    *reinterpret_cast<uint4*>(o + d) = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+            }
+            p.lse[((int64_t)b * p.heads + h) * p.n + qi] = (m_run + log2f(l_run)) * 0.69314718055994530942f;
+        }
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+// 3-D bf16 tensor map over (batch, rows, cols) with element strides (bs, rs, 1); box = 64 cols x box_rows x 1
+static int make_tmap3(CUtensorMap* map, const void* base, int64_t cols, int64_t rows, int64_t batch, int64_t rs, int64_t bs,
+                      int box_rows) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) {
+        set_error("cuTensorMapEncodeTiled entry point not available from the driver");
+        return PIO_ERR_CUDA;
+    }
+    PIO_CHECK_ARG((((uintptr_t)base) & 15) == 0 && rs % 8 == 0 && bs % 8 == 0,
+                  "attention (bf16): operand base/strides must be 16-byte aligned (base %p, row stride %lld, batch stride %lld)",
+                  base, (long long)rs, (long long)bs);
+    cuuint64_t gdim[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)batch};
+    cuuint64_t gstr[2] = {(cuuint64_t)rs * 2, (cuuint64_t)bs * 2};
+    cuuint32_t box[3] = {64u, (cuuint32_t)box_rows, 1u};
+    cuuint32_t estr[3] = {1u, 1u, 1u};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim, gstr, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled (3-D) failed with CUresult %d", (int)r);
+        return PIO_ERR_CUDA;
+    }
+    return PIO_OK;
+}
+
+bool attn_fwd_tc_supported(const pio_attn_desc* d) { return d->dh == 64 && d->n > 0 && d->m > 0 && d->batch > 0; }
+
+// q, k, v of the descriptor are bf16 (element strides as given); writes o (fp32, optional via d->o),
+// o16 (optional) and lse.
+int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st) {
+    PIO_CHECK_ARG(d && d->q && d->k && d->v && d->lse && (d->o || o16), "attn_fwd_tc: null pointer");
+    PIO_CHECK_ARG(attn_fwd_tc_supported(d), "attn_fwd_tc: unsupported shape (head dim %d)", d->dh);
+    PIO_CHECK_ARG(d->heads <= 65535 && d->batch <= 65535, "attn_fwd_tc: batch/heads exceed grid limits");
+    constexpr int BKV = 64;
+    const int64_t cols = (int64_t)d->heads * d->dh;
+    CUtensorMap tq, tk, tv;
+    PIO_TRY(make_tmap3(&tq, d->q, cols, d->n, d->batch, d->q_rs, d->q_bs, FA_BQ));
+    PIO_TRY(make_tmap3(&tk, d->k, cols, d->m, d->batch, d->k_rs, d->k_bs, BKV));
+    PIO_TRY(make_tmap3(&tv, d->v, cols, d->m, d->batch, d->v_rs, d->v_bs, BKV));
+    FaParams p{};
+    p.pad = d->pad;
+    p.o32 = d->o;
+    p.o16 = o16;
+    p.lse = d->lse;
+    p.o_bs = d->o_bs; p.o_rs = d->o_rs;
+    p.batch = d->batch; p.heads = d->heads; p.n = d->n; p.m = d->m;
+    p.scale_log2e = d->scale * 1.44269504088896340736f;
+    const size_t smem = (size_t)FA_BQ * 64 * 2 + 4 * (size_t)BKV * 64 * 2 + (size_t)FA_BQ * BKV * 2 + 2 * BKV * 4 + 128 + 1024;
+    static bool configured = false;
+    if (!configured) {
+        PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    dim3 grid((unsigned)cdiv(d->n, FA_BQ), (unsigned)d->heads, (unsigned)d->batch);
+    attn_fwd_tc_kernel<BKV><<<grid, FA_THREADS, smem, st>>>(tq, tk, tv, p);
+    PIO_LAUNCH_CHECK();
+    return PIO_OK;
+}
+
+}  // namespace pio

@@ -202,6 +202,16 @@ static void fill_attn(pio_attn_desc& a, const bf16* q, int64_t q_rs, const bf16*
     a.scale = 1.0f / sqrtf((float)(e / heads));
 }
 
+// bf16 q/k/v -> o (fp32 + bf16) and lse: tensor-core flash kernel when the head size allows, else
+// the fp32-arithmetic kernel reading the same bf16 operands
+static int attention_fwd(const pio_attn_desc& a, bf16* o16, cudaStream_t st) {
+    if (attn_fwd_tc_supported(&a)) return attn_fwd_tc(&a, o16, st);
+    AttnBf16Out ex;
+    ex.o16 = o16;
+    ex.in16 = 1;
+    return attn_fwd_simt(&a, st, &ex);
+}
+
 // ---------------------------------------------------------------- query side of cross-attention
 struct XaSaved {
     float *stats, *o, *lse;
@@ -236,10 +246,7 @@ int cross_attend_fwd(Ctx& c, const float* x_q, const float* kv, const uint8_t* p
     const bf16* kv16 = reinterpret_cast<const bf16*>(kv);
     pio_attn_desc a{};
     fill_attn(a, s.q, e, kv16, kv16 + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
-    AttnBf16Out ex;
-    ex.o16 = s.o16;
-    ex.in16 = 1;
-    PIO_TRY(attn_fwd_simt(&a, c.st, &ex));
+    PIO_TRY(attention_fwd(a, s.o16, c.st));
     PIO_TRY(tc_xwT(c, s.o16, e, (const bf16*)w->wo, e, rows, e, e, y, e, nullptr, 0, w->bo, residual ? x_q : nullptr, e, 0,
                    nullptr, 0));
     return PIO_OK;
@@ -321,10 +328,7 @@ int self_attn_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* w, v
                    nullptr, 0));
     pio_attn_desc a{};
     fill_attn(a, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
-    AttnBf16Out ex;
-    ex.o16 = s.o16;
-    ex.in16 = 1;
-    PIO_TRY(attn_fwd_simt(&a, c.st, &ex));
+    PIO_TRY(attention_fwd(a, s.o16, c.st));
     PIO_TRY(tc_xwT(c, s.o16, ch, (const bf16*)w->wo, ch, rows, ch, ch, y, ch, nullptr, 0, w->bo, residual ? x : nullptr, ch, 0,
                    nullptr, 0));
     return PIO_OK;

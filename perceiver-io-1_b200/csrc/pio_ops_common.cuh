@@ -15,6 +15,10 @@ struct AttnBf16Out {
 int attn_fwd_simt(const pio_attn_desc* d, cudaStream_t st, const AttnBf16Out* extra = nullptr);
 int attn_bwd_simt(const pio_attn_bwd_desc* d, cudaStream_t st, const AttnBf16Out* extra = nullptr);
 
+// tcgen05 flash attention forward (pio_attn_tc.cu): q, k, v of the descriptor are bf16
+bool attn_fwd_tc_supported(const pio_attn_desc* d);
+int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st);
+
 int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream_t st);
 int cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_src, int64_t ld_dst, cudaStream_t st);
 
