@@ -14,6 +14,7 @@
 // non-pipelined per-CTA schedule.
 // Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..5 = softmax.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "pio_ops_common.cuh"
 #include "pio_tc_common.cuh"
@@ -293,7 +294,10 @@ static int make_tmap3(CUtensorMap* map, const void* base, int64_t cols, int64_t 
     return PIO_OK;
 }
 
-bool attn_fwd_tc_supported(const pio_attn_desc* d) { return d->dh == 64 && d->n > 0 && d->m > 0 && d->batch > 0; }
+bool attn_fwd_tc_supported(const pio_attn_desc* d) {
+    static const bool disabled = getenv("PIO_DISABLE_TC_ATTN") != nullptr;  // debugging aid: force the fp32-arithmetic kernel
+    return !disabled && d->dh == 64 && d->n > 0 && d->m > 0 && d->batch > 0;
+}
 
 // q, k, v of the descriptor are bf16 (element strides as given); writes o (fp32, optional via d->o),
 // o16 (optional) and lse.
