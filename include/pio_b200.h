@@ -95,6 +95,21 @@ int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const
                       int64_t rows, int c, void* ws, size_t ws_bytes, pio_stream_t stream);
 size_t pio_layernorm_bwd_ws_bytes(int64_t rows, int c);
 
+/* No counterpart in the reference (which is Python over torch's allocator): pio_layernorm_bwd for
+ * callers that cannot allocate device memory — code running under stream capture or in hooks where
+ * cudaMalloc / torch's allocator is off limits, plugin hosts that pass only inputs and outputs,
+ * embedders with a fixed device-memory budget.  Identical arguments and results, but the scratch for
+ * the dgamma / dbeta partial sums is a static device array inside the library (1 MiB per GPU that
+ * loads it, held until exit) instead of a workspace.  c must be <= PIO_LN_NOALLOC_MAX_C (PIO_ERR_ARG
+ * otherwise).  The first call on a device looks up the array's address and should be made before any
+ * stream capture.  All calls on a device share the array: calls that can overlap on the GPU race, so
+ * serialise them; stale contents from the previous call are harmless (every partial row read is
+ * written first by the same call).  Calls no cudaMalloc / cudaFree / allocating routine. */
+#define PIO_LN_NOALLOC_MAX_C 1024
+int pio_layernorm_bwd_noalloc(const float* dy, const float* x, const float* stats, const float* w,
+                              const float* dres, float* dx, float* dw, float* db, int accumulate,
+                              int64_t rows, int c, pio_stream_t stream);
+
 /* C[m,n] = sum_k A(m,k) B(n,k) with a fused epilogue — nn.Linear forward / backward
  * (model.py:23,25; adapter.py:146-149) and the MHA projections (model.py:66-74).
  *   a_kmajor: A(m,k) = a[m*lda+k] else a[k*lda+m];  b_kmajor: B(n,k) = b[n*ldb+k] else b[k*ldb+n].

@@ -3,6 +3,7 @@
 // reductions, cross-entropy fwd/bwd.  All coalesced along the channel axis.
 #include <stdarg.h>
 #include <atomic>
+#include <mutex>
 
 #include "pio_common.cuh"
 
@@ -473,6 +474,35 @@ __global__ void ce_bwd_kernel(const float* __restrict__ logits, const int64_t* _
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Scratch for pio_layernorm_bwd_noalloc (see that entry point below): the per-block partial sums of
+// dgamma / dbeta, held in device memory that is part of the loaded library image instead of a
+// caller-provided workspace.  PIO_LN_NOALLOC_BLOCKS x 2 x PIO_LN_NOALLOC_MAX_C floats = 1 MiB,
+// resident on every GPU that loads the library until the process exits.
+// ---------------------------------------------------------------------------------------------
+constexpr int PIO_LN_NOALLOC_BLOCKS = 128;
+static __device__ __align__(256) float g_ln_noalloc_scratch[PIO_LN_NOALLOC_BLOCKS * 2 * PIO_LN_NOALLOC_MAX_C];
+
+// On the host the array's name is only a handle for the runtime, not a device address: a kernel
+// handed &g_ln_noalloc_scratch[0] from host code would fault (or scribble on host-reachable memory).
+// The device address is resolved once per device, with that device current, and cached.
+static int ln_noalloc_scratch(float** out) {
+    static std::mutex mu;
+    static float* per_device[64] = {nullptr};
+    int dev = -1;
+    PIO_CUDA(cudaGetDevice(&dev));
+    PIO_CHECK_ARG(dev >= 0 && dev < 64, "pio_layernorm_bwd_noalloc: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (per_device[dev] == nullptr) {
+        float* ptr = nullptr;
+        PIO_CUDA(cudaGetSymbolAddress((void**)&ptr, g_ln_noalloc_scratch));
+        PIO_CHECK_ARG(ptr != nullptr, "pio_layernorm_bwd_noalloc: could not resolve the scratch array on device %d", dev);
+        per_device[dev] = ptr;
+    }
+    *out = per_device[dev];
+    return PIO_OK;
+}
+
 }  // namespace pio
 
 using namespace pio;
@@ -619,6 +649,53 @@ int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const
 #undef PIO_LN_BWD
     PIO_LAUNCH_CHECK();
     // partial rows are [dw(c) | db(c)] : reduce both with one launch
+    return reduce_partials(partial, blocks, (int64_t)2 * c, dw, c, db, c, accumulate, st);
+}
+
+// LayerNorm backward for callers that cannot allocate device memory.
+//
+// Same arithmetic and arguments as pio_layernorm_bwd, minus the workspace: the partial sums go to
+// the library's own static device array.  Meant for callers that have nowhere to get scratch from —
+// code that runs while a stream is being captured or inside a hook where cudaMalloc (and torch's
+// caching allocator, which can fall through to it) must not be called, plugin hosts that pass a
+// kernel library only their input and output buffers, and embedders that must not grow device
+// memory after start-up.
+//
+// Contract:
+//   * c <= PIO_LN_NOALLOC_MAX_C, otherwise PIO_ERR_ARG with a message saying so (nothing launched);
+//   * the first call on each device resolves the array's device address (cudaGetSymbolAddress);
+//     make that first call outside any stream capture;
+//   * every call on a device uses the same array: two calls whose kernels can overlap on the GPU
+//     (e.g. on different streams) race — serialise them;
+//   * the array keeps whatever the previous call left; that is harmless, because every partial row
+//     the final reduction reads is written in full by the same call first (nothing needs zeroing);
+//   * no cudaMalloc / cudaFree / allocating library routine is called, here or underneath.
+int pio_layernorm_bwd_noalloc(const float* dy, const float* x, const float* stats, const float* w, const float* dres,
+                              float* dx, float* dw, float* db, int accumulate, int64_t rows, int c, pio_stream_t stream) {
+    PIO_CHECK_ARG(dy && x && stats && w && dw && db && c > 0 && rows >= 0, "pio_layernorm_bwd_noalloc: bad arguments");
+    PIO_CHECK_ARG(c <= PIO_LN_NOALLOC_MAX_C,
+                  "pio_layernorm_bwd_noalloc: %d channels exceed the built-in scratch (at most %d); use pio_layernorm_bwd "
+                  "with a caller-provided workspace",
+                  c, PIO_LN_NOALLOC_MAX_C);
+    if (rows == 0) return PIO_OK;
+    float* partial = nullptr;
+    PIO_TRY(ln_noalloc_scratch(&partial));
+    const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>(cdiv(rows, 8), PIO_LN_NOALLOC_BLOCKS));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t smem = (size_t)8 * 2 * c * sizeof(float);
+#define PIO_LN_BWD_NA(NCH)                                                                                      \
+    do {                                                                                                        \
+        if (smem > 48 * 1024)                                                                                   \
+            PIO_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                          (int)smem));                                                          \
+        layernorm_bwd_kernel<NCH><<<blocks, 256, smem, st>>>(dy, x, stats, w, dres, dx, partial, rows, c);       \
+    } while (0)
+    if (c <= 128) PIO_LN_BWD_NA(4);
+    else if (c <= 256) PIO_LN_BWD_NA(8);
+    else if (c <= 512) PIO_LN_BWD_NA(16);
+    else PIO_LN_BWD_NA(32);
+#undef PIO_LN_BWD_NA
+    PIO_LAUNCH_CHECK();
     return reduce_partials(partial, blocks, (int64_t)2 * c, dw, c, db, c, accumulate, st);
 }
 

@@ -78,6 +78,7 @@ _SIGNATURES = {
     "pio_layernorm_fwd": (c_int, [P, P, P, P, P, c_int64, c_int, c_float, P]),
     "pio_layernorm_bwd": (c_int, [P, P, P, P, P, P, P, P, c_int, c_int64, c_int, P, c_size_t, P]),
     "pio_layernorm_bwd_ws_bytes": (c_size_t, [c_int64, c_int]),
+    "pio_layernorm_bwd_noalloc": (c_int, [P, P, P, P, P, P, P, P, c_int, c_int64, c_int, P]),
     "pio_gemm_f32": (c_int, [POINTER(GemmDesc), P, c_size_t, P]),
     "pio_gemm_f32_ws_bytes": (c_size_t, [c_int64, c_int64, c_int64]),
     "pio_gemm_bf16": (c_int, [POINTER(GemmBf16Desc), P, c_size_t, P]),
