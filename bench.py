@@ -207,12 +207,14 @@ def cross_attention_core_tflops(mode, pk):
     b, m, n, heads, dh = 32, 16384, 256, 8, 64
     e = heads * dh
     dev = torch.device("cuda", torch.cuda.current_device())
-    q = torch.randn(b, n, e, device=dev)
-    kv = torch.randn(b, m, 2 * e, device=dev)
+    dt = torch.float32 if mode == 0 else torch.bfloat16  # bf16 mode: bf16 q / kv feed the tcgen05 flash kernel
+    q = torch.randn(b, n, e, device=dev).to(dt)
+    kv = torch.randn(b, m, 2 * e, device=dev).to(dt)
+    esz = q.element_size()
     o = torch.empty(b, n, e, device=dev)
     lse = torch.empty(b, heads, n, device=dev)
     d = N.AttnDesc()
-    d.q, d.k, d.v, d.pad, d.o, d.lse = q.data_ptr(), kv.data_ptr(), kv.data_ptr() + 4 * e, None, o.data_ptr(), lse.data_ptr()
+    d.q, d.k, d.v, d.pad, d.o, d.lse = q.data_ptr(), kv.data_ptr(), kv.data_ptr() + esz * e, None, o.data_ptr(), lse.data_ptr()
     d.q_bs, d.q_rs, d.k_bs, d.k_rs, d.v_bs, d.v_rs, d.o_bs, d.o_rs = n * e, e, m * 2 * e, 2 * e, m * 2 * e, 2 * e, n * e, e
     d.batch, d.heads, d.n, d.m, d.dh, d.scale = b, heads, n, m, dh, dh ** -0.5
     L = N.lib()
@@ -229,8 +231,8 @@ def cross_attention_core_tflops(mode, pk):
     ms = sum(times) / len(times)
     flops = 4.0 * b * n * m * e
     tf = flops / (ms * 1e-3) / 1e12
-    return {"shape": "B32 M16384 N256 H8 dh64 fwd", "ms": round(ms, 3), "tflops": round(tf, 2),
-            "frac_of_bf16_peak": round(tf / pk["tflops"], 5)}
+    return {"shape": "B32 M16384 N256 H8 dh64 fwd", "kernel": "attn_fwd_tc_kernel (tcgen05 flash)" if mode else "attn_fwd_kernel (fp32 FFMA)",
+            "ms": round(ms, 3), "tflops": round(tf, 2), "frac_of_bf16_peak": round(tf / pk["tflops"], 5)}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -381,7 +383,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--profile-only", action="store_true", help="timed steps only (for ncu launch lists)")
-    ap.add_argument("--mode", default=os.environ.get("PIO_MODE", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--mode", default=os.environ.get("PIO_MODE", "bf16"), choices=["fp32", "bf16"])
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)
