@@ -193,6 +193,13 @@ typedef struct {
     float* delta;       /* scratch (batch,heads,n) */
 } pio_attn_bwd_desc;
 int pio_attn_bwd(const pio_attn_bwd_desc* d, int mode, pio_stream_t stream);
+/* The all-bf16 tensor-core backward used inside the PIO_MODE_BF16 operators (dh == 64 only, else
+ * PIO_ERR_UNSUPPORTED): q, k, v of `fwd`, d_o (strides of o) and the outputs dq / dk / dv (strides of
+ * q / k / v) are bf16; o and lse fp32.  Two kernels, both recomputing P from lse with QK^T, dO V^T and
+ * the three gradient products on tcgen05: one per 128 query rows (dq, delta), one per 128 key rows
+ * (dk, dv).  delta: scratch (batch, heads, n). */
+int pio_attn_bwd_bf16(const pio_attn_desc* fwd, const void* d_o16, void* dq16, void* dk16, void* dv16,
+                      float* delta, pio_stream_t stream);
 
 /* nn.CrossEntropyLoss (lightning.py:61,184,225-226): mean over targets != ignore_index of
  * logsumexp(logits) - logits[target].  out3 = {loss, n_valid, loss_sum}; row_lse holds 2*rows floats: the per-row

@@ -269,6 +269,398 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Backward.  P is recomputed from the saved log-sum-exp (nothing of size N x M was stored).  Two
+// kernels, mirroring the forward: one owns query rows and produces dQ (and the row term
+// delta = dO.O), one owns key rows and produces dK and dV — so no gradient needs atomics.
+// All five products run on tcgen05 with their accumulators in TMEM; dQ, dK and dV accumulate across
+// the streamed tiles directly in TMEM (no online rescaling exists in the backward).
+// ---------------------------------------------------------------------------------------------
+struct FaBwdParams {
+    const uint8_t* pad;      // (batch, m) or null
+    const float* o32;        // forward output (for delta)
+    const __nv_bfloat16* do16;
+    const float* lse;        // (batch, heads, n), natural log
+    float* delta;            // (batch, heads, n): written by the dQ kernel, read by the dK/dV kernel
+    __nv_bfloat16* dq16;
+    __nv_bfloat16* dk16;
+    __nv_bfloat16* dv16;
+    int64_t o_bs, o_rs, q_bs, q_rs, k_bs, k_rs, v_bs, v_rs;
+    int batch, heads, n, m;
+    float scale, scale_log2e;
+};
+
+// 32 fp32 values -> bf16, into row `row` of a 128-row x 128-byte swizzled (K-major, SW128) region;
+// half = which 64-byte half of the 128-byte row (columns 0..31 or 32..63 of the 64-column region)
+__device__ __forceinline__ void store_row_half_bf16(uint8_t* region, int row, int half, const float (&v)[32]) {
+    uint8_t* prow = region + row * 128;
+#pragma unroll
+    for (int piece = 0; piece < 4; ++piece) {
+        uint32_t w[4];
+#pragma unroll
+        for (int e2 = 0; e2 < 4; ++e2) {
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[piece * 8 + 2 * e2], v[piece * 8 + 2 * e2 + 1]);
+            w[e2] = *reinterpret_cast<uint32_t*>(&h2);
+        }
+        const int ci = half * 4 + piece;
+        *reinterpret_cast<uint4*>(prow + ((ci ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+__device__ __forceinline__ void store_row64_bf16_global(__nv_bfloat16* dst, const float (&v)[32], int c0) {
+#pragma unroll
+    for (int d = 0; d < 32; d += 8) {
+        uint32_t w[4];
+#pragma unroll
+        for (int e2 = 0; e2 < 4; ++e2) {
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[d + 2 * e2], v[d + 2 * e2 + 1]);
+            w[e2] = *reinterpret_cast<uint32_t*>(&h2);
+        }
+        *reinterpret_cast<uint4*>(dst + c0 + d) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+// dQ: CTA = 128 query rows of one (batch, head); streams key tiles of 64.
+__global__ void __launch_bounds__(FA_THREADS, 2)
+    attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
+                          const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const FaBwdParams p) {
+    constexpr int DH = 64, BKV = 64;
+    constexpr int Q_BYTES = FA_BQ * DH * 2, KV_BYTES = BKV * DH * 2, DS_BYTES = FA_BQ * BKV * 2;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* sQ = smem;
+    uint8_t* sdO = sQ + Q_BYTES;
+    uint8_t* sK = sdO + Q_BYTES;      // [2]
+    uint8_t* sV = sK + 2 * KV_BYTES;  // [2]
+    uint8_t* sdS = sV + 2 * KV_BYTES;
+    float* sBias = (float*)(sdS + DS_BYTES);  // [2][BKV]
+    uint64_t* bars = (uint64_t*)(sBias + 2 * BKV);
+    uint64_t* qdo_full = bars;
+    uint64_t* kv_full = bars + 1;   // [2]
+    uint64_t* kv_empty = bars + 3;  // [2]
+    uint64_t* sdp_full = bars + 5;
+    uint64_t* ds_full = bars + 6;
+    uint64_t* dq_done = bars + 7;
+    uint32_t* tmem_slot = (uint32_t*)(bars + 8);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q0 = blockIdx.x * FA_BQ, h = blockIdx.y, b = blockIdx.z;
+    const int T = (p.m + BKV - 1) / BKV;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmQ); prefetch_tmap(&tmdO); prefetch_tmap(&tmK); prefetch_tmap(&tmV);
+        mbar_init(qdo_full, 1);
+        for (int s = 0; s < 2; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+        mbar_init(sdp_full, 1);
+        mbar_init(ds_full, 4);
+        mbar_init(dq_done, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_s = tmem_base, tmem_dp = tmem_base + 64, tmem_dq = tmem_base + 128;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(qdo_full, 2 * Q_BYTES);
+            tma_load_3d(sQ, &tmQ, h * DH, q0, b, qdo_full);
+            tma_load_3d(sdO, &tmdO, h * DH, q0, b, qdo_full);
+            for (int j = 0; j < T; ++j) {
+                const int s = j & 1;
+                const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+                mbar_wait(&kv_empty[s], ph ^ 1u);
+                mbar_expect_tx(&kv_full[s], 2 * KV_BYTES);
+                tma_load_3d(sK + s * KV_BYTES, &tmK, h * DH, j * BKV, b, &kv_full[s]);
+                tma_load_3d(sV + s * KV_BYTES, &tmV, h * DH, j * BKV, b, &kv_full[s]);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc_kk = make_idesc(BKV, false, false);  // S, dP: both operands K-major
+            const uint32_t idesc_dq = make_idesc(DH, false, true);    // dQ: dS K-major, K tile MN-major
+            mbar_wait(qdo_full, 0);
+            const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sdO), ds_addr = smem_u32(sdS);
+            for (int j = 0; j < T; ++j) {
+                const int s = j & 1;
+                const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+                mbar_wait(&kv_full[s], ph);
+                tc_fence_after();
+                const uint32_t k_addr = smem_u32(sK + s * KV_BYTES), v_addr = smem_u32(sV + s * KV_BYTES);
+#pragma unroll
+                for (int t = 0; t < DH / 16; ++t)
+                    umma_bf16(tmem_s, make_smem_desc(q_addr + t * 32, 16, 1024), make_smem_desc(k_addr + t * 32, 16, 1024), idesc_kk,
+                              t > 0 ? 1u : 0u);
+#pragma unroll
+                for (int t = 0; t < DH / 16; ++t)
+                    umma_bf16(tmem_dp, make_smem_desc(do_addr + t * 32, 16, 1024), make_smem_desc(v_addr + t * 32, 16, 1024), idesc_kk,
+                              t > 0 ? 1u : 0u);
+                umma_commit(sdp_full);
+                mbar_wait(ds_full, (uint32_t)j & 1u);
+                tc_fence_after();
+#pragma unroll
+                for (int t = 0; t < BKV / 16; ++t)
+                    umma_bf16(tmem_dq, make_smem_desc(ds_addr + t * 32, 16, 1024), make_smem_desc(k_addr + t * 2048, BKV * 128, 1024),
+                              idesc_dq, (j > 0 || t > 0) ? 1u : 0u);
+                umma_commit(dq_done);
+                umma_commit(&kv_empty[s]);
+            }
+        }
+        __syncwarp();
+    } else {
+        const int qd = warp & 3;
+        const int row = qd * 32 + lane;
+        const int tid = (warp - 2) * 32 + lane;
+        const uint32_t lane_off = (uint32_t)(qd * 32) << 16;
+        const uint8_t* padb = p.pad ? p.pad + (int64_t)b * p.m : nullptr;
+        const int qi = q0 + row;
+        const bool q_ok = qi < p.n;
+        // delta = dO . O for this row; lse in the base-2 domain
+        float delta = 0.f, lse2 = INFINITY;  // invalid rows: p = exp2(-inf) = 0
+        if (q_ok) {
+            const int64_t off = (int64_t)b * p.o_bs + (int64_t)qi * p.o_rs + (int64_t)h * DH;
+            const float* o = p.o32 + off;
+            const __nv_bfloat16* g = p.do16 + off;
+#pragma unroll
+            for (int d = 0; d < DH; d += 8) {
+                const float4 o0 = *reinterpret_cast<const float4*>(o + d), o1 = *reinterpret_cast<const float4*>(o + d + 4);
+                const uint4 u = *reinterpret_cast<const uint4*>(g + d);
+                const __nv_bfloat162* gb = reinterpret_cast<const __nv_bfloat162*>(&u);
+                delta += o0.x * __low2float(gb[0]) + o0.y * __high2float(gb[0]) + o0.z * __low2float(gb[1]) + o0.w * __high2float(gb[1]) +
+                         o1.x * __low2float(gb[2]) + o1.y * __high2float(gb[2]) + o1.z * __low2float(gb[3]) + o1.w * __high2float(gb[3]);
+            }
+            const int64_t si = ((int64_t)b * p.heads + h) * p.n + qi;
+            lse2 = p.lse[si] * 1.44269504088896340736f;
+            p.delta[si] = delta;
+        }
+        for (int j = 0; j < T; ++j) {
+            const int j0 = j * BKV;
+            const bool masked = (padb != nullptr) || (j0 + BKV > p.m);
+            float* bias = sBias + (j & 1) * BKV;
+            if (masked) {
+                if (tid < BKV) {
+                    const int key = j0 + tid;
+                    bias[tid] = ((key >= p.m) || (padb != nullptr && padb[key] != 0)) ? -INFINITY : 0.f;
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            }
+            mbar_wait(sdp_full, (uint32_t)j & 1u);
+            tc_fence_after();
+            if (j > 0) mbar_wait(dq_done, (uint32_t)(j - 1) & 1u);  // previous dQ MMA has consumed the dS tile
+#pragma unroll
+            for (int c0 = 0; c0 < BKV; c0 += 32) {
+                uint32_t rs[32], rp[32];
+                tmem_ld32(tmem_s + lane_off + (uint32_t)c0, rs);
+                tmem_ld32(tmem_dp + lane_off + (uint32_t)c0, rp);
+                tmem_ld_wait();
+                float ds[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    float e = __uint_as_float(rs[i]) * p.scale_log2e - lse2;
+                    if (masked) e += bias[c0 + i];
+                    const float pv = fast_exp2(e);
+                    ds[i] = pv * (__uint_as_float(rp[i]) - delta) * p.scale;
+                }
+                store_row_half_bf16(sdS, row, c0 / 32, ds);
+            }
+            tc_fence_before();
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(ds_full);
+        }
+        mbar_wait(dq_done, (uint32_t)(T - 1) & 1u);
+        tc_fence_after();
+#pragma unroll
+        for (int c0 = 0; c0 < DH; c0 += 32) {
+            uint32_t r[32];
+            tmem_ld32(tmem_dq + lane_off + (uint32_t)c0, r);
+            tmem_ld_wait();
+            if (q_ok) {
+                float v[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+                store_row64_bf16_global(p.dq16 + (int64_t)b * p.q_bs + (int64_t)qi * p.q_rs + (int64_t)h * DH, v, c0);
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 256);
+    }
+}
+
+// dK, dV: CTA = 128 key rows of one (batch, head); streams query tiles of 64.  Works on the
+// transposed score tile S^T = K Q^T (thread = key row, column = query), so P^T and dS^T come out in
+// exactly the K-major layout the dV = P^T dO and dK = dS^T Q products read.
+__global__ void __launch_bounds__(FA_THREADS, 2)
+    attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
+                           const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const FaBwdParams p) {
+    constexpr int DH = 64, BQ2 = 64, BK2 = 128;
+    constexpr int K_BYTES = BK2 * DH * 2, Q_BYTES = BQ2 * DH * 2, P_BYTES = BK2 * BQ2 * 2;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* sK = smem;
+    uint8_t* sV = sK + K_BYTES;
+    uint8_t* sQ = sV + K_BYTES;        // [2]
+    uint8_t* sdO = sQ + 2 * Q_BYTES;   // [2]
+    uint8_t* sP = sdO + 2 * Q_BYTES;   // P^T  (128 keys x 64 queries)
+    uint8_t* sdS = sP + P_BYTES;       // dS^T
+    float* sLse = (float*)(sdS + P_BYTES);  // [2][BQ2]
+    float* sDelta = sLse + 2 * BQ2;         // [2][BQ2]
+    uint64_t* bars = (uint64_t*)(sDelta + 2 * BQ2);
+    uint64_t* kv_full = bars;
+    uint64_t* q_full = bars + 1;   // [2]
+    uint64_t* q_empty = bars + 3;  // [2]
+    uint64_t* sdp_full = bars + 5;
+    uint64_t* pds_full = bars + 6;
+    uint64_t* acc_done = bars + 7;
+    uint32_t* tmem_slot = (uint32_t*)(bars + 8);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int k0 = blockIdx.x * BK2, h = blockIdx.y, b = blockIdx.z;
+    const int T = (p.n + BQ2 - 1) / BQ2;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmQ); prefetch_tmap(&tmdO); prefetch_tmap(&tmK); prefetch_tmap(&tmV);
+        mbar_init(kv_full, 1);
+        for (int s = 0; s < 2; ++s) { mbar_init(&q_full[s], 1); mbar_init(&q_empty[s], 1); }
+        mbar_init(sdp_full, 1);
+        mbar_init(pds_full, 4);
+        mbar_init(acc_done, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_st = tmem_base, tmem_dpt = tmem_base + 64, tmem_dv = tmem_base + 128, tmem_dk = tmem_base + 192;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(kv_full, 2 * K_BYTES);
+            tma_load_3d(sK, &tmK, h * DH, k0, b, kv_full);
+            tma_load_3d(sV, &tmV, h * DH, k0, b, kv_full);
+            for (int i = 0; i < T; ++i) {
+                const int s = i & 1;
+                const uint32_t ph = (uint32_t)(i >> 1) & 1u;
+                mbar_wait(&q_empty[s], ph ^ 1u);
+                mbar_expect_tx(&q_full[s], 2 * Q_BYTES);
+                tma_load_3d(sQ + s * Q_BYTES, &tmQ, h * DH, i * BQ2, b, &q_full[s]);
+                tma_load_3d(sdO + s * Q_BYTES, &tmdO, h * DH, i * BQ2, b, &q_full[s]);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc_kk = make_idesc(BQ2, false, false);  // S^T, dP^T: K-major x K-major, N = 64 queries
+            const uint32_t idesc_acc = make_idesc(DH, false, true);   // dV, dK: P^T / dS^T K-major, dO / Q tile MN-major
+            mbar_wait(kv_full, 0);
+            const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV), p_addr = smem_u32(sP), ds_addr = smem_u32(sdS);
+            for (int i = 0; i < T; ++i) {
+                const int s = i & 1;
+                const uint32_t ph = (uint32_t)(i >> 1) & 1u;
+                mbar_wait(&q_full[s], ph);
+                tc_fence_after();
+                const uint32_t q_addr = smem_u32(sQ + s * Q_BYTES), do_addr = smem_u32(sdO + s * Q_BYTES);
+#pragma unroll
+                for (int t = 0; t < DH / 16; ++t)
+                    umma_bf16(tmem_st, make_smem_desc(k_addr + t * 32, 16, 1024), make_smem_desc(q_addr + t * 32, 16, 1024), idesc_kk,
+                              t > 0 ? 1u : 0u);
+#pragma unroll
+                for (int t = 0; t < DH / 16; ++t)
+                    umma_bf16(tmem_dpt, make_smem_desc(v_addr + t * 32, 16, 1024), make_smem_desc(do_addr + t * 32, 16, 1024), idesc_kk,
+                              t > 0 ? 1u : 0u);
+                umma_commit(sdp_full);
+                mbar_wait(pds_full, (uint32_t)i & 1u);
+                tc_fence_after();
+#pragma unroll
+                for (int t = 0; t < BQ2 / 16; ++t)
+                    umma_bf16(tmem_dv, make_smem_desc(p_addr + t * 32, 16, 1024), make_smem_desc(do_addr + t * 2048, BQ2 * 128, 1024),
+                              idesc_acc, (i > 0 || t > 0) ? 1u : 0u);
+#pragma unroll
+                for (int t = 0; t < BQ2 / 16; ++t)
+                    umma_bf16(tmem_dk, make_smem_desc(ds_addr + t * 32, 16, 1024), make_smem_desc(q_addr + t * 2048, BQ2 * 128, 1024),
+                              idesc_acc, (i > 0 || t > 0) ? 1u : 0u);
+                umma_commit(acc_done);
+                umma_commit(&q_empty[s]);
+            }
+        }
+        __syncwarp();
+    } else {
+        const int qd = warp & 3;
+        const int row = qd * 32 + lane;  // key row within the tile
+        const int tid = (warp - 2) * 32 + lane;
+        const uint32_t lane_off = (uint32_t)(qd * 32) << 16;
+        const int key = k0 + row;
+        const bool key_ok = key < p.m;
+        const bool dead_key = !key_ok || (p.pad != nullptr && p.pad[(int64_t)b * p.m + key] != 0);
+        const int64_t stat_base = ((int64_t)b * p.heads + h) * p.n;
+        for (int i = 0; i < T; ++i) {
+            float* lse_s = sLse + (i & 1) * BQ2;
+            float* del_s = sDelta + (i & 1) * BQ2;
+            if (tid < BQ2) {
+                const int qi = i * BQ2 + tid;
+                lse_s[tid] = (qi < p.n) ? p.lse[stat_base + qi] * 1.44269504088896340736f : INFINITY;  // invalid query: p = 0
+                del_s[tid] = (qi < p.n) ? p.delta[stat_base + qi] : 0.f;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            mbar_wait(sdp_full, (uint32_t)i & 1u);
+            tc_fence_after();
+            if (i > 0) mbar_wait(acc_done, (uint32_t)(i - 1) & 1u);  // previous dV / dK MMAs have consumed P^T, dS^T
+#pragma unroll
+            for (int c0 = 0; c0 < BQ2; c0 += 32) {
+                uint32_t rs[32], rp[32];
+                tmem_ld32(tmem_st + lane_off + (uint32_t)c0, rs);
+                tmem_ld32(tmem_dpt + lane_off + (uint32_t)c0, rp);
+                tmem_ld_wait();
+                float pv[32], ds[32];
+#pragma unroll
+                for (int q = 0; q < 32; ++q) {
+                    const float pr = dead_key ? 0.f : fast_exp2(__uint_as_float(rs[q]) * p.scale_log2e - lse_s[c0 + q]);
+                    pv[q] = pr;
+                    ds[q] = pr * (__uint_as_float(rp[q]) - del_s[c0 + q]) * p.scale;
+                }
+                store_row_half_bf16(sP, row, c0 / 32, pv);
+                store_row_half_bf16(sdS, row, c0 / 32, ds);
+            }
+            tc_fence_before();
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(pds_full);
+        }
+        mbar_wait(acc_done, (uint32_t)(T - 1) & 1u);
+        tc_fence_after();
+#pragma unroll
+        for (int c0 = 0; c0 < DH; c0 += 32) {
+            uint32_t rv[32], rk[32];
+            tmem_ld32(tmem_dv + lane_off + (uint32_t)c0, rv);
+            tmem_ld32(tmem_dk + lane_off + (uint32_t)c0, rk);
+            tmem_ld_wait();
+            if (key_ok) {
+                float v[32];
+#pragma unroll
+                for (int q = 0; q < 32; ++q) v[q] = __uint_as_float(rv[q]);
+                store_row64_bf16_global(p.dv16 + (int64_t)b * p.v_bs + (int64_t)key * p.v_rs + (int64_t)h * DH, v, c0);
+#pragma unroll
+                for (int q = 0; q < 32; ++q) v[q] = __uint_as_float(rk[q]);
+                store_row64_bf16_global(p.dk16 + (int64_t)b * p.k_bs + (int64_t)key * p.k_rs + (int64_t)h * DH, v, c0);
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 256);
+    }
+}
+
 // 3-D bf16 tensor map over (batch, rows, cols) with element strides (bs, rs, 1); box = 64 cols x box_rows x 1
 static int make_tmap3(CUtensorMap* map, const void* base, int64_t cols, int64_t rows, int64_t batch, int64_t rs, int64_t bs,
                       int box_rows) {
@@ -331,4 +723,61 @@ int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st) {
     return PIO_OK;
 }
 
+// q, k, v, dO bf16; o fp32; lse fp32 -> dq16, dk16, dv16 (bf16, strides of q / k / v); delta scratch (batch, heads, n)
+int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta, __nv_bfloat16* dq16, __nv_bfloat16* dk16,
+                __nv_bfloat16* dv16, cudaStream_t st) {
+    PIO_CHECK_ARG(d && d->q && d->k && d->v && d->o && d->lse && do16 && delta && dq16 && dk16 && dv16, "attn_bwd_tc: null pointer");
+    PIO_CHECK_ARG(attn_fwd_tc_supported(d), "attn_bwd_tc: unsupported shape (head dim %d)", d->dh);
+    PIO_CHECK_ARG(d->heads <= 65535 && d->batch <= 65535, "attn_bwd_tc: batch/heads exceed grid limits");
+    const int64_t cols = (int64_t)d->heads * d->dh;
+    FaBwdParams p{};
+    p.pad = d->pad; p.o32 = d->o; p.do16 = do16; p.lse = d->lse; p.delta = delta;
+    p.dq16 = dq16; p.dk16 = dk16; p.dv16 = dv16;
+    p.o_bs = d->o_bs; p.o_rs = d->o_rs; p.q_bs = d->q_bs; p.q_rs = d->q_rs;
+    p.k_bs = d->k_bs; p.k_rs = d->k_rs; p.v_bs = d->v_bs; p.v_rs = d->v_rs;
+    p.batch = d->batch; p.heads = d->heads; p.n = d->n; p.m = d->m;
+    p.scale = d->scale;
+    p.scale_log2e = d->scale * 1.44269504088896340736f;
+    static bool configured = false;
+    const size_t smem_dq = 2 * 16384 + 4 * 8192 + 16384 + 2 * 64 * 4 + 128 + 1024;
+    const size_t smem_dkv = 2 * 16384 + 4 * 8192 + 2 * 16384 + 4 * 64 * 4 + 128 + 1024;
+    if (!configured) {
+        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dq));
+        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dkv));
+        configured = true;
+    }
+    {   // dQ + delta: 128-row query tiles, 64-row key tiles
+        CUtensorMap tq, tdo, tk, tv;
+        PIO_TRY(make_tmap3(&tq, d->q, cols, d->n, d->batch, d->q_rs, d->q_bs, FA_BQ));
+        PIO_TRY(make_tmap3(&tdo, do16, cols, d->n, d->batch, d->o_rs, d->o_bs, FA_BQ));
+        PIO_TRY(make_tmap3(&tk, d->k, cols, d->m, d->batch, d->k_rs, d->k_bs, 64));
+        PIO_TRY(make_tmap3(&tv, d->v, cols, d->m, d->batch, d->v_rs, d->v_bs, 64));
+        dim3 grid((unsigned)cdiv(d->n, FA_BQ), (unsigned)d->heads, (unsigned)d->batch);
+        attn_bwd_dq_tc_kernel<<<grid, FA_THREADS, smem_dq, st>>>(tq, tdo, tk, tv, p);
+        PIO_LAUNCH_CHECK();
+    }
+    {   // dK, dV: 128-row key tiles, 64-row query tiles
+        CUtensorMap tq, tdo, tk, tv;
+        PIO_TRY(make_tmap3(&tq, d->q, cols, d->n, d->batch, d->q_rs, d->q_bs, 64));
+        PIO_TRY(make_tmap3(&tdo, do16, cols, d->n, d->batch, d->o_rs, d->o_bs, 64));
+        PIO_TRY(make_tmap3(&tk, d->k, cols, d->m, d->batch, d->k_rs, d->k_bs, 128));
+        PIO_TRY(make_tmap3(&tv, d->v, cols, d->m, d->batch, d->v_rs, d->v_bs, 128));
+        dim3 grid((unsigned)cdiv(d->m, 128), (unsigned)d->heads, (unsigned)d->batch);
+        attn_bwd_dkv_tc_kernel<<<grid, FA_THREADS, smem_dkv, st>>>(tq, tdo, tk, tv, p);
+        PIO_LAUNCH_CHECK();
+    }
+    return PIO_OK;
+}
+
 }  // namespace pio
+
+extern "C" int pio_attn_bwd_bf16(const pio_attn_desc* fwd, const void* d_o16, void* dq16, void* dk16, void* dv16, float* delta,
+                                 pio_stream_t stream) {
+    PIO_CHECK_ARG(fwd != nullptr, "pio_attn_bwd_bf16: null descriptor");
+    if (!pio::attn_fwd_tc_supported(fwd)) {
+        pio::set_error("pio_attn_bwd_bf16: head dim %d has no tensor-core backward (use pio_attn_bwd)", fwd->dh);
+        return PIO_ERR_UNSUPPORTED;
+    }
+    return pio::attn_bwd_tc(fwd, (const __nv_bfloat16*)d_o16, delta, (__nv_bfloat16*)dq16, (__nv_bfloat16*)dk16,
+                            (__nv_bfloat16*)dv16, (cudaStream_t)stream);
+}

@@ -265,17 +265,23 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
     PIO_TAKE_BYTES(float, dhq, c, (size_t)rows * e * 4, "pio_cross_attend_bwd");
     PIO_TAKE_BYTES(float, delta, c, (size_t)batch * heads * n * 4, "pio_cross_attend_bwd");
     PIO_TRY(cast_colsum_f32(dy, e, dy16, e, g->bo, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
-    PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)w->wo, e, rows, e, e, d_o, e, nullptr, 0, 0, nullptr, 0, 0));
     PIO_TRY(tc_dW(c, dy16, e, s.o16, e, g->wo, rows, e, e, acc));
     const bf16* kv16 = reinterpret_cast<const bf16*>(kv);
     bf16* dkv16 = reinterpret_cast<bf16*>(dkv);
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.q, e, kv16, kv16 + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
-    b.d_o = d_o; b.delta = delta;
-    AttnBf16Out ex;
-    ex.in16 = 1;
-    ex.dq16 = dq16; ex.dk16 = dkv16; ex.dv16 = dkv16 + e;
-    PIO_TRY(attn_bwd_simt(&b, c.st, &ex));
+    if (attn_fwd_tc_supported(&b.fwd)) {
+        bf16* d_o16 = reinterpret_cast<bf16*>(d_o);  // the fp32 scratch is large enough for the bf16 tile
+        PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)w->wo, e, rows, e, e, nullptr, 0, d_o16, e, 0, nullptr, 0, 0));
+        PIO_TRY(attn_bwd_tc(&b.fwd, d_o16, delta, dq16, dkv16, dkv16 + e, c.st));
+    } else {
+        PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)w->wo, e, rows, e, e, d_o, e, nullptr, 0, 0, nullptr, 0, 0));
+        b.d_o = d_o; b.delta = delta;
+        AttnBf16Out ex;
+        ex.in16 = 1;
+        ex.dq16 = dq16; ex.dk16 = dkv16; ex.dv16 = dkv16 + e;
+        PIO_TRY(attn_bwd_simt(&b, c.st, &ex));
+    }
     PIO_TRY(colsum_bf16(dq16, e, g->bq, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
     PIO_TRY(tc_dyW(c, dq16, e, (const bf16*)w->wq, e, rows, e, e, dhq, e, nullptr, 0, 0, nullptr, 0, 0));
     PIO_TRY(tc_dW(c, dq16, e, s.hq, e, g->wq, rows, e, e, acc));
@@ -350,15 +356,21 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
     PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ch * 4, "pio_self_attn_bwd");
     PIO_TAKE_BYTES(float, delta, c, (size_t)batch * heads * n * 4, "pio_self_attn_bwd");
     PIO_TRY(cast_colsum_f32(dy, ch, dy16, ch, g->bo, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
-    PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->wo, ch, rows, ch, ch, d_o, ch, nullptr, 0, 0, nullptr, 0, 0));
     PIO_TRY(tc_dW(c, dy16, ch, s.o16, ch, g->wo, rows, ch, ch, acc));
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
-    b.d_o = d_o; b.delta = delta;
-    AttnBf16Out ex;
-    ex.in16 = 1;
-    ex.dq16 = dqkv16; ex.dk16 = dqkv16 + ch; ex.dv16 = dqkv16 + 2 * ch;
-    PIO_TRY(attn_bwd_simt(&b, c.st, &ex));
+    if (attn_fwd_tc_supported(&b.fwd)) {
+        bf16* d_o16 = reinterpret_cast<bf16*>(d_o);
+        PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->wo, ch, rows, ch, ch, nullptr, 0, d_o16, ch, 0, nullptr, 0, 0));
+        PIO_TRY(attn_bwd_tc(&b.fwd, d_o16, delta, dqkv16, dqkv16 + ch, dqkv16 + 2 * ch, c.st));
+    } else {
+        PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->wo, ch, rows, ch, ch, d_o, ch, nullptr, 0, 0, nullptr, 0, 0));
+        b.d_o = d_o; b.delta = delta;
+        AttnBf16Out ex;
+        ex.in16 = 1;
+        ex.dq16 = dqkv16; ex.dk16 = dqkv16 + ch; ex.dv16 = dqkv16 + 2 * ch;
+        PIO_TRY(attn_bwd_simt(&b, c.st, &ex));
+    }
     PIO_TRY(colsum_bf16(dqkv16, 3 * ch, g->bq, acc, rows, 3 * ch, c.rest(), c.rest_bytes(), c.st));
     PIO_TRY(tc_dyW(c, dqkv16, 3 * ch, (const bf16*)w->wq, ch, rows, 3 * ch, ch, dh0, ch, nullptr, 0, 0, nullptr, 0, 0));
     PIO_TRY(tc_dW(c, dqkv16, 3 * ch, s.h0, ch, g->wq, rows, 3 * ch, ch, acc));

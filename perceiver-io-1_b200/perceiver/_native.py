@@ -86,6 +86,7 @@ _SIGNATURES = {
     "pio_cast_bf16": (c_int, [P, P, c_int64, c_int, c_int64, c_int64, P]),
     "pio_attn_fwd": (c_int, [POINTER(AttnDesc), c_int, P]),
     "pio_attn_bwd": (c_int, [POINTER(AttnBwdDesc), c_int, P]),
+    "pio_attn_bwd_bf16": (c_int, [POINTER(AttnDesc), P, P, P, P, P, P]),
     "pio_cross_entropy_fwd": (c_int, [P, P, P, P, c_int64, c_int64, c_int64, c_int64, P]),
     "pio_cross_entropy_bwd": (c_int, [P, P, P, P, P, P, c_int64, c_int64, c_int64, c_int64, P]),
     "pio_mlp_saved_bytes": (c_size_t, [c_int64, c_int, c_int]),

@@ -102,3 +102,76 @@ def test_bf16_inputs_other_head_sizes_use_the_fp32_arithmetic_kernel(N):
     o, lse = _run(N, q16, kv16, kv16[..., e:], e, 2 * e, None, b, heads, n, m, dh)
     assert_rel(o, o_ref, 1e-5, "o")
     assert_rel(lse, lse_ref, 1e-5, "lse")
+
+
+def _ref_grads(q, k, v, do, pad, heads):
+    q, k, v = (t.clone().requires_grad_(True) for t in (q, k, v))
+    o, lse = _ref(q, k, v, pad, heads)
+    (o * do).sum().backward()
+    return o.detach(), lse.detach(), q.grad, k.grad, v.grad
+
+
+@pytest.mark.parametrize("b,n,m,heads,padded", [
+    (2, 128, 64, 1, False), (2, 64, 512, 4, True), (2, 256, 1024, 2, False), (2, 70, 200, 2, True), (1, 1, 64, 1, False),
+    (2, 512, 64, 4, False), (1, 300, 1100, 2, True), (3, 64, 64, 4, False)])
+def test_flash_tc_backward(N, b, n, m, heads, padded):
+    """dq, dk, dv of the tcgen05 backward against fp64 autograd over the same bf16-rounded q, k, v, dO.
+    The kernels round P, dS and the outputs to bf16, hence the bf16 tolerance."""
+    torch.manual_seed(3)
+    dh = 64
+    e = heads * dh
+    q, kv, do = torch.randn(b, n, e), torch.randn(b, m, 2 * e), torch.randn(b, n, e)
+    pad = None
+    if padded:
+        lens = torch.randint(1, m + 1, (b,))
+        lens[0] = m
+        pad = torch.arange(m)[None, :] >= lens[:, None]
+    q16, kv16, do16 = (t.to(DEV).to(torch.bfloat16) for t in (q, kv, do))
+    o_ref, lse_ref, dq_ref, dk_ref, dv_ref = _ref_grads(q16.double().cpu(), kv16[..., :e].double().cpu(),
+                                                        kv16[..., e:].double().cpu(), do16.double().cpu(), pad, heads)
+    padd = pad.to(DEV) if pad is not None else None
+    # forward through the tensor-core kernel (its fp32 o and lse are what the backward consumes)
+    L = N.lib()
+    o = torch.empty(b, n, e, device=DEV)
+    lse = torch.empty(b, heads, n, device=DEV)
+    d = N.AttnDesc()
+    d.q, d.k, d.v, d.pad, d.o, d.lse = q16.data_ptr(), kv16.data_ptr(), kv16.data_ptr() + 2 * e, N.ptr(padd), o.data_ptr(), lse.data_ptr()
+    d.q_bs, d.q_rs, d.k_bs, d.k_rs, d.v_bs, d.v_rs, d.o_bs, d.o_rs = n * e, e, m * 2 * e, 2 * e, m * 2 * e, 2 * e, n * e, e
+    d.batch, d.heads, d.n, d.m, d.dh, d.scale = b, heads, n, m, dh, dh ** -0.5
+    N.check(L.pio_attn_fwd(ctypes.byref(d), 1, N.stream_ptr()), "pio_attn_fwd")
+    dq16 = torch.full((b, n, e), float("nan"), device=DEV, dtype=torch.bfloat16)
+    dkv16 = torch.full((b, m, 2 * e), float("nan"), device=DEV, dtype=torch.bfloat16)
+    delta = torch.empty(b, heads, n, device=DEV)
+    N.check(L.pio_attn_bwd_bf16(ctypes.byref(d), do16.data_ptr(), dq16.data_ptr(), dkv16.data_ptr(), dkv16.data_ptr() + 2 * e,
+                                delta.data_ptr(), N.stream_ptr()), "pio_attn_bwd_bf16")
+    torch.cuda.synchronize()
+    assert_rel(delta, (o_ref * do16.double().cpu()).view(b, n, heads, dh).sum(-1).transpose(1, 2), 2e-2, "delta")
+    assert_rel(dq16.float(), dq_ref, 2e-2, "dq")
+    assert_rel(dkv16[..., :e].float(), dk_ref, 2e-2, "dk")
+    assert_rel(dkv16[..., e:].float(), dv_ref, 2e-2, "dv")
+
+
+def test_flash_tc_backward_packed_qkv(N):
+    torch.manual_seed(4)
+    b, n, heads, dh = 3, 100, 2, 64
+    c = heads * dh
+    x16 = torch.randn(b, n, 3 * c, device=DEV).to(torch.bfloat16)
+    do16 = torch.randn(b, n, c, device=DEV).to(torch.bfloat16)
+    xr = x16.double().cpu()
+    _, _, dq_ref, dk_ref, dv_ref = _ref_grads(xr[..., :c], xr[..., c:2 * c], xr[..., 2 * c:], do16.double().cpu(), None, heads)
+    L = N.lib()
+    o = torch.empty(b, n, c, device=DEV)
+    lse = torch.empty(b, heads, n, device=DEV)
+    d = N.AttnDesc()
+    d.q, d.k, d.v, d.pad, d.o, d.lse = x16.data_ptr(), x16.data_ptr() + 2 * c, x16.data_ptr() + 4 * c, None, o.data_ptr(), lse.data_ptr()
+    d.q_bs, d.q_rs, d.k_bs, d.k_rs, d.v_bs, d.v_rs, d.o_bs, d.o_rs = n * 3 * c, 3 * c, n * 3 * c, 3 * c, n * 3 * c, 3 * c, n * c, c
+    d.batch, d.heads, d.n, d.m, d.dh, d.scale = b, heads, n, n, dh, dh ** -0.5
+    N.check(L.pio_attn_fwd(ctypes.byref(d), 1, N.stream_ptr()))
+    dx16 = torch.full((b, n, 3 * c), float("nan"), device=DEV, dtype=torch.bfloat16)
+    delta = torch.empty(b, heads, n, device=DEV)
+    N.check(L.pio_attn_bwd_bf16(ctypes.byref(d), do16.data_ptr(), dx16.data_ptr(), dx16.data_ptr() + 2 * c, dx16.data_ptr() + 4 * c,
+                                delta.data_ptr(), N.stream_ptr()))
+    torch.cuda.synchronize()
+    assert_rel(dx16[..., :c].float(), dq_ref, 2e-2, "dq")
+    assert_rel(dx16[..., c:2 * c].float(), dk_ref, 2e-2, "dk")
+    assert_rel(dx16[..., 2 * c:].float(), dv_ref, 2e-2, "dv")
