@@ -267,9 +267,14 @@ def gpu_arm(args):
     ids_h, pad_h = ids_h.pin_memory(), pad_h.pin_memory()
     ids_d, pad_d = ids_h.to(dev), pad_h.to(dev)
 
+    fused_loss = (mode == 1)  # bf16 mode: vocabulary projection + CE as one chunked operator (logits never stored)
+
     def step(ids, pad):
-        logits, labels = net(ids.clone(), pad)  # masking is in place: keep the resident batch intact
-        loss = perceiver.cross_entropy(logits, labels)
+        if fused_loss:
+            loss, _ = net(ids.clone(), pad, return_loss=True)  # masking is in place: keep the resident batch intact
+        else:
+            logits, labels = net(ids.clone(), pad)
+            loss = perceiver.cross_entropy(logits, labels)
         opt.zero_grad(set_to_none=True)
         loss.backward()
         opt.step()

@@ -307,6 +307,17 @@ int pio_linear_bwd(const float* dy, const float* x, const float* w, float* dx, f
                    int accumulate, int64_t rows, int c_in, int64_t c_out, int mode, void* ws,
                    size_t ws_bytes, pio_stream_t stream);
 
+/* Output-adapter Linear fused with the cross-entropy loss for training (TextOutputAdapter.linear,
+ * adapter.py:146-149,166-173 + nn.CrossEntropyLoss, lightning.py:184,225-226).
+ * PIO_MODE_BF16 only (`w` = bf16 shadow).  Rows are processed in L2-sized chunks: logits GEMM, one
+ * kernel producing per-row losses and bf16 dlogits, and the two gradient GEMMs — every logit is
+ * computed, none is stored in HBM.  out3 = {loss, n_valid, loss_sum}; dx (rows,c_in), dw (classes,c_in),
+ * db (classes) are the gradients for d(loss) = 1 (scale them by the incoming gradient). */
+size_t pio_linear_ce_ws_bytes(int64_t rows, int c_in, int64_t classes, int mode);
+int pio_linear_ce_fwd_bwd(const float* x, const float* w, const float* b, const int64_t* labels, float* out3,
+                          float* dx, float* dw, float* db, int64_t rows, int c_in, int64_t classes,
+                          int64_t ignore_index, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -547,4 +547,23 @@ int pio_linear_bwd(const float* dy, const float* x, const float* w, float* dx, f
     return gemm_dW(ctx, dy, c_out, x, c_in, dw, db, rows, c_out, c_in, accumulate);
 }
 
+// ---- output linear fused with cross-entropy (training)
+size_t pio_linear_ce_ws_bytes(int64_t rows, int c_in, int64_t classes, int mode) {
+    (void)mode;
+    return bf::linear_ce_ws_bytes(rows, c_in, classes);
+}
+
+int pio_linear_ce_fwd_bwd(const float* x, const float* w, const float* b, const int64_t* labels, float* out3, float* dx, float* dw,
+                          float* db, int64_t rows, int c_in, int64_t classes, int64_t ignore_index, int mode, void* ws,
+                          size_t ws_bytes, pio_stream_t stream) {
+    if (mode != PIO_MODE_BF16) {
+        set_error("pio_linear_ce_fwd_bwd: only PIO_MODE_BF16 has the fused path (compose pio_linear_* and pio_cross_entropy_* in fp32)");
+        return PIO_ERR_UNSUPPORTED;
+    }
+    PIO_CHECK_ARG(x && w && b && labels && out3 && dx && dw && db && rows > 0 && c_in > 0 && classes > 0,
+                  "pio_linear_ce_fwd_bwd: bad arguments");
+    Ctx ctx(ws, ws_bytes, stream);
+    return bf::linear_ce_fwd_bwd(ctx, x, w, b, labels, out3, dx, dw, db, rows, c_in, classes, ignore_index);
+}
+
 }  // extern "C"

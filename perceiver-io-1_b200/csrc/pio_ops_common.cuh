@@ -105,6 +105,9 @@ size_t linear_ws_bytes(int64_t rows, int c_in, int64_t c_out);
 int linear_fwd(Ctx& c, const float* x, const float* w16, const float* b, float* y, int64_t rows, int c_in, int64_t c_out);
 int linear_bwd(Ctx& c, const float* dy, const float* x, const float* w16, float* dx, float* dw, float* db, int acc, int64_t rows,
                int c_in, int64_t c_out);
+size_t linear_ce_ws_bytes(int64_t rows, int c_in, int64_t classes);
+int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, const int64_t* labels, float* out3, float* dx,
+                      float* dw, float* db, int64_t rows, int c_in, int64_t classes, int64_t ignore);
 }  // namespace bf
 
 }  // namespace pio

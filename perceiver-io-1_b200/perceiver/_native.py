@@ -118,6 +118,8 @@ _SIGNATURES = {
                                      POINTER(MlpWeights), c_int, c_int, c_int, c_int, c_int, c_int, c_int, P, c_size_t, P]),
     "pio_linear_ws_bytes": (c_size_t, [c_int64, c_int, c_int64, c_int]),
     "pio_linear_fwd": (c_int, [P, P, P, P, c_int64, c_int, c_int64, c_int, P, c_size_t, P]),
+    "pio_linear_ce_ws_bytes": (c_size_t, [c_int64, c_int, c_int64, c_int]),
+    "pio_linear_ce_fwd_bwd": (c_int, [P, P, P, P, P, P, P, P, c_int64, c_int, c_int64, c_int64, c_int, P, c_size_t, P]),
     "pio_linear_bwd": (c_int, [P, P, P, P, P, P, c_int, c_int64, c_int, c_int64, c_int, P, c_size_t, P]),
 }
 

@@ -535,5 +535,46 @@ class CrossEntropyFn(torch.autograd.Function):
         return dlogits, None, None
 
 
+class LinearCrossEntropyFn(torch.autograd.Function):
+    """Output-adapter linear + cross-entropy in one call (bf16 mode): the logits are produced and
+    consumed chunk by chunk inside L2, and the gradients of x, W and b are formed in the same pass
+    (for d(loss) = 1; backward only scales them).  SURVEY.md section 8f row 1."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, labels, ignore_index):
+        x, w, b = _c(x), _c(w), _c(b)
+        labels = _c(labels, torch.int64)
+        classes, c_in = w.shape
+        rows = x.numel() // c_in
+        if labels.numel() != rows:
+            raise ValueError(f"labels shape {tuple(labels.shape)} does not match inputs {tuple(x.shape)}")
+        mode = get_compute_mode()
+        L = N.lib()
+        dev = x.device
+        out3 = torch.empty(3, dtype=torch.float32, device=dev)
+        dx, dw, db = torch.empty_like(x), torch.empty_like(w), torch.empty_like(b)
+        ws = N.workspace(L.pio_linear_ce_ws_bytes(rows, c_in, classes, mode), dev)
+        wm = _mat(w, mode)
+        N.check(L.pio_linear_ce_fwd_bwd(x.data_ptr(), wm.data_ptr(), b.data_ptr(), labels.data_ptr(), out3.data_ptr(),
+                                        dx.data_ptr(), dw.data_ptr(), db.data_ptr(), rows, c_in, classes, int(ignore_index), mode,
+                                        ws.data_ptr(), ws.numel(), N.stream_ptr(dev)), "pio_linear_ce_fwd_bwd")
+        ctx.save_for_backward(dx, dw, db)
+        return out3[0].clone()
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dloss):
+        dx, dw, db = ctx.saved_tensors
+        return dx * dloss, dw * dloss, db * dloss, None, None
+
+
+def linear_cross_entropy(x, weight, bias, labels, ignore_index=-100):
+    """loss = CE(x @ weight.T + bias, labels), mean over labels != ignore_index.  Fused in bf16 mode;
+    composed from the linear and cross-entropy operators in fp32 mode."""
+    if get_compute_mode() == N.MODE_BF16 and torch.is_grad_enabled():
+        return LinearCrossEntropyFn.apply(x, weight, bias, labels, ignore_index)
+    return CrossEntropyFn.apply(LinearFn.apply(x, weight, bias), labels, ignore_index)
+
+
 def cross_entropy(logits, labels, ignore_index=-100):
     return CrossEntropyFn.apply(logits, labels, ignore_index)

@@ -215,14 +215,17 @@ class PerceiverDecoder(nn.Module):
         with torch.no_grad():
             self.output.normal_(0.0, 0.02).clamp_(-2.0, 2.0)
 
-    def forward(self, x, pad_mask=None, num_queries: Optional[int] = None):
+    def decode(self, x, num_queries: Optional[int] = None):
+        """(B, K, C_out) decoder output before the output adapter."""
         b, *d = x.shape
         if tuple(d) != tuple(self.latent_shape):
             raise ValueError(f'Latent shape {tuple(d)} different from required shape {self.latent_shape}')
         q = self.output if num_queries is None else self.output[:num_queries]
         q = q.unsqueeze(0).expand(b, -1, -1).contiguous()
-        out = self.cross_attention(q, x)  # pad_mask is accepted and unused, as in the reference
-        return self.output_adapter(out)
+        return self.cross_attention(q, x)  # no mask on the latents, as in the reference
+
+    def forward(self, x, pad_mask=None, num_queries: Optional[int] = None):
+        return self.output_adapter(self.decode(x, num_queries))  # pad_mask is accepted and unused, as in the reference
 
 
 class TextMasking(nn.Module):
@@ -256,13 +259,23 @@ class PerceiverMLM(nn.Module):
         self.decoder = decoder
         self.masking = masking
 
-    def forward(self, x_input, pad_mask=None, masking=True):
+    def forward(self, x_input, pad_mask=None, masking=True, return_loss=False):
+        """-> (logits[:, :l], labels) like the reference.  ``return_loss=True`` (training) returns
+        (loss, labels) instead: the vocabulary projection and the cross-entropy of
+        LitMaskedLanguageModel.step (reference lightning.py:223-226) run as one fused operator and the
+        (B, l, vocab) logits are never stored."""
         _, l = x_input.shape
         if masking:
             x_masked, x_labels = self.masking(x_input, pad_mask)
         else:
             x_masked, x_labels = x_input, None
         x_latent, _ = self.encoder(x_masked, pad_mask)
+        if return_loss:
+            if x_labels is None:
+                raise ValueError('return_loss=True needs masking=True (labels come from the masking step)')
+            lin = self.decoder.output_adapter.linear
+            hidden = self.decoder.decode(x_latent, num_queries=l)
+            return F.linear_cross_entropy(hidden, lin.weight, lin.bias, x_labels), x_labels
         x_logits = self.decoder(x_latent, pad_mask, num_queries=l)
         return x_logits, x_labels
 

@@ -141,3 +141,53 @@ def test_weight_shadow_follows_parameter_updates():
     assert rel_err(y1, y0) > 1e-2
     sd = {"module." + k: v.cpu() for k, v in ff.state_dict().items()}
     assert_rel(y1, O.mlp_residual(sd, "", x.cpu()) - x.cpu(), BF16_TOL, "after update")
+
+
+@pytest.mark.parametrize("rows,c,classes", [(300, 64, 517), (4096, 256, 10003)])
+def test_fused_linear_cross_entropy_matches_oracle(rows, c, classes):
+    """pio_linear_ce_fwd_bwd (chunked, logits never stored) against the fp64 oracle of linear + CE."""
+    import perceiver
+    torch.manual_seed(7)
+    x = torch.randn(rows, c)
+    w = torch.randn(classes, c) * 0.1
+    b = torch.randn(classes) * 0.1
+    y = torch.randint(0, classes, (rows,))
+    y[torch.rand(rows) < 0.8] = -100
+    y[0] = 3
+    xr, wr, br = (t.double().requires_grad_(True) for t in (x, w, b))
+    ref = O.cross_entropy(O.linear(xr, wr, br), y)
+    (ref * 1.5).backward()
+    xd, wd, bd = (t.to(DEV).requires_grad_(True) for t in (x, w, b))
+    loss = perceiver.linear_cross_entropy(xd, wd, bd, y.to(DEV))
+    (loss * 1.5).backward()
+    assert_rel(loss, ref, BF16_TOL, "loss")
+    assert_rel(xd.grad, xr.grad, 2e-2, "dx")
+    assert_rel(wd.grad, wr.grad, 2e-2, "dw")
+    assert_rel(bd.grad, br.grad, 2e-2, "db")
+
+
+def test_mlm_return_loss_equals_logits_then_cross_entropy():
+    """PerceiverMLM(..., return_loss=True) == cross_entropy(PerceiverMLM(...)[0], labels), values and grads."""
+    import perceiver
+    from perceiver import PerceiverDecoder, PerceiverEncoder, PerceiverMLM, TextInputAdapter, TextMasking, TextOutputAdapter
+    torch.manual_seed(8)
+    enc = PerceiverEncoder(TextInputAdapter(1003, 128, 64), (32, 64), 2, 1, 1, 2)
+    dec = PerceiverDecoder(TextOutputAdapter(1003, 128, 64), (32, 64), 1)
+    model = PerceiverMLM(enc, dec, TextMasking(1003, 1, 2, 3)).to(DEV)
+    ids = torch.randint(3, 1003, (6, 100), device=DEV)
+    pad = torch.arange(100, device=DEV)[None, :] >= torch.tensor([100, 90, 80, 70, 60, 50], device=DEV)[:, None]
+    g1 = torch.Generator(device=DEV).manual_seed(1)
+    torch.manual_seed(5)
+    logits, labels = model(ids.clone(), pad)
+    loss_a = perceiver.cross_entropy(logits, labels)
+    loss_a.backward()
+    ga = {k: p.grad.clone() for k, p in model.named_parameters()}
+    model.zero_grad(set_to_none=True)
+    torch.manual_seed(5)
+    loss_b, labels_b = model(ids.clone(), pad, return_loss=True)
+    loss_b.backward()
+    assert torch.equal(labels, labels_b)
+    assert_rel(loss_b, loss_a, 2e-3, "loss")
+    num = sum(((p.grad - ga[k]).double().norm() ** 2).item() for k, p in model.named_parameters())
+    den = sum((ga[k].double().norm() ** 2).item() for k in ga)
+    assert (num / den) ** 0.5 < 1e-2
