@@ -16,6 +16,10 @@
  *     asynchronous, re-entrant, and may come from any host thread (autograd's worker thread);
  *   - return value: PIO_OK or a PIO_ERR_* code; pio_last_error() gives the text (thread-local).
  *     No C++ exception crosses this boundary.  There is no CPU fallback anywhere.
+ *   - `accumulate` (backward entry points): 0 = gradients are overwritten, 1 = added to (deterministic
+ *     partial sums + reduction pass), 2 = added to with fp32 atomics straight from the producing kernels
+ *     (destinations must hold zeros or a running sum; no reduction passes; summation order, hence the last
+ *     bits, vary run to run).  2 is honoured by the PIO_MODE_BF16 pipelines and treated as 1 elsewhere.
  *   - `mode`: PIO_MODE_FP32 = fp32 FFMA arithmetic end to end (parity mode, rel 1e-4);
  *             PIO_MODE_BF16 = bf16 tcgen05 tensor-core contractions, fp32 accumulate/residual
  *             stream (performance mode, rel 1e-2).

@@ -48,7 +48,7 @@ template <typename TIn>
 __global__ void __launch_bounds__(256) colsum_partial_kernel(const TIn* __restrict__ src, int64_t ld_src,
                                                              __nv_bfloat16* __restrict__ dst16, int64_t ld_dst,
                                                              float* __restrict__ partial, int64_t rows, int c,
-                                                             int64_t rows_per_chunk, int pad_cols) {
+                                                             int64_t rows_per_chunk, int pad_cols, float* __restrict__ atomic_out) {
     __shared__ float s_part[256];
     const int col = blockIdx.x * 128 + (threadIdx.x & 127);
     const int sub = threadIdx.x >> 7;
@@ -68,7 +68,11 @@ __global__ void __launch_bounds__(256) colsum_partial_kernel(const TIn* __restri
     }
     s_part[threadIdx.x] = acc;
     __syncthreads();
-    if (partial && sub == 0 && col < c) partial[(int64_t)blockIdx.y * c + col] = acc + s_part[threadIdx.x + 128];
+    if (sub == 0 && col < c) {
+        const float total = acc + s_part[threadIdx.x + 128];
+        if (atomic_out) atomicAdd(atomic_out + col, total);
+        else if (partial) partial[(int64_t)blockIdx.y * c + col] = total;
+    }
 }
 
 static int colsum_chunks(int64_t rows, int c) {
@@ -86,7 +90,8 @@ static int colsum_impl(const TIn* src, int64_t ld_src, __nv_bfloat16* dst16, int
     if (rows == 0) return PIO_OK;
     const int chunks = colsum_chunks(rows, c);
     float* partial = nullptr;
-    if (colsum) {
+    const bool atomic = (accumulate == 2);  // add straight into the (pre-zeroed / running) destination
+    if (colsum && !atomic) {
         Workspace W(ws, ws_bytes);
         partial = W.takef((size_t)chunks * c);
         if (!partial) {
@@ -96,9 +101,10 @@ static int colsum_impl(const TIn* src, int64_t ld_src, __nv_bfloat16* dst16, int
     }
     const int pad_cols = dst16 ? (int)ld_dst : c;
     dim3 grid((unsigned)cdiv(std::max(pad_cols, c), 128), (unsigned)chunks);
-    colsum_partial_kernel<TIn><<<grid, 256, 0, st>>>(src, ld_src, dst16, ld_dst, partial, rows, c, cdiv(rows, chunks), pad_cols);
+    colsum_partial_kernel<TIn><<<grid, 256, 0, st>>>(src, ld_src, dst16, ld_dst, partial, rows, c, cdiv(rows, chunks), pad_cols,
+                                                     (colsum && atomic) ? colsum : nullptr);
     PIO_LAUNCH_CHECK();
-    if (colsum) PIO_TRY(reduce_partials(partial, chunks, c, colsum, c, nullptr, 0, accumulate, st));
+    if (colsum && !atomic) PIO_TRY(reduce_partials(partial, chunks, c, colsum, c, nullptr, 0, accumulate, st));
     return PIO_OK;
 }
 

@@ -276,7 +276,8 @@ template <int NCH>
 __global__ void __launch_bounds__(256) layernorm_bwd_kernel(
     const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ stats,
     const float* __restrict__ w, const float* __restrict__ dres, float* __restrict__ dx,
-    float* __restrict__ partial, int64_t rows, int c) {
+    float* __restrict__ partial, int64_t rows, int c, float* __restrict__ atomic_dw = nullptr,
+    float* __restrict__ atomic_db = nullptr) {
     extern __shared__ float s_acc[];  // [warps][2][c]
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
     float gw[NCH], gb[NCH], wv[NCH];
@@ -334,7 +335,8 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(
     for (int j = threadIdx.x; j < 2 * c; j += blockDim.x) {
         float acc = 0.f;
         for (int w2 = 0; w2 < nw; ++w2) acc += s_acc[(size_t)w2 * 2 * c + j];
-        partial[(size_t)blockIdx.x * 2 * c + j] = acc;
+        if (atomic_dw != nullptr) atomicAdd(j < c ? atomic_dw + j : atomic_db + (j - c), acc);
+        else partial[(size_t)blockIdx.x * 2 * c + j] = acc;
     }
 }
 
@@ -628,11 +630,14 @@ int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const
     if (rows == 0) return PIO_OK;
     Workspace W(ws, ws_bytes);
     const int blocks = ln_bwd_blocks(rows);
-    float* partial = W.takef((size_t)blocks * 2 * c);
-    if (!partial) {
+    const bool atomic = (accumulate == 2);  // dw / db hold a running sum (or zeros): add with atomics, no reduction pass
+    float* partial = atomic ? nullptr : W.takef((size_t)blocks * 2 * c);
+    if (!partial && !atomic) {
         set_error("pio_layernorm_bwd: workspace too small (%zu bytes)", ws_bytes);
         return PIO_ERR_WORKSPACE;
     }
+    float* adw = atomic ? dw : nullptr;
+    float* adb = atomic ? db : nullptr;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t smem = (size_t)8 * 2 * c * sizeof(float);
 #define PIO_LN_BWD(NCH)                                                                                         \
@@ -640,7 +645,7 @@ int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const
         if (smem > 48 * 1024)                                                                                   \
             PIO_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                           (int)smem));                                                          \
-        layernorm_bwd_kernel<NCH><<<blocks, 256, smem, st>>>(dy, x, stats, w, dres, dx, partial, rows, c);       \
+        layernorm_bwd_kernel<NCH><<<blocks, 256, smem, st>>>(dy, x, stats, w, dres, dx, partial, rows, c, adw, adb); \
     } while (0)
     if (c <= 128) PIO_LN_BWD(4);
     else if (c <= 256) PIO_LN_BWD(8);
@@ -648,6 +653,7 @@ int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const
     else PIO_LN_BWD(32);
 #undef PIO_LN_BWD
     PIO_LAUNCH_CHECK();
+    if (atomic) return PIO_OK;
     // partial rows are [dw(c) | db(c)] : reduce both with one launch
     return reduce_partials(partial, blocks, (int64_t)2 * c, dw, c, db, c, accumulate, st);
 }

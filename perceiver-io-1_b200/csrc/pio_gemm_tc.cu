@@ -53,7 +53,8 @@ enum EpiKind : int {
     EPI_B16_GELU = 4,   // aux16 = acc + bias ; c16 = gelu(aux)
     EPI_B16_DGELU = 5,  // c16 = acc * gelu'(aux16)
     EPI_PARTIAL = 6,    // split-K partial sums
-    EPI_GENERIC = 7     // any other combination of outputs / flags
+    EPI_GENERIC = 7,    // any other combination of outputs / flags
+    EPI_F32_ATOMIC = 8  // c32 += acc with fp32 atomics (split-K without a reduction pass; order not deterministic)
 };
 
 __device__ __forceinline__ void store4_f32(float* o, const float (&v)[4], bool vec, int valid) {
@@ -114,7 +115,7 @@ __device__ __forceinline__ void epilogue_rows(const TcParams& p, const float* st
     const int n = n0 + col;
     const int valid = min(4, p.N - n);  // <= 0: this lane has no columns
     float bias[4] = {0.f, 0.f, 0.f, 0.f};
-    if (p.bias && KIND != EPI_PARTIAL && KIND != EPI_B16_DGELU) {
+    if (p.bias && KIND != EPI_PARTIAL && KIND != EPI_B16_DGELU && KIND != EPI_F32_ATOMIC) {
 #pragma unroll
         for (int j = 0; j < 4; ++j)
             if (j < valid) bias[j] = __ldg(p.bias + n + j);
@@ -141,6 +142,11 @@ __device__ __forceinline__ void epilogue_rows(const TcParams& p, const float* st
 #pragma unroll
             for (int j = 0; j < 4; ++j) v[j] += r[j];
             store4_f32(p.c32 + gm * p.ldc32 + n, v, v32, valid);
+        } else if (KIND == EPI_F32_ATOMIC) {
+            float* o = p.c32 + gm * p.ldc32 + n;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (j < valid) atomicAdd(o + j, v[j]);
         } else if (KIND == EPI_F32_ACC) {
             float r[4];
             load4_f32(p.c32 + gm * p.ldc32 + n, r, v32, valid);
@@ -306,6 +312,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
             case EPI_B16_GELU: epilogue_rows<BN, EPI_B16_GELU>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
             case EPI_B16_DGELU: epilogue_rows<BN, EPI_B16_DGELU>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
             case EPI_PARTIAL: epilogue_rows<BN, EPI_PARTIAL>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
+            case EPI_F32_ATOMIC: epilogue_rows<BN, EPI_F32_ATOMIC>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
             default: epilogue_rows<BN, EPI_GENERIC>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
         }
         tc_fence_before();
@@ -392,7 +399,9 @@ int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream
     p.aux16 = (__nv_bfloat16*)d->aux16; p.ldaux = d->ldaux;
     p.act = d->act; p.accumulate = d->accumulate;
     p.partial_stride = d->m * d->n;
-    if (splits > 1) {
+    const bool atomic = (d->accumulate == 2);
+    if (atomic) PIO_CHECK_ARG(splittable, "pio_gemm_bf16: accumulate=2 (atomic) needs a plain fp32 output without epilogue");
+    if (splits > 1 && !atomic) {
         Workspace W(ws, ws_bytes);
         p.partial = W.takef((size_t)splits * (size_t)p.partial_stride);
         if (!p.partial) {
@@ -405,7 +414,8 @@ int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream
     {
         const bool o32 = d->c32 != nullptr, o16 = d->c16 != nullptr;
         int kind = EPI_GENERIC;
-        if (splits > 1) kind = EPI_PARTIAL;
+        if (atomic) kind = EPI_F32_ATOMIC;
+        else if (splits > 1) kind = EPI_PARTIAL;
         else if (o32 && !o16 && d->act == 0 && !d->residual && !d->accumulate) kind = EPI_F32;
         else if (o32 && !o16 && d->act == 0 && d->residual && !d->accumulate) kind = EPI_F32_RES;
         else if (o32 && !o16 && d->act == 0 && !d->residual && d->accumulate) kind = EPI_F32_ACC;
@@ -436,7 +446,8 @@ int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream
     else PIO_TC(128);
 #undef PIO_TC
     PIO_TRY(rc);
-    if (splits > 1) PIO_TRY(reduce_partials(p.partial, splits, p.partial_stride, d->c32, d->m * d->n, nullptr, 0, d->accumulate, st));
+    if (splits > 1 && !atomic)
+        PIO_TRY(reduce_partials(p.partial, splits, p.partial_stride, d->c32, d->m * d->n, nullptr, 0, d->accumulate, st));
     return PIO_OK;
 }
 

@@ -73,6 +73,29 @@ def _mat(w, mode):
     return _w16(w)
 
 
+def _grads_like(params, mode):
+    """Gradient buffers shaped like ``params`` (None stays None) and the `accumulate` flag to pass.
+    fp32 mode: uninitialised buffers, overwritten (0).  bf16 mode: views into one zero-filled slab so the
+    kernels can add into them with atomics (2) and skip their reduction passes."""
+    if mode == N.MODE_FP32:
+        return [torch.empty_like(p) if p is not None else None for p in params], 0
+    live = [p for p in params if p is not None]
+    offs, total = [], 0
+    for p in live:
+        offs.append(total)
+        total += (p.numel() + 3) // 4 * 4
+    slab = torch.zeros(total, dtype=torch.float32, device=live[0].device)
+    it = iter(zip(live, offs))
+    out = []
+    for p in params:
+        if p is None:
+            out.append(None)
+        else:
+            q, o = next(it)
+            out.append(slab[o:o + q.numel()].view(q.shape))
+    return out, 2
+
+
 def _mha_ptrs(w_packed, w_q, w_k, w_v, bias, e):
     """Device addresses of (wq, wk, wv, bq, bk, bv) for packed (3E,E) or split storage; matrix
     weights may be fp32 or bf16 shadows (the packed row pitch is E in both)."""
@@ -221,12 +244,12 @@ class MlpFn(torch.autograd.Function):
         rows, c, residual, mode = ctx.meta
         dy = _c(dy)
         L = N.lib()
-        grads = [torch.empty_like(p) for p in params]
+        grads, accf = _grads_like(params, mode)
         dx = torch.empty_like(x)
         ws = N.workspace(L.pio_mlp_ws_bytes(rows, c, mode), x.device)
         w = ctx.wstruct
         g = N.mlp_struct(**dict(zip(N.MlpWeights._names, grads)))
-        N.check(L.pio_mlp_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g), 0,
+        N.check(L.pio_mlp_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g), accf,
                               rows, c, residual, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_mlp_bwd")
         ctx.saved_buf = None
         return (dx, *grads, None)
@@ -269,18 +292,22 @@ class KVProjectFn(torch.autograd.Function):
         dkv = _c(dkv, torch.float32 if mode == N.MODE_FP32 else torch.bfloat16)
         L = N.lib()
         dev = x_kv.device
-        dln_w, dln_b = torch.empty_like(ln_w), torch.empty_like(ln_b)
-        dbias = torch.zeros_like(bias)
-        dwp = torch.zeros_like(w_packed) if w_packed is not None else None
-        dwk = torch.empty_like(w_k) if w_k is not None else None
-        dwv = torch.empty_like(w_v) if w_v is not None else None
+        if mode == N.MODE_FP32:
+            dln_w, dln_b = torch.empty_like(ln_w), torch.empty_like(ln_b)
+            dbias = torch.zeros_like(bias)
+            dwp = torch.zeros_like(w_packed) if w_packed is not None else None
+            dwk = torch.empty_like(w_k) if w_k is not None else None
+            dwv = torch.empty_like(w_v) if w_v is not None else None
+            accf = 0
+        else:
+            (dln_w, dln_b, dbias, dwp, dwk, dwv), accf = _grads_like((ln_w, ln_b, bias, w_packed, w_k, w_v), mode)
         dx = torch.empty_like(x_kv) if ctx.needs_input_grad[0] else None
         _, gwk, gwv, _, gbk, gbv = _mha_ptrs(dwp, None, dwk, dwv, dbias, e)
         w = ctx.wstruct
         g = N.attn_struct(wk=gwk, wv=gwv, bk=gbk, bv=gbv, kv_ln_w=dln_w, kv_ln_b=dln_b)
         ws = N.workspace(L.pio_kv_project_ws_bytes(rows, ckv, e, mode), dev)
         N.check(L.pio_kv_project_bwd(dkv.data_ptr(), x_kv.data_ptr(), N.ptr(dx), byref(w), ctx.saved_buf.data_ptr(),
-                                     byref(g), 0, rows, ckv, e, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
+                                     byref(g), accf, rows, ckv, e, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
                 "pio_kv_project_bwd")
         ctx.saved_buf = None
         return dx, dln_w, dln_b, dbias, dwp, dwk, dwv, None
@@ -326,11 +353,15 @@ class CrossAttendFn(torch.autograd.Function):
         dy = _c(dy)
         L = N.lib()
         dev = x_q.device
-        dln_w, dln_b = torch.empty_like(ln_w), torch.empty_like(ln_b)
-        dbias = torch.zeros_like(bias)
-        dwp = torch.zeros_like(w_packed) if w_packed is not None else None
-        dwq = torch.empty_like(w_q) if w_q is not None else None
-        dwo, dbo = torch.empty_like(wo), torch.empty_like(bo)
+        if mode == N.MODE_FP32:
+            dln_w, dln_b = torch.empty_like(ln_w), torch.empty_like(ln_b)
+            dbias = torch.zeros_like(bias)
+            dwp = torch.zeros_like(w_packed) if w_packed is not None else None
+            dwq = torch.empty_like(w_q) if w_q is not None else None
+            dwo, dbo = torch.empty_like(wo), torch.empty_like(bo)
+            accf = 0
+        else:
+            (dln_w, dln_b, dbias, dwp, dwq, dwo, dbo), accf = _grads_like((ln_w, ln_b, bias, w_packed, w_q, wo, bo), mode)
         dx = torch.empty_like(x_q)
         dkv = torch.empty_like(kv)
         gwq, _, _, gbq, _, _ = _mha_ptrs(dwp, dwq, None, None, dbias, e)
@@ -338,7 +369,7 @@ class CrossAttendFn(torch.autograd.Function):
         g = N.attn_struct(ln_w=dln_w, ln_b=dln_b, wq=gwq, bq=gbq, wo=dwo, bo=dbo)
         ws = N.workspace(L.pio_cross_attend_ws_bytes(b, n, m, e, heads, mode), dev)
         N.check(L.pio_cross_attend_bwd(dy.data_ptr(), x_q.data_ptr(), kv.data_ptr(), N.ptr(pad), dx.data_ptr(),
-                                       dkv.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g), 0, b, n, m, e, heads,
+                                       dkv.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g), accf, b, n, m, e, heads,
                                        residual, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
                 "pio_cross_attend_bwd")
         ctx.saved_buf = None
@@ -388,7 +419,7 @@ class SelfAttnFn(torch.autograd.Function):
         b, n, c, heads, residual, mode = ctx.meta
         dy = _c(dy)
         L = N.lib()
-        grads = [torch.empty_like(p) for p in params]
+        grads, accf = _grads_like(params, mode)
         dx = torch.empty_like(x)
         w = ctx.wstruct
         gfields = _sa_struct(*grads, c)
@@ -396,7 +427,7 @@ class SelfAttnFn(torch.autograd.Function):
         g = N.attn_struct(**gfields)
         ws = N.workspace(L.pio_self_attn_ws_bytes(b, n, c, heads, mode), x.device)
         N.check(L.pio_self_attn_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g),
-                                    0, b, n, c, heads, residual, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)),
+                                    accf, b, n, c, heads, residual, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)),
                 "pio_self_attn_bwd")
         ctx.saved_buf = None
         return (dx, *grads, None, None)
@@ -452,13 +483,13 @@ class LatentBlockFn(torch.autograd.Function):
         layers, b, n, c, heads, mode = ctx.meta
         dy = _c(dy)
         L = N.lib()
-        grads = [torch.empty_like(p) for p in params]
+        grads, accf = _grads_like(params, mode)
         dx = torch.empty_like(x)
         attn, mlp = ctx.wstructs
         attn_g, mlp_g, _ = LatentBlockFn._structs(grads, layers, c)
         ws = N.workspace(L.pio_latent_block_ws_bytes(layers, b, n, c, heads, mode), x.device)
         N.check(L.pio_latent_block_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), attn, mlp, ctx.saved_buf.data_ptr(), attn_g,
-                                       mlp_g, 0, layers, b, n, c, heads, mode, ws.data_ptr(), ws.numel(),
+                                       mlp_g, accf, layers, b, n, c, heads, mode, ws.data_ptr(), ws.numel(),
                                        N.stream_ptr(x.device)), "pio_latent_block_bwd")
         ctx.saved_buf = None
         return (dx, None, *grads)

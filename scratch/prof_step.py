@@ -12,8 +12,11 @@ opt = torch.optim.AdamW(model.parameters(), lr=3e-3, fused=True)
 ids, pad = bench.synthetic_batch(0, 64, 512, 10003)
 ids, pad = ids.to(dev), pad.to(dev)
 def step():
-    logits, labels = model(ids.clone(), pad)
-    loss = perceiver.cross_entropy(logits, labels)
+    if mode == "bf16":
+        loss, _ = model(ids.clone(), pad, return_loss=True)
+    else:
+        logits, labels = model(ids.clone(), pad)
+        loss = perceiver.cross_entropy(logits, labels)
     opt.zero_grad(set_to_none=True); loss.backward(); opt.step()
 for _ in range(3): step()
 torch.cuda.synchronize()
