@@ -259,20 +259,21 @@ class PerceiverMLM(nn.Module):
         self.decoder = decoder
         self.masking = masking
 
-    def forward(self, x_input, pad_mask=None, masking=True, return_loss=False):
+    def forward(self, x_input, pad_mask=None, masking=True, return_loss=False, labels=None):
         """-> (logits[:, :l], labels) like the reference.  ``return_loss=True`` (training) returns
         (loss, labels) instead: the vocabulary projection and the cross-entropy of
         LitMaskedLanguageModel.step (reference lightning.py:223-226) run as one fused operator and the
-        (B, l, vocab) logits are never stored."""
+        (B, l, vocab) logits are never stored.  With ``masking=False`` the already masked batch can bring
+        its own ``labels`` (e.g. when the masking step runs outside a captured CUDA graph)."""
         _, l = x_input.shape
         if masking:
             x_masked, x_labels = self.masking(x_input, pad_mask)
         else:
-            x_masked, x_labels = x_input, None
+            x_masked, x_labels = x_input, labels
         x_latent, _ = self.encoder(x_masked, pad_mask)
         if return_loss:
             if x_labels is None:
-                raise ValueError('return_loss=True needs masking=True (labels come from the masking step)')
+                raise ValueError('return_loss=True needs labels: masking=True, or masking=False with labels=...')
             lin = self.decoder.output_adapter.linear
             hidden = self.decoder.decode(x_latent, num_queries=l)
             return F.linear_cross_entropy(hidden, lin.weight, lin.bias, x_labels), x_labels
