@@ -165,38 +165,71 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 
 def roofline_dominant_kernel(mode, pk, reps=10):
-    """Dominant kernel of the cfg2 step = the vocabulary-head GEMM (58% of the step's forward FLOPs,
-    SURVEY §8d): logits (B*l, vocab) = x (B*l, 256) W^T + b through pio_linear_fwd.  Algorithmic
-    work per launch = 2*rows*256*vocab FLOP; time = CUDA events on the current stream; an L2 flush
-    (256 MB write) runs between repetitions."""
+    """Dominant kernel of the cfg2 step: the GEMM kernel (gemm_tc_kernel in bf16 mode, gemm_f32_kernel in
+    fp32 mode) on the step's largest products, the vocabulary head: logits = x W^T (32768 x 10003 x 256),
+    dx = dlogits W and dW = dlogits^T x.  Algorithmic work = 2*m*n*k FLOP per launch (SURVEY section 8d);
+    time = CUDA events on the launching stream around each launch, 256 MB L2 flush between launches;
+    achieved = total FLOP / total time over the three products."""
+    import ctypes
     from perceiver import _native as N
     rows, c, v = CFG["batch"] * CFG["seq"], CFG["latent"][1], CFG["vocab"]
+    vp = (v + 7) // 8 * 8
     dev = torch.device("cuda", torch.cuda.current_device())
-    x = torch.randn(rows, c, device=dev)
-    w = torch.randn(v, c, device=dev) * 0.05
-    b = torch.zeros(v, device=dev)
-    y = torch.empty(rows, v, device=dev)
     L = N.lib()
-    ws = N.workspace(L.pio_linear_ws_bytes(rows, c, v, mode), dev)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     st = N.stream_ptr(dev)
-    times = []
-    for i in range(reps + 3):
-        flush.zero_()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        N.check(L.pio_linear_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), rows, c, v, mode, ws.data_ptr(),
-                                 ws.numel(), st), "pio_linear_fwd")
-        e1.record()
-        e1.synchronize()
-        if i >= 3:
-            times.append(e0.elapsed_time(e1))
-    ms = sum(times) / len(times)
-    flops = 2.0 * rows * c * v
-    achieved = flops / (ms * 1e-3) / 1e12
-    return {"kernel": "vocab-head GEMM (pio_linear_fwd: 32768x256 @ 256x10003)", "bound": "tensor",
-            "achieved": round(achieved, 3), "peak": pk["tflops"], "unit": "TFLOP/s", "frac": round(achieved / pk["tflops"], 5),
-            "traffic": None, "ms_per_launch": round(ms, 4), "flops_per_launch": flops, "peak_source": pk["source"] + " (burst)"}
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    out = {}
+    if mode == 1:
+        x = torch.randn(rows, c, device=dev).to(torch.bfloat16)
+        w = (torch.randn(v, c, device=dev) * 0.05).to(torch.bfloat16)
+        dl = torch.zeros(rows, vp, device=dev, dtype=torch.bfloat16)
+        dl[:, :v] = torch.randn(rows, v, device=dev).to(torch.bfloat16)
+        shapes = {"logits": (x, w, rows, v, c, 1, 1), "dx": (dl, w, rows, c, v, 1, 0), "dW": (dl, x, v, c, rows, 0, 0)}
+        ws = torch.empty(64 << 20, dtype=torch.uint8, device=dev)
+        for name, (a, b, m, n, k, ak, bk) in shapes.items():
+            cbuf = torch.empty(m, n, device=dev)
+            d = N.GemmBf16Desc()
+            d.a, d.b, d.m, d.n, d.k, d.lda, d.ldb = a.data_ptr(), b.data_ptr(), m, n, k, a.shape[1], b.shape[1]
+            d.a_kmajor, d.b_kmajor, d.c32, d.ldc32 = ak, bk, cbuf.data_ptr(), n
+            ts = []
+            for i in range(reps + 3):
+                flush.zero_()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                N.check(L.pio_gemm_bf16(ctypes.byref(d), ws.data_ptr(), ws.numel(), st), "pio_gemm_bf16")
+                e1.record()
+                e1.synchronize()
+                if i >= 3:
+                    ts.append(e0.elapsed_time(e1))
+            out[name] = sum(ts) / len(ts)
+        kernel = "gemm_tc_kernel (tcgen05 + TMA), vocabulary-head products"
+    else:
+        x = torch.randn(rows, c, device=dev)
+        w = torch.randn(v, c, device=dev) * 0.05
+        b = torch.zeros(v, device=dev)
+        y = torch.empty(rows, v, device=dev)
+        ws = N.workspace(L.pio_linear_ws_bytes(rows, c, v, mode), dev)
+        ts = []
+        for i in range(reps + 3):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            N.check(L.pio_linear_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), rows, c, v, mode, ws.data_ptr(),
+                                     ws.numel(), st), "pio_linear_fwd")
+            e1.record()
+            e1.synchronize()
+            if i >= 3:
+                ts.append(e0.elapsed_time(e1))
+        out["logits"] = sum(ts) / len(ts)
+        kernel = "gemm_f32_kernel (FFMA), vocabulary-head logits"
+    flops_each = 2.0 * rows * c * v
+    total_ms = sum(out.values())
+    achieved = flops_each * len(out) / (total_ms * 1e-3) / 1e12
+    return {"kernel": kernel, "bound": "tensor", "achieved": round(achieved, 2), "peak": pk["tflops"], "unit": "TFLOP/s",
+            "frac": round(achieved / pk["tflops"], 5), "traffic": None,
+            "ms_per_launch": {k: round(t, 4) for k, t in out.items()},
+            "tflops_per_launch": {k: round(flops_each / (t * 1e-3) / 1e12, 1) for k, t in out.items()},
+            "flops_per_launch": flops_each, "peak_source": pk["source"] + " (burst)"}
 
 
 def cross_attention_core_tflops(mode, pk):
@@ -316,8 +349,10 @@ def gpu_arm(args):
         mask_into_static(ids_d, pad_d)
         opt.zero_grad(set_to_none=True)
         graph = torch.cuda.CUDAGraph()
+        captured0 = N.lib().pio_launch_count()
         with torch.cuda.graph(graph):
             g_loss = body()
+        graph_launches = N.lib().pio_launch_count() - captured0  # kernels of this library inside one replay
 
         def step(ids, pad):  # noqa: F811
             mask_into_static(ids, pad)
@@ -352,6 +387,8 @@ def gpu_arm(args):
     launches0 = N.lib().pio_launch_count()
     total_ms = timed(lambda: step(ids_d, pad_d), args.steps)
     launches = N.lib().pio_launch_count() - launches0
+    if graph is not None:
+        launches += graph_launches * args.steps  # replays do not pass through the host-side counter
     clocks = sampler.stop() if rank == 0 else None
     if args.profile_only:
         if rank == 0:
