@@ -111,7 +111,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -142,7 +142,7 @@ class ClockSampler:
         window = "timed region"
         if len(inside) < 2:
             inside = [ln for _, ln in self.lines]
-            window = "warm-up + timed region (timed region shorter than two 100 ms samples)"
+            window = "warm-up + timed region (timed region shorter than two 50 ms samples)"
         for ln in inside:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 6:
