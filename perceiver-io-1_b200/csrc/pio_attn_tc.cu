@@ -51,30 +51,49 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// 32 fp32 values -> bf16, into row `row` of a 128-row x 128-byte swizzled (K-major, SW128) region;
+// half = which 64-byte half of the 128-byte row (columns 0..31 or 32..63 of the 64-column region)
+__device__ __forceinline__ void store_row_half_bf16(uint8_t* region, int row, int half, const float (&v)[32]) {
+    uint8_t* prow = region + row * 128;
+#pragma unroll
+    for (int piece = 0; piece < 4; ++piece) {
+        uint32_t w[4];
+#pragma unroll
+        for (int e2 = 0; e2 < 4; ++e2) {
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[piece * 8 + 2 * e2], v[piece * 8 + 2 * e2 + 1]);
+            w[e2] = *reinterpret_cast<uint32_t*>(&h2);
+        }
+        const int ci = half * 4 + piece;
+        *reinterpret_cast<uint4*>(prow + ((ci ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
 template <int BKV>
 __global__ void __launch_bounds__(FA_THREADS, 2)
     attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const FaParams p) {
+    static_assert(BKV == 64, "the pipelined schedule is laid out for 64-key tiles");
     constexpr int DH = 64;
+    constexpr int KV_STAGES = 3;
     constexpr int Q_BYTES = FA_BQ * DH * 2;   // 16 KB
-    constexpr int KV_BYTES = BKV * DH * 2;    // 8 KB at BKV = 64
-    constexpr int P_BYTES = FA_BQ * BKV * 2;  // 16 KB at BKV = 64
-    constexpr int TMEM_COLS = (BKV + DH <= 128) ? 128 : 256;
+    constexpr int KV_BYTES = BKV * DH * 2;    // 8 KB
+    constexpr int P_BYTES = FA_BQ * BKV * 2;  // 16 KB
+    constexpr int TMEM_COLS = 256;            // S0 | S1 | O0 | O1, 64 columns each
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* sQ = smem;
-    uint8_t* sK = sQ + Q_BYTES;           // [2][KV_BYTES]
-    uint8_t* sV = sK + 2 * KV_BYTES;      // [2][KV_BYTES]
-    uint8_t* sP = sV + 2 * KV_BYTES;      // BKV/64 regions of 128 rows x 128 B
-    float* sBias = (float*)(sP + P_BYTES);  // [2][BKV]
+    uint8_t* sK = sQ + Q_BYTES;                  // [KV_STAGES][KV_BYTES]
+    uint8_t* sV = sK + KV_STAGES * KV_BYTES;     // [KV_STAGES][KV_BYTES]
+    uint8_t* sP = sV + KV_STAGES * KV_BYTES;     // [2][P_BYTES]
+    float* sBias = (float*)(sP + 2 * P_BYTES);   // [2][BKV]
     uint64_t* bars = (uint64_t*)(sBias + 2 * BKV);
     uint64_t* q_full = bars;
-    uint64_t* kv_full = bars + 1;   // [2]
-    uint64_t* kv_empty = bars + 3;  // [2]
-    uint64_t* s_full = bars + 5;
-    uint64_t* p_full = bars + 6;
-    uint64_t* o_full = bars + 7;
-    uint32_t* tmem_slot = (uint32_t*)(bars + 8);
+    uint64_t* kv_full = bars + 1;               // [3]
+    uint64_t* kv_empty = bars + 4;              // [3]
+    uint64_t* s_full = bars + 7;                // [2]
+    uint64_t* o_full = bars + 9;                // [2]
+    uint64_t* p_full = bars + 11;
+    uint32_t* tmem_slot = (uint32_t*)(bars + 12);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q0 = blockIdx.x * FA_BQ, h = blockIdx.y, b = blockIdx.z;
@@ -85,13 +104,15 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
         prefetch_tmap(&tmK);
         prefetch_tmap(&tmV);
         mbar_init(q_full, 1);
-        for (int s = 0; s < 2; ++s) {
+        for (int s = 0; s < KV_STAGES; ++s) {
             mbar_init(&kv_full[s], 1);
             mbar_init(&kv_empty[s], 1);
         }
-        mbar_init(s_full, 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&s_full[s], 1);
+            mbar_init(&o_full[s], 1);
+        }
         mbar_init(p_full, 4);
-        mbar_init(o_full, 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -99,16 +120,14 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t tmem_s = tmem_base;
-    const uint32_t tmem_o = tmem_base + BKV;
 
     if (warp == 0) {
         if (lane == 0) {
             mbar_expect_tx(q_full, Q_BYTES);
             tma_load_3d(sQ, &tmQ, h * DH, q0, b, q_full);
             for (int j = 0; j < T; ++j) {
-                const int s = j & 1;
-                const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+                const int s = j % KV_STAGES;
+                const uint32_t ph = (uint32_t)(j / KV_STAGES) & 1u;
                 mbar_wait(&kv_empty[s], ph ^ 1u);
                 mbar_expect_tx(&kv_full[s], 2 * KV_BYTES);
                 tma_load_3d(sK + s * KV_BYTES, &tmK, h * DH, j * BKV, b, &kv_full[s]);
@@ -118,28 +137,36 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
         __syncwarp();
     } else if (warp == 1) {
         if (lane == 0) {
+            // Software pipeline: S(j+1) = Q K(j+1)^T is issued before waiting for P(j), so the tensor core works
+            // on the next score tile while the softmax warps are busy with the current one, and O(j) = P(j) V(j)
+            // lands in the TMEM buffer the softmax warps only read one tile later.
             const uint32_t idesc_s = make_idesc(BKV, false, false);
             const uint32_t idesc_o = make_idesc(DH, false, true);
-            mbar_wait(q_full, 0);
-            for (int j = 0; j < T; ++j) {
-                const int s = j & 1;
-                const uint32_t ph = (uint32_t)(j >> 1) & 1u;
-                mbar_wait(&kv_full[s], ph);
+            const uint32_t q_addr = smem_u32(sQ);
+            auto issue_s = [&](int j) {
+                const int s = j % KV_STAGES;
+                mbar_wait(&kv_full[s], (uint32_t)(j / KV_STAGES) & 1u);
                 tc_fence_after();
-                const uint32_t q_addr = smem_u32(sQ), k_addr = smem_u32(sK + s * KV_BYTES), v_addr = smem_u32(sV + s * KV_BYTES);
+                const uint32_t k_addr = smem_u32(sK + s * KV_BYTES);
 #pragma unroll
                 for (int t = 0; t < DH / 16; ++t)
-                    umma_bf16(tmem_s, make_smem_desc(q_addr + t * 32, 16, 1024), make_smem_desc(k_addr + t * 32, 16, 1024), idesc_s,
-                              t > 0 ? 1u : 0u);
-                umma_commit(s_full);
+                    umma_bf16(tmem_base + (uint32_t)(j & 1) * 64, make_smem_desc(q_addr + t * 32, 16, 1024),
+                              make_smem_desc(k_addr + t * 32, 16, 1024), idesc_s, t > 0 ? 1u : 0u);
+                umma_commit(&s_full[j & 1]);
+            };
+            mbar_wait(q_full, 0);
+            issue_s(0);
+            for (int j = 0; j < T; ++j) {
+                if (j + 1 < T) issue_s(j + 1);
                 mbar_wait(p_full, (uint32_t)j & 1u);
                 tc_fence_after();
-                const uint32_t p_addr = smem_u32(sP);
+                const int s = j % KV_STAGES;
+                const uint32_t p_addr = smem_u32(sP + (j & 1) * P_BYTES), v_addr = smem_u32(sV + s * KV_BYTES);
 #pragma unroll
                 for (int t = 0; t < BKV / 16; ++t)
-                    umma_bf16(tmem_o, make_smem_desc(p_addr + (t / 4) * 16384 + (t % 4) * 32, 16, 1024),
+                    umma_bf16(tmem_base + 128 + (uint32_t)(j & 1) * 64, make_smem_desc(p_addr + t * 32, 16, 1024),
                               make_smem_desc(v_addr + t * 2048, BKV * 128, 1024), idesc_o, t > 0 ? 1u : 0u);
-                umma_commit(o_full);
+                umma_commit(&o_full[j & 1]);
                 umma_commit(&kv_empty[s]);
             }
         }
@@ -147,14 +174,27 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     } else {
         // ---------------- softmax warps: thread = query row, TMEM lane quadrant = warp id mod 4
         const int qd = warp & 3;
-        const int row = qd * 32 + lane;      // 0..127 within the tile
+        const int row = qd * 32 + lane;          // 0..127 within the tile
         const int tid = (warp - 2) * 32 + lane;  // 0..127 for cooperative loads
         const uint32_t lane_off = (uint32_t)(qd * 32) << 16;
         const uint8_t* padb = p.pad ? p.pad + (int64_t)b * p.m : nullptr;
-        float m_run = -INFINITY, l_run = 0.f;
+        float m_run = -INFINITY, l_run = 0.f, alpha_prev = 1.f;
         float acc[DH];
 #pragma unroll
         for (int d = 0; d < DH; ++d) acc[d] = 0.f;
+        auto fold_o = [&](int j, float alpha) {  // acc = acc * alpha + O(j)
+            mbar_wait(&o_full[j & 1], (uint32_t)(j >> 1) & 1u);
+            tc_fence_after();
+            const uint32_t to = tmem_base + 128 + (uint32_t)(j & 1) * 64 + lane_off;
+#pragma unroll
+            for (int c0 = 0; c0 < DH; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld32(to + (uint32_t)c0, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[c0 + i] = fmaf(acc[c0 + i], alpha, __uint_as_float(r[i]));
+            }
+        };
         for (int j = 0; j < T; ++j) {
             const int j0 = j * BKV;
             const bool masked = (padb != nullptr) || (j0 + BKV > p.m);  // CTA-uniform
@@ -167,74 +207,52 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                 }
                 asm volatile("bar.sync 1, 128;" ::: "memory");
             }
-            mbar_wait(s_full, (uint32_t)j & 1u);
+            mbar_wait(&s_full[j & 1], (uint32_t)(j >> 1) & 1u);
             tc_fence_after();
-            // pass 1: row maximum of the scaled scores
-            float mx = -INFINITY;
+            const uint32_t ts = tmem_base + (uint32_t)(j & 1) * 64 + lane_off;
+            // the whole 64-column score row lives in registers: one TMEM read, max, then exp
+            uint32_t r0[32], r1[32];
+            tmem_ld32(ts, r0);
+            tmem_ld32(ts + 32, r1);
+            tmem_ld_wait();
+            float sv[64];
 #pragma unroll
-            for (int c0 = 0; c0 < BKV; c0 += 32) {
-                uint32_t r[32];
-                tmem_ld32(tmem_s + lane_off + (uint32_t)c0, r);
-                tmem_ld_wait();
-                if (masked) {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]) * p.scale_log2e + bias[c0 + i]);
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]) * p.scale_log2e);
-                }
+            for (int i = 0; i < 32; ++i) {
+                sv[i] = __uint_as_float(r0[i]) * p.scale_log2e;
+                sv[32 + i] = __uint_as_float(r1[i]) * p.scale_log2e;
             }
+            if (masked) {
+#pragma unroll
+                for (int i = 0; i < 64; ++i) sv[i] += bias[i];
+            }
+            float mx = sv[0];
+#pragma unroll
+            for (int i = 1; i < 64; ++i) mx = fmaxf(mx, sv[i]);
             const float m_new = fmaxf(m_run, mx);
             const float m_use = (m_new == -INFINITY) ? 0.f : m_new;  // fully masked so far: every p below is 0
             const float alpha = fast_exp2(m_run - m_use);            // exp2(-inf) = 0 on the first live tile
-            // pass 2: p = exp2(s - m), row sum, bf16 P into the swizzled K-major layout
             float l_tile = 0.f;
+            uint8_t* pbuf = sP + (j & 1) * P_BYTES;
 #pragma unroll
-            for (int c0 = 0; c0 < BKV; c0 += 32) {
-                uint32_t r[32];
-                tmem_ld32(tmem_s + lane_off + (uint32_t)c0, r);
-                tmem_ld_wait();
+            for (int half = 0; half < 2; ++half) {
                 float pv[32];
-                if (masked) {
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) pv[i] = fast_exp2(__uint_as_float(r[i]) * p.scale_log2e + bias[c0 + i] - m_use);
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) pv[i] = fast_exp2(__uint_as_float(r[i]) * p.scale_log2e - m_use);
+                for (int i = 0; i < 32; ++i) {
+                    pv[i] = fast_exp2(sv[half * 32 + i] - m_use);
+                    l_tile += pv[i];
                 }
-#pragma unroll
-                for (int i = 0; i < 32; ++i) l_tile += pv[i];
-                uint8_t* prow = sP + (c0 / 64) * 16384 + row * 128;
-#pragma unroll
-                for (int piece = 0; piece < 4; ++piece) {
-                    uint32_t w[4];
-#pragma unroll
-                    for (int e2 = 0; e2 < 4; ++e2) {
-                        __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[piece * 8 + 2 * e2], pv[piece * 8 + 2 * e2 + 1]);
-                        w[e2] = *reinterpret_cast<uint32_t*>(&h2);
-                    }
-                    const int ci = ((c0 % 64) / 32) * 4 + piece;  // 16-byte chunk index within the 128-byte row
-                    *reinterpret_cast<uint4*>(prow + ((ci ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
-                }
+                store_row_half_bf16(pbuf, row, half, pv);
             }
             l_run = l_run * alpha + l_tile;
             m_run = m_new;
-            tc_fence_before();     // TMEM reads of S are done before the next MMA may overwrite it
-            fence_proxy_async();   // P stores visible to the tensor-core (async) proxy
+            tc_fence_before();    // TMEM reads of S(j) are done before a later MMA may overwrite the buffer
+            fence_proxy_async();  // P stores visible to the tensor-core (async) proxy
             __syncwarp();
             if (lane == 0) mbar_arrive(p_full);
-            // fold O_tile = P V into the register accumulator
-            mbar_wait(o_full, (uint32_t)j & 1u);
-            tc_fence_after();
-#pragma unroll
-            for (int c0 = 0; c0 < DH; c0 += 32) {
-                uint32_t r[32];
-                tmem_ld32(tmem_o + lane_off + (uint32_t)c0, r);
-                tmem_ld_wait();
-#pragma unroll
-                for (int i = 0; i < 32; ++i) acc[c0 + i] = fmaf(acc[c0 + i], alpha, __uint_as_float(r[i]));
-            }
+            if (j > 0) fold_o(j - 1, alpha_prev);  // O(j-1) finished while this tile's softmax ran
+            alpha_prev = alpha;
         }
+        fold_o(T - 1, alpha_prev);
         tc_fence_before();
         const int qi = q0 + row;
         if (qi < p.n) {
@@ -289,23 +307,6 @@ struct FaBwdParams {
     int batch, heads, n, m;
     float scale, scale_log2e;
 };
-
-// 32 fp32 values -> bf16, into row `row` of a 128-row x 128-byte swizzled (K-major, SW128) region;
-// half = which 64-byte half of the 128-byte row (columns 0..31 or 32..63 of the 64-column region)
-__device__ __forceinline__ void store_row_half_bf16(uint8_t* region, int row, int half, const float (&v)[32]) {
-    uint8_t* prow = region + row * 128;
-#pragma unroll
-    for (int piece = 0; piece < 4; ++piece) {
-        uint32_t w[4];
-#pragma unroll
-        for (int e2 = 0; e2 < 4; ++e2) {
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[piece * 8 + 2 * e2], v[piece * 8 + 2 * e2 + 1]);
-            w[e2] = *reinterpret_cast<uint32_t*>(&h2);
-        }
-        const int ci = half * 4 + piece;
-        *reinterpret_cast<uint4*>(prow + ((ci ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
-    }
-}
 
 __device__ __forceinline__ void store_row64_bf16_global(__nv_bfloat16* dst, const float (&v)[32], int c0) {
 #pragma unroll
@@ -711,7 +712,7 @@ int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st) {
     p.o_bs = d->o_bs; p.o_rs = d->o_rs;
     p.batch = d->batch; p.heads = d->heads; p.n = d->n; p.m = d->m;
     p.scale_log2e = d->scale * 1.44269504088896340736f;
-    const size_t smem = (size_t)FA_BQ * 64 * 2 + 4 * (size_t)BKV * 64 * 2 + (size_t)FA_BQ * BKV * 2 + 2 * BKV * 4 + 128 + 1024;
+    const size_t smem = (size_t)FA_BQ * 64 * 2 + 6 * (size_t)BKV * 64 * 2 + 2 * (size_t)FA_BQ * BKV * 2 + 2 * BKV * 4 + 128 + 1024;
     static bool configured = false;
     if (!configured) {
         PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
