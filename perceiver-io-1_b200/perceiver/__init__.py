@@ -6,6 +6,7 @@ hand-written sm_100a CUDA kernels (libpio_b200.so, C ABI in include/pio_b200.h).
 """
 from .adapter import (ClassificationOutputAdapter, ImageInputAdapter, InputAdapter, OutputAdapter,
                       SemanticSegOutputAdapter, TextInputAdapter, TextOutputAdapter)
+from .lightning import LitImageClassifier, LitMaskedLanguageModel, LitTextClassifier
 from .functional import cross_entropy, get_compute_mode, linear_cross_entropy, set_compute_mode
 from .model import (CrossAttention, MultiHeadAttention, PerceiverDecoder, PerceiverEncoder, PerceiverIO, PerceiverMLM,
                     Residual, SelfAttention, TextMasking, cross_attention_layer, mlp, self_attention_block,
