@@ -3,6 +3,10 @@
 // stream, softmax and all parameter gradients stay fp32.  Matrix weights arrive as bf16 shadows
 // (row pitch padded to 8 elements) in the same pio_*_weights structs; LayerNorm parameters and
 // biases stay fp32.  Saved activations that only feed GEMMs are kept in bf16.
+#include <stdlib.h>
+
+#include <mutex>
+
 #include "pio_ops_common.cuh"
 
 namespace pio {
@@ -31,6 +35,63 @@ struct ByteCarver {
 
 static int tc_gemm(Ctx& c, const pio_gemm_bf16_desc& d) { return gemm_bf16(&d, c.rest(), c.rest_bytes(), c.st); }
 
+// ---------------------------------------------------------------- side stream for weight gradients
+// In the backward pass the weight / bias gradients (dW = dY^T X, db = colsum dY) hang off the critical
+// dX chain: nothing downstream in the same operator reads them.  With atomic accumulation (accumulate
+// == 2) they need no scratch either, so they are forked onto a per-device auxiliary stream and joined at
+// the end of the operator; the small, latency-bound kernels of the two chains then overlap on the GPU
+// (under stream capture the fork/join becomes two parallel branches of the graph).
+struct SideRes {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+};
+static SideRes* side_res() {
+    static SideRes res[64];
+    static std::mutex mu;
+    static const bool disabled = getenv("PIO_NO_SIDE_STREAM") != nullptr;
+    if (disabled) return nullptr;
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lock(mu);
+    SideRes& r = res[dev];
+    if (r.stream == nullptr) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        (void)cs;
+        if (cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking) != cudaSuccess) { r.stream = nullptr; return nullptr; }
+        if (cudaEventCreateWithFlags(&r.fork, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&r.join, cudaEventDisableTiming) != cudaSuccess) {
+            r.stream = nullptr;
+            return nullptr;
+        }
+    }
+    return &r;
+}
+
+struct Side {
+    Ctx& c;
+    SideRes* r;
+    bool used = false;
+    Side(Ctx& ctx, int acc) : c(ctx), r(acc == 2 ? side_res() : nullptr) {}
+    bool active() const { return r != nullptr; }
+    cudaStream_t stream() const { return r ? r->stream : c.st; }
+    // everything enqueued on the main stream so far becomes visible to the side stream
+    int fork() {
+        if (!r) return PIO_OK;
+        PIO_CUDA(cudaEventRecord(r->fork, c.st));
+        PIO_CUDA(cudaStreamWaitEvent(r->stream, r->fork, 0));
+        used = true;
+        return PIO_OK;
+    }
+    // the main stream waits for everything enqueued on the side stream
+    int join() {
+        if (!r || !used) return PIO_OK;
+        PIO_CUDA(cudaEventRecord(r->join, r->stream));
+        PIO_CUDA(cudaStreamWaitEvent(c.st, r->join, 0));
+        used = false;
+        return PIO_OK;
+    }
+};
+
 // y = act(x16 W16^T + bias) (+ residual)
 static int tc_xwT(Ctx& c, const bf16* x, int64_t ldx, const bf16* w, int64_t ldw, int64_t rows, int64_t n, int64_t k,
                   float* c32, int64_t ldc32, bf16* c16, int64_t ldc16, const float* bias, const float* res, int64_t ldr,
@@ -52,11 +113,16 @@ static int tc_dyW(Ctx& c, const bf16* dy, int64_t lddy, const bf16* w, int64_t l
 }
 // dw[nout, kin] (+)= dy16[rows, nout]^T x16[rows, kin]   (both read MN-major, in place; split-K)
 static int tc_dW(Ctx& c, const bf16* dy, int64_t lddy, const bf16* x, int64_t ldx, float* dw, int64_t rows, int64_t nout,
-                 int64_t kin, int accumulate) {
+                 int64_t kin, int accumulate, cudaStream_t st = nullptr) {
     pio_gemm_bf16_desc d{};
     d.a = dy; d.b = x; d.m = nout; d.n = kin; d.k = rows; d.lda = lddy; d.ldb = ldx; d.a_kmajor = 0; d.b_kmajor = 0;
     d.c32 = dw; d.ldc32 = kin; d.accumulate = accumulate;
-    return tc_gemm(c, d);
+    if (st == nullptr || st == c.st) return tc_gemm(c, d);
+    return gemm_bf16(&d, nullptr, 0, st);  // side stream: atomic accumulation, no scratch
+}
+static int side_colsum(Ctx& c, const Side& sd, const bf16* src, int64_t ld, float* out, int acc, int64_t rows, int cols) {
+    if (sd.active()) return colsum_bf16(src, ld, out, acc, rows, cols, nullptr, 0, sd.stream());
+    return colsum_bf16(src, ld, out, acc, rows, cols, c.rest(), c.rest_bytes(), c.st);
 }
 
 static size_t scratch_bytes(int64_t rows, int64_t nout, int64_t kin) {
@@ -106,14 +172,18 @@ int mlp_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_mlp_we
     PIO_TAKE_BYTES(bf16, dy16, c, (size_t)rows * ch * 2, "pio_mlp_bwd");
     PIO_TAKE_BYTES(bf16, dh1, c, (size_t)rows * ch * 2, "pio_mlp_bwd");
     PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ch * 4, "pio_mlp_bwd");
+    Side side(c, acc);
     PIO_TRY(cast_colsum_f32(dy, ch, dy16, ch, g->b2, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(side.fork());
+    PIO_TRY(tc_dW(c, dy16, ch, s.g, ch, g->w2, rows, ch, ch, acc, side.stream()));
     PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->w2, ch, rows, ch, ch, nullptr, 0, dh1, ch, 2, s.h1, ch, 0));
-    PIO_TRY(tc_dW(c, dy16, ch, s.g, ch, g->w2, rows, ch, ch, acc));
-    PIO_TRY(colsum_bf16(dh1, ch, g->b1, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(side.fork());
+    PIO_TRY(side_colsum(c, side, dh1, ch, g->b1, acc, rows, ch));
+    PIO_TRY(tc_dW(c, dh1, ch, s.h0, ch, g->w1, rows, ch, ch, acc, side.stream()));
     PIO_TRY(tc_dyW(c, dh1, ch, (const bf16*)w->w1, ch, rows, ch, ch, dh0, ch, nullptr, 0, 0, nullptr, 0, 0));
-    PIO_TRY(tc_dW(c, dh1, ch, s.h0, ch, g->w1, rows, ch, ch, acc));
     PIO_TRY(pio_layernorm_bwd(dh0, x, s.stats, w->ln_w, residual ? dy : nullptr, dx, g->ln_w, g->ln_b, acc, rows, ch,
                               c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(side.join());
     c.W.off = mark;
     return PIO_OK;
 }
@@ -164,11 +234,19 @@ int kv_project_bwd(Ctx& c, const float* dkv, const float* x_kv, float* dx_kv, co
     const size_t mark = c.W.off;
     const bf16* dkv16 = reinterpret_cast<const bf16*>(dkv);  // bf16 mode: the kv gradient is bf16
     PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ckv * 4, "pio_kv_project_bwd");
+    Side side(c, acc);
+    PIO_TRY(side.fork());
     if (g->bv == g->bk + e) {
-        PIO_TRY(colsum_bf16(dkv16, 2 * e, g->bk, acc, rows, 2 * e, c.rest(), c.rest_bytes(), c.st));
+        PIO_TRY(side_colsum(c, side, dkv16, 2 * e, g->bk, acc, rows, 2 * e));
     } else {
-        PIO_TRY(colsum_bf16(dkv16, 2 * e, g->bk, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
-        PIO_TRY(colsum_bf16(dkv16 + e, 2 * e, g->bv, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
+        PIO_TRY(side_colsum(c, side, dkv16, 2 * e, g->bk, acc, rows, e));
+        PIO_TRY(side_colsum(c, side, dkv16 + e, 2 * e, g->bv, acc, rows, e));
+    }
+    if (g->wv == g->wk + (size_t)e * ckv) {
+        PIO_TRY(tc_dW(c, dkv16, 2 * e, s.h0, ckp, g->wk, rows, 2 * e, ckv, acc, side.stream()));
+    } else {
+        PIO_TRY(tc_dW(c, dkv16, 2 * e, s.h0, ckp, g->wk, rows, e, ckv, acc, side.stream()));
+        PIO_TRY(tc_dW(c, dkv16 + e, 2 * e, s.h0, ckp, g->wv, rows, e, ckv, acc, side.stream()));
     }
     if (packed16(w->wk, w->wv, e, ckp)) {
         PIO_TRY(tc_dyW(c, dkv16, 2 * e, (const bf16*)w->wk, ckp, rows, 2 * e, ckv, dh0, ckv, nullptr, 0, 0, nullptr, 0, 0));
@@ -176,14 +254,9 @@ int kv_project_bwd(Ctx& c, const float* dkv, const float* x_kv, float* dx_kv, co
         PIO_TRY(tc_dyW(c, dkv16, 2 * e, (const bf16*)w->wk, ckp, rows, e, ckv, dh0, ckv, nullptr, 0, 0, nullptr, 0, 0));
         PIO_TRY(tc_dyW(c, dkv16 + e, 2 * e, (const bf16*)w->wv, ckp, rows, e, ckv, dh0, ckv, nullptr, 0, 0, nullptr, 0, 1));
     }
-    if (g->wv == g->wk + (size_t)e * ckv) {
-        PIO_TRY(tc_dW(c, dkv16, 2 * e, s.h0, ckp, g->wk, rows, 2 * e, ckv, acc));
-    } else {
-        PIO_TRY(tc_dW(c, dkv16, 2 * e, s.h0, ckp, g->wk, rows, e, ckv, acc));
-        PIO_TRY(tc_dW(c, dkv16 + e, 2 * e, s.h0, ckp, g->wv, rows, e, ckv, acc));
-    }
     PIO_TRY(pio_layernorm_bwd(dh0, x_kv, s.stats, w->kv_ln_w, nullptr, dx_kv, g->kv_ln_w, g->kv_ln_b, acc, rows, ckv, c.rest(),
                               c.rest_bytes(), c.st));
+    PIO_TRY(side.join());
     c.W.off = mark;
     return PIO_OK;
 }
@@ -264,8 +337,10 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
     PIO_TAKE_BYTES(float, d_o, c, (size_t)rows * e * 4, "pio_cross_attend_bwd");
     PIO_TAKE_BYTES(float, dhq, c, (size_t)rows * e * 4, "pio_cross_attend_bwd");
     PIO_TAKE_BYTES(float, delta, c, (size_t)batch * heads * n * 4, "pio_cross_attend_bwd");
+    Side side(c, acc);
     PIO_TRY(cast_colsum_f32(dy, e, dy16, e, g->bo, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
-    PIO_TRY(tc_dW(c, dy16, e, s.o16, e, g->wo, rows, e, e, acc));
+    PIO_TRY(side.fork());
+    PIO_TRY(tc_dW(c, dy16, e, s.o16, e, g->wo, rows, e, e, acc, side.stream()));
     const bf16* kv16 = reinterpret_cast<const bf16*>(kv);
     bf16* dkv16 = reinterpret_cast<bf16*>(dkv);
     pio_attn_bwd_desc b{};
@@ -282,11 +357,13 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
         ex.dq16 = dq16; ex.dk16 = dkv16; ex.dv16 = dkv16 + e;
         PIO_TRY(attn_bwd_simt(&b, c.st, &ex));
     }
-    PIO_TRY(colsum_bf16(dq16, e, g->bq, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(side.fork());
+    PIO_TRY(side_colsum(c, side, dq16, e, g->bq, acc, rows, e));
+    PIO_TRY(tc_dW(c, dq16, e, s.hq, e, g->wq, rows, e, e, acc, side.stream()));
     PIO_TRY(tc_dyW(c, dq16, e, (const bf16*)w->wq, e, rows, e, e, dhq, e, nullptr, 0, 0, nullptr, 0, 0));
-    PIO_TRY(tc_dW(c, dq16, e, s.hq, e, g->wq, rows, e, e, acc));
     PIO_TRY(pio_layernorm_bwd(dhq, x_q, s.stats, w->ln_w, residual ? dy : nullptr, dx_q, g->ln_w, g->ln_b, acc, rows, e,
                               c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(side.join());
     c.W.off = mark;
     return PIO_OK;
 }
@@ -355,8 +432,10 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
     PIO_TAKE_BYTES(float, d_o, c, (size_t)rows * ch * 4, "pio_self_attn_bwd");
     PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ch * 4, "pio_self_attn_bwd");
     PIO_TAKE_BYTES(float, delta, c, (size_t)batch * heads * n * 4, "pio_self_attn_bwd");
+    Side side(c, acc);
     PIO_TRY(cast_colsum_f32(dy, ch, dy16, ch, g->bo, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
-    PIO_TRY(tc_dW(c, dy16, ch, s.o16, ch, g->wo, rows, ch, ch, acc));
+    PIO_TRY(side.fork());
+    PIO_TRY(tc_dW(c, dy16, ch, s.o16, ch, g->wo, rows, ch, ch, acc, side.stream()));
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
     if (attn_fwd_tc_supported(&b.fwd)) {
@@ -371,11 +450,13 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
         ex.dq16 = dqkv16; ex.dk16 = dqkv16 + ch; ex.dv16 = dqkv16 + 2 * ch;
         PIO_TRY(attn_bwd_simt(&b, c.st, &ex));
     }
-    PIO_TRY(colsum_bf16(dqkv16, 3 * ch, g->bq, acc, rows, 3 * ch, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(side.fork());
+    PIO_TRY(side_colsum(c, side, dqkv16, 3 * ch, g->bq, acc, rows, 3 * ch));
+    PIO_TRY(tc_dW(c, dqkv16, 3 * ch, s.h0, ch, g->wq, rows, 3 * ch, ch, acc, side.stream()));
     PIO_TRY(tc_dyW(c, dqkv16, 3 * ch, (const bf16*)w->wq, ch, rows, 3 * ch, ch, dh0, ch, nullptr, 0, 0, nullptr, 0, 0));
-    PIO_TRY(tc_dW(c, dqkv16, 3 * ch, s.h0, ch, g->wq, rows, 3 * ch, ch, acc));
     PIO_TRY(pio_layernorm_bwd(dh0, x, s.stats, w->ln_w, residual ? dy : nullptr, dx, g->ln_w, g->ln_b, acc, rows, ch, c.rest(),
                               c.rest_bytes(), c.st));
+    PIO_TRY(side.join());
     c.W.off = mark;
     return PIO_OK;
 }
