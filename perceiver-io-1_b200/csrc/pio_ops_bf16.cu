@@ -682,6 +682,11 @@ int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, 
     count_valid_kernel<<<1, 1024, 0, c.st>>>(labels, rows, classes, ignore, out3);
     PIO_LAUNCH_CHECK();
     PIO_TRY(cast_bf16(x, x16, rows, c_in, c_in, cip, c.st));
+    // dW / db accumulate with atomics on the side stream while the main stream forms dx for the same chunk
+    // (first chunk: the destinations are zeroed up front so every chunk can simply add)
+    PIO_CUDA(cudaMemsetAsync(dw, 0, (size_t)classes * c_in * sizeof(float), c.st));
+    PIO_CUDA(cudaMemsetAsync(db, 0, (size_t)classes * sizeof(float), c.st));
+    Side side(c, 2);
     for (int64_t r0 = 0; r0 < rows; r0 += ch) {
         const int64_t nr = std::min(ch, rows - r0);
         const bf16* xc = x16 + r0 * cip;
@@ -689,9 +694,11 @@ int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, 
         const int blocks = (int)std::min<int64_t>(nr, (int64_t)num_sms() * 8);
         ce_chunk_kernel<<<blocks, 256, 0, c.st>>>(logits, classes, labels + r0, out3, dl16, cop, row_loss + r0, nr, classes, ignore);
         PIO_LAUNCH_CHECK();
+        PIO_TRY(side.fork());
+        PIO_TRY(tc_dW(c, dl16, cop, xc, cip, dw, nr, classes, c_in, 2, side.stream()));
+        PIO_TRY(side_colsum(c, side, dl16, cop, db, 2, nr, (int)classes));
         PIO_TRY(tc_dyW(c, dl16, cop, (const bf16*)w16, cip, nr, classes, c_in, dx + r0 * c_in, c_in, nullptr, 0, 0, nullptr, 0, 0));
-        PIO_TRY(tc_dW(c, dl16, cop, xc, cip, dw, nr, classes, c_in, r0 > 0 ? 1 : 0));
-        PIO_TRY(colsum_bf16(dl16, cop, db, r0 > 0 ? 1 : 0, nr, (int)classes, c.rest(), c.rest_bytes(), c.st));
+        PIO_TRY(side.join());  // the next chunk overwrites dl16
     }
     loss_finalize_kernel<<<1, 1024, 0, c.st>>>(row_loss, rows, out3);
     PIO_LAUNCH_CHECK();
