@@ -95,6 +95,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     uint64_t* p_full = bars + 11;
     uint32_t* tmem_slot = (uint32_t*)(bars + 12);
 
+    pdl_trigger();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q0 = blockIdx.x * FA_BQ, h = blockIdx.y, b = blockIdx.z;
     const int T = (p.m + BKV - 1) / BKV;
@@ -120,6 +121,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // prologue done; everything below depends on earlier kernels' results
 
     if (warp == 0) {
         if (lane == 0) {
@@ -344,6 +346,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     uint64_t* dq_done = bars + 7;
     uint32_t* tmem_slot = (uint32_t*)(bars + 8);
 
+    pdl_trigger();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q0 = blockIdx.x * FA_BQ, h = blockIdx.y, b = blockIdx.z;
     const int T = (p.m + BKV - 1) / BKV;
@@ -362,6 +365,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // prologue done; everything below depends on earlier kernels' results
     const uint32_t tmem_s = tmem_base, tmem_dp = tmem_base + 64, tmem_dq = tmem_base + 128;
 
     if (warp == 0) {
@@ -522,6 +526,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     uint64_t* acc_done = bars + 7;
     uint32_t* tmem_slot = (uint32_t*)(bars + 8);
 
+    pdl_trigger();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int k0 = blockIdx.x * BK2, h = blockIdx.y, b = blockIdx.z;
     const int T = (p.n + BQ2 - 1) / BQ2;
@@ -540,6 +545,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // prologue done; everything below depends on earlier kernels' results
     const uint32_t tmem_st = tmem_base, tmem_dpt = tmem_base + 64, tmem_dv = tmem_base + 128, tmem_dk = tmem_base + 192;
 
     if (warp == 0) {
@@ -719,8 +725,8 @@ int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st) {
         configured = true;
     }
     dim3 grid((unsigned)cdiv(d->n, FA_BQ), (unsigned)d->heads, (unsigned)d->batch);
-    attn_fwd_tc_kernel<BKV><<<grid, FA_THREADS, smem, st>>>(tq, tk, tv, p);
-    PIO_LAUNCH_CHECK();
+    PIO_CUDA(launch_pdl(attn_fwd_tc_kernel<BKV>, grid, dim3(FA_THREADS), smem, st, tq, tk, tv, p));
+    count_launch();
     return PIO_OK;
 }
 
@@ -754,8 +760,8 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
         PIO_TRY(make_tmap3(&tk, d->k, cols, d->m, d->batch, d->k_rs, d->k_bs, 64));
         PIO_TRY(make_tmap3(&tv, d->v, cols, d->m, d->batch, d->v_rs, d->v_bs, 64));
         dim3 grid((unsigned)cdiv(d->n, FA_BQ), (unsigned)d->heads, (unsigned)d->batch);
-        attn_bwd_dq_tc_kernel<<<grid, FA_THREADS, smem_dq, st>>>(tq, tdo, tk, tv, p);
-        PIO_LAUNCH_CHECK();
+        PIO_CUDA(launch_pdl(attn_bwd_dq_tc_kernel, grid, dim3(FA_THREADS), smem_dq, st, tq, tdo, tk, tv, p));
+        count_launch();
     }
     {   // dK, dV: 128-row key tiles, 64-row query tiles
         CUtensorMap tq, tdo, tk, tv;
@@ -764,8 +770,8 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
         PIO_TRY(make_tmap3(&tk, d->k, cols, d->m, d->batch, d->k_rs, d->k_bs, 128));
         PIO_TRY(make_tmap3(&tv, d->v, cols, d->m, d->batch, d->v_rs, d->v_bs, 128));
         dim3 grid((unsigned)cdiv(d->m, 128), (unsigned)d->heads, (unsigned)d->batch);
-        attn_bwd_dkv_tc_kernel<<<grid, FA_THREADS, smem_dkv, st>>>(tq, tdo, tk, tv, p);
-        PIO_LAUNCH_CHECK();
+        PIO_CUDA(launch_pdl(attn_bwd_dkv_tc_kernel, grid, dim3(FA_THREADS), smem_dkv, st, tq, tdo, tk, tv, p));
+        count_launch();
     }
     return PIO_OK;
 }

@@ -7,6 +7,8 @@ namespace pio {
 __global__ void layernorm_fwd_bf16_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                           const float* __restrict__ b, __nv_bfloat16* __restrict__ y, int64_t ldy,
                                           float* __restrict__ stats, int64_t rows, int c, float eps) {
+    pdl_trigger();
+    pdl_wait();
     const int lane = threadIdx.x & 31;
     const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -38,8 +40,8 @@ int layernorm_fwd_bf16(const float* x, const float* w, const float* b, __nv_bflo
     if (rows == 0) return PIO_OK;
     const int threads = 256;
     const int blocks = (int)std::min<int64_t>(cdiv(rows, threads / 32), (int64_t)num_sms() * 16);
-    layernorm_fwd_bf16_kernel<<<blocks, threads, 0, st>>>(x, w, b, y, ldy, stats, rows, c, eps);
-    PIO_LAUNCH_CHECK();
+    PIO_CUDA(launch_pdl(layernorm_fwd_bf16_kernel, dim3(blocks), dim3(threads), 0, st, x, w, b, y, ldy, stats, rows, c, eps));
+    count_launch();
     return PIO_OK;
 }
 
@@ -50,6 +52,8 @@ __global__ void __launch_bounds__(256) colsum_partial_kernel(const TIn* __restri
                                                              float* __restrict__ partial, int64_t rows, int c,
                                                              int64_t rows_per_chunk, int pad_cols, float* __restrict__ atomic_out) {
     __shared__ float s_part[256];
+    pdl_trigger();
+    pdl_wait();
     const int col = blockIdx.x * 128 + (threadIdx.x & 127);
     const int sub = threadIdx.x >> 7;
     const int64_t r0 = (int64_t)blockIdx.y * rows_per_chunk;
@@ -101,9 +105,9 @@ static int colsum_impl(const TIn* src, int64_t ld_src, __nv_bfloat16* dst16, int
     }
     const int pad_cols = dst16 ? (int)ld_dst : c;
     dim3 grid((unsigned)cdiv(std::max(pad_cols, c), 128), (unsigned)chunks);
-    colsum_partial_kernel<TIn><<<grid, 256, 0, st>>>(src, ld_src, dst16, ld_dst, partial, rows, c, cdiv(rows, chunks), pad_cols,
-                                                     (colsum && atomic) ? colsum : nullptr);
-    PIO_LAUNCH_CHECK();
+    PIO_CUDA(launch_pdl(colsum_partial_kernel<TIn>, grid, dim3(256), 0, st, src, ld_src, dst16, ld_dst, partial, rows, c,
+                        cdiv(rows, chunks), pad_cols, (colsum && atomic) ? colsum : (float*)nullptr));
+    count_launch();
     if (colsum && !atomic) PIO_TRY(reduce_partials(partial, chunks, c, colsum, c, nullptr, 0, accumulate, st));
     return PIO_OK;
 }

@@ -71,6 +71,32 @@ struct Workspace {
     float* takef(size_t n) { return (float*)take(n * sizeof(float)); }
 };
 
+// Programmatic dependent launch (PDL).  A kernel launched through launch_pdl() may start while its
+// predecessor in the stream is still running; it must call pdl_wait() before it touches global memory
+// (the wait returns once every prerequisite grid has completed and its writes are visible).  Kernels call
+// pdl_trigger() first thing so their own successor can be scheduled early and get its prologue (barrier
+// init, TMEM allocation, descriptor prefetch, launch latency) out of the way.  Both are no-ops for a
+// kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -2,6 +2,7 @@
 // generator, text embedding fwd/bwd, MLM masking select/apply, LayerNorm fwd/bwd, partial
 // reductions, cross-entropy fwd/bwd.  All coalesced along the channel axis.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <atomic>
 #include <mutex>
 
@@ -20,6 +21,11 @@ void set_error(const char* fmt, ...) {
 
 static std::atomic<long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+bool pdl_enabled() {
+    static const bool on = getenv("PIO_NO_PDL") == nullptr;
+    return on;
+}
 
 int num_sms() {
     static int cached[64] = {0};
@@ -279,6 +285,8 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(
     float* __restrict__ partial, int64_t rows, int c, float* __restrict__ atomic_dw = nullptr,
     float* __restrict__ atomic_db = nullptr) {
     extern __shared__ float s_acc[];  // [warps][2][c]
+    pdl_trigger();
+    pdl_wait();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
     float gw[NCH], gb[NCH], wv[NCH];
 #pragma unroll
@@ -344,6 +352,8 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(
 __global__ void reduce_partials_kernel(const float* __restrict__ part, int splits, int64_t stride,
                                        float* __restrict__ out1, int64_t n1, float* __restrict__ out2,
                                        int64_t n2, int accumulate) {
+    pdl_trigger();
+    pdl_wait();
     const int64_t total = n1 + n2;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
          i += (int64_t)gridDim.x * blockDim.x) {
@@ -361,8 +371,8 @@ int reduce_partials(const float* part, int splits, int64_t stride, float* out1, 
     if (total <= 0) return PIO_OK;
     const int threads = 256;
     const int blocks = (int)std::min<int64_t>(cdiv(total, threads), (int64_t)num_sms() * 8);
-    reduce_partials_kernel<<<blocks, threads, 0, st>>>(part, splits, stride, out1, n1, out2, n2, accumulate);
-    PIO_LAUNCH_CHECK();
+    PIO_CUDA(launch_pdl(reduce_partials_kernel, dim3(blocks), dim3(threads), 0, st, part, splits, stride, out1, n1, out2, n2, accumulate));
+    count_launch();
     return PIO_OK;
 }
 
@@ -645,7 +655,8 @@ int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const
         if (smem > 48 * 1024)                                                                                   \
             PIO_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                           (int)smem));                                                          \
-        layernorm_bwd_kernel<NCH><<<blocks, 256, smem, st>>>(dy, x, stats, w, dres, dx, partial, rows, c, adw, adb); \
+        PIO_CUDA(launch_pdl(layernorm_bwd_kernel<NCH>, dim3(blocks), dim3(256), smem, st, dy, x, stats, w, dres, dx, partial, rows, c, adw, \
+                            adb));                                                                              \
     } while (0)
     if (c <= 128) PIO_LN_BWD(4);
     else if (c <= 256) PIO_LN_BWD(8);

@@ -212,6 +212,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
     uint64_t* tmem_full = empty_bar + TC_STAGES;
     uint32_t* tmem_slot = (uint32_t*)(tmem_full + 1);
 
+    pdl_trigger();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.y * TC_BM, n0 = blockIdx.x * BN;
     const int kb_begin = blockIdx.z * p.kb_per_split;
@@ -233,6 +234,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // prologue done; from here on the kernel reads / writes what earlier kernels produced
 
     if (warp == 0) {
         if (lane == 0) {
@@ -374,8 +376,8 @@ static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParam
         PIO_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = true;
     }
-    gemm_tc_kernel<BN, A_MN, B_MN><<<grid, TC_THREADS, smem, st>>>(ta, tb, p);
-    PIO_LAUNCH_CHECK();
+    PIO_CUDA(launch_pdl(gemm_tc_kernel<BN, A_MN, B_MN>, grid, dim3(TC_THREADS), smem, st, ta, tb, p));
+    count_launch();
     return PIO_OK;
 }
 
@@ -454,6 +456,8 @@ int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream
 // fp32 -> bf16 with a (possibly padded) destination pitch; pad columns are zero-filled
 __global__ void cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t rows, int cols,
                                  int64_t ld_src, int64_t ld_dst) {
+    pdl_trigger();
+    pdl_wait();
     const int64_t total = rows * ld_dst;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t r = i / ld_dst;
@@ -467,8 +471,9 @@ int cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_sr
     if (rows == 0) return PIO_OK;
     const int64_t total = rows * ld_dst;
     const int blocks = (int)std::min<int64_t>(cdiv(total, 256 * 4), (int64_t)num_sms() * 16);
-    cast_bf16_kernel<<<std::max(blocks, 1), 256, 0, st>>>(src, (__nv_bfloat16*)dst, rows, cols, ld_src, ld_dst);
-    PIO_LAUNCH_CHECK();
+    PIO_CUDA(launch_pdl(cast_bf16_kernel, dim3(std::max(blocks, 1)), dim3(256), 0, st, src, (__nv_bfloat16*)dst, rows, cols, ld_src,
+                        ld_dst));
+    count_launch();
     return PIO_OK;
 }
 
