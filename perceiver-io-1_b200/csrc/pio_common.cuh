@@ -76,11 +76,13 @@ struct Workspace {
 // (the wait returns once every prerequisite grid has completed and its writes are visible).  Kernels call
 // pdl_trigger() first thing so their own successor can be scheduled early and get its prologue (barrier
 // init, TMEM allocation, descriptor prefetch, launch latency) out of the way.  Both are no-ops for a
-// kernel launched the ordinary way.
+// kernel launched the ordinary way.  Measured on the cfg2 step: eager launches 9.57 -> 9.02 ms; inside a
+// captured graph the early-scheduled dependents only take SM resources from the side-stream branch
+// (7.58 -> 8.01 ms), so launches made while the stream is capturing do not use it.
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
-bool pdl_enabled();
+bool pdl_enabled(cudaStream_t st);
 
 template <typename... KArgs, typename... Args>
 static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
@@ -93,7 +95,7 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cfg.numAttrs = pdl_enabled(st) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 

@@ -22,9 +22,12 @@ void set_error(const char* fmt, ...) {
 static std::atomic<long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
-bool pdl_enabled() {
+bool pdl_enabled(cudaStream_t st) {
     static const bool on = getenv("PIO_NO_PDL") == nullptr;
-    return on;
+    if (!on) return false;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) return false;
+    return cs == cudaStreamCaptureStatusNone;
 }
 
 int num_sms() {
