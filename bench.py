@@ -268,6 +268,52 @@ def cross_attention_core_tflops(mode, pk):
             "ms": round(ms, 3), "tflops": round(tf, 2), "frac_of_bf16_peak": round(tf / pk["tflops"], 5)}
 
 
+def other_config_throughput(mode):
+    """Side numbers for the other BASELINE configs (eager, fwd + loss + bwd + AdamW, synthetic data):
+    config 1 MNIST-shaped image classifier (batch 128) and config 4 long-input stress (M = 16384, latent
+    (256,512), 8 cross heads, batch 32).  Reported, not the headline."""
+    import perceiver
+    from perceiver import (ClassificationOutputAdapter, ImageInputAdapter, PerceiverDecoder, PerceiverEncoder, PerceiverIO,
+                           TextInputAdapter)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    out = {}
+
+    def run(model, batch_fn, batch, steps=5, warm=2):
+        model = model.to(dev)
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-3, fused=True)
+        args, y = batch_fn()
+
+        def step():
+            loss = perceiver.cross_entropy(model(*args), y)
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
+        for _ in range(warm):
+            step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        e1.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        return {"ms_per_step": round(ms, 3), "samples_per_s": round(batch / (ms * 1e-3), 1)}
+
+    torch.manual_seed(0)
+    enc = PerceiverEncoder(ImageInputAdapter((28, 28, 1), 32), (32, 128), 3, 4, 4, 3)
+    dec = PerceiverDecoder(ClassificationOutputAdapter(10, num_output_channels=128), (32, 128), 1)
+    out["cfg1_mnist_b128"] = run(PerceiverIO(enc, dec),
+                                 lambda: ((torch.rand(128, 28, 28, 1, device=dev) * 2 - 1,), torch.randint(0, 10, (128,), device=dev)),
+                                 128)
+    enc = PerceiverEncoder(TextInputAdapter(10003, 16384, 512), (256, 512), 3, 8, 4, 6)
+    dec = PerceiverDecoder(ClassificationOutputAdapter(2, num_output_channels=512), (256, 512), 1)
+    out["cfg4_long_input_b32_m16384"] = run(
+        PerceiverIO(enc, dec),
+        lambda: ((torch.randint(3, 10003, (32, 16384), device=dev),), torch.randint(0, 2, (32,), device=dev)), 32, steps=3, warm=1)
+    return out
+
+
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
@@ -433,6 +479,10 @@ def gpu_arm(args):
             xattn = cross_attention_core_tflops(mode, pk)
         except Exception as ex:  # side metric must never sink the headline line
             xattn = {"error": str(ex)[:200]}
+        try:
+            others = other_config_throughput(mode)
+        except Exception as ex:
+            others = {"error": str(ex)[:200]}
         sample_b = 16
         cpu = cpu_reference_arm(steps=3, warmup=2, batch=sample_b) if world == 1 else None  # CPU baseline: N=1 only
         result = {
@@ -454,6 +504,7 @@ def gpu_arm(args):
             "gpu_launches": int(launches),
             "roofline": roof,
             "cross_attention_core": xattn,
+            "other_configs": others,
             "cpu_baseline": None if cpu is None else {
                 "value": round(cpu["samples_per_s"], 3), "unit": "samples/s", "cores": cpu["cores"], "kind": "port",
                 "sample": f"same step at batch {sample_b} (2 warm-up + 3 timed steps), oracle port of the "

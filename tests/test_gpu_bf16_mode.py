@@ -191,3 +191,19 @@ def test_mlm_return_loss_equals_logits_then_cross_entropy():
     num = sum(((p.grad - ga[k]).double().norm() ** 2).item() for k, p in model.named_parameters())
     den = sum((ga[k].double().norm() ** 2).item() for k in ga)
     assert (num / den) ** 0.5 < 1e-2
+
+
+def test_config4_long_input_shape_bf16():
+    """BASELINE configs[3] scaled down (M=2048, latent (256,512), 8 cross heads of 64 -> tcgen05 flash
+    kernels; 4 self heads of 128 and a 1-head decoder of 512 -> fp32-arithmetic kernels on bf16 operands)."""
+    from perceiver import ClassificationOutputAdapter, PerceiverDecoder, PerceiverEncoder, PerceiverIO, TextInputAdapter
+    torch.manual_seed(2)
+    enc = PerceiverEncoder(TextInputAdapter(10003, 2048, 512), (256, 512), 2, 8, 4, 2)
+    dec = PerceiverDecoder(ClassificationOutputAdapter(2, num_output_channels=512), (256, 512), 1)
+    b = 2
+    ids = torch.randint(3, 10003, (b, 2048))
+    pad = torch.arange(2048)[None, :] >= torch.tensor([2048, 1500])[:, None]
+    ids[pad] = 0
+    y = torch.randint(0, 2, (b,))
+    _vs_oracle("text", PerceiverIO(enc, dec), ids, pad, y,
+               dict(num_layers=2, cross_heads=8, self_heads=4, sa_layers=2, dec_heads=1))
