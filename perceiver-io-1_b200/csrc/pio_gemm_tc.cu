@@ -12,6 +12,7 @@
 // every product of the forward and backward pass reads its operands where they already lie.
 // Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..5 = epilogue.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include <mutex>
 
@@ -354,7 +355,9 @@ int make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t col
 
 static void tc_choose(int64_t m, int64_t n, int64_t k, bool splittable, int* bn, int* splits, int* kb_per) {
     const int sms = num_sms();
-    *bn = (n <= 64) ? 64 : 128;
+    // 64-wide tiles when 128-wide ones would leave most SMs idle (the latent GEMMs: 4096 x 256 outputs)
+    static const bool narrow = getenv("PIO_TC_NO_NARROW") == nullptr;
+    *bn = (n <= 64 || (narrow && cdiv(m, TC_BM) * cdiv(n, 128) < sms / 2)) ? 64 : 128;
     const int64_t tiles = cdiv(m, TC_BM) * cdiv(n, *bn);
     const int num_kb = (int)cdiv(k, TC_BK);
     int s = 1;
