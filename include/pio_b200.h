@@ -134,6 +134,8 @@ typedef struct {
     int act;
     int accumulate;
     float* rowsum_a;
+    float dropout_p;       /* Residual's dropout (model.py:51,56): applied to the value before `+ residual` */
+    uint64_t dropout_seed; /* element (m, n) is kept iff hash(seed, m*n_cols + n) >= p * 2^32, scaled by 1/(1-p) */
 } pio_gemm_desc;
 int pio_gemm_f32(const pio_gemm_desc* d, void* ws, size_t ws_bytes, pio_stream_t stream);
 size_t pio_gemm_f32_ws_bytes(int64_t m, int64_t n, int64_t k);
@@ -159,6 +161,8 @@ typedef struct {
     int64_t ldaux;
     int act;
     int accumulate;
+    float dropout_p;       /* as in pio_gemm_desc */
+    uint64_t dropout_seed;
 } pio_gemm_bf16_desc;
 int pio_gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, pio_stream_t stream);
 size_t pio_gemm_bf16_ws_bytes(int64_t m, int64_t n, int64_t k);
@@ -219,6 +223,19 @@ int pio_cross_entropy_bwd(const float* logits, const int64_t* labels, const floa
  * Fused operators (one call per reference module)
  * ---------------------------------------------------------------------------------------- */
 
+/* Dropout of the reference's training mode (nn.MultiheadAttention(dropout=p) on the attention
+ * probabilities, model.py:70; Residual's nn.Dropout on the branch output, model.py:51,56).  NULL or
+ * p == 0 = off.  Masks are a counter-based hash of (seed, element index): the backward call must get
+ * the same struct as the forward call it differentiates; nothing is stored.  Each operator derives its
+ * sites from `seed` (seed+0 attention probabilities, seed+1 residual; the latent block uses seed+4*layer
+ * for the attention layer and seed+4*layer+2 for the MLP).  With attention dropout active the bf16
+ * pipelines use the fp32-arithmetic attention kernels (the tensor-core ones carry no mask yet).
+ * torch's own Philox stream cannot be reproduced, so parity with the reference at p > 0 is statistical. */
+typedef struct {
+    float p;
+    uint64_t seed;
+} pio_dropout;
+
 /* Residual(mlp(C)), model.py:20-26,47-56: y = Linear2(GELU(Linear1(LN(x)))) + x.
  * `residual` = 0 gives the bare module (mlp / CrossAttention / SelfAttention .forward) without
  * the `+ x` of Residual.forward (model.py:54-56); same flag on the attention operators below. */
@@ -231,10 +248,10 @@ typedef struct {
 size_t pio_mlp_saved_bytes(int64_t rows, int c, int mode);
 size_t pio_mlp_ws_bytes(int64_t rows, int c, int mode);
 int pio_mlp_fwd(const float* x, float* y, const pio_mlp_weights* w, void* saved, int64_t rows, int c,
-                int residual, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+                int residual, const pio_dropout* drop, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
 int pio_mlp_bwd(const float* dy, const float* x, float* dx, const pio_mlp_weights* w, const void* saved,
-                const pio_mlp_grads* g, int accumulate, int64_t rows, int c, int residual, int mode,
-                void* ws, size_t ws_bytes, pio_stream_t stream);
+                const pio_mlp_grads* g, int accumulate, int64_t rows, int c, int residual,
+                const pio_dropout* drop, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
 
 /* Attention weights as torch.nn.MultiheadAttention stores them (model.py:66-71): wq (E,E),
  * wk / wv (E,C_kv); they may alias one packed (3E,E) in_proj_weight.  Biases likewise. */
@@ -274,33 +291,37 @@ size_t pio_cross_attend_saved_bytes(int batch, int n, int m, int e, int heads, i
 size_t pio_cross_attend_ws_bytes(int batch, int n, int m, int e, int heads, int mode);
 int pio_cross_attend_fwd(const float* x_q, const float* kv, const uint8_t* pad, float* y,
                          const pio_attn_weights* w, void* saved, int batch, int n, int m, int e,
-                         int heads, int residual, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+                         int heads, int residual, const pio_dropout* drop, int mode, void* ws, size_t ws_bytes,
+                         pio_stream_t stream);
 int pio_cross_attend_bwd(const float* dy, const float* x_q, const float* kv, const uint8_t* pad,
                          float* dx_q, float* dkv, const pio_attn_weights* w, const void* saved,
                          const pio_attn_grads* g, int accumulate, int batch, int n, int m, int e,
-                         int heads, int residual, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+                         int heads, int residual, const pio_dropout* drop, int mode, void* ws, size_t ws_bytes,
+                         pio_stream_t stream);
 
 /* Residual(SelfAttention), model.py:102-116 + :54-56, one layer: y = out_proj(attn(qkv(LN(x)))) + x. */
 size_t pio_self_attn_saved_bytes(int batch, int n, int c, int heads, int mode);
 size_t pio_self_attn_ws_bytes(int batch, int n, int c, int heads, int mode);
 int pio_self_attn_fwd(const float* x, float* y, const pio_attn_weights* w, void* saved, int batch, int n,
-                      int c, int heads, int residual, int mode, void* ws, size_t ws_bytes,
-                      pio_stream_t stream);
+                      int c, int heads, int residual, const pio_dropout* drop, int mode, void* ws,
+                      size_t ws_bytes, pio_stream_t stream);
 int pio_self_attn_bwd(const float* dy, const float* x, float* dx, const pio_attn_weights* w,
                       const void* saved, const pio_attn_grads* g, int accumulate, int batch, int n, int c,
-                      int heads, int residual, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+                      int heads, int residual, const pio_dropout* drop, int mode, void* ws, size_t ws_bytes,
+                      pio_stream_t stream);
 
 /* self_attention_block, model.py:36-44,102-116: `layers` x [Residual(SelfAttention) ->
  * Residual(mlp)] applied to x (batch,n,c).  `attn`/`mlp` are arrays of `layers` structs. */
 size_t pio_latent_block_saved_bytes(int layers, int batch, int n, int c, int heads, int mode);
 size_t pio_latent_block_ws_bytes(int layers, int batch, int n, int c, int heads, int mode);
 int pio_latent_block_fwd(const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp,
-                         void* saved, int layers, int batch, int n, int c, int heads, int mode,
-                         void* ws, size_t ws_bytes, pio_stream_t stream);
+                         void* saved, int layers, int batch, int n, int c, int heads, const pio_dropout* drop,
+                         int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
 int pio_latent_block_bwd(const float* dy, const float* x, float* dx, const pio_attn_weights* attn,
                          const pio_mlp_weights* mlp, const void* saved, const pio_attn_grads* attn_g,
                          const pio_mlp_grads* mlp_g, int accumulate, int layers, int batch, int n, int c,
-                         int heads, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
+                         int heads, const pio_dropout* drop, int mode, void* ws, size_t ws_bytes,
+                         pio_stream_t stream);
 
 /* nn.Linear of Classification/TextOutputAdapter, adapter.py:146-149: y = x W^T + b. */
 size_t pio_linear_ws_bytes(int64_t rows, int c_in, int64_t c_out, int mode);

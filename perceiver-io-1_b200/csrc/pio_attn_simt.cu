@@ -23,6 +23,7 @@ struct AttnP {
     int batch, heads, n, m, dh;
     float scale;
     int in16;  // q, k, v are bf16 (same element strides) instead of fp32
+    DropCfg drop;  // dropout on the attention probabilities (nn.MultiheadAttention(dropout=p)); threshold 0 = off
 };
 
 __device__ __forceinline__ float load_in(const void* base, int64_t idx, bool in16) {
@@ -131,6 +132,10 @@ __global__ void __launch_bounds__(AT_THREADS) attn_fwd_kernel(const AttnP p) {
             m_run[i] = m_new;
 #pragma unroll
             for (int c = 0; c < NCH; ++c) acc[i][c] *= alpha;
+            if (p.drop.threshold != 0) {  // the softmax normalisation sees every key; only P.V sees the mask
+                const uint64_t idx = (((uint64_t)b * p.heads + h) * p.n + (q0 + wid * AT_RPW + i)) * (uint64_t)p.m + j;
+                pv = drop_keep(p.drop, idx) ? pv * p.drop.inv_keep : 0.f;
+            }
             pr[i] = pv;
         }
         *reinterpret_cast<float4*>(Pw + lane * 4) = make_float4(pr[0], pr[1], pr[2], pr[3]);
@@ -231,7 +236,12 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_dq_kernel(const AttnP p) 
 #pragma unroll
         for (int i = 0; i < AT_RPW; ++i) {
             const float pv = dead ? 0.f : expf(s[i] * p.scale - lse[i]);
-            ds[i] = pv * (dp[i] - delta[i]) * p.scale;
+            float dpi = dp[i];
+            if (p.drop.threshold != 0) {
+                const uint64_t idx = (((uint64_t)b * p.heads + h) * p.n + (q0 + wid * AT_RPW + i)) * (uint64_t)p.m + j;
+                dpi = drop_keep(p.drop, idx) ? dpi * p.drop.inv_keep : 0.f;
+            }
+            ds[i] = pv * (dpi - delta[i]) * p.scale;
         }
         *reinterpret_cast<float4*>(dSw + lane * 4) = make_float4(ds[0], ds[1], ds[2], ds[3]);
         __syncwarp();
@@ -334,8 +344,13 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_dkv_kernel(const AttnP p)
 #pragma unroll
         for (int i = 0; i < AT_RPW; ++i) {
             const float pv = (qdead || kdead[i]) ? 0.f : expf(s[i] * p.scale - lse);
-            pr[i] = pv;
-            ds[i] = pv * (dp[i] - del) * p.scale;
+            float keep_scale = 1.f;
+            if (p.drop.threshold != 0) {
+                const uint64_t idx = (((uint64_t)b * p.heads + h) * p.n + (i0 + lane)) * (uint64_t)p.m + (k0 + wid * AT_RPW + i);
+                keep_scale = drop_keep(p.drop, idx) ? p.drop.inv_keep : 0.f;
+            }
+            pr[i] = pv * keep_scale;
+            ds[i] = pv * (dp[i] * keep_scale - del) * p.scale;
         }
         *reinterpret_cast<float4*>(Pw + lane * 4) = make_float4(pr[0], pr[1], pr[2], pr[3]);
         *reinterpret_cast<float4*>(dSw + lane * 4) = make_float4(ds[0], ds[1], ds[2], ds[3]);
@@ -424,6 +439,7 @@ int attn_fwd_simt(const pio_attn_desc* d, cudaStream_t st, const AttnBf16Out* ex
     if (extra) {
         p.out16 = extra->o16;
         p.in16 = extra->in16;
+        p.drop = extra->drop;
     }
     dim3 grid((unsigned)cdiv(d->n, AT_ROWS), (unsigned)d->heads, (unsigned)d->batch);
     int rc = PIO_OK;
@@ -445,6 +461,7 @@ int attn_bwd_simt(const pio_attn_bwd_desc* bd, cudaStream_t st, const AttnBf16Ou
     p.d_o = bd->d_o;
     p.dq = bd->dq; p.dk = bd->dk; p.dv = bd->dv; p.delta = bd->delta;
     if (extra) {
+        p.drop = extra->drop;
         p.in16 = extra->in16;
         p.dq16 = extra->dq16;
         p.dk16 = extra->dk16;

@@ -110,6 +110,39 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
+// Counter-based dropout: element `idx` of dropout site `seed` is kept iff hash >= threshold, so the
+// forward and the backward kernels regenerate the same mask from (seed, index) without storing it.
+struct DropCfg {
+    uint64_t seed;
+    uint32_t threshold;  // p * 2^32 ; 0 = dropout off
+    float inv_keep;      // 1 / (1 - p)
+};
+static inline DropCfg make_drop(float p, uint64_t seed) {
+    DropCfg d;
+    d.seed = seed;
+    if (!(p > 0.f)) {
+        d.threshold = 0;
+        d.inv_keep = 1.f;
+    } else {
+        const double t = (double)p * 4294967296.0;
+        d.threshold = t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
+        d.inv_keep = 1.0f / (1.0f - p);
+    }
+    return d;
+}
+__device__ __forceinline__ bool drop_keep(const DropCfg& d, uint64_t idx) {
+    uint64_t z = (idx + d.seed) * 0x9E3779B97F4A7C15ull;
+    z ^= z >> 32;
+    z *= 0xD6E8FEB86659FD93ull;
+    z ^= z >> 32;
+    z *= 0xD6E8FEB86659FD93ull;
+    z ^= z >> 32;
+    return (uint32_t)z >= d.threshold;
+}
+
+// out = dropout-mask(in): gradient of a dropout site w.r.t. its input (same mask as the forward)
+int dropout_mask(const float* in, float* out, int64_t n, const DropCfg& d, cudaStream_t st);
+
 __device__ __forceinline__ float gelu_erf(float x) {
     return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
 }

@@ -379,6 +379,20 @@ int reduce_partials(const float* part, int splits, int64_t stride, float* out1, 
     return PIO_OK;
 }
 
+// out[i] = keep(i) ? in[i] / (1-p) : 0 — the gradient of Residual's dropout w.r.t. its branch
+__global__ void dropout_mask_kernel(const float* __restrict__ in, float* __restrict__ out, int64_t n, DropCfg d) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = drop_keep(d, (uint64_t)i) ? in[i] * d.inv_keep : 0.f;
+}
+
+int dropout_mask(const float* in, float* out, int64_t n, const DropCfg& d, cudaStream_t st) {
+    if (n <= 0) return PIO_OK;
+    const int blocks = (int)std::min<int64_t>(cdiv(n, 256), (int64_t)num_sms() * 16);
+    dropout_mask_kernel<<<blocks, 256, 0, st>>>(in, out, n, d);
+    PIO_LAUNCH_CHECK();
+    return PIO_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // cross entropy
 // ---------------------------------------------------------------------------------------------

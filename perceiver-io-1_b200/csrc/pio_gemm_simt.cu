@@ -29,6 +29,7 @@ struct GemmParams {
     int64_t k_per_split;
     float* partial;          // [splits][m*n + (rowsum ? m : 0)]
     int64_t partial_stride;
+    DropCfg drop;            // dropout on the value before the residual add
 };
 
 template <bool KMAJOR, int BMN>
@@ -176,6 +177,7 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_f32_kernel(const GemmParams
             } else if (g.act == 2) {
                 v *= gelu_erf_grad(g.aux[m * g.ldaux + n]);
             }
+            if (g.drop.threshold != 0) v = drop_keep(g.drop, (uint64_t)m * (uint64_t)g.n + (uint64_t)n) ? v * g.drop.inv_keep : 0.f;
             if (g.residual) v += g.residual[m * g.ldr + n];
             float* dst = g.c + m * g.ldc + n;
             if (g.accumulate) v += *dst;
@@ -235,8 +237,9 @@ int pio_gemm_f32(const pio_gemm_desc* d, void* ws, size_t ws_bytes, pio_stream_t
     g.bias = d->bias; g.residual = d->residual; g.ldr = d->ldr;
     g.aux = d->aux; g.ldaux = d->ldaux; g.act = d->act; g.accumulate = d->accumulate;
     g.rowsum_a = d->rowsum_a;
+    g.drop = make_drop(d->dropout_p, d->dropout_seed);
 
-    const bool splittable = !d->bias && !d->residual && d->act == 0 && d->ldc == d->n;
+    const bool splittable = !d->bias && !d->residual && d->act == 0 && d->ldc == d->n && !(d->dropout_p > 0.f);
     int splits;
     int64_t kp;
     bool small;

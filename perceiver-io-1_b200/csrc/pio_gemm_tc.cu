@@ -42,6 +42,7 @@ struct TcParams {
     float* partial;
     int64_t partial_stride;
     int epi_kind;
+    DropCfg drop;  // dropout on the value before the residual add (generic epilogue only)
 };
 
 // Epilogue flavours, resolved on the host so the row loop below carries no run-time flag tests
@@ -177,6 +178,11 @@ __device__ __forceinline__ void epilogue_rows(const TcParams& p, const float* st
                 load4_b16(p.aux16 + gm * p.ldaux + n, a, vaux, valid);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) v[j] *= gelu_erf_grad(a[j]);
+            }
+            if (p.drop.threshold != 0) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    v[j] = drop_keep(p.drop, (uint64_t)gm * (uint64_t)p.N + (uint64_t)(n + j)) ? v[j] * p.drop.inv_keep : 0.f;
             }
             if (p.residual) {
                 float r[4];
@@ -391,7 +397,8 @@ int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream
     PIO_CHECK_ARG(d->m < (1ll << 31) && d->n < (1ll << 31) && d->k < (1ll << 31), "pio_gemm_bf16: dims exceed 2^31");
     if (d->m == 0 || d->n == 0) return PIO_OK;
     const bool a_mn = !d->a_kmajor, b_mn = !d->b_kmajor;
-    const bool splittable = !d->bias && !d->residual && d->act == 0 && d->c32 && !d->c16 && d->ldc32 == d->n;
+    const bool dropping = d->dropout_p > 0.f;
+    const bool splittable = !d->bias && !d->residual && d->act == 0 && d->c32 && !d->c16 && d->ldc32 == d->n && !dropping;
     int bn, splits, kb_per;
     tc_choose(d->m, d->n, d->k, splittable, &bn, &splits, &kb_per);
 
@@ -403,6 +410,7 @@ int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream
     p.bias = d->bias; p.residual = d->residual; p.ldr = d->ldr;
     p.aux16 = (__nv_bfloat16*)d->aux16; p.ldaux = d->ldaux;
     p.act = d->act; p.accumulate = d->accumulate;
+    p.drop = make_drop(d->dropout_p, d->dropout_seed);
     p.partial_stride = d->m * d->n;
     const bool atomic = (d->accumulate == 2);
     if (atomic) PIO_CHECK_ARG(splittable, "pio_gemm_bf16: accumulate=2 (atomic) needs a plain fp32 output without epilogue");
@@ -421,6 +429,7 @@ int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream
         int kind = EPI_GENERIC;
         if (atomic) kind = EPI_F32_ATOMIC;
         else if (splits > 1) kind = EPI_PARTIAL;
+        else if (dropping) kind = EPI_GENERIC;
         else if (o32 && !o16 && d->act == 0 && !d->residual && !d->accumulate) kind = EPI_F32;
         else if (o32 && !o16 && d->act == 0 && d->residual && !d->accumulate) kind = EPI_F32_RES;
         else if (o32 && !o16 && d->act == 0 && !d->residual && d->accumulate) kind = EPI_F32_ACC;

@@ -11,8 +11,9 @@ namespace {
 // y[rows, n] = act(x[rows,k] W[n,k]^T + bias) (+ residual)
 int gemm_xwT(Ctx& c, const float* x, int64_t ldx, const float* w, int64_t ldw, float* y, int64_t ldy, int64_t rows,
              int64_t n, int64_t k, const float* bias, const float* residual, int64_t ldr, int act, float* aux,
-             int64_t ldaux, int accumulate = 0) {
+             int64_t ldaux, int accumulate = 0, float drop_p = 0.f, uint64_t drop_seed = 0) {
     pio_gemm_desc d{};
+    d.dropout_p = drop_p; d.dropout_seed = drop_seed;
     d.a = x; d.b = w; d.c = y;
     d.m = rows; d.n = n; d.k = k;
     d.lda = ldx; d.ldb = ldw; d.ldc = ldy;
@@ -49,6 +50,20 @@ int gemm_dW(Ctx& c, const float* dy, int64_t lddy, const float* x, int64_t ldx, 
 
 size_t dW_scratch(int64_t nout, int64_t kin, int64_t rows) { return pio_gemm_f32_ws_bytes(nout, kin, rows); }
 
+// gradient entering the branch of a Residual with dropout: dy masked like the forward output was
+int branch_grad(Ctx& c, const float* dy, int64_t count, int residual, const float** out, const char* who) {
+    *out = dy;
+    if (!(residual && c.drop_p > 0.f)) return PIO_OK;
+    float* tmp = c.W.takef((size_t)count);
+    if (!tmp) {
+        set_error("%s: workspace too small (%zu bytes given)", who, c.W.size);
+        return PIO_ERR_WORKSPACE;
+    }
+    PIO_TRY(dropout_mask(dy, tmp, count, c.res_drop(residual), c.st));
+    *out = tmp;
+    return PIO_OK;
+}
+
 // ---------------------------------------------------------------- mlp
 struct MlpSaved {
     float *stats, *h0, *h1, *g;
@@ -69,12 +84,13 @@ int mlp_fwd(Ctx& c, const float* x, float* y, const pio_mlp_weights* w, void* sa
     MlpSaved s(saved, rows, ch);
     PIO_TRY(pio_layernorm_fwd(x, w->ln_w, w->ln_b, s.h0, s.stats, rows, ch, LN_EPS, c.st));
     PIO_TRY(gemm_xwT(c, s.h0, ch, w->w1, ch, s.g, ch, rows, ch, ch, w->b1, nullptr, 0, 1, s.h1, ch));
-    PIO_TRY(gemm_xwT(c, s.g, ch, w->w2, ch, y, ch, rows, ch, ch, w->b2, residual ? x : nullptr, ch, 0, nullptr, 0));
+    PIO_TRY(gemm_xwT(c, s.g, ch, w->w2, ch, y, ch, rows, ch, ch, w->b2, residual ? x : nullptr, ch, 0, nullptr, 0, 0,
+                     residual ? c.drop_p : 0.f, c.drop_seed + 1));
     return PIO_OK;
 }
 
 size_t mlp_bwd_ws(int64_t rows, int ch) {
-    return 2 * align_up((size_t)rows * ch * 4, 256) + pio_layernorm_bwd_ws_bytes(rows, ch) + dW_scratch(ch, ch, rows) + 1024;
+    return 3 * align_up((size_t)rows * ch * 4, 256) + pio_layernorm_bwd_ws_bytes(rows, ch) + dW_scratch(ch, ch, rows) + 1024;
 }
 
 int mlp_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_mlp_weights* w, const void* saved,
@@ -83,8 +99,10 @@ int mlp_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_mlp_we
     const size_t mark = c.W.off;
     PIO_TAKE(dh1, c, (size_t)rows * ch, "pio_mlp_bwd");
     PIO_TAKE(dh0, c, (size_t)rows * ch, "pio_mlp_bwd");
-    PIO_TRY(gemm_dyW(c, dy, ch, w->w2, ch, dh1, ch, rows, ch, ch, 2, s.h1, ch, 0));
-    PIO_TRY(gemm_dW(c, dy, ch, s.g, ch, g->w2, g->b2, rows, ch, ch, acc));
+    const float* dyb;
+    PIO_TRY(branch_grad(c, dy, rows * ch, residual, &dyb, "pio_mlp_bwd"));
+    PIO_TRY(gemm_dyW(c, dyb, ch, w->w2, ch, dh1, ch, rows, ch, ch, 2, s.h1, ch, 0));
+    PIO_TRY(gemm_dW(c, dyb, ch, s.g, ch, g->w2, g->b2, rows, ch, ch, acc));
     PIO_TRY(gemm_dyW(c, dh1, ch, w->w1, ch, dh0, ch, rows, ch, ch, 0, nullptr, 0, 0));
     PIO_TRY(gemm_dW(c, dh1, ch, s.h0, ch, g->w1, g->b1, rows, ch, ch, acc));
     PIO_TRY(pio_layernorm_bwd(dh0, x, s.stats, w->ln_w, residual ? dy : nullptr, dx, g->ln_w, g->ln_b, acc, rows, ch,
@@ -188,14 +206,17 @@ int cross_attend_fwd(Ctx& c, const float* x_q, const float* kv, const uint8_t* p
     PIO_TRY(gemm_xwT(c, s.hq, e, w->wq, e, s.q, e, rows, e, e, w->bq, nullptr, 0, 0, nullptr, 0));
     pio_attn_desc a{};
     fill_attn(a, s.q, e, kv, kv + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
-    PIO_TRY(attn_fwd_simt(&a, c.st));
-    PIO_TRY(gemm_xwT(c, s.o, e, w->wo, e, y, e, rows, e, e, w->bo, residual ? x_q : nullptr, e, 0, nullptr, 0));
+    AttnBf16Out ex;
+    ex.drop = c.attn_drop();
+    PIO_TRY(attn_fwd_simt(&a, c.st, &ex));
+    PIO_TRY(gemm_xwT(c, s.o, e, w->wo, e, y, e, rows, e, e, w->bo, residual ? x_q : nullptr, e, 0, nullptr, 0, 0,
+                     residual ? c.drop_p : 0.f, c.drop_seed + 1));
     return PIO_OK;
 }
 
 size_t cross_attend_bwd_ws(int batch, int n, int e, int heads) {
     const size_t r = (size_t)batch * n;
-    return 3 * align_up(r * e * 4, 256) + align_up((size_t)batch * heads * n * 4, 256) +
+    return 4 * align_up(r * e * 4, 256) + align_up((size_t)batch * heads * n * 4, 256) +
            pio_layernorm_bwd_ws_bytes(r, e) + dW_scratch(e, e, r) + 1024;
 }
 
@@ -209,12 +230,16 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
     PIO_TAKE(dq, c, (size_t)rows * e, "pio_cross_attend_bwd");
     PIO_TAKE(dhq, c, (size_t)rows * e, "pio_cross_attend_bwd");
     PIO_TAKE(delta, c, (size_t)batch * heads * n, "pio_cross_attend_bwd");
-    PIO_TRY(gemm_dyW(c, dy, e, w->wo, e, d_o, e, rows, e, e, 0, nullptr, 0, 0));
-    PIO_TRY(gemm_dW(c, dy, e, s.o, e, g->wo, g->bo, rows, e, e, acc));
+    const float* dyb;
+    PIO_TRY(branch_grad(c, dy, rows * e, residual, &dyb, "pio_cross_attend_bwd"));
+    PIO_TRY(gemm_dyW(c, dyb, e, w->wo, e, d_o, e, rows, e, e, 0, nullptr, 0, 0));
+    PIO_TRY(gemm_dW(c, dyb, e, s.o, e, g->wo, g->bo, rows, e, e, acc));
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.q, e, kv, kv + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
     b.d_o = d_o; b.dq = dq; b.dk = dkv; b.dv = dkv + e; b.delta = delta;
-    PIO_TRY(attn_bwd_simt(&b, c.st));
+    AttnBf16Out exb;
+    exb.drop = c.attn_drop();
+    PIO_TRY(attn_bwd_simt(&b, c.st, &exb));
     PIO_TRY(gemm_dyW(c, dq, e, w->wq, e, dhq, e, rows, e, e, 0, nullptr, 0, 0));
     PIO_TRY(gemm_dW(c, dq, e, s.hq, e, g->wq, g->bq, rows, e, e, acc));
     PIO_TRY(pio_layernorm_bwd(dhq, x_q, s.stats, w->ln_w, residual ? dy : nullptr, dx_q, g->ln_w, g->ln_b, acc, rows, e,
@@ -260,14 +285,17 @@ int self_attn_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* w, v
     }
     pio_attn_desc a{};
     fill_attn(a, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
-    PIO_TRY(attn_fwd_simt(&a, c.st));
-    PIO_TRY(gemm_xwT(c, s.o, ch, w->wo, ch, y, ch, rows, ch, ch, w->bo, residual ? x : nullptr, ch, 0, nullptr, 0));
+    AttnBf16Out ex;
+    ex.drop = c.attn_drop();
+    PIO_TRY(attn_fwd_simt(&a, c.st, &ex));
+    PIO_TRY(gemm_xwT(c, s.o, ch, w->wo, ch, y, ch, rows, ch, ch, w->bo, residual ? x : nullptr, ch, 0, nullptr, 0, 0,
+                     residual ? c.drop_p : 0.f, c.drop_seed + 1));
     return PIO_OK;
 }
 
 size_t self_attn_bwd_ws(int batch, int n, int ch, int heads) {
     const size_t r = (size_t)batch * n;
-    return 2 * align_up(r * ch * 4, 256) + align_up(3 * r * ch * 4, 256) + align_up((size_t)batch * heads * n * 4, 256) +
+    return 3 * align_up(r * ch * 4, 256) + align_up(3 * r * ch * 4, 256) + align_up((size_t)batch * heads * n * 4, 256) +
            pio_layernorm_bwd_ws_bytes(r, ch) + dW_scratch(3 * ch, ch, r) + 1024;
 }
 
@@ -280,12 +308,16 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
     PIO_TAKE(dqkv, c, (size_t)rows * 3 * ch, "pio_self_attn_bwd");
     PIO_TAKE(dh0, c, (size_t)rows * ch, "pio_self_attn_bwd");
     PIO_TAKE(delta, c, (size_t)batch * heads * n, "pio_self_attn_bwd");
-    PIO_TRY(gemm_dyW(c, dy, ch, w->wo, ch, d_o, ch, rows, ch, ch, 0, nullptr, 0, 0));
-    PIO_TRY(gemm_dW(c, dy, ch, s.o, ch, g->wo, g->bo, rows, ch, ch, acc));
+    const float* dyb;
+    PIO_TRY(branch_grad(c, dy, rows * ch, residual, &dyb, "pio_self_attn_bwd"));
+    PIO_TRY(gemm_dyW(c, dyb, ch, w->wo, ch, d_o, ch, rows, ch, ch, 0, nullptr, 0, 0));
+    PIO_TRY(gemm_dW(c, dyb, ch, s.o, ch, g->wo, g->bo, rows, ch, ch, acc));
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
     b.d_o = d_o; b.dq = dqkv; b.dk = dqkv + ch; b.dv = dqkv + 2 * ch; b.delta = delta;
-    PIO_TRY(attn_bwd_simt(&b, c.st));
+    AttnBf16Out exb;
+    exb.drop = c.attn_drop();
+    PIO_TRY(attn_bwd_simt(&b, c.st, &exb));
     const bool wpk = qkv_packed(w->wq, w->wk, w->wv, w->bq, w->bk, w->bv, ch);
     const bool gpk = qkv_packed(g->wq, g->wk, g->wv, g->bq, g->bk, g->bv, ch);
     if (wpk) {
@@ -345,20 +377,20 @@ size_t pio_mlp_saved_bytes(int64_t rows, int c, int mode) {
 size_t pio_mlp_ws_bytes(int64_t rows, int c, int mode) { return mode == PIO_MODE_BF16 ? bf::mlp_ws_bytes(rows, c) : mlp_bwd_ws(rows, c); }
 
 int pio_mlp_fwd(const float* x, float* y, const pio_mlp_weights* w, void* saved, int64_t rows, int c, int residual,
-                int mode, void* ws, size_t ws_bytes, pio_stream_t stream) {
+                const pio_dropout* drop, int mode, void* ws, size_t ws_bytes, pio_stream_t stream) {
     PIO_TRY(check_mode(mode, "pio_mlp_fwd"));
     PIO_CHECK_ARG(x && y && w && saved && rows >= 0 && c > 0, "pio_mlp_fwd: bad arguments");
-    Ctx ctx(ws, ws_bytes, stream);
+    Ctx ctx(ws, ws_bytes, stream, drop);
     if (mode == PIO_MODE_BF16) return bf::mlp_fwd(ctx, x, y, w, saved, rows, c, residual);
     return mlp_fwd(ctx, x, y, w, saved, rows, c, residual);
 }
 
 int pio_mlp_bwd(const float* dy, const float* x, float* dx, const pio_mlp_weights* w, const void* saved,
-                const pio_mlp_grads* g, int accumulate, int64_t rows, int c, int residual, int mode, void* ws,
-                size_t ws_bytes, pio_stream_t stream) {
+                const pio_mlp_grads* g, int accumulate, int64_t rows, int c, int residual, const pio_dropout* drop, int mode,
+                void* ws, size_t ws_bytes, pio_stream_t stream) {
     PIO_TRY(check_mode(mode, "pio_mlp_bwd"));
     PIO_CHECK_ARG(dy && x && dx && w && saved && g && rows >= 0 && c > 0, "pio_mlp_bwd: bad arguments");
-    Ctx ctx(ws, ws_bytes, stream);
+    Ctx ctx(ws, ws_bytes, stream, drop);
     if (mode == PIO_MODE_BF16) return bf::mlp_bwd(ctx, dy, x, dx, w, saved, g, accumulate, rows, c, residual);
     return mlp_bwd(ctx, dy, x, dx, w, saved, g, accumulate, rows, c, residual);
 }
@@ -409,24 +441,24 @@ static int check_heads(int e, int heads, const char* who) {
 }
 
 int pio_cross_attend_fwd(const float* x_q, const float* kv, const uint8_t* pad, float* y, const pio_attn_weights* w,
-                         void* saved, int batch, int n, int m, int e, int heads, int residual, int mode, void* ws,
-                         size_t ws_bytes, pio_stream_t stream) {
+                         void* saved, int batch, int n, int m, int e, int heads, int residual, const pio_dropout* drop,
+                         int mode, void* ws, size_t ws_bytes, pio_stream_t stream) {
     PIO_TRY(check_mode(mode, "pio_cross_attend_fwd"));
     PIO_CHECK_ARG(x_q && kv && y && w && saved && batch >= 0 && n >= 0 && m >= 0, "pio_cross_attend_fwd: bad arguments");
     PIO_TRY(check_heads(e, heads, "pio_cross_attend_fwd"));
-    Ctx ctx(ws, ws_bytes, stream);
+    Ctx ctx(ws, ws_bytes, stream, drop);
     if (mode == PIO_MODE_BF16) return bf::cross_attend_fwd(ctx, x_q, kv, pad, y, w, saved, batch, n, m, e, heads, residual);
     return cross_attend_fwd(ctx, x_q, kv, pad, y, w, saved, batch, n, m, e, heads, residual);
 }
 
 int pio_cross_attend_bwd(const float* dy, const float* x_q, const float* kv, const uint8_t* pad, float* dx_q, float* dkv,
                          const pio_attn_weights* w, const void* saved, const pio_attn_grads* g, int accumulate, int batch,
-                         int n, int m, int e, int heads, int residual, int mode, void* ws, size_t ws_bytes,
-                         pio_stream_t stream) {
+                         int n, int m, int e, int heads, int residual, const pio_dropout* drop, int mode, void* ws,
+                         size_t ws_bytes, pio_stream_t stream) {
     PIO_TRY(check_mode(mode, "pio_cross_attend_bwd"));
     PIO_CHECK_ARG(dy && x_q && kv && dx_q && dkv && w && saved && g, "pio_cross_attend_bwd: bad arguments");
     PIO_TRY(check_heads(e, heads, "pio_cross_attend_bwd"));
-    Ctx ctx(ws, ws_bytes, stream);
+    Ctx ctx(ws, ws_bytes, stream, drop);
     if (mode == PIO_MODE_BF16)
         return bf::cross_attend_bwd(ctx, dy, x_q, kv, pad, dx_q, dkv, w, saved, g, accumulate, batch, n, m, e, heads, residual);
     return cross_attend_bwd(ctx, dy, x_q, kv, pad, dx_q, dkv, w, saved, g, accumulate, batch, n, m, e, heads, residual);
@@ -441,22 +473,22 @@ size_t pio_self_attn_ws_bytes(int batch, int n, int c, int heads, int mode) {
 }
 
 int pio_self_attn_fwd(const float* x, float* y, const pio_attn_weights* w, void* saved, int batch, int n, int c, int heads,
-                      int residual, int mode, void* ws, size_t ws_bytes, pio_stream_t stream) {
+                      int residual, const pio_dropout* drop, int mode, void* ws, size_t ws_bytes, pio_stream_t stream) {
     PIO_TRY(check_mode(mode, "pio_self_attn_fwd"));
     PIO_CHECK_ARG(x && y && w && saved && batch >= 0 && n >= 0, "pio_self_attn_fwd: bad arguments");
     PIO_TRY(check_heads(c, heads, "pio_self_attn_fwd"));
-    Ctx ctx(ws, ws_bytes, stream);
+    Ctx ctx(ws, ws_bytes, stream, drop);
     if (mode == PIO_MODE_BF16) return bf::self_attn_fwd(ctx, x, y, w, saved, batch, n, c, heads, residual);
     return self_attn_fwd(ctx, x, y, w, saved, batch, n, c, heads, residual);
 }
 
 int pio_self_attn_bwd(const float* dy, const float* x, float* dx, const pio_attn_weights* w, const void* saved,
-                      const pio_attn_grads* g, int accumulate, int batch, int n, int c, int heads, int residual, int mode,
-                      void* ws, size_t ws_bytes, pio_stream_t stream) {
+                      const pio_attn_grads* g, int accumulate, int batch, int n, int c, int heads, int residual,
+                      const pio_dropout* drop, int mode, void* ws, size_t ws_bytes, pio_stream_t stream) {
     PIO_TRY(check_mode(mode, "pio_self_attn_bwd"));
     PIO_CHECK_ARG(dy && x && dx && w && saved && g, "pio_self_attn_bwd: bad arguments");
     PIO_TRY(check_heads(c, heads, "pio_self_attn_bwd"));
-    Ctx ctx(ws, ws_bytes, stream);
+    Ctx ctx(ws, ws_bytes, stream, drop);
     if (mode == PIO_MODE_BF16) return bf::self_attn_bwd(ctx, dy, x, dx, w, saved, g, accumulate, batch, n, c, heads, residual);
     return self_attn_bwd(ctx, dy, x, dx, w, saved, g, accumulate, batch, n, c, heads, residual);
 }
@@ -475,12 +507,12 @@ size_t pio_latent_block_ws_bytes(int layers, int batch, int n, int c, int heads,
 }
 
 int pio_latent_block_fwd(const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,
-                         int layers, int batch, int n, int c, int heads, int mode, void* ws, size_t ws_bytes,
-                         pio_stream_t stream) {
+                         int layers, int batch, int n, int c, int heads, const pio_dropout* drop, int mode, void* ws,
+                         size_t ws_bytes, pio_stream_t stream) {
     PIO_TRY(check_mode(mode, "pio_latent_block_fwd"));
     PIO_CHECK_ARG(x && y && attn && mlp && saved && layers >= 1 && batch >= 0 && n >= 0, "pio_latent_block_fwd: bad arguments");
     PIO_TRY(check_heads(c, heads, "pio_latent_block_fwd"));
-    Ctx ctx(ws, ws_bytes, stream);
+    Ctx ctx(ws, ws_bytes, stream, drop);
     if (mode == PIO_MODE_BF16) return bf::latent_block_fwd(ctx, x, y, attn, mlp, saved, layers, batch, n, c, heads);
     BlockLayout L(batch, n, c, heads);
     const int64_t rows = (int64_t)batch * n;
@@ -489,8 +521,12 @@ int pio_latent_block_fwd(const float* x, float* y, const pio_attn_weights* attn,
         float* slab = (float*)saved + (size_t)s * L.per_layer;
         float* xmid = slab + L.xmid;
         float* out = (s == layers - 1) ? y : slab + L.xnext;
+        const uint64_t seed0 = ctx.drop_seed;
+        ctx.drop_seed = seed0 + 4 * (uint64_t)s;
         PIO_TRY(self_attn_fwd(ctx, cur, xmid, &attn[s], slab + L.sa, batch, n, c, heads));
+        ctx.drop_seed = seed0 + 4 * (uint64_t)s + 2;
         PIO_TRY(mlp_fwd(ctx, xmid, out, &mlp[s], slab + L.mlp, rows, c));
+        ctx.drop_seed = seed0;
         cur = out;
     }
     return PIO_OK;
@@ -498,12 +534,12 @@ int pio_latent_block_fwd(const float* x, float* y, const pio_attn_weights* attn,
 
 int pio_latent_block_bwd(const float* dy, const float* x, float* dx, const pio_attn_weights* attn, const pio_mlp_weights* mlp,
                          const void* saved, const pio_attn_grads* attn_g, const pio_mlp_grads* mlp_g, int accumulate,
-                         int layers, int batch, int n, int c, int heads, int mode, void* ws, size_t ws_bytes,
-                         pio_stream_t stream) {
+                         int layers, int batch, int n, int c, int heads, const pio_dropout* drop, int mode, void* ws,
+                         size_t ws_bytes, pio_stream_t stream) {
     PIO_TRY(check_mode(mode, "pio_latent_block_bwd"));
     PIO_CHECK_ARG(dy && x && dx && attn && mlp && saved && attn_g && mlp_g && layers >= 1, "pio_latent_block_bwd: bad arguments");
     PIO_TRY(check_heads(c, heads, "pio_latent_block_bwd"));
-    Ctx ctx(ws, ws_bytes, stream);
+    Ctx ctx(ws, ws_bytes, stream, drop);
     if (mode == PIO_MODE_BF16)
         return bf::latent_block_bwd(ctx, dy, x, dx, attn, mlp, saved, attn_g, mlp_g, accumulate, layers, batch, n, c, heads);
     BlockLayout L(batch, n, c, heads);
@@ -514,9 +550,13 @@ int pio_latent_block_bwd(const float* dy, const float* x, float* dx, const pio_a
     for (int s = layers - 1; s >= 0; --s) {
         const float* slab = (const float*)saved + (size_t)s * L.per_layer;
         const float* x_in = (s == 0) ? x : ((const float*)saved + (size_t)(s - 1) * L.per_layer + L.xnext);
+        const uint64_t seed0 = ctx.drop_seed;
+        ctx.drop_seed = seed0 + 4 * (uint64_t)s + 2;
         PIO_TRY(mlp_bwd(ctx, grad, slab + L.xmid, dmid, &mlp[s], slab + L.mlp, &mlp_g[s], accumulate, rows, c));
         float* out = (s == 0) ? dx : dcur;
+        ctx.drop_seed = seed0 + 4 * (uint64_t)s;
         PIO_TRY(self_attn_bwd(ctx, dmid, x_in, out, &attn[s], slab + L.sa, &attn_g[s], accumulate, batch, n, c, heads));
+        ctx.drop_seed = seed0;
         grad = out;
     }
     return PIO_OK;

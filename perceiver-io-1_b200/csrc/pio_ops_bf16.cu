@@ -95,8 +95,9 @@ struct Side {
 // y = act(x16 W16^T + bias) (+ residual)
 static int tc_xwT(Ctx& c, const bf16* x, int64_t ldx, const bf16* w, int64_t ldw, int64_t rows, int64_t n, int64_t k,
                   float* c32, int64_t ldc32, bf16* c16, int64_t ldc16, const float* bias, const float* res, int64_t ldr,
-                  int act, bf16* aux, int64_t ldaux) {
+                  int act, bf16* aux, int64_t ldaux, float drop_p = 0.f, uint64_t drop_seed = 0) {
     pio_gemm_bf16_desc d{};
+    d.dropout_p = drop_p; d.dropout_seed = drop_seed;
     d.a = x; d.b = w; d.m = rows; d.n = n; d.k = k; d.lda = ldx; d.ldb = ldw; d.a_kmajor = 1; d.b_kmajor = 1;
     d.c32 = c32; d.ldc32 = ldc32; d.c16 = c16; d.ldc16 = ldc16;
     d.bias = bias; d.residual = res; d.ldr = ldr; d.act = act; d.aux16 = aux; d.ldaux = ldaux;
@@ -130,6 +131,20 @@ static size_t scratch_bytes(int64_t rows, int64_t nout, int64_t kin) {
                     pio_layernorm_bwd_ws_bytes(rows, (int)kin)) + 1024;
 }
 
+// gradient entering the branch of a Residual with dropout (same mask as the forward epilogue)
+static int branch_grad(Ctx& c, const float* dy, int64_t count, int residual, const float** out, const char* who) {
+    *out = dy;
+    if (!(residual && c.drop_p > 0.f)) return PIO_OK;
+    float* tmp = c.W.takef((size_t)count);
+    if (!tmp) {
+        set_error("%s: workspace too small (%zu bytes given)", who, c.W.size);
+        return PIO_ERR_WORKSPACE;
+    }
+    PIO_TRY(dropout_mask(dy, tmp, count, c.res_drop(residual), c.st));
+    *out = tmp;
+    return PIO_OK;
+}
+
 static int need_mult8(int v, const char* what, const char* who) {
     PIO_CHECK_ARG(v % 8 == 0, "%s: %s = %d must be a multiple of 8 in bf16 mode", who, what, v);
     return PIO_OK;
@@ -151,7 +166,7 @@ struct MlpSaved {
 };
 size_t mlp_saved_bytes(int64_t rows, int ch) { return MlpSaved(nullptr, rows, ch).total + 256; }
 size_t mlp_ws_bytes(int64_t rows, int ch) {
-    return 2 * align_up((size_t)rows * ch * 2, 256) + align_up((size_t)rows * ch * 4, 256) + scratch_bytes(rows, ch, ch);
+    return 2 * align_up((size_t)rows * ch * 2, 256) + 2 * align_up((size_t)rows * ch * 4, 256) + scratch_bytes(rows, ch, ch);
 }
 
 int mlp_fwd(Ctx& c, const float* x, float* y, const pio_mlp_weights* w, void* saved, int64_t rows, int ch, int residual) {
@@ -160,7 +175,7 @@ int mlp_fwd(Ctx& c, const float* x, float* y, const pio_mlp_weights* w, void* sa
     PIO_TRY(layernorm_fwd_bf16(x, w->ln_w, w->ln_b, s.h0, ch, s.stats, rows, ch, LN_EPS, c.st));
     PIO_TRY(tc_xwT(c, s.h0, ch, (const bf16*)w->w1, ch, rows, ch, ch, nullptr, 0, s.g, ch, w->b1, nullptr, 0, 1, s.h1, ch));
     PIO_TRY(tc_xwT(c, s.g, ch, (const bf16*)w->w2, ch, rows, ch, ch, y, ch, nullptr, 0, w->b2, residual ? x : nullptr, ch, 0,
-                   nullptr, 0));
+                   nullptr, 0, residual ? c.drop_p : 0.f, c.drop_seed + 1));
     return PIO_OK;
 }
 
@@ -173,7 +188,9 @@ int mlp_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_mlp_we
     PIO_TAKE_BYTES(bf16, dh1, c, (size_t)rows * ch * 2, "pio_mlp_bwd");
     PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ch * 4, "pio_mlp_bwd");
     Side side(c, acc);
-    PIO_TRY(cast_colsum_f32(dy, ch, dy16, ch, g->b2, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
+    const float* dyb;
+    PIO_TRY(branch_grad(c, dy, rows * ch, residual, &dyb, "pio_mlp_bwd"));
+    PIO_TRY(cast_colsum_f32(dyb, ch, dy16, ch, g->b2, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
     PIO_TRY(side.fork());
     PIO_TRY(tc_dW(c, dy16, ch, s.g, ch, g->w2, rows, ch, ch, acc, side.stream()));
     PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->w2, ch, rows, ch, ch, nullptr, 0, dh1, ch, 2, s.h1, ch, 0));
@@ -277,11 +294,12 @@ static void fill_attn(pio_attn_desc& a, const bf16* q, int64_t q_rs, const bf16*
 
 // bf16 q/k/v -> o (fp32 + bf16) and lse: tensor-core flash kernel when the head size allows, else
 // the fp32-arithmetic kernel reading the same bf16 operands
-static int attention_fwd(const pio_attn_desc& a, bf16* o16, cudaStream_t st) {
-    if (attn_fwd_tc_supported(&a)) return attn_fwd_tc(&a, o16, st);
+static int attention_fwd(const pio_attn_desc& a, bf16* o16, cudaStream_t st, const DropCfg& drop) {
+    if (drop.threshold == 0 && attn_fwd_tc_supported(&a)) return attn_fwd_tc(&a, o16, st);
     AttnBf16Out ex;
     ex.o16 = o16;
     ex.in16 = 1;
+    ex.drop = drop;
     return attn_fwd_simt(&a, st, &ex);
 }
 
@@ -305,7 +323,7 @@ struct XaSaved {
 size_t xa_saved_bytes(int batch, int n, int e, int heads) { return XaSaved(nullptr, batch, n, e, heads).total + 256; }
 size_t xa_ws_bytes(int batch, int n, int e, int heads) {
     const size_t r = (size_t)batch * n;
-    return 2 * align_up(r * e * 2, 256) + 3 * align_up(r * e * 4, 256) + align_up((size_t)batch * heads * n * 4, 256) +
+    return 2 * align_up(r * e * 2, 256) + 4 * align_up(r * e * 4, 256) + align_up((size_t)batch * heads * n * 4, 256) +
            scratch_bytes(r, e, e);
 }
 
@@ -319,9 +337,9 @@ int cross_attend_fwd(Ctx& c, const float* x_q, const float* kv, const uint8_t* p
     const bf16* kv16 = reinterpret_cast<const bf16*>(kv);
     pio_attn_desc a{};
     fill_attn(a, s.q, e, kv16, kv16 + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
-    PIO_TRY(attention_fwd(a, s.o16, c.st));
+    PIO_TRY(attention_fwd(a, s.o16, c.st, c.attn_drop()));
     PIO_TRY(tc_xwT(c, s.o16, e, (const bf16*)w->wo, e, rows, e, e, y, e, nullptr, 0, w->bo, residual ? x_q : nullptr, e, 0,
-                   nullptr, 0));
+                   nullptr, 0, residual ? c.drop_p : 0.f, c.drop_seed + 1));
     return PIO_OK;
 }
 
@@ -338,14 +356,17 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
     PIO_TAKE_BYTES(float, dhq, c, (size_t)rows * e * 4, "pio_cross_attend_bwd");
     PIO_TAKE_BYTES(float, delta, c, (size_t)batch * heads * n * 4, "pio_cross_attend_bwd");
     Side side(c, acc);
-    PIO_TRY(cast_colsum_f32(dy, e, dy16, e, g->bo, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
+    const float* dyb;
+    PIO_TRY(branch_grad(c, dy, rows * e, residual, &dyb, "pio_cross_attend_bwd"));
+    PIO_TRY(cast_colsum_f32(dyb, e, dy16, e, g->bo, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
     PIO_TRY(side.fork());
     PIO_TRY(tc_dW(c, dy16, e, s.o16, e, g->wo, rows, e, e, acc, side.stream()));
     const bf16* kv16 = reinterpret_cast<const bf16*>(kv);
     bf16* dkv16 = reinterpret_cast<bf16*>(dkv);
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.q, e, kv16, kv16 + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
-    if (attn_fwd_tc_supported(&b.fwd)) {
+    const DropCfg adrop = c.attn_drop();
+    if (adrop.threshold == 0 && attn_fwd_tc_supported(&b.fwd)) {
         bf16* d_o16 = reinterpret_cast<bf16*>(d_o);  // the fp32 scratch is large enough for the bf16 tile
         PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)w->wo, e, rows, e, e, nullptr, 0, d_o16, e, 0, nullptr, 0, 0));
         PIO_TRY(attn_bwd_tc(&b.fwd, d_o16, delta, dq16, dkv16, dkv16 + e, c.st));
@@ -354,6 +375,7 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
         b.d_o = d_o; b.delta = delta;
         AttnBf16Out ex;
         ex.in16 = 1;
+        ex.drop = adrop;
         ex.dq16 = dq16; ex.dk16 = dkv16; ex.dv16 = dkv16 + e;
         PIO_TRY(attn_bwd_simt(&b, c.st, &ex));
     }
@@ -388,7 +410,7 @@ struct SaSaved {
 size_t sa_saved_bytes(int batch, int n, int ch, int heads) { return SaSaved(nullptr, batch, n, ch, heads).total + 256; }
 size_t sa_ws_bytes(int batch, int n, int ch, int heads) {
     const size_t r = (size_t)batch * n;
-    return align_up(r * ch * 2, 256) + align_up(3 * r * ch * 2, 256) + 2 * align_up(r * ch * 4, 256) +
+    return align_up(r * ch * 2, 256) + align_up(3 * r * ch * 2, 256) + 3 * align_up(r * ch * 4, 256) +
            align_up(3 * r * ch * 4, 256) + align_up((size_t)batch * heads * n * 4, 256) + scratch_bytes(r, 3 * ch, ch);
 }
 
@@ -411,9 +433,9 @@ int self_attn_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* w, v
                    nullptr, 0));
     pio_attn_desc a{};
     fill_attn(a, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
-    PIO_TRY(attention_fwd(a, s.o16, c.st));
+    PIO_TRY(attention_fwd(a, s.o16, c.st, c.attn_drop()));
     PIO_TRY(tc_xwT(c, s.o16, ch, (const bf16*)w->wo, ch, rows, ch, ch, y, ch, nullptr, 0, w->bo, residual ? x : nullptr, ch, 0,
-                   nullptr, 0));
+                   nullptr, 0, residual ? c.drop_p : 0.f, c.drop_seed + 1));
     return PIO_OK;
 }
 
@@ -433,12 +455,15 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
     PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ch * 4, "pio_self_attn_bwd");
     PIO_TAKE_BYTES(float, delta, c, (size_t)batch * heads * n * 4, "pio_self_attn_bwd");
     Side side(c, acc);
-    PIO_TRY(cast_colsum_f32(dy, ch, dy16, ch, g->bo, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
+    const float* dyb;
+    PIO_TRY(branch_grad(c, dy, rows * ch, residual, &dyb, "pio_self_attn_bwd"));
+    PIO_TRY(cast_colsum_f32(dyb, ch, dy16, ch, g->bo, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
     PIO_TRY(side.fork());
     PIO_TRY(tc_dW(c, dy16, ch, s.o16, ch, g->wo, rows, ch, ch, acc, side.stream()));
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
-    if (attn_fwd_tc_supported(&b.fwd)) {
+    const DropCfg adrop = c.attn_drop();
+    if (adrop.threshold == 0 && attn_fwd_tc_supported(&b.fwd)) {
         bf16* d_o16 = reinterpret_cast<bf16*>(d_o);
         PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->wo, ch, rows, ch, ch, nullptr, 0, d_o16, ch, 0, nullptr, 0, 0));
         PIO_TRY(attn_bwd_tc(&b.fwd, d_o16, delta, dqkv16, dqkv16 + ch, dqkv16 + 2 * ch, c.st));
@@ -447,6 +472,7 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
         b.d_o = d_o; b.delta = delta;
         AttnBf16Out ex;
         ex.in16 = 1;
+        ex.drop = adrop;
         ex.dq16 = dqkv16; ex.dk16 = dqkv16 + ch; ex.dv16 = dqkv16 + 2 * ch;
         PIO_TRY(attn_bwd_simt(&b, c.st, &ex));
     }
@@ -491,8 +517,12 @@ int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* a
         char* slab = (char*)saved + (size_t)s * L.per_layer;
         float* xmid = (float*)(slab + L.xmid);
         float* out = (s == layers - 1) ? y : (float*)(slab + L.xnext);
+        const uint64_t seed0 = c.drop_seed;
+        c.drop_seed = seed0 + 4 * (uint64_t)s;
         PIO_TRY(self_attn_fwd(c, cur, xmid, &attn[s], slab + L.sa, batch, n, ch, heads, 1));
+        c.drop_seed = seed0 + 4 * (uint64_t)s + 2;
         PIO_TRY(mlp_fwd(c, xmid, out, &mlp[s], slab + L.mlp, rows, ch, 1));
+        c.drop_seed = seed0;
         cur = out;
     }
     return PIO_OK;
@@ -509,9 +539,13 @@ int latent_block_bwd(Ctx& c, const float* dy, const float* x, float* dx, const p
     for (int s = layers - 1; s >= 0; --s) {
         const char* slab = (const char*)saved + (size_t)s * L.per_layer;
         const float* x_in = (s == 0) ? x : (const float*)((const char*)saved + (size_t)(s - 1) * L.per_layer + L.xnext);
+        const uint64_t seed0 = c.drop_seed;
+        c.drop_seed = seed0 + 4 * (uint64_t)s + 2;
         PIO_TRY(mlp_bwd(c, grad, (const float*)(slab + L.xmid), dmid, &mlp[s], slab + L.mlp, &mlp_g[s], acc, rows, ch, 1));
         float* out = (s == 0) ? dx : dcur;
+        c.drop_seed = seed0 + 4 * (uint64_t)s;
         PIO_TRY(self_attn_bwd(c, dmid, x_in, out, &attn[s], slab + L.sa, &attn_g[s], acc, batch, n, ch, heads, 1));
+        c.drop_seed = seed0;
         grad = out;
     }
     return PIO_OK;

@@ -11,6 +11,7 @@ struct AttnBf16Out {
     __nv_bfloat16* dk16 = nullptr;
     __nv_bfloat16* dv16 = nullptr;
     int in16 = 0;  // q, k, v of the descriptor point at bf16 data (same element strides)
+    DropCfg drop = DropCfg{0, 0, 1.f};  // attention-probability dropout (fp32-arithmetic kernels only)
 };
 int attn_fwd_simt(const pio_attn_desc* d, cudaStream_t st, const AttnBf16Out* extra = nullptr);
 int attn_bwd_simt(const pio_attn_bwd_desc* d, cudaStream_t st, const AttnBf16Out* extra = nullptr);
@@ -40,7 +41,18 @@ constexpr float LN_EPS = 1e-5f;  // nn.LayerNorm default, used everywhere in the
 struct Ctx {
     cudaStream_t st;
     Workspace W;
+    // dropout of the operator being run (0 = off): site seed+0 = attention probabilities, seed+1 = Residual
+    float drop_p = 0.f;
+    uint64_t drop_seed = 0;
     Ctx(void* ws, size_t n, pio_stream_t s) : st((cudaStream_t)s), W(ws, n) {}
+    Ctx(void* ws, size_t n, pio_stream_t s, const pio_dropout* d) : st((cudaStream_t)s), W(ws, n) {
+        if (d != nullptr && d->p > 0.f) {
+            drop_p = d->p;
+            drop_seed = d->seed;
+        }
+    }
+    DropCfg attn_drop() const { return make_drop(drop_p, drop_seed); }
+    DropCfg res_drop(int residual) const { return make_drop(residual ? drop_p : 0.f, drop_seed + 1); }
     void* rest() { return W.base ? W.base + align_up(W.off, 256) : nullptr; }
     size_t rest_bytes() {
         const size_t o = align_up(W.off, 256);

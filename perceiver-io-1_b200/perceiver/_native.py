@@ -38,7 +38,8 @@ class GemmDesc(Structure):
                 ("a_kmajor", c_int), ("b_kmajor", c_int),
                 ("bias", c_void_p), ("residual", c_void_p), ("ldr", c_int64),
                 ("aux", c_void_p), ("ldaux", c_int64),
-                ("act", c_int), ("accumulate", c_int), ("rowsum_a", c_void_p)]
+                ("act", c_int), ("accumulate", c_int), ("rowsum_a", c_void_p),
+                ("dropout_p", c_float), ("dropout_seed", ctypes.c_uint64)]
 
 
 class GemmBf16Desc(Structure):
@@ -47,7 +48,12 @@ class GemmBf16Desc(Structure):
                 ("a_kmajor", c_int), ("b_kmajor", c_int),
                 ("c32", c_void_p), ("ldc32", c_int64), ("c16", c_void_p), ("ldc16", c_int64),
                 ("bias", c_void_p), ("residual", c_void_p), ("ldr", c_int64),
-                ("aux16", c_void_p), ("ldaux", c_int64), ("act", c_int), ("accumulate", c_int)]
+                ("aux16", c_void_p), ("ldaux", c_int64), ("act", c_int), ("accumulate", c_int),
+                ("dropout_p", c_float), ("dropout_seed", ctypes.c_uint64)]
+
+
+class Dropout(Structure):
+    _fields_ = [("p", c_float), ("seed", ctypes.c_uint64)]
 
 
 class AttnDesc(Structure):
@@ -91,9 +97,9 @@ _SIGNATURES = {
     "pio_cross_entropy_bwd": (c_int, [P, P, P, P, P, P, c_int64, c_int64, c_int64, c_int64, P]),
     "pio_mlp_saved_bytes": (c_size_t, [c_int64, c_int, c_int]),
     "pio_mlp_ws_bytes": (c_size_t, [c_int64, c_int, c_int]),
-    "pio_mlp_fwd": (c_int, [P, P, POINTER(MlpWeights), P, c_int64, c_int, c_int, c_int, P, c_size_t, P]),
-    "pio_mlp_bwd": (c_int, [P, P, P, POINTER(MlpWeights), P, POINTER(MlpWeights), c_int, c_int64, c_int, c_int, c_int,
-                            P, c_size_t, P]),
+    "pio_mlp_fwd": (c_int, [P, P, POINTER(MlpWeights), P, c_int64, c_int, c_int, POINTER(Dropout), c_int, P, c_size_t, P]),
+    "pio_mlp_bwd": (c_int, [P, P, P, POINTER(MlpWeights), P, POINTER(MlpWeights), c_int, c_int64, c_int, c_int,
+                            POINTER(Dropout), c_int, P, c_size_t, P]),
     "pio_kv_project_saved_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),
     "pio_kv_project_ws_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),
     "pio_kv_project_fwd": (c_int, [P, P, POINTER(AttnWeights), P, c_int64, c_int, c_int, c_int, P, c_size_t, P]),
@@ -101,21 +107,23 @@ _SIGNATURES = {
                                    c_int, P, c_size_t, P]),
     "pio_cross_attend_saved_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int, c_int]),
     "pio_cross_attend_ws_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int, c_int]),
-    "pio_cross_attend_fwd": (c_int, [P, P, P, P, POINTER(AttnWeights), P, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
-                                     P, c_size_t, P]),
+    "pio_cross_attend_fwd": (c_int, [P, P, P, P, POINTER(AttnWeights), P, c_int, c_int, c_int, c_int, c_int, c_int,
+                                     POINTER(Dropout), c_int, P, c_size_t, P]),
     "pio_cross_attend_bwd": (c_int, [P, P, P, P, P, P, POINTER(AttnWeights), P, POINTER(AttnWeights), c_int, c_int, c_int,
-                                     c_int, c_int, c_int, c_int, c_int, P, c_size_t, P]),
+                                     c_int, c_int, c_int, c_int, POINTER(Dropout), c_int, P, c_size_t, P]),
     "pio_self_attn_saved_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
     "pio_self_attn_ws_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
-    "pio_self_attn_fwd": (c_int, [P, P, POINTER(AttnWeights), P, c_int, c_int, c_int, c_int, c_int, c_int, P, c_size_t, P]),
+    "pio_self_attn_fwd": (c_int, [P, P, POINTER(AttnWeights), P, c_int, c_int, c_int, c_int, c_int, POINTER(Dropout), c_int, P,
+                                  c_size_t, P]),
     "pio_self_attn_bwd": (c_int, [P, P, P, POINTER(AttnWeights), P, POINTER(AttnWeights), c_int, c_int, c_int, c_int,
-                                  c_int, c_int, c_int, P, c_size_t, P]),
+                                  c_int, c_int, POINTER(Dropout), c_int, P, c_size_t, P]),
     "pio_latent_block_saved_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int, c_int]),
     "pio_latent_block_ws_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int, c_int]),
     "pio_latent_block_fwd": (c_int, [P, P, POINTER(AttnWeights), POINTER(MlpWeights), P, c_int, c_int, c_int, c_int,
-                                     c_int, c_int, P, c_size_t, P]),
+                                     c_int, POINTER(Dropout), c_int, P, c_size_t, P]),
     "pio_latent_block_bwd": (c_int, [P, P, P, POINTER(AttnWeights), POINTER(MlpWeights), P, POINTER(AttnWeights),
-                                     POINTER(MlpWeights), c_int, c_int, c_int, c_int, c_int, c_int, c_int, P, c_size_t, P]),
+                                     POINTER(MlpWeights), c_int, c_int, c_int, c_int, c_int, c_int, POINTER(Dropout), c_int, P,
+                                     c_size_t, P]),
     "pio_linear_ws_bytes": (c_size_t, [c_int64, c_int, c_int64, c_int]),
     "pio_linear_fwd": (c_int, [P, P, P, P, c_int64, c_int, c_int64, c_int, P, c_size_t, P]),
     "pio_linear_ce_ws_bytes": (c_size_t, [c_int64, c_int, c_int64, c_int]),

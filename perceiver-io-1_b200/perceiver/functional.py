@@ -27,6 +27,27 @@ def get_compute_mode():
     return _MODE["mode"]
 
 
+_drop_calls = [0]
+
+
+def next_dropout_seed():
+    """A fresh 64-bit seed for one operator call, derived from torch's seed and a call counter (so
+    torch.manual_seed makes dropout reproducible).  Operators use seed .. seed + 4*layers for their sites."""
+    _drop_calls[0] += 1
+    return (torch.initial_seed() * 0x9E3779B97F4A7C15 + _drop_calls[0] * 0x632BE59BD9B4E019) & 0xFFFFFFFFFFFFFFFF
+
+
+def _drop_struct(p, seed):
+    """ctypes pio_dropout (or None when off)"""
+    if not p:
+        return None
+    return N.Dropout(float(p), int(seed))
+
+
+def _dref(d):
+    return byref(d) if d is not None else None
+
+
 def _c(t, dtype=torch.float32):
     """contiguous CUDA tensor of the expected dtype (no silent device moves)."""
     N.require_cuda(t)
@@ -217,7 +238,7 @@ class MlpFn(torch.autograd.Function):
     """Residual(mlp(C)) (reference model.py:20-26,47-56)."""
 
     @staticmethod
-    def forward(ctx, x, ln_w, ln_b, w1, b1, w2, b2, residual):
+    def forward(ctx, x, ln_w, ln_b, w1, b1, w2, b2, residual, drop_p=0.0, drop_seed=0):
         x = _c(x)
         params = [_c(p) for p in (ln_w, ln_b, w1, b1, w2, b2)]
         c = x.shape[-1]
@@ -229,19 +250,20 @@ class MlpFn(torch.autograd.Function):
         y = torch.empty_like(x)
         ops = _mlp_operands(params, mode)
         w = N.mlp_struct(**dict(zip(N.MlpWeights._names, ops)))
-        N.check(L.pio_mlp_fwd(x.data_ptr(), y.data_ptr(), byref(w), saved.data_ptr(), rows, c, int(residual), mode,
+        drop = _drop_struct(drop_p, drop_seed)
+        N.check(L.pio_mlp_fwd(x.data_ptr(), y.data_ptr(), byref(w), saved.data_ptr(), rows, c, int(residual), _dref(drop), mode,
                               ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_mlp_fwd")
         ctx.save_for_backward(x, *params)
         ctx.wstruct, ctx.keep = w, ops
         ctx.saved_buf = saved
-        ctx.meta = (rows, c, int(residual), mode)
+        ctx.meta = (rows, c, int(residual), mode, drop)
         return y
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dy):
         x, *params = ctx.saved_tensors
-        rows, c, residual, mode = ctx.meta
+        rows, c, residual, mode, drop = ctx.meta
         dy = _c(dy)
         L = N.lib()
         grads, accf = _grads_like(params, mode)
@@ -250,9 +272,10 @@ class MlpFn(torch.autograd.Function):
         w = ctx.wstruct
         g = N.mlp_struct(**dict(zip(N.MlpWeights._names, grads)))
         N.check(L.pio_mlp_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g), accf,
-                              rows, c, residual, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_mlp_bwd")
+                              rows, c, residual, _dref(drop), mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)),
+                "pio_mlp_bwd")
         ctx.saved_buf = None
-        return (dx, *grads, None)
+        return (dx, *grads, None, None, None)
 
 
 class KVProjectFn(torch.autograd.Function):
@@ -318,7 +341,7 @@ class CrossAttendFn(torch.autograd.Function):
     q in-projection, attention over the projected kv, out-projection, + x_q."""
 
     @staticmethod
-    def forward(ctx, x_q, kv, pad, ln_w, ln_b, bias, w_packed, w_q, wo, bo, heads, residual):
+    def forward(ctx, x_q, kv, pad, ln_w, ln_b, bias, w_packed, w_q, wo, bo, heads, residual, drop_p=0.0, drop_seed=0):
         mode = get_compute_mode()
         x_q, kv = _c(x_q), _c(kv, torch.float32 if mode == N.MODE_FP32 else torch.bfloat16)
         ln_w, ln_b, bias, wo, bo = _c(ln_w), _c(ln_b), _c(bias), _c(wo), _c(bo)
@@ -337,19 +360,20 @@ class CrossAttendFn(torch.autograd.Function):
         saved = _saved(L.pio_cross_attend_saved_bytes(b, n, m, e, heads, mode), x_q.device)
         ws = N.workspace(L.pio_cross_attend_ws_bytes(b, n, m, e, heads, mode), x_q.device)
         y = torch.empty_like(x_q)
+        drop = _drop_struct(drop_p, drop_seed)
         N.check(L.pio_cross_attend_fwd(x_q.data_ptr(), kv.data_ptr(), N.ptr(pad), y.data_ptr(), byref(w), saved.data_ptr(),
-                                       b, n, m, e, heads, int(residual), mode, ws.data_ptr(), ws.numel(),
+                                       b, n, m, e, heads, int(residual), _dref(drop), mode, ws.data_ptr(), ws.numel(),
                                        N.stream_ptr(x_q.device)), "pio_cross_attend_fwd")
         ctx.save_for_backward(x_q, kv, pad, ln_w, ln_b, bias, w_packed, w_q, wo, bo)
         ctx.saved_buf = saved
-        ctx.meta = (b, n, m, e, heads, int(residual), mode)
+        ctx.meta = (b, n, m, e, heads, int(residual), mode, drop)
         return y
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dy):
         x_q, kv, pad, ln_w, ln_b, bias, w_packed, w_q, wo, bo = ctx.saved_tensors
-        b, n, m, e, heads, residual, mode = ctx.meta
+        b, n, m, e, heads, residual, mode, drop = ctx.meta
         dy = _c(dy)
         L = N.lib()
         dev = x_q.device
@@ -370,10 +394,10 @@ class CrossAttendFn(torch.autograd.Function):
         ws = N.workspace(L.pio_cross_attend_ws_bytes(b, n, m, e, heads, mode), dev)
         N.check(L.pio_cross_attend_bwd(dy.data_ptr(), x_q.data_ptr(), kv.data_ptr(), N.ptr(pad), dx.data_ptr(),
                                        dkv.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g), accf, b, n, m, e, heads,
-                                       residual, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
+                                       residual, _dref(drop), mode, ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
                 "pio_cross_attend_bwd")
         ctx.saved_buf = None
-        return dx, dkv, None, dln_w, dln_b, dbias, dwp, dwq, dwo, dbo, None, None
+        return dx, dkv, None, dln_w, dln_b, dbias, dwp, dwq, dwo, dbo, None, None, None, None
 
 
 _SA_NAMES = ("ln_w", "ln_b", "in_w", "in_b", "wo", "bo")
@@ -392,7 +416,7 @@ class SelfAttnFn(torch.autograd.Function):
     """Residual(SelfAttention) (reference model.py:102-116, :54-56), one layer."""
 
     @staticmethod
-    def forward(ctx, x, ln_w, ln_b, in_w, in_b, wo, bo, heads, residual):
+    def forward(ctx, x, ln_w, ln_b, in_w, in_b, wo, bo, heads, residual, drop_p=0.0, drop_seed=0):
         x = _c(x)
         params = [_c(p) for p in (ln_w, ln_b, in_w, in_b, wo, bo)]
         b, n, c = x.shape
@@ -405,18 +429,19 @@ class SelfAttnFn(torch.autograd.Function):
         saved = _saved(L.pio_self_attn_saved_bytes(b, n, c, heads, mode), x.device)
         ws = N.workspace(L.pio_self_attn_ws_bytes(b, n, c, heads, mode), x.device)
         y = torch.empty_like(x)
+        drop = _drop_struct(drop_p, drop_seed)
         N.check(L.pio_self_attn_fwd(x.data_ptr(), y.data_ptr(), byref(w), saved.data_ptr(), b, n, c, heads, int(residual),
-                                    mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_self_attn_fwd")
+                                    _dref(drop), mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_self_attn_fwd")
         ctx.save_for_backward(x, *params)
         ctx.saved_buf = saved
-        ctx.meta = (b, n, c, heads, int(residual), mode)
+        ctx.meta = (b, n, c, heads, int(residual), mode, drop)
         return y
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dy):
         x, *params = ctx.saved_tensors
-        b, n, c, heads, residual, mode = ctx.meta
+        b, n, c, heads, residual, mode, drop = ctx.meta
         dy = _c(dy)
         L = N.lib()
         grads, accf = _grads_like(params, mode)
@@ -427,10 +452,11 @@ class SelfAttnFn(torch.autograd.Function):
         g = N.attn_struct(**gfields)
         ws = N.workspace(L.pio_self_attn_ws_bytes(b, n, c, heads, mode), x.device)
         N.check(L.pio_self_attn_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), byref(w), ctx.saved_buf.data_ptr(), byref(g),
-                                    accf, b, n, c, heads, residual, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)),
+                                    accf, b, n, c, heads, residual, _dref(drop), mode, ws.data_ptr(), ws.numel(),
+                                    N.stream_ptr(x.device)),
                 "pio_self_attn_bwd")
         ctx.saved_buf = None
-        return (dx, *grads, None, None)
+        return (dx, *grads, None, None, None, None)
 
 
 class LatentBlockFn(torch.autograd.Function):
@@ -456,7 +482,7 @@ class LatentBlockFn(torch.autograd.Function):
         return attn, mlp, keep
 
     @staticmethod
-    def forward(ctx, x, heads, *params):
+    def forward(ctx, x, heads, drop_p, drop_seed, *params):
         x = _c(x)
         params = [_c(p) for p in params]
         layers = len(params) // _LAYER_PARAMS
@@ -469,18 +495,20 @@ class LatentBlockFn(torch.autograd.Function):
         saved = _saved(L.pio_latent_block_saved_bytes(layers, b, n, c, heads, mode), x.device)
         ws = N.workspace(L.pio_latent_block_ws_bytes(layers, b, n, c, heads, mode), x.device)
         y = torch.empty_like(x)
-        N.check(L.pio_latent_block_fwd(x.data_ptr(), y.data_ptr(), attn, mlp, saved.data_ptr(), layers, b, n, c, heads, mode,
-                                       ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_latent_block_fwd")
+        drop = _drop_struct(drop_p, drop_seed)
+        N.check(L.pio_latent_block_fwd(x.data_ptr(), y.data_ptr(), attn, mlp, saved.data_ptr(), layers, b, n, c, heads,
+                                       _dref(drop), mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)),
+                "pio_latent_block_fwd")
         ctx.save_for_backward(x, *params)
         ctx.saved_buf = saved
-        ctx.meta = (layers, b, n, c, heads, mode)
+        ctx.meta = (layers, b, n, c, heads, mode, drop)
         return y
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dy):
         x, *params = ctx.saved_tensors
-        layers, b, n, c, heads, mode = ctx.meta
+        layers, b, n, c, heads, mode, drop = ctx.meta
         dy = _c(dy)
         L = N.lib()
         grads, accf = _grads_like(params, mode)
@@ -489,10 +517,10 @@ class LatentBlockFn(torch.autograd.Function):
         attn_g, mlp_g, _ = LatentBlockFn._structs(grads, layers, c)
         ws = N.workspace(L.pio_latent_block_ws_bytes(layers, b, n, c, heads, mode), x.device)
         N.check(L.pio_latent_block_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), attn, mlp, ctx.saved_buf.data_ptr(), attn_g,
-                                       mlp_g, accf, layers, b, n, c, heads, mode, ws.data_ptr(), ws.numel(),
+                                       mlp_g, accf, layers, b, n, c, heads, _dref(drop), mode, ws.data_ptr(), ws.numel(),
                                        N.stream_ptr(x.device)), "pio_latent_block_bwd")
         ctx.saved_buf = None
-        return (dx, None, *grads)
+        return (dx, None, None, None, *grads)
 
 
 class LinearFn(torch.autograd.Function):

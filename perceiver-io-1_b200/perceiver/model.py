@@ -7,8 +7,10 @@ that are deliberate and documented in DESIGN.md:
     by its (num_layers-1) applications (same weights, same input — reference model.py:186-187);
   * ``PerceiverMLM.forward`` uses the wiring the reference evidently intends (its own raises a
     TypeError, SURVEY.md §0) and only decodes the ``l`` queries it returns;
-  * dropout > 0 is only supported in eval mode (identity) for now; ``attn_mask`` is rejected
-    (no caller of the reference ever passes one).
+  * dropout > 0 (training mode) uses the kernels' own counter-based masks — same sites and scaling as
+    the reference (attention probabilities, Residual branch output), seeded from torch.initial_seed(),
+    but not torch's Philox stream, so parity at p > 0 is statistical; ``attn_mask`` is rejected (no
+    caller of the reference ever passes one).
 """
 from typing import Optional, Tuple
 
@@ -22,9 +24,9 @@ from .tokenizer import MASK_TOKEN, SPECIAL_TOKENS, UNK_TOKEN
 from .utils import Sequential
 
 
-def _no_dropout(module: nn.Module, p: float):
-    if p > 0.0 and module.training:
-        raise NotImplementedError('dropout > 0 in training mode is not implemented by the B200 kernels yet')
+def _active_p(module: nn.Module, p: float) -> float:
+    """dropout probability in effect: the module's p in training mode, 0 in eval mode"""
+    return float(p) if (module.training and p > 0.0) else 0.0
 
 
 def _no_attn_mask(attn_mask):
@@ -42,8 +44,10 @@ class MLP(Sequential):
     def _params(self):
         return (self[0].weight, self[0].bias, self[1].weight, self[1].bias, self[3].weight, self[3].bias)
 
-    def forward(self, x, residual: bool = False):
-        return F.MlpFn.apply(x, *self._params(), residual)
+    def forward(self, x, residual: bool = False, dropout_p: float = 0.0):
+        """``dropout_p`` is the enclosing Residual's dropout (only applied together with ``residual``)."""
+        seed = F.next_dropout_seed() if dropout_p else 0
+        return F.MlpFn.apply(x, *self._params(), residual, dropout_p, seed)
 
 
 def mlp(num_channels: int):
@@ -73,15 +77,16 @@ class CrossAttention(nn.Module):
         return F.KVProjectFn.apply(x_kv, self.kv_norm.weight, self.kv_norm.bias, a.in_proj_bias, w_packed, w_k, w_v,
                                    a.embed_dim)
 
-    def forward(self, x_q, x_kv, pad_mask=None, attn_mask=None, kv=None, residual: bool = False):
+    def forward(self, x_q, x_kv, pad_mask=None, attn_mask=None, kv=None, residual: bool = False, dropout_p=None):
         _no_attn_mask(attn_mask)
-        _no_dropout(self, self.dropout_p)
+        p = _active_p(self, self.dropout_p) if dropout_p is None else dropout_p
         a = self.attention.attention
         if kv is None:
             kv = self.project_kv(x_kv)
         w_packed, w_q, _, _ = a.packed()
+        seed = F.next_dropout_seed() if p else 0
         return F.CrossAttendFn.apply(x_q, kv, pad_mask, self.q_norm.weight, self.q_norm.bias, a.in_proj_bias, w_packed,
-                                     w_q, a.out_proj.weight, a.out_proj.bias, a.num_heads, residual)
+                                     w_q, a.out_proj.weight, a.out_proj.bias, a.num_heads, residual, p, seed)
 
 
 class SelfAttention(nn.Module):
@@ -96,12 +101,13 @@ class SelfAttention(nn.Module):
         a = self.attention.attention
         return (self.norm.weight, self.norm.bias, a.in_proj_weight, a.in_proj_bias, a.out_proj.weight, a.out_proj.bias)
 
-    def forward(self, x, pad_mask=None, attn_mask=None, residual: bool = False):
+    def forward(self, x, pad_mask=None, attn_mask=None, residual: bool = False, dropout_p=None):
         _no_attn_mask(attn_mask)
-        _no_dropout(self, self.dropout_p)
+        p = _active_p(self, self.dropout_p) if dropout_p is None else dropout_p
         if pad_mask is not None:
             raise NotImplementedError('SelfAttention with a pad mask is never reached in the reference model')
-        return F.SelfAttnFn.apply(x, *self._params(), self.attention.attention.num_heads, residual)
+        seed = F.next_dropout_seed() if p else 0
+        return F.SelfAttnFn.apply(x, *self._params(), self.attention.attention.num_heads, residual, p, seed)
 
 
 class Residual(nn.Module):
@@ -115,9 +121,10 @@ class Residual(nn.Module):
         self.dropout_p = dropout
 
     def forward(self, *args, **kwargs):
-        _no_dropout(self, self.dropout_p)
         if isinstance(self.module, (CrossAttention, SelfAttention, MLP)):
-            return self.module(*args, residual=True, **kwargs)
+            # one p for the module's own attention dropout and for this Residual's dropout, like the
+            # reference's cross_attention_layer / self_attention_layer constructors (model.py:29-40)
+            return self.module(*args, residual=True, dropout_p=_active_p(self, self.dropout_p), **kwargs)
         return self.dropout(self.module(*args, **kwargs)) + args[0]
 
 
@@ -138,11 +145,12 @@ class SelfAttentionBlock(Sequential):
         params = []
         for layer in self:
             sa, ff = layer[0], layer[1]
-            _no_dropout(sa, sa.dropout_p)
             params.extend(sa.module._params())
             params.extend(ff.module._params())
         heads = self[0][0].module.attention.attention.num_heads
-        return F.LatentBlockFn.apply(x, heads, *params)
+        p = _active_p(self, self[0][0].dropout_p)
+        seed = F.next_dropout_seed() if p else 0
+        return F.LatentBlockFn.apply(x, heads, p, seed, *params)
 
 
 def self_attention_block(num_layers: int, num_channels: int, num_heads: int, dropout: float):

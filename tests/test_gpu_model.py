@@ -246,13 +246,9 @@ def test_standalone_modules_without_residual():
     assert_rel(ff.to(DEV)(x.to(DEV)), O.mlp_residual(sd, "", x) - x, 1e-5, "mlp")
 
 
-def test_dropout_and_attn_mask_are_rejected_not_ignored():
+def test_attn_mask_is_rejected_not_ignored():
     from perceiver import PerceiverEncoder, TextInputAdapter
-    enc = PerceiverEncoder(TextInputAdapter(50, 8, 16), (4, 16), 1, 2, 2, 1, dropout=0.1).to(DEV)
+    enc = PerceiverEncoder(TextInputAdapter(50, 8, 16), (4, 16), 1, 2, 2, 1).to(DEV)
     ids = torch.randint(3, 50, (2, 8), device=DEV)
-    with pytest.raises(NotImplementedError):
-        enc(ids)
-    enc.eval()
-    enc(ids)  # identity dropout in eval
     with pytest.raises(NotImplementedError):
         enc(ids, None, torch.zeros(4, 8, device=DEV))
