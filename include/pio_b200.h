@@ -228,8 +228,7 @@ int pio_cross_entropy_bwd(const float* logits, const int64_t* labels, const floa
  * p == 0 = off.  Masks are a counter-based hash of (seed, element index): the backward call must get
  * the same struct as the forward call it differentiates; nothing is stored.  Each operator derives its
  * sites from `seed` (seed+0 attention probabilities, seed+1 residual; the latent block uses seed+4*layer
- * for the attention layer and seed+4*layer+2 for the MLP).  With attention dropout active the bf16
- * pipelines use the fp32-arithmetic attention kernels (the tensor-core ones carry no mask yet).
+ * for the attention layer and seed+4*layer+2 for the MLP).
  * torch's own Philox stream cannot be reproduced, so parity with the reference at p > 0 is statistical. */
 typedef struct {
     float p;

@@ -32,6 +32,7 @@ struct FaParams {
     int64_t o_bs, o_rs;
     int batch, heads, n, m;
     float scale_log2e;
+    DropCfg drop;  // dropout on the attention probabilities (threshold 0 = off)
 };
 
 __device__ __forceinline__ float fast_exp2(float x) {
@@ -68,7 +69,7 @@ __device__ __forceinline__ void store_row_half_bf16(uint8_t* region, int row, in
     }
 }
 
-template <int BKV>
+template <int BKV, bool DROP>
 __global__ void __launch_bounds__(FA_THREADS, 2)
     attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const FaParams p) {
@@ -243,6 +244,11 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                     pv[i] = fast_exp2(sv[half * 32 + i] - m_use);
                     l_tile += pv[i];
                 }
+                if constexpr (DROP) {  // the normaliser sees every key; only P.V sees the mask
+                    const uint64_t base = (((uint64_t)b * p.heads + h) * p.n + (uint64_t)(q0 + row)) * (uint64_t)p.m + (uint64_t)(j0 + half * 32);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) pv[i] = drop_keep(p.drop, base + i) ? pv[i] * p.drop.inv_keep : 0.f;
+                }
                 store_row_half_bf16(pbuf, row, half, pv);
             }
             l_run = l_run * alpha + l_tile;
@@ -308,6 +314,7 @@ struct FaBwdParams {
     int64_t o_bs, o_rs, q_bs, q_rs, k_bs, k_rs, v_bs, v_rs;
     int batch, heads, n, m;
     float scale, scale_log2e;
+    DropCfg drop;
 };
 
 __device__ __forceinline__ void store_row64_bf16_global(__nv_bfloat16* dst, const float (&v)[32], int c0) {
@@ -467,7 +474,12 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                     float e = __uint_as_float(rs[i]) * p.scale_log2e - lse2;
                     if (masked) e += bias[c0 + i];
                     const float pv = fast_exp2(e);
-                    ds[i] = pv * (__uint_as_float(rp[i]) - delta) * p.scale;
+                    float dpi = __uint_as_float(rp[i]);
+                    if (p.drop.threshold != 0) {
+                        const uint64_t idx = (((uint64_t)b * p.heads + h) * p.n + (uint64_t)qi) * (uint64_t)p.m + (uint64_t)(j0 + c0 + i);
+                        dpi = drop_keep(p.drop, idx) ? dpi * p.drop.inv_keep : 0.f;
+                    }
+                    ds[i] = pv * (dpi - delta) * p.scale;
                 }
                 store_row_half_bf16(sdS, row, c0 / 32, ds);
             }
@@ -630,8 +642,13 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
 #pragma unroll
                 for (int q = 0; q < 32; ++q) {
                     const float pr = dead_key ? 0.f : fast_exp2(__uint_as_float(rs[q]) * p.scale_log2e - lse_s[c0 + q]);
-                    pv[q] = pr;
-                    ds[q] = pr * (__uint_as_float(rp[q]) - del_s[c0 + q]) * p.scale;
+                    float keep_scale = 1.f;
+                    if (p.drop.threshold != 0) {
+                        const uint64_t idx = (((uint64_t)b * p.heads + h) * p.n + (uint64_t)(i * BQ2 + c0 + q)) * (uint64_t)p.m + (uint64_t)key;
+                        keep_scale = drop_keep(p.drop, idx) ? p.drop.inv_keep : 0.f;
+                    }
+                    pv[q] = pr * keep_scale;
+                    ds[q] = pr * (__uint_as_float(rp[q]) * keep_scale - del_s[c0 + q]) * p.scale;
                 }
                 store_row_half_bf16(sP, row, c0 / 32, pv);
                 store_row_half_bf16(sdS, row, c0 / 32, ds);
@@ -700,7 +717,7 @@ bool attn_fwd_tc_supported(const pio_attn_desc* d) {
 
 // q, k, v of the descriptor are bf16 (element strides as given); writes o (fp32, optional via d->o),
 // o16 (optional) and lse.
-int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st) {
+int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st, const DropCfg* drop) {
     PIO_CHECK_ARG(d && d->q && d->k && d->v && d->lse && (d->o || o16), "attn_fwd_tc: null pointer");
     PIO_CHECK_ARG(attn_fwd_tc_supported(d), "attn_fwd_tc: unsupported shape (head dim %d)", d->dh);
     PIO_CHECK_ARG(d->heads <= 65535 && d->batch <= 65535, "attn_fwd_tc: batch/heads exceed grid limits");
@@ -718,21 +735,24 @@ int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st) {
     p.o_bs = d->o_bs; p.o_rs = d->o_rs;
     p.batch = d->batch; p.heads = d->heads; p.n = d->n; p.m = d->m;
     p.scale_log2e = d->scale * 1.44269504088896340736f;
+    p.drop = drop ? *drop : DropCfg{0, 0, 1.f};
     const size_t smem = (size_t)FA_BQ * 64 * 2 + 6 * (size_t)BKV * 64 * 2 + 2 * (size_t)FA_BQ * BKV * 2 + 2 * BKV * 4 + 128 + 1024;
     static bool configured = false;
     if (!configured) {
-        PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = true;
     }
     dim3 grid((unsigned)cdiv(d->n, FA_BQ), (unsigned)d->heads, (unsigned)d->batch);
-    PIO_CUDA(launch_pdl(attn_fwd_tc_kernel<BKV>, grid, dim3(FA_THREADS), smem, st, tq, tk, tv, p));
+    if (p.drop.threshold != 0) PIO_CUDA(launch_pdl(attn_fwd_tc_kernel<BKV, true>, grid, dim3(FA_THREADS), smem, st, tq, tk, tv, p));
+    else PIO_CUDA(launch_pdl(attn_fwd_tc_kernel<BKV, false>, grid, dim3(FA_THREADS), smem, st, tq, tk, tv, p));
     count_launch();
     return PIO_OK;
 }
 
 // q, k, v, dO bf16; o fp32; lse fp32 -> dq16, dk16, dv16 (bf16, strides of q / k / v); delta scratch (batch, heads, n)
 int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta, __nv_bfloat16* dq16, __nv_bfloat16* dk16,
-                __nv_bfloat16* dv16, cudaStream_t st) {
+                __nv_bfloat16* dv16, cudaStream_t st, const DropCfg* drop) {
     PIO_CHECK_ARG(d && d->q && d->k && d->v && d->o && d->lse && do16 && delta && dq16 && dk16 && dv16, "attn_bwd_tc: null pointer");
     PIO_CHECK_ARG(attn_fwd_tc_supported(d), "attn_bwd_tc: unsupported shape (head dim %d)", d->dh);
     PIO_CHECK_ARG(d->heads <= 65535 && d->batch <= 65535, "attn_bwd_tc: batch/heads exceed grid limits");
@@ -745,6 +765,7 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
     p.batch = d->batch; p.heads = d->heads; p.n = d->n; p.m = d->m;
     p.scale = d->scale;
     p.scale_log2e = d->scale * 1.44269504088896340736f;
+    p.drop = drop ? *drop : DropCfg{0, 0, 1.f};
     static bool configured = false;
     const size_t smem_dq = 2 * 16384 + 4 * 8192 + 16384 + 2 * 64 * 4 + 128 + 1024;
     const size_t smem_dkv = 2 * 16384 + 4 * 8192 + 2 * 16384 + 4 * 64 * 4 + 128 + 1024;
@@ -786,5 +807,5 @@ extern "C" int pio_attn_bwd_bf16(const pio_attn_desc* fwd, const void* d_o16, vo
         return PIO_ERR_UNSUPPORTED;
     }
     return pio::attn_bwd_tc(fwd, (const __nv_bfloat16*)d_o16, delta, (__nv_bfloat16*)dq16, (__nv_bfloat16*)dk16,
-                            (__nv_bfloat16*)dv16, (cudaStream_t)stream);
+                            (__nv_bfloat16*)dv16, (cudaStream_t)stream, nullptr);
 }

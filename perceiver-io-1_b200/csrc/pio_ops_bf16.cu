@@ -295,7 +295,7 @@ static void fill_attn(pio_attn_desc& a, const bf16* q, int64_t q_rs, const bf16*
 // bf16 q/k/v -> o (fp32 + bf16) and lse: tensor-core flash kernel when the head size allows, else
 // the fp32-arithmetic kernel reading the same bf16 operands
 static int attention_fwd(const pio_attn_desc& a, bf16* o16, cudaStream_t st, const DropCfg& drop) {
-    if (drop.threshold == 0 && attn_fwd_tc_supported(&a)) return attn_fwd_tc(&a, o16, st);
+    if (attn_fwd_tc_supported(&a)) return attn_fwd_tc(&a, o16, st, &drop);
     AttnBf16Out ex;
     ex.o16 = o16;
     ex.in16 = 1;
@@ -366,10 +366,10 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.q, e, kv16, kv16 + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
     const DropCfg adrop = c.attn_drop();
-    if (adrop.threshold == 0 && attn_fwd_tc_supported(&b.fwd)) {
+    if (attn_fwd_tc_supported(&b.fwd)) {
         bf16* d_o16 = reinterpret_cast<bf16*>(d_o);  // the fp32 scratch is large enough for the bf16 tile
         PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)w->wo, e, rows, e, e, nullptr, 0, d_o16, e, 0, nullptr, 0, 0));
-        PIO_TRY(attn_bwd_tc(&b.fwd, d_o16, delta, dq16, dkv16, dkv16 + e, c.st));
+        PIO_TRY(attn_bwd_tc(&b.fwd, d_o16, delta, dq16, dkv16, dkv16 + e, c.st, &adrop));
     } else {
         PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)w->wo, e, rows, e, e, d_o, e, nullptr, 0, 0, nullptr, 0, 0));
         b.d_o = d_o; b.delta = delta;
@@ -463,10 +463,10 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
     const DropCfg adrop = c.attn_drop();
-    if (adrop.threshold == 0 && attn_fwd_tc_supported(&b.fwd)) {
+    if (attn_fwd_tc_supported(&b.fwd)) {
         bf16* d_o16 = reinterpret_cast<bf16*>(d_o);
         PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->wo, ch, rows, ch, ch, nullptr, 0, d_o16, ch, 0, nullptr, 0, 0));
-        PIO_TRY(attn_bwd_tc(&b.fwd, d_o16, delta, dqkv16, dqkv16 + ch, dqkv16 + 2 * ch, c.st));
+        PIO_TRY(attn_bwd_tc(&b.fwd, d_o16, delta, dqkv16, dqkv16 + ch, dqkv16 + 2 * ch, c.st, &adrop));
     } else {
         PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->wo, ch, rows, ch, ch, d_o, ch, nullptr, 0, 0, nullptr, 0, 0));
         b.d_o = d_o; b.delta = delta;

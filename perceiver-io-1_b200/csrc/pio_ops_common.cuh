@@ -18,10 +18,10 @@ int attn_bwd_simt(const pio_attn_bwd_desc* d, cudaStream_t st, const AttnBf16Out
 
 // tcgen05 flash attention forward (pio_attn_tc.cu): q, k, v of the descriptor are bf16
 bool attn_fwd_tc_supported(const pio_attn_desc* d);
-int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st);
+int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st, const DropCfg* drop = nullptr);
 // tcgen05 backward: dO bf16 (strides of o), gradients bf16 with the strides of q / k / v
 int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta, __nv_bfloat16* dq16, __nv_bfloat16* dk16,
-                __nv_bfloat16* dv16, cudaStream_t st);
+                __nv_bfloat16* dv16, cudaStream_t st, const DropCfg* drop = nullptr);
 
 int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream_t st);
 int cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_src, int64_t ld_dst, cudaStream_t st);
