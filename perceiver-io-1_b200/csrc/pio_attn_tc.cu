@@ -331,6 +331,7 @@ __device__ __forceinline__ void store_row64_bf16_global(__nv_bfloat16* dst, cons
 }
 
 // dQ: CTA = 128 query rows of one (batch, head); streams key tiles of 64.
+template <bool DROP>
 __global__ void __launch_bounds__(FA_THREADS, 2)
     attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                           const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const FaBwdParams p) {
@@ -475,7 +476,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                     if (masked) e += bias[c0 + i];
                     const float pv = fast_exp2(e);
                     float dpi = __uint_as_float(rp[i]);
-                    if (p.drop.threshold != 0) {
+                    if constexpr (DROP) {
                         const uint64_t idx = (((uint64_t)b * p.heads + h) * p.n + (uint64_t)qi) * (uint64_t)p.m + (uint64_t)(j0 + c0 + i);
                         dpi = drop_keep(p.drop, idx) ? dpi * p.drop.inv_keep : 0.f;
                     }
@@ -514,6 +515,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
 // dK, dV: CTA = 128 key rows of one (batch, head); streams query tiles of 64.  Works on the
 // transposed score tile S^T = K Q^T (thread = key row, column = query), so P^T and dS^T come out in
 // exactly the K-major layout the dV = P^T dO and dK = dS^T Q products read.
+template <bool DROP>
 __global__ void __launch_bounds__(FA_THREADS, 2)
     attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                            const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const FaBwdParams p) {
@@ -643,7 +645,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                 for (int q = 0; q < 32; ++q) {
                     const float pr = dead_key ? 0.f : fast_exp2(__uint_as_float(rs[q]) * p.scale_log2e - lse_s[c0 + q]);
                     float keep_scale = 1.f;
-                    if (p.drop.threshold != 0) {
+                    if constexpr (DROP) {
                         const uint64_t idx = (((uint64_t)b * p.heads + h) * p.n + (uint64_t)(i * BQ2 + c0 + q)) * (uint64_t)p.m + (uint64_t)key;
                         keep_scale = drop_keep(p.drop, idx) ? p.drop.inv_keep : 0.f;
                     }
@@ -770,8 +772,10 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
     const size_t smem_dq = 2 * 16384 + 4 * 8192 + 16384 + 2 * 64 * 4 + 128 + 1024;
     const size_t smem_dkv = 2 * 16384 + 4 * 8192 + 2 * 16384 + 4 * 64 * 4 + 128 + 1024;
     if (!configured) {
-        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dq));
-        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dkv));
+        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dq));
+        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dq));
+        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dkv));
+        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dkv));
         configured = true;
     }
     {   // dQ + delta: 128-row query tiles, 64-row key tiles
@@ -781,7 +785,8 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
         PIO_TRY(make_tmap3(&tk, d->k, cols, d->m, d->batch, d->k_rs, d->k_bs, 64));
         PIO_TRY(make_tmap3(&tv, d->v, cols, d->m, d->batch, d->v_rs, d->v_bs, 64));
         dim3 grid((unsigned)cdiv(d->n, FA_BQ), (unsigned)d->heads, (unsigned)d->batch);
-        PIO_CUDA(launch_pdl(attn_bwd_dq_tc_kernel, grid, dim3(FA_THREADS), smem_dq, st, tq, tdo, tk, tv, p));
+        if (p.drop.threshold != 0) PIO_CUDA(launch_pdl(attn_bwd_dq_tc_kernel<true>, grid, dim3(FA_THREADS), smem_dq, st, tq, tdo, tk, tv, p));
+        else PIO_CUDA(launch_pdl(attn_bwd_dq_tc_kernel<false>, grid, dim3(FA_THREADS), smem_dq, st, tq, tdo, tk, tv, p));
         count_launch();
     }
     {   // dK, dV: 128-row key tiles, 64-row query tiles
@@ -791,7 +796,8 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
         PIO_TRY(make_tmap3(&tk, d->k, cols, d->m, d->batch, d->k_rs, d->k_bs, 128));
         PIO_TRY(make_tmap3(&tv, d->v, cols, d->m, d->batch, d->v_rs, d->v_bs, 128));
         dim3 grid((unsigned)cdiv(d->m, 128), (unsigned)d->heads, (unsigned)d->batch);
-        PIO_CUDA(launch_pdl(attn_bwd_dkv_tc_kernel, grid, dim3(FA_THREADS), smem_dkv, st, tq, tdo, tk, tv, p));
+        if (p.drop.threshold != 0) PIO_CUDA(launch_pdl(attn_bwd_dkv_tc_kernel<true>, grid, dim3(FA_THREADS), smem_dkv, st, tq, tdo, tk, tv, p));
+        else PIO_CUDA(launch_pdl(attn_bwd_dkv_tc_kernel<false>, grid, dim3(FA_THREADS), smem_dkv, st, tq, tdo, tk, tv, p));
         count_launch();
     }
     return PIO_OK;

@@ -322,7 +322,7 @@ def test_bad_arguments_return_errors_not_crashes(N):
     # workspace too small must be reported, not overrun
     saved = torch.empty(L.pio_mlp_saved_bytes(4, 8, 0), dtype=torch.uint8, device=DEV)
     rc = L.pio_mlp_bwd(x.data_ptr(), x.data_ptr(), x.data_ptr(), ctypes.byref(w), saved.data_ptr(), ctypes.byref(w), 0, 4, 8, 1,
-                       0, None, 0, N.stream_ptr())
+                       None, 0, None, 0, N.stream_ptr())
     assert rc == 3 and b"workspace" in L.pio_last_error()
     with pytest.raises(RuntimeError, match="pio_b200 error"):
         N.check(rc, "pio_mlp_bwd")
