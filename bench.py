@@ -453,6 +453,25 @@ def gpu_arm(args):
         launches += graph_launches * args.steps  # replays do not pass through the host-side counter
     clocks = sampler.stop() if rank == 0 else None
     if args.profile_only:
+        if rank == 0 and args.timeline:
+            from torch.profiler import ProfilerActivity, profile
+            with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                for _ in range(2):
+                    step(ids_d, pad_d)
+                torch.cuda.synchronize()
+            import csv as _csv
+            import json as _json
+            tmp = args.timeline + ".trace.json"
+            prof.export_chrome_trace(tmp)
+            evs = [e for e in _json.load(open(tmp))["traceEvents"] if e.get("cat") in ("kernel", "gpu_memcpy", "gpu_memset")]
+            os.remove(tmp)
+            evs.sort(key=lambda e: e["ts"])
+            with open(args.timeline, "w", newline="") as f:
+                w = _csv.writer(f)
+                w.writerow(["stream", "start_us", "dur_us", "kernel"])
+                t0 = evs[0]["ts"] if evs else 0
+                for e in evs:
+                    w.writerow([e["args"].get("stream"), round(e["ts"] - t0, 3), round(e["dur"], 3), e["name"][:100]])
         if rank == 0:
             print(json.dumps({"profile_only": True, "ms_per_step": total_ms / args.steps, "gpu_launches": int(launches)}))
         if distributed:
@@ -544,6 +563,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="do not capture the step into a CUDA graph")
     ap.add_argument("--profile-only", action="store_true", help="timed steps only (for ncu launch lists)")
+    ap.add_argument("--timeline", default=None, help="with --profile-only: CSV of (stream, start_us, dur_us, kernel) of 2 more steps")
     ap.add_argument("--mode", default=os.environ.get("PIO_MODE", "bf16"), choices=["fp32", "bf16"])
     args = ap.parse_args()
     if args.impl == "reference":

@@ -169,6 +169,19 @@ size_t pio_gemm_bf16_ws_bytes(int64_t m, int64_t n, int64_t k);
 /* fp32 (rows, cols; pitch ld_src) -> bf16 with pitch ld_dst >= cols (pad columns zero-filled). */
 int pio_cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_src, int64_t ld_dst,
                   pio_stream_t stream);
+/* The same cast for a whole set of weight matrices in ONE launch: `items` is a table of `count`
+ * entries in DEVICE memory (src is dense, pitch = cols; only the cols real columns of dst are
+ * written, so dst's pad columns must have been zeroed once, e.g. by pio_cast_bf16).  Refreshes the
+ * bf16 weight shadows after an optimizer step (reference lightning.py:67-72 steps torch optimizers,
+ * some of which update parameters without moving their version counters). */
+typedef struct {
+    const float* src;
+    void* dst;
+    int64_t rows;
+    int32_t cols;
+    int32_t ld_dst;
+} pio_cast_item;
+int pio_cast_bf16_multi(const pio_cast_item* items, int count, pio_stream_t stream);
 
 /* Attention core of nn.MultiheadAttention as called at model.py:74 (dropout 0):
  * S = (q dh^-1/2) k^T, padded keys -> -inf, P = softmax(S), O = P v.  Flash-style: P is never

@@ -279,10 +279,13 @@ __global__ void layernorm_fwd_kernel(const float* __restrict__ x, const float* _
     }
 }
 
-// dx per row (warp per row) + per-block partial sums of dgamma/dbeta (deterministic, no atomics):
-// partial layout [gridDim.x][2][c].
+// dx per row (warp per row) + per-block sums of dgamma/dbeta, either written as partials
+// [gridDim.x][2][c] for a deterministic second pass or added to dgamma/dbeta with one atomic per
+// column per block.  The grid gives every warp one row where it can (this kernel is a chain of
+// dependent latencies, not a bandwidth problem, at the latent sizes): all three row loads (dy, x and
+// the residual gradient) are issued before the first reduction.
 template <int NCH>
-__global__ void __launch_bounds__(256) layernorm_bwd_kernel(
+__global__ void __launch_bounds__(NCH <= 8 ? 512 : 256, NCH <= 16 ? 2 : 1) layernorm_bwd_kernel(
     const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ stats,
     const float* __restrict__ w, const float* __restrict__ dres, float* __restrict__ dx,
     float* __restrict__ partial, int64_t rows, int c, float* __restrict__ atomic_dw = nullptr,
@@ -291,45 +294,45 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(
     pdl_trigger();
     pdl_wait();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    float gw[NCH], gb[NCH], wv[NCH];
+    float gw[NCH], gb[NCH];
 #pragma unroll
     for (int i = 0; i < NCH; ++i) {
         gw[i] = 0.f;
         gb[i] = 0.f;
-        const int j = lane + 32 * i;
-        wv[i] = (j < c) ? __ldg(w + j) : 0.f;
     }
     const float inv_c = 1.0f / (float)c;
     for (int64_t r = (int64_t)blockIdx.x * nw + wid; r < rows; r += (int64_t)gridDim.x * nw) {
-        const float mean = stats[2 * r], rstd = stats[2 * r + 1];
         const float* dyr = dy + r * c;
         const float* xr = x + r * c;
-        float g[NCH], xh[NCH];
+        float d[NCH], xh[NCH], rs[NCH];
+#pragma unroll
+        for (int i = 0; i < NCH; ++i) {
+            const int j = lane + 32 * i;
+            const bool in = j < c;
+            d[i] = in ? dyr[j] : 0.f;
+            xh[i] = in ? xr[j] : 0.f;
+            rs[i] = (in && dres != nullptr) ? dres[r * c + j] : 0.f;
+        }
+        const float mean = stats[2 * r], rstd = stats[2 * r + 1];
         float c1 = 0.f, c2 = 0.f;
 #pragma unroll
         for (int i = 0; i < NCH; ++i) {
             const int j = lane + 32 * i;
-            float d = 0.f, xv = mean;
-            if (j < c) {
-                d = dyr[j];
-                xv = xr[j];
-            }
-            xh[i] = (xv - mean) * rstd;
-            g[i] = d * wv[i];
-            gw[i] += d * xh[i];
-            gb[i] += d;
-            c1 += g[i];
-            c2 += g[i] * xh[i];
+            const bool in = j < c;
+            xh[i] = in ? (xh[i] - mean) * rstd : 0.f;
+            gw[i] += d[i] * xh[i];
+            gb[i] += d[i];
+            d[i] *= in ? __ldg(w + j) : 0.f;  // g = dy * gamma
+            c1 += d[i];
+            c2 += d[i] * xh[i];
         }
         c1 = warp_sum(c1) * inv_c;
         c2 = warp_sum(c2) * inv_c;
+        if (dx != nullptr) {
 #pragma unroll
-        for (int i = 0; i < NCH; ++i) {
-            const int j = lane + 32 * i;
-            if (j < c) {
-                float v = rstd * (g[i] - c1 - xh[i] * c2);
-                if (dres != nullptr) v += dres[r * c + j];
-                if (dx != nullptr) dx[r * c + j] = v;
+            for (int i = 0; i < NCH; ++i) {
+                const int j = lane + 32 * i;
+                if (j < c) dx[r * c + j] = rstd * (d[i] - c1 - xh[i] * c2) + rs[i];
             }
         }
     }
@@ -368,10 +371,42 @@ __global__ void reduce_partials_kernel(const float* __restrict__ part, int split
     }
 }
 
+// The same reduction for few outputs and many partial rows (LayerNorm / bias gradients): a block owns 32
+// outputs, its 32 warps stride over the partial rows, shared memory folds the 32 sub-sums in a fixed order.
+__global__ void __launch_bounds__(1024) reduce_partials_tall_kernel(const float* __restrict__ part, int splits, int64_t stride,
+                                                                    float* __restrict__ out1, int64_t n1,
+                                                                    float* __restrict__ out2, int64_t n2, int accumulate) {
+    __shared__ float sub[32][33];
+    pdl_trigger();
+    pdl_wait();
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int64_t i = (int64_t)blockIdx.x * 32 + tx;
+    const int64_t total = n1 + n2;
+    float acc = 0.f;
+    if (i < total)
+        for (int s = ty; s < splits; s += 32) acc += part[(int64_t)s * stride + i];
+    sub[ty][tx] = acc;
+    __syncthreads();
+    if (ty == 0 && i < total) {
+        float v = 0.f;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) v += sub[k][tx];
+        float* dst = (i < n1) ? (out1 + i) : (out2 + (i - n1));
+        if (accumulate) v += *dst;
+        *dst = v;
+    }
+}
+
 int reduce_partials(const float* part, int splits, int64_t stride, float* out1, int64_t n1, float* out2,
                     int64_t n2, int accumulate, cudaStream_t st) {
     const int64_t total = n1 + n2;
     if (total <= 0) return PIO_OK;
+    if (splits >= 32 && total <= 32 * (int64_t)num_sms() * 2) {
+        PIO_CUDA(launch_pdl(reduce_partials_tall_kernel, dim3((unsigned)cdiv(total, 32)), dim3(1024), 0, st, part, splits, stride, out1,
+                            n1, out2, n2, accumulate));
+        count_launch();
+        return PIO_OK;
+    }
     const int threads = 256;
     const int blocks = (int)std::min<int64_t>(cdiv(total, threads), (int64_t)num_sms() * 8);
     PIO_CUDA(launch_pdl(reduce_partials_kernel, dim3(blocks), dim3(threads), 0, st, part, splits, stride, out1, n1, out2, n2, accumulate));
@@ -641,12 +676,13 @@ int pio_layernorm_fwd(const float* x, const float* w, const float* b, float* y, 
     return PIO_OK;
 }
 
-static int ln_bwd_blocks(int64_t rows) {
-    return (int)std::max<int64_t>(1, std::min<int64_t>(cdiv(rows, 8), (int64_t)pio::num_sms() * 2));
+static int ln_bwd_warps(int c) { return c <= 256 ? 16 : 8; }  // matches the kernel's launch bounds per NCH
+static int ln_bwd_blocks(int64_t rows, int c) {
+    return (int)std::max<int64_t>(1, std::min<int64_t>(cdiv(rows, ln_bwd_warps(c)), (int64_t)pio::num_sms() * 4));
 }
 
 size_t pio_layernorm_bwd_ws_bytes(int64_t rows, int c) {
-    return align_up((size_t)ln_bwd_blocks(rows) * 2 * c * sizeof(float), 256) + 256;
+    return align_up((size_t)ln_bwd_blocks(rows, c) * 2 * c * sizeof(float), 256) + 256;
 }
 
 int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const float* w, const float* dres,
@@ -656,7 +692,7 @@ int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const
     PIO_CHECK_ARG(c <= 1024, "pio_layernorm_bwd: channels %d > 1024 unsupported", c);
     if (rows == 0) return PIO_OK;
     Workspace W(ws, ws_bytes);
-    const int blocks = ln_bwd_blocks(rows);
+    const int blocks = ln_bwd_blocks(rows, c);
     const bool atomic = (accumulate == 2);  // dw / db hold a running sum (or zeros): add with atomics, no reduction pass
     float* partial = atomic ? nullptr : W.takef((size_t)blocks * 2 * c);
     if (!partial && !atomic) {
@@ -666,13 +702,14 @@ int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const
     float* adw = atomic ? dw : nullptr;
     float* adb = atomic ? db : nullptr;
     cudaStream_t st = (cudaStream_t)stream;
-    const size_t smem = (size_t)8 * 2 * c * sizeof(float);
+    const int warps = ln_bwd_warps(c);
+    const size_t smem = (size_t)warps * 2 * c * sizeof(float);
 #define PIO_LN_BWD(NCH)                                                                                         \
     do {                                                                                                        \
         if (smem > 48 * 1024)                                                                                   \
             PIO_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                           (int)smem));                                                          \
-        PIO_CUDA(launch_pdl(layernorm_bwd_kernel<NCH>, dim3(blocks), dim3(256), smem, st, dy, x, stats, w, dres, dx, partial, rows, c, adw, \
+        PIO_CUDA(launch_pdl(layernorm_bwd_kernel<NCH>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, c, adw, \
                             adb));                                                                              \
     } while (0)
     if (c <= 128) PIO_LN_BWD(4);

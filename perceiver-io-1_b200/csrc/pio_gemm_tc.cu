@@ -489,11 +489,52 @@ int cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_sr
     return PIO_OK;
 }
 
+// one launch for a table of matrices: blockIdx.y = table entry, blockIdx.x strides over its elements
+__global__ void cast_bf16_multi_kernel(const pio_cast_item* __restrict__ items) {
+    pdl_trigger();
+    pdl_wait();
+    const pio_cast_item it = items[blockIdx.y];
+    const float* __restrict__ src = it.src;
+    __nv_bfloat16* __restrict__ dst = (__nv_bfloat16*)it.dst;
+    const int64_t total = it.rows * it.cols;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    if (it.cols == it.ld_dst && (it.cols & 3) == 0) {  // dense: 4 elements per thread per trip
+        const int64_t n4 = total >> 2;
+        for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += stride) {
+            const float4 v = reinterpret_cast<const float4*>(src)[i];
+            __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+            uint2 o;
+            o.x = *reinterpret_cast<uint32_t*>(&lo);
+            o.y = *reinterpret_cast<uint32_t*>(&hi);
+            reinterpret_cast<uint2*>(dst)[i] = o;
+        }
+        return;
+    }
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += stride) {
+        const int64_t r = i / it.cols;
+        const int c = (int)(i - r * it.cols);
+        dst[r * it.ld_dst + c] = __float2bfloat16(src[i]);
+    }
+}
+
+int cast_bf16_multi(const pio_cast_item* items, int count, cudaStream_t st) {
+    PIO_CHECK_ARG(count >= 0 && (items || count == 0), "pio_cast_bf16_multi: bad arguments");
+    if (count == 0) return PIO_OK;
+    PIO_CHECK_ARG(count <= 65535, "pio_cast_bf16_multi: at most 65535 entries per call");
+    PIO_CUDA(launch_pdl(cast_bf16_multi_kernel, dim3(64, count), dim3(256), 0, st, items));
+    count_launch();
+    return PIO_OK;
+}
+
 }  // namespace pio
 
 using namespace pio;
 
 extern "C" {
+
+int pio_cast_bf16_multi(const pio_cast_item* items, int count, pio_stream_t stream) {
+    return cast_bf16_multi(items, count, (cudaStream_t)stream);
+}
 
 size_t pio_gemm_bf16_ws_bytes(int64_t m, int64_t n, int64_t k) {
     int bn, splits, kb_per;

@@ -5,6 +5,7 @@ autograd graph.  Saved-for-backward state is an opaque byte buffer whose layout 
 library knows (pio_*_saved_bytes).
 """
 import ctypes
+import weakref
 from ctypes import byref
 
 import torch
@@ -61,30 +62,118 @@ def _saved(nbytes, device):
 
 
 def invalidate_weight_cache(module=None):
-    """Drop bf16 weight shadows (only needed after writing through ``param.data``, which does not
-    bump the version counter the shadows are keyed on)."""
+    """Drop bf16 weight shadows (only needed after writing a frozen parameter through ``param.data``
+    outside training; trainable parameters are re-cast on every training forward anyway)."""
     if module is not None:
+        _TABLES.pop(module, None)
         for p in module.parameters():
             if hasattr(p, "_pio_w16"):
                 del p._pio_w16
 
 
-def _w16(w):
-    """bf16 shadow of a 2-D fp32 weight, row pitch padded to 8 elements (TMA).  The shadow lives on
-    the parameter object itself and is rebuilt whenever the parameter's version counter moves
-    (optimizer step, load_state_dict, .to())."""
-    hit = getattr(w, "_pio_w16", None)
-    if hit is not None and hit[0] == w._version and hit[1] == w.data_ptr():
-        return hit[2]
+# bf16 weight shadows.  A shadow is valid for ONE training forward: optimizers such as
+# torch.optim.AdamW(fused=True) update parameters without moving their version counters, so "version
+# unchanged" proves nothing for a trainable parameter.  Model-level forwards open a `shadow_scope`; the
+# first one records which matrices were shadowed, every later one re-casts all of them with a single
+# pio_cast_bf16_multi launch (in place: the buffers keep their addresses, so captured graphs stay valid).
+# Frozen parameters and no-grad forwards keep the version-keyed cache.
+_SH = {"epoch": 0, "depth": 0, "seen": None, "grad": True}
+_TABLES = weakref.WeakKeyDictionary()  # top-level module -> (key, device table, weights)
+
+
+def _trainable(w):
+    """may an optimizer have touched `w` since its shadow was made?  Grad mode is read where the scope was
+    opened (inside autograd.Function.forward it is always off); outside any scope assume yes."""
+    return w.requires_grad and (_SH["grad"] if _SH["depth"] > 0 else True)
+
+
+def _cast_one(w, out):
     rows, cols = w.shape
     ld = (cols + 7) // 8 * 8
-    out = torch.empty(rows, ld, dtype=torch.bfloat16, device=w.device)
+    if out is None or out.shape != (rows, ld) or out.device != w.device:
+        out = torch.empty(rows, ld, dtype=torch.bfloat16, device=w.device)
     N.check(N.lib().pio_cast_bf16(w.data_ptr(), out.data_ptr(), rows, cols, cols, ld, N.stream_ptr(w.device)), "pio_cast_bf16")
-    try:
-        w._pio_w16 = (w._version, w.data_ptr(), out)
-    except Exception:
-        pass
     return out
+
+
+def _w16(w):
+    """bf16 shadow of a 2-D fp32 weight, row pitch padded to 8 elements (TMA); lives on the parameter
+    object.  Entry = (version, data_ptr, shadow, epoch, made_in_training)."""
+    hit = getattr(w, "_pio_w16", None)
+    train = _trainable(w)
+    epoch = _SH["epoch"] if _SH["depth"] > 0 else None
+    same = hit is not None and hit[0] == w._version and hit[1] == w.data_ptr()
+    if same and ((train and epoch is not None and hit[3] == epoch) or (not train and not hit[4])):
+        out = hit[2]
+    else:
+        out = _cast_one(w, hit[2] if hit is not None else None)
+        try:
+            w._pio_w16 = (w._version, w.data_ptr(), out, epoch, train)
+        except Exception:
+            pass
+    if train and _SH["seen"] is not None:
+        _SH["seen"][id(w)] = w
+    return out
+
+
+def _refresh_shadows(module, epoch):
+    """one launch re-casting every matrix the previous training forward of `module` shadowed"""
+    tab = _TABLES.get(module)
+    if tab is None:
+        return
+    _, table, weights = tab
+    for w in weights:
+        hit = getattr(w, "_pio_w16", None)
+        if hit is None or hit[1] != w.data_ptr() or not w.requires_grad or w.device != table.device:
+            _TABLES.pop(module, None)  # parameters were replaced / moved / frozen: start over
+            return
+    N.check(N.lib().pio_cast_bf16_multi(table.data_ptr(), len(weights), N.stream_ptr(table.device)), "pio_cast_bf16_multi")
+    for w in weights:
+        w._pio_w16 = (w._version, w.data_ptr(), w._pio_w16[2], epoch, True)
+
+
+def _remember_shadows(module, seen):
+    weights = [w for w in seen.values() if getattr(w, "_pio_w16", None) is not None]
+    if not weights:
+        return
+    key = tuple((id(w), w.data_ptr(), w._pio_w16[2].data_ptr()) for w in weights)
+    tab = _TABLES.get(module)
+    if tab is not None and tab[0] == key:
+        return
+    dev = weights[0].device
+    if any(w.device != dev for w in weights) or torch.cuda.is_current_stream_capturing():
+        return
+    rows = []
+    for w in weights:
+        out = w._pio_w16[2]
+        rows.append([w.data_ptr(), out.data_ptr(), w.shape[0], w.shape[1] | (out.shape[1] << 32)])  # pio_cast_item
+    table = torch.tensor(rows, dtype=torch.int64).to(dev)
+    _TABLES[module] = (key, table, weights)
+
+
+class shadow_scope:
+    """Opened by the model-level forwards (PerceiverIO, PerceiverMLM, encoder, decoder); nests."""
+
+    def __init__(self, module):
+        self.module = module
+
+    def __enter__(self):
+        _SH["depth"] += 1
+        if _SH["depth"] == 1:
+            _SH["grad"] = torch.is_grad_enabled()
+        if _SH["depth"] == 1 and _MODE["mode"] == N.MODE_BF16 and _SH["grad"]:
+            _SH["epoch"] += 1
+            _SH["seen"] = {}
+            _refresh_shadows(self.module, _SH["epoch"])
+        return self
+
+    def __exit__(self, *exc):
+        _SH["depth"] -= 1
+        if _SH["depth"] == 0:
+            seen, _SH["seen"] = _SH["seen"], None
+            if seen and exc[0] is None:
+                _remember_shadows(self.module, seen)
+        return False
 
 
 def _mat(w, mode):

@@ -24,6 +24,17 @@ from .tokenizer import MASK_TOKEN, SPECIAL_TOKENS, UNK_TOKEN
 from .utils import Sequential
 
 
+def _scoped(forward):
+    """run a model-level forward inside a bf16 weight-shadow scope (functional.shadow_scope)"""
+    import functools
+
+    @functools.wraps(forward)
+    def wrapped(self, *args, **kwargs):
+        with F.shadow_scope(self):
+            return forward(self, *args, **kwargs)
+    return wrapped
+
+
 def _active_p(module: nn.Module, p: float) -> float:
     """dropout probability in effect: the module's p in training mode, 0 in eval mode"""
     return float(p) if (module.training and p > 0.0) else 0.0
@@ -193,6 +204,7 @@ class PerceiverEncoder(nn.Module):
         x_latent = cross[1](x_latent)
         return block(x_latent)
 
+    @_scoped
     def forward(self, x, pad_mask=None, attn_mask=None):
         b = x.shape[0]
         x = self.input_adapter(x)
@@ -232,6 +244,7 @@ class PerceiverDecoder(nn.Module):
         q = q.unsqueeze(0).expand(b, -1, -1).contiguous()
         return self.cross_attention(q, x)  # no mask on the latents, as in the reference
 
+    @_scoped
     def forward(self, x, pad_mask=None, num_queries: Optional[int] = None):
         return self.output_adapter(self.decode(x, num_queries))  # pad_mask is accepted and unused, as in the reference
 
@@ -267,6 +280,7 @@ class PerceiverMLM(nn.Module):
         self.decoder = decoder
         self.masking = masking
 
+    @_scoped
     def forward(self, x_input, pad_mask=None, masking=True, return_loss=False, labels=None):
         """-> (logits[:, :l], labels) like the reference.  ``return_loss=True`` (training) returns
         (loss, labels) instead: the vocabulary projection and the cross-entropy of
@@ -292,3 +306,7 @@ class PerceiverMLM(nn.Module):
 class PerceiverIO(Sequential):
     def __init__(self, encoder: PerceiverEncoder, decoder: PerceiverDecoder):
         super().__init__(encoder, decoder)
+
+    @_scoped
+    def forward(self, *inputs):
+        return super().forward(*inputs)

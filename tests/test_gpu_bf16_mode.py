@@ -207,3 +207,50 @@ def test_config4_long_input_shape_bf16():
     y = torch.randint(0, 2, (b,))
     _vs_oracle("text", PerceiverIO(enc, dec), ids, pad, y,
                dict(num_layers=2, cross_heads=8, self_heads=4, sa_layers=2, dec_heads=1))
+
+
+def test_bf16_shadows_follow_fused_optimizer_steps():
+    """torch.optim.AdamW(fused=True) updates parameters WITHOUT moving their version counters, so the bf16
+    weight shadows must be re-cast on every training forward (one pio_cast_bf16_multi launch from the second
+    forward on), in place, and must equal the current fp32 weights rounded to bf16."""
+    import perceiver
+    from perceiver import functional as F
+    from perceiver import _native as N
+    perceiver.set_compute_mode("bf16")
+    try:
+        torch.manual_seed(0)
+        meta = dict(vocab=503, seq=64, latent=(16, 64), layers=2, sa=2)
+        from perceiver import (PerceiverDecoder, PerceiverEncoder, PerceiverMLM, TextInputAdapter, TextMasking,
+                               TextOutputAdapter)
+        enc = PerceiverEncoder(TextInputAdapter(meta["vocab"], meta["seq"], 64), meta["latent"], meta["layers"], 4, 4, meta["sa"])
+        dec = PerceiverDecoder(TextOutputAdapter(meta["vocab"], meta["seq"], num_output_channels=64), meta["latent"], 4)
+        model = PerceiverMLM(enc, dec, TextMasking(meta["vocab"], 1, 2, 3)).cuda()
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-2, fused=True)
+        ids = torch.randint(3, meta["vocab"], (8, meta["seq"]), device="cuda")
+        pad = torch.zeros(8, meta["seq"], dtype=torch.bool, device="cuda")
+        ptrs = None
+        for it in range(4):
+            before = N.lib().pio_launch_count()
+            loss, _ = model(ids.clone(), pad, return_loss=True)
+            shadowed = [p for p in model.parameters() if getattr(p, "_pio_w16", None) is not None]
+            assert len(shadowed) >= 10
+            for p in shadowed:
+                cols = p.shape[1]
+                assert torch.equal(p._pio_w16[2][:, :cols], p.detach().to(torch.bfloat16)), f"stale shadow at step {it}"
+                assert not p._pio_w16[2][:, cols:].any()
+            now = [p._pio_w16[2].data_ptr() for p in shadowed]
+            if ptrs is not None:
+                assert now == ptrs  # refreshed in place
+            ptrs = now
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
+        assert model in F._TABLES and len(F._TABLES[model][2]) == len(shadowed)
+        # eval after the last optimizer step must not reuse the last training forward's shadows
+        model.eval()
+        with torch.no_grad():
+            model(ids.clone(), pad)
+            for p in shadowed:
+                assert torch.equal(p._pio_w16[2][:, :p.shape[1]], p.detach().to(torch.bfloat16))
+    finally:
+        perceiver.set_compute_mode("fp32")
