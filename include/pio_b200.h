@@ -163,6 +163,14 @@ typedef struct {
     int accumulate;
     float dropout_p;       /* as in pio_gemm_desc */
     uint64_t dropout_seed;
+    /* Optional device-side row count (NULL = off): v = clamp(*dyn_rows - dyn_offset, 0, m or k) replaces
+     * m (dyn_axis 0: output tiles at or beyond row v are skipped, rows >= v are not written) or k
+     * (dyn_axis 1: 64-row k-blocks at or beyond v are skipped; needs accumulate == 2, and operand rows
+     * between v and the next multiple of 64 must be finite with one side zero).  Lets a captured graph
+     * run a product whose row count is only known on the device (rows with a label). */
+    const int32_t* dyn_rows;
+    int64_t dyn_offset;
+    int dyn_axis;
 } pio_gemm_bf16_desc;
 int pio_gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, pio_stream_t stream);
 size_t pio_gemm_bf16_ws_bytes(int64_t m, int64_t n, int64_t k);
@@ -346,10 +354,14 @@ int pio_linear_bwd(const float* dy, const float* x, const float* w, float* dx, f
 
 /* Output-adapter Linear fused with the cross-entropy loss for training (TextOutputAdapter.linear,
  * adapter.py:146-149,166-173 + nn.CrossEntropyLoss, lightning.py:184,225-226).
- * PIO_MODE_BF16 only (`w` = bf16 shadow).  Rows are processed in L2-sized chunks: logits GEMM, one
- * kernel producing per-row losses and bf16 dlogits, and the two gradient GEMMs — every logit is
- * computed, none is stored in HBM.  out3 = {loss, n_valid, loss_sum}; dx (rows,c_in), dw (classes,c_in),
- * db (classes) are the gradients for d(loss) = 1 (scale them by the incoming gradient). */
+ * PIO_MODE_BF16 only (`w` = bf16 shadow).  Rows with an ignored label contribute exactly zero to the loss
+ * and to every gradient, so only the valid rows are projected: they are compacted on the device (the count
+ * never reaches the host — kernels are launched for the worst case and skip tiles past the count, so the call
+ * can be captured in a CUDA graph and replayed on other labels) and go through in L2-sized chunks: logits
+ * GEMM (bf16), one kernel producing per-row losses and bf16 dlogits in place, the two gradient GEMMs and the
+ * bias column sums.  No logit is stored in HBM.  out3 = {loss, n_valid, loss_sum}; dx (rows,c_in; zero rows
+ * for ignored labels), dw (classes,c_in), db (classes) are the gradients for d(loss) = 1 (scale them by the
+ * incoming gradient). */
 size_t pio_linear_ce_ws_bytes(int64_t rows, int c_in, int64_t classes, int mode);
 int pio_linear_ce_fwd_bwd(const float* x, const float* w, const float* b, const int64_t* labels, float* out3,
                           float* dx, float* dw, float* db, int64_t rows, int c_in, int64_t classes,

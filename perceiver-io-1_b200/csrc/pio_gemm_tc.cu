@@ -43,6 +43,8 @@ struct TcParams {
     int64_t partial_stride;
     int epi_kind;
     DropCfg drop;  // dropout on the value before the residual add (generic epilogue only)
+    const int* dyn_rows;  // device-side row count (see pio_gemm_bf16_desc), or null
+    int dyn_off, dyn_axis;
 };
 
 // Epilogue flavours, resolved on the host so the row loop below carries no run-time flag tests
@@ -222,9 +224,6 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
     pdl_trigger();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.y * TC_BM, n0 = blockIdx.x * BN;
-    const int kb_begin = blockIdx.z * p.kb_per_split;
-    const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
-    const int nkb = kb_end - kb_begin;
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmA);
@@ -243,7 +242,19 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();  // prologue done; from here on the kernel reads / writes what earlier kernels produced
 
-    if (warp == 0) {
+    int m_eff = p.M, num_kb = p.num_kb;
+    if (p.dyn_rows != nullptr) {  // block-uniform
+        const int v = max(0, __ldg(p.dyn_rows) - p.dyn_off);
+        if (p.dyn_axis == 0) m_eff = min(m_eff, v);
+        else num_kb = min(num_kb, (v + TC_BK - 1) / TC_BK);
+    }
+    const int kb_begin = blockIdx.z * p.kb_per_split;
+    const int kb_end = min(num_kb, kb_begin + p.kb_per_split);
+    const int nkb = (m0 < m_eff) ? kb_end - kb_begin : 0;  // <= 0: this CTA has nothing to do
+
+    if (nkb <= 0) {
+        // fall through to the common tail (TMEM release)
+    } else if (warp == 0) {
         if (lane == 0) {
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % TC_STAGES;
@@ -312,7 +323,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
         }
         __syncwarp();
         const int64_t gm0 = (int64_t)m0 + q * 32;
-        const int rows_here = (int)min((int64_t)32, (int64_t)p.M - gm0);  // may be <= 0
+        const int rows_here = (int)min((int64_t)32, (int64_t)m_eff - gm0);  // may be <= 0
         switch (p.epi_kind) {
             case EPI_F32: epilogue_rows<BN, EPI_F32>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
             case EPI_F32_RES: epilogue_rows<BN, EPI_F32_RES>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
@@ -398,7 +409,9 @@ int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream
     if (d->m == 0 || d->n == 0) return PIO_OK;
     const bool a_mn = !d->a_kmajor, b_mn = !d->b_kmajor;
     const bool dropping = d->dropout_p > 0.f;
-    const bool splittable = !d->bias && !d->residual && d->act == 0 && d->c32 && !d->c16 && d->ldc32 == d->n && !dropping;
+    // (a device-side row count rules out the partial-sum reduction pass, which would touch skipped rows)
+    const bool splittable = !d->bias && !d->residual && d->act == 0 && d->c32 && !d->c16 && d->ldc32 == d->n && !dropping &&
+                            !(d->dyn_rows && d->accumulate != 2);
     int bn, splits, kb_per;
     tc_choose(d->m, d->n, d->k, splittable, &bn, &splits, &kb_per);
 
@@ -412,6 +425,10 @@ int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream
     p.act = d->act; p.accumulate = d->accumulate;
     p.drop = make_drop(d->dropout_p, d->dropout_seed);
     p.partial_stride = d->m * d->n;
+    p.dyn_rows = d->dyn_rows; p.dyn_off = (int)d->dyn_offset; p.dyn_axis = d->dyn_axis;
+    PIO_CHECK_ARG(!d->dyn_rows || (d->dyn_axis == 0 || (d->dyn_axis == 1 && d->accumulate == 2)),
+                  "pio_gemm_bf16: dyn_axis must be 0, or 1 with accumulate == 2");
+    PIO_CHECK_ARG(!d->dyn_rows || (d->dyn_offset >= 0 && d->dyn_offset < (1ll << 31)), "pio_gemm_bf16: bad dyn_offset");
     const bool atomic = (d->accumulate == 2);
     if (atomic) PIO_CHECK_ARG(splittable, "pio_gemm_bf16: accumulate=2 (atomic) needs a plain fp32 output without epilogue");
     if (splits > 1 && !atomic) {

@@ -582,57 +582,149 @@ int linear_bwd(Ctx& c, const float* dy, const float* x, const float* w16, float*
 }
 
 // ---------------------------------------------------------------- output linear fused with cross-entropy
-// Training only needs the loss and its gradients, never the (rows x classes) logits as a stored
-// tensor.  The rows are processed in chunks sized so that a chunk's fp32 logits and bf16 dlogits stay
-// in the 126 MB L2: logits GEMM -> one kernel that turns them into per-row losses and bf16 dlogits
-// -> the two gradient GEMMs (dW accumulating across chunks).  Every logit is still computed; what
-// disappears is ~5 passes over 1.3 GB of HBM (at vocab 10003, 32768 rows).
-__global__ void count_valid_kernel(const int64_t* __restrict__ labels, int64_t rows, int64_t classes, int64_t ignore,
-                                   float* __restrict__ out3) {
-    __shared__ int s_cnt[32];
+// loss = mean over valid rows of CE(x W^T + b, labels) and its gradients without the (rows, classes) logits
+// tensor ever existing.
+//  * Rows whose label is ignored contribute exactly zero to the loss and to every gradient, so they are
+//    never projected: the valid rows are compacted on the device (an MLM batch labels ~15 % of its
+//    positions), and dx of the ignored rows is written as zeros.  The number of valid rows stays on the
+//    device — every kernel below is launched for the worst case (all rows) and skips the tiles beyond
+//    the count it reads from memory (pio_gemm_bf16_desc::dyn_rows), so the sequence can be captured in a
+//    CUDA graph and replayed on batches with different label counts.
+//  * The compacted rows go through in chunks sized so that a chunk's bf16 logits stay in the 126 MB L2:
+//    logits GEMM (bf16 out) -> one kernel that turns them in place into bf16 dlogits and per-row losses
+//    -> the two gradient GEMMs and the bias column sums (dW / db accumulating across chunks with atomics
+//    on the side stream while the main stream forms dx).
+struct LceIndex {
+    int* count;        // number of valid rows
+    int* idx;          // [rows] compact position -> source row
+    int* pos;          // [rows] source row -> compact position, -1 for ignored rows
+    int64_t* labels;   // [rows] labels of the compacted rows
+};
+
+// single block: stable compaction of the valid rows (thread t owns a contiguous run of rows)
+__global__ void __launch_bounds__(1024) lce_compact_kernel(const int64_t* __restrict__ labels, int64_t rows, int64_t classes,
+                                                           int64_t ignore, float* __restrict__ out3, LceIndex ix) {
+    __shared__ int s_warp[32];
+    __shared__ int s_total;
+    const int per = (int)((rows + blockDim.x - 1) / blockDim.x);
+    const int64_t r_begin = (int64_t)threadIdx.x * per, r_end = min(rows, r_begin + per);
     int local = 0;
-    for (int64_t r = threadIdx.x; r < rows; r += blockDim.x) {
+    for (int64_t r = r_begin; r < r_end; ++r) {
         const int64_t y = labels[r];
         local += (y == ignore || y < 0 || y >= classes) ? 0 : 1;
     }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int incl = local;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
-    if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = local;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[wid] = incl;
     __syncthreads();
+    if (wid == 0) {
+        int v = (lane < (int)(blockDim.x >> 5)) ? s_warp[lane] : 0;
+        int inc2 = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc2, o);
+            if (lane >= o) inc2 += t;
+        }
+        s_warp[lane] = inc2 - v;  // exclusive prefix of the warp totals
+        if (lane == 31) s_total = inc2;
+    }
+    __syncthreads();
+    int at = s_warp[wid] + incl - local;
+    for (int64_t r = r_begin; r < r_end; ++r) {
+        const int64_t y = labels[r];
+        const bool valid = !(y == ignore || y < 0 || y >= classes);
+        if (valid) {
+            ix.idx[at] = (int)r;
+            ix.labels[at] = y;
+            ix.pos[r] = at;
+            ++at;
+        } else {
+            ix.pos[r] = -1;
+        }
+    }
     if (threadIdx.x == 0) {
-        int t = 0;
-        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += s_cnt[w];
-        out3[1] = (float)t;
+        *ix.count = s_total;
+        out3[1] = (float)s_total;
     }
 }
 
-// one CTA per row: logsumexp, loss, and dlogits = (softmax - onehot) / n_valid as bf16 (0 for ignored rows)
-__global__ void __launch_bounds__(256) ce_chunk_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __restrict__ labels,
-                                                       const float* __restrict__ out3, bf16* __restrict__ dl, int64_t ld_dl,
-                                                       float* __restrict__ row_loss, int64_t rows, int64_t classes, int64_t ignore) {
+// x16c[i] = bf16(x[idx[i]]) for i < count; rows up to the next multiple of 128 are zero-filled (they are read
+// as operand padding by the partial tiles / k-blocks); nothing beyond is touched.  Warp per row.
+__global__ void __launch_bounds__(256) lce_gather_kernel(const float* __restrict__ x, int c_in, bf16* __restrict__ x16c, int64_t ld,
+                                                         LceIndex ix, int64_t rows) {
+    const int count = *ix.count;
+    const int64_t upto = min(rows, ((int64_t)count + 127) / 128 * 128);
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t i = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < upto; i += warps) {
+        bf16* dst = x16c + i * ld;
+        if (i < count) {
+            const float* src = x + (int64_t)ix.idx[i] * c_in;
+            for (int j = lane; j < (int)ld; j += 32) dst[j] = __float2bfloat16(j < c_in ? src[j] : 0.f);
+        } else {
+            for (int j = lane; j < (int)ld; j += 32) dst[j] = __float2bfloat16(0.f);
+        }
+    }
+}
+
+// dx[r] = dxc[pos[r]] for valid rows, 0 for ignored rows.  Warp per row.
+__global__ void __launch_bounds__(256) lce_scatter_kernel(const float* __restrict__ dxc, int c_in, float* __restrict__ dx,
+                                                          LceIndex ix, int64_t rows) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < rows; r += warps) {
+        const int p = ix.pos[r];
+        float* dst = dx + r * c_in;
+        if (p >= 0) {
+            const float* src = dxc + (int64_t)p * c_in;
+            for (int j = lane; j < c_in; j += 32) dst[j] = src[j];
+        } else {
+            for (int j = lane; j < c_in; j += 32) dst[j] = 0.f;
+        }
+    }
+}
+
+__device__ __forceinline__ void online_max_sum(float v, float& m, float& s) {
+    if (v > m) {
+        s = s * __expf(m - v) + 1.0f;
+        m = v;
+    } else {
+        s += __expf(v - m);
+    }
+}
+
+// One CTA per compacted row of the chunk [r0, r0 + nr): bf16 logits -> logsumexp, row loss, and in place
+// dlogits = (softmax - onehot) / n_valid as bf16 (pad columns zeroed).  Rows between the valid count and
+// the next multiple of 64 are zero-filled: the dW product reads them as k-block padding.
+__global__ void __launch_bounds__(256) ce_chunk_kernel(bf16* __restrict__ lg, int64_t ld, const int64_t* __restrict__ labels_c,
+                                                       const float* __restrict__ out3, const int* __restrict__ count, int64_t r0,
+                                                       int64_t nr, float* __restrict__ row_loss, int64_t classes) {
     __shared__ float s_m[8], s_s[8];
     __shared__ float s_lse;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int64_t live = max((int64_t)0, min(nr, (int64_t)*count - r0));
+    const int64_t upto = min(nr, (live + 63) / 64 * 64);
     const float inv_n = 1.0f / out3[1];
-    for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
-        const float* z = logits + r * ld;
-        bf16* d = dl + r * ld_dl;
-        const int64_t y = labels[r];
-        const bool valid = !(y == ignore || y < 0 || y >= classes);
-        if (!valid) {  // block-uniform
-            for (int64_t j = threadIdx.x; j < ld_dl; j += blockDim.x) d[j] = __float2bfloat16(0.f);
-            if (threadIdx.x == 0) row_loss[r] = 0.f;
+    const int nvec = (int)(ld >> 3);  // ld is a multiple of 8: rows are 16-byte aligned vectors of 8
+    for (int64_t r = blockIdx.x; r < upto; r += gridDim.x) {
+        uint4* zv = reinterpret_cast<uint4*>(lg + r * ld);
+        if (r >= live) {  // block-uniform
+            for (int j = threadIdx.x; j < nvec; j += blockDim.x) zv[j] = make_uint4(0u, 0u, 0u, 0u);
             continue;
         }
+        const int64_t y = labels_c[r0 + r];
         float m = -INFINITY, s = 0.f;
-        for (int64_t j = threadIdx.x; j < classes; j += blockDim.x) {
-            const float v = z[j];
-            if (v > m) {
-                s = s * __expf(m - v) + 1.0f;
-                m = v;
-            } else {
-                s += __expf(v - m);
-            }
+        for (int j = threadIdx.x; j < nvec; j += blockDim.x) {
+            const uint4 u = zv[j];
+            const bf16* e = reinterpret_cast<const bf16*>(&u);
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                if ((int64_t)j * 8 + k < classes) online_max_sum(__bfloat162float(e[k]), m, s);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -657,27 +749,54 @@ __global__ void __launch_bounds__(256) ce_chunk_kernel(const float* __restrict__
                 if (s_m[w] != -INFINITY) ss += s_s[w] * __expf(s_m[w] - mm);
             const float lse = mm + logf(ss);
             s_lse = lse;
-            row_loss[r] = lse - z[y];
+            row_loss[r0 + r] = lse - __bfloat162float(lg[r * ld + y]);
         }
         __syncthreads();
         const float lse = s_lse;
-        for (int64_t j = threadIdx.x; j < ld_dl; j += blockDim.x) {
-            float g = 0.f;
-            if (j < classes) {
-                g = __expf(z[j] - lse);
-                if (j == y) g -= 1.0f;
-                g *= inv_n;
+        for (int j = threadIdx.x; j < nvec; j += blockDim.x) {
+            uint4 u = zv[j];
+            bf16* e = reinterpret_cast<bf16*>(&u);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int64_t col = (int64_t)j * 8 + k;
+                float g = 0.f;
+                if (col < classes) {
+                    g = __expf(__bfloat162float(e[k]) - lse);
+                    if (col == y) g -= 1.0f;
+                    g *= inv_n;
+                }
+                e[k] = __float2bfloat16(g);
             }
-            d[j] = __float2bfloat16(g);
+            zv[j] = u;
         }
         __syncthreads();
     }
 }
 
-__global__ void __launch_bounds__(1024) loss_finalize_kernel(const float* __restrict__ row_loss, int64_t rows, float* __restrict__ out3) {
+// db[j] += sum over the chunk's live rows of dl[r][j]: block = 128 rows x 256 columns (2 per thread), one atomic
+// per column per block.
+__global__ void __launch_bounds__(128) lce_colsum_kernel(const bf16* __restrict__ dl, int64_t ld, float* __restrict__ db,
+                                                         const int* __restrict__ count, int64_t r0, int64_t nr, int64_t classes) {
+    const int64_t live = max((int64_t)0, min(nr, (int64_t)*count - r0));
+    const int64_t rb = (int64_t)blockIdx.y * 128, re = min(live, rb + 128);
+    const int64_t col = ((int64_t)blockIdx.x * 128 + threadIdx.x) * 2;
+    if (rb >= live || col >= classes) return;
+    float a0 = 0.f, a1 = 0.f;
+    for (int64_t r = rb; r < re; ++r) {
+        const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(dl + r * ld + col);
+        a0 += __low2float(v);
+        a1 += __high2float(v);
+    }
+    atomicAdd(db + col, a0);
+    if (col + 1 < classes) atomicAdd(db + col + 1, a1);
+}
+
+__global__ void __launch_bounds__(1024) loss_finalize_kernel(const float* __restrict__ row_loss, const int* __restrict__ count,
+                                                             float* __restrict__ out3) {
     __shared__ double s_l[32];
+    const int rows = *count;
     double l = 0.0;
-    for (int64_t r = threadIdx.x; r < rows; r += blockDim.x) l += (double)row_loss[r];
+    for (int r = threadIdx.x; r < rows; r += blockDim.x) l += (double)row_loss[r];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
     if ((threadIdx.x & 31) == 0) s_l[threadIdx.x >> 5] = l;
@@ -691,50 +810,83 @@ __global__ void __launch_bounds__(1024) loss_finalize_kernel(const float* __rest
 }
 
 static int64_t lce_chunk_rows(int64_t classes) {
-    // fp32 logits + bf16 dlogits of a chunk within ~100 MB so they stay L2-resident between kernels
-    int64_t rows = (100ll << 20) / (6 * classes);
+    // bf16 logits (turned into dlogits in place) of a chunk within ~84 MB so they stay L2-resident between kernels
+    int64_t rows = (84ll << 20) / (2 * pad8(classes));
     rows = std::max<int64_t>(128, rows / 128 * 128);
-    return std::min<int64_t>(rows, 4096);
+    return std::min<int64_t>(rows, 8192);
 }
 
 size_t linear_ce_ws_bytes(int64_t rows, int c_in, int64_t classes) {
     const int64_t ch = std::min(rows, lce_chunk_rows(classes));
-    return align_up((size_t)rows * pad8(c_in) * 2, 256) + align_up((size_t)ch * classes * 4, 256) +
-           align_up((size_t)ch * pad8(classes) * 2, 256) + align_up((size_t)rows * 4, 256) + scratch_bytes(ch, classes, c_in) +
-           colsum_ws_bytes(ch, (int)classes) + 2048;
+    return align_up((size_t)rows * pad8(c_in) * 2, 256) + align_up((size_t)ch * pad8(classes) * 2, 256) +
+           align_up((size_t)rows * c_in * 4, 256) + 4 * align_up((size_t)rows * 8, 256) + 256 +
+           pio_gemm_bf16_ws_bytes(ch, c_in, classes) + 4096;
 }
 
 int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, const int64_t* labels, float* out3, float* dx,
                       float* dw, float* db, int64_t rows, int c_in, int64_t classes, int64_t ignore) {
+    const char* who = "pio_linear_ce_fwd_bwd";
+    PIO_CHECK_ARG(rows < (1ll << 31), "%s: more than 2^31 rows", who);
     const int64_t cip = pad8(c_in), cop = pad8(classes);
     const int64_t ch = std::min(rows, lce_chunk_rows(classes));
     const size_t mark = c.W.off;
-    PIO_TAKE_BYTES(bf16, x16, c, (size_t)rows * cip * 2, "pio_linear_ce_fwd_bwd");
-    PIO_TAKE_BYTES(float, logits, c, (size_t)ch * classes * 4, "pio_linear_ce_fwd_bwd");
-    PIO_TAKE_BYTES(bf16, dl16, c, (size_t)ch * cop * 2, "pio_linear_ce_fwd_bwd");
-    PIO_TAKE_BYTES(float, row_loss, c, (size_t)rows * 4, "pio_linear_ce_fwd_bwd");
-    count_valid_kernel<<<1, 1024, 0, c.st>>>(labels, rows, classes, ignore, out3);
+    PIO_TAKE_BYTES(bf16, x16c, c, (size_t)rows * cip * 2, who);
+    PIO_TAKE_BYTES(bf16, lg16, c, (size_t)ch * cop * 2, who);
+    PIO_TAKE_BYTES(float, dxc, c, (size_t)rows * c_in * 4, who);
+    PIO_TAKE_BYTES(float, row_loss, c, (size_t)rows * 4, who);
+    LceIndex ix;
+    PIO_TAKE_BYTES(int, idx, c, (size_t)rows * 4, who);
+    PIO_TAKE_BYTES(int, pos, c, (size_t)rows * 4, who);
+    PIO_TAKE_BYTES(int64_t, labels_c, c, (size_t)rows * 8, who);
+    PIO_TAKE_BYTES(int, count, c, 256, who);
+    ix.count = count; ix.idx = idx; ix.pos = pos; ix.labels = labels_c;
+
+    lce_compact_kernel<<<1, 1024, 0, c.st>>>(labels, rows, classes, ignore, out3, ix);
     PIO_LAUNCH_CHECK();
-    PIO_TRY(cast_bf16(x, x16, rows, c_in, c_in, cip, c.st));
+    const int row_blocks = (int)std::min<int64_t>(cdiv(rows, 8), (int64_t)num_sms() * 8);
+    lce_gather_kernel<<<row_blocks, 256, 0, c.st>>>(x, c_in, x16c, cip, ix, rows);
+    PIO_LAUNCH_CHECK();
     // dW / db accumulate with atomics on the side stream while the main stream forms dx for the same chunk
-    // (first chunk: the destinations are zeroed up front so every chunk can simply add)
+    // (the destinations are zeroed up front so every chunk can simply add)
     PIO_CUDA(cudaMemsetAsync(dw, 0, (size_t)classes * c_in * sizeof(float), c.st));
     PIO_CUDA(cudaMemsetAsync(db, 0, (size_t)classes * sizeof(float), c.st));
     Side side(c, 2);
     for (int64_t r0 = 0; r0 < rows; r0 += ch) {
         const int64_t nr = std::min(ch, rows - r0);
-        const bf16* xc = x16 + r0 * cip;
-        PIO_TRY(tc_xwT(c, xc, cip, (const bf16*)w16, cip, nr, classes, c_in, logits, classes, nullptr, 0, b, nullptr, 0, 0, nullptr, 0));
+        const bf16* xc = x16c + r0 * cip;
+        {  // logits (bf16) = x W^T + b for the live rows of this chunk
+            pio_gemm_bf16_desc d{};
+            d.a = xc; d.b = w16; d.m = nr; d.n = classes; d.k = c_in; d.lda = cip; d.ldb = cip; d.a_kmajor = 1; d.b_kmajor = 1;
+            d.c16 = lg16; d.ldc16 = cop; d.bias = b;
+            d.dyn_rows = count; d.dyn_offset = r0; d.dyn_axis = 0;
+            PIO_TRY(tc_gemm(c, d));
+        }
         const int blocks = (int)std::min<int64_t>(nr, (int64_t)num_sms() * 8);
-        ce_chunk_kernel<<<blocks, 256, 0, c.st>>>(logits, classes, labels + r0, out3, dl16, cop, row_loss + r0, nr, classes, ignore);
+        ce_chunk_kernel<<<blocks, 256, 0, c.st>>>(lg16, cop, labels_c, out3, count, r0, nr, row_loss, classes);
         PIO_LAUNCH_CHECK();
         PIO_TRY(side.fork());
-        PIO_TRY(tc_dW(c, dl16, cop, xc, cip, dw, nr, classes, c_in, 2, side.stream()));
-        PIO_TRY(side_colsum(c, side, dl16, cop, db, 2, nr, (int)classes));
-        PIO_TRY(tc_dyW(c, dl16, cop, (const bf16*)w16, cip, nr, classes, c_in, dx + r0 * c_in, c_in, nullptr, 0, 0, nullptr, 0, 0));
-        PIO_TRY(side.join());  // the next chunk overwrites dl16
+        {  // dW += dlogits^T x   (contraction over the live rows)
+            pio_gemm_bf16_desc d{};
+            d.a = lg16; d.b = xc; d.m = classes; d.n = c_in; d.k = nr; d.lda = cop; d.ldb = cip; d.a_kmajor = 0; d.b_kmajor = 0;
+            d.c32 = dw; d.ldc32 = c_in; d.accumulate = 2;
+            d.dyn_rows = count; d.dyn_offset = r0; d.dyn_axis = 1;
+            PIO_TRY(gemm_bf16(&d, nullptr, 0, side.stream()));
+        }
+        lce_colsum_kernel<<<dim3((unsigned)cdiv(cdiv(classes, 2), 128), (unsigned)cdiv(nr, 128)), 128, 0, side.stream()>>>(
+            lg16, cop, db, count, r0, nr, classes);
+        PIO_LAUNCH_CHECK();
+        {  // dx (compacted) = dlogits W
+            pio_gemm_bf16_desc d{};
+            d.a = lg16; d.b = w16; d.m = nr; d.n = c_in; d.k = classes; d.lda = cop; d.ldb = cip; d.a_kmajor = 1; d.b_kmajor = 0;
+            d.c32 = dxc + r0 * c_in; d.ldc32 = c_in;
+            d.dyn_rows = count; d.dyn_offset = r0; d.dyn_axis = 0;
+            PIO_TRY(tc_gemm(c, d));
+        }
+        PIO_TRY(side.join());  // the next chunk overwrites lg16
     }
-    loss_finalize_kernel<<<1, 1024, 0, c.st>>>(row_loss, rows, out3);
+    lce_scatter_kernel<<<row_blocks, 256, 0, c.st>>>(dxc, c_in, dx, ix, rows);
+    PIO_LAUNCH_CHECK();
+    loss_finalize_kernel<<<1, 1024, 0, c.st>>>(row_loss, count, out3);
     PIO_LAUNCH_CHECK();
     c.W.off = mark;
     return PIO_OK;

@@ -49,7 +49,8 @@ class GemmBf16Desc(Structure):
                 ("c32", c_void_p), ("ldc32", c_int64), ("c16", c_void_p), ("ldc16", c_int64),
                 ("bias", c_void_p), ("residual", c_void_p), ("ldr", c_int64),
                 ("aux16", c_void_p), ("ldaux", c_int64), ("act", c_int), ("accumulate", c_int),
-                ("dropout_p", c_float), ("dropout_seed", ctypes.c_uint64)]
+                ("dropout_p", c_float), ("dropout_seed", ctypes.c_uint64),
+                ("dyn_rows", c_void_p), ("dyn_offset", c_int64), ("dyn_axis", c_int)]
 
 
 class Dropout(Structure):

@@ -143,16 +143,18 @@ def test_weight_shadow_follows_parameter_updates():
     assert_rel(y1, O.mlp_residual(sd, "", x.cpu()) - x.cpu(), BF16_TOL, "after update")
 
 
-@pytest.mark.parametrize("rows,c,classes", [(300, 64, 517), (4096, 256, 10003)])
-def test_fused_linear_cross_entropy_matches_oracle(rows, c, classes):
-    """pio_linear_ce_fwd_bwd (chunked, logits never stored) against the fp64 oracle of linear + CE."""
+@pytest.mark.parametrize("rows,c,classes,p_ignore", [(300, 64, 517, 0.8), (4096, 256, 10003, 0.8), (9000, 64, 517, 0.0),
+                                                     (9001, 72, 1001, 0.05), (257, 131, 40, 0.5)])
+def test_fused_linear_cross_entropy_matches_oracle(rows, c, classes, p_ignore):
+    """pio_linear_ce_fwd_bwd (valid rows compacted on the device, chunked, logits never stored) against the fp64
+    oracle of linear + CE; rows past one chunk (8192), counts off the 64/128-row tile grid, no ignored rows."""
     import perceiver
     torch.manual_seed(7)
     x = torch.randn(rows, c)
     w = torch.randn(classes, c) * 0.1
     b = torch.randn(classes) * 0.1
     y = torch.randint(0, classes, (rows,))
-    y[torch.rand(rows) < 0.8] = -100
+    y[torch.rand(rows) < p_ignore] = -100
     y[0] = 3
     xr, wr, br = (t.double().requires_grad_(True) for t in (x, w, b))
     ref = O.cross_entropy(O.linear(xr, wr, br), y)
@@ -164,6 +166,59 @@ def test_fused_linear_cross_entropy_matches_oracle(rows, c, classes):
     assert_rel(xd.grad, xr.grad, 2e-2, "dx")
     assert_rel(wd.grad, wr.grad, 2e-2, "dw")
     assert_rel(bd.grad, br.grad, 2e-2, "db")
+    assert not xd.grad[(y == -100).to(DEV)].any()  # ignored rows: exactly zero
+
+
+def test_fused_linear_cross_entropy_graph_replay_with_other_label_counts():
+    """The number of labelled rows never reaches the host: a CUDA graph captured on one batch gives the eager
+    result on batches with fewer, more, or no ignored labels."""
+    from perceiver import _native as N
+    L = N.lib()
+    rows, c, classes = 3000, 64, 517
+    torch.manual_seed(11)
+    x = torch.randn(rows, c, device=DEV)
+    w = (torch.randn(classes, c, device=DEV) * 0.1)
+    w16 = w.to(torch.bfloat16).contiguous()
+    b = torch.randn(classes, device=DEV) * 0.1
+    labels = torch.empty(rows, dtype=torch.int64, device=DEV)
+    ws = torch.empty(L.pio_linear_ce_ws_bytes(rows, c, classes, 1), dtype=torch.uint8, device=DEV)
+
+    def make(p_ignore, seed):
+        g = torch.Generator().manual_seed(seed)
+        y = torch.randint(0, classes, (rows,), generator=g)
+        y[torch.rand(rows, generator=g) < p_ignore] = -100
+        y[5] = 1
+        return y.to(DEV)
+
+    def run(out3, dx, dw, db):
+        N.check(L.pio_linear_ce_fwd_bwd(x.data_ptr(), w16.data_ptr(), b.data_ptr(), labels.data_ptr(), out3.data_ptr(),
+                                        dx.data_ptr(), dw.data_ptr(), db.data_ptr(), rows, c, classes, -100, 1, ws.data_ptr(),
+                                        ws.numel(), N.stream_ptr(x.device)), "pio_linear_ce_fwd_bwd")
+
+    outs = [torch.empty(3, device=DEV), torch.empty(rows, c, device=DEV), torch.empty(classes, c, device=DEV),
+            torch.empty(classes, device=DEV)]
+    labels.copy_(make(0.85, 1))
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        run(*outs)
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        run(*outs)
+    for p_ignore, seed in [(0.85, 1), (0.3, 2), (0.0, 3), (0.97, 4), (0.5, 5)]:
+        labels.copy_(make(p_ignore, seed))
+        graph.replay()
+        torch.cuda.synchronize()
+        got = [t.clone() for t in outs]
+        eager = [torch.empty_like(t) for t in outs]
+        run(*eager)
+        torch.cuda.synchronize()
+        assert got[0][1].item() == (labels != -100).sum().item()
+        assert_rel(got[0][0], eager[0][0], 1e-5, f"loss p={p_ignore}")
+        assert torch.equal(got[1], eager[1]), f"dx p={p_ignore}"
+        assert_rel(got[2], eager[2], 1e-4, f"dw p={p_ignore}")  # atomics: summation order differs
+        assert_rel(got[3], eager[3], 1e-4, f"db p={p_ignore}")
 
 
 def test_mlm_return_loss_equals_logits_then_cross_entropy():
