@@ -133,18 +133,46 @@ __global__ void text_embed_fwd_kernel(const int64_t* __restrict__ ids, const flo
     }
 }
 
-__global__ void text_embed_bwd_emb_kernel(const int64_t* __restrict__ ids, const float* __restrict__ dout,
-                                          float* __restrict__ demb, int64_t tokens, int c, int64_t vocab,
-                                          float scale) {
-    const int lane = threadIdx.x & 31;
-    const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (int64_t t = warp; t < tokens; t += nwarps) {
+// d_embedding[ids[t]] += dout[t] * scale.  MLM batches repeat a few ids thousands of times ([MASK] alone is
+// ~12 % of the tokens), and same-address atomics serialise in L2, so every block first folds its tokens into a
+// small direct-mapped cache of embedding rows in shared memory (tag = id; a token whose slot is taken by
+// another id goes straight to global memory) and flushes the cache with one atomic per element at the end.
+constexpr int EMB_SLOTS = 16;
+__global__ void __launch_bounds__(256) text_embed_bwd_emb_kernel(const int64_t* __restrict__ ids, const float* __restrict__ dout,
+                                                                 float* __restrict__ demb, int64_t tokens, int c, int64_t vocab,
+                                                                 float scale, int slots) {
+    extern __shared__ float s_cache[];  // [slots][c]
+    __shared__ long long s_tag[EMB_SLOTS];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int i = threadIdx.x; i < slots * c; i += blockDim.x) s_cache[i] = 0.f;
+    if (threadIdx.x < EMB_SLOTS) s_tag[threadIdx.x] = -1;
+    __syncthreads();
+    const int64_t per = (tokens + gridDim.x - 1) / gridDim.x;  // a contiguous run of tokens per block
+    const int64_t t_end = min(tokens, (int64_t)(blockIdx.x + 1) * per);
+    for (int64_t t = (int64_t)blockIdx.x * per + wid; t < t_end; t += nw) {
         int64_t id = ids[t];
         id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
         const float* g = dout + t * c;
-        float* d = demb + id * c;
-        for (int j = lane; j < c; j += 32) atomicAdd(d + j, g[j] * scale);
+        int slot = -1;
+        if (slots > 0) {
+            const int cand = (int)(((uint64_t)id * 0x9E3779B97F4A7C15ull) >> 40) % slots;
+            long long old = 0;
+            if (lane == 0) old = atomicCAS((unsigned long long*)&s_tag[cand], (unsigned long long)-1ll, (unsigned long long)id);
+            old = __shfl_sync(0xffffffffu, old, 0);
+            if (old == -1 || old == id) slot = cand;
+        }
+        if (slot >= 0) {
+            float* d = s_cache + (size_t)slot * c;
+            for (int j = lane; j < c; j += 32) atomicAdd(d + j, g[j] * scale);
+        } else {
+            float* d = demb + id * c;
+            for (int j = lane; j < c; j += 32) atomicAdd(d + j, g[j] * scale);
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < slots * c; i += blockDim.x) {
+        const long long id = s_tag[i / c];
+        if (id >= 0) atomicAdd(demb + id * c + (i % c), s_cache[i]);
     }
 }
 
@@ -628,8 +656,11 @@ int pio_text_embed_bwd(const int64_t* ids, const float* dout, float* demb, float
     if (tokens == 0) return PIO_OK;
     const int threads = 256;
     if (demb) {
-        const int blocks = (int)std::min<int64_t>(cdiv(tokens, threads / 32), (int64_t)num_sms() * 16);
-        text_embed_bwd_emb_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(ids, dout, demb, tokens, c, vocab, scale);
+        // blocks own >= 64 tokens each so the per-block cache has duplicates to absorb
+        const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>(cdiv(tokens, 64), (int64_t)num_sms() * 2));
+        const int slots = c <= 512 ? EMB_SLOTS : (c <= 2048 ? 4 : 0);
+        text_embed_bwd_emb_kernel<<<blocks, threads, (size_t)slots * c * sizeof(float), (cudaStream_t)stream>>>(
+            ids, dout, demb, tokens, c, vocab, scale, slots);
         PIO_LAUNCH_CHECK();
     }
     if (dpos) {

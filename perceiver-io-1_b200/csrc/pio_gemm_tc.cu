@@ -224,6 +224,14 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
     pdl_trigger();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.y * TC_BM, n0 = blockIdx.x * BN;
+    int m_eff = p.M, num_kb = p.num_kb;
+    if (p.dyn_rows != nullptr) {  // block-uniform; the count comes from an earlier kernel, so no prologue overlap here
+        pdl_wait();
+        const int v = max(0, __ldg(p.dyn_rows) - p.dyn_off);
+        if (p.dyn_axis == 0) m_eff = min(m_eff, v);
+        else num_kb = min(num_kb, (v + TC_BK - 1) / TC_BK);
+        if (m0 >= m_eff || blockIdx.z * p.kb_per_split >= num_kb) return;  // nothing to do: leave before any set-up
+    }
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmA);
@@ -242,19 +250,11 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();  // prologue done; from here on the kernel reads / writes what earlier kernels produced
 
-    int m_eff = p.M, num_kb = p.num_kb;
-    if (p.dyn_rows != nullptr) {  // block-uniform
-        const int v = max(0, __ldg(p.dyn_rows) - p.dyn_off);
-        if (p.dyn_axis == 0) m_eff = min(m_eff, v);
-        else num_kb = min(num_kb, (v + TC_BK - 1) / TC_BK);
-    }
     const int kb_begin = blockIdx.z * p.kb_per_split;
     const int kb_end = min(num_kb, kb_begin + p.kb_per_split);
-    const int nkb = (m0 < m_eff) ? kb_end - kb_begin : 0;  // <= 0: this CTA has nothing to do
+    const int nkb = kb_end - kb_begin;
 
-    if (nkb <= 0) {
-        // fall through to the common tail (TMEM release)
-    } else if (warp == 0) {
+    if (warp == 0) {
         if (lane == 0) {
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % TC_STAGES;

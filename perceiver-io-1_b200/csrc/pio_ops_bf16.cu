@@ -601,55 +601,69 @@ struct LceIndex {
     int64_t* labels;   // [rows] labels of the compacted rows
 };
 
-// single block: stable compaction of the valid rows (thread t owns a contiguous run of rows)
+// Stable compaction of the valid rows, 1024 rows per block: pass 1 counts per block, pass 2 turns the block
+// counts into offsets (every block re-scans the short count array) and writes the index maps.
+__device__ __forceinline__ bool lce_valid(int64_t y, int64_t classes, int64_t ignore) {
+    return !(y == ignore || y < 0 || y >= classes);
+}
+__global__ void __launch_bounds__(1024) lce_count_kernel(const int64_t* __restrict__ labels, int64_t rows, int64_t classes,
+                                                         int64_t ignore, int* __restrict__ block_counts) {
+    const int64_t r = (int64_t)blockIdx.x * 1024 + threadIdx.x;
+    const bool v = r < rows && lce_valid(labels[r], classes, ignore);
+    const int n = __syncthreads_count(v);
+    if (threadIdx.x == 0) block_counts[blockIdx.x] = n;
+}
 __global__ void __launch_bounds__(1024) lce_compact_kernel(const int64_t* __restrict__ labels, int64_t rows, int64_t classes,
-                                                           int64_t ignore, float* __restrict__ out3, LceIndex ix) {
+                                                           int64_t ignore, const int* __restrict__ block_counts,
+                                                           float* __restrict__ out3, LceIndex ix) {
+    __shared__ int s_red[32];
     __shared__ int s_warp[32];
-    __shared__ int s_total;
-    const int per = (int)((rows + blockDim.x - 1) / blockDim.x);
-    const int64_t r_begin = (int64_t)threadIdx.x * per, r_end = min(rows, r_begin + per);
-    int local = 0;
-    for (int64_t r = r_begin; r < r_end; ++r) {
-        const int64_t y = labels[r];
-        local += (y == ignore || y < 0 || y >= classes) ? 0 : 1;
-    }
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    int incl = local;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += t;
+    // offset of this block = sum of the counts of the blocks before it (and the grand total for block 0's report)
+    int before = 0, total = 0;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += 1024) {
+        const int cnt = block_counts[i];
+        total += cnt;
+        if (i < (int)blockIdx.x) before += cnt;
     }
-    if (lane == 31) s_warp[wid] = incl;
-    __syncthreads();
-    if (wid == 0) {
-        int v = (lane < (int)(blockDim.x >> 5)) ? s_warp[lane] : 0;
-        int inc2 = v;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc2, o);
-            if (lane >= o) inc2 += t;
-        }
-        s_warp[lane] = inc2 - v;  // exclusive prefix of the warp totals
-        if (lane == 31) s_total = inc2;
+    for (int o = 16; o > 0; o >>= 1) {
+        before += __shfl_xor_sync(0xffffffffu, before, o);
+        total += __shfl_xor_sync(0xffffffffu, total, o);
+    }
+    if (lane == 0) {
+        s_red[wid] = before;
+        s_warp[wid] = total;
     }
     __syncthreads();
-    int at = s_warp[wid] + incl - local;
-    for (int64_t r = r_begin; r < r_end; ++r) {
-        const int64_t y = labels[r];
-        const bool valid = !(y == ignore || y < 0 || y >= classes);
-        if (valid) {
+    before = 0;
+    total = 0;
+    for (int w = 0; w < 32; ++w) {
+        before += s_red[w];
+        total += s_warp[w];
+    }
+    __syncthreads();
+    const int64_t r = (int64_t)blockIdx.x * 1024 + threadIdx.x;
+    const int64_t y = r < rows ? labels[r] : ignore;
+    const bool v = r < rows && lce_valid(y, classes, ignore);
+    const unsigned ballot = __ballot_sync(0xffffffffu, v);
+    if (lane == 0) s_warp[wid] = __popc(ballot);
+    __syncthreads();
+    int warp_base = 0;
+    for (int w = 0; w < wid; ++w) warp_base += s_warp[w];
+    if (r < rows) {
+        if (v) {
+            const int at = before + warp_base + __popc(ballot & ((1u << lane) - 1u));
             ix.idx[at] = (int)r;
             ix.labels[at] = y;
             ix.pos[r] = at;
-            ++at;
         } else {
             ix.pos[r] = -1;
         }
     }
-    if (threadIdx.x == 0) {
-        *ix.count = s_total;
-        out3[1] = (float)s_total;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        *ix.count = total;
+        out3[1] = (float)total;
     }
 }
 
@@ -820,6 +834,7 @@ size_t linear_ce_ws_bytes(int64_t rows, int c_in, int64_t classes) {
     const int64_t ch = std::min(rows, lce_chunk_rows(classes));
     return align_up((size_t)rows * pad8(c_in) * 2, 256) + align_up((size_t)ch * pad8(classes) * 2, 256) +
            align_up((size_t)rows * c_in * 4, 256) + 4 * align_up((size_t)rows * 8, 256) + 256 +
+           align_up((size_t)cdiv(rows, 1024) * 4, 256) +
            pio_gemm_bf16_ws_bytes(ch, c_in, classes) + 4096;
 }
 
@@ -839,9 +854,13 @@ int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, 
     PIO_TAKE_BYTES(int, pos, c, (size_t)rows * 4, who);
     PIO_TAKE_BYTES(int64_t, labels_c, c, (size_t)rows * 8, who);
     PIO_TAKE_BYTES(int, count, c, 256, who);
+    PIO_TAKE_BYTES(int, block_counts, c, (size_t)cdiv(rows, 1024) * 4, who);
     ix.count = count; ix.idx = idx; ix.pos = pos; ix.labels = labels_c;
 
-    lce_compact_kernel<<<1, 1024, 0, c.st>>>(labels, rows, classes, ignore, out3, ix);
+    const unsigned cblocks = (unsigned)cdiv(rows, 1024);
+    lce_count_kernel<<<cblocks, 1024, 0, c.st>>>(labels, rows, classes, ignore, block_counts);
+    PIO_LAUNCH_CHECK();
+    lce_compact_kernel<<<cblocks, 1024, 0, c.st>>>(labels, rows, classes, ignore, block_counts, out3, ix);
     PIO_LAUNCH_CHECK();
     const int row_blocks = (int)std::min<int64_t>(cdiv(rows, 8), (int64_t)num_sms() * 8);
     lce_gather_kernel<<<row_blocks, 256, 0, c.st>>>(x, c_in, x16c, cip, ix, rows);
