@@ -142,8 +142,10 @@ size_t pio_gemm_f32_ws_bytes(int64_t m, int64_t n, int64_t k);
 
 /* The same product on the bf16 tensor cores (tcgen05.mma, TMA-staged operands, fp32 accumulator in
  * TMEM) for PIO_MODE_BF16.  a / b are bf16; leading dimensions must be multiples of 8 elements and
- * bases 16-byte aligned (TMA).  Outputs: fp32 (c32) and/or bf16 (c16).  aux16 (bf16) plays the role
- * of `aux` above.  No rowsum: bias gradients are reduced by pio_colsum_bf16. */
+ * bases 16-byte aligned (TMA).  Outputs: fp32 (c32) and/or bf16 (c16).  aux16 (bf16) carries the GELU
+ * derivative between the passes: act 1 stores GELU'(pre-activation) to it (one erf serves both values),
+ * act 2 multiplies by it — the backward epilogue is a plain product.  No rowsum: bias gradients are
+ * reduced by pio_colsum_bf16. */
 typedef struct {
     const void* a;
     const void* b;

@@ -153,4 +153,11 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
     return cdf + x * pdf;
 }
 
+// GELU and its derivative from one erf evaluation
+__device__ __forceinline__ void gelu_erf_both(float x, float& g, float& dg) {
+    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+    g = x * cdf;
+    dg = cdf + x * 0.39894228040143267794f * __expf(-0.5f * x * x);
+}
+
 }  // namespace pio

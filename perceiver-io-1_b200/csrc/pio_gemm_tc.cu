@@ -54,8 +54,8 @@ enum EpiKind : int {
     EPI_F32_RES = 1,    // c32 = acc + bias + residual
     EPI_F32_ACC = 2,    // c32 += acc + bias
     EPI_B16 = 3,        // c16 = acc + bias
-    EPI_B16_GELU = 4,   // aux16 = acc + bias ; c16 = gelu(aux)
-    EPI_B16_DGELU = 5,  // c16 = acc * gelu'(aux16)
+    EPI_B16_GELU = 4,   // pre = acc + bias ; c16 = gelu(pre) ; aux16 = gelu'(pre)
+    EPI_B16_DGELU = 5,  // c16 = acc * aux16   (aux16 = gelu' saved by the forward)
     EPI_PARTIAL = 6,    // split-K partial sums
     EPI_GENERIC = 7,    // any other combination of outputs / flags
     EPI_F32_ATOMIC = 8  // c32 += acc with fp32 atomics (split-K without a reduction pass; order not deterministic)
@@ -160,26 +160,28 @@ __device__ __forceinline__ void epilogue_rows(const TcParams& p, const float* st
         } else if (KIND == EPI_B16) {
             store4_b16(p.c16 + gm * p.ldc16 + n, v, v16, valid);
         } else if (KIND == EPI_B16_GELU) {
-            if (p.aux16) store4_b16(p.aux16 + gm * p.ldaux + n, v, vaux, valid);
+            float dg[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v[j] = gelu_erf(v[j]);
+            for (int j = 0; j < 4; ++j) gelu_erf_both(v[j], v[j], dg[j]);
+            if (p.aux16) store4_b16(p.aux16 + gm * p.ldaux + n, dg, vaux, valid);
             store4_b16(p.c16 + gm * p.ldc16 + n, v, v16, valid);
         } else if (KIND == EPI_B16_DGELU) {
             float a[4];
             load4_b16(p.aux16 + gm * p.ldaux + n, a, vaux, valid);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v[j] *= gelu_erf_grad(a[j]);
+            for (int j = 0; j < 4; ++j) v[j] *= a[j];
             store4_b16(p.c16 + gm * p.ldc16 + n, v, v16, valid);
         } else {  // EPI_GENERIC
             if (p.act == 1) {
-                if (p.aux16) store4_b16(p.aux16 + gm * p.ldaux + n, v, vaux, valid);
+                float dg[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) v[j] = gelu_erf(v[j]);
+                for (int j = 0; j < 4; ++j) gelu_erf_both(v[j], v[j], dg[j]);
+                if (p.aux16) store4_b16(p.aux16 + gm * p.ldaux + n, dg, vaux, valid);
             } else if (p.act == 2) {
                 float a[4];
                 load4_b16(p.aux16 + gm * p.ldaux + n, a, vaux, valid);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) v[j] *= gelu_erf_grad(a[j]);
+                for (int j = 0; j < 4; ++j) v[j] *= a[j];
             }
             if (p.drop.threshold != 0) {
 #pragma unroll
@@ -378,8 +380,9 @@ static void tc_choose(int64_t m, int64_t n, int64_t k, bool splittable, int* bn,
     const int64_t tiles = cdiv(m, TC_BM) * cdiv(n, *bn);
     const int num_kb = (int)cdiv(k, TC_BK);
     int s = 1;
+    static const int min_kb = getenv("PIO_TC_SPLIT_MIN_KB") ? atoi(getenv("PIO_TC_SPLIT_MIN_KB")) : 16;
     if (splittable && num_kb >= 16 && tiles < sms) {
-        s = (int)std::min<int64_t>(cdiv(sms, tiles), num_kb / 4);
+        s = (int)std::min<int64_t>(cdiv(sms, tiles), num_kb / min_kb);
         s = std::max(s, 1);
     }
     int per = (int)cdiv(num_kb, s);

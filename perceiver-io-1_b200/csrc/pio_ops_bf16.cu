@@ -153,7 +153,7 @@ static int need_mult8(int v, const char* what, const char* who) {
 // ---------------------------------------------------------------- mlp
 struct MlpSaved {
     float* stats;
-    bf16 *h0, *h1, *g;
+    bf16 *h0, *h1, *g;  // LayerNorm output, GELU'(pre-activation) (written by the GELU epilogue), GELU output
     size_t total;
     MlpSaved(void* p, int64_t rows, int ch) {
         ByteCarver k{(char*)p, 0};

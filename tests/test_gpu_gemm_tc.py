@@ -118,21 +118,21 @@ def test_tc_gemm_epilogues(N, m, n, k):
     ref = xb[:, :k].double().cpu() @ wb[:, :k].double().cpu().t()
     c = _run(N, xb, wb, m, n, k, True, True, bias=bias.to(DEV), residual=res.to(DEV))
     assert_rel(c, ref + bias.double() + res.double(), 1e-5, "bias+res")
-    # GELU with bf16 pre-activation save and bf16 output
+    # GELU with the derivative saved as bf16 (one erf for both) and bf16 output
     ldn = _pad8(n)
     aux = torch.zeros(m, ldn, dtype=torch.bfloat16, device=DEV)
     c16 = torch.zeros(m, ldn, dtype=torch.bfloat16, device=DEV)
     c = _run(N, xb, wb, m, n, k, True, True, bias=bias.to(DEV), aux16=aux, act=1, c16=c16)
-    pre = ref + bias.double()
-    assert_rel(aux[:, :n].float(), pre, 8e-3, "preact bf16")
+    pre = (ref + bias.double()).requires_grad_(True)
+    O.gelu_erf(pre).sum().backward()
+    assert_rel(aux[:, :n].float(), pre.grad, 8e-3, "gelu' bf16")
+    pre = pre.detach()
     assert_rel(c, O.gelu_erf(pre), 1e-5, "gelu fp32")
     assert_rel(c16[:, :n].float(), O.gelu_erf(pre), 8e-3, "gelu bf16")
     assert (c16[:, n:] == 0).all()
-    # act=2 multiplies by GELU'(aux) evaluated on the bf16-rounded pre-activation
-    pre_t = aux[:, :n].double().cpu().requires_grad_(True)
-    O.gelu_erf(pre_t).sum().backward()
+    # act=2 multiplies by the saved derivative
     c = _run(N, xb, wb, m, n, k, True, True, aux16=aux, act=2)
-    assert_rel(c, ref * pre_t.grad, 2e-5, "dgelu")
+    assert_rel(c, ref * aux[:, :n].double().cpu(), 2e-5, "dgelu")
     # bf16-only output
     c16.zero_()
     _run(N, xb, wb, m, n, k, True, True, c16=c16, no_c32=True)
