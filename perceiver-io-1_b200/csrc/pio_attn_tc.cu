@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     constexpr int Q_BYTES = FA_BQ * DH * 2;   // 16 KB
     constexpr int KV_BYTES = BKV * DH * 2;    // 8 KB
     constexpr int P_BYTES = FA_BQ * BKV * 2;  // 16 KB
-    constexpr int TMEM_COLS = 256;            // S0 | S1 | O0 | O1, 64 columns each
+    constexpr int TMEM_COLS = 256;            // S0 | S1 | O (64 columns each; 256 allocated: power of two)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* sQ = smem;
@@ -166,9 +166,9 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                 const int s = j % KV_STAGES;
                 const uint32_t p_addr = smem_u32(sP + (j & 1) * P_BYTES), v_addr = smem_u32(sV + s * KV_BYTES);
 #pragma unroll
-                for (int t = 0; t < BKV / 16; ++t)
-                    umma_bf16(tmem_base + 128 + (uint32_t)(j & 1) * 64, make_smem_desc(p_addr + t * 32, 16, 1024),
-                              make_smem_desc(v_addr + t * 2048, BKV * 128, 1024), idesc_o, t > 0 ? 1u : 0u);
+                for (int t = 0; t < BKV / 16; ++t)  // O accumulates in TMEM across the key tiles
+                    umma_bf16(tmem_base + 128, make_smem_desc(p_addr + t * 32, 16, 1024),
+                              make_smem_desc(v_addr + t * 2048, BKV * 128, 1024), idesc_o, (j > 0 || t > 0) ? 1u : 0u);
                 umma_commit(&o_full[j & 1]);
                 umma_commit(&kv_empty[s]);
             }
@@ -181,23 +181,12 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
         const int tid = (warp - 2) * 32 + lane;  // 0..127 for cooperative loads
         const uint32_t lane_off = (uint32_t)(qd * 32) << 16;
         const uint8_t* padb = p.pad ? p.pad + (int64_t)b * p.m : nullptr;
-        float m_run = -INFINITY, l_run = 0.f, alpha_prev = 1.f;
-        float acc[DH];
-#pragma unroll
-        for (int d = 0; d < DH; ++d) acc[d] = 0.f;
-        auto fold_o = [&](int j, float alpha) {  // acc = acc * alpha + O(j)
-            mbar_wait(&o_full[j & 1], (uint32_t)(j >> 1) & 1u);
-            tc_fence_after();
-            const uint32_t to = tmem_base + 128 + (uint32_t)(j & 1) * 64 + lane_off;
-#pragma unroll
-            for (int c0 = 0; c0 < DH; c0 += 32) {
-                uint32_t r[32];
-                tmem_ld32(to + (uint32_t)c0, r);
-                tmem_ld_wait();
-#pragma unroll
-                for (int i = 0; i < 32; ++i) acc[c0 + i] = fmaf(acc[c0 + i], alpha, __uint_as_float(r[i]));
-            }
-        };
+        // Online softmax with a lazily updated reference maximum (m_ref, in log2 units): P = 2^(s - m_ref) may
+        // grow to 2^8 before the row's O accumulator (in TMEM) and running sum are rescaled, so after the first
+        // tiles almost no tile pays for a rescale and none pays for folding O through registers.
+        constexpr float LAZY = 8.0f;
+        float m_ref = -INFINITY, l_run = 0.f;
+        const uint32_t to = tmem_base + 128 + lane_off;
         for (int j = 0; j < T; ++j) {
             const int j0 = j * BKV;
             const bool masked = (padb != nullptr) || (j0 + BKV > p.m);  // CTA-uniform
@@ -221,8 +210,8 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
             float sv[64];
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
-                sv[i] = __uint_as_float(r0[i]) * p.scale_log2e;
-                sv[32 + i] = __uint_as_float(r1[i]) * p.scale_log2e;
+                sv[i] = __uint_as_float(r0[i]);
+                sv[32 + i] = __uint_as_float(r1[i]);
             }
             if (masked) {
 #pragma unroll
@@ -231,9 +220,32 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
             float mx = sv[0];
 #pragma unroll
             for (int i = 1; i < 64; ++i) mx = fmaxf(mx, sv[i]);
-            const float m_new = fmaxf(m_run, mx);
-            const float m_use = (m_new == -INFINITY) ? 0.f : m_new;  // fully masked so far: every p below is 0
-            const float alpha = fast_exp2(m_run - m_use);            // exp2(-inf) = 0 on the first live tile
+            mx *= p.scale_log2e;  // scale > 0: max commutes with it
+            // P(j) goes to the buffer PV(j-2) read: that product must be done
+            if (j >= 2) mbar_wait(&o_full[j & 1], (uint32_t)((j - 2) >> 1) & 1u);
+            const bool grow = mx > m_ref + LAZY || (m_ref == -INFINITY && mx != -INFINITY);
+            if (__any_sync(0xffffffffu, grow)) {
+                const float m_new = grow ? mx : m_ref;
+                const float alpha = (m_ref == -INFINITY) ? 0.f : fast_exp2(m_ref - m_new);  // 1 for rows that keep m_ref
+                if (j > 0) {  // O holds the sum over tiles < j: rescale this row of it
+                    mbar_wait(&o_full[(j - 1) & 1], (uint32_t)((j - 1) >> 1) & 1u);
+                    tc_fence_after();
+#pragma unroll
+                    for (int c0 = 0; c0 < DH; c0 += 32) {
+                        uint32_t r[32];
+                        tmem_ld32(to + (uint32_t)c0, r);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+                        tmem_st32(to + (uint32_t)c0, r);
+                    }
+                    tmem_st_wait();
+                }
+                l_run *= alpha;
+                m_ref = m_new;
+            }
+            const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;  // fully masked so far: every p below is 0
+            const float neg_m = -m_use;
             float l_tile = 0.f;
             uint8_t* pbuf = sP + (j & 1) * P_BYTES;
 #pragma unroll
@@ -241,7 +253,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                 float pv[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
-                    pv[i] = fast_exp2(sv[half * 32 + i] - m_use);
+                    pv[i] = fast_exp2(fmaf(sv[half * 32 + i], p.scale_log2e, neg_m));
                     l_tile += pv[i];
                 }
                 if constexpr (DROP) {  // the normaliser sees every key; only P.V sees the mask
@@ -251,16 +263,24 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                 }
                 store_row_half_bf16(pbuf, row, half, pv);
             }
-            l_run = l_run * alpha + l_tile;
-            m_run = m_new;
-            tc_fence_before();    // TMEM reads of S(j) are done before a later MMA may overwrite the buffer
+            l_run += l_tile;
+            tc_fence_before();    // TMEM reads of S(j) (and the rescale of O) are done before a later MMA touches them
             fence_proxy_async();  // P stores visible to the tensor-core (async) proxy
             __syncwarp();
             if (lane == 0) mbar_arrive(p_full);
-            if (j > 0) fold_o(j - 1, alpha_prev);  // O(j-1) finished while this tile's softmax ran
-            alpha_prev = alpha;
         }
-        fold_o(T - 1, alpha_prev);
+        mbar_wait(&o_full[(T - 1) & 1], (uint32_t)((T - 1) >> 1) & 1u);
+        tc_fence_after();
+        float acc[DH];
+#pragma unroll
+        for (int c0 = 0; c0 < DH; c0 += 32) {
+            uint32_t r[32];
+            tmem_ld32(to + (uint32_t)c0, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[c0 + i] = __uint_as_float(r[i]);
+        }
+        const float m_run = m_ref;
         tc_fence_before();
         const int qi = q0 + row;
         if (qi < p.n) {
