@@ -78,15 +78,14 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     constexpr int KV_STAGES = 3;
     constexpr int Q_BYTES = FA_BQ * DH * 2;   // 16 KB
     constexpr int KV_BYTES = BKV * DH * 2;    // 8 KB
-    constexpr int P_BYTES = FA_BQ * BKV * 2;  // 16 KB
-    constexpr int TMEM_COLS = 256;            // S0 | S1 | O (64 columns each; 256 allocated: power of two)
+    constexpr int TMEM_COLS = 256;            // S0 | S1 | O (64 columns each) | P0 | P1 (bf16 pairs, 32 columns each)
+    constexpr uint32_t TM_O = 128, TM_P = 192;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* sQ = smem;
     uint8_t* sK = sQ + Q_BYTES;                  // [KV_STAGES][KV_BYTES]
     uint8_t* sV = sK + KV_STAGES * KV_BYTES;     // [KV_STAGES][KV_BYTES]
-    uint8_t* sP = sV + KV_STAGES * KV_BYTES;     // [2][P_BYTES]
-    float* sBias = (float*)(sP + 2 * P_BYTES);   // [2][BKV]
+    float* sBias = (float*)(sV + KV_STAGES * KV_BYTES);  // [2][BKV]
     uint64_t* bars = (uint64_t*)(sBias + 2 * BKV);
     uint64_t* q_full = bars;
     uint64_t* kv_full = bars + 1;               // [3]
@@ -164,11 +163,12 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                 mbar_wait(p_full, (uint32_t)j & 1u);
                 tc_fence_after();
                 const int s = j % KV_STAGES;
-                const uint32_t p_addr = smem_u32(sP + (j & 1) * P_BYTES), v_addr = smem_u32(sV + s * KV_BYTES);
+                const uint32_t v_addr = smem_u32(sV + s * KV_BYTES);
+                const uint32_t p_tmem = tmem_base + TM_P + (uint32_t)(j & 1) * 32;
 #pragma unroll
-                for (int t = 0; t < BKV / 16; ++t)  // O accumulates in TMEM across the key tiles
-                    umma_bf16(tmem_base + 128, make_smem_desc(p_addr + t * 32, 16, 1024),
-                              make_smem_desc(v_addr + t * 2048, BKV * 128, 1024), idesc_o, (j > 0 || t > 0) ? 1u : 0u);
+                for (int t = 0; t < BKV / 16; ++t)  // P read from TMEM (no shared-memory A traffic); O accumulates in TMEM
+                    umma_bf16_ts(tmem_base + TM_O, p_tmem + (uint32_t)t * 8, make_smem_desc(v_addr + t * 2048, BKV * 128, 1024),
+                                 idesc_o, (j > 0 || t > 0) ? 1u : 0u);
                 umma_commit(&o_full[j & 1]);
                 umma_commit(&kv_empty[s]);
             }
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
         // tiles almost no tile pays for a rescale and none pays for folding O through registers.
         constexpr float LAZY = 8.0f;
         float m_ref = -INFINITY, l_run = 0.f;
-        const uint32_t to = tmem_base + 128 + lane_off;
+        const uint32_t to = tmem_base + TM_O + lane_off;
         for (int j = 0; j < T; ++j) {
             const int j0 = j * BKV;
             const bool masked = (padb != nullptr) || (j0 + BKV > p.m);  // CTA-uniform
@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
             const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;  // fully masked so far: every p below is 0
             const float neg_m = -m_use;
             float l_tile = 0.f;
-            uint8_t* pbuf = sP + (j & 1) * P_BYTES;
+            uint32_t pw[32];  // this row of P as bf16 pairs
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
                 float pv[32];
@@ -261,11 +261,16 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
 #pragma unroll
                     for (int i = 0; i < 32; ++i) pv[i] = drop_keep(p.drop, base + i) ? pv[i] * p.drop.inv_keep : 0.f;
                 }
-                store_row_half_bf16(pbuf, row, half, pv);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    __nv_bfloat162 h2 = __floats2bfloat162_rn(pv[2 * i], pv[2 * i + 1]);
+                    pw[half * 16 + i] = *reinterpret_cast<uint32_t*>(&h2);
+                }
             }
+            tmem_st32(tmem_base + TM_P + (uint32_t)(j & 1) * 32 + lane_off, pw);
+            tmem_st_wait();
             l_run += l_tile;
-            tc_fence_before();    // TMEM reads of S(j) (and the rescale of O) are done before a later MMA touches them
-            fence_proxy_async();  // P stores visible to the tensor-core (async) proxy
+            tc_fence_before();  // P is in TMEM, the reads of S(j) (and the rescale of O) are done: the MMA warp may go on
             __syncwarp();
             if (lane == 0) mbar_arrive(p_full);
         }
@@ -758,7 +763,7 @@ int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st, con
     p.batch = d->batch; p.heads = d->heads; p.n = d->n; p.m = d->m;
     p.scale_log2e = d->scale * 1.44269504088896340736f;
     p.drop = drop ? *drop : DropCfg{0, 0, 1.f};
-    const size_t smem = (size_t)FA_BQ * 64 * 2 + 6 * (size_t)BKV * 64 * 2 + 2 * (size_t)FA_BQ * BKV * 2 + 2 * BKV * 4 + 128 + 1024;
+    const size_t smem = (size_t)FA_BQ * 64 * 2 + 6 * (size_t)BKV * 64 * 2 + 2 * BKV * 4 + 128 + 1024;
     static bool configured = false;
     if (!configured) {
         PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

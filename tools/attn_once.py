@@ -3,7 +3,8 @@ import sys, ctypes, torch
 sys.path.insert(0,'/root/repo'); sys.path.insert(0,'/root/repo/perceiver-io-1_b200')
 from perceiver import _native as N
 L=N.lib(); DEV="cuda"
-b,n,m,heads,dh=32,256,16384,8,64; e=heads*dh
+import os
+b,n,m,heads,dh=int(os.environ.get("AB","32")),256,16384,8,64; e=heads*dh
 q=torch.randn(b,n,e,device=DEV).to(torch.bfloat16); kv=torch.randn(b,m,2*e,device=DEV).to(torch.bfloat16)
 do=torch.randn(b,n,e,device=DEV).to(torch.bfloat16)
 o=torch.empty(b,n,e,device=DEV); lse=torch.empty(b,heads,n,device=DEV)
