@@ -361,23 +361,23 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                           const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const FaBwdParams p) {
     constexpr int DH = 64, BKV = 64;
-    constexpr int Q_BYTES = FA_BQ * DH * 2, KV_BYTES = BKV * DH * 2, DS_BYTES = FA_BQ * BKV * 2;
+    constexpr int Q_BYTES = FA_BQ * DH * 2, KV_BYTES = BKV * DH * 2, KV_STAGES = 3;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* sQ = smem;
     uint8_t* sdO = sQ + Q_BYTES;
-    uint8_t* sK = sdO + Q_BYTES;      // [2]
-    uint8_t* sV = sK + 2 * KV_BYTES;  // [2]
-    uint8_t* sdS = sV + 2 * KV_BYTES;
-    float* sBias = (float*)(sdS + DS_BYTES);  // [2][BKV]
+    uint8_t* sK = sdO + Q_BYTES;              // [KV_STAGES]
+    uint8_t* sV = sK + KV_STAGES * KV_BYTES;  // [KV_STAGES]
+    float* sBias = (float*)(sV + KV_STAGES * KV_BYTES);  // [2][BKV]
     uint64_t* bars = (uint64_t*)(sBias + 2 * BKV);
     uint64_t* qdo_full = bars;
-    uint64_t* kv_full = bars + 1;   // [2]
-    uint64_t* kv_empty = bars + 3;  // [2]
-    uint64_t* sdp_full = bars + 5;
-    uint64_t* ds_full = bars + 6;
-    uint64_t* dq_done = bars + 7;
-    uint32_t* tmem_slot = (uint32_t*)(bars + 8);
+    uint64_t* kv_full = bars + 1;   // [3]
+    uint64_t* kv_empty = bars + 4;  // [3]
+    uint64_t* sdp_full = bars + 7;
+    uint64_t* sdp_read = bars + 8;  // the math warps hold S(j), dP(j) in registers: the next pair may be issued
+    uint64_t* ds_full = bars + 9;
+    uint64_t* dq_done = bars + 10;  // [2], one per dS buffer
+    uint32_t* tmem_slot = (uint32_t*)(bars + 12);
 
     pdl_trigger();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -387,10 +387,12 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmQ); prefetch_tmap(&tmdO); prefetch_tmap(&tmK); prefetch_tmap(&tmV);
         mbar_init(qdo_full, 1);
-        for (int s = 0; s < 2; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+        for (int s = 0; s < KV_STAGES; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
         mbar_init(sdp_full, 1);
+        mbar_init(sdp_read, 4);
         mbar_init(ds_full, 4);
-        mbar_init(dq_done, 1);
+        mbar_init(&dq_done[0], 1);
+        mbar_init(&dq_done[1], 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, 256);
@@ -399,7 +401,8 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();  // prologue done; everything below depends on earlier kernels' results
-    const uint32_t tmem_s = tmem_base, tmem_dp = tmem_base + 64, tmem_dq = tmem_base + 128;
+    // S | dP | dQ (64 columns each) | dS0 | dS1 (bf16 pairs, 32 columns each)
+    const uint32_t tmem_s = tmem_base, tmem_dp = tmem_base + 64, tmem_dq = tmem_base + 128, tmem_ds = tmem_base + 192;
 
     if (warp == 0) {
         if (lane == 0) {
@@ -407,8 +410,8 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
             tma_load_3d(sQ, &tmQ, h * DH, q0, b, qdo_full);
             tma_load_3d(sdO, &tmdO, h * DH, q0, b, qdo_full);
             for (int j = 0; j < T; ++j) {
-                const int s = j & 1;
-                const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+                const int s = j % KV_STAGES;
+                const uint32_t ph = (uint32_t)(j / KV_STAGES) & 1u;
                 mbar_wait(&kv_empty[s], ph ^ 1u);
                 mbar_expect_tx(&kv_full[s], 2 * KV_BYTES);
                 tma_load_3d(sK + s * KV_BYTES, &tmK, h * DH, j * BKV, b, &kv_full[s]);
@@ -421,11 +424,12 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
             const uint32_t idesc_kk = make_idesc(BKV, false, false);  // S, dP: both operands K-major
             const uint32_t idesc_dq = make_idesc(DH, false, true);    // dQ: dS K-major, K tile MN-major
             mbar_wait(qdo_full, 0);
-            const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sdO), ds_addr = smem_u32(sdS);
-            for (int j = 0; j < T; ++j) {
-                const int s = j & 1;
-                const uint32_t ph = (uint32_t)(j >> 1) & 1u;
-                mbar_wait(&kv_full[s], ph);
+            const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sdO);
+            // Software pipeline: S(j+1), dP(j+1) are issued as soon as the math warps have S(j), dP(j) in registers,
+            // so the tensor core works on the next score tile while they turn the current one into dS(j).
+            auto issue_sdp = [&](int j) {
+                const int s = j % KV_STAGES;
+                mbar_wait(&kv_full[s], (uint32_t)(j / KV_STAGES) & 1u);
                 tc_fence_after();
                 const uint32_t k_addr = smem_u32(sK + s * KV_BYTES), v_addr = smem_u32(sV + s * KV_BYTES);
 #pragma unroll
@@ -437,13 +441,24 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                     umma_bf16(tmem_dp, make_smem_desc(do_addr + t * 32, 16, 1024), make_smem_desc(v_addr + t * 32, 16, 1024), idesc_kk,
                               t > 0 ? 1u : 0u);
                 umma_commit(sdp_full);
+            };
+            issue_sdp(0);
+            for (int j = 0; j < T; ++j) {
+                const int s = j % KV_STAGES;
+                if (j + 1 < T) {
+                    mbar_wait(sdp_read, (uint32_t)j & 1u);
+                    tc_fence_after();
+                    issue_sdp(j + 1);
+                }
                 mbar_wait(ds_full, (uint32_t)j & 1u);
                 tc_fence_after();
+                const uint32_t k_addr = smem_u32(sK + s * KV_BYTES);
+                const uint32_t ds_tmem = tmem_ds + (uint32_t)(j & 1) * 32;
 #pragma unroll
-                for (int t = 0; t < BKV / 16; ++t)
-                    umma_bf16(tmem_dq, make_smem_desc(ds_addr + t * 32, 16, 1024), make_smem_desc(k_addr + t * 2048, BKV * 128, 1024),
-                              idesc_dq, (j > 0 || t > 0) ? 1u : 0u);
-                umma_commit(dq_done);
+                for (int t = 0; t < BKV / 16; ++t)  // A = dS from tensor memory
+                    umma_bf16_ts(tmem_dq, ds_tmem + (uint32_t)t * 8, make_smem_desc(k_addr + t * 2048, BKV * 128, 1024), idesc_dq,
+                                 (j > 0 || t > 0) ? 1u : 0u);
+                umma_commit(&dq_done[j & 1]);
                 umma_commit(&kv_empty[s]);
             }
         }
@@ -487,34 +502,45 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
             }
             mbar_wait(sdp_full, (uint32_t)j & 1u);
             tc_fence_after();
-            if (j > 0) mbar_wait(dq_done, (uint32_t)(j - 1) & 1u);  // previous dQ MMA has consumed the dS tile
+            if (j >= 2) mbar_wait(&dq_done[j & 1], (uint32_t)((j - 2) >> 1) & 1u);  // dQ(j-2) has consumed this dS buffer
+            uint32_t dw[32];  // this row of dS as bf16 pairs
 #pragma unroll
             for (int c0 = 0; c0 < BKV; c0 += 32) {
                 uint32_t rs[32], rp[32];
                 tmem_ld32(tmem_s + lane_off + (uint32_t)c0, rs);
                 tmem_ld32(tmem_dp + lane_off + (uint32_t)c0, rp);
                 tmem_ld_wait();
-                float ds[32];
-#pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    float e = __uint_as_float(rs[i]) * p.scale_log2e - lse2;
-                    if (masked) e += bias[c0 + i];
-                    const float pv = fast_exp2(e);
-                    float dpi = __uint_as_float(rp[i]);
-                    if constexpr (DROP) {
-                        const uint64_t idx = (((uint64_t)b * p.heads + h) * p.n + (uint64_t)qi) * (uint64_t)p.m + (uint64_t)(j0 + c0 + i);
-                        dpi = drop_keep(p.drop, idx) ? dpi * p.drop.inv_keep : 0.f;
-                    }
-                    ds[i] = pv * (dpi - delta) * p.scale;
+                if (c0 + 32 == BKV) {  // S(j), dP(j) are out of tensor memory: let the MMA warp issue the next pair
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(sdp_read);
                 }
-                store_row_half_bf16(sdS, row, c0 / 32, ds);
+#pragma unroll
+                for (int i = 0; i < 32; i += 2) {
+                    float ds2[2];
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) {
+                        float e = __uint_as_float(rs[i + u]) * p.scale_log2e - lse2;
+                        if (masked) e += bias[c0 + i + u];
+                        const float pv = fast_exp2(e);
+                        float dpi = __uint_as_float(rp[i + u]);
+                        if constexpr (DROP) {
+                            const uint64_t idx = (((uint64_t)b * p.heads + h) * p.n + (uint64_t)qi) * (uint64_t)p.m + (uint64_t)(j0 + c0 + i + u);
+                            dpi = drop_keep(p.drop, idx) ? dpi * p.drop.inv_keep : 0.f;
+                        }
+                        ds2[u] = pv * (dpi - delta) * p.scale;
+                    }
+                    __nv_bfloat162 hd = __floats2bfloat162_rn(ds2[0], ds2[1]);
+                    dw[(c0 + i) >> 1] = *reinterpret_cast<uint32_t*>(&hd);
+                }
             }
+            tmem_st32(tmem_ds + (uint32_t)(j & 1) * 32 + lane_off, dw);
+            tmem_st_wait();
             tc_fence_before();
-            fence_proxy_async();
             __syncwarp();
             if (lane == 0) mbar_arrive(ds_full);
         }
-        mbar_wait(dq_done, (uint32_t)(T - 1) & 1u);
+        mbar_wait(&dq_done[(T - 1) & 1], (uint32_t)((T - 1) >> 1) & 1u);
         tc_fence_after();
 #pragma unroll
         for (int c0 = 0; c0 < DH; c0 += 32) {
@@ -545,16 +571,14 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                            const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const FaBwdParams p) {
     constexpr int DH = 64, BQ2 = 64, BK2 = 128;
-    constexpr int K_BYTES = BK2 * DH * 2, Q_BYTES = BQ2 * DH * 2, P_BYTES = BK2 * BQ2 * 2;
+    constexpr int K_BYTES = BK2 * DH * 2, Q_BYTES = BQ2 * DH * 2;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* sK = smem;
     uint8_t* sV = sK + K_BYTES;
     uint8_t* sQ = sV + K_BYTES;        // [2]
     uint8_t* sdO = sQ + 2 * Q_BYTES;   // [2]
-    uint8_t* sP = sdO + 2 * Q_BYTES;   // P^T  (128 keys x 64 queries)
-    uint8_t* sdS = sP + P_BYTES;       // dS^T
-    float* sLse = (float*)(sdS + P_BYTES);  // [2][BQ2]
+    float* sLse = (float*)(sdO + 2 * Q_BYTES);  // [2][BQ2]
     float* sDelta = sLse + 2 * BQ2;         // [2][BQ2]
     uint64_t* bars = (uint64_t*)(sDelta + 2 * BQ2);
     uint64_t* kv_full = bars;
@@ -607,7 +631,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
             const uint32_t idesc_kk = make_idesc(BQ2, false, false);  // S^T, dP^T: K-major x K-major, N = 64 queries
             const uint32_t idesc_acc = make_idesc(DH, false, true);   // dV, dK: P^T / dS^T K-major, dO / Q tile MN-major
             mbar_wait(kv_full, 0);
-            const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV), p_addr = smem_u32(sP), ds_addr = smem_u32(sdS);
+            const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV);
             for (int i = 0; i < T; ++i) {
                 const int s = i & 1;
                 const uint32_t ph = (uint32_t)(i >> 1) & 1u;
@@ -626,13 +650,13 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                 mbar_wait(pds_full, (uint32_t)i & 1u);
                 tc_fence_after();
 #pragma unroll
-                for (int t = 0; t < BQ2 / 16; ++t)
-                    umma_bf16(tmem_dv, make_smem_desc(p_addr + t * 32, 16, 1024), make_smem_desc(do_addr + t * 2048, BQ2 * 128, 1024),
-                              idesc_acc, (i > 0 || t > 0) ? 1u : 0u);
+                for (int t = 0; t < BQ2 / 16; ++t)  // A = P^T from tensor memory (it overwrote S^T in place)
+                    umma_bf16_ts(tmem_dv, tmem_st + (uint32_t)t * 8, make_smem_desc(do_addr + t * 2048, BQ2 * 128, 1024), idesc_acc,
+                                 (i > 0 || t > 0) ? 1u : 0u);
 #pragma unroll
-                for (int t = 0; t < BQ2 / 16; ++t)
-                    umma_bf16(tmem_dk, make_smem_desc(ds_addr + t * 32, 16, 1024), make_smem_desc(q_addr + t * 2048, BQ2 * 128, 1024),
-                              idesc_acc, (i > 0 || t > 0) ? 1u : 0u);
+                for (int t = 0; t < BQ2 / 16; ++t)  // A = dS^T from tensor memory (over dP^T)
+                    umma_bf16_ts(tmem_dk, tmem_dpt + (uint32_t)t * 8, make_smem_desc(q_addr + t * 2048, BQ2 * 128, 1024), idesc_acc,
+                                 (i > 0 || t > 0) ? 1u : 0u);
                 umma_commit(acc_done);
                 umma_commit(&q_empty[s]);
             }
@@ -647,41 +671,56 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
         const bool key_ok = key < p.m;
         const bool dead_key = !key_ok || (p.pad != nullptr && p.pad[(int64_t)b * p.m + key] != 0);
         const int64_t stat_base = ((int64_t)b * p.heads + h) * p.n;
-        for (int i = 0; i < T; ++i) {
-            float* lse_s = sLse + (i & 1) * BQ2;
-            float* del_s = sDelta + (i & 1) * BQ2;
+        // lse / delta of a query tile are staged through shared memory one tile ahead, so their global loads are
+        // off the MMA -> math -> MMA chain
+        auto stage_stats = [&](int i) {
             if (tid < BQ2) {
                 const int qi = i * BQ2 + tid;
-                lse_s[tid] = (qi < p.n) ? p.lse[stat_base + qi] * 1.44269504088896340736f : INFINITY;  // invalid query: p = 0
-                del_s[tid] = (qi < p.n) ? p.delta[stat_base + qi] : 0.f;
+                sLse[(i & 1) * BQ2 + tid] = (qi < p.n) ? p.lse[stat_base + qi] * 1.44269504088896340736f : INFINITY;  // invalid query: p = 0
+                sDelta[(i & 1) * BQ2 + tid] = (qi < p.n) ? p.delta[stat_base + qi] : 0.f;
             }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+        };
+        stage_stats(0);
+        for (int i = 0; i < T; ++i) {
+            const float* lse_s = sLse + (i & 1) * BQ2;
+            const float* del_s = sDelta + (i & 1) * BQ2;
+            asm volatile("bar.sync 1, 128;" ::: "memory");  // stats of tile i visible; everyone is done with tile i-1's
+            if (i + 1 < T) stage_stats(i + 1);
             mbar_wait(sdp_full, (uint32_t)i & 1u);
             tc_fence_after();
-            if (i > 0) mbar_wait(acc_done, (uint32_t)(i - 1) & 1u);  // previous dV / dK MMAs have consumed P^T, dS^T
+            // P^T and dS^T go back into the TMEM columns S^T / dP^T came from (as bf16 pairs, 32 columns each) and feed
+            // the dV / dK products from there.  The next S^T / dP^T products are issued after those, on the same
+            // in-order tensor pipe, so nothing is overwritten early.
+            uint32_t pw[32], dw[32];
 #pragma unroll
             for (int c0 = 0; c0 < BQ2; c0 += 32) {
                 uint32_t rs[32], rp[32];
                 tmem_ld32(tmem_st + lane_off + (uint32_t)c0, rs);
                 tmem_ld32(tmem_dpt + lane_off + (uint32_t)c0, rp);
                 tmem_ld_wait();
-                float pv[32], ds[32];
 #pragma unroll
-                for (int q = 0; q < 32; ++q) {
-                    const float pr = dead_key ? 0.f : fast_exp2(__uint_as_float(rs[q]) * p.scale_log2e - lse_s[c0 + q]);
-                    float keep_scale = 1.f;
-                    if constexpr (DROP) {
-                        const uint64_t idx = (((uint64_t)b * p.heads + h) * p.n + (uint64_t)(i * BQ2 + c0 + q)) * (uint64_t)p.m + (uint64_t)key;
-                        keep_scale = drop_keep(p.drop, idx) ? p.drop.inv_keep : 0.f;
+                for (int q = 0; q < 32; q += 2) {
+                    float pv2[2], ds2[2];
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) {
+                        const float pr = dead_key ? 0.f : fast_exp2(__uint_as_float(rs[q + u]) * p.scale_log2e - lse_s[c0 + q + u]);
+                        float keep_scale = 1.f;
+                        if constexpr (DROP) {
+                            const uint64_t idx = (((uint64_t)b * p.heads + h) * p.n + (uint64_t)(i * BQ2 + c0 + q + u)) * (uint64_t)p.m + (uint64_t)key;
+                            keep_scale = drop_keep(p.drop, idx) ? p.drop.inv_keep : 0.f;
+                        }
+                        pv2[u] = pr * keep_scale;
+                        ds2[u] = pr * (__uint_as_float(rp[q + u]) * keep_scale - del_s[c0 + q + u]) * p.scale;
                     }
-                    pv[q] = pr * keep_scale;
-                    ds[q] = pr * (__uint_as_float(rp[q]) * keep_scale - del_s[c0 + q]) * p.scale;
+                    __nv_bfloat162 hp = __floats2bfloat162_rn(pv2[0], pv2[1]), hd = __floats2bfloat162_rn(ds2[0], ds2[1]);
+                    pw[(c0 + q) >> 1] = *reinterpret_cast<uint32_t*>(&hp);
+                    dw[(c0 + q) >> 1] = *reinterpret_cast<uint32_t*>(&hd);
                 }
-                store_row_half_bf16(sP, row, c0 / 32, pv);
-                store_row_half_bf16(sdS, row, c0 / 32, ds);
             }
+            tmem_st32(tmem_st + lane_off, pw);
+            tmem_st32(tmem_dpt + lane_off, dw);
+            tmem_st_wait();
             tc_fence_before();
-            fence_proxy_async();
             __syncwarp();
             if (lane == 0) mbar_arrive(pds_full);
         }
@@ -794,8 +833,8 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
     p.scale_log2e = d->scale * 1.44269504088896340736f;
     p.drop = drop ? *drop : DropCfg{0, 0, 1.f};
     static bool configured = false;
-    const size_t smem_dq = 2 * 16384 + 4 * 8192 + 16384 + 2 * 64 * 4 + 128 + 1024;
-    const size_t smem_dkv = 2 * 16384 + 4 * 8192 + 2 * 16384 + 4 * 64 * 4 + 128 + 1024;
+    const size_t smem_dq = 2 * 16384 + 6 * 8192 + 2 * 64 * 4 + 128 + 1024;
+    const size_t smem_dkv = 2 * 16384 + 4 * 8192 + 4 * 64 * 4 + 128 + 1024;
     if (!configured) {
         PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dq));
         PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dq));
