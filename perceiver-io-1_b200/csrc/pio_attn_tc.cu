@@ -41,12 +41,24 @@ __device__ __forceinline__ float fast_exp2(float x) {
     return y;
 }
 
+// descriptor of k-step t (16 elements) of a K-major operand tile of `rows` rows whose K extent may span several
+// 64-column swizzle atoms (each atom = rows x 128 bytes, stored one after the other)
+__device__ __forceinline__ uint64_t kmajor_desc(uint32_t base, int rows, int t) {
+    return make_smem_desc(base + (uint32_t)(t >> 2) * (uint32_t)(rows * 128) + (uint32_t)(t & 3) * 32, 16, 1024);
+}
+
 __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
             smem_u32(smem_dst)),
         "l"((uint64_t)map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
+}
+// a (rows x DH) bf16 tile as DH/64 swizzle atoms of rows x 64 columns
+template <int DH>
+__device__ __forceinline__ void tma_load_tile(uint8_t* dst, const CUtensorMap* map, int col0, int row0, int b, int rows, uint64_t* bar) {
+#pragma unroll
+    for (int a = 0; a < DH / 64; ++a) tma_load_3d(dst + a * rows * 128, map, col0 + a * 64, row0, b, bar);
 }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -69,17 +81,31 @@ __device__ __forceinline__ void store_row_half_bf16(uint8_t* region, int row, in
     }
 }
 
-template <int BKV, bool DROP>
-__global__ void __launch_bounds__(FA_THREADS, 2)
+__device__ __forceinline__ void store_row64_bf16_global(__nv_bfloat16* dst, const float (&v)[32], int c0) {
+#pragma unroll
+    for (int d = 0; d < 32; d += 8) {
+        uint32_t w[4];
+#pragma unroll
+        for (int e2 = 0; e2 < 4; ++e2) {
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[d + 2 * e2], v[d + 2 * e2 + 1]);
+            w[e2] = *reinterpret_cast<uint32_t*>(&h2);
+        }
+        *reinterpret_cast<uint4*>(dst + c0 + d) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+template <int BKV, bool DROP, int DH>
+__global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
     attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const FaParams p) {
     static_assert(BKV == 64, "the pipelined schedule is laid out for 64-key tiles");
-    constexpr int DH = 64;
+    static_assert(DH == 64 || DH == 128, "head size 64 or 128");
     constexpr int KV_STAGES = 3;
     constexpr int Q_BYTES = FA_BQ * DH * 2;   // 16 KB
     constexpr int KV_BYTES = BKV * DH * 2;    // 8 KB
-    constexpr int TMEM_COLS = 256;            // S0 | S1 | O (64 columns each) | P0 | P1 (bf16 pairs, 32 columns each)
-    constexpr uint32_t TM_O = 128, TM_P = 192;
+    // S0 | S1 (64 columns each) | O (DH columns) | P0 | P1 (bf16 pairs, 32 columns each)
+    constexpr int TMEM_COLS = DH == 64 ? 256 : 512;
+    constexpr uint32_t TM_O = 128, TM_P = 128 + DH;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* sQ = smem;
@@ -126,14 +152,14 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     if (warp == 0) {
         if (lane == 0) {
             mbar_expect_tx(q_full, Q_BYTES);
-            tma_load_3d(sQ, &tmQ, h * DH, q0, b, q_full);
+            tma_load_tile<DH>(sQ, &tmQ, h * DH, q0, b, FA_BQ, q_full);
             for (int j = 0; j < T; ++j) {
                 const int s = j % KV_STAGES;
                 const uint32_t ph = (uint32_t)(j / KV_STAGES) & 1u;
                 mbar_wait(&kv_empty[s], ph ^ 1u);
                 mbar_expect_tx(&kv_full[s], 2 * KV_BYTES);
-                tma_load_3d(sK + s * KV_BYTES, &tmK, h * DH, j * BKV, b, &kv_full[s]);
-                tma_load_3d(sV + s * KV_BYTES, &tmV, h * DH, j * BKV, b, &kv_full[s]);
+                tma_load_tile<DH>(sK + s * KV_BYTES, &tmK, h * DH, j * BKV, b, BKV, &kv_full[s]);
+                tma_load_tile<DH>(sV + s * KV_BYTES, &tmV, h * DH, j * BKV, b, BKV, &kv_full[s]);
             }
         }
         __syncwarp();
@@ -152,8 +178,8 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                 const uint32_t k_addr = smem_u32(sK + s * KV_BYTES);
 #pragma unroll
                 for (int t = 0; t < DH / 16; ++t)
-                    umma_bf16(tmem_base + (uint32_t)(j & 1) * 64, make_smem_desc(q_addr + t * 32, 16, 1024),
-                              make_smem_desc(k_addr + t * 32, 16, 1024), idesc_s, t > 0 ? 1u : 0u);
+                    umma_bf16(tmem_base + (uint32_t)(j & 1) * 64, kmajor_desc(q_addr, FA_BQ, t), kmajor_desc(k_addr, BKV, t), idesc_s,
+                              t > 0 ? 1u : 0u);
                 umma_commit(&s_full[j & 1]);
             };
             mbar_wait(q_full, 0);
@@ -276,40 +302,29 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
         }
         mbar_wait(&o_full[(T - 1) & 1], (uint32_t)((T - 1) >> 1) & 1u);
         tc_fence_after();
-        float acc[DH];
+        const float m_run = m_ref;
+        const int qi = q0 + row;
+        const float inv = 1.0f / l_run;  // l = 0 (every key padded): inf * 0 = NaN, like the reference
+        const int64_t off = (int64_t)b * p.o_bs + (int64_t)qi * p.o_rs + (int64_t)h * DH;
 #pragma unroll
         for (int c0 = 0; c0 < DH; c0 += 32) {
             uint32_t r[32];
-            tmem_ld32(to + (uint32_t)c0, r);
+            tmem_ld32(to + (uint32_t)c0, r);  // warp-collective: every lane takes part, valid row or not
             tmem_ld_wait();
+            if (qi < p.n) {
+                float acc[32];
 #pragma unroll
-            for (int i = 0; i < 32; ++i) acc[c0 + i] = __uint_as_float(r[i]);
-        }
-        const float m_run = m_ref;
-        tc_fence_before();
-        const int qi = q0 + row;
-        if (qi < p.n) {
-            const float inv = 1.0f / l_run;  // l = 0 (every key padded): inf * 0 = NaN, like the reference
-            const int64_t off = (int64_t)b * p.o_bs + (int64_t)qi * p.o_rs + (int64_t)h * DH;
-            if (p.o32) {
-                float* o = p.o32 + off;
+                for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(r[i]) * inv;
+                if (p.o32) {
+                    float* o = p.o32 + off + c0;
 #pragma unroll
-                for (int d = 0; d < DH; d += 4)
-                    *reinterpret_cast<float4*>(o + d) = make_float4(acc[d] * inv, acc[d + 1] * inv, acc[d + 2] * inv, acc[d + 3] * inv);
-            }
-            if (p.o16) {
-                __nv_bfloat16* o = p.o16 + off;
-#pragma unroll
-                for (int d = 0; d < DH; d += 8) {
-                    uint32_t w[4];
-#pragma unroll
-                    for (int e2 = 0; e2 < 4; ++e2) {
-                        __nv_bfloat162 h2 = __floats2bfloat162_rn(acc[d + 2 * e2] * inv, acc[d + 2 * e2 + 1] * inv);
-                        w[e2] = *reinterpret_cast<uint32_t*>(&h2);
-                    }
-                    *reinterpret_cast<uint4*>(o + d) = make_uint4(w[0], w[1], w[2], w[3]);
+                    for (int d = 0; d < 32; d += 4) *reinterpret_cast<float4*>(o + d) = make_float4(acc[d], acc[d + 1], acc[d + 2], acc[d + 3]);
                 }
+                if (p.o16) store_row64_bf16_global(p.o16 + off, acc, c0);
             }
+        }
+        tc_fence_before();
+        if (qi < p.n) {
             p.lse[((int64_t)b * p.heads + h) * p.n + qi] = (m_run + log2f(l_run)) * 0.69314718055994530942f;
         }
     }
@@ -342,26 +357,15 @@ struct FaBwdParams {
     DropCfg drop;
 };
 
-__device__ __forceinline__ void store_row64_bf16_global(__nv_bfloat16* dst, const float (&v)[32], int c0) {
-#pragma unroll
-    for (int d = 0; d < 32; d += 8) {
-        uint32_t w[4];
-#pragma unroll
-        for (int e2 = 0; e2 < 4; ++e2) {
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[d + 2 * e2], v[d + 2 * e2 + 1]);
-            w[e2] = *reinterpret_cast<uint32_t*>(&h2);
-        }
-        *reinterpret_cast<uint4*>(dst + c0 + d) = make_uint4(w[0], w[1], w[2], w[3]);
-    }
-}
-
 // dQ: CTA = 128 query rows of one (batch, head); streams key tiles of 64.
-template <bool DROP>
-__global__ void __launch_bounds__(FA_THREADS, 2)
+template <bool DROP, int DH>
+__global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
     attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                           const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const FaBwdParams p) {
-    constexpr int DH = 64, BKV = 64;
+    static_assert(DH == 64 || DH == 128, "head size 64 or 128");
+    constexpr int BKV = 64;
     constexpr int Q_BYTES = FA_BQ * DH * 2, KV_BYTES = BKV * DH * 2, KV_STAGES = 3;
+    constexpr int TMEM_COLS = DH == 64 ? 256 : 512;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* sQ = smem;
@@ -395,27 +399,27 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
         mbar_init(&dq_done[1], 1);
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc(tmem_slot, 256);
+    if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();  // prologue done; everything below depends on earlier kernels' results
-    // S | dP | dQ (64 columns each) | dS0 | dS1 (bf16 pairs, 32 columns each)
-    const uint32_t tmem_s = tmem_base, tmem_dp = tmem_base + 64, tmem_dq = tmem_base + 128, tmem_ds = tmem_base + 192;
+    // S | dP (64 columns each) | dQ (DH columns) | dS0 | dS1 (bf16 pairs, 32 columns each)
+    const uint32_t tmem_s = tmem_base, tmem_dp = tmem_base + 64, tmem_dq = tmem_base + 128, tmem_ds = tmem_base + 128 + DH;
 
     if (warp == 0) {
         if (lane == 0) {
             mbar_expect_tx(qdo_full, 2 * Q_BYTES);
-            tma_load_3d(sQ, &tmQ, h * DH, q0, b, qdo_full);
-            tma_load_3d(sdO, &tmdO, h * DH, q0, b, qdo_full);
+            tma_load_tile<DH>(sQ, &tmQ, h * DH, q0, b, FA_BQ, qdo_full);
+            tma_load_tile<DH>(sdO, &tmdO, h * DH, q0, b, FA_BQ, qdo_full);
             for (int j = 0; j < T; ++j) {
                 const int s = j % KV_STAGES;
                 const uint32_t ph = (uint32_t)(j / KV_STAGES) & 1u;
                 mbar_wait(&kv_empty[s], ph ^ 1u);
                 mbar_expect_tx(&kv_full[s], 2 * KV_BYTES);
-                tma_load_3d(sK + s * KV_BYTES, &tmK, h * DH, j * BKV, b, &kv_full[s]);
-                tma_load_3d(sV + s * KV_BYTES, &tmV, h * DH, j * BKV, b, &kv_full[s]);
+                tma_load_tile<DH>(sK + s * KV_BYTES, &tmK, h * DH, j * BKV, b, BKV, &kv_full[s]);
+                tma_load_tile<DH>(sV + s * KV_BYTES, &tmV, h * DH, j * BKV, b, BKV, &kv_full[s]);
             }
         }
         __syncwarp();
@@ -434,12 +438,10 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                 const uint32_t k_addr = smem_u32(sK + s * KV_BYTES), v_addr = smem_u32(sV + s * KV_BYTES);
 #pragma unroll
                 for (int t = 0; t < DH / 16; ++t)
-                    umma_bf16(tmem_s, make_smem_desc(q_addr + t * 32, 16, 1024), make_smem_desc(k_addr + t * 32, 16, 1024), idesc_kk,
-                              t > 0 ? 1u : 0u);
+                    umma_bf16(tmem_s, kmajor_desc(q_addr, FA_BQ, t), kmajor_desc(k_addr, BKV, t), idesc_kk, t > 0 ? 1u : 0u);
 #pragma unroll
                 for (int t = 0; t < DH / 16; ++t)
-                    umma_bf16(tmem_dp, make_smem_desc(do_addr + t * 32, 16, 1024), make_smem_desc(v_addr + t * 32, 16, 1024), idesc_kk,
-                              t > 0 ? 1u : 0u);
+                    umma_bf16(tmem_dp, kmajor_desc(do_addr, FA_BQ, t), kmajor_desc(v_addr, BKV, t), idesc_kk, t > 0 ? 1u : 0u);
                 umma_commit(sdp_full);
             };
             issue_sdp(0);
@@ -559,19 +561,21 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 256);
+        tmem_dealloc(tmem_base, TMEM_COLS);
     }
 }
 
 // dK, dV: CTA = 128 key rows of one (batch, head); streams query tiles of 64.  Works on the
 // transposed score tile S^T = K Q^T (thread = key row, column = query), so P^T and dS^T come out in
 // exactly the K-major layout the dV = P^T dO and dK = dS^T Q products read.
-template <bool DROP>
-__global__ void __launch_bounds__(FA_THREADS, 2)
+template <bool DROP, int DH>
+__global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
     attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                            const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const FaBwdParams p) {
-    constexpr int DH = 64, BQ2 = 64, BK2 = 128;
+    static_assert(DH == 64 || DH == 128, "head size 64 or 128");
+    constexpr int BQ2 = 64, BK2 = 128;
     constexpr int K_BYTES = BK2 * DH * 2, Q_BYTES = BQ2 * DH * 2;
+    constexpr int TMEM_COLS = DH == 64 ? 256 : 512;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* sK = smem;
@@ -603,26 +607,27 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
         mbar_init(acc_done, 1);
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc(tmem_slot, 256);
+    if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();  // prologue done; everything below depends on earlier kernels' results
-    const uint32_t tmem_st = tmem_base, tmem_dpt = tmem_base + 64, tmem_dv = tmem_base + 128, tmem_dk = tmem_base + 192;
+    // S^T | dP^T (64 columns each) | dV | dK (DH columns each)
+    const uint32_t tmem_st = tmem_base, tmem_dpt = tmem_base + 64, tmem_dv = tmem_base + 128, tmem_dk = tmem_base + 128 + DH;
 
     if (warp == 0) {
         if (lane == 0) {
             mbar_expect_tx(kv_full, 2 * K_BYTES);
-            tma_load_3d(sK, &tmK, h * DH, k0, b, kv_full);
-            tma_load_3d(sV, &tmV, h * DH, k0, b, kv_full);
+            tma_load_tile<DH>(sK, &tmK, h * DH, k0, b, BK2, kv_full);
+            tma_load_tile<DH>(sV, &tmV, h * DH, k0, b, BK2, kv_full);
             for (int i = 0; i < T; ++i) {
                 const int s = i & 1;
                 const uint32_t ph = (uint32_t)(i >> 1) & 1u;
                 mbar_wait(&q_empty[s], ph ^ 1u);
                 mbar_expect_tx(&q_full[s], 2 * Q_BYTES);
-                tma_load_3d(sQ + s * Q_BYTES, &tmQ, h * DH, i * BQ2, b, &q_full[s]);
-                tma_load_3d(sdO + s * Q_BYTES, &tmdO, h * DH, i * BQ2, b, &q_full[s]);
+                tma_load_tile<DH>(sQ + s * Q_BYTES, &tmQ, h * DH, i * BQ2, b, BQ2, &q_full[s]);
+                tma_load_tile<DH>(sdO + s * Q_BYTES, &tmdO, h * DH, i * BQ2, b, BQ2, &q_full[s]);
             }
         }
         __syncwarp();
@@ -640,12 +645,10 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
                 const uint32_t q_addr = smem_u32(sQ + s * Q_BYTES), do_addr = smem_u32(sdO + s * Q_BYTES);
 #pragma unroll
                 for (int t = 0; t < DH / 16; ++t)
-                    umma_bf16(tmem_st, make_smem_desc(k_addr + t * 32, 16, 1024), make_smem_desc(q_addr + t * 32, 16, 1024), idesc_kk,
-                              t > 0 ? 1u : 0u);
+                    umma_bf16(tmem_st, kmajor_desc(k_addr, BK2, t), kmajor_desc(q_addr, BQ2, t), idesc_kk, t > 0 ? 1u : 0u);
 #pragma unroll
                 for (int t = 0; t < DH / 16; ++t)
-                    umma_bf16(tmem_dpt, make_smem_desc(v_addr + t * 32, 16, 1024), make_smem_desc(do_addr + t * 32, 16, 1024), idesc_kk,
-                              t > 0 ? 1u : 0u);
+                    umma_bf16(tmem_dpt, kmajor_desc(v_addr, BK2, t), kmajor_desc(do_addr, BQ2, t), idesc_kk, t > 0 ? 1u : 0u);
                 umma_commit(sdp_full);
                 mbar_wait(pds_full, (uint32_t)i & 1u);
                 tc_fence_after();
@@ -747,7 +750,7 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 256);
+        tmem_dealloc(tmem_base, TMEM_COLS);
     }
 }
 
@@ -778,7 +781,52 @@ static int make_tmap3(CUtensorMap* map, const void* base, int64_t cols, int64_t 
 
 bool attn_fwd_tc_supported(const pio_attn_desc* d) {
     static const bool disabled = getenv("PIO_DISABLE_TC_ATTN") != nullptr;  // debugging aid: force the fp32-arithmetic kernel
-    return !disabled && d->dh == 64 && d->n > 0 && d->m > 0 && d->batch > 0;
+    return !disabled && (d->dh == 64 || d->dh == 128) && d->n > 0 && d->m > 0 && d->batch > 0;
+}
+
+template <int DH>
+static int launch_fwd(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const FaParams& p) {
+    constexpr int BKV = 64;
+    const size_t smem = (size_t)FA_BQ * DH * 2 + 6 * (size_t)BKV * DH * 2 + 2 * BKV * 4 + 128 + 1024;
+    static bool configured = false;  // per head size
+    if (!configured) {
+        PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV, false, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV, true, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    if (p.drop.threshold != 0) PIO_CUDA(launch_pdl(attn_fwd_tc_kernel<BKV, true, DH>, grid, dim3(FA_THREADS), smem, st, tq, tk, tv, p));
+    else PIO_CUDA(launch_pdl(attn_fwd_tc_kernel<BKV, false, DH>, grid, dim3(FA_THREADS), smem, st, tq, tk, tv, p));
+    return PIO_OK;
+}
+
+template <int DH>
+static int launch_bwd_dq(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const CUtensorMap& tdo, const CUtensorMap& tk,
+                         const CUtensorMap& tv, const FaBwdParams& p) {
+    const size_t smem = 2 * (size_t)FA_BQ * DH * 2 + 6 * (size_t)64 * DH * 2 + 2 * 64 * 4 + 128 + 1024;
+    static bool configured = false;
+    if (!configured) {
+        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<false, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<true, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    if (p.drop.threshold != 0) PIO_CUDA(launch_pdl(attn_bwd_dq_tc_kernel<true, DH>, grid, dim3(FA_THREADS), smem, st, tq, tdo, tk, tv, p));
+    else PIO_CUDA(launch_pdl(attn_bwd_dq_tc_kernel<false, DH>, grid, dim3(FA_THREADS), smem, st, tq, tdo, tk, tv, p));
+    return PIO_OK;
+}
+
+template <int DH>
+static int launch_bwd_dkv(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const CUtensorMap& tdo, const CUtensorMap& tk,
+                          const CUtensorMap& tv, const FaBwdParams& p) {
+    const size_t smem = 2 * (size_t)128 * DH * 2 + 4 * (size_t)64 * DH * 2 + 4 * 64 * 4 + 128 + 1024;
+    static bool configured = false;
+    if (!configured) {
+        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<false, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<true, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    if (p.drop.threshold != 0) PIO_CUDA(launch_pdl(attn_bwd_dkv_tc_kernel<true, DH>, grid, dim3(FA_THREADS), smem, st, tq, tdo, tk, tv, p));
+    else PIO_CUDA(launch_pdl(attn_bwd_dkv_tc_kernel<false, DH>, grid, dim3(FA_THREADS), smem, st, tq, tdo, tk, tv, p));
+    return PIO_OK;
 }
 
 // q, k, v of the descriptor are bf16 (element strides as given); writes o (fp32, optional via d->o),
@@ -802,16 +850,9 @@ int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st, con
     p.batch = d->batch; p.heads = d->heads; p.n = d->n; p.m = d->m;
     p.scale_log2e = d->scale * 1.44269504088896340736f;
     p.drop = drop ? *drop : DropCfg{0, 0, 1.f};
-    const size_t smem = (size_t)FA_BQ * 64 * 2 + 6 * (size_t)BKV * 64 * 2 + 2 * BKV * 4 + 128 + 1024;
-    static bool configured = false;
-    if (!configured) {
-        PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
-    }
     dim3 grid((unsigned)cdiv(d->n, FA_BQ), (unsigned)d->heads, (unsigned)d->batch);
-    if (p.drop.threshold != 0) PIO_CUDA(launch_pdl(attn_fwd_tc_kernel<BKV, true>, grid, dim3(FA_THREADS), smem, st, tq, tk, tv, p));
-    else PIO_CUDA(launch_pdl(attn_fwd_tc_kernel<BKV, false>, grid, dim3(FA_THREADS), smem, st, tq, tk, tv, p));
+    if (d->dh == 64) PIO_TRY((launch_fwd<64>(grid, st, tq, tk, tv, p)));
+    else PIO_TRY((launch_fwd<128>(grid, st, tq, tk, tv, p)));
     count_launch();
     return PIO_OK;
 }
@@ -832,16 +873,6 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
     p.scale = d->scale;
     p.scale_log2e = d->scale * 1.44269504088896340736f;
     p.drop = drop ? *drop : DropCfg{0, 0, 1.f};
-    static bool configured = false;
-    const size_t smem_dq = 2 * 16384 + 6 * 8192 + 2 * 64 * 4 + 128 + 1024;
-    const size_t smem_dkv = 2 * 16384 + 4 * 8192 + 4 * 64 * 4 + 128 + 1024;
-    if (!configured) {
-        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dq));
-        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dq));
-        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dkv));
-        PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_dkv));
-        configured = true;
-    }
     {   // dQ + delta: 128-row query tiles, 64-row key tiles
         CUtensorMap tq, tdo, tk, tv;
         PIO_TRY(make_tmap3(&tq, d->q, cols, d->n, d->batch, d->q_rs, d->q_bs, FA_BQ));
@@ -849,8 +880,8 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
         PIO_TRY(make_tmap3(&tk, d->k, cols, d->m, d->batch, d->k_rs, d->k_bs, 64));
         PIO_TRY(make_tmap3(&tv, d->v, cols, d->m, d->batch, d->v_rs, d->v_bs, 64));
         dim3 grid((unsigned)cdiv(d->n, FA_BQ), (unsigned)d->heads, (unsigned)d->batch);
-        if (p.drop.threshold != 0) PIO_CUDA(launch_pdl(attn_bwd_dq_tc_kernel<true>, grid, dim3(FA_THREADS), smem_dq, st, tq, tdo, tk, tv, p));
-        else PIO_CUDA(launch_pdl(attn_bwd_dq_tc_kernel<false>, grid, dim3(FA_THREADS), smem_dq, st, tq, tdo, tk, tv, p));
+        if (d->dh == 64) PIO_TRY((launch_bwd_dq<64>(grid, st, tq, tdo, tk, tv, p)));
+        else PIO_TRY((launch_bwd_dq<128>(grid, st, tq, tdo, tk, tv, p)));
         count_launch();
     }
     {   // dK, dV: 128-row key tiles, 64-row query tiles
@@ -860,8 +891,8 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
         PIO_TRY(make_tmap3(&tk, d->k, cols, d->m, d->batch, d->k_rs, d->k_bs, 128));
         PIO_TRY(make_tmap3(&tv, d->v, cols, d->m, d->batch, d->v_rs, d->v_bs, 128));
         dim3 grid((unsigned)cdiv(d->m, 128), (unsigned)d->heads, (unsigned)d->batch);
-        if (p.drop.threshold != 0) PIO_CUDA(launch_pdl(attn_bwd_dkv_tc_kernel<true>, grid, dim3(FA_THREADS), smem_dkv, st, tq, tdo, tk, tv, p));
-        else PIO_CUDA(launch_pdl(attn_bwd_dkv_tc_kernel<false>, grid, dim3(FA_THREADS), smem_dkv, st, tq, tdo, tk, tv, p));
+        if (d->dh == 64) PIO_TRY((launch_bwd_dkv<64>(grid, st, tq, tdo, tk, tv, p)));
+        else PIO_TRY((launch_bwd_dkv<128>(grid, st, tq, tdo, tk, tv, p)));
         count_launch();
     }
     return PIO_OK;

@@ -45,13 +45,13 @@ def _run(N, q16, k16, v16, q_rs, k_rs, pad, b, heads, n, m, dh, mode=1):
     return o, lse
 
 
+@pytest.mark.parametrize("dh", [64, 128])
 @pytest.mark.parametrize("b,n,m,heads,padded", [
     (2, 128, 64, 1, False), (2, 128, 128, 2, False), (3, 64, 512, 4, True), (2, 256, 1024, 8, False), (2, 70, 200, 2, True),
     (1, 1, 64, 1, False), (2, 512, 64, 4, False), (1, 300, 4100, 2, True), (2, 64, 64, 4, False)])
-def test_flash_tc_forward_cross_layout(N, b, n, m, heads, padded):
-    """separate q (B,N,E) and packed kv (B,M,2E) — the cross-attention layout"""
+def test_flash_tc_forward_cross_layout(N, b, n, m, heads, padded, dh):
+    """separate q (B,N,E) and packed kv (B,M,2E) — the cross-attention layout; head sizes 64 and 128"""
     torch.manual_seed(0)
-    dh = 64
     e = heads * dh
     q = torch.randn(b, n, e)
     kv = torch.randn(b, m, 2 * e)
@@ -111,14 +111,14 @@ def _ref_grads(q, k, v, do, pad, heads):
     return o.detach(), lse.detach(), q.grad, k.grad, v.grad
 
 
+@pytest.mark.parametrize("dh", [64, 128])
 @pytest.mark.parametrize("b,n,m,heads,padded", [
     (2, 128, 64, 1, False), (2, 64, 512, 4, True), (2, 256, 1024, 2, False), (2, 70, 200, 2, True), (1, 1, 64, 1, False),
-    (2, 512, 64, 4, False), (1, 300, 1100, 2, True), (3, 64, 64, 4, False)])
-def test_flash_tc_backward(N, b, n, m, heads, padded):
+    (2, 512, 64, 4, False), (1, 300, 1100, 2, True), (3, 64, 64, 4, False), (2, 256, 256, 4, False)])
+def test_flash_tc_backward(N, b, n, m, heads, padded, dh):
     """dq, dk, dv of the tcgen05 backward against fp64 autograd over the same bf16-rounded q, k, v, dO.
-    The kernels round P, dS and the outputs to bf16, hence the bf16 tolerance."""
+    The kernels round P, dS and the outputs to bf16, hence the bf16 tolerance.  Head sizes 64 and 128."""
     torch.manual_seed(3)
-    dh = 64
     e = heads * dh
     q, kv, do = torch.randn(b, n, e), torch.randn(b, m, 2 * e), torch.randn(b, n, e)
     pad = None

@@ -3,8 +3,8 @@ sys.path.insert(0,'/root/repo'); sys.path.insert(0,'/root/repo/perceiver-io-1_b2
 from perceiver import _native as N
 L=N.lib(); DEV="cuda"
 which = sys.argv[1] if len(sys.argv)>1 else "all"
-def run(b,n,m,heads,reps=5,bwd=True):
-    dh=64; e=heads*dh
+def run(b,n,m,heads,reps=5,bwd=True,dh=64):
+    e=heads*dh
     q=torch.randn(b,n,e,device=DEV).to(torch.bfloat16); kv=torch.randn(b,m,2*e,device=DEV).to(torch.bfloat16)
     do=torch.randn(b,n,e,device=DEV).to(torch.bfloat16)
     o=torch.empty(b,n,e,device=DEV); lse=torch.empty(b,heads,n,device=DEV)
@@ -31,6 +31,7 @@ def run(b,n,m,heads,reps=5,bwd=True):
 if which=="fwdonly":
     run(32,256,16384,8,reps=1,bwd=False); sys.exit(0)
 run(32,256,16384,8)
+run(32,256,256,4,dh=128)
 run(32,256,8192,8)
 run(8,256,65536,8)
 run(64,64,512,4)
