@@ -466,6 +466,10 @@ def gpu_arm(args):
         launches += graph_launches * args.steps  # replays do not pass through the host-side counter
     clocks = sampler.stop() if rank == 0 else None
     if args.profile_only:
+        if args.timeline and rank != 0:  # every rank runs the two extra steps (they hold a collective); rank 0 records
+            for _ in range(2):
+                step(ids_d, pad_d)
+            torch.cuda.synchronize()
         if rank == 0 and args.timeline:
             from torch.profiler import ProfilerActivity, profile
             with profile(activities=[ProfilerActivity.CUDA]) as prof:
