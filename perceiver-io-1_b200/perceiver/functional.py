@@ -161,6 +161,7 @@ class shadow_scope:
         _SH["depth"] += 1
         if _SH["depth"] == 1:
             _SH["grad"] = torch.is_grad_enabled()
+            _PENDING.clear()  # (a backward pass that died half-way never ran its clean-up callback)
         if _SH["depth"] == 1 and _MODE["mode"] == N.MODE_BF16 and _SH["grad"]:
             _SH["epoch"] += 1
             _SH["seen"] = {}
@@ -183,27 +184,80 @@ def _mat(w, mode):
     return _w16(w)
 
 
+# Parameters applied more than once in a forward (the shared `layer_n` of PerceiverEncoder, reference
+# model.py:186-187) get one gradient buffer per backward pass: the first backward that reaches such a parameter
+# allocates it and hands it to autograd, later ones add into the same memory (the kernels accumulate with
+# atomics anyway) and report None — so autograd has nothing left to sum, which was one small add kernel per shared
+# tensor per step.  Keyed by the parameter's storage address; forgotten when the backward pass ends.
+_PENDING = {}  # parameter storage -> device address of its gradient buffer (an address only: a tensor reference
+#                here would stop autograd from adopting the buffer as .grad without a copy)
+_REUSED = set()
+
+
+class _Alias:
+    """stands in for a gradient tensor that autograd already holds: just its address"""
+
+    def __init__(self, address):
+        self._address = address
+
+    def data_ptr(self):
+        return self._address
+
+    def element_size(self):
+        return 4
+
+
+def _forget_pending():
+    _PENDING.clear()
+
+
 def _grads_like(params, mode):
     """Gradient buffers shaped like ``params`` (None stays None) and the `accumulate` flag to pass.
     fp32 mode: uninitialised buffers, overwritten (0).  bf16 mode: views into one zero-filled slab so the
-    kernels can add into them with atomics (2) and skip their reduction passes."""
+    kernels can add into them with atomics (2) and skip their reduction passes; a parameter that already got a
+    buffer earlier in this backward pass gets that one again (return the result through `_out`)."""
     if mode == N.MODE_FP32:
         return [torch.empty_like(p) if p is not None else None for p in params], 0
-    live = [p for p in params if p is not None]
+    _REUSED.clear()
+    keys = [None if p is None else (p.data_ptr(), p.numel(), p.device) for p in params]
+    fresh = [p for p, k in zip(params, keys) if p is not None and k not in _PENDING]
     offs, total = [], 0
-    for p in live:
+    for p in fresh:
         offs.append(total)
         total += (p.numel() + 3) // 4 * 4
-    slab = torch.zeros(total, dtype=torch.float32, device=live[0].device)
-    it = iter(zip(live, offs))
+    slab = torch.zeros(total, dtype=torch.float32, device=fresh[0].device) if fresh else None
+    share = bool(_PENDING)  # a non-empty table means this pass already registered its end-of-pass callback
+    if fresh and not share:
+        try:
+            torch.autograd.Variable._execution_engine.queue_callback(_forget_pending)
+            share = True
+        except RuntimeError:  # not inside a backward pass (direct call): nothing to share across calls
+            share = False
+    it = iter(offs)
     out = []
-    for p in params:
+    for p, k in zip(params, keys):
         if p is None:
             out.append(None)
+        elif k in _PENDING:
+            g = _Alias(_PENDING[k])
+            _REUSED.add(id(g))
+            out.append(g)
         else:
-            q, o = next(it)
-            out.append(slab[o:o + q.numel()].view(q.shape))
+            o = next(it)
+            g = slab[o:o + p.numel()].view(p.shape)
+            if share:
+                _PENDING[k] = g.data_ptr()
+            out.append(g)
     return out, 2
+
+
+def _out(*grads):
+    """what a backward returns: buffers autograd already holds (see _grads_like) are reported as None"""
+    if not _REUSED:
+        return grads
+    res = tuple(None if (g is not None and id(g) in _REUSED) else g for g in grads)
+    _REUSED.clear()
+    return res
 
 
 def _mha_ptrs(w_packed, w_q, w_k, w_v, bias, e):
@@ -364,7 +418,7 @@ class MlpFn(torch.autograd.Function):
                               rows, c, residual, _dref(drop), mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)),
                 "pio_mlp_bwd")
         ctx.saved_buf = None
-        return (dx, *grads, None, None, None)
+        return _out(dx, *grads, None, None, None)
 
 
 class KVProjectFn(torch.autograd.Function):
@@ -422,7 +476,7 @@ class KVProjectFn(torch.autograd.Function):
                                      byref(g), accf, rows, ckv, e, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
                 "pio_kv_project_bwd")
         ctx.saved_buf = None
-        return dx, dln_w, dln_b, dbias, dwp, dwk, dwv, None
+        return _out(dx, dln_w, dln_b, dbias, dwp, dwk, dwv, None)
 
 
 class CrossAttendFn(torch.autograd.Function):
@@ -486,7 +540,7 @@ class CrossAttendFn(torch.autograd.Function):
                                        residual, _dref(drop), mode, ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
                 "pio_cross_attend_bwd")
         ctx.saved_buf = None
-        return dx, dkv, None, dln_w, dln_b, dbias, dwp, dwq, dwo, dbo, None, None, None, None
+        return _out(dx, dkv, None, dln_w, dln_b, dbias, dwp, dwq, dwo, dbo, None, None, None, None)
 
 
 _SA_NAMES = ("ln_w", "ln_b", "in_w", "in_b", "wo", "bo")
@@ -545,7 +599,7 @@ class SelfAttnFn(torch.autograd.Function):
                                     N.stream_ptr(x.device)),
                 "pio_self_attn_bwd")
         ctx.saved_buf = None
-        return (dx, *grads, None, None, None, None)
+        return _out(dx, *grads, None, None, None, None)
 
 
 class LatentBlockFn(torch.autograd.Function):
@@ -609,7 +663,7 @@ class LatentBlockFn(torch.autograd.Function):
                                        mlp_g, accf, layers, b, n, c, heads, _dref(drop), mode, ws.data_ptr(), ws.numel(),
                                        N.stream_ptr(x.device)), "pio_latent_block_bwd")
         ctx.saved_buf = None
-        return (dx, None, None, None, *grads)
+        return _out(dx, None, None, None, *grads)
 
 
 class LinearFn(torch.autograd.Function):
