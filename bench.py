@@ -234,8 +234,19 @@ def roofline_dominant_kernel(mode, pk, reps=10):
     flops_each = 2.0 * rows * c * v
     total_ms = sum(out.values())
     achieved = flops_each * len(out) / (total_ms * 1e-3) / 1e12
+    traffic, traffic_note = None, None
+    if mode == 1:  # DRAM bytes per launch from the committed ncu --set full capture of these same three launches
+        try:
+            tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_roofline_traffic.json")))
+            per = tj["bytes_per_launch"]
+            traffic = round(sum(per[k] for k in out) / len(out))
+            traffic_note = {"per_product": per, "source": tj["source"],
+                            "algorithmic_bytes": {"logits": 2 * (rows * c + v * c + rows * vp), "dx": 2 * (rows * vp + v * c) + 4 * rows * c,
+                                                  "dW": 2 * (rows * vp + rows * c) + 4 * v * c}}
+        except Exception:
+            pass
     return {"kernel": kernel, "bound": "tensor", "achieved": round(achieved, 2), "peak": pk["tflops"], "unit": "TFLOP/s",
-            "frac": round(achieved / pk["tflops"], 5), "traffic": None,
+            "frac": round(achieved / pk["tflops"], 5), "traffic": traffic, "traffic_detail": traffic_note,
             "ms_per_launch": {k: round(t, 4) for k, t in out.items()},
             "tflops_per_launch": {k: round(flops_each / (t * 1e-3) / 1e12, 1) for k, t in out.items()},
             "flops_per_launch": flops_each, "shape_mnk": [rows, v, c], "peak_source": pk["source"] + " (burst)"}
