@@ -363,7 +363,13 @@ def gpu_arm(args):
     if distributed and not graph_ok:
         net = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local_rank], gradient_as_bucket_view=True,
                                                         find_unused_parameters=False)
-    opt = torch.optim.AdamW(model.parameters(), lr=CFG["lr"], fused=True)
+    def make_optimizer(capturable=False):
+        """bf16 mode: the library's own one-launch AdamW (also writes the bf16 weight shadows; same update as
+        torch.optim.AdamW, tests/test_gpu_optim.py).  fp32 mode and --torch-optimizer: torch's fused AdamW."""
+        if mode == 1 and not args.torch_optimizer:
+            return perceiver.FusedAdamW(model.parameters(), lr=CFG["lr"])
+        return torch.optim.AdamW(model.parameters(), lr=CFG["lr"], fused=True, capturable=capturable)
+    opt = make_optimizer()
     ids_h, pad_h = synthetic_batch(rank, CFG["batch"], CFG["seq"], CFG["vocab"])  # distinct data per rank
     ids_h, pad_h = ids_h.pin_memory(), pad_h.pin_memory()
     ids_d, pad_d = ids_h.to(dev), pad_h.to(dev)
@@ -388,7 +394,7 @@ def gpu_arm(args):
     use_graph = fused_loss and not args.no_graph
     graph = None
     if use_graph:
-        opt = torch.optim.AdamW(model.parameters(), lr=CFG["lr"], fused=True, capturable=True)
+        opt = make_optimizer(capturable=True)
         g_ids = torch.empty_like(ids_d)
         g_labels = torch.empty_like(ids_d)
         g_pad = pad_d.clone()
@@ -554,7 +560,9 @@ def gpu_arm(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32" if mode == 0 else "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "global_batch": world * CFG["batch"], "seq_len": CFG["seq"],
-                       "parallelism": f"dp{world}", "optimizer": "AdamW(fused) lr 3e-3",
+                       "parallelism": f"dp{world}",
+                       "optimizer": ("perceiver.FusedAdamW (pio_adamw_step, one launch) lr 3e-3" if (mode == 1 and not args.torch_optimizer)
+                                     else "torch.optim.AdamW(fused) lr 3e-3"),
                        "grad_exchange": ("none" if not distributed else
                                          ("flat NCCL all-reduce(avg) after the captured forward+backward graph" if graph is not None
                                           else "torch DDP buckets overlapped with backward")),
@@ -610,6 +618,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="do not capture the step into a CUDA graph")
     ap.add_argument("--profile-only", action="store_true", help="timed steps only (for ncu launch lists)")
+    ap.add_argument("--torch-optimizer", action="store_true", help="torch.optim.AdamW(fused=True) instead of perceiver.FusedAdamW")
     ap.add_argument("--timeline", default=None, help="with --profile-only: CSV of (stream, start_us, dur_us, kernel) of 2 more steps")
     ap.add_argument("--mode", default=os.environ.get("PIO_MODE", "bf16"), choices=["fp32", "bf16"])
     args = ap.parse_args()

@@ -193,6 +193,35 @@ typedef struct {
 } pio_cast_item;
 int pio_cast_bf16_multi(const pio_cast_item* items, int count, pio_stream_t stream);
 
+/* AdamW (decoupled weight decay) over a whole parameter set in one launch — the optimizer step of the
+ * reference's LightningModules (torch.optim.AdamW, lightning.py:67-72).  Same update as
+ * torch.optim.AdamW:  p *= 1 - lr*wd;  m = b1*m + (1-b1)*g;  v = b2*v + (1-b2)*g*g;
+ * p -= lr/(1-b1^t) * m / (sqrt(v)/sqrt(1-b2^t) + eps), with t = hyper[5] + 1.
+ * `tensors` and `chunks` live in DEVICE memory: one entry per parameter tensor, and a list cutting the tensors
+ * into pieces of at most PIO_ADAMW_CHUNK elements, one CTA each.  When shadow16 is non-null the updated
+ * parameter is also written as bf16 at row pitch ld16 (the weight shadow the bf16 GEMMs read), so no separate
+ * cast pass follows the step.  `hyper` (DEVICE memory, 6 floats) = {lr, beta1, beta2, eps, weight_decay,
+ * steps_done}: the kernel reads it, so a captured launch follows schedulers that rewrite it; pio_adamw_tick
+ * adds 1 to steps_done afterwards. */
+#define PIO_ADAMW_CHUNK 16384
+typedef struct {
+    float* p;
+    const float* g;
+    float* m;
+    float* v;
+    void* shadow16;   /* bf16 shadow of p (rows x ld16), or NULL */
+    int32_t cols;     /* row length of p (for the shadow's pitch); 0 when shadow16 is NULL */
+    int32_t ld16;
+} pio_adamw_tensor;
+typedef struct {
+    int32_t tensor;   /* index into `tensors` */
+    int32_t count;    /* elements in this piece (<= PIO_ADAMW_CHUNK) */
+    int64_t offset;   /* first element of this piece within the tensor */
+} pio_adamw_chunk;
+int pio_adamw_step(const pio_adamw_tensor* tensors, const pio_adamw_chunk* chunks, int n_chunks, const float* hyper,
+                   pio_stream_t stream);
+int pio_adamw_tick(float* hyper, pio_stream_t stream);
+
 /* Attention core of nn.MultiheadAttention as called at model.py:74 (dropout 0):
  * S = (q dh^-1/2) k^T, padded keys -> -inf, P = softmax(S), O = P v.  Flash-style: P is never
  * stored; lse (batch,heads,n) = logsumexp of the scaled scores, saved for the backward, which

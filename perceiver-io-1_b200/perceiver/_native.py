@@ -92,6 +92,8 @@ _SIGNATURES = {
     "pio_gemm_bf16_ws_bytes": (c_size_t, [c_int64, c_int64, c_int64]),
     "pio_cast_bf16": (c_int, [P, P, c_int64, c_int, c_int64, c_int64, P]),
     "pio_cast_bf16_multi": (c_int, [P, c_int, P]),
+    "pio_adamw_step": (c_int, [P, P, c_int, P, P]),
+    "pio_adamw_tick": (c_int, [P, P]),
     "pio_attn_fwd": (c_int, [POINTER(AttnDesc), c_int, P]),
     "pio_attn_bwd": (c_int, [POINTER(AttnBwdDesc), c_int, P]),
     "pio_attn_bwd_bf16": (c_int, [POINTER(AttnDesc), P, P, P, P, P, P]),

@@ -127,8 +127,12 @@ def _refresh_shadows(module, epoch):
         if hit is None or hit[1] != w.data_ptr() or not w.requires_grad or w.device != table.device:
             _TABLES.pop(module, None)  # parameters were replaced / moved / frozen: start over
             return
-    N.check(N.lib().pio_cast_bf16_multi(table.data_ptr(), len(weights), N.stream_ptr(table.device)), "pio_cast_bf16_multi")
+    if all(getattr(w, "_pio_fresh16", False) and w._pio_w16[0] == w._version for w in weights):
+        pass  # perceiver.optim.FusedAdamW wrote every shadow together with the parameter: nothing to cast
+    else:
+        N.check(N.lib().pio_cast_bf16_multi(table.data_ptr(), len(weights), N.stream_ptr(table.device)), "pio_cast_bf16_multi")
     for w in weights:
+        w._pio_fresh16 = False
         w._pio_w16 = (w._version, w.data_ptr(), w._pio_w16[2], epoch, True)
 
 
