@@ -29,8 +29,11 @@ def average_gradients(params: Iterable[torch.nn.Parameter], group: Optional[dist
     if world == 1:
         return
     flat = flatten_gradients(params)
-    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
-    flat.div_(world)
+    if flat.is_cuda and dist.get_backend(group) == "nccl":
+        dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=group)  # NCCL averages in the collective: one pass less
+    else:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        flat.div_(world)
     offset = 0
     views = []
     for p in params:
