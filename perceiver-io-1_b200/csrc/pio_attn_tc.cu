@@ -54,11 +54,21 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
         "l"((uint64_t)map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
-// a (rows x DH) bf16 tile as DH/64 swizzle atoms of rows x 64 columns
+// a bf16 tile of `rows` rows as ATOMS swizzle atoms of rows x 64 columns, starting at column col0.  Head size 32
+// loads the 64-column box that holds the head and its neighbour; the products then address the head's half of
+// each 128-byte row (HeadGeom::sub) and run two k-steps instead of four.
+template <int DH>
+struct HeadGeom {
+    static constexpr int ATOMS = (DH + 63) / 64;
+    static constexpr int TILE_COLS = ATOMS * 64;
+    static constexpr int KS = DH / 16;
+    __device__ static int col0(int h) { return DH == 32 ? (h >> 1) * 64 : h * DH; }
+    __device__ static uint32_t sub(int h) { return DH == 32 ? (uint32_t)(h & 1) * 64u : 0u; }
+};
 template <int DH>
 __device__ __forceinline__ void tma_load_tile(uint8_t* dst, const CUtensorMap* map, int col0, int row0, int b, int rows, uint64_t* bar) {
 #pragma unroll
-    for (int a = 0; a < DH / 64; ++a) tma_load_3d(dst + a * rows * 128, map, col0 + a * 64, row0, b, bar);
+    for (int a = 0; a < HeadGeom<DH>::ATOMS; ++a) tma_load_3d(dst + a * rows * 128, map, col0 + a * 64, row0, b, bar);
 }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -95,16 +105,17 @@ __device__ __forceinline__ void store_row64_bf16_global(__nv_bfloat16* dst, cons
 }
 
 template <int BKV, bool DROP, int DH>
-__global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
+__global__ void __launch_bounds__(FA_THREADS, DH == 128 ? 1 : 2)
     attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const FaParams p) {
     static_assert(BKV == 64, "the pipelined schedule is laid out for 64-key tiles");
-    static_assert(DH == 64 || DH == 128, "head size 64 or 128");
+    static_assert(DH == 32 || DH == 64 || DH == 128, "head size 32, 64 or 128");
+    using G = HeadGeom<DH>;
     constexpr int KV_STAGES = 3;
-    constexpr int Q_BYTES = FA_BQ * DH * 2;   // 16 KB
-    constexpr int KV_BYTES = BKV * DH * 2;    // 8 KB
+    constexpr int Q_BYTES = FA_BQ * G::TILE_COLS * 2;   // 16 KB per atom
+    constexpr int KV_BYTES = BKV * G::TILE_COLS * 2;    // 8 KB per atom
     // S0 | S1 (64 columns each) | O (DH columns) | P0 | P1 (bf16 pairs, 32 columns each)
-    constexpr int TMEM_COLS = DH == 64 ? 256 : 512;
+    constexpr int TMEM_COLS = DH == 128 ? 512 : 256;
     constexpr uint32_t TM_O = 128, TM_P = 128 + DH;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -152,14 +163,14 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
     if (warp == 0) {
         if (lane == 0) {
             mbar_expect_tx(q_full, Q_BYTES);
-            tma_load_tile<DH>(sQ, &tmQ, h * DH, q0, b, FA_BQ, q_full);
+            tma_load_tile<DH>(sQ, &tmQ, G::col0(h), q0, b, FA_BQ, q_full);
             for (int j = 0; j < T; ++j) {
                 const int s = j % KV_STAGES;
                 const uint32_t ph = (uint32_t)(j / KV_STAGES) & 1u;
                 mbar_wait(&kv_empty[s], ph ^ 1u);
                 mbar_expect_tx(&kv_full[s], 2 * KV_BYTES);
-                tma_load_tile<DH>(sK + s * KV_BYTES, &tmK, h * DH, j * BKV, b, BKV, &kv_full[s]);
-                tma_load_tile<DH>(sV + s * KV_BYTES, &tmV, h * DH, j * BKV, b, BKV, &kv_full[s]);
+                tma_load_tile<DH>(sK + s * KV_BYTES, &tmK, G::col0(h), j * BKV, b, BKV, &kv_full[s]);
+                tma_load_tile<DH>(sV + s * KV_BYTES, &tmV, G::col0(h), j * BKV, b, BKV, &kv_full[s]);
             }
         }
         __syncwarp();
@@ -170,14 +181,14 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
             // lands in the TMEM buffer the softmax warps only read one tile later.
             const uint32_t idesc_s = make_idesc(BKV, false, false);
             const uint32_t idesc_o = make_idesc(DH, false, true);
-            const uint32_t q_addr = smem_u32(sQ);
+            const uint32_t q_addr = smem_u32(sQ) + G::sub(h);
             auto issue_s = [&](int j) {
                 const int s = j % KV_STAGES;
                 mbar_wait(&kv_full[s], (uint32_t)(j / KV_STAGES) & 1u);
                 tc_fence_after();
-                const uint32_t k_addr = smem_u32(sK + s * KV_BYTES);
+                const uint32_t k_addr = smem_u32(sK + s * KV_BYTES) + G::sub(h);
 #pragma unroll
-                for (int t = 0; t < DH / 16; ++t)
+                for (int t = 0; t < G::KS; ++t)
                     umma_bf16(tmem_base + (uint32_t)(j & 1) * 64, kmajor_desc(q_addr, FA_BQ, t), kmajor_desc(k_addr, BKV, t), idesc_s,
                               t > 0 ? 1u : 0u);
                 umma_commit(&s_full[j & 1]);
@@ -189,7 +200,7 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
                 mbar_wait(p_full, (uint32_t)j & 1u);
                 tc_fence_after();
                 const int s = j % KV_STAGES;
-                const uint32_t v_addr = smem_u32(sV + s * KV_BYTES);
+                const uint32_t v_addr = smem_u32(sV + s * KV_BYTES) + G::sub(h);
                 const uint32_t p_tmem = tmem_base + TM_P + (uint32_t)(j & 1) * 32;
 #pragma unroll
                 for (int t = 0; t < BKV / 16; ++t)  // P read from TMEM (no shared-memory A traffic); O accumulates in TMEM
@@ -359,13 +370,14 @@ struct FaBwdParams {
 
 // dQ: CTA = 128 query rows of one (batch, head); streams key tiles of 64.
 template <bool DROP, int DH>
-__global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
+__global__ void __launch_bounds__(FA_THREADS, DH == 128 ? 1 : 2)
     attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                           const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const FaBwdParams p) {
-    static_assert(DH == 64 || DH == 128, "head size 64 or 128");
+    static_assert(DH == 32 || DH == 64 || DH == 128, "head size 32, 64 or 128");
+    using G = HeadGeom<DH>;
     constexpr int BKV = 64;
-    constexpr int Q_BYTES = FA_BQ * DH * 2, KV_BYTES = BKV * DH * 2, KV_STAGES = 3;
-    constexpr int TMEM_COLS = DH == 64 ? 256 : 512;
+    constexpr int Q_BYTES = FA_BQ * G::TILE_COLS * 2, KV_BYTES = BKV * G::TILE_COLS * 2, KV_STAGES = 3;
+    constexpr int TMEM_COLS = DH == 128 ? 512 : 256;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* sQ = smem;
@@ -411,15 +423,15 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
     if (warp == 0) {
         if (lane == 0) {
             mbar_expect_tx(qdo_full, 2 * Q_BYTES);
-            tma_load_tile<DH>(sQ, &tmQ, h * DH, q0, b, FA_BQ, qdo_full);
-            tma_load_tile<DH>(sdO, &tmdO, h * DH, q0, b, FA_BQ, qdo_full);
+            tma_load_tile<DH>(sQ, &tmQ, G::col0(h), q0, b, FA_BQ, qdo_full);
+            tma_load_tile<DH>(sdO, &tmdO, G::col0(h), q0, b, FA_BQ, qdo_full);
             for (int j = 0; j < T; ++j) {
                 const int s = j % KV_STAGES;
                 const uint32_t ph = (uint32_t)(j / KV_STAGES) & 1u;
                 mbar_wait(&kv_empty[s], ph ^ 1u);
                 mbar_expect_tx(&kv_full[s], 2 * KV_BYTES);
-                tma_load_tile<DH>(sK + s * KV_BYTES, &tmK, h * DH, j * BKV, b, BKV, &kv_full[s]);
-                tma_load_tile<DH>(sV + s * KV_BYTES, &tmV, h * DH, j * BKV, b, BKV, &kv_full[s]);
+                tma_load_tile<DH>(sK + s * KV_BYTES, &tmK, G::col0(h), j * BKV, b, BKV, &kv_full[s]);
+                tma_load_tile<DH>(sV + s * KV_BYTES, &tmV, G::col0(h), j * BKV, b, BKV, &kv_full[s]);
             }
         }
         __syncwarp();
@@ -428,19 +440,19 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
             const uint32_t idesc_kk = make_idesc(BKV, false, false);  // S, dP: both operands K-major
             const uint32_t idesc_dq = make_idesc(DH, false, true);    // dQ: dS K-major, K tile MN-major
             mbar_wait(qdo_full, 0);
-            const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sdO);
+            const uint32_t q_addr = smem_u32(sQ) + G::sub(h), do_addr = smem_u32(sdO) + G::sub(h);
             // Software pipeline: S(j+1), dP(j+1) are issued as soon as the math warps have S(j), dP(j) in registers,
             // so the tensor core works on the next score tile while they turn the current one into dS(j).
             auto issue_sdp = [&](int j) {
                 const int s = j % KV_STAGES;
                 mbar_wait(&kv_full[s], (uint32_t)(j / KV_STAGES) & 1u);
                 tc_fence_after();
-                const uint32_t k_addr = smem_u32(sK + s * KV_BYTES), v_addr = smem_u32(sV + s * KV_BYTES);
+                const uint32_t k_addr = smem_u32(sK + s * KV_BYTES) + G::sub(h), v_addr = smem_u32(sV + s * KV_BYTES) + G::sub(h);
 #pragma unroll
-                for (int t = 0; t < DH / 16; ++t)
+                for (int t = 0; t < G::KS; ++t)
                     umma_bf16(tmem_s, kmajor_desc(q_addr, FA_BQ, t), kmajor_desc(k_addr, BKV, t), idesc_kk, t > 0 ? 1u : 0u);
 #pragma unroll
-                for (int t = 0; t < DH / 16; ++t)
+                for (int t = 0; t < G::KS; ++t)
                     umma_bf16(tmem_dp, kmajor_desc(do_addr, FA_BQ, t), kmajor_desc(v_addr, BKV, t), idesc_kk, t > 0 ? 1u : 0u);
                 umma_commit(sdp_full);
             };
@@ -454,7 +466,7 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
                 }
                 mbar_wait(ds_full, (uint32_t)j & 1u);
                 tc_fence_after();
-                const uint32_t k_addr = smem_u32(sK + s * KV_BYTES);
+                const uint32_t k_addr = smem_u32(sK + s * KV_BYTES) + G::sub(h);
                 const uint32_t ds_tmem = tmem_ds + (uint32_t)(j & 1) * 32;
 #pragma unroll
                 for (int t = 0; t < BKV / 16; ++t)  // A = dS from tensor memory
@@ -569,13 +581,14 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
 // transposed score tile S^T = K Q^T (thread = key row, column = query), so P^T and dS^T come out in
 // exactly the K-major layout the dV = P^T dO and dK = dS^T Q products read.
 template <bool DROP, int DH>
-__global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
+__global__ void __launch_bounds__(FA_THREADS, DH == 128 ? 1 : 2)
     attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmdO,
                            const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const FaBwdParams p) {
-    static_assert(DH == 64 || DH == 128, "head size 64 or 128");
+    static_assert(DH == 32 || DH == 64 || DH == 128, "head size 32, 64 or 128");
+    using G = HeadGeom<DH>;
     constexpr int BQ2 = 64, BK2 = 128;
-    constexpr int K_BYTES = BK2 * DH * 2, Q_BYTES = BQ2 * DH * 2;
-    constexpr int TMEM_COLS = DH == 64 ? 256 : 512;
+    constexpr int K_BYTES = BK2 * G::TILE_COLS * 2, Q_BYTES = BQ2 * G::TILE_COLS * 2;
+    constexpr int TMEM_COLS = DH == 128 ? 512 : 256;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* sK = smem;
@@ -619,15 +632,15 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
     if (warp == 0) {
         if (lane == 0) {
             mbar_expect_tx(kv_full, 2 * K_BYTES);
-            tma_load_tile<DH>(sK, &tmK, h * DH, k0, b, BK2, kv_full);
-            tma_load_tile<DH>(sV, &tmV, h * DH, k0, b, BK2, kv_full);
+            tma_load_tile<DH>(sK, &tmK, G::col0(h), k0, b, BK2, kv_full);
+            tma_load_tile<DH>(sV, &tmV, G::col0(h), k0, b, BK2, kv_full);
             for (int i = 0; i < T; ++i) {
                 const int s = i & 1;
                 const uint32_t ph = (uint32_t)(i >> 1) & 1u;
                 mbar_wait(&q_empty[s], ph ^ 1u);
                 mbar_expect_tx(&q_full[s], 2 * Q_BYTES);
-                tma_load_tile<DH>(sQ + s * Q_BYTES, &tmQ, h * DH, i * BQ2, b, BQ2, &q_full[s]);
-                tma_load_tile<DH>(sdO + s * Q_BYTES, &tmdO, h * DH, i * BQ2, b, BQ2, &q_full[s]);
+                tma_load_tile<DH>(sQ + s * Q_BYTES, &tmQ, G::col0(h), i * BQ2, b, BQ2, &q_full[s]);
+                tma_load_tile<DH>(sdO + s * Q_BYTES, &tmdO, G::col0(h), i * BQ2, b, BQ2, &q_full[s]);
             }
         }
         __syncwarp();
@@ -636,18 +649,18 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 64 ? 2 : 1)
             const uint32_t idesc_kk = make_idesc(BQ2, false, false);  // S^T, dP^T: K-major x K-major, N = 64 queries
             const uint32_t idesc_acc = make_idesc(DH, false, true);   // dV, dK: P^T / dS^T K-major, dO / Q tile MN-major
             mbar_wait(kv_full, 0);
-            const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV);
+            const uint32_t k_addr = smem_u32(sK) + G::sub(h), v_addr = smem_u32(sV) + G::sub(h);
             for (int i = 0; i < T; ++i) {
                 const int s = i & 1;
                 const uint32_t ph = (uint32_t)(i >> 1) & 1u;
                 mbar_wait(&q_full[s], ph);
                 tc_fence_after();
-                const uint32_t q_addr = smem_u32(sQ + s * Q_BYTES), do_addr = smem_u32(sdO + s * Q_BYTES);
+                const uint32_t q_addr = smem_u32(sQ + s * Q_BYTES) + G::sub(h), do_addr = smem_u32(sdO + s * Q_BYTES) + G::sub(h);
 #pragma unroll
-                for (int t = 0; t < DH / 16; ++t)
+                for (int t = 0; t < G::KS; ++t)
                     umma_bf16(tmem_st, kmajor_desc(k_addr, BK2, t), kmajor_desc(q_addr, BQ2, t), idesc_kk, t > 0 ? 1u : 0u);
 #pragma unroll
-                for (int t = 0; t < DH / 16; ++t)
+                for (int t = 0; t < G::KS; ++t)
                     umma_bf16(tmem_dpt, kmajor_desc(v_addr, BK2, t), kmajor_desc(do_addr, BQ2, t), idesc_kk, t > 0 ? 1u : 0u);
                 umma_commit(sdp_full);
                 mbar_wait(pds_full, (uint32_t)i & 1u);
@@ -781,13 +794,14 @@ static int make_tmap3(CUtensorMap* map, const void* base, int64_t cols, int64_t 
 
 bool attn_fwd_tc_supported(const pio_attn_desc* d) {
     static const bool disabled = getenv("PIO_DISABLE_TC_ATTN") != nullptr;  // debugging aid: force the fp32-arithmetic kernel
-    return !disabled && (d->dh == 64 || d->dh == 128) && d->n > 0 && d->m > 0 && d->batch > 0;
+    return !disabled && (d->dh == 32 || d->dh == 64 || d->dh == 128) && d->n > 0 && d->m > 0 && d->batch > 0;
 }
 
 template <int DH>
 static int launch_fwd(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const FaParams& p) {
     constexpr int BKV = 64;
-    const size_t smem = (size_t)FA_BQ * DH * 2 + 6 * (size_t)BKV * DH * 2 + 2 * BKV * 4 + 128 + 1024;
+    constexpr int TC = HeadGeom<DH>::TILE_COLS;
+    const size_t smem = (size_t)FA_BQ * TC * 2 + 6 * (size_t)BKV * TC * 2 + 2 * BKV * 4 + 128 + 1024;
     static bool configured = false;  // per head size
     if (!configured) {
         PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV, false, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -802,7 +816,8 @@ static int launch_fwd(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const C
 template <int DH>
 static int launch_bwd_dq(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const CUtensorMap& tdo, const CUtensorMap& tk,
                          const CUtensorMap& tv, const FaBwdParams& p) {
-    const size_t smem = 2 * (size_t)FA_BQ * DH * 2 + 6 * (size_t)64 * DH * 2 + 2 * 64 * 4 + 128 + 1024;
+    constexpr int TC = HeadGeom<DH>::TILE_COLS;
+    const size_t smem = 2 * (size_t)FA_BQ * TC * 2 + 6 * (size_t)64 * TC * 2 + 2 * 64 * 4 + 128 + 1024;
     static bool configured = false;
     if (!configured) {
         PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<false, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -817,7 +832,8 @@ static int launch_bwd_dq(dim3 grid, cudaStream_t st, const CUtensorMap& tq, cons
 template <int DH>
 static int launch_bwd_dkv(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const CUtensorMap& tdo, const CUtensorMap& tk,
                           const CUtensorMap& tv, const FaBwdParams& p) {
-    const size_t smem = 2 * (size_t)128 * DH * 2 + 4 * (size_t)64 * DH * 2 + 4 * 64 * 4 + 128 + 1024;
+    constexpr int TC = HeadGeom<DH>::TILE_COLS;
+    const size_t smem = 2 * (size_t)128 * TC * 2 + 4 * (size_t)64 * TC * 2 + 4 * 64 * 4 + 128 + 1024;
     static bool configured = false;
     if (!configured) {
         PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<false, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -851,7 +867,8 @@ int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st, con
     p.scale_log2e = d->scale * 1.44269504088896340736f;
     p.drop = drop ? *drop : DropCfg{0, 0, 1.f};
     dim3 grid((unsigned)cdiv(d->n, FA_BQ), (unsigned)d->heads, (unsigned)d->batch);
-    if (d->dh == 64) PIO_TRY((launch_fwd<64>(grid, st, tq, tk, tv, p)));
+    if (d->dh == 32) PIO_TRY((launch_fwd<32>(grid, st, tq, tk, tv, p)));
+    else if (d->dh == 64) PIO_TRY((launch_fwd<64>(grid, st, tq, tk, tv, p)));
     else PIO_TRY((launch_fwd<128>(grid, st, tq, tk, tv, p)));
     count_launch();
     return PIO_OK;
@@ -880,7 +897,8 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
         PIO_TRY(make_tmap3(&tk, d->k, cols, d->m, d->batch, d->k_rs, d->k_bs, 64));
         PIO_TRY(make_tmap3(&tv, d->v, cols, d->m, d->batch, d->v_rs, d->v_bs, 64));
         dim3 grid((unsigned)cdiv(d->n, FA_BQ), (unsigned)d->heads, (unsigned)d->batch);
-        if (d->dh == 64) PIO_TRY((launch_bwd_dq<64>(grid, st, tq, tdo, tk, tv, p)));
+        if (d->dh == 32) PIO_TRY((launch_bwd_dq<32>(grid, st, tq, tdo, tk, tv, p)));
+        else if (d->dh == 64) PIO_TRY((launch_bwd_dq<64>(grid, st, tq, tdo, tk, tv, p)));
         else PIO_TRY((launch_bwd_dq<128>(grid, st, tq, tdo, tk, tv, p)));
         count_launch();
     }
@@ -891,7 +909,8 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
         PIO_TRY(make_tmap3(&tk, d->k, cols, d->m, d->batch, d->k_rs, d->k_bs, 128));
         PIO_TRY(make_tmap3(&tv, d->v, cols, d->m, d->batch, d->v_rs, d->v_bs, 128));
         dim3 grid((unsigned)cdiv(d->m, 128), (unsigned)d->heads, (unsigned)d->batch);
-        if (d->dh == 64) PIO_TRY((launch_bwd_dkv<64>(grid, st, tq, tdo, tk, tv, p)));
+        if (d->dh == 32) PIO_TRY((launch_bwd_dkv<32>(grid, st, tq, tdo, tk, tv, p)));
+        else if (d->dh == 64) PIO_TRY((launch_bwd_dkv<64>(grid, st, tq, tdo, tk, tv, p)));
         else PIO_TRY((launch_bwd_dkv<128>(grid, st, tq, tdo, tk, tv, p)));
         count_launch();
     }

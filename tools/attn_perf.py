@@ -32,6 +32,8 @@ if which=="fwdonly":
     run(32,256,16384,8,reps=1,bwd=False); sys.exit(0)
 run(32,256,16384,8)
 run(32,256,256,4,dh=128)
+run(128,32,784,4,dh=32)
+run(128,32,32,4,dh=32)
 run(32,256,8192,8)
 run(8,256,65536,8)
 run(64,64,512,4)
