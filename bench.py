@@ -309,17 +309,38 @@ def other_config_throughput(mode):
             opt.zero_grad(set_to_none=True)
             loss.backward()
             opt.step()
+        def timed_ms(fn):
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                fn()
+            e1.record()
+            e1.synchronize()
+            return e0.elapsed_time(e1) / steps
         for _ in range(warm):
             step()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            step()
-        e1.record()
-        e1.synchronize()
-        ms = e0.elapsed_time(e1) / steps
-        return {"ms_per_step": round(ms, 3), "samples_per_s": round(batch / (ms * 1e-3), 1)}
+        ms = timed_ms(step)
+        out_ = {"ms_per_step": round(ms, 3), "samples_per_s": round(batch / (ms * 1e-3), 1), "mode": "eager"}
+        if mode == 1:  # the same step replayed from a CUDA graph (static inputs, own AdamW inside the graph)
+            try:
+                side = torch.cuda.Stream()
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    step()
+                torch.cuda.current_stream().wait_stream(side)
+                opt.zero_grad(set_to_none=True)
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    loss = perceiver.cross_entropy(model(*args), y)
+                    loss.backward()
+                    opt.step()
+                graph.replay()
+                gms = timed_ms(graph.replay)
+                out_.update({"graph_ms_per_step": round(gms, 3), "graph_samples_per_s": round(batch / (gms * 1e-3), 1)})
+            except Exception as ex:
+                out_["graph_error"] = str(ex)[:160]
+        return out_
 
     torch.manual_seed(0)
     enc = PerceiverEncoder(ImageInputAdapter((28, 28, 1), 32), (32, 128), 3, 4, 4, 3)

@@ -230,7 +230,7 @@ int pio_adamw_tick(float* hyper, pio_stream_t stream);
  * A query whose keys are all padded yields NaN, like the reference.
  * mode = PIO_MODE_BF16: q, k, v point at bf16 data (same element strides); the forward then runs the
  * tcgen05 flash kernel (TMA-staged K/V tiles, QK^T and PV on the tensor cores, accumulators in TMEM)
- * when dh == 64 and the fp32-arithmetic kernel otherwise; o, lse and the gradients stay fp32. */
+ * when dh is 32, 64 or 128 and the fp32-arithmetic kernel otherwise; o, lse and the gradients stay fp32. */
 typedef struct {
     const float* q;
     const float* k;
