@@ -253,7 +253,7 @@ typedef struct {
     float* delta;       /* scratch (batch,heads,n) */
 } pio_attn_bwd_desc;
 int pio_attn_bwd(const pio_attn_bwd_desc* d, int mode, pio_stream_t stream);
-/* The all-bf16 tensor-core backward used inside the PIO_MODE_BF16 operators (dh == 64 only, else
+/* The all-bf16 tensor-core backward used inside the PIO_MODE_BF16 operators (dh 32, 64 or 128, else
  * PIO_ERR_UNSUPPORTED): q, k, v of `fwd`, d_o (strides of o) and the outputs dq / dk / dv (strides of
  * q / k / v) are bf16; o and lse fp32.  Two kernels, both recomputing P from lse with QK^T, dO V^T and
  * the three gradient products on tcgen05: one per 128 query rows (dq, delta), one per 128 key rows
