@@ -153,11 +153,25 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
     return cdf + x * pdf;
 }
 
-// GELU and its derivative from one erf evaluation
+// GELU and its derivative for the tensor-core epilogues, where four warps per CTA do all the element-wise math:
+// erf by Abramowitz-Stegun 7.1.26 (|error| < 1.5e-7, i.e. at fp32 rounding level for the cdf), whose exp(-u^2) with
+// u = x / sqrt(2) is the very exp(-x^2 / 2) the derivative's density term needs — one ex2 and one reciprocal per
+// element instead of erff + expf.
 __device__ __forceinline__ void gelu_erf_both(float x, float& g, float& dg) {
-    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+    const float a = fabsf(x) * 0.70710678118654752440f;
+    float t;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, a, 1.0f)));
+    float poly = fmaf(t, 1.061405429f, -1.453152027f);
+    poly = fmaf(t, poly, 1.421413741f);
+    poly = fmaf(t, poly, -0.284496736f);
+    poly = fmaf(t, poly, 0.254829592f);
+    poly *= t;
+    float e;  // exp(-x^2 / 2)
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-a * a * 1.44269504088896340736f));
+    const float erf_abs = fmaf(-poly, e, 1.0f);
+    const float cdf = 0.5f * (1.0f + copysignf(erf_abs, x));
     g = x * cdf;
-    dg = cdf + x * 0.39894228040143267794f * __expf(-0.5f * x * x);
+    dg = fmaf(x * 0.39894228040143267794f, e, cdf);
 }
 
 }  // namespace pio
