@@ -23,7 +23,7 @@ namespace pio {
 
 constexpr int TC_BK = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int TC_STAGES = 3;  // 3 x 32 KB + barriers: two CTAs per SM, so one tile's epilogue overlaps another's mainloop
-constexpr int TC_THREADS = 192;
+constexpr int TC_THREADS = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue (two per TMEM lane quadrant, half the columns each)
 
 struct TcParams {
     int M, N, K;
@@ -327,14 +327,16 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
         // tcgen05.ld hands each thread one accumulator ROW; the rows are staged in shared memory
         // (aliasing the now idle operand ring) and read back with lane = 4 consecutive columns.
         const int q = warp & 3;
-        constexpr int PITCH = BN + 4;
+        const int half = (warp - 2) >> 2;  // which half of the tile's columns this warp finishes
+        constexpr int HN = BN / 2;
+        constexpr int PITCH = HN + 4;
         mbar_wait(tmem_full, 0);
         tc_fence_after();
-        float* stile = reinterpret_cast<float*>(smem) + q * (32 * PITCH);
+        float* stile = reinterpret_cast<float*>(smem) + (half * 4 + q) * (32 * PITCH);
 #pragma unroll
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = 0; c0 < HN; c0 += 32) {
             uint32_t r[32];
-            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * HN + c0), r);
             tmem_ld_wait();
 #pragma unroll
             for (int j = 0; j < 32; j += 4)
@@ -344,16 +346,17 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
         __syncwarp();
         const int64_t gm0 = (int64_t)m0 + q * 32;
         const int rows_here = (int)min((int64_t)32, (int64_t)m_eff - gm0);  // may be <= 0
+        const int nh = n0 + half * HN;
         switch (p.epi_kind) {
-            case EPI_F32: epilogue_rows<BN, EPI_F32>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
-            case EPI_F32_RES: epilogue_rows<BN, EPI_F32_RES>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
-            case EPI_F32_ACC: epilogue_rows<BN, EPI_F32_ACC>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
-            case EPI_B16: epilogue_rows<BN, EPI_B16>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
-            case EPI_B16_GELU: epilogue_rows<BN, EPI_B16_GELU>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
-            case EPI_B16_DGELU: epilogue_rows<BN, EPI_B16_DGELU>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
-            case EPI_PARTIAL: epilogue_rows<BN, EPI_PARTIAL>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
-            case EPI_F32_ATOMIC: epilogue_rows<BN, EPI_F32_ATOMIC>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
-            default: epilogue_rows<BN, EPI_GENERIC>(p, stile, lane, n0, gm0, rows_here, blockIdx.z); break;
+            case EPI_F32: epilogue_rows<HN, EPI_F32>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
+            case EPI_F32_RES: epilogue_rows<HN, EPI_F32_RES>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
+            case EPI_F32_ACC: epilogue_rows<HN, EPI_F32_ACC>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
+            case EPI_B16: epilogue_rows<HN, EPI_B16>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
+            case EPI_B16_GELU: epilogue_rows<HN, EPI_B16_GELU>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
+            case EPI_B16_DGELU: epilogue_rows<HN, EPI_B16_DGELU>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
+            case EPI_PARTIAL: epilogue_rows<HN, EPI_PARTIAL>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
+            case EPI_F32_ATOMIC: epilogue_rows<HN, EPI_F32_ATOMIC>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
+            default: epilogue_rows<HN, EPI_GENERIC>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
         }
         tc_fence_before();
     }
