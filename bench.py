@@ -371,7 +371,10 @@ def gpu_arm(args):
     dev = torch.device("cuda", local_rank)
     distributed = world > 1
     if distributed:
+        import faulthandler
         import torch.distributed as dist
+        # a rank stuck in a collective would hold its GPU until the launcher's limit: every rank ends itself instead
+        faulthandler.dump_traceback_later(int(os.environ.get("PIO_BENCH_WATCHDOG_S", "600")), exit=True)
         dist.init_process_group("nccl", device_id=dev)
     perceiver.set_compute_mode(args.mode)
     mode = perceiver.get_compute_mode()
