@@ -222,6 +222,18 @@ int pio_adamw_step(const pio_adamw_tensor* tensors, const pio_adamw_chunk* chunk
                    pio_stream_t stream);
 int pio_adamw_tick(float* hyper, pio_stream_t stream);
 
+/* Gather a set of fp32 tensors into one flat buffer (to_flat = 1) or scatter the flat buffer back into them,
+ * multiplied by `scale` (to_flat = 0), in one launch — the flatten / unflatten around the single gradient
+ * all-reduce of data-parallel training (reference: Lightning DDP, scripts/trainer.yaml:47).  `tensors[i]` =
+ * {base pointer, offset of the tensor inside the flat buffer (a multiple of 4 elements)}; `chunks` as in
+ * pio_adamw_step.  Both tables live in DEVICE memory. */
+typedef struct {
+    float* tensor;
+    int64_t flat_offset;
+} pio_flat_tensor;
+int pio_flat_copy_f32(float* flat, const pio_flat_tensor* tensors, const pio_adamw_chunk* chunks, int n_chunks, int to_flat,
+                      float scale, pio_stream_t stream);
+
 /* Attention core of nn.MultiheadAttention as called at model.py:74 (dropout 0):
  * S = (q dh^-1/2) k^T, padded keys -> -inf, P = softmax(S), O = P v.  Flash-style: P is never
  * stored; lse (batch,heads,n) = logsumexp of the scaled scores, saved for the backward, which

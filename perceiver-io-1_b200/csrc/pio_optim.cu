@@ -105,6 +105,30 @@ __global__ void adamw_tick_kernel(float* hyper) {
     hyper[5] += 1.0f;
 }
 
+// flat <-> tensors, one CTA per chunk (the flatten / unflatten around the gradient all-reduce)
+__global__ void __launch_bounds__(256) flat_copy_kernel(float* __restrict__ flat, const pio_flat_tensor* __restrict__ tensors,
+                                                        const pio_adamw_chunk* __restrict__ chunks, int to_flat, float scale) {
+    pdl_trigger();
+    pdl_wait();
+    const pio_adamw_chunk c = chunks[blockIdx.x];
+    const pio_flat_tensor t = tensors[c.tensor];
+    float* __restrict__ a = t.tensor + c.offset;
+    float* __restrict__ f = flat + t.flat_offset + c.offset;
+    const bool vec = ((c.offset & 3) == 0) && ((t.flat_offset & 3) == 0) && ((((uintptr_t)t.tensor | (uintptr_t)flat) & 15) == 0);
+    const int n4 = vec ? (c.count >> 2) : 0;
+    if (to_flat) {
+        for (int i = threadIdx.x; i < n4; i += blockDim.x) reinterpret_cast<float4*>(f)[i] = reinterpret_cast<const float4*>(a)[i];
+        for (int i = 4 * n4 + threadIdx.x; i < c.count; i += blockDim.x) f[i] = a[i];
+    } else {
+        for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+            float4 v = reinterpret_cast<const float4*>(f)[i];
+            v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
+            reinterpret_cast<float4*>(a)[i] = v;
+        }
+        for (int i = 4 * n4 + threadIdx.x; i < c.count; i += blockDim.x) a[i] = f[i] * scale;
+    }
+}
+
 }  // namespace pio
 
 using namespace pio;
@@ -116,6 +140,16 @@ int pio_adamw_step(const pio_adamw_tensor* tensors, const pio_adamw_chunk* chunk
     PIO_CHECK_ARG(n_chunks >= 0 && (n_chunks == 0 || (chunks && tensors)) && hyper, "pio_adamw_step: bad arguments");
     if (n_chunks == 0) return PIO_OK;
     PIO_CUDA(launch_pdl(adamw_kernel, dim3((unsigned)n_chunks), dim3(256), 0, (cudaStream_t)stream, tensors, chunks, hyper));
+    count_launch();
+    return PIO_OK;
+}
+
+int pio_flat_copy_f32(float* flat, const pio_flat_tensor* tensors, const pio_adamw_chunk* chunks, int n_chunks, int to_flat,
+                      float scale, pio_stream_t stream) {
+    PIO_CHECK_ARG(n_chunks >= 0 && (n_chunks == 0 || (flat && tensors && chunks)), "pio_flat_copy_f32: bad arguments");
+    if (n_chunks == 0) return PIO_OK;
+    PIO_CUDA(launch_pdl(flat_copy_kernel, dim3((unsigned)n_chunks), dim3(256), 0, (cudaStream_t)stream, flat, tensors, chunks, to_flat,
+                        scale));
     count_launch();
     return PIO_OK;
 }

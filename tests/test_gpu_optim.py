@@ -128,3 +128,35 @@ def test_step_inside_a_cuda_graph_advances_its_own_counter():
     for a, b in zip(pa, pb):
         torch.testing.assert_close(b, a, rtol=2e-5, atol=1e-6)
     assert float(ob.state[pb[0]]["step"].item()) == 5.0
+
+
+def test_flat_gather_and_scatter_around_the_gradient_all_reduce():
+    """pio_flat_copy_f32 through perceiver.distributed._native_plan: gather == torch.cat, scatter(scale) == views * scale."""
+    from perceiver import _native as N
+    from perceiver import distributed as D
+    params = _params(9)
+    g = torch.Generator().manual_seed(10)
+    for p in params:
+        p.grad = torch.randn(p.shape, generator=g).to(DEV)
+    plan = D._native_plan(params)
+    assert plan is not None
+    L, st = plan["lib"], plan["stream"]
+    N.check(L.pio_flat_copy_f32(plan["flat"].data_ptr(), plan["table"].data_ptr(), plan["chunks"].data_ptr(), plan["n_chunks"], 1, 1.0, st), "gather")
+    torch.cuda.synchronize()
+    for p, off in zip(params, plan["offs"]):
+        assert torch.equal(plan["flat"][off:off + p.numel()], p.grad.reshape(-1))
+    want = [p.grad.clone() * 0.25 for p in params]
+    for p in params:
+        p.grad.fill_(float("nan"))
+    N.check(L.pio_flat_copy_f32(plan["flat"].data_ptr(), plan["table"].data_ptr(), plan["chunks"].data_ptr(), plan["n_chunks"], 0, 0.25, st), "scatter")
+    torch.cuda.synchronize()
+    for p, w in zip(params, want):
+        assert torch.equal(p.grad, w)
+    # new gradient buffers (eager training): the pointer table follows
+    for p in params:
+        p.grad = torch.ones_like(p)
+    plan2 = D._native_plan(params)
+    assert plan2 is plan
+    N.check(L.pio_flat_copy_f32(plan["flat"].data_ptr(), plan["table"].data_ptr(), plan["chunks"].data_ptr(), plan["n_chunks"], 1, 1.0, st), "gather")
+    torch.cuda.synchronize()
+    assert all(bool((plan["flat"][off:off + p.numel()] == 1).all()) for p, off in zip(params, plan["offs"]))
