@@ -155,7 +155,11 @@ __global__ void __launch_bounds__(256) text_embed_bwd_emb_kernel(const int64_t* 
         const float* g = dout + t * c;
         int slot = -1;
         if (slots > 0) {
-            const int cand = (int)(((uint64_t)id * 0x9E3779B97F4A7C15ull) >> 40) % slots;
+            // the lowest ids are the tokenizer's special tokens ([PAD], [UNK], [MASK], ...: reference tokenizer.py puts
+            // them first) and by far the most frequent: they get slots of their own, everything else shares the rest
+            const int reserved = slots >= 16 ? 8 : 0;
+            const int cand = (id < reserved) ? (int)id
+                                             : reserved + (int)((((uint64_t)id * 0x9E3779B97F4A7C15ull) >> 40) % (uint64_t)(slots - reserved));
             long long old = 0;
             if (lane == 0) old = atomicCAS((unsigned long long*)&s_tag[cand], (unsigned long long)-1ll, (unsigned long long)id);
             old = __shfl_sync(0xffffffffu, old, 0);
