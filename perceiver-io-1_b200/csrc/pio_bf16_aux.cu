@@ -34,12 +34,76 @@ __global__ void layernorm_fwd_bf16_kernel(const float* __restrict__ x, const flo
     }
 }
 
+// The same for rows of NV * 128 channels with a dense bf16 output (ldy == c): the row lives in registers
+// (one float4 per lane per 128 channels), is read once and written as 8-byte bf16 quads.
+template <int NV>
+__global__ void __launch_bounds__(256) layernorm_fwd_bf16_vec_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                                     const float* __restrict__ b, __nv_bfloat16* __restrict__ y,
+                                                                     float* __restrict__ stats, int64_t rows, float eps) {
+    pdl_trigger();
+    pdl_wait();
+    constexpr int C = NV * 128;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    float4 wv[NV], bv[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        wv[i] = __ldg(reinterpret_cast<const float4*>(w) + i * 32 + lane);
+        bv[i] = __ldg(reinterpret_cast<const float4*>(b) + i * 32 + lane);
+    }
+    for (int64_t r = warp; r < rows; r += nwarps) {
+        const float4* xr = reinterpret_cast<const float4*>(x + r * C);
+        float4 v[NV];
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            v[i] = xr[i * 32 + lane];
+            s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+        }
+        const float mean = warp_sum(s) * (1.0f / C);
+        float q = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            v[i].x -= mean; v[i].y -= mean; v[i].z -= mean; v[i].w -= mean;
+            q += (v[i].x * v[i].x + v[i].y * v[i].y) + (v[i].z * v[i].z + v[i].w * v[i].w);
+        }
+        const float rstd = rsqrtf(warp_sum(q) * (1.0f / C) + eps);
+        uint2* yr = reinterpret_cast<uint2*>(y + r * C);
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(v[i].x * rstd * wv[i].x + bv[i].x, v[i].y * rstd * wv[i].y + bv[i].y);
+            __nv_bfloat162 hi = __floats2bfloat162_rn(v[i].z * rstd * wv[i].z + bv[i].z, v[i].w * rstd * wv[i].w + bv[i].w);
+            uint2 o;
+            o.x = *reinterpret_cast<uint32_t*>(&lo);
+            o.y = *reinterpret_cast<uint32_t*>(&hi);
+            yr[i * 32 + lane] = o;
+        }
+        if (lane == 0 && stats != nullptr) {
+            stats[2 * r] = mean;
+            stats[2 * r + 1] = rstd;
+        }
+    }
+}
+
 int layernorm_fwd_bf16(const float* x, const float* w, const float* b, __nv_bfloat16* y, int64_t ldy, float* stats,
                        int64_t rows, int c, float eps, cudaStream_t st) {
     PIO_CHECK_ARG(x && w && b && y && c > 0 && ldy >= c, "layernorm_fwd_bf16: bad arguments");
     if (rows == 0) return PIO_OK;
     const int threads = 256;
     const int blocks = (int)std::min<int64_t>(cdiv(rows, threads / 32), (int64_t)num_sms() * 16);
+    const bool vec_ok = ldy == c && (c % 128) == 0 && c <= 512 &&
+                        ((((uintptr_t)x | (uintptr_t)w | (uintptr_t)b) & 15) == 0) && ((((uintptr_t)y) & 7) == 0);
+    if (vec_ok) {
+        switch (c / 128) {
+            case 1: PIO_CUDA(launch_pdl(layernorm_fwd_bf16_vec_kernel<1>, dim3(blocks), dim3(threads), 0, st, x, w, b, y, stats, rows, eps)); break;
+            case 2: PIO_CUDA(launch_pdl(layernorm_fwd_bf16_vec_kernel<2>, dim3(blocks), dim3(threads), 0, st, x, w, b, y, stats, rows, eps)); break;
+            case 3: PIO_CUDA(launch_pdl(layernorm_fwd_bf16_vec_kernel<3>, dim3(blocks), dim3(threads), 0, st, x, w, b, y, stats, rows, eps)); break;
+            default: PIO_CUDA(launch_pdl(layernorm_fwd_bf16_vec_kernel<4>, dim3(blocks), dim3(threads), 0, st, x, w, b, y, stats, rows, eps)); break;
+        }
+        count_launch();
+        return PIO_OK;
+    }
     PIO_CUDA(launch_pdl(layernorm_fwd_bf16_kernel, dim3(blocks), dim3(threads), 0, st, x, w, b, y, ldy, stats, rows, c, eps));
     count_launch();
     return PIO_OK;
