@@ -386,6 +386,79 @@ __global__ void __launch_bounds__(NCH <= 8 ? 512 : 256, NCH <= 16 ? 2 : 1) layer
     }
 }
 
+// The same for rows of NV * 128 channels: one float4 per lane per 128 channels (three 16-byte loads per lane for
+// dy, x and the residual gradient instead of twelve 4-byte ones at C = 256), same block-level reduction.
+template <int NV>
+__global__ void __launch_bounds__(512, 2) layernorm_bwd_vec_kernel(
+    const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ stats,
+    const float* __restrict__ w, const float* __restrict__ dres, float* __restrict__ dx,
+    float* __restrict__ partial, int64_t rows, float* __restrict__ atomic_dw, float* __restrict__ atomic_db) {
+    extern __shared__ float s_acc[];  // [warps][2][c]
+    pdl_trigger();
+    pdl_wait();
+    constexpr int C = NV * 128;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    float4 gw[NV], gb[NV], wv[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        gw[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        gb[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        wv[i] = __ldg(reinterpret_cast<const float4*>(w) + i * 32 + lane);
+    }
+    for (int64_t r = (int64_t)blockIdx.x * nw + wid; r < rows; r += (int64_t)gridDim.x * nw) {
+        const float4* dyr = reinterpret_cast<const float4*>(dy + r * C);
+        const float4* xr = reinterpret_cast<const float4*>(x + r * C);
+        float4 d[NV], xh[NV], rs[NV];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            d[i] = dyr[i * 32 + lane];
+            xh[i] = xr[i * 32 + lane];
+            rs[i] = dres != nullptr ? reinterpret_cast<const float4*>(dres + r * C)[i * 32 + lane] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        const float mean = stats[2 * r], rstd = stats[2 * r + 1];
+        float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+#define PIO_LNV(f)                          \
+    xh[i].f = (xh[i].f - mean) * rstd;      \
+    gw[i].f += d[i].f * xh[i].f;            \
+    gb[i].f += d[i].f;                      \
+    d[i].f *= wv[i].f;                      \
+    c1 += d[i].f;                           \
+    c2 += d[i].f * xh[i].f;
+            PIO_LNV(x) PIO_LNV(y) PIO_LNV(z) PIO_LNV(w)
+#undef PIO_LNV
+        }
+        c1 = warp_sum(c1) * (1.0f / C);
+        c2 = warp_sum(c2) * (1.0f / C);
+        if (dx != nullptr) {
+            float4* dxr = reinterpret_cast<float4*>(dx + r * C);
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                float4 o;
+                o.x = rstd * (d[i].x - c1 - xh[i].x * c2) + rs[i].x;
+                o.y = rstd * (d[i].y - c1 - xh[i].y * c2) + rs[i].y;
+                o.z = rstd * (d[i].z - c1 - xh[i].z * c2) + rs[i].z;
+                o.w = rstd * (d[i].w - c1 - xh[i].w * c2) + rs[i].w;
+                dxr[i * 32 + lane] = o;
+            }
+        }
+    }
+    float* mine = s_acc + (size_t)wid * 2 * C;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        reinterpret_cast<float4*>(mine)[i * 32 + lane] = gw[i];
+        reinterpret_cast<float4*>(mine + C)[i * 32 + lane] = gb[i];
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < 2 * C; j += blockDim.x) {
+        float acc = 0.f;
+        for (int w2 = 0; w2 < nw; ++w2) acc += s_acc[(size_t)w2 * 2 * C + j];
+        if (atomic_dw != nullptr) atomicAdd(j < C ? atomic_dw + j : atomic_db + (j - C), acc);
+        else partial[(size_t)blockIdx.x * 2 * C + j] = acc;
+    }
+}
+
 // out1[i] (+)= sum_s part[s*stride + i], i < n1 ; out2[i] (+)= sum_s part[s*stride + n1 + i], i < n2
 __global__ void reduce_partials_kernel(const float* __restrict__ part, int splits, int64_t stride,
                                        float* __restrict__ out1, int64_t n1, float* __restrict__ out2,
@@ -739,6 +812,17 @@ int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const
     cudaStream_t st = (cudaStream_t)stream;
     const int warps = ln_bwd_warps(c);
     const size_t smem = (size_t)warps * 2 * c * sizeof(float);
+    const bool vec_ok = (c == 128 || c == 256) &&
+                        ((((uintptr_t)dy | (uintptr_t)x | (uintptr_t)w | (uintptr_t)dres | (uintptr_t)dx) & 15) == 0);
+    if (vec_ok) {  // warps == 16 for these widths; smem = 16 * 2 * c * 4 <= 32 KB
+        if (c == 128)
+            PIO_CUDA(launch_pdl(layernorm_bwd_vec_kernel<1>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, adw, adb));
+        else
+            PIO_CUDA(launch_pdl(layernorm_bwd_vec_kernel<2>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, adw, adb));
+        PIO_LAUNCH_CHECK();
+        if (atomic) return PIO_OK;
+        return reduce_partials(partial, blocks, (int64_t)2 * c, dw, c, db, c, accumulate, st);
+    }
 #define PIO_LN_BWD(NCH)                                                                                         \
     do {                                                                                                        \
         if (smem > 48 * 1024)                                                                                   \
