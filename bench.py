@@ -375,8 +375,10 @@ def gpu_arm(args):
         import torch.distributed as dist
         # a rank stuck in a collective would hold its GPU until the launcher's limit: every rank ends itself instead
         faulthandler.dump_traceback_later(int(os.environ.get("PIO_BENCH_WATCHDOG_S", "600")), exit=True)
-        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
+        # keep stdout to the one JSON line: NCCL prints its version banner there at NCCL_DEBUG=VERSION, which this image
+        # sets (environment or nccl.conf; a variable present in the environment wins over the file)
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     perceiver.set_compute_mode(args.mode)
     mode = perceiver.get_compute_mode()
