@@ -375,10 +375,12 @@ def gpu_arm(args):
         import torch.distributed as dist
         # a rank stuck in a collective would hold its GPU until the launcher's limit: every rank ends itself instead
         faulthandler.dump_traceback_later(int(os.environ.get("PIO_BENCH_WATCHDOG_S", "600")), exit=True)
-        # keep stdout to the one JSON line: NCCL prints its version banner there at NCCL_DEBUG=VERSION, which this image
-        # sets (environment or nccl.conf; a variable present in the environment wins over the file)
+        # keep stdout to the one JSON line: NCCL writes its version banner (debug level VERSION, which sits BELOW
+        # WARN) to stdout unless told where else to log
+        # (and NCCL honours NCCL_DEBUG_FILE only above level VERSION)
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     perceiver.set_compute_mode(args.mode)
     mode = perceiver.get_compute_mode()
