@@ -513,6 +513,34 @@ int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* a
     BlockLayout L(batch, n, ch, heads);
     const int64_t rows = (int64_t)batch * n;
     const float* cur = x;
+    if (latent_fused_supported(n, ch, heads, c.drop_p)) {
+        // one persistent kernel per (up to 8) layers: pio_latent_tc.cu
+        bool packed = true;
+        for (int s = 0; s < layers; ++s) packed = packed && check_packed_self(&attn[s], ch, "pio_latent_block_fwd") == PIO_OK;
+        if (packed) {
+            for (int s0 = 0; s0 < layers; s0 += PIO_LATENT_FUSED_MAX_LAYERS) {
+                const int cnt = std::min(PIO_LATENT_FUSED_MAX_LAYERS, layers - s0);
+                LatentFusedLayer fl[PIO_LATENT_FUSED_MAX_LAYERS];
+                for (int i = 0; i < cnt; ++i) {
+                    const int s = s0 + i;
+                    char* slab = (char*)saved + (size_t)s * L.per_layer;
+                    SaSaved sa(slab + L.sa, batch, n, ch, heads);
+                    MlpSaved ms(slab + L.mlp, rows, ch);
+                    LatentFusedLayer& f = fl[i];
+                    f.wqkv = attn[s].wq; f.wo = attn[s].wo; f.w1 = mlp[s].w1; f.w2 = mlp[s].w2;
+                    f.ln1_w = attn[s].ln_w; f.ln1_b = attn[s].ln_b; f.bqkv = attn[s].bq; f.bo = attn[s].bo;
+                    f.ln2_w = mlp[s].ln_w; f.ln2_b = mlp[s].ln_b; f.b1 = mlp[s].b1; f.b2 = mlp[s].b2;
+                    f.sa_stats = sa.stats; f.sa_h0 = sa.h0; f.qkv = sa.qkv; f.o32 = sa.o; f.o16 = sa.o16; f.lse = sa.lse;
+                    f.xmid = (float*)(slab + L.xmid);
+                    f.mlp_stats = ms.stats; f.mlp_h0 = ms.h0; f.mlp_h1 = ms.h1; f.mlp_g = ms.g;
+                    f.xout = (s == layers - 1) ? y : (float*)(slab + L.xnext);
+                }
+                PIO_TRY(latent_block_fwd_fused(cur, fl, cnt, batch, n, c.st));
+                cur = fl[cnt - 1].xout;
+            }
+            return PIO_OK;
+        }
+    }
     for (int s = 0; s < layers; ++s) {
         char* slab = (char*)saved + (size_t)s * L.per_layer;
         float* xmid = (float*)(slab + L.xmid);

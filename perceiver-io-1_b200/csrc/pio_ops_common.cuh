@@ -81,6 +81,21 @@ struct Carver {
 
 static inline int64_t pad8(int64_t x) { return (x + 7) / 8 * 8; }
 
+// Fused latent-block forward (pio_latent_tc.cu): one launch for up to PIO_LATENT_FUSED_MAX_LAYERS layers of a
+// self-attention block.  Per layer: bf16 weight shadows, fp32 LayerNorm parameters / biases, and where each piece
+// of saved-for-backward state goes (the layout of the unfused bf16 operators, so their backward runs on it).
+#define PIO_LATENT_FUSED_MAX_LAYERS 8
+struct LatentFusedLayer {
+    const void *wqkv, *wo, *w1, *w2;                                    // bf16, row pitch C
+    const float *ln1_w, *ln1_b, *bqkv, *bo, *ln2_w, *ln2_b, *b1, *b2;  // fp32
+    float* sa_stats; void* sa_h0; void* qkv; float* o32; void* o16; float* lse;
+    float* xmid;
+    float* mlp_stats; void* mlp_h0; void* mlp_h1; void* mlp_g;
+    float* xout;
+};
+bool latent_fused_supported(int n, int ch, int heads, float drop_p);
+int latent_block_fwd_fused(const float* x, const LatentFusedLayer* layers, int nlayers, int batch, int n, cudaStream_t st);
+
 // PIO_MODE_BF16 pipelines (pio_ops_bf16.cu)
 namespace bf {
 size_t mlp_saved_bytes(int64_t rows, int ch);

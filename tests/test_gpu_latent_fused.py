@@ -1,0 +1,87 @@
+"""The persistent fused latent-block kernel (pio_latent_tc.cu: one launch per self_attention_block,
+reference model.py:36-44) against (a) the unfused bf16 operators it replaces and (b) the fp32 oracle.
+The fused forward writes the same saved-for-backward state as the unfused one, so gradients through it
+check every saved tensor."""
+import os
+
+import pytest
+import torch
+
+from gpu_util import BF16_TOL, assert_rel, rel_err
+from oracle import perceiver_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+@pytest.fixture(autouse=True)
+def bf16_mode():
+    import perceiver
+    perceiver.set_compute_mode("bf16")
+    os.environ.pop("PIO_NO_FUSED_LATENT", None)
+    yield
+    os.environ.pop("PIO_NO_FUSED_LATENT", None)
+    perceiver.set_compute_mode("fp32")
+
+
+def _run(block, x, dy):
+    block.zero_grad(set_to_none=True)
+    xin = x.clone().requires_grad_(True)
+    y = block(xin)
+    y.backward(dy)
+    torch.cuda.synchronize()
+    return y.detach(), xin.grad.detach(), {k: p.grad.detach().clone() for k, p in block.named_parameters()}
+
+
+@pytest.mark.parametrize("batch,n,layers", [(2, 64, 1), (4, 64, 2), (3, 64, 6), (5, 32, 3), (3, 128, 2), (2, 64, 9), (64, 64, 6)])
+def test_fused_block_matches_unfused_operators(batch, n, layers):
+    from perceiver import _native as N
+    from perceiver.model import self_attention_block
+    torch.manual_seed(batch * 100 + n + layers)
+    block = self_attention_block(layers, 256, 4, 0.0).to(DEV)
+    with torch.no_grad():  # LayerNorm affine terms and biases away from their 1 / 0 initial values
+        for k, p in block.named_parameters():
+            if p.dim() == 1:
+                p.add_(torch.randn_like(p) * 0.1)
+    x = torch.randn(batch, n, 256, device=DEV)
+    dy = torch.randn(batch, n, 256, device=DEV)
+    c0 = N.lib().pio_launch_count()
+    y_f, dx_f, g_f = _run(block, x, dy)
+    fused_launches = N.lib().pio_launch_count() - c0
+    os.environ["PIO_NO_FUSED_LATENT"] = "1"
+    c0 = N.lib().pio_launch_count()
+    y_u, dx_u, g_u = _run(block, x, dy)
+    unfused_launches = N.lib().pio_launch_count() - c0
+    os.environ.pop("PIO_NO_FUSED_LATENT")
+    assert fused_launches < unfused_launches - 5 * layers, (fused_launches, unfused_launches)  # the fused path really ran
+    assert_rel(y_f, y_u, 4e-3, "y (fused vs unfused)")
+    assert_rel(dx_f, dx_u, 1e-2, "dx (fused vs unfused)")
+    for k in g_u:
+        assert_rel(g_f[k], g_u[k], 1.5e-2, f"grad {k} (fused vs unfused)")
+
+
+@pytest.mark.parametrize("batch,n,layers", [(4, 64, 3), (6, 32, 2)])
+def test_fused_block_matches_oracle(batch, n, layers):
+    from perceiver.model import self_attention_block
+    torch.manual_seed(3)
+    block = self_attention_block(layers, 256, 4, 0.0)
+    with torch.no_grad():
+        for k, p in block.named_parameters():
+            if p.dim() == 1:
+                p.add_(torch.randn_like(p) * 0.1)
+    sd = {k: v.detach().clone().requires_grad_(True) for k, v in block.state_dict().items()}
+    x = torch.randn(batch, n, 256)
+    xr = x.clone().requires_grad_(True)
+    ref = xr
+    for s in range(layers):
+        ref = O.self_attention_residual(sd, f"{s}.0.", ref, 4)
+        ref = O.mlp_residual(sd, f"{s}.1.", ref)
+    dy = torch.randn_like(ref)
+    ref.backward(dy)
+    block = block.to(DEV)
+    y, dx, g = _run(block, x.to(DEV), dy.to(DEV))
+    assert_rel(y, ref, BF16_TOL, "y")
+    assert_rel(dx, xr.grad, 2e-2, "dx")
+    num = sum(((g[k].cpu().double() - sd[k].grad.double()) ** 2).sum().item() for k in g)
+    den = sum((sd[k].grad.double() ** 2).sum().item() for k in g)
+    assert (num / den) ** 0.5 < BF16_TOL, (num / den) ** 0.5
