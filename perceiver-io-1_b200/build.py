@@ -28,7 +28,13 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, extra_flags=(), lib=None, obj_dir=None):
+    """extra_flags / lib / obj_dir: instrumented variants (e.g. -DPIO_LB_TRACE -> libpio_b200_trace.so for tools/latent_trace.py)"""
+    global OBJ, LIB
+    if lib is not None:
+        LIB = lib
+    if obj_dir is not None:
+        OBJ = obj_dir
     os.makedirs(OBJ, exist_ok=True)
     srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
     hdrs = glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(INCLUDE, "*.h"))
@@ -40,7 +46,7 @@ def build(force=False, verbose=False):
 
     def compile_one(so):
         s, o = so
-        cmd = [NVCC] + FLAGS + ["-c", s, "-o", o]
+        cmd = [NVCC] + FLAGS + list(extra_flags) + ["-c", s, "-o", o]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)
@@ -63,4 +69,8 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--trace" in sys.argv:
+        print(build(force=True, extra_flags=["-DPIO_LB_TRACE"], lib=os.path.join(HERE, "libpio_b200_trace.so"),
+                    obj_dir=os.path.join(HERE, "build_trace")))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -356,6 +356,7 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 128 ? 1 : 2)
 struct FaBwdParams {
     const uint8_t* pad;      // (batch, m) or null
     const float* o32;        // forward output (for delta)
+    const __nv_bfloat16* o16;  // the same as bf16: used instead of o32 when given (the fused latent block saves only this)
     const __nv_bfloat16* do16;
     const float* lse;        // (batch, heads, n), natural log
     float* delta;            // (batch, heads, n): written by the dQ kernel, read by the dK/dV kernel
@@ -489,11 +490,19 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 128 ? 1 : 2)
         float delta = 0.f, lse2 = INFINITY;  // invalid rows: p = exp2(-inf) = 0
         if (q_ok) {
             const int64_t off = (int64_t)b * p.o_bs + (int64_t)qi * p.o_rs + (int64_t)h * DH;
-            const float* o = p.o32 + off;
             const __nv_bfloat16* g = p.do16 + off;
 #pragma unroll
             for (int d = 0; d < DH; d += 8) {
-                const float4 o0 = *reinterpret_cast<const float4*>(o + d), o1 = *reinterpret_cast<const float4*>(o + d + 4);
+                float4 o0, o1;
+                if (p.o16 != nullptr) {
+                    const uint4 uo = *reinterpret_cast<const uint4*>(p.o16 + off + d);
+                    const __nv_bfloat162* ob = reinterpret_cast<const __nv_bfloat162*>(&uo);
+                    o0 = make_float4(__low2float(ob[0]), __high2float(ob[0]), __low2float(ob[1]), __high2float(ob[1]));
+                    o1 = make_float4(__low2float(ob[2]), __high2float(ob[2]), __low2float(ob[3]), __high2float(ob[3]));
+                } else {
+                    o0 = *reinterpret_cast<const float4*>(p.o32 + off + d);
+                    o1 = *reinterpret_cast<const float4*>(p.o32 + off + d + 4);
+                }
                 const uint4 u = *reinterpret_cast<const uint4*>(g + d);
                 const __nv_bfloat162* gb = reinterpret_cast<const __nv_bfloat162*>(&u);
                 delta += o0.x * __low2float(gb[0]) + o0.y * __high2float(gb[0]) + o0.z * __low2float(gb[1]) + o0.w * __high2float(gb[1]) +
@@ -876,13 +885,14 @@ int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st, con
 
 // q, k, v, dO bf16; o fp32; lse fp32 -> dq16, dk16, dv16 (bf16, strides of q / k / v); delta scratch (batch, heads, n)
 int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta, __nv_bfloat16* dq16, __nv_bfloat16* dk16,
-                __nv_bfloat16* dv16, cudaStream_t st, const DropCfg* drop) {
-    PIO_CHECK_ARG(d && d->q && d->k && d->v && d->o && d->lse && do16 && delta && dq16 && dk16 && dv16, "attn_bwd_tc: null pointer");
+                __nv_bfloat16* dv16, cudaStream_t st, const DropCfg* drop, const __nv_bfloat16* o16) {
+    PIO_CHECK_ARG(d && d->q && d->k && d->v && (d->o || o16) && d->lse && do16 && delta && dq16 && dk16 && dv16,
+                  "attn_bwd_tc: null pointer");
     PIO_CHECK_ARG(attn_fwd_tc_supported(d), "attn_bwd_tc: unsupported shape (head dim %d)", d->dh);
     PIO_CHECK_ARG(d->heads <= 65535 && d->batch <= 65535, "attn_bwd_tc: batch/heads exceed grid limits");
     const int64_t cols = (int64_t)d->heads * d->dh;
     FaBwdParams p{};
-    p.pad = d->pad; p.o32 = d->o; p.do16 = do16; p.lse = d->lse; p.delta = delta;
+    p.pad = d->pad; p.o32 = d->o; p.o16 = o16; p.do16 = do16; p.lse = d->lse; p.delta = delta;
     p.dq16 = dq16; p.dk16 = dk16; p.dv16 = dv16;
     p.o_bs = d->o_bs; p.o_rs = d->o_rs; p.q_bs = d->q_bs; p.q_rs = d->q_rs;
     p.k_bs = d->k_bs; p.k_rs = d->k_rs; p.v_bs = d->v_bs; p.v_rs = d->v_rs;
@@ -927,5 +937,5 @@ extern "C" int pio_attn_bwd_bf16(const pio_attn_desc* fwd, const void* d_o16, vo
         return PIO_ERR_UNSUPPORTED;
     }
     return pio::attn_bwd_tc(fwd, (const __nv_bfloat16*)d_o16, delta, (__nv_bfloat16*)dq16, (__nv_bfloat16*)dk16,
-                            (__nv_bfloat16*)dv16, (cudaStream_t)stream, nullptr);
+                            (__nv_bfloat16*)dv16, (cudaStream_t)stream, nullptr, nullptr);
 }

@@ -112,14 +112,24 @@ __device__ __forceinline__ float warp_max(float v) {
 
 // Counter-based dropout: element `idx` of dropout site `seed` is kept iff hash >= threshold, so the
 // forward and the backward kernels regenerate the same mask from (seed, index) without storing it.
+// Sites are told apart by small seed offsets (seed + 1 = the Residual site, seed + 4 s + {0, 2} for latent layer
+// s ...), so the site key is first run through a full 64-bit mixer on the host (make_drop) and only then
+// combined with the element index: masks of neighbouring sites are independent bit patterns, not shifted
+// copies of one another (tests/test_gpu_dropout.py::test_masks_of_neighbouring_sites_are_uncorrelated).
 struct DropCfg {
-    uint64_t seed;
+    uint64_t seed;       // mixed site key (make_drop), not the caller's raw seed
     uint32_t threshold;  // p * 2^32 ; 0 = dropout off
     float inv_keep;      // 1 / (1 - p)
 };
+static inline uint64_t mix64(uint64_t z) {  // splitmix64 finaliser
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
 static inline DropCfg make_drop(float p, uint64_t seed) {
     DropCfg d;
-    d.seed = seed;
+    d.seed = mix64(mix64(seed) ^ 0xA0761D6478BD642Full);
     if (!(p > 0.f)) {
         d.threshold = 0;
         d.inv_keep = 1.f;
@@ -131,7 +141,7 @@ static inline DropCfg make_drop(float p, uint64_t seed) {
     return d;
 }
 __device__ __forceinline__ bool drop_keep(const DropCfg& d, uint64_t idx) {
-    uint64_t z = (idx + d.seed) * 0x9E3779B97F4A7C15ull;
+    uint64_t z = (idx * 0x9E3779B97F4A7C15ull) ^ d.seed;
     z ^= z >> 32;
     z *= 0xD6E8FEB86659FD93ull;
     z ^= z >> 32;

@@ -21,12 +21,25 @@
 //   * self-attention of the 128 / N samples of a tile is one 128 x 128 score product per head whose
 //     off-diagonal (cross-sample) blocks are never read; P is written with zeros there.
 //
-// Warp roles: warps 0..7 element-wise math (quadrant = warp & 3, column half = warp >> 2), warp 8 = TMA
-// producer, warp 9 = TMEM allocator + MMA issuer.  The element-wise warps and the MMA thread alternate
-// strictly (mbarriers ew_done / mma_done): this first version does not overlap the two.
+// Warp roles: warps 0..15 element-wise math (TMEM lane quadrant = warp & 3, column group = warp >> 2: a thread
+// owns 64 of its row's 256 channels, i.e. its row of one 64-column operand atom), warp 16 = TMA producer,
+// warp 17 = TMEM allocator + MMA issuer.  The element-wise warps and the MMA thread alternate strictly
+// (mbarriers ew_done / mma_done).  Measured on the way (tools/latent_trace.py, cycles per layer and CTA): with
+// 8 element-wise warps the element-wise phases took 42.7 K and the MMA side 30.1 K of 73 K cycles, the
+// element-wise warps issuing at 0.4 IPC per scheduler in chains of tensor-memory loads, shared-memory
+// stores and fences: hence four warps per scheduler, and rows kept in registers across the LayerNorm
+// reduction instead of a second pass over tensor memory.
 //
 // What it writes for the backward pass is the layout of SaSaved / MlpSaved (pio_ops_bf16.cu), so the
-// unfused backward operators run unchanged on its output.
+// unfused backward operators run unchanged on its output.  Thread = row is the wrong shape for global
+// stores (32 lanes = 32 different rows: every 16-byte store instruction touched 32 cache lines and the first
+// version spent a third of its time in the LSU), so nothing but the per-row scalars is stored from
+// registers: the bf16 tensors leave by TMA straight from the swizzled operand tiles the MMAs read (the MMA
+// thread issues the store when the element-wise warps hand a tile over, and waits for the store's read of
+// shared memory before it lets them overwrite it), the fp32 residual copies through the 4 KB of the
+// LayerNorm-output atom that the warp itself is about to fill (32 rows x 128 bytes, swizzled: private to
+// the warp, so only its own lane 0 has to wait for the store's read).  GELU' has no tile to leave from and
+// is the one tensor still stored from registers.
 #include <cuda.h>
 #include <stdlib.h>
 
@@ -45,14 +58,18 @@ constexpr int C = 256;
 constexpr int DH = 64;
 constexpr int H = 4;
 constexpr int ROWS = 128;
-constexpr int THREADS = 320;
-constexpr int EW_THREADS = 256;
+constexpr int EW_WARPS = 16;
+constexpr int EW_THREADS = EW_WARPS * 32;
+constexpr int THREADS = EW_THREADS + 64;
 constexpr int STAGES = 3;
 constexpr int STAGE_BYTES = 32768;
 constexpr int QKV_STAGE_BYTES = 3 * 64 * 128;  // 24 KB: 64 rows each of Wq_h, Wk_h, Wv_h x one 64-column k-block
 constexpr int A_BYTES = 4 * ROWS * 128;        // 64 KB: 128 rows x 256 bf16 as four 64-column swizzle atoms
 constexpr int HEAD_BYTES = ROWS * 128;         // 16 KB: 128 rows x 64 bf16
 constexpr int TMEM_COLS = 512;
+// per-layer parameter block in shared memory (floats)
+constexpr int PAR_LN1_W = 0, PAR_LN1_B = 256, PAR_BQKV = 512, PAR_BO = 1280, PAR_LN2_W = 1536, PAR_LN2_B = 1792, PAR_B1 = 2048,
+              PAR_B2 = 2304, PAR_FLOATS = 2560;
 
 struct LayerPtrs {
     const float *ln1_w, *ln1_b, *bqkv, *bo, *ln2_w, *ln2_b, *b1, *b2;
@@ -70,8 +87,12 @@ struct LayerPtrs {
     float* xout;
 };
 
+// output tensor maps: (columns, rows, layer) with the layer stride of the saved buffer
+enum OutMap : int { OM_SA_H0 = 0, OM_QKV, OM_O16, OM_MLP_H0, OM_MLP_G, OM_MLP_H1, OM_XMID, OM_XNEXT, OM_Y, OM_COUNT };
+
 struct Params {
     CUtensorMap maps[PIO_LATENT_FUSED_MAX_LAYERS][4];  // Wqkv (768 x 256), Wo, W1, W2 (256 x 256), bf16 row-major
+    CUtensorMap out[OM_COUNT];
     LayerPtrs layer[PIO_LATENT_FUSED_MAX_LAYERS];
     const float* x;
     int layers;
@@ -79,6 +100,26 @@ struct Params {
     int64_t total_rows;
     float scale_log2e;
 };
+
+// Phase timeline for tuning (only in builds with -DPIO_LB_TRACE, tools/latent_trace.py): CTA 0's MMA thread (who 0)
+// and lane 0 of element-wise warp 0 (who 1) log (tag, clock64) pairs.
+#ifdef PIO_LB_TRACE
+__device__ long long g_trace[2][2][8192];
+__device__ int g_trace_n[2];
+#define LB_TRACE(who, tag)                                              \
+    do {                                                                \
+        if (blockIdx.x == 0) {                                          \
+            const int _i = g_trace_n[who];                              \
+            if (_i < 8192) {                                            \
+                g_trace[who][0][_i] = (tag);                            \
+                g_trace[who][1][_i] = clock64();                        \
+                g_trace_n[who] = _i + 1;                                \
+            }                                                           \
+        }                                                               \
+    } while (0)
+#else
+#define LB_TRACE(who, tag) do { } while (0)
+#endif
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -88,7 +129,22 @@ __device__ __forceinline__ float ex2(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
-__device__ __forceinline__ void bar_ew() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ void bar_ew() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"((uint64_t)map),
+                 "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// 32 fp32 of row `row` (0..31) into a 32-row x 128-byte swizzled staging slice
+__device__ __forceinline__ void stage_row_f32(uint8_t* slice, int row, const float (&v)[32]) {
+    uint8_t* prow = slice + row * 128;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(prow + ((j ^ (row & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+}
 
 __device__ __forceinline__ void ld_chunk(uint32_t taddr, float (&v)[32]) {
     uint32_t r[32];
@@ -135,11 +191,11 @@ __device__ __forceinline__ void store32_f32_global(float* dst, const float (&v)[
 #pragma unroll
     for (int d = 0; d < 32; d += 4) *reinterpret_cast<float4*>(dst + d) = make_float4(v[d], v[d + 1], v[d + 2], v[d + 3]);
 }
-// v[i] += p[i], p warp-uniform (one transaction per load)
-__device__ __forceinline__ void add_vec32(float (&v)[32], const float* __restrict__ p) {
+// v[i] += p[i], p in shared memory and warp-uniform (a broadcast read)
+__device__ __forceinline__ void add_vec32(float (&v)[32], const float* p) {
 #pragma unroll
     for (int d = 0; d < 32; d += 4) {
-        const float4 t = __ldg(reinterpret_cast<const float4*>(p + d));
+        const float4 t = *reinterpret_cast<const float4*>(p + d);
         v[d] += t.x; v[d + 1] += t.y; v[d + 2] += t.z; v[d + 3] += t.w;
     }
 }
@@ -183,13 +239,17 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
     uint8_t* sK = sQ + HEAD_BYTES;
     uint8_t* sV = sK + HEAD_BYTES;
     uint8_t* ring = sV + HEAD_BYTES;         // [STAGES][32 KB] weight tiles
-    float2* sRed = (float2*)(ring + STAGES * STAGE_BYTES);  // [2 buffers][2 halves][128 rows]
-    uint64_t* bars = (uint64_t*)(sRed + 2 * 2 * ROWS);
+    float2* sRed = (float2*)(ring + STAGES * STAGE_BYTES);  // [4 column groups][128 rows]; reused only after an ew_done / mma_done round trip
+    // the current layer's LayerNorm parameters and biases (read by every thread for every chunk: from L2 each read
+    // cost a full memory round trip in a dependent chain, ncu: 40 % of the stall samples)
+    float* sPar = (float*)(sRed + 4 * ROWS);
+    uint64_t* bars = (uint64_t*)(sPar + PAR_FLOATS);
     uint64_t* full = bars;                   // [STAGES]
     uint64_t* empty = bars + STAGES;         // [STAGES]
     uint64_t* mma_done = bars + 2 * STAGES;
     uint64_t* ew_done = bars + 2 * STAGES + 1;
-    uint32_t* tmem_slot = (uint32_t*)(bars + 2 * STAGES + 2);
+    uint64_t* sa_free = bars + 2 * STAGES + 2;  // the TMA stores out of sA issued by the MMA thread have read it
+    uint32_t* tmem_slot = (uint32_t*)(bars + 2 * STAGES + 3);
 
     pdl_trigger();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -200,10 +260,11 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
             mbar_init(&empty[s], 1);
         }
         mbar_init(mma_done, 1);
-        mbar_init(ew_done, 8);
+        mbar_init(ew_done, EW_WARPS);
+        mbar_init(sa_free, 1);
         fence_barrier_init();
     }
-    if (warp == 9) tmem_alloc(tmem_slot, TMEM_COLS);
+    if (warp == EW_WARPS + 1) tmem_alloc(tmem_slot, TMEM_COLS);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -212,7 +273,7 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
     const uint32_t T_S1 = tmem_base + 256;   // scratch: [Q_h | K_h | V_h] (192) / S (128) + P (64 packed) + O_h (64) / MLP hidden (256)
     pdl_wait();  // everything below reads what earlier kernels wrote (activations, bf16 weight shadows)
 
-    if (warp == 8) {
+    if (warp == EW_WARPS) {
         // ------------------------------------------------------------ TMA producer
         if (lane == 0) {
             int prod = 0;
@@ -255,8 +316,8 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
             }
         }
         __syncwarp();
-    } else if (warp == 9) {
-        // ------------------------------------------------------------ MMA issuer
+    } else if (warp == EW_WARPS + 1) {
+        // ------------------------------------------------------------ MMA issuer (+ TMA stores of the operand tiles)
         if (lane == 0) {
             const uint32_t idesc_qkv = make_idesc(192, false, false);
             const uint32_t idesc_s = make_idesc(128, false, false);
@@ -265,10 +326,14 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
             const uint32_t a_addr = smem_u32(sA), q_addr = smem_u32(sQ), k_addr = smem_u32(sK), v_addr = smem_u32(sV);
             int cons = 0;
             uint32_t ew_phase = 0;
+            int tr = 0;
             auto wait_ew = [&]() {
+                LB_TRACE(0, 1000 + tr);
                 mbar_wait(ew_done, ew_phase);
                 ew_phase ^= 1u;
                 tc_fence_after();
+                LB_TRACE(0, 2000 + tr);
+                ++tr;
             };
             auto ring_wait = [&]() -> uint32_t {
                 const int s = cons % STAGES;
@@ -289,7 +354,9 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
             };
             auto full_k = [&](uint32_t tmem_d, bool into_residual) {  // D (+)= sA W^T over the four k-blocks of the ring
                 for (int kb = 0; kb < 4; ++kb) {
+                    LB_TRACE(0, 3000 + kb);
                     const uint32_t b = ring_wait();
+                    LB_TRACE(0, 3100 + kb);
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
                         umma_bf16(tmem_d, make_smem_desc(a_addr + kb * (ROWS * 128) + k * 32, 16, 1024),
@@ -297,10 +364,22 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
                     ring_release();
                 }
             };
+            const int row0 = blockIdx.x * ROWS;
+            auto store_tile = [&](int which, const uint8_t* tile, int col0, int l) {  // one 128-row x 64-column bf16 atom
+                tma_store_3d(&p.out[which], tile, col0, row0, l);
+            };
             for (int l = 0; l < p.layers; ++l) {
                 for (int h = 0; h < H; ++h) {
                     wait_ew();  // h = 0: LayerNorm output in sA; h > 0: O_{h-1} in sQ
-                    if (h > 0) out_proj();
+                    if (h == 0) {
+#pragma unroll
+                        for (int a = 0; a < 4; ++a) store_tile(OM_SA_H0, sA + a * (ROWS * 128), a * 64, l);
+                        tma_store_commit();
+                    } else {
+                        store_tile(OM_O16, sQ, (h - 1) * DH, l);
+                        tma_store_commit();
+                        out_proj();
+                    }
                     for (int kb = 0; kb < 4; ++kb) {  // [Q_h | K_h | V_h] = LN(x) [Wq_h; Wk_h; Wv_h]^T
                         const uint32_t b = ring_wait();
 #pragma unroll
@@ -309,8 +388,13 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
                                       make_smem_desc(b + k * 32, 16, 1024), idesc_qkv, (kb > 0 || k > 0) ? 1u : 0u);
                         ring_release();
                     }
+                    if (h > 0) tma_store_wait_read();  // O_{h-1} has left sQ: the element-wise warps may write Q_h over it
                     umma_commit(mma_done);
                     wait_ew();  // Q_h, K_h, V_h as bf16 in shared memory
+                    store_tile(OM_QKV, sQ, h * DH, l);
+                    store_tile(OM_QKV, sK, C + h * DH, l);
+                    store_tile(OM_QKV, sV, 2 * C + h * DH, l);
+                    tma_store_commit();
 #pragma unroll
                     for (int k = 0; k < 4; ++k)  // S = Q_h K_h^T for all 128 x 128 (row, key) pairs of the tile
                         umma_bf16(T_S1, make_smem_desc(q_addr + k * 32, 16, 1024), make_smem_desc(k_addr + k * 32, 16, 1024), idesc_s,
@@ -321,24 +405,41 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
                     for (int t = 0; t < 8; ++t)  // O_h = P V_h
                         umma_bf16_ts(T_S1 + 192, T_S1 + 128 + (uint32_t)t * 8, make_smem_desc(v_addr + t * 2048, ROWS * 128, 1024),
                                      idesc_pv, t > 0 ? 1u : 0u);
+                    tma_store_wait_read();  // Q_h has left sQ (O_h goes there next); K_h, V_h and (h = 0) the LayerNorm copy likewise
                     umma_commit(mma_done);
                 }
                 wait_ew();
+                store_tile(OM_O16, sQ, (H - 1) * DH, l);
+                tma_store_commit();
                 out_proj();
                 umma_commit(mma_done);
                 wait_ew();  // LayerNorm 2 output in sA
+#pragma unroll
+                for (int a = 0; a < 4; ++a) store_tile(OM_MLP_H0, sA + a * (ROWS * 128), a * 64, l);
+                tma_store_commit();
                 full_k(T_S1, false);
                 umma_commit(mma_done);
+                LB_TRACE(0, 3200);
+                tma_store_wait_read();  // off the critical path: the element-wise warps first turn the hidden tile into GELU values
+                LB_TRACE(0, 3201);
+                mbar_arrive(sa_free);
                 wait_ew();  // GELU output in sA
+#pragma unroll
+                for (int a = 0; a < 4; ++a) store_tile(OM_MLP_G, sA + a * (ROWS * 128), a * 64, l);
+                tma_store_commit();
                 full_k(T_RES, true);
                 umma_commit(mma_done);
+                tma_store_wait_read();
+                mbar_arrive(sa_free);
             }
+            tma_store_wait_all();
         }
         __syncwarp();
     } else {
         // ------------------------------------------------------------ element-wise warps
-        const int q = warp & 3, half = warp >> 2;
+        const int q = warp & 3, cg = warp >> 2;   // TMEM lane quadrant, column group (= operand atom) of this warp
         const int row = q * 32 + lane;
+        const int col_base = cg * 64;
         const uint32_t lane_off = (uint32_t)(q * 32) << 16;
         const int64_t grow = (int64_t)blockIdx.x * ROWS + row;
         const bool row_ok = grow < p.total_rows;
@@ -346,12 +447,24 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
         const int64_t sample = grow / n;
         const int qi = (int)(grow - sample * n);
         const int kbase = (row / n) * n;  // first key column of this row's sample (warp-uniform: n >= 32)
-        uint32_t mma_phase = 0;
-        int red_buf = 0;
+        uint32_t mma_phase = 0, sa_phase = 0;
+        // this warp's rows of its own LayerNorm-output atom: 32 rows x 128 bytes = 4 KB nobody else touches; doubles
+        // as the staging slice of the fp32 residual copies (x_mid, x_next) that leave by TMA
+        uint8_t* atom = sA + cg * (ROWS * 128);
+        uint8_t* slice = atom + q * 4096;
+        const int slice_row0 = blockIdx.x * ROWS + q * 32;
+        int tr = 0;
         auto wait_mma = [&]() {
+            if (threadIdx.x == 0) LB_TRACE(1, 1000 + tr);
             mbar_wait(mma_done, mma_phase);
             mma_phase ^= 1u;
             tc_fence_after();
+            if (threadIdx.x == 0) LB_TRACE(1, 2000 + tr);
+            ++tr;
+        };
+        auto wait_sa_free = [&]() {
+            mbar_wait(sa_free, sa_phase);
+            sa_phase ^= 1u;
         };
         auto signal = [&]() {  // everything this warp wrote (shared memory, tensor memory) is visible to the MMA thread
             tc_fence_before();
@@ -359,94 +472,128 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
             __syncwarp();
             if (lane == 0) mbar_arrive(ew_done);
         };
-        // combine the two column halves' statistics, write (mean, rstd), then normalise the row out of tensor memory
-        // into sA (and the bf16 copy the backward pass reads)
-        auto ln_finish = [&](const Stat& st, const float* __restrict__ gamma, const float* __restrict__ beta, float* stats_out,
-                             bf16* h0_out) {
-            float2* mine = sRed + (red_buf * 2 + half) * ROWS;
-            const float2* other = sRed + (red_buf * 2 + (half ^ 1)) * ROWS;
-            red_buf ^= 1;
-            mine[row] = make_float2(st.mean, st.m2);
-            bar_ew();
-            const float2 o = other[row];
-            Stat t = st;
-            stat_merge(t, 128.f, o.x, o.y);
-            const float mean = t.mean;
-            const float rstd = rsqrtf(t.m2 * (1.0f / C) + LN_EPS);
-            if (half == 0 && row_ok) *reinterpret_cast<float2*>(stats_out + 2 * grow) = make_float2(mean, rstd);
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                const int col0 = half * 128 + c * 32;
-                float v[32];
-                ld_chunk(T_RES + lane_off + (uint32_t)col0, v);
+        // 32 fp32 per row -> the warp's slice -> TMA store; an earlier store out of the slice must have read it
+        auto stage_store_f32 = [&](int which, int col0, int l, const float* v) {
+            if (lane == 0) tma_store_wait_read();
+            __syncwarp();
+            uint8_t* prow = slice + lane * 128;
 #pragma unroll
-                for (int d = 0; d < 32; d += 4) {
-                    const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + col0 + d));
-                    const float4 b = __ldg(reinterpret_cast<const float4*>(beta + col0 + d));
-                    v[d] = fmaf((v[d] - mean) * rstd, g.x, b.x);
-                    v[d + 1] = fmaf((v[d + 1] - mean) * rstd, g.y, b.y);
-                    v[d + 2] = fmaf((v[d + 2] - mean) * rstd, g.z, b.z);
-                    v[d + 3] = fmaf((v[d + 3] - mean) * rstd, g.w, b.w);
-                }
-                store_half_row_smem(sA + (col0 >> 6) * (ROWS * 128), row, (col0 >> 5) & 1, v);
-                if (row_ok) store32_bf16_global(h0_out + grow * C + col0, v);
+            for (int j = 0; j < 8; ++j)
+                *reinterpret_cast<float4*>(prow + ((j ^ (lane & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_3d(&p.out[which], slice, col0, slice_row0, l);
+                tma_store_commit();
             }
         };
+        // v = this thread's 64 channels of its row, st their statistics: combine the four column groups' statistics,
+        // write (mean, rstd), normalise in registers and write the bf16 row into the warp's atom of sA
+        auto ln_finish = [&](float (&v)[64], const Stat& st, const float* gamma, const float* beta, float* stats_out) {
+            float2* red = sRed;
+            red[cg * ROWS + row] = make_float2(st.mean, st.m2);
+            if (threadIdx.x == 0) LB_TRACE(1, 6000);
+            bar_ew();
+            if (threadIdx.x == 0) LB_TRACE(1, 6001);
+            Stat t{0.f, 0.f, 0.f};
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {  // same order in every thread: the four warps of a row agree bit for bit
+                const float2 o = red[g * ROWS + row];
+                if (g == 0) {
+                    t.n = 64.f; t.mean = o.x; t.m2 = o.y;
+                } else {
+                    stat_merge(t, 64.f, o.x, o.y);
+                }
+            }
+            const float mean = t.mean;
+            const float rstd = rsqrtf(t.m2 * (1.0f / C) + LN_EPS);
+            if (cg == 0 && row_ok) *reinterpret_cast<float2*>(stats_out + 2 * grow) = make_float2(mean, rstd);
+#pragma unroll
+            for (int d = 0; d < 64; d += 4) {
+                const float4 g = *reinterpret_cast<const float4*>(gamma + col_base + d);
+                const float4 b = *reinterpret_cast<const float4*>(beta + col_base + d);
+                v[d] = fmaf((v[d] - mean) * rstd, g.x, b.x);
+                v[d + 1] = fmaf((v[d + 1] - mean) * rstd, g.y, b.y);
+                v[d + 2] = fmaf((v[d + 2] - mean) * rstd, g.z, b.z);
+                v[d + 3] = fmaf((v[d + 3] - mean) * rstd, g.w, b.w);
+            }
+            if (threadIdx.x == 0) LB_TRACE(1, 6002);
+            if (lane == 0) tma_store_wait_read();  // the residual copy staged in this slice has left it
+            __syncwarp();
+            if (threadIdx.x == 0) LB_TRACE(1, 6003);
+            store_half_row_smem(atom, row, 0, *reinterpret_cast<float(*)[32]>(&v[0]));
+            store_half_row_smem(atom, row, 1, *reinterpret_cast<float(*)[32]>(&v[32]));
+        };
+
+        // parameters of a layer: five coalesced loads per thread into registers (prefetch), later into sPar
+        float pre[5];
+        auto prefetch_params = [&](int l) {
+            const LayerPtrs& Lp = p.layer[l];
+            const float* seg[10] = {Lp.ln1_w, Lp.ln1_b, Lp.bqkv, Lp.bqkv + 256, Lp.bqkv + 512, Lp.bo, Lp.ln2_w, Lp.ln2_b, Lp.b1, Lp.b2};
+#pragma unroll
+            for (int k = 0; k < 5; ++k)  // element k * 512 + tid of the 2560: segment 2k or 2k + 1 (constant indices: no local array)
+                pre[k] = __ldg(((threadIdx.x >> 8) ? seg[2 * k + 1] : seg[2 * k]) + (threadIdx.x & 255));
+        };
+        auto commit_params = [&]() {
+#pragma unroll
+            for (int k = 0; k < 5; ++k) sPar[k * EW_THREADS + threadIdx.x] = pre[k];
+        };
+        prefetch_params(0);
 
         // ---- layer 0 input: global -> tensor memory, statistics on the way
+        float v[64];
         Stat st{0.f, 0.f, 0.f};
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-            const int col0 = half * 128 + c * 32;
-            float v[32];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const int col0 = col_base + c * 32;
+            float(&vc)[32] = *reinterpret_cast<float(*)[32]>(&v[c * 32]);
             if (row_ok) {
                 const float4* src = reinterpret_cast<const float4*>(p.x + grow * C + col0);
 #pragma unroll
                 for (int d = 0; d < 8; ++d) {
                     const float4 t = src[d];
-                    v[4 * d] = t.x; v[4 * d + 1] = t.y; v[4 * d + 2] = t.z; v[4 * d + 3] = t.w;
+                    vc[4 * d] = t.x; vc[4 * d + 1] = t.y; vc[4 * d + 2] = t.z; vc[4 * d + 3] = t.w;
                 }
             } else {
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = 0.f;
+                for (int i = 0; i < 32; ++i) vc[i] = 0.f;
             }
-            st_chunk(T_RES + lane_off + (uint32_t)col0, v);
-            stat_chunk(st, v);
+            st_chunk(T_RES + lane_off + (uint32_t)col0, vc);
+            stat_chunk(st, vc);
         }
         tmem_st_wait();
+        commit_params();  // (the barrier inside ln_finish orders these writes before anyone's reads)
 
         for (int l = 0; l < p.layers; ++l) {
             const LayerPtrs& L = p.layer[l];
-            ln_finish(st, L.ln1_w, L.ln1_b, L.sa_stats, L.sa_h0);
+            ln_finish(v, st, sPar + PAR_LN1_W, sPar + PAR_LN1_B, L.sa_stats);
             signal();
 
             for (int h = 0; h < H; ++h) {
-                // ---- [Q_h | K_h | V_h] + bias -> bf16 operand tiles (+ the qkv copy for the backward pass)
+                // ---- [Q_h | K_h | V_h] + bias -> bf16 operand tiles (column groups 0, 1, 2 take Q, K, V)
                 wait_mma();
-#pragma unroll 1
-                for (int cc = 0; cc < 3; ++cc) {
-                    const int c = half * 3 + cc;  // 32-column chunk of the 192
-                    const int which = c >> 1, hh = c & 1;
-                    float v[32];
-                    ld_chunk(T_S1 + lane_off + (uint32_t)(c * 32), v);
-                    const int fcol = which * C + h * DH + hh * 32;  // feature index in the packed (3C) projection
-                    add_vec32(v, L.bqkv + fcol);
-                    uint8_t* tile = which == 0 ? sQ : (which == 1 ? sK : sV);
-                    store_half_row_smem(tile, row, hh, v);
-                    if (row_ok) store32_bf16_global(L.qkv + grow * (3 * C) + fcol, v);
+                if (cg < 3) {
+                    uint8_t* tile = cg == 0 ? sQ : (cg == 1 ? sK : sV);
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        float t[32];
+                        ld_chunk(T_S1 + lane_off + (uint32_t)(cg * 64 + c * 32), t);
+                        add_vec32(t, sPar + PAR_BQKV + cg * C + h * DH + c * 32);
+                        store_half_row_smem(tile, row, c, t);
+                    }
                 }
                 signal();
 
-                // ---- softmax over the row's own sample (column half 0 warps; the others have nothing to do here)
+                // ---- softmax over the row's own sample (column group 0 warps)
                 wait_mma();
                 float inv_l = 0.f;
-                if (half == 0) {
+                if (cg == 0) {
                     float mx = -INFINITY;
                     for (int c = 0; c < (n >> 5); ++c) {
-                        float v[32];
-                        ld_chunk(T_S1 + lane_off + (uint32_t)(kbase + c * 32), v);
+                        float t[32];
+                        ld_chunk(T_S1 + lane_off + (uint32_t)(kbase + c * 32), t);
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, v[i]);
+                        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, t[i]);
                     }
                     const float m2 = mx * p.scale_log2e;
                     float lsum = 0.f;
@@ -457,16 +604,16 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
                         for (int c2 = 0; c2 < 2; ++c2) {
                             const int key0 = g * 64 + c2 * 32;
                             if (key0 >= kbase && key0 < kbase + n) {  // warp-uniform
-                                float v[32];
-                                ld_chunk(T_S1 + lane_off + (uint32_t)key0, v);
+                                float t[32];
+                                ld_chunk(T_S1 + lane_off + (uint32_t)key0, t);
 #pragma unroll
                                 for (int i = 0; i < 32; ++i) {
-                                    v[i] = ex2(fmaf(v[i], p.scale_log2e, -m2));
-                                    lsum += v[i];
+                                    t[i] = ex2(fmaf(t[i], p.scale_log2e, -m2));
+                                    lsum += t[i];
                                 }
 #pragma unroll
                                 for (int i = 0; i < 16; ++i) {
-                                    __nv_bfloat162 h2 = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+                                    __nv_bfloat162 h2 = __floats2bfloat162_rn(t[2 * i], t[2 * i + 1]);
                                     pw[c2 * 16 + i] = *reinterpret_cast<uint32_t*>(&h2);
                                 }
                             } else {
@@ -482,83 +629,94 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
                 }
                 signal();
 
-                // ---- O_h / l -> bf16 operand of the out-projection (over Q_h) + the copies for the backward pass
+                // ---- O_h / l -> bf16 operand of the out-projection (over Q_h)
                 wait_mma();
-                if (half == 0) {
-#pragma unroll 1
-                    for (int c = 0; c < 2; ++c) {
-                        float v[32];
-                        ld_chunk(T_S1 + 192 + lane_off + (uint32_t)(c * 32), v);
+                if (cg == 0) {
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) v[i] *= inv_l;
-                        store_half_row_smem(sQ, row, c, v);
-                        if (row_ok) {
-                            const int64_t off = grow * C + h * DH + c * 32;
-                            store32_f32_global(L.o32 + off, v);
-                            store32_bf16_global(L.o16 + off, v);
-                        }
+                    for (int c = 0; c < 2; ++c) {
+                        float t[32];
+                        ld_chunk(T_S1 + 192 + lane_off + (uint32_t)(c * 32), t);
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) t[i] *= inv_l;
+                        store_half_row_smem(sQ, row, c, t);
                     }
                 }
                 signal();
             }
 
-            // ---- x_mid = x + attention + bo (back into the residual columns), LayerNorm 2
+            // ---- x_mid = x + attention + bo (back into the residual columns, fp32 copy out), LayerNorm 2
             wait_mma();
             st = Stat{0.f, 0.f, 0.f};
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                const int col0 = half * 128 + c * 32;
-                float v[32];
-                ld_chunk(T_RES + lane_off + (uint32_t)col0, v);
-                add_vec32(v, L.bo + col0);
-                st_chunk(T_RES + lane_off + (uint32_t)col0, v);
-                if (row_ok) store32_f32_global(L.xmid + grow * C + col0, v);
-                stat_chunk(st, v);
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                const int col0 = col_base + c * 32;
+                float(&vc)[32] = *reinterpret_cast<float(*)[32]>(&v[c * 32]);
+                ld_chunk(T_RES + lane_off + (uint32_t)col0, vc);
+                add_vec32(vc, sPar + PAR_BO + col0);
+                st_chunk(T_RES + lane_off + (uint32_t)col0, vc);
+                if (threadIdx.x == 0) LB_TRACE(1, 5000 + c);
+                stage_store_f32(OM_XMID, col0, l, vc);
+                if (threadIdx.x == 0) LB_TRACE(1, 5010 + c);
+                stat_chunk(st, vc);
             }
             tmem_st_wait();
-            ln_finish(st, L.ln2_w, L.ln2_b, L.mlp_stats, L.mlp_h0);
+            if (threadIdx.x == 0) LB_TRACE(1, 5020);
+            ln_finish(v, st, sPar + PAR_LN2_W, sPar + PAR_LN2_B, L.mlp_stats);
+            if (threadIdx.x == 0) LB_TRACE(1, 5021);
             signal();
+            if (threadIdx.x == 0) LB_TRACE(1, 5022);
 
-            // ---- GELU(hidden + b1) -> sA (+ GELU and GELU' copies for the backward pass)
+            // ---- GELU(hidden + b1) -> sA (bf16; leaves by TMA), GELU' (bf16) for the backward pass from registers
             wait_mma();
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                const int col0 = half * 128 + c * 32;
-                float v[32], dg[32];
-                ld_chunk(T_S1 + lane_off + (uint32_t)col0, v);
-                add_vec32(v, L.b1 + col0);
+            if (threadIdx.x == 0) LB_TRACE(1, 4000);
+            wait_sa_free();  // the LayerNorm-2 copy has left sA
+            if (threadIdx.x == 0) LB_TRACE(1, 4001);
 #pragma unroll
-                for (int i = 0; i < 32; ++i) gelu_erf_both(v[i], v[i], dg[i]);
-                store_half_row_smem(sA + (col0 >> 6) * (ROWS * 128), row, (col0 >> 5) & 1, v);
-                if (row_ok) {
-                    store32_bf16_global(L.mlp_g + grow * C + col0, v);
-                    store32_bf16_global(L.mlp_h1 + grow * C + col0, dg);
-                }
+            for (int c = 0; c < 2; ++c) {
+                const int col0 = col_base + c * 32;
+                float t[32], dg[32];
+                if (threadIdx.x == 0) LB_TRACE(1, 4010 + c);
+                ld_chunk(T_S1 + lane_off + (uint32_t)col0, t);
+                add_vec32(t, sPar + PAR_B1 + col0);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) gelu_erf_both(t[i], t[i], dg[i]);
+                store_half_row_smem(atom, row, c, t);
+                if (row_ok) store32_bf16_global(L.mlp_h1 + grow * C + col0, dg);
             }
+            if (threadIdx.x == 0) LB_TRACE(1, 4020);
             signal();
+            if (threadIdx.x == 0) LB_TRACE(1, 4021);
 
-            // ---- x_next = x_mid + mlp + b2: out to global; stays in the residual columns for the next layer
+            // ---- x_next = x_mid + mlp + b2: fp32 copy out; stays in the residual columns (and registers) for the next layer
             wait_mma();
+            wait_sa_free();  // the GELU copy has left sA: the slices are free for staging
             const bool last = (l + 1 == p.layers);
+            if (!last) prefetch_params(l + 1);
             st = Stat{0.f, 0.f, 0.f};
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                const int col0 = half * 128 + c * 32;
-                float v[32];
-                ld_chunk(T_RES + lane_off + (uint32_t)col0, v);
-                add_vec32(v, L.b2 + col0);
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                const int col0 = col_base + c * 32;
+                float(&vc)[32] = *reinterpret_cast<float(*)[32]>(&v[c * 32]);
+                ld_chunk(T_RES + lane_off + (uint32_t)col0, vc);
+                add_vec32(vc, sPar + PAR_B2 + col0);
                 if (!last) {
-                    st_chunk(T_RES + lane_off + (uint32_t)col0, v);
-                    stat_chunk(st, v);
+                    st_chunk(T_RES + lane_off + (uint32_t)col0, vc);
+                    stat_chunk(st, vc);
                 }
-                if (row_ok) store32_f32_global(L.xout + grow * C + col0, v);
+                stage_store_f32(last ? OM_Y : OM_XNEXT, col0, last ? 0 : l, vc);
             }
-            if (!last) tmem_st_wait();
+            if (!last) {
+                tmem_st_wait();
+                bar_ew();  // every warp is done with this layer's parameters
+                commit_params();
+            }
         }
+        if (lane == 0) tma_store_wait_all();
+        __syncwarp();
         tc_fence_before();
     }
     __syncthreads();
-    if (warp == 9) {
+    if (warp == EW_WARPS + 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, TMEM_COLS);
     }
@@ -566,9 +724,60 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
 
 }  // namespace lb
 
-bool latent_fused_supported(int n, int ch, int heads, float drop_p) {
-    const bool disabled = getenv("PIO_NO_FUSED_LATENT") != nullptr;  // read per call: tests compare both paths in one process
-    return !disabled && ch == lb::C && heads == lb::H && (n == 32 || n == 64 || n == 128) && !(drop_p > 0.f);
+// (cols, rows, layers) tensor map with byte strides (pitch, layer_stride); box = box_cols x box_rows x 1, 128-byte swizzle
+static int make_out_map(CUtensorMap* map, bool f32, const void* base, int64_t cols, int64_t rows, int64_t nl, int64_t pitch,
+                        int64_t layer_stride, int box_cols, int box_rows) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) {
+        set_error("cuTensorMapEncodeTiled entry point not available from the driver");
+        return PIO_ERR_CUDA;
+    }
+    PIO_CHECK_ARG((((uintptr_t)base) & 15) == 0 && pitch % 16 == 0 && layer_stride % 16 == 0 && layer_stride > 0,
+                  "latent_block_fwd_fused: saved-state tensor not 16-byte aligned (base %p pitch %lld layer stride %lld)", base,
+                  (long long)pitch, (long long)layer_stride);
+    cuuint64_t gdim[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)nl};
+    cuuint64_t gstr[2] = {(cuuint64_t)pitch, (cuuint64_t)layer_stride};
+    cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1u};
+    cuuint32_t estr[3] = {1u, 1u, 1u};
+    CUresult r = fn(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim,
+                    gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled (latent block output) failed with CUresult %d", (int)r);
+        return PIO_ERR_CUDA;
+    }
+    return PIO_OK;
+}
+
+#ifdef PIO_LB_TRACE
+extern "C" int pio_debug_lb_trace(long long* out, int max_pairs, int who, int reset) {
+    int n = 0;
+    cudaMemcpyFromSymbol(&n, lb::g_trace_n, sizeof(int), who * sizeof(int));
+    n = std::min(n, max_pairs);
+    if (out && n > 0) {
+        cudaMemcpyFromSymbol(out, lb::g_trace, (size_t)n * 8, (size_t)(who * 2 + 0) * 8192 * 8);
+        cudaMemcpyFromSymbol(out + max_pairs, lb::g_trace, (size_t)n * 8, (size_t)(who * 2 + 1) * 8192 * 8);
+    }
+    if (reset) {
+        int z[2] = {0, 0};
+        cudaMemcpyToSymbol(lb::g_trace_n, z, sizeof(z));
+    }
+    return n;
+}
+#endif
+
+// When the fused kernel is used.  One CTA runs a whole layer for 128 rows, so its time per layer barely depends on
+// the batch (measured on B200, 6 layers, N = 64: 42.7 us per layer at 32 tiles, 44.8 at 64, 48.5 at 148), while the
+// unfused operators spread every product over all SMs and scale with the rows (34.6 us per layer at 32 tiles, 51.5
+// at 64, 80.0 at 148).  The crossover is near 50 tiles; below it the seven launches per layer are faster, because a
+// tile's element-wise work (~80 K warp instructions per layer) and its 1.5 MB of weight + saved-state traffic
+// per layer are then concentrated on a quarter of the SMs.  PIO_FUSED_LATENT_MIN_ROWS overrides the threshold
+// (0 = always), PIO_NO_FUSED_LATENT switches the kernel off; both are read per call (tests compare the two paths).
+bool latent_fused_supported(int64_t rows, int n, int ch, int heads, float drop_p) {
+    if (getenv("PIO_NO_FUSED_LATENT") != nullptr) return false;
+    int64_t min_rows = 56 * lb::ROWS;
+    if (const char* e = getenv("PIO_FUSED_LATENT_MIN_ROWS")) min_rows = atoll(e);
+    return rows >= min_rows && ch == lb::C && heads == lb::H && (n == 32 || n == 64 || n == 128) && !(drop_p > 0.f);
 }
 
 int latent_block_fwd_fused(const float* x, const LatentFusedLayer* layers, int nlayers, int batch, int n, cudaStream_t st) {
@@ -589,13 +798,37 @@ int latent_block_fwd_fused(const float* x, const LatentFusedLayer* layers, int n
         d.lse = s.lse; d.xmid = s.xmid; d.mlp_stats = s.mlp_stats; d.mlp_h0 = (lb::bf16*)s.mlp_h0; d.mlp_h1 = (lb::bf16*)s.mlp_h1;
         d.mlp_g = (lb::bf16*)s.mlp_g; d.xout = s.xout;
     }
+    {
+        using namespace lb;
+        const LatentFusedLayer& f0 = layers[0];
+        auto stride_of = [&](const void* a0, const void* a1) -> int64_t {
+            return nlayers > 1 ? (int64_t)((const char*)a1 - (const char*)a0) : (int64_t)256;
+        };
+        const LatentFusedLayer& f1 = layers[nlayers > 1 ? 1 : 0];
+        for (int l = 2; l < nlayers; ++l)  // the layers' slabs must be equally spaced (they are: BlockLayout::per_layer)
+            PIO_CHECK_ARG((const char*)layers[l].xmid - (const char*)layers[l - 1].xmid == (const char*)f1.xmid - (const char*)f0.xmid,
+                          "latent_block_fwd_fused: saved slabs are not equally spaced");
+        PIO_TRY(make_out_map(&p.out[OM_SA_H0], false, f0.sa_h0, C, rows, nlayers, C * 2, stride_of(f0.sa_h0, f1.sa_h0), 64, ROWS));
+        PIO_TRY(make_out_map(&p.out[OM_QKV], false, f0.qkv, 3 * C, rows, nlayers, 3 * C * 2, stride_of(f0.qkv, f1.qkv), 64, ROWS));
+        PIO_TRY(make_out_map(&p.out[OM_O16], false, f0.o16, C, rows, nlayers, C * 2, stride_of(f0.o16, f1.o16), 64, ROWS));
+        PIO_TRY(make_out_map(&p.out[OM_MLP_H0], false, f0.mlp_h0, C, rows, nlayers, C * 2, stride_of(f0.mlp_h0, f1.mlp_h0), 64, ROWS));
+        PIO_TRY(make_out_map(&p.out[OM_MLP_G], false, f0.mlp_g, C, rows, nlayers, C * 2, stride_of(f0.mlp_g, f1.mlp_g), 64, ROWS));
+        PIO_TRY(make_out_map(&p.out[OM_MLP_H1], false, f0.mlp_h1, C, rows, nlayers, C * 2, stride_of(f0.mlp_h1, f1.mlp_h1), 64, 32));
+        PIO_TRY(make_out_map(&p.out[OM_XMID], true, f0.xmid, C, rows, nlayers, C * 4, stride_of(f0.xmid, f1.xmid), 32, 32));
+        if (nlayers > 1)  // (the last layer's output is the OM_Y map; the slabs are spaced like every other saved tensor)
+            PIO_TRY(make_out_map(&p.out[OM_XNEXT], true, f0.xout, C, rows, nlayers - 1, C * 4, stride_of(f0.xmid, f1.xmid), 32, 32));
+        PIO_TRY(make_out_map(&p.out[OM_Y], true, layers[nlayers - 1].xout, C, rows, 1, C * 4, 256, 32, 32));
+    }
     p.x = x;
     p.layers = nlayers;
     p.n = n;
     p.total_rows = rows;
     p.scale_log2e = (1.0f / sqrtf((float)lb::DH)) * 1.44269504088896340736f;
-    const size_t smem = (size_t)lb::A_BYTES + 3 * lb::HEAD_BYTES + lb::STAGES * lb::STAGE_BYTES + 2 * 2 * lb::ROWS * sizeof(float2) +
-                        16 * sizeof(uint64_t) + 1024;
+    const size_t smem = (size_t)lb::A_BYTES + 3 * lb::HEAD_BYTES + lb::STAGES * lb::STAGE_BYTES + 4 * lb::ROWS * sizeof(float2) +
+                        lb::PAR_FLOATS * sizeof(float) + 16 * sizeof(uint64_t) + 1024;
+    static_assert((size_t)lb::A_BYTES + 3 * lb::HEAD_BYTES + lb::STAGES * lb::STAGE_BYTES + 4 * lb::ROWS * sizeof(float2) +
+                          lb::PAR_FLOATS * sizeof(float) + 16 * sizeof(uint64_t) + 1024 <= 232448,
+                  "latent block kernel: more than 227 KB of shared memory");
     int dev = 0;
     PIO_CUDA(cudaGetDevice(&dev));
     static bool configured[64] = {};

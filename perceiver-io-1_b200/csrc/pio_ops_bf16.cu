@@ -466,7 +466,7 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
     if (attn_fwd_tc_supported(&b.fwd)) {
         bf16* d_o16 = reinterpret_cast<bf16*>(d_o);
         PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->wo, ch, rows, ch, ch, nullptr, 0, d_o16, ch, 0, nullptr, 0, 0));
-        PIO_TRY(attn_bwd_tc(&b.fwd, d_o16, delta, dqkv16, dqkv16 + ch, dqkv16 + 2 * ch, c.st, &adrop));
+        PIO_TRY(attn_bwd_tc(&b.fwd, d_o16, delta, dqkv16, dqkv16 + ch, dqkv16 + 2 * ch, c.st, &adrop, s.o16));
     } else {
         PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->wo, ch, rows, ch, ch, d_o, ch, nullptr, 0, 0, nullptr, 0, 0));
         b.d_o = d_o; b.delta = delta;
@@ -513,7 +513,7 @@ int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* a
     BlockLayout L(batch, n, ch, heads);
     const int64_t rows = (int64_t)batch * n;
     const float* cur = x;
-    if (latent_fused_supported(n, ch, heads, c.drop_p)) {
+    if (latent_fused_supported(rows, n, ch, heads, c.drop_p)) {
         // one persistent kernel per (up to 8) layers: pio_latent_tc.cu
         bool packed = true;
         for (int s = 0; s < layers; ++s) packed = packed && check_packed_self(&attn[s], ch, "pio_latent_block_fwd") == PIO_OK;

@@ -20,8 +20,9 @@ int attn_bwd_simt(const pio_attn_bwd_desc* d, cudaStream_t st, const AttnBf16Out
 bool attn_fwd_tc_supported(const pio_attn_desc* d);
 int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st, const DropCfg* drop = nullptr);
 // tcgen05 backward: dO bf16 (strides of o), gradients bf16 with the strides of q / k / v
+// (o16 given: the row term delta = dO . O is formed from the bf16 copy of the output instead of d->o)
 int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta, __nv_bfloat16* dq16, __nv_bfloat16* dk16,
-                __nv_bfloat16* dv16, cudaStream_t st, const DropCfg* drop = nullptr);
+                __nv_bfloat16* dv16, cudaStream_t st, const DropCfg* drop = nullptr, const __nv_bfloat16* o16 = nullptr);
 
 int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream_t st);
 int cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_src, int64_t ld_dst, cudaStream_t st);
@@ -93,7 +94,7 @@ struct LatentFusedLayer {
     float* mlp_stats; void* mlp_h0; void* mlp_h1; void* mlp_g;
     float* xout;
 };
-bool latent_fused_supported(int n, int ch, int heads, float drop_p);
+bool latent_fused_supported(int64_t rows, int n, int ch, int heads, float drop_p);
 int latent_block_fwd_fused(const float* x, const LatentFusedLayer* layers, int nlayers, int batch, int n, cudaStream_t st);
 
 // PIO_MODE_BF16 pipelines (pio_ops_bf16.cu)

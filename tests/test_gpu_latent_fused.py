@@ -19,8 +19,10 @@ def bf16_mode():
     import perceiver
     perceiver.set_compute_mode("bf16")
     os.environ.pop("PIO_NO_FUSED_LATENT", None)
+    os.environ["PIO_FUSED_LATENT_MIN_ROWS"] = "0"  # by default the fused kernel only takes blocks of >= 56 row tiles
     yield
     os.environ.pop("PIO_NO_FUSED_LATENT", None)
+    os.environ.pop("PIO_FUSED_LATENT_MIN_ROWS", None)
     perceiver.set_compute_mode("fp32")
 
 
@@ -33,7 +35,7 @@ def _run(block, x, dy):
     return y.detach(), xin.grad.detach(), {k: p.grad.detach().clone() for k, p in block.named_parameters()}
 
 
-@pytest.mark.parametrize("batch,n,layers", [(2, 64, 1), (4, 64, 2), (3, 64, 6), (5, 32, 3), (3, 128, 2), (2, 64, 9), (64, 64, 6)])
+@pytest.mark.parametrize("batch,n,layers", [(2, 64, 1), (4, 64, 2), (3, 64, 6), (5, 32, 3), (3, 128, 2), (2, 64, 9), (64, 64, 6), (128, 64, 2)])
 def test_fused_block_matches_unfused_operators(batch, n, layers):
     from perceiver import _native as N
     from perceiver.model import self_attention_block
