@@ -424,63 +424,21 @@ def gpu_arm(args):
     # round trips per step from the critical path.
     use_graph = fused_loss and not args.no_graph
     graph = None
+    grad_exchange = "none"
     if use_graph:
+        # perceiver.GraphedMLMStep: masking prefetched on a side stream; forward + fused loss head + backward (gradients
+        # written in place into one flat buffer) + AdamW captured once and replayed; with N > 1 the flat buffer's buckets
+        # are all-reduced on a side stream from inside the captured backward pass (decoder + head first, the shared
+        # layer_n and the embedding last), so the collectives are part of the graph too.
         opt = make_optimizer(capturable=True)
-        g_ids = torch.empty_like(ids_d)
-        g_labels = torch.empty_like(ids_d)
-        g_pad = pad_d.clone()
-
-        params = [p for p in model.parameters() if p.requires_grad]
-        sizes = [p.numel() for p in params]
-
-        def tail():
-            """data-parallel gradient exchange + optimizer, eager (a handful of launches): one flat NCCL
-            all-reduce (mean) of the 45 MB fp32 gradient set over NVLink, then fused AdamW"""
-            average_gradients(params)  # no-op on one rank
-            opt.step()
-
-        def body():
-            loss, _ = model(g_ids, g_pad, masking=False, return_loss=True, labels=g_labels)
-            loss.backward()
-            if not distributed:
-                opt.step()  # single GPU: the optimizer is part of the captured graph
-            return loss
-
-        # TextMasking's host read (the randint length) would idle the GPU between steps: the batch of step i+1
-        # is copied in and masked on a side stream while step i computes (perceiver.MaskingPrefetcher; one
-        # masking per step, same kernels and RNG draws, only earlier).
-        prefetch = perceiver.MaskingPrefetcher(model.masking, dev)
-
-        def mask_into_static(ids, pad):
-            if not prefetch.pending:
-                prefetch.submit(ids, pad)
-            prefetch.take(g_ids, g_labels, g_pad)
-
-        side = torch.cuda.Stream()
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
-            for _ in range(3):
-                mask_into_static(ids_d, pad_d)
-                opt.zero_grad(set_to_none=True)
-                body()
-                if distributed:
-                    tail()
-        torch.cuda.current_stream().wait_stream(side)
-        mask_into_static(ids_d, pad_d)
-        opt.zero_grad(set_to_none=True)
-        graph = torch.cuda.CUDAGraph()
-        captured0 = N.lib().pio_launch_count()
-        with torch.cuda.graph(graph):
-            g_loss = body()
-        graph_launches = N.lib().pio_launch_count() - captured0  # kernels of this library inside one replay
-
-        def step(ids, pad):  # noqa: F811
-            mask_into_static(ids, pad)  # consume the prefetched batch
-            graph.replay()
-            if distributed:
-                tail()
-            prefetch.submit(ids, pad)  # next step's batch: H2D (when ids/pad are host tensors) + masking, overlapped
-            return g_loss
+        gstep = perceiver.GraphedMLMStep(model, opt, ids_d, pad_d, overlap_allreduce=not args.flat_allreduce_after,
+                                         bucket_bytes=args.bucket_mb << 20)
+        graph, graph_launches, g_labels = gstep.graph, gstep.launches_per_replay, gstep.labels
+        if distributed:
+            grad_exchange = (f"overlapped: {len(gstep.fg.views)} buckets of ~{args.bucket_mb} MB all-reduced (NCCL avg) on a side "
+                             "stream from inside the captured backward pass, in completion order; AdamW in the same graph"
+                             if gstep.fg is not None else "flat NCCL all-reduce(avg) after the captured forward+backward graph")
+        step = gstep  # noqa: F811
 
     def sync_all():
         if distributed:
@@ -629,8 +587,7 @@ def gpu_arm(args):
                        "optimizer": ("perceiver.FusedAdamW (pio_adamw_step, one launch) lr 3e-3" if (mode == 1 and not args.torch_optimizer)
                                      else "torch.optim.AdamW(fused) lr 3e-3"),
                        "grad_exchange": ("none" if not distributed else
-                                         ("flat NCCL all-reduce(avg) after the captured forward+backward graph" if graph is not None
-                                          else "torch DDP buckets overlapped with backward")),
+                                         (grad_exchange if graph is not None else "torch DDP buckets overlapped with backward")),
                        "cuda_graph": bool(graph is not None), "fused_vocab_ce": bool(fused_loss),
                        "masking_prefetch": bool(graph is not None),
                        "l2": "per-step working set (activations + saved state of 22 layers at batch 64, 45 MB of fp32 "
@@ -685,6 +642,9 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="do not capture the step into a CUDA graph")
     ap.add_argument("--profile-only", action="store_true", help="timed steps only (for ncu launch lists)")
     ap.add_argument("--torch-optimizer", action="store_true", help="torch.optim.AdamW(fused=True) instead of perceiver.FusedAdamW")
+    ap.add_argument("--flat-allreduce-after", action="store_true",
+                    help="N > 1: previous scheme, one flat all-reduce after the captured graph instead of overlapped buckets")
+    ap.add_argument("--bucket-mb", type=int, default=8, help="gradient bucket size of the overlapped all-reduce")
     ap.add_argument("--timeline", default=None, help="with --profile-only: CSV of (stream, start_us, dur_us, kernel) of 2 more steps")
     ap.add_argument("--mode", default=os.environ.get("PIO_MODE", "bf16"), choices=["fp32", "bf16"])
     args = ap.parse_args()

@@ -234,6 +234,12 @@ typedef struct {
 int pio_flat_copy_f32(float* flat, const pio_flat_tensor* tensors, const pio_adamw_chunk* chunks, int n_chunks, int to_flat,
                       float scale, pio_stream_t stream);
 
+/* In-place a *= *scale, b *= *scale, c *= *scale with the scale read from DEVICE memory; a scale of exactly 1 makes
+ * the launch a no-op.  Backward of the fused linear + cross-entropy operator: its gradients are formed in the
+ * forward for d(loss) = 1 and only need the incoming d(loss) applied (reference: autograd through
+ * nn.CrossEntropyLoss, lightning.py:225-226).  Null pointers are allowed with a count of 0. */
+int pio_scale3_f32(float* a, int64_t na, float* b, int64_t nb, float* c, int64_t nc, const float* scale, pio_stream_t stream);
+
 /* Attention core of nn.MultiheadAttention as called at model.py:74 (dropout 0):
  * S = (q dh^-1/2) k^T, padded keys -> -inf, P = softmax(S), O = P v.  Flash-style: P is never
  * stored; lse (batch,heads,n) = logsumexp of the scaled scores, saved for the backward, which

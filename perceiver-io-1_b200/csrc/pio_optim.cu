@@ -129,11 +129,37 @@ __global__ void __launch_bounds__(256) flat_copy_kernel(float* __restrict__ flat
     }
 }
 
+// a[i] *= *scale over up to three arrays; every CTA leaves at once when the scale is exactly 1 (what
+// loss.backward() hands a loss: the gradients formed in the forward are then already final)
+__global__ void __launch_bounds__(256) scale3_kernel(float* __restrict__ a, int64_t na, float* __restrict__ b, int64_t nb,
+                                                     float* __restrict__ c, int64_t nc, const float* __restrict__ scale) {
+    pdl_trigger();
+    pdl_wait();
+    const float s = __ldg(scale);
+    if (s == 1.0f) return;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (int64_t i = i0; i < na; i += stride) a[i] *= s;
+    for (int64_t i = i0; i < nb; i += stride) b[i] *= s;
+    for (int64_t i = i0; i < nc; i += stride) c[i] *= s;
+}
+
 }  // namespace pio
 
 using namespace pio;
 
 extern "C" {
+
+int pio_scale3_f32(float* a, int64_t na, float* b, int64_t nb, float* c, int64_t nc, const float* scale, pio_stream_t stream) {
+    PIO_CHECK_ARG(scale && na >= 0 && nb >= 0 && nc >= 0 && (a || na == 0) && (b || nb == 0) && (c || nc == 0),
+                  "pio_scale3_f32: bad arguments");
+    const int64_t most = std::max(na, std::max(nb, nc));
+    if (most == 0) return PIO_OK;
+    const int blocks = (int)std::min<int64_t>(cdiv(most, 256 * 8), (int64_t)num_sms() * 8);
+    PIO_CUDA(launch_pdl(scale3_kernel, dim3(std::max(blocks, 1)), dim3(256), 0, (cudaStream_t)stream, a, na, b, nb, c, nc, scale));
+    count_launch();
+    return PIO_OK;
+}
 
 int pio_adamw_step(const pio_adamw_tensor* tensors, const pio_adamw_chunk* chunks, int n_chunks, const float* hyper,
                    pio_stream_t stream) {

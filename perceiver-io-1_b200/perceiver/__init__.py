@@ -11,6 +11,7 @@ from .functional import cross_entropy, get_compute_mode, linear_cross_entropy, s
 from .model import (CrossAttention, MultiHeadAttention, PerceiverDecoder, PerceiverEncoder, PerceiverIO, PerceiverMLM,
                     Residual, SelfAttention, TextMasking, cross_attention_layer, mlp, self_attention_block,
                     self_attention_layer)
+from .distributed import FlatGradients, average_gradients
 from .optim import FusedAdamW
-from .pipeline import MaskingPrefetcher
+from .pipeline import GraphedMLMStep, MaskingPrefetcher
 from .utils import Sequential, freeze, predict_masked_samples

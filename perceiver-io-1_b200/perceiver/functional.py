@@ -5,6 +5,7 @@ autograd graph.  Saved-for-backward state is an opaque byte buffer whose layout 
 library knows (pio_*_saved_bytes).
 """
 import ctypes
+import threading
 import weakref
 from ctypes import byref
 
@@ -69,6 +70,23 @@ def invalidate_weight_cache(module=None):
         for p in module.parameters():
             if hasattr(p, "_pio_w16"):
                 del p._pio_w16
+
+
+def refresh_weight_shadows(module):
+    """Re-cast, IN PLACE, every bf16 weight shadow the last training forward of ``module`` used (one launch).  For
+    code that writes trainable parameters behind the optimizer's back (``param.copy_`` / ``load_state_dict``) while
+    a captured CUDA graph holds the shadow addresses: the graph does not re-cast them itself when the optimizer is
+    `perceiver.FusedAdamW`, which writes the shadows together with the parameters."""
+    tab = _TABLES.get(module)
+    if tab is None:
+        return False
+    _, table, weights = tab
+    N.check(N.lib().pio_cast_bf16_multi(table.data_ptr(), len(weights), N.stream_ptr(table.device)), "pio_cast_bf16_multi")
+    for w in weights:
+        hit = getattr(w, "_pio_w16", None)
+        if hit is not None:
+            w._pio_w16 = (w._version, w.data_ptr(), hit[2], hit[3], hit[4])
+    return True
 
 
 # bf16 weight shadows.  A shadow is valid for ONE training forward: optimizers such as
@@ -165,7 +183,7 @@ class shadow_scope:
         _SH["depth"] += 1
         if _SH["depth"] == 1:
             _SH["grad"] = torch.is_grad_enabled()
-            _PENDING.clear()  # (a backward pass that died half-way never ran its clean-up callback)
+            _forget_pending()  # (a backward pass that died half-way never ran its clean-up callback)
         if _SH["depth"] == 1 and _MODE["mode"] == N.MODE_BF16 and _SH["grad"]:
             _SH["epoch"] += 1
             _SH["seen"] = {}
@@ -189,13 +207,90 @@ def _mat(w, mode):
 
 
 # Parameters applied more than once in a forward (the shared `layer_n` of PerceiverEncoder, reference
-# model.py:186-187) get one gradient buffer per backward pass: the first backward that reaches such a parameter
-# allocates it and hands it to autograd, later ones add into the same memory (the kernels accumulate with
-# atomics anyway) and report None — so autograd has nothing left to sum, which was one small add kernel per shared
-# tensor per step.  Keyed by the parameter's storage address; forgotten when the backward pass ends.
-_PENDING = {}  # parameter storage -> device address of its gradient buffer (an address only: a tensor reference
-#                here would stop autograd from adopting the buffer as .grad without a copy)
-_REUSED = set()
+# model.py:186-187; the packed in-projection that KVProjectFn and CrossAttendFn both read) get one gradient buffer
+# per backward pass: the first backward that reaches such a parameter allocates it and hands it to autograd, later
+# ones add into the same memory (the kernels accumulate with atomics anyway) and report None — so autograd has
+# nothing left to sum, which was one small add kernel per shared tensor per step.
+#   * Only parameters whose gradient autograd actually asked for (ctx.needs_input_grad) are registered: a frozen
+#     parameter's buffer is dropped by autograd as soon as the backward returns, and a later operator must not be
+#     handed its address.  (The kernels still need somewhere to write, so a frozen parameter gets scratch space in
+#     the slab; its gradient is computed and discarded.)
+#   * The slab every buffer of a call is carved from is kept alive until the end of the backward pass
+#     (_PASS_SLABS, cleared by the engine's end-of-pass callback), so a registered address can never point at
+#     memory the caching allocator has handed to someone else.  Holding the slab does not stop autograd from
+#     adopting the per-parameter views as .grad without a copy (that test looks at the view's own reference count).
+#   * Known limit, by construction of "report None": a parameter shared between one of these operators and a
+#     foreign torch op that ALSO produces a gradient for it in the same pass relies on autograd's own summation;
+#     the Perceiver models here never do that.
+# The tables are shared by all threads under a lock (autograd runs a device's backward on a worker thread, and the
+# end-of-pass callback may run on another one); keys carry the device, and a pass whose entries were cleared early by
+# another device's callback just allocates fresh buffers again, which autograd then sums the ordinary way.
+class _PassState:
+    def __init__(self):
+        self.lock = threading.RLock()
+        self.pending = {}  # (data_ptr, numel, device) of a parameter -> device address of its gradient buffer
+        self.slabs = []    # keeps the memory behind those addresses alive for the pass
+        self._tls = threading.local()
+
+    @property
+    def reused(self):  # between _grads_like and _out of ONE backward call: same thread
+        r = getattr(self._tls, "reused", None)
+        if r is None:
+            r = self._tls.reused = set()
+        return r
+
+
+_PASS = _PassState()
+
+# Flat gradient destinations (perceiver.distributed.FlatGradients): a parameter registered here has a permanent,
+# pre-zeroed home for its gradient inside one flat buffer (p.grad is a view of it).  The backward operators add
+# straight into that memory and report None, so there is no per-operator slab to zero, nothing for autograd to
+# accumulate, nothing to flatten before the data-parallel all-reduce — and the owner is told after every operator
+# which parameters were written, which is how it knows the moment a bucket is complete and its all-reduce can start
+# while the rest of the backward pass is still running.
+_DST = {}          # (data_ptr, numel, device) of a parameter -> (device address of its gradient, owner)
+_TOUCH_LOG = None  # FlatGradients' profiling pass: parameter keys in the order the backward pass wrote them
+
+
+def _pkey(p):
+    return (p.data_ptr(), p.numel(), p.device)
+
+
+def _touched_list():
+    t = getattr(_PASS._tls, "touched", None)
+    if t is None:
+        t = _PASS._tls.touched = []
+    return t
+
+
+def _direct_target(p):
+    """Backward of an operator that writes a parameter gradient itself: the address of the parameter's registered
+    destination (the caller then writes / adds there and returns None for it), or None.  Counts as this pass's
+    write of the parameter either way (profiling), so call it exactly once per gradient produced."""
+    k = _pkey(p)
+    if _TOUCH_LOG is not None:
+        _TOUCH_LOG.append(k)
+    hit = _DST.get(k)
+    if hit is None:
+        return None
+    _touched_list().append((hit[1], k))
+    return hit[0]
+
+
+def _dst_address(p):
+    """the registered destination of p's gradient, or None — without counting a write (see LinearCrossEntropyFn)"""
+    hit = _DST.get(_pkey(p))
+    return None if hit is None else hit[0]
+
+
+def _after_op():
+    """end of a backward operator: tell the owners which destinations are now written"""
+    t = _touched_list()
+    if t:
+        done = list(t)
+        t.clear()
+        for owner, k in done:
+            owner._written(k)
 
 
 class _Alias:
@@ -212,55 +307,91 @@ class _Alias:
 
 
 def _forget_pending():
-    _PENDING.clear()
+    with _PASS.lock:
+        _PASS.pending.clear()
+        _PASS.slabs.clear()
 
 
-def _grads_like(params, mode):
+def _grads_like(params, mode, needs=None):
     """Gradient buffers shaped like ``params`` (None stays None) and the `accumulate` flag to pass.
     fp32 mode: uninitialised buffers, overwritten (0).  bf16 mode: views into one zero-filled slab so the
     kernels can add into them with atomics (2) and skip their reduction passes; a parameter that already got a
-    buffer earlier in this backward pass gets that one again (return the result through `_out`)."""
+    buffer earlier in this backward pass gets that one again (return the result through `_out`).
+    ``needs[i]`` (ctx.needs_input_grad of the parameter) False: scratch that is neither registered nor returned."""
+    if needs is None:
+        needs = [True] * len(params)
     if mode == N.MODE_FP32:
         return [torch.empty_like(p) if p is not None else None for p in params], 0
-    _REUSED.clear()
-    keys = [None if p is None else (p.data_ptr(), p.numel(), p.device) for p in params]
-    fresh = [p for p, k in zip(params, keys) if p is not None and k not in _PENDING]
+    st = _PASS
+    st.reused.clear()
+    with st.lock:
+        return _grads_like_locked(st, params, needs)
+
+
+def _grads_like_locked(st, params, needs):
+    keys = [None if p is None else _pkey(p) for p in params]
+    kinds = []  # per parameter: None | "dst" | "pending" | "fresh"
+    for p, k, need in zip(params, keys, needs):
+        if p is None:
+            kinds.append(None)
+        elif need and k in _DST:
+            kinds.append("dst")
+        elif k in st.pending:
+            kinds.append("pending")
+        else:
+            kinds.append("fresh")
+    fresh = [p for p, kind in zip(params, kinds) if kind == "fresh"]
     offs, total = [], 0
     for p in fresh:
         offs.append(total)
         total += (p.numel() + 3) // 4 * 4
     slab = torch.zeros(total, dtype=torch.float32, device=fresh[0].device) if fresh else None
-    share = bool(_PENDING)  # a non-empty table means this pass already registered its end-of-pass callback
+    share = bool(st.slabs)  # a non-empty list means this pass already registered its end-of-pass callback
     if fresh and not share:
         try:
             torch.autograd.Variable._execution_engine.queue_callback(_forget_pending)
             share = True
         except RuntimeError:  # not inside a backward pass (direct call): nothing to share across calls
             share = False
+    if share and slab is not None:
+        st.slabs.append(slab)
     it = iter(offs)
     out = []
-    for p, k in zip(params, keys):
-        if p is None:
+    touched = _touched_list()
+    for p, k, need, kind in zip(params, keys, needs, kinds):
+        if kind is None:
             out.append(None)
-        elif k in _PENDING:
-            g = _Alias(_PENDING[k])
-            _REUSED.add(id(g))
-            out.append(g)
+            continue
+        if need and _TOUCH_LOG is not None:
+            _TOUCH_LOG.append(k)
+        if kind == "dst":
+            addr, owner = _DST[k]
+            g = _Alias(addr)
+            st.reused.add(id(g))
+            touched.append((owner, k))
+        elif kind == "pending":
+            g = _Alias(st.pending[k])
+            st.reused.add(id(g))
         else:
             o = next(it)
             g = slab[o:o + p.numel()].view(p.shape)
-            if share:
-                _PENDING[k] = g.data_ptr()
-            out.append(g)
+            if not need:
+                st.reused.add(id(g))  # scratch: reported as None
+            elif share:
+                st.pending[k] = g.data_ptr()
+        out.append(g)
     return out, 2
 
 
 def _out(*grads):
-    """what a backward returns: buffers autograd already holds (see _grads_like) are reported as None"""
-    if not _REUSED:
+    """what a backward returns: buffers autograd already holds, and scratch of frozen parameters (see _grads_like),
+    are reported as None"""
+    reused = _PASS.reused
+    if not reused:
         return grads
-    res = tuple(None if (g is not None and id(g) in _REUSED) else g for g in grads)
-    _REUSED.clear()
+    res = tuple(None if (g is not None and id(g) in reused) else g for g in grads)
+    reused.clear()
+    _after_op()
     return res
 
 
@@ -319,21 +450,30 @@ class TextEmbedFn(torch.autograd.Function):
         out = torch.empty(b, l, c, dtype=torch.float32, device=emb.device)
         N.check(N.lib().pio_text_embed_fwd(ids.data_ptr(), emb.data_ptr(), pos.data_ptr(), out.data_ptr(), b, l, c, vocab,
                                            float(scale), N.stream_ptr(emb.device)), "pio_text_embed_fwd")
-        ctx.save_for_backward(ids)
+        ctx.save_for_backward(ids, emb, pos)
         ctx.meta = (vocab, c, pos.shape[0], float(scale))
         return out
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dout):
-        (ids,) = ctx.saved_tensors
+        ids, emb, pos = ctx.saved_tensors
         vocab, c, max_len, scale = ctx.meta
         dout = _c(dout)
         b, l = ids.shape
-        demb = torch.zeros(vocab, c, dtype=torch.float32, device=dout.device) if ctx.needs_input_grad[1] else None
-        dpos = torch.zeros(max_len, c, dtype=torch.float32, device=dout.device) if ctx.needs_input_grad[2] else None
-        N.check(N.lib().pio_text_embed_bwd(ids.data_ptr(), dout.data_ptr(), N.ptr(demb), N.ptr(dpos), b, l, c, vocab, scale,
+        # a registered flat destination (FlatGradients) is zero at this point and takes the scatter-add directly
+        a_emb = _direct_target(emb) if ctx.needs_input_grad[1] else None
+        a_pos = _direct_target(pos) if ctx.needs_input_grad[2] else None
+        demb = dpos = None
+        if ctx.needs_input_grad[1] and a_emb is None:
+            demb = torch.zeros(vocab, c, dtype=torch.float32, device=dout.device)
+            a_emb = demb.data_ptr()
+        if ctx.needs_input_grad[2] and a_pos is None:
+            dpos = torch.zeros(max_len, c, dtype=torch.float32, device=dout.device)
+            a_pos = dpos.data_ptr()
+        N.check(N.lib().pio_text_embed_bwd(ids.data_ptr(), dout.data_ptr(), a_emb, a_pos, b, l, c, vocab, scale,
                                            N.stream_ptr(dout.device)), "pio_text_embed_bwd")
+        _after_op()
         return None, demb, dpos, None
 
 
@@ -413,7 +553,7 @@ class MlpFn(torch.autograd.Function):
         rows, c, residual, mode, drop = ctx.meta
         dy = _c(dy)
         L = N.lib()
-        grads, accf = _grads_like(params, mode)
+        grads, accf = _grads_like(params, mode, ctx.needs_input_grad[1:7])
         dx = torch.empty_like(x)
         ws = N.workspace(L.pio_mlp_ws_bytes(rows, c, mode), x.device)
         w = ctx.wstruct
@@ -470,7 +610,8 @@ class KVProjectFn(torch.autograd.Function):
             dwv = torch.empty_like(w_v) if w_v is not None else None
             accf = 0
         else:
-            (dln_w, dln_b, dbias, dwp, dwk, dwv), accf = _grads_like((ln_w, ln_b, bias, w_packed, w_k, w_v), mode)
+            (dln_w, dln_b, dbias, dwp, dwk, dwv), accf = _grads_like((ln_w, ln_b, bias, w_packed, w_k, w_v), mode,
+                                                                    ctx.needs_input_grad[1:7])
         dx = torch.empty_like(x_kv) if ctx.needs_input_grad[0] else None
         _, gwk, gwv, _, gbk, gbv = _mha_ptrs(dwp, None, dwk, dwv, dbias, e)
         w = ctx.wstruct
@@ -532,7 +673,8 @@ class CrossAttendFn(torch.autograd.Function):
             dwo, dbo = torch.empty_like(wo), torch.empty_like(bo)
             accf = 0
         else:
-            (dln_w, dln_b, dbias, dwp, dwq, dwo, dbo), accf = _grads_like((ln_w, ln_b, bias, w_packed, w_q, wo, bo), mode)
+            (dln_w, dln_b, dbias, dwp, dwq, dwo, dbo), accf = _grads_like((ln_w, ln_b, bias, w_packed, w_q, wo, bo), mode,
+                                                                         ctx.needs_input_grad[3:10])
         dx = torch.empty_like(x_q)
         dkv = torch.empty_like(kv)
         gwq, _, _, gbq, _, _ = _mha_ptrs(dwp, dwq, None, None, dbias, e)
@@ -591,7 +733,7 @@ class SelfAttnFn(torch.autograd.Function):
         b, n, c, heads, residual, mode, drop = ctx.meta
         dy = _c(dy)
         L = N.lib()
-        grads, accf = _grads_like(params, mode)
+        grads, accf = _grads_like(params, mode, ctx.needs_input_grad[1:7])
         dx = torch.empty_like(x)
         w = ctx.wstruct
         gfields = _sa_struct(*grads, c)
@@ -658,7 +800,7 @@ class LatentBlockFn(torch.autograd.Function):
         layers, b, n, c, heads, mode, drop = ctx.meta
         dy = _c(dy)
         L = N.lib()
-        grads, accf = _grads_like(params, mode)
+        grads, accf = _grads_like(params, mode, ctx.needs_input_grad[4:])
         dx = torch.empty_like(x)
         attn, mlp = ctx.wstructs
         attn_g, mlp_g, _ = LatentBlockFn._structs(grads, layers, c)
@@ -687,6 +829,7 @@ class LinearFn(torch.autograd.Function):
         N.check(L.pio_linear_fwd(x.data_ptr(), wm.data_ptr(), b.data_ptr(), y.data_ptr(), rows, c_in, c_out, mode,
                                  ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_linear_fwd")
         ctx.save_for_backward(x, w)
+        ctx.bias = b
         ctx.meta = (rows, c_in, c_out, mode)
         return y
 
@@ -698,11 +841,19 @@ class LinearFn(torch.autograd.Function):
         dy = _c(dy)
         L = N.lib()
         dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
-        dw = torch.empty_like(w)
-        db = torch.empty(c_out, dtype=torch.float32, device=x.device)
+        a_w = _direct_target(w)  # (the operator overwrites: a parameter with a flat destination is used once per pass)
+        a_b = _direct_target(ctx.bias)
+        dw = db = None
+        if a_w is None:
+            dw = torch.empty_like(w)
+            a_w = dw.data_ptr()
+        if a_b is None:
+            db = torch.empty(c_out, dtype=torch.float32, device=x.device)
+            a_b = db.data_ptr()
         ws = N.workspace(L.pio_linear_ws_bytes(rows, c_in, c_out, mode), x.device)
-        N.check(L.pio_linear_bwd(dy.data_ptr(), x.data_ptr(), ctx.wm.data_ptr(), N.ptr(dx), dw.data_ptr(), db.data_ptr(), 0, rows,
+        N.check(L.pio_linear_bwd(dy.data_ptr(), x.data_ptr(), ctx.wm.data_ptr(), N.ptr(dx), a_w, a_b, 0, rows,
                                  c_in, c_out, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)), "pio_linear_bwd")
+        _after_op()
         return dx, dw, db
 
 
@@ -744,7 +895,9 @@ class CrossEntropyFn(torch.autograd.Function):
 class LinearCrossEntropyFn(torch.autograd.Function):
     """Output-adapter linear + cross-entropy in one call (bf16 mode): the logits are produced and
     consumed chunk by chunk inside L2, and the gradients of x, W and b are formed in the same pass
-    (for d(loss) = 1; backward only scales them).  SURVEY.md section 8f row 1."""
+    (for d(loss) = 1; backward applies the incoming d(loss) with one launch that is a no-op when it is 1, which is
+    what loss.backward() passes).  SURVEY.md section 8f row 1.  With flat gradient destinations registered
+    (perceiver.FlatGradients) dW and db are written straight into them by the forward."""
 
     @staticmethod
     def forward(ctx, x, w, b, labels, ignore_index):
@@ -758,20 +911,35 @@ class LinearCrossEntropyFn(torch.autograd.Function):
         L = N.lib()
         dev = x.device
         out3 = torch.empty(3, dtype=torch.float32, device=dev)
-        dx, dw, db = torch.empty_like(x), torch.empty_like(w), torch.empty_like(b)
+        dx = torch.empty_like(x)
+        a_w, a_b = _dst_address(w), _dst_address(b)
+        dw = torch.empty_like(w) if a_w is None else None
+        db = torch.empty_like(b) if a_b is None else None
         ws = N.workspace(L.pio_linear_ce_ws_bytes(rows, c_in, classes, mode), dev)
         wm = _mat(w, mode)
         N.check(L.pio_linear_ce_fwd_bwd(x.data_ptr(), wm.data_ptr(), b.data_ptr(), labels.data_ptr(), out3.data_ptr(),
-                                        dx.data_ptr(), dw.data_ptr(), db.data_ptr(), rows, c_in, classes, int(ignore_index), mode,
+                                        dx.data_ptr(), a_w if dw is None else dw.data_ptr(), a_b if db is None else db.data_ptr(),
+                                        rows, c_in, classes, int(ignore_index), mode,
                                         ws.data_ptr(), ws.numel(), N.stream_ptr(dev)), "pio_linear_ce_fwd_bwd")
-        ctx.save_for_backward(dx, dw, db)
+        ctx.save_for_backward(dx, dw, db, w, b)
+        ctx.sizes = (w.numel(), b.numel())
         return out3[0].clone()
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dloss):
-        dx, dw, db = ctx.saved_tensors
-        return dx * dloss, dw * dloss, db * dloss, None, None
+        dx, dw, db, w, b = ctx.saved_tensors
+        nw, nb = ctx.sizes
+        dloss = _c(dloss.reshape(1).to(torch.float32))
+        t_w, t_b = _direct_target(w), _direct_target(b)
+        if (t_w is None) != (dw is not None) or (t_b is None) != (db is not None):
+            raise RuntimeError("LinearCrossEntropyFn: flat gradient destinations changed between forward and backward")
+        a_w = t_w if dw is None else dw.data_ptr()
+        a_b = t_b if db is None else db.data_ptr()
+        N.check(N.lib().pio_scale3_f32(dx.data_ptr(), dx.numel(), a_w, nw, a_b, nb, dloss.data_ptr(), N.stream_ptr(dx.device)),
+                "pio_scale3_f32")
+        _after_op()
+        return dx, dw, db, None, None
 
 
 def linear_cross_entropy(x, weight, bias, labels, ignore_index=-100):

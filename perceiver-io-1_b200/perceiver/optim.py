@@ -52,8 +52,7 @@ class FusedAdamW(torch.optim.Optimizer):
             hyper = torch.zeros(6, dtype=torch.float32, device=dev)
             hyper[5] = steps
             plan = dict(ident=ident, chunks=chunk_t, n_chunks=len(chunks), hyper=hyper, hyper_host=None, key=None,
-                        table=torch.empty(len(params), 6, dtype=torch.int64, device=dev),
-                        staging=torch.empty(len(params), 6, dtype=torch.int64).pin_memory())
+                        table=torch.empty(len(params), 6, dtype=torch.int64, device=dev))
             for p in params:
                 self.state[p]["step"] = hyper[5:6]  # one device counter per group, shared by its tensors
             self._plans[gi] = plan
@@ -72,17 +71,41 @@ class FusedAdamW(torch.optim.Optimizer):
                 g = p.grad
                 if g.dtype != torch.float32 or not g.is_contiguous() or g.device != dev:
                     raise TypeError("FusedAdamW: gradients must be contiguous fp32 tensors on the parameters' device")
-            plan["staging"].copy_(torch.from_numpy(np.asarray(rows, dtype=np.int64)))
-            plan["table"].copy_(plan["staging"], non_blocking=True)
+            if torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("FusedAdamW: parameter / gradient / shadow addresses changed while the stream is being "
+                                   "captured; run one eager step with the final buffers first")
+            # a plain synchronous copy from pageable memory: the host array may be rewritten as soon as this returns
+            # (a pinned staging buffer + non_blocking copy could be overwritten by the next step's table while the
+            # previous copy was still in flight — eager training hands out new gradient buffers every step)
+            plan["table"].copy_(torch.from_numpy(np.asarray(rows, dtype=np.int64)))
             plan["key"] = key
             plan["shadowed"] = [p for p, r in zip(params, rows) if r[4] != 0]
         # hyper-parameters (the step counter stays on the device)
         hp = (float(group["lr"]), float(group["betas"][0]), float(group["betas"][1]), float(group["eps"]),
               float(group["weight_decay"]))
         if hp != plan["hyper_host"]:
-            plan["hyper"][:5].copy_(torch.tensor(hp, dtype=torch.float32).pin_memory(), non_blocking=True)
+            plan["hyper"][:5].copy_(torch.tensor(hp, dtype=torch.float32))
             plan["hyper_host"] = hp
         return plan
+
+    def sync_hyper(self):
+        """Mirror ``param_groups`` (lr, betas, eps, weight_decay — e.g. after ``scheduler.step()``) into the device
+        buffers the kernel reads.  ``step()`` does this itself; a step REPLAYED from a CUDA graph does not run any
+        Python, so call this before ``graph.replay()`` whenever a scheduler changed the values."""
+        for gi, group in enumerate(self.param_groups):
+            plan = self._plans.get(gi)
+            if plan is None:
+                continue
+            hp = (float(group["lr"]), float(group["betas"][0]), float(group["betas"][1]), float(group["eps"]),
+                  float(group["weight_decay"]))
+            if hp != plan["hyper_host"]:
+                plan["hyper"][:5].copy_(torch.tensor(hp, dtype=torch.float32))
+                plan["hyper_host"] = hp
+
+    def load_state_dict(self, state_dict):
+        """resume: the launch plans (and their device step counters) are rebuilt from the loaded state"""
+        super().load_state_dict(state_dict)
+        self._plans = {}
 
     @torch.no_grad()
     def step(self, closure=None):

@@ -70,3 +70,140 @@ def test_two_rank_gloo_gradient_mean_equals_full_batch_gradient(tmp_path):
     ((lin(data) - target) ** 2).mean().backward()
     ref = torch.cat([p.grad.reshape(-1) for p in lin.parameters()] + [torch.zeros(4)])
     torch.testing.assert_close(got[0]["flat"], ref, rtol=1e-5, atol=1e-6)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# FlatGradients: gradients written in place into one flat buffer, bucketed all-reduce started from inside the
+# backward pass.  The CUDA operators are replaced by a CPU stand-in that asks for its gradient buffers exactly the
+# way they do (functional._grads_like / _out) and adds into the address it is given.
+# ---------------------------------------------------------------------------------------------------------------
+import ctypes  # noqa: E402
+
+import numpy as np  # noqa: E402
+
+from perceiver import _native as N  # noqa: E402
+from perceiver import functional as F  # noqa: E402
+from perceiver.distributed import FlatGradients  # noqa: E402
+
+
+def _add_at(buf, value):
+    """buf: a tensor or functional._Alias (an address): buf += value, like a kernel with accumulate = 2"""
+    if isinstance(buf, torch.Tensor):
+        buf.add_(value)
+    else:
+        n = value.numel()
+        arr = np.ctypeslib.as_array((ctypes.c_float * n).from_address(buf.data_ptr()))
+        arr += value.detach().reshape(-1).numpy()
+
+
+class _FakeLinear(torch.autograd.Function):
+    """y = x w^T with the gradient-buffer protocol of the fused operators"""
+
+    @staticmethod
+    def forward(ctx, x, w):
+        ctx.save_for_backward(x, w)
+        return x @ w.t()
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        (gw,), acc = F._grads_like([w], N.MODE_BF16, ctx.needs_input_grad[1:2])
+        assert acc == 2
+        _add_at(gw, dy.t() @ x)
+        return F._out(dy @ w, gw)
+
+
+def _fg_model():
+    torch.manual_seed(0)
+    w1 = torch.nn.Parameter(torch.randn(5, 6) * 0.3)   # used twice (like the shared layer_n)
+    w2 = torch.nn.Parameter(torch.randn(4, 5) * 0.3)
+    w3 = torch.nn.Parameter(torch.randn(3, 4) * 0.3)
+    foreign = torch.nn.Parameter(torch.randn(3) * 0.1)  # gradient from an ordinary torch op
+    unused = torch.nn.Parameter(torch.zeros(7))
+    return [w1, w2, w3, foreign, unused]
+
+
+def _fg_loss(params, x, y):
+    w1, w2, w3, foreign, _ = params
+    h = _FakeLinear.apply(x, w1)
+    h = torch.tanh(_FakeLinear.apply(h @ torch.ones(5, 6), w1))
+    h = torch.tanh(_FakeLinear.apply(h, w2))
+    out = _FakeLinear.apply(h, w3) + foreign
+    return ((out - y) ** 2).mean()
+
+
+def _fg_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    F.set_compute_mode("bf16")
+    params = _fg_model()
+    torch.manual_seed(1)
+    data, target = torch.randn(8, 6), torch.randn(8, 3)
+    x, y = shard_batch(data, rank, world), shard_batch(target, rank, world)
+    fg = FlatGradients(params, bucket_bytes=64)  # tiny buckets: several of them, cut in completion order
+    with fg.profile():
+        _fg_loss(params, x, y).backward()
+    fired_inside = []
+    orig = fg._reduce
+    fg._reduce = lambda b: (fired_inside.append(b), orig(b))[1]
+    results = []
+    for step in range(2):  # twice: the per-step state resets
+        fg.step_begin()
+        _fg_loss(params, x, y).backward()
+        n_in_backward = len(fired_inside)
+        fg.step_end()
+        results.append(torch.cat([p.grad.reshape(-1) for p in params]).clone())
+        fired_inside.clear()
+    torch.save({"g0": results[0], "g1": results[1], "buckets": len(fg.views), "fired_in_backward": n_in_backward,
+                "views": all(p.grad.data_ptr() >= fg.flat.data_ptr() for p in params)},
+               os.path.join(out_dir, f"fg{rank}.pt"))
+    fg.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_flat_gradients_two_rank_gloo_bucketed_mean_equals_full_batch_gradient(tmp_path):
+    world = 2
+    mp.spawn(_fg_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    got = [torch.load(tmp_path / f"fg{r}.pt") for r in range(world)]
+    assert torch.equal(got[0]["g0"], got[1]["g0"]) and torch.equal(got[0]["g0"], got[0]["g1"])
+    assert got[0]["views"] and got[0]["buckets"] >= 3
+    assert got[0]["fired_in_backward"] >= 2  # buckets went out while the backward pass was still running
+    # reference: one process, whole batch, plain autograd
+    params = _fg_model()
+    torch.manual_seed(1)
+    data, target = torch.randn(8, 6), torch.randn(8, 3)
+    w1, w2, w3, foreign, unused = params
+    h = data @ w1.t()
+    h = torch.tanh((h @ torch.ones(5, 6)) @ w1.t())
+    h = torch.tanh(h @ w2.t())
+    (((h @ w3.t() + foreign) - target) ** 2).mean().backward()
+    ref = torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1) for p in params])
+    torch.testing.assert_close(got[0]["g0"], ref, rtol=1e-5, atol=1e-6)
+
+
+def test_flat_gradients_single_process_matches_autograd():
+    F.set_compute_mode("bf16")
+    try:
+        params = _fg_model()
+        torch.manual_seed(2)
+        x, y = torch.randn(4, 6), torch.randn(4, 3)
+        fg = FlatGradients(params, bucket_bytes=1 << 20)
+        with fg.profile():
+            _fg_loss(params, x, y).backward()
+        fg.step_begin()
+        _fg_loss(params, x, y).backward()
+        fg.step_end()
+        got = [p.grad.clone() for p in params]
+        fg.close()
+        assert not F._DST
+        for p in params:
+            p.grad = None
+        _fg_loss(params, x, y).backward()
+        for g, p in zip(got, params):
+            ref = p.grad if p.grad is not None else torch.zeros_like(p)
+            torch.testing.assert_close(g, ref, rtol=1e-5, atol=1e-6)
+    finally:
+        F.set_compute_mode("fp32")

@@ -29,10 +29,10 @@ def fake(monkeypatch):
     monkeypatch.setattr(N, "stream_ptr", lambda device=None: 0)
     monkeypatch.setattr(torch.cuda, "is_current_stream_capturing", lambda: False)
     F.set_compute_mode("bf16")
-    F._PENDING.clear()
+    F._forget_pending()
     yield rec
     F.set_compute_mode("fp32")
-    F._PENDING.clear()
+    F._forget_pending()
 
 
 class _Toy(torch.nn.Module):
@@ -124,7 +124,38 @@ def test_second_use_of_a_parameter_adds_into_the_first_buffer(fake):
     assert issubclass(t1, torch.Tensor) and t2 is F._Alias
     assert p2 == p1                                         # same memory, handed to autograd only once
     assert w.grad is not None and w.grad.data_ptr() == p1   # adopted without a copy or an add
-    assert F._PENDING == {}                                 # forgotten when the backward pass ended
+    assert F._PASS.pending == {} and F._PASS.slabs == []                                 # forgotten when the backward pass ended
+
+
+class _Frozen(torch.autograd.Function):
+    """an operator whose parameter is frozen while its input still needs a gradient"""
+    seen = []
+
+    @staticmethod
+    def forward(ctx, x, w):
+        ctx.save_for_backward(w)
+        return x * 1.0
+
+    @staticmethod
+    def backward(ctx, dy):
+        (w,) = ctx.saved_tensors
+        (g,), acc = F._grads_like([w], N.MODE_BF16, ctx.needs_input_grad[1:2])
+        _Frozen.seen.append((type(g), g.data_ptr()))
+        return F._out(dy, g)
+
+
+def test_frozen_parameter_buffers_are_never_registered_or_returned(fake):
+    """a frozen shared parameter's buffer dies with the backward that made it; a later operator must get
+    fresh scratch, not an alias to freed memory, and nothing may come back to autograd for it."""
+    w = torch.nn.Parameter(torch.randn(5, 3), requires_grad=False)
+    x = torch.randn(5, 3, requires_grad=True)
+    _Frozen.seen = []
+    y = _Frozen.apply(_Frozen.apply(x, w), w)
+    y.sum().backward()
+    (t1, p1), (t2, p2) = _Frozen.seen
+    assert issubclass(t1, torch.Tensor) and issubclass(t2, torch.Tensor)  # scratch both times, never an _Alias
+    assert w.grad is None and x.grad is not None
+    assert F._PASS.pending == {} and F._PASS.slabs == []
 
 
 def test_direct_calls_outside_a_backward_pass_share_nothing(fake):
@@ -132,4 +163,4 @@ def test_direct_calls_outside_a_backward_pass_share_nothing(fake):
     (g1,), _ = F._grads_like([w], N.MODE_BF16)
     (g2,), _ = F._grads_like([w], N.MODE_BF16)
     assert isinstance(g1, torch.Tensor) and isinstance(g2, torch.Tensor) and g1.data_ptr() != g2.data_ptr()
-    assert F._PENDING == {}
+    assert F._PASS.pending == {} and F._PASS.slabs == []
