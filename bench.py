@@ -164,8 +164,8 @@ class ClockSampler:
 # dominant-kernel roofline, measured live with CUDA events on the launching stream
 # ------------------------------------------------------------------------------------------------
 
-def roofline_dominant_kernel(mode, pk, reps=10):
-    """Dominant kernel of the cfg2 step: the GEMM kernel (gemm_tc_kernel in bf16 mode, gemm_f32_kernel in
+def roofline_vocab_head(mode, pk, reps=10):
+    """Side figure (round 1's roofline): the step's LARGEST products.  Dominant kernel of the cfg2 step: the GEMM kernel (gemm_tc_kernel in bf16 mode, gemm_f32_kernel in
     fp32 mode) on the step's largest products, the vocabulary head: logits = x W^T, dx = dlogits W and
     dW = dlogits^T x.  bf16 mode times them at the shape the step launches them with — one L2-sized chunk of
     labelled rows (4352 x 10003 x 256, bf16 logits with bias); fp32 mode at all 32768 rows.  Algorithmic work =
@@ -252,6 +252,181 @@ def roofline_dominant_kernel(mode, pk, reps=10):
             "flops_per_launch": flops_each, "shape_mnk": [rows, v, c], "peak_source": pk["source"] + " (burst)"}
 
 
+def roofline_dominant_kernel(mode, pk, reps=20):
+    """The kernel with the largest time share inside the step: gemm_tc_kernel on the products of the 18 latent
+    self-attention layers and their MLPs, m x n x k = 4096 x 256 x 256 per product (B*N = 64*64 rows, C = 256) —
+    forward X W^T (+bias, bf16 out), backward dX = dY W (fp32 out) and dW = dY^T X (k = 4096, fp32 atomics), the three
+    flavours the step launches ~240 times.  Algorithmic work 2*m*n*k = 0.537 GFLOP per launch (SURVEY section 8d);
+    time = CUDA events on the launching stream around each launch with a 256 MB L2 flush between launches (`cold`),
+    and back to back without a flush (`warm`, the state inside the step, where the 2 MB operands stay in L2).
+    `share_of_step` is read from the committed timeline summary of the graph replay."""
+    import ctypes
+    from perceiver import _native as N
+    if mode != 1:
+        return None
+    dev = torch.device("cuda", torch.cuda.current_device())
+    L = N.lib()
+    st = N.stream_ptr(dev)
+    rows, c = CFG["batch"] * CFG["latent"][0], CFG["latent"][1]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    x = torch.randn(rows, c, device=dev).to(torch.bfloat16)
+    w = (torch.randn(c, c, device=dev) * 0.05).to(torch.bfloat16)
+    dy = torch.randn(rows, c, device=dev).to(torch.bfloat16)
+    bias = torch.zeros(c, device=dev)
+    ws = torch.empty(16 << 20, dtype=torch.uint8, device=dev)
+
+    def desc(name):
+        d = N.GemmBf16Desc()
+        if name == "fwd":
+            out = torch.empty(rows, c, device=dev, dtype=torch.bfloat16)
+            d.a, d.b, d.m, d.n, d.k, d.lda, d.ldb, d.a_kmajor, d.b_kmajor = x.data_ptr(), w.data_ptr(), rows, c, c, c, c, 1, 1
+            d.c16, d.ldc16, d.bias = out.data_ptr(), c, bias.data_ptr()
+        elif name == "dX":
+            out = torch.empty(rows, c, device=dev)
+            d.a, d.b, d.m, d.n, d.k, d.lda, d.ldb, d.a_kmajor, d.b_kmajor = dy.data_ptr(), w.data_ptr(), rows, c, c, c, c, 1, 0
+            d.c32, d.ldc32 = out.data_ptr(), c
+        else:
+            out = torch.zeros(c, c, device=dev)
+            d.a, d.b, d.m, d.n, d.k, d.lda, d.ldb, d.a_kmajor, d.b_kmajor = dy.data_ptr(), x.data_ptr(), c, c, rows, c, c, 0, 0
+            d.c32, d.ldc32, d.accumulate = out.data_ptr(), c, 2
+        return d, out
+
+    cold, warm = {}, {}
+    for name in ("fwd", "dX", "dW"):
+        d, keep = desc(name)
+        ts = []
+        for i in range(reps + 3):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            N.check(L.pio_gemm_bf16(ctypes.byref(d), ws.data_ptr(), ws.numel(), st), "pio_gemm_bf16")
+            e1.record()
+            e1.synchronize()
+            if i >= 3:
+                ts.append(e0.elapsed_time(e1))
+        cold[name] = sum(ts) / len(ts)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for _ in range(3):
+            N.check(L.pio_gemm_bf16(ctypes.byref(d), ws.data_ptr(), ws.numel(), st), "pio_gemm_bf16")
+        e0.record()
+        for _ in range(50):
+            N.check(L.pio_gemm_bf16(ctypes.byref(d), ws.data_ptr(), ws.numel(), st), "pio_gemm_bf16")
+        e1.record()
+        e1.synchronize()
+        warm[name] = e0.elapsed_time(e1) / 50
+    flops_each = 2.0 * rows * c * c
+    achieved = flops_each * 3 / (sum(cold.values()) * 1e-3) / 1e12
+    achieved_warm = flops_each * 3 / (sum(warm.values()) * 1e-3) / 1e12
+    share, share_src = None, None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r02_dominant_kernel.json")))
+        share, share_src = tj.get("share_of_step"), tj.get("source")
+        traffic = tj.get("dram_bytes_per_launch")
+    except Exception:
+        traffic = None
+    return {"kernel": "gemm_tc_kernel (tcgen05 + TMA) at the latent-layer products 4096 x 256 x 256 (fwd / dX / dW)", "bound": "tensor",
+            "achieved": round(achieved, 2), "peak": pk["tflops"], "unit": "TFLOP/s", "frac": round(achieved / pk["tflops"], 5),
+            "traffic": traffic,
+            "achieved_warm_l2": round(achieved_warm, 2), "frac_warm_l2": round(achieved_warm / pk["tflops"], 5),
+            "ms_per_launch": {k: round(t, 5) for k, t in cold.items()}, "ms_per_launch_warm_l2": {k: round(t, 5) for k, t in warm.items()},
+            "flops_per_launch": flops_each, "shape_mnk": [rows, c, c], "share_of_step": share, "share_source": share_src,
+            "peak_source": pk["source"] + " (burst)",
+            "note": "0.5 GFLOP per launch: launch / prologue / epilogue latency bound, nowhere near a roofline; the fused "
+                    "latent-block kernel (pio_latent_tc.cu) replaces these launches from 56 row tiles (batch 112) up"}
+
+
+def reference_on_b200(steps=3, warmup=2):
+    """The reference's own arithmetic on the same B200 (SURVEY section 8d last bullet): the oracle port of the reference
+    step (torch eager ops: LayerNorm, Linear, math-path attention with the (B,H,N,M) probabilities materialised, GELU,
+    Embedding, CrossEntropyLoss, torch.optim.AdamW) at batch 64 on `cuda`, (a) fp32 with TF32 off — the reference's
+    precision: 32 — and (b) under bf16 autocast.  Reported next to cpu_baseline; not the thing measured."""
+    from oracle import perceiver_oracle as O
+    dev = torch.device("cuda", torch.cuda.current_device())
+    out = {}
+    ids, pad = synthetic_batch(0, CFG["batch"], CFG["seq"], CFG["vocab"])
+    ids, pad = ids.to(dev), pad.to(dev)
+    h = CFG["heads"]
+    for name in ("fp32", "bf16_autocast"):
+        tf32 = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+        torch.backends.cuda.matmul.allow_tf32 = False
+        torch.backends.cudnn.allow_tf32 = False
+        try:
+            torch.manual_seed(0)
+            model = build_model()
+            sd = {k: v.detach().to(dev).clone().requires_grad_(v.is_floating_point()) for k, v in model.state_dict().items()}
+            params = [v for v in sd.values() if v.requires_grad]
+            opt = torch.optim.AdamW(params, lr=CFG["lr"])
+
+            def step():
+                x, labels = O.text_masking(ids.clone(), pad, vocab_size=CFG["vocab"], unk_token_id=1, mask_token_id=2,
+                                           num_special_tokens=3)
+                with torch.autocast("cuda", dtype=torch.bfloat16, enabled=(name == "bf16_autocast")):
+                    logits = O.mlm_forward(sd, x, pad, num_layers=CFG["layers"], cross_heads=h[0], self_heads=h[1],
+                                           sa_layers=CFG["sa"], dec_heads=h[2])
+                    loss = O.cross_entropy(logits.float(), labels)
+                opt.zero_grad(set_to_none=True)
+                loss.backward()
+                opt.step()
+                return loss
+            for _ in range(warmup):
+                step()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                step()
+            e1.record()
+            e1.synchronize()
+            ms = e0.elapsed_time(e1) / steps
+            out[name] = {"ms_per_step": round(ms, 3), "samples_per_s": round(CFG["batch"] / (ms * 1e-3), 1)}
+        except Exception as ex:
+            out[name] = {"error": str(ex)[:200]}
+        finally:
+            torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = tf32
+            del model
+            torch.cuda.empty_cache()
+    out["what"] = ("oracle port of the reference step in torch eager on this GPU, batch 64: fp32 (allow_tf32=False) and "
+                   "bf16 autocast; the Python reference tree itself is absent on the GPU box")
+    return out
+
+
+def fp32_mode_step(steps=5, warmup=2):
+    """The same train step in PIO_MODE_FP32 (FFMA kernels end to end, the rel-1e-4 parity mode), eager."""
+    import perceiver
+    dev = torch.device("cuda", torch.cuda.current_device())
+    prev = perceiver.get_compute_mode()
+    perceiver.set_compute_mode("fp32")
+    try:
+        torch.manual_seed(0)
+        model = build_model().to(dev)
+        opt = torch.optim.AdamW(model.parameters(), lr=CFG["lr"], fused=True)
+        ids, pad = synthetic_batch(0, CFG["batch"], CFG["seq"], CFG["vocab"])
+        ids, pad = ids.to(dev), pad.to(dev)
+
+        def step():
+            logits, labels = model(ids.clone(), pad)
+            loss = perceiver.cross_entropy(logits, labels)
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
+        for _ in range(warmup):
+            step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        e1.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        return {"ms_per_step": round(ms, 3), "samples_per_s": round(CFG["batch"] / (ms * 1e-3), 1), "mode": "fp32 kernels, eager"}
+    except Exception as ex:
+        return {"error": str(ex)[:200]}
+    finally:
+        perceiver.set_compute_mode(prev)
+        torch.cuda.empty_cache()
+
+
 def cross_attention_core_tflops(mode, pk):
     """North-star side metric: cross-attention core (QK^T + PV) at BASELINE configs[3] shape
     (B 32, M 16384, N 256, 8 heads, dh 64), forward, 4*B*N*M*E FLOP per launch."""
@@ -290,7 +465,8 @@ def cross_attention_core_tflops(mode, pk):
 
 def other_config_throughput(mode):
     """Side numbers for the other BASELINE configs (eager, fwd + loss + bwd + AdamW, synthetic data):
-    config 1 MNIST-shaped image classifier (batch 128) and config 4 long-input stress (M = 16384, latent
+    config 1 MNIST-shaped image classifier (batch 128), config 3 sequence classifier (batch 128, unfrozen, dropout 0 and
+    0.1) and config 4 long-input stress (M = 16384, latent
     (256,512), 8 cross heads, batch 32).  Reported, not the headline."""
     import perceiver
     from perceiver import (ClassificationOutputAdapter, ImageInputAdapter, PerceiverDecoder, PerceiverEncoder, PerceiverIO,
@@ -348,6 +524,13 @@ def other_config_throughput(mode):
     out["cfg1_mnist_b128"] = run(PerceiverIO(enc, dec),
                                  lambda: ((torch.rand(128, 28, 28, 1, device=dev) * 2 - 1,), torch.randint(0, 10, (128,), device=dev)),
                                  128)
+    for p_drop in (0.0, 0.1):  # config 3: text classifier on the MLM encoder, batch 128, everything trainable (README.md:98: dropout 0.1)
+        torch.manual_seed(0)
+        enc = PerceiverEncoder(TextInputAdapter(10003, 512, 256), (64, 256), 3, 4, 4, 6, dropout=p_drop)
+        dec = PerceiverDecoder(ClassificationOutputAdapter(2, num_output_channels=256), (64, 256), 1, dropout=p_drop)
+        ids3, pad3 = synthetic_batch(3, 128, 512, 10003)
+        out[f"cfg3_seq_clf_b128_dropout{p_drop}"] = run(
+            PerceiverIO(enc, dec), lambda: ((ids3.to(dev), pad3.to(dev)), torch.randint(0, 2, (128,), device=dev)), 128)
     enc = PerceiverEncoder(TextInputAdapter(10003, 16384, 512), (256, 512), 3, 8, 4, 6)
     dec = PerceiverDecoder(ClassificationOutputAdapter(2, num_output_channels=512), (256, 512), 1)
     out["cfg4_long_input_b32_m16384"] = run(
@@ -566,7 +749,19 @@ def gpu_arm(args):
         ms_per_step = total_ms / args.steps
         value = world * CFG["batch"] / (ms_per_step * 1e-3)
         e2e_value = world * CFG["batch"] / (e2e_ms / args.steps * 1e-3)
-        roof = roofline_dominant_kernel(mode, pk)
+        roof = roofline_dominant_kernel(mode, pk) or roofline_vocab_head(mode, pk)
+        try:
+            vocab_roof = roofline_vocab_head(mode, pk) if mode == 1 else None
+        except Exception as ex:
+            vocab_roof = {"error": str(ex)[:200]}
+        ref_gpu = fp32_step = None
+        if world == 1:
+            try:
+                ref_gpu = reference_on_b200()
+            except Exception as ex:
+                ref_gpu = {"error": str(ex)[:200]}
+            if mode == 1:
+                fp32_step = fp32_mode_step()
         try:
             xattn = cross_attention_core_tflops(mode, pk)
         except Exception as ex:  # side metric must never sink the headline line
@@ -575,8 +770,8 @@ def gpu_arm(args):
             others = other_config_throughput(mode)
         except Exception as ex:
             others = {"error": str(ex)[:200]}
-        sample_b = 16
-        cpu = cpu_reference_arm(steps=3, warmup=2, batch=sample_b) if world == 1 else None  # CPU baseline: N=1 only
+        sample_b = CFG["batch"]  # the same batch of 64 (same_config)
+        cpu = cpu_reference_arm(steps=3, warmup=1, batch=sample_b) if world == 1 else None  # CPU baseline: N=1 only
         result = {
             "metric": "train_samples_per_sec", "value": round(value, 2), "unit": "samples/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms_per_step, 4),
@@ -598,14 +793,18 @@ def gpu_arm(args):
                     "h2d_bytes_per_step": ids_h.numel() * 8 + pad_h.numel(), "d2h_bytes_per_step": 4},
             "gpu_launches": int(launches),
             "roofline": roof,
+            "vocab_head_gemm": vocab_roof,
+            "reference_on_b200": ref_gpu,
+            "fp32_mode_step": fp32_step,
             "cross_attention_core": xattn,
             "optimizer_kernel": adamw_roof,
             "vocab_head": head_note,
             "other_configs": others,
             "cpu_baseline": None if cpu is None else {
                 "value": round(cpu["samples_per_s"], 3), "unit": "samples/s", "cores": cpu["cores"], "kind": "port",
-                "sample": f"same step at batch {sample_b} (2 warm-up + 3 timed steps), oracle port of the "
-                          "reference (torch CPU fp32)"},
+                "same_config": True,
+                "sample": f"the same step at the same batch {sample_b} (1 warm-up + 3 timed steps), oracle port of the "
+                          "reference (torch CPU fp32, all host cores)"},
         }
         print(json.dumps(result), flush=True)
     if distributed:
@@ -618,7 +817,7 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample_b = 16
+    sample_b = CFG["batch"]
     r = cpu_reference_arm(steps=args.steps, warmup=args.warmup, batch=sample_b)
     out = {
         "impl": "reference", "metric": "train_samples_per_sec", "value": round(r["samples_per_s"], 3), "unit": "samples/s",
@@ -626,7 +825,8 @@ def reference_arm(args):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "global_batch": CFG["batch"], "seq_len": CFG["seq"], "parallelism": "cpu"},
         "cpu_baseline": {"value": round(r["samples_per_s"], 3), "unit": "samples/s", "cores": r["cores"], "kind": "port",
-                         "sample": f"each step = the full train step on a batch of {sample_b} of the 64 samples "
+                         "same_config": True,
+                         "sample": f"each step = the full train step on the full batch of {sample_b} (~1.4 s on 16 cores) "
                                    "(oracle port of the reference; the Python reference tree is absent on the GPU box)"},
         "e2e": {"value": round(r["samples_per_s"], 3), "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }

@@ -19,3 +19,43 @@ def assert_rel(got, ref, tol, what=""):
     assert torch.isfinite(got).all(), f"{what}: non-finite values"
     e = rel_err(got, ref)
     assert e <= tol, f"{what}: rel err {e:.3e} > {tol:.1e}"
+
+
+def grad_table(got: dict, ref: dict, min_abs=1e-10):
+    """per-tensor (name, max-abs error / max |ref|, relative L2, numel) sorted worst first, and the relative L2 error of
+    the whole gradient (all tensors concatenated)"""
+    rows, num, den = [], 0.0, 0.0
+    for k, r in ref.items():
+        if r is None or r.abs().max() < min_abs:
+            continue
+        g = got[k].detach().double().cpu()
+        r = r.detach().double().cpu()
+        d = (g - r).norm().item()
+        rows.append((k, (g - r).abs().max().item() / r.abs().max().item(), d / max(r.norm().item(), 1e-300), r.numel()))
+        num += d * d
+        den += r.norm().item() ** 2
+    rows.sort(key=lambda t: -t[1])
+    return rows, (num / max(den, 1e-300)) ** 0.5
+
+
+# bf16-mode per-tensor gradient bounds (max-abs error over the tensor's largest magnitude; note that this, like
+# rel_err above, is a tensor-scale metric, not an element-wise relative error).  The north-star tolerance 1e-2 holds
+# for the gradient as a whole (relative L2 over all parameters: measured 7.2e-3 at the benchmarked cfg2 batch 64).
+# Per tensor, measured against the fp32 oracle on B200 (tests/test_gpu_train_step.py -s, cfg2 batch 64 and the small
+# config): every matrix <= 1.3e-2, every LayerNorm / bias vector <= 1.8e-2 — bounded here by 2e-2 and 3e-2 — with ONE
+# exception, the LayerNorm affine terms of the decoder queries (1.3e-1): sums over B*K rows of a softmax gradient whose
+# rows sum to zero, so the terms cancel almost exactly while the unbiased bf16 rounding noise of the operands does
+# not (a CPU run of the oracle with only the GEMM / attention operands rounded to bf16 already moves them by 2.5e-2;
+# the tensor-core attention additionally rounds P to bf16, as every flash-attention kernel does).
+BF16_GRAD_BOUNDS = [
+    ("decoder.cross_attention.0.module.q_norm.", 2e-1), ("1.cross_attention.0.module.q_norm.", 2e-1),
+    ("norm.", 3e-2), (".module.0.", 3e-2), ("bias", 3e-2), ("latent", 3e-2), ("output", 3e-2),
+    ("", 2e-2),
+]
+
+
+def bf16_grad_bound(name: str) -> float:
+    for frag, tol in BF16_GRAD_BOUNDS:
+        if frag in name:
+            return tol
+    return 2e-2

@@ -5,24 +5,19 @@ import pytest
 import torch
 
 from conftest import load_golden
-from gpu_util import BF16_TOL, assert_rel, rel_err
+from gpu_util import BF16_TOL, assert_rel, bf16_grad_bound, rel_err
 from oracle import perceiver_oracle as O
 from test_dropin_api import build_from_meta
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
-# Logits, loss and the gradient as a whole (all parameters concatenated, relative L2) keep the
-# north-star bf16 tolerance of 1e-2.  Individual small gradient tensors are noisier.  The worst are the
-# LayerNorm affine terms of the decoder queries: sums over B*K rows that cancel almost exactly (the
-# softmax gradient of each row sums to zero), so unbiased bf16 rounding noise does not shrink with them.
-# Rounding only the GEMM / attention operands to bf16 in an otherwise exact CPU run of the oracle already
-# moves them by 2.5e-2; the tensor-core attention additionally rounds P to bf16 before P.V (as every
-# flash-attention kernel does), which brings the measured worst case to 7e-2 while every other tensor
-# stays near 1e-2.  Per-tensor bound: 1e-1 (a wrong operand or layout shows up as O(1)).  On the
-# 8..16-channel golden fixtures, vectors of fewer than 32 numbers are held to the whole-gradient
-# criterion only.
+# Logits, loss and the gradient as a whole (all parameters concatenated, relative L2) keep the north-star bf16
+# tolerance of 1e-2.  Per tensor the bound comes from gpu_util.BF16_GRAD_BOUNDS (2e-2 for matrices, 3e-2 for
+# LayerNorm / bias vectors, 2e-1 for the decoder-query LayerNorm terms — each measured and justified there).  Only the
+# 8..16-channel golden fixtures keep a blanket 1e-1: with so few numbers per tensor a single bf16 rounding is a visible
+# fraction of the largest entry (vectors of fewer than 32 numbers are held to the whole-gradient criterion only).
 GRAD_TOL_TINY = 1e-1
-GRAD_TOL = 1e-1
+GRAD_TOL = None  # = the per-tensor table
 GLOBAL_GRAD_TOL = BF16_TOL
 
 
@@ -48,6 +43,8 @@ def _check_grads(model, ref_grads, tol, global_tol=None, min_numel=0):
         l2 = diff / g.double().norm().item()
         num += diff ** 2
         den += g.double().norm().item() ** 2
+        if tol is None:
+            assert e <= bf16_grad_bound(k), f"grad {k}: rel err {e:.3e} > {bf16_grad_bound(k):.1e}"
         if e > worst[1] and g.numel() >= min_numel:
             worst = (k, e)
         if l2 > worst_l2[1]:
@@ -55,7 +52,7 @@ def _check_grads(model, ref_grads, tol, global_tol=None, min_numel=0):
     glob = (num / max(den, 1e-300)) ** 0.5
     print(f"gradient: global L2-rel {glob:.3e}; worst tensor max-rel {worst[1]:.3e} ({worst[0]}), "
           f"L2-rel {worst_l2[1]:.3e} ({worst_l2[0]})")
-    assert worst[1] <= tol, f"worst grad {worst}"
+    assert tol is None or worst[1] <= tol, f"worst grad {worst}"
     if global_tol is not None:
         assert glob <= global_tol, f"global gradient L2-rel {glob}"
 
