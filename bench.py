@@ -498,22 +498,13 @@ def other_config_throughput(mode):
             step()
         ms = timed_ms(step)
         out_ = {"ms_per_step": round(ms, 3), "samples_per_s": round(batch / (ms * 1e-3), 1), "mode": "eager"}
-        if mode == 1:  # the same step replayed from a CUDA graph (static inputs, own AdamW inside the graph)
+        if mode == 1:  # the same step replayed from a CUDA graph (perceiver.GraphedTrainStep: flat gradients, AdamW in the graph)
             try:
-                side = torch.cuda.Stream()
-                side.wait_stream(torch.cuda.current_stream())
-                with torch.cuda.stream(side):
-                    step()
-                torch.cuda.current_stream().wait_stream(side)
-                opt.zero_grad(set_to_none=True)
-                graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph):
-                    loss = perceiver.cross_entropy(model(*args), y)
-                    loss.backward()
-                    opt.step()
-                graph.replay()
-                gms = timed_ms(graph.replay)
+                gs = perceiver.GraphedTrainStep(model.parameters(), opt, lambda: perceiver.cross_entropy(model(*args), y))
+                gs.replay()
+                gms = timed_ms(gs.replay)
                 out_.update({"graph_ms_per_step": round(gms, 3), "graph_samples_per_s": round(batch / (gms * 1e-3), 1)})
+                gs.fg.close()
             except Exception as ex:
                 out_["graph_error"] = str(ex)[:160]
         return out_

@@ -13,5 +13,5 @@ from .model import (CrossAttention, MultiHeadAttention, PerceiverDecoder, Percei
                     self_attention_layer)
 from .distributed import FlatGradients, average_gradients
 from .optim import FusedAdamW
-from .pipeline import GraphedMLMStep, MaskingPrefetcher
+from .pipeline import GraphedMLMStep, GraphedTrainStep, MaskingPrefetcher
 from .utils import Sequential, freeze, predict_masked_samples

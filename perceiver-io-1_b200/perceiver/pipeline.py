@@ -58,55 +58,45 @@ class MaskingPrefetcher:
         self.pending = False
 
 
-class GraphedMLMStep:
-    """The whole masked-LM train step of LitMaskedLanguageModel (reference lightning.py:219-231: masking, forward,
-    cross-entropy, backward; then the optimizer step) as ONE replayed CUDA graph per batch.
+class GraphedTrainStep:
+    """forward + loss + backward + optimizer step of any model built from this package's operators as ONE replayed CUDA
+    graph.  ``loss_fn()`` computes the loss from tensors at fixed addresses (copy each batch into them before calling
+    ``replay()``); parameter gradients are written in place into one flat buffer (`FlatGradients`), and with an
+    initialised process group of more than one rank its buckets are all-reduced (mean) on a side stream from inside the
+    captured backward pass.  ``overlap_allreduce=False``: one flat all-reduce and the optimizer run eagerly after the
+    graph (the previous scheme).  bf16 compute mode; the optimizer must be capturable (`perceiver.FusedAdamW`).
+    Dropout seeds are launch arguments, so a replay repeats the captured masks: fine for timing, not for training with
+    dropout > 0 (train those eagerly)."""
 
-        step = GraphedMLMStep(model, optimizer, ids, pad)     # model: PerceiverMLM on a CUDA device, bf16 mode
-        for ids, pad in batches:                               # host (pinned) or device tensors of the same shape
-            loss = step(ids, pad)                              # a device scalar (valid until the next call)
-
-    * TextMasking runs outside the graph on a side stream, one batch ahead (`MaskingPrefetcher`): its one host read
-      (the length of the reference's randint draw) no longer idles the GPU, results are bit-identical.
-    * Inside the graph: forward with the fused vocabulary-projection + cross-entropy head, backward with every
-      parameter gradient written in place into one flat buffer (`FlatGradients`), the optimizer step.
-    * With an initialised process group of more than one rank the flat buffer's buckets are all-reduced (mean) on a
-      side stream from inside the captured backward pass, in the order the pass completes them; the collectives are
-      part of the graph.  ``overlap_allreduce=False`` keeps the previous scheme (one flat all-reduce and the
-      optimizer run eagerly after the graph).
-    The optimizer must be capturable (`perceiver.FusedAdamW`, or torch's with ``capturable=True``)."""
-
-    def __init__(self, model, optimizer, ids, pad, overlap_allreduce=True, flat_gradients=True, bucket_bytes=8 << 20, warmup=3):
+    def __init__(self, params, optimizer, loss_fn, overlap_allreduce=True, bucket_bytes=8 << 20, warmup=3, before_warmup_step=None):
         import torch.distributed as dist
         from . import _native as N
         from .distributed import FlatGradients, average_gradients
-        dev = next(model.parameters()).device
-        self.model, self.opt, self.device = model, optimizer, dev
+        self.params = [p for p in params if p.requires_grad]
+        dev = self.params[0].device
+        self.opt, self.device, self.loss_fn = optimizer, dev, loss_fn
         self.world = dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
-        self.ids = torch.empty(ids.shape, dtype=torch.int64, device=dev)
-        self.labels = torch.empty_like(self.ids)
-        self.pad = torch.empty(pad.shape, dtype=torch.bool, device=dev)
-        self.params = [p for p in model.parameters() if p.requires_grad]
-        use_fg = flat_gradients and (overlap_allreduce or self.world == 1)
+        use_fg = overlap_allreduce or self.world == 1
         self.fg = FlatGradients(self.params, bucket_bytes=bucket_bytes) if use_fg else None
         self._average = average_gradients
-        self.prefetch = MaskingPrefetcher(model.masking, dev)
         side = torch.cuda.Stream(dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
             if self.fg is not None:  # one ordinary pass teaches FlatGradients the completion order of the parameters
-                self._fill(ids, pad)
+                if before_warmup_step is not None:
+                    before_warmup_step()
                 with self.fg.profile():
-                    loss, _ = model(self.ids, self.pad, masking=False, return_loss=True, labels=self.labels)
-                    loss.backward()
+                    loss_fn().backward()
             for _ in range(warmup):
-                self._fill(ids, pad)
+                if before_warmup_step is not None:
+                    before_warmup_step()
                 if self.fg is None:
                     optimizer.zero_grad(set_to_none=True)
                 self._body()
                 self._tail()
         torch.cuda.current_stream(dev).wait_stream(side)
-        self._fill(ids, pad)
+        if before_warmup_step is not None:
+            before_warmup_step()
         if self.fg is None:
             optimizer.zero_grad(set_to_none=True)
         self.graph = torch.cuda.CUDAGraph()
@@ -119,15 +109,10 @@ class GraphedMLMStep:
     def in_graph_optimizer(self):
         return self.fg is not None or self.world == 1
 
-    def _fill(self, ids, pad):
-        if not self.prefetch.pending:
-            self.prefetch.submit(ids, pad)
-        self.prefetch.take(self.ids, self.labels, self.pad)
-
     def _body(self):
         if self.fg is not None:
             self.fg.step_begin()
-        loss, _ = self.model(self.ids, self.pad, masking=False, return_loss=True, labels=self.labels)
+        loss = self.loss_fn()
         loss.backward()
         if self.fg is not None:
             self.fg.step_end()
@@ -140,9 +125,46 @@ class GraphedMLMStep:
             self._average(self.params)
             self.opt.step()
 
-    def __call__(self, ids, pad):
-        self._fill(ids, pad)        # consume the prefetched batch (the first call masks its own)
+    def replay(self):
         self.graph.replay()
         self._tail()
-        self.prefetch.submit(ids, pad)  # next call's batch: H2D (for host tensors) + masking, overlapped with this step
         return self.loss
+
+
+class GraphedMLMStep(GraphedTrainStep):
+    """The whole masked-LM train step of LitMaskedLanguageModel (reference lightning.py:219-231: masking, forward,
+    cross-entropy, backward; then the optimizer step) as ONE replayed CUDA graph per batch.
+
+        step = GraphedMLMStep(model, optimizer, ids, pad)     # model: PerceiverMLM on a CUDA device, bf16 mode
+        for ids, pad in batches:                               # host (pinned) or device tensors of the same shape
+            loss = step(ids, pad)                              # a device scalar (valid until the next call)
+
+    * TextMasking runs outside the graph on a side stream, one batch ahead (`MaskingPrefetcher`): its one host read
+      (the length of the reference's randint draw) no longer idles the GPU, results are bit-identical.
+    * Inside the graph (`GraphedTrainStep`): forward with the fused vocabulary-projection + cross-entropy head,
+      backward with every parameter gradient written in place into one flat buffer, the optimizer step, and for
+      more than one rank the bucketed gradient all-reduce overlapped with the backward pass."""
+
+    def __init__(self, model, optimizer, ids, pad, overlap_allreduce=True, bucket_bytes=8 << 20, warmup=3):
+        dev = next(model.parameters()).device
+        self.model = model
+        self.ids = torch.empty(ids.shape, dtype=torch.int64, device=dev)
+        self.labels = torch.empty_like(self.ids)
+        self.pad = torch.empty(pad.shape, dtype=torch.bool, device=dev)
+        self.prefetch = MaskingPrefetcher(model.masking, dev)
+
+        def loss_fn():
+            return model(self.ids, self.pad, masking=False, return_loss=True, labels=self.labels)[0]
+        super().__init__(model.parameters(), optimizer, loss_fn, overlap_allreduce=overlap_allreduce, bucket_bytes=bucket_bytes,
+                         warmup=warmup, before_warmup_step=lambda: self._fill(ids, pad))
+
+    def _fill(self, ids, pad):
+        if not self.prefetch.pending:
+            self.prefetch.submit(ids, pad)
+        self.prefetch.take(self.ids, self.labels, self.pad)
+
+    def __call__(self, ids, pad):
+        self._fill(ids, pad)        # consume the prefetched batch (the first call masks its own)
+        loss = self.replay()
+        self.prefetch.submit(ids, pad)  # next call's batch: H2D (for host tensors) + masking, overlapped with this step
+        return loss
