@@ -87,6 +87,21 @@ def cpu_reference_arm(steps, warmup, batch, threads=None):
     return dict(samples_per_s=batch / dt, ms_per_step=dt * 1e3, cores=threads, batch=batch)
 
 
+def leave_distributed(graph_holder=None):
+    """End of a multi-rank run.  Captured graphs that contain NCCL kernels are released BEFORE the communicator goes
+    (tearing the communicator down underneath them hung the ranks), and the process then exits without
+    destroy_process_group(): every rank has synchronised its device and passed a last barrier, nothing is in flight."""
+    import torch.distributed as dist
+    torch.cuda.synchronize()
+    dist.barrier()
+    if graph_holder is not None and getattr(graph_holder, "graph", None) is not None:
+        graph_holder.graph.reset()
+    torch.cuda.synchronize()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
+
+
 def build_model():
     from perceiver import (PerceiverDecoder, PerceiverEncoder, PerceiverMLM, TextInputAdapter, TextMasking,
                            TextOutputAdapter)
@@ -672,7 +687,7 @@ def gpu_arm(args):
         if rank == 0:
             print(json.dumps({"profile_only": True, "ms_per_step": total_ms / args.steps, "gpu_launches": int(launches)}))
         if distributed:
-            dist.destroy_process_group()
+            leave_distributed(gstep if graph is not None else None)
         return None
 
     # end to end through the public API with HOST buffers: H2D of the batch and D2H of the loss each step
@@ -799,8 +814,7 @@ def gpu_arm(args):
         }
         print(json.dumps(result), flush=True)
     if distributed:
-        dist.barrier()
-        dist.destroy_process_group()
+        leave_distributed(gstep if graph is not None else None)
     return result
 
 
@@ -835,7 +849,7 @@ def main():
     ap.add_argument("--torch-optimizer", action="store_true", help="torch.optim.AdamW(fused=True) instead of perceiver.FusedAdamW")
     ap.add_argument("--flat-allreduce-after", action="store_true",
                     help="N > 1: previous scheme, one flat all-reduce after the captured graph instead of overlapped buckets")
-    ap.add_argument("--bucket-mb", type=int, default=8, help="gradient bucket size of the overlapped all-reduce")
+    ap.add_argument("--bucket-mb", type=int, default=24, help="gradient bucket size of the overlapped all-reduce")
     ap.add_argument("--timeline", default=None, help="with --profile-only: CSV of (stream, start_us, dur_us, kernel) of 2 more steps")
     ap.add_argument("--mode", default=os.environ.get("PIO_MODE", "bf16"), choices=["fp32", "bf16"])
     args = ap.parse_args()

@@ -118,7 +118,7 @@ class FlatGradients:
     still removes the per-operator gradient slabs and their zero-fill launches.
     Do not call ``zero_grad(set_to_none=True)`` afterwards: it would drop the views."""
 
-    def __init__(self, params, group: Optional[dist.ProcessGroup] = None, bucket_bytes: int = 8 << 20):
+    def __init__(self, params, group: Optional[dist.ProcessGroup] = None, bucket_bytes: int = 24 << 20):
         self.params = [p for p in params if p.requires_grad]
         if not self.params:
             raise ValueError("FlatGradients: no trainable parameters")
@@ -162,15 +162,22 @@ class FlatGradients:
         self.bucket_of, self.expected, self.bounds = {}, [], []
         off, start, nbytes, exp = 0, 0, 0, 0
         offsets = {}
+        sizes = [4 * ((by_key[k].numel() + 3) // 4 * 4) for k in order]
+        left_touched = sum(sizes[:len(touched)])
         for i, k in enumerate(order):
             p = by_key[k]
             offsets[k] = off
             n = (p.numel() + 3) // 4 * 4
             off += n
             nbytes += 4 * n
+            if i < len(touched):
+                left_touched -= 4 * n
             exp += count.get(k, 0)
             self.bucket_of[k] = len(self.bounds)
-            boundary = nbytes >= self.bucket_bytes or i + 1 == len(order) or (i + 1 == len(touched) and untouched)
+            # a bucket closes when it is full — unless what is left of the pass would make a runt (a collective of a few
+            # hundred KB costs the same latency as one of several MB, and the last one is the exposed one)
+            full = nbytes >= self.bucket_bytes and (i >= len(touched) or left_touched == 0 or left_touched >= self.bucket_bytes // 4)
+            boundary = full or i + 1 == len(order) or (i + 1 == len(touched) and untouched)
             if boundary:
                 self.bounds.append((start, off))
                 self.expected.append(exp)

@@ -477,6 +477,38 @@ class TextEmbedFn(torch.autograd.Function):
         return None, demb, dpos, None
 
 
+class BroadcastRowsFn(torch.autograd.Function):
+    """(K, C) parameter (first ``rows`` rows) -> (B, rows, C): the learned latent array / decoder query array repeated
+    over the batch (reference model.py:183, :235 `repeat(self.latent, '... -> b ...')`).  Backward: the sum over the
+    batch, written straight into the parameter's flat gradient destination when one is registered (FlatGradients)."""
+
+    @staticmethod
+    def forward(ctx, param, batch, rows):
+        ctx.save_for_backward(param)
+        ctx.rows = rows
+        return param[:rows].unsqueeze(0).expand(batch, -1, -1).contiguous()
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        (param,) = ctx.saved_tensors
+        rows = ctx.rows
+        hit = _DST.get(_pkey(param))
+        if hit is not None and param.grad is not None and param.grad.data_ptr() == hit[0]:
+            _direct_target(param)  # counts the write
+            torch.sum(dy, dim=0, out=param.grad[:rows])  # (rows beyond `rows` stay zero: the buffer was cleared)
+            _after_op()
+            return None, None, None
+        if _TOUCH_LOG is not None:
+            _TOUCH_LOG.append(_pkey(param))
+        g = dy.sum(dim=0)
+        if rows != param.shape[0]:
+            full = torch.zeros_like(param)
+            full[:rows] = g
+            g = full
+        return g, None, None
+
+
 def text_mask(ids, pad_mask, vocab_size, unk_token_id, mask_token_id, num_special_tokens, mask_p, generator=None):
     """TextMasking.forward (reference model.py:265-293), in place on ``ids``; returns labels.
 

@@ -208,7 +208,7 @@ class PerceiverEncoder(nn.Module):
     def forward(self, x, pad_mask=None, attn_mask=None):
         b = x.shape[0]
         x = self.input_adapter(x)
-        x_latent = self.latent.unsqueeze(0).expand(b, -1, -1).contiguous()
+        x_latent = F.BroadcastRowsFn.apply(self.latent, b, self.latent.shape[0])
         x_latent = self._apply_layer(self.layer_1, x_latent, x, pad_mask, attn_mask)
         if self.num_layers > 1:
             kv_n = self.layer_n[0][0].module.project_kv(x)  # once for all repeats of the shared layer
@@ -240,8 +240,7 @@ class PerceiverDecoder(nn.Module):
         b, *d = x.shape
         if tuple(d) != tuple(self.latent_shape):
             raise ValueError(f'Latent shape {tuple(d)} different from required shape {self.latent_shape}')
-        q = self.output if num_queries is None else self.output[:num_queries]
-        q = q.unsqueeze(0).expand(b, -1, -1).contiguous()
+        q = F.BroadcastRowsFn.apply(self.output, b, self.output.shape[0] if num_queries is None else num_queries)
         return self.cross_attention(q, x)  # no mask on the latents, as in the reference
 
     @_scoped

@@ -78,8 +78,13 @@ def main():
         rel = (num / den) ** 0.5
         assert rel < 5e-3, f"averaged 2-rank gradient vs full-batch gradient: rel L2 {rel}"
         print(f"DDP_WORKER_OK rel={rel:.3e} buckets={len(step.fg.views)} launches_per_replay={step.launches_per_replay}", flush=True)
+    # leave like bench.py: release the graph (it holds NCCL kernels) before the communicator, skip destroy_process_group
+    torch.cuda.synchronize()
     dist.barrier()
-    dist.destroy_process_group()
+    step.graph.reset()
+    torch.cuda.synchronize()
+    sys.stdout.flush()
+    os._exit(0)
 
 
 if __name__ == "__main__":
