@@ -401,6 +401,33 @@ int pio_linear_bwd(const float* dy, const float* x, const float* w, float* dx, f
                    int accumulate, int64_t rows, int c_in, int64_t c_out, int mode, void* ws,
                    size_t ws_bytes, pio_stream_t stream);
 
+/* PerceiverDecoder's cross_attention_layer (model.py:203-206, :229-237: Residual(CrossAttention(q = learned output array,
+ * kv = latents)) then Residual(mlp)) evaluated ONLY for the (sample, position) pairs that carry a label in a masked-LM
+ * batch (PerceiverMLM with the loss of LitMaskedLanguageModel.step, model.py:306-318, lightning.py:223-226).  Each decoder
+ * query is independent of the others and an ignored position adds exactly zero to the loss and to every gradient, so the
+ * result (loss, gradients) is that of decoding every position.  PIO_MODE_BF16 only.
+ *   pio_label_compact: idx[i] = flat position b*l + pos of the i-th labelled pair (stable order), labels_c[i] its label
+ *     (`ignore` for i >= count), *count their number — all in DEVICE memory; the host never learns the count.
+ *   pio_decode_rows_fwd/bwd: row i of y / dy (max_rows = batch*l rows allocated, the first *count used) belongs to pair
+ *     idx[i].  queries (K >= l, e) is the decoder's learned output array, kv the bf16 (batch, n, 2e) tensor of
+ *     pio_kv_project_fwd on the latents.  attn: ln_w/ln_b = q_norm, wq/bq, wo/bo (bf16 matrices); mlp as pio_mlp_fwd.
+ *     Backward (accumulate must be 2): parameter gradients are ADDED into zero-filled / running buffers, dqueries (K, e)
+ *     likewise; dkv (bf16, batch x n x 2e) is overwritten.  Every launch is sized for max_rows and clamps at *count, so
+ *     the sequence can be captured in a CUDA graph and replayed on batches with other label counts. */
+size_t pio_label_compact_ws_bytes(int64_t rows);
+int pio_label_compact(const int64_t* labels, int64_t rows, int64_t classes, int64_t ignore, int32_t* idx, int64_t* labels_c,
+                      int32_t* count, void* ws, size_t ws_bytes, pio_stream_t stream);
+int pio_decode_rows_supported(int n, int e, int heads);
+size_t pio_decode_rows_saved_bytes(int64_t max_rows, int e, int heads);
+size_t pio_decode_rows_ws_bytes(int64_t max_rows, int e, int heads);
+int pio_decode_rows_fwd(const float* queries, const void* kv, const int32_t* idx, const int32_t* count, float* y,
+                        const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved, int64_t max_rows, int l, int batch,
+                        int n, int e, int heads, void* ws, size_t ws_bytes, pio_stream_t stream);
+int pio_decode_rows_bwd(const float* dy, const void* kv, const int32_t* idx, const int32_t* count, float* dqueries, void* dkv,
+                        const pio_attn_weights* attn, const pio_mlp_weights* mlp, const void* saved, const pio_attn_grads* attn_g,
+                        const pio_mlp_grads* mlp_g, int accumulate, int64_t max_rows, int l, int batch, int n, int e, int heads,
+                        void* ws, size_t ws_bytes, pio_stream_t stream);
+
 /* Output-adapter Linear fused with the cross-entropy loss for training (TextOutputAdapter.linear,
  * adapter.py:146-149,166-173 + nn.CrossEntropyLoss, lightning.py:184,225-226).
  * PIO_MODE_BF16 only (`w` = bf16 shadow).  Rows with an ignored label contribute exactly zero to the loss

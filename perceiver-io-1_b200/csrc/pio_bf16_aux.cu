@@ -6,13 +6,21 @@ namespace pio {
 
 __global__ void layernorm_fwd_bf16_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                           const float* __restrict__ b, __nv_bfloat16* __restrict__ y, int64_t ldy,
-                                          float* __restrict__ stats, int64_t rows, int c, float eps) {
+                                          float* __restrict__ stats, int64_t rows, int c, float eps,
+                                          const int* __restrict__ dyn_rows) {
     pdl_trigger();
     pdl_wait();
     const int lane = threadIdx.x & 31;
     const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const float inv_c = 1.0f / (float)c;
+    const int64_t alloc_rows = rows;
+    if (dyn_rows != nullptr) {  // device-side row count: rows up to the next multiple of 128 are zero-filled (operand padding)
+        rows = min(rows, (int64_t)*dyn_rows);
+        const int64_t upto = min(alloc_rows, (rows + 127) / 128 * 128);
+        for (int64_t r = rows + warp; r < upto; r += nwarps)
+            for (int j = lane; j < (int)ldy; j += 32) y[r * ldy + j] = __float2bfloat16(0.f);
+    }
     for (int64_t r = warp; r < rows; r += nwarps) {
         const float* xr = x + r * c;
         float s = 0.f;
@@ -39,13 +47,21 @@ __global__ void layernorm_fwd_bf16_kernel(const float* __restrict__ x, const flo
 template <int NV>
 __global__ void __launch_bounds__(256) layernorm_fwd_bf16_vec_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                                      const float* __restrict__ b, __nv_bfloat16* __restrict__ y,
-                                                                     float* __restrict__ stats, int64_t rows, float eps) {
+                                                                     float* __restrict__ stats, int64_t rows, float eps,
+                                                                     const int* __restrict__ dyn_rows) {
     pdl_trigger();
     pdl_wait();
     constexpr int C = NV * 128;
     const int lane = threadIdx.x & 31;
     const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    if (dyn_rows != nullptr) {
+        const int64_t alloc_rows = rows;
+        rows = min(rows, (int64_t)*dyn_rows);
+        const int64_t upto = min(alloc_rows, (rows + 127) / 128 * 128);
+        for (int64_t r = rows + warp; r < upto; r += nwarps)
+            for (int i = 0; i < NV; ++i) reinterpret_cast<uint2*>(y + r * C)[i * 32 + lane] = make_uint2(0u, 0u);
+    }
     float4 wv[NV], bv[NV];
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
@@ -87,7 +103,7 @@ __global__ void __launch_bounds__(256) layernorm_fwd_bf16_vec_kernel(const float
 }
 
 int layernorm_fwd_bf16(const float* x, const float* w, const float* b, __nv_bfloat16* y, int64_t ldy, float* stats,
-                       int64_t rows, int c, float eps, cudaStream_t st) {
+                       int64_t rows, int c, float eps, cudaStream_t st, const int* dyn_rows) {
     PIO_CHECK_ARG(x && w && b && y && c > 0 && ldy >= c, "layernorm_fwd_bf16: bad arguments");
     if (rows == 0) return PIO_OK;
     const int threads = 256;
@@ -96,15 +112,15 @@ int layernorm_fwd_bf16(const float* x, const float* w, const float* b, __nv_bflo
                         ((((uintptr_t)x | (uintptr_t)w | (uintptr_t)b) & 15) == 0) && ((((uintptr_t)y) & 7) == 0);
     if (vec_ok) {
         switch (c / 128) {
-            case 1: PIO_CUDA(launch_pdl(layernorm_fwd_bf16_vec_kernel<1>, dim3(blocks), dim3(threads), 0, st, x, w, b, y, stats, rows, eps)); break;
-            case 2: PIO_CUDA(launch_pdl(layernorm_fwd_bf16_vec_kernel<2>, dim3(blocks), dim3(threads), 0, st, x, w, b, y, stats, rows, eps)); break;
-            case 3: PIO_CUDA(launch_pdl(layernorm_fwd_bf16_vec_kernel<3>, dim3(blocks), dim3(threads), 0, st, x, w, b, y, stats, rows, eps)); break;
-            default: PIO_CUDA(launch_pdl(layernorm_fwd_bf16_vec_kernel<4>, dim3(blocks), dim3(threads), 0, st, x, w, b, y, stats, rows, eps)); break;
+            case 1: PIO_CUDA(launch_pdl(layernorm_fwd_bf16_vec_kernel<1>, dim3(blocks), dim3(threads), 0, st, x, w, b, y, stats, rows, eps, dyn_rows)); break;
+            case 2: PIO_CUDA(launch_pdl(layernorm_fwd_bf16_vec_kernel<2>, dim3(blocks), dim3(threads), 0, st, x, w, b, y, stats, rows, eps, dyn_rows)); break;
+            case 3: PIO_CUDA(launch_pdl(layernorm_fwd_bf16_vec_kernel<3>, dim3(blocks), dim3(threads), 0, st, x, w, b, y, stats, rows, eps, dyn_rows)); break;
+            default: PIO_CUDA(launch_pdl(layernorm_fwd_bf16_vec_kernel<4>, dim3(blocks), dim3(threads), 0, st, x, w, b, y, stats, rows, eps, dyn_rows)); break;
         }
         count_launch();
         return PIO_OK;
     }
-    PIO_CUDA(launch_pdl(layernorm_fwd_bf16_kernel, dim3(blocks), dim3(threads), 0, st, x, w, b, y, ldy, stats, rows, c, eps));
+    PIO_CUDA(launch_pdl(layernorm_fwd_bf16_kernel, dim3(blocks), dim3(threads), 0, st, x, w, b, y, ldy, stats, rows, c, eps, dyn_rows));
     count_launch();
     return PIO_OK;
 }
@@ -114,14 +130,23 @@ template <typename TIn>
 __global__ void __launch_bounds__(256) colsum_partial_kernel(const TIn* __restrict__ src, int64_t ld_src,
                                                              __nv_bfloat16* __restrict__ dst16, int64_t ld_dst,
                                                              float* __restrict__ partial, int64_t rows, int c,
-                                                             int64_t rows_per_chunk, int pad_cols, float* __restrict__ atomic_out) {
+                                                             int64_t rows_per_chunk, int pad_cols, float* __restrict__ atomic_out,
+                                                             const int* __restrict__ dyn_rows) {
     __shared__ float s_part[256];
     pdl_trigger();
     pdl_wait();
     const int col = blockIdx.x * 128 + (threadIdx.x & 127);
     const int sub = threadIdx.x >> 7;
     const int64_t r0 = (int64_t)blockIdx.y * rows_per_chunk;
+    int64_t pad_to = 0;
+    if (dyn_rows != nullptr) {  // device-side row count; the bf16 copy is zero-filled up to the next multiple of 128 rows
+        const int64_t live = min(rows, (int64_t)*dyn_rows);
+        pad_to = min(rows, (live + 127) / 128 * 128);
+        rows = live;
+    }
     const int64_t r1 = min(rows, r0 + rows_per_chunk);
+    if (dst16 && pad_to > rows && col < pad_cols)
+        for (int64_t r = max(rows, r0) + sub; r < min(pad_to, r0 + rows_per_chunk); r += 2) dst16[r * ld_dst + col] = __float2bfloat16(0.f);
     float acc = 0.f;
     if (col < c) {
         for (int64_t r = r0 + sub; r < r1; r += 2) {
@@ -153,7 +178,7 @@ size_t colsum_ws_bytes(int64_t rows, int c) { return align_up((size_t)colsum_chu
 
 template <typename TIn>
 static int colsum_impl(const TIn* src, int64_t ld_src, __nv_bfloat16* dst16, int64_t ld_dst, float* colsum, int accumulate,
-                       int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t st) {
+                       int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t st, const int* dyn_rows) {
     PIO_CHECK_ARG(src && c > 0 && rows >= 0, "colsum: bad arguments");
     if (rows == 0) return PIO_OK;
     const int chunks = colsum_chunks(rows, c);
@@ -170,20 +195,20 @@ static int colsum_impl(const TIn* src, int64_t ld_src, __nv_bfloat16* dst16, int
     const int pad_cols = dst16 ? (int)ld_dst : c;
     dim3 grid((unsigned)cdiv(std::max(pad_cols, c), 128), (unsigned)chunks);
     PIO_CUDA(launch_pdl(colsum_partial_kernel<TIn>, grid, dim3(256), 0, st, src, ld_src, dst16, ld_dst, partial, rows, c,
-                        cdiv(rows, chunks), pad_cols, (colsum && atomic) ? colsum : (float*)nullptr));
+                        cdiv(rows, chunks), pad_cols, (colsum && atomic) ? colsum : (float*)nullptr, dyn_rows));
     count_launch();
     if (colsum && !atomic) PIO_TRY(reduce_partials(partial, chunks, c, colsum, c, nullptr, 0, accumulate, st));
     return PIO_OK;
 }
 
 int cast_colsum_f32(const float* src, int64_t ld_src, __nv_bfloat16* dst16, int64_t ld_dst, float* colsum, int accumulate,
-                    int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t st) {
-    return colsum_impl<float>(src, ld_src, dst16, ld_dst, colsum, accumulate, rows, c, ws, ws_bytes, st);
+                    int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t st, const int* dyn_rows) {
+    return colsum_impl<float>(src, ld_src, dst16, ld_dst, colsum, accumulate, rows, c, ws, ws_bytes, st, dyn_rows);
 }
 
 int colsum_bf16(const __nv_bfloat16* src, int64_t ld_src, float* colsum, int accumulate, int64_t rows, int c, void* ws,
-                size_t ws_bytes, cudaStream_t st) {
-    return colsum_impl<__nv_bfloat16>(src, ld_src, nullptr, 0, colsum, accumulate, rows, c, ws, ws_bytes, st);
+                size_t ws_bytes, cudaStream_t st, const int* dyn_rows) {
+    return colsum_impl<__nv_bfloat16>(src, ld_src, nullptr, 0, colsum, accumulate, rows, c, ws, ws_bytes, st, dyn_rows);
 }
 
 }  // namespace pio

@@ -321,10 +321,11 @@ __global__ void __launch_bounds__(NCH <= 8 ? 512 : 256, NCH <= 16 ? 2 : 1) layer
     const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ stats,
     const float* __restrict__ w, const float* __restrict__ dres, float* __restrict__ dx,
     float* __restrict__ partial, int64_t rows, int c, float* __restrict__ atomic_dw = nullptr,
-    float* __restrict__ atomic_db = nullptr) {
+    float* __restrict__ atomic_db = nullptr, const int* __restrict__ dyn_rows = nullptr) {
     extern __shared__ float s_acc[];  // [warps][2][c]
     pdl_trigger();
     pdl_wait();
+    if (dyn_rows != nullptr) rows = min(rows, (int64_t)*dyn_rows);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
     float gw[NCH], gb[NCH];
 #pragma unroll
@@ -392,10 +393,12 @@ template <int NV>
 __global__ void __launch_bounds__(512, 2) layernorm_bwd_vec_kernel(
     const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ stats,
     const float* __restrict__ w, const float* __restrict__ dres, float* __restrict__ dx,
-    float* __restrict__ partial, int64_t rows, float* __restrict__ atomic_dw, float* __restrict__ atomic_db) {
+    float* __restrict__ partial, int64_t rows, float* __restrict__ atomic_dw, float* __restrict__ atomic_db,
+    const int* __restrict__ dyn_rows) {
     extern __shared__ float s_acc[];  // [warps][2][c]
     pdl_trigger();
     pdl_wait();
+    if (dyn_rows != nullptr) rows = min(rows, (int64_t)*dyn_rows);
     constexpr int C = NV * 128;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
     float4 gw[NV], gb[NV], wv[NV];
@@ -793,9 +796,24 @@ size_t pio_layernorm_bwd_ws_bytes(int64_t rows, int c) {
     return align_up((size_t)ln_bwd_blocks(rows, c) * 2 * c * sizeof(float), 256) + 256;
 }
 
+}  // extern "C"
+namespace pio {
+int layernorm_bwd(const float* dy, const float* x, const float* stats, const float* w, const float* dres, float* dx, float* dw,
+                  float* db, int accumulate, int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t stream,
+                  const int* dyn_rows);
+}
+extern "C" {
 int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const float* w, const float* dres,
                       float* dx, float* dw, float* db, int accumulate, int64_t rows, int c, void* ws, size_t ws_bytes,
                       pio_stream_t stream) {
+    return pio::layernorm_bwd(dy, x, stats, w, dres, dx, dw, db, accumulate, rows, c, ws, ws_bytes, (cudaStream_t)stream, nullptr);
+}
+}  // extern "C"
+
+namespace pio {
+int layernorm_bwd(const float* dy, const float* x, const float* stats, const float* w, const float* dres, float* dx, float* dw,
+                  float* db, int accumulate, int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t stream,
+                  const int* dyn_rows) {
     PIO_CHECK_ARG(dy && x && stats && w && dw && db && c > 0 && rows >= 0, "pio_layernorm_bwd: bad arguments");
     PIO_CHECK_ARG(c <= 1024, "pio_layernorm_bwd: channels %d > 1024 unsupported", c);
     if (rows == 0) return PIO_OK;
@@ -816,9 +834,9 @@ int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const
                         ((((uintptr_t)dy | (uintptr_t)x | (uintptr_t)w | (uintptr_t)dres | (uintptr_t)dx) & 15) == 0);
     if (vec_ok) {  // warps == 16 for these widths; smem = 16 * 2 * c * 4 <= 32 KB
         if (c == 128)
-            PIO_CUDA(launch_pdl(layernorm_bwd_vec_kernel<1>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, adw, adb));
+            PIO_CUDA(launch_pdl(layernorm_bwd_vec_kernel<1>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, adw, adb, dyn_rows));
         else
-            PIO_CUDA(launch_pdl(layernorm_bwd_vec_kernel<2>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, adw, adb));
+            PIO_CUDA(launch_pdl(layernorm_bwd_vec_kernel<2>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, adw, adb, dyn_rows));
         PIO_LAUNCH_CHECK();
         if (atomic) return PIO_OK;
         return reduce_partials(partial, blocks, (int64_t)2 * c, dw, c, db, c, accumulate, st);
@@ -829,7 +847,7 @@ int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const
             PIO_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                           (int)smem));                                                          \
         PIO_CUDA(launch_pdl(layernorm_bwd_kernel<NCH>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, c, adw, \
-                            adb));                                                                              \
+                            adb, dyn_rows));                                                                    \
     } while (0)
     if (c <= 128) PIO_LN_BWD(4);
     else if (c <= 256) PIO_LN_BWD(8);
@@ -841,6 +859,9 @@ int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const
     // partial rows are [dw(c) | db(c)] : reduce both with one launch
     return reduce_partials(partial, blocks, (int64_t)2 * c, dw, c, db, c, accumulate, st);
 }
+}  // namespace pio
+
+extern "C" {
 
 // LayerNorm backward for callers that cannot allocate device memory.
 //

@@ -346,6 +346,16 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
         __syncwarp();
         const int64_t gm0 = (int64_t)m0 + q * 32;
         const int rows_here = (int)min((int64_t)32, (int64_t)m_eff - gm0);  // may be <= 0
+        if (p.dyn_rows != nullptr && p.dyn_axis == 0 && p.c16 != nullptr && rows_here < 32) {
+            // rows between the device-side count and the end of this 128-row tile: zero in the bf16 output, so a later
+            // product over the row axis can read them as operand padding (its k-blocks end at a multiple of 64 rows)
+            const int first = max(rows_here, 0);
+            const int last = (int)min((int64_t)32, (int64_t)p.M - gm0);
+            const int nh0 = n0 + half * (BN / 2);
+            for (int rr = first; rr < last; ++rr)
+                for (int cc = lane; cc < BN / 2; cc += 32)
+                    if (nh0 + cc < p.N) p.c16[(gm0 + rr) * p.ldc16 + nh0 + cc] = __float2bfloat16(0.f);
+        }
         const int nh = n0 + half * HN;
         switch (p.epi_kind) {
             case EPI_F32: epilogue_rows<HN, EPI_F32>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;

@@ -395,6 +395,51 @@ int pio_mlp_bwd(const float* dy, const float* x, float* dx, const pio_mlp_weight
     return mlp_bwd(ctx, dy, x, dx, w, saved, g, accumulate, rows, c, residual);
 }
 
+// ---- decoder on the labelled rows of a masked-LM batch (PIO_MODE_BF16)
+size_t pio_label_compact_ws_bytes(int64_t rows) {
+    return align_up((size_t)std::max<int64_t>(rows, 1) * 4, 256) + align_up((size_t)cdiv(std::max<int64_t>(rows, 1), 1024) * 4, 256) + 512;
+}
+int pio_label_compact(const int64_t* labels, int64_t rows, int64_t classes, int64_t ignore, int32_t* idx, int64_t* labels_c,
+                      int32_t* count, void* ws, size_t ws_bytes, pio_stream_t stream) {
+    PIO_CHECK_ARG(labels && idx && labels_c && count && rows >= 1 && rows < (1ll << 31), "pio_label_compact: bad arguments");
+    Workspace W(ws, ws_bytes);
+    int* pos = (int*)W.take((size_t)rows * 4);
+    int* block_counts = (int*)W.take((size_t)cdiv(rows, 1024) * 4);
+    float* out3 = W.takef(4);
+    if (!pos || !block_counts || !out3) {
+        set_error("pio_label_compact: workspace too small (%zu bytes given)", ws_bytes);
+        return PIO_ERR_WORKSPACE;
+    }
+    return bf::label_compact(labels, rows, classes, ignore, idx, labels_c, count, pos, block_counts, out3, (cudaStream_t)stream);
+}
+int pio_decode_rows_supported(int n, int e, int heads) { return bf::decode_rows_supported(n, e, heads) ? 1 : 0; }
+size_t pio_decode_rows_saved_bytes(int64_t max_rows, int e, int heads) { return bf::decode_rows_saved_bytes(max_rows, e, heads); }
+size_t pio_decode_rows_ws_bytes(int64_t max_rows, int e, int heads) { return bf::decode_rows_ws_bytes(max_rows, e, heads); }
+
+int pio_decode_rows_fwd(const float* queries, const void* kv, const int32_t* idx, const int32_t* count, float* y,
+                        const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved, int64_t max_rows, int l, int batch,
+                        int n, int e, int heads, void* ws, size_t ws_bytes, pio_stream_t stream) {
+    PIO_CHECK_ARG(queries && kv && idx && count && y && attn && mlp && saved && max_rows >= 1 && l >= 1 && batch >= 1,
+                  "pio_decode_rows_fwd: bad arguments");
+    PIO_CHECK_ARG(heads >= 1 && e % heads == 0, "pio_decode_rows_fwd: embed dim %d not divisible by %d heads", e, heads);
+    Ctx ctx(ws, ws_bytes, stream);
+    ctx.dyn = count;
+    return bf::decode_rows_fwd(ctx, queries, kv, idx, y, attn, mlp, saved, max_rows, l, batch, n, e, heads);
+}
+
+int pio_decode_rows_bwd(const float* dy, const void* kv, const int32_t* idx, const int32_t* count, float* dqueries, void* dkv,
+                        const pio_attn_weights* attn, const pio_mlp_weights* mlp, const void* saved, const pio_attn_grads* attn_g,
+                        const pio_mlp_grads* mlp_g, int accumulate, int64_t max_rows, int l, int batch, int n, int e, int heads,
+                        void* ws, size_t ws_bytes, pio_stream_t stream) {
+    PIO_CHECK_ARG(dy && kv && idx && count && dqueries && dkv && attn && mlp && saved && attn_g && mlp_g && max_rows >= 1,
+                  "pio_decode_rows_bwd: bad arguments");
+    PIO_CHECK_ARG(heads >= 1 && e % heads == 0, "pio_decode_rows_bwd: embed dim %d not divisible by %d heads", e, heads);
+    Ctx ctx(ws, ws_bytes, stream);
+    ctx.dyn = count;
+    return bf::decode_rows_bwd(ctx, dy, kv, idx, dqueries, dkv, attn, mlp, saved, attn_g, mlp_g, accumulate, max_rows, l, batch, n, e,
+                               heads);
+}
+
 // ---- kv projection
 size_t pio_kv_project_saved_bytes(int64_t rows, int c_kv, int e, int mode) {
     (void)e;

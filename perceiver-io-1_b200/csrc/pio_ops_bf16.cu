@@ -101,6 +101,7 @@ static int tc_xwT(Ctx& c, const bf16* x, int64_t ldx, const bf16* w, int64_t ldw
     d.a = x; d.b = w; d.m = rows; d.n = n; d.k = k; d.lda = ldx; d.ldb = ldw; d.a_kmajor = 1; d.b_kmajor = 1;
     d.c32 = c32; d.ldc32 = ldc32; d.c16 = c16; d.ldc16 = ldc16;
     d.bias = bias; d.residual = res; d.ldr = ldr; d.act = act; d.aux16 = aux; d.ldaux = ldaux;
+    d.dyn_rows = c.dyn; d.dyn_axis = 0;
     return tc_gemm(c, d);
 }
 // dx (+)= dy16[rows, nout] W16[nout, kin]   (B read MN-major, in place)
@@ -110,6 +111,7 @@ static int tc_dyW(Ctx& c, const bf16* dy, int64_t lddy, const bf16* w, int64_t l
     d.a = dy; d.b = w; d.m = rows; d.n = kin; d.k = nout; d.lda = lddy; d.ldb = ldw; d.a_kmajor = 1; d.b_kmajor = 0;
     d.c32 = c32; d.ldc32 = ldc32; d.c16 = c16; d.ldc16 = ldc16; d.act = act; d.aux16 = aux; d.ldaux = ldaux;
     d.accumulate = accumulate;
+    d.dyn_rows = c.dyn; d.dyn_axis = 0;
     return tc_gemm(c, d);
 }
 // dw[nout, kin] (+)= dy16[rows, nout]^T x16[rows, kin]   (both read MN-major, in place; split-K)
@@ -118,12 +120,16 @@ static int tc_dW(Ctx& c, const bf16* dy, int64_t lddy, const bf16* x, int64_t ld
     pio_gemm_bf16_desc d{};
     d.a = dy; d.b = x; d.m = nout; d.n = kin; d.k = rows; d.lda = lddy; d.ldb = ldx; d.a_kmajor = 0; d.b_kmajor = 0;
     d.c32 = dw; d.ldc32 = kin; d.accumulate = accumulate;
+    if (c.dyn != nullptr) {  // contraction over the live rows only (the operands are zero up to the next multiple of 64)
+        PIO_CHECK_ARG(accumulate == 2, "a device-side row count needs atomic weight-gradient accumulation (accumulate = 2)");
+        d.dyn_rows = c.dyn; d.dyn_axis = 1;
+    }
     if (st == nullptr || st == c.st) return tc_gemm(c, d);
     return gemm_bf16(&d, nullptr, 0, st);  // side stream: atomic accumulation, no scratch
 }
 static int side_colsum(Ctx& c, const Side& sd, const bf16* src, int64_t ld, float* out, int acc, int64_t rows, int cols) {
-    if (sd.active()) return colsum_bf16(src, ld, out, acc, rows, cols, nullptr, 0, sd.stream());
-    return colsum_bf16(src, ld, out, acc, rows, cols, c.rest(), c.rest_bytes(), c.st);
+    if (sd.active()) return colsum_bf16(src, ld, out, acc, rows, cols, nullptr, 0, sd.stream(), c.dyn);
+    return colsum_bf16(src, ld, out, acc, rows, cols, c.rest(), c.rest_bytes(), c.st, c.dyn);
 }
 
 static size_t scratch_bytes(int64_t rows, int64_t nout, int64_t kin) {
@@ -172,7 +178,7 @@ size_t mlp_ws_bytes(int64_t rows, int ch) {
 int mlp_fwd(Ctx& c, const float* x, float* y, const pio_mlp_weights* w, void* saved, int64_t rows, int ch, int residual) {
     PIO_TRY(need_mult8(ch, "channels", "pio_mlp_fwd"));
     MlpSaved s(saved, rows, ch);
-    PIO_TRY(layernorm_fwd_bf16(x, w->ln_w, w->ln_b, s.h0, ch, s.stats, rows, ch, LN_EPS, c.st));
+    PIO_TRY(layernorm_fwd_bf16(x, w->ln_w, w->ln_b, s.h0, ch, s.stats, rows, ch, LN_EPS, c.st, c.dyn));
     PIO_TRY(tc_xwT(c, s.h0, ch, (const bf16*)w->w1, ch, rows, ch, ch, nullptr, 0, s.g, ch, w->b1, nullptr, 0, 1, s.h1, ch));
     PIO_TRY(tc_xwT(c, s.g, ch, (const bf16*)w->w2, ch, rows, ch, ch, y, ch, nullptr, 0, w->b2, residual ? x : nullptr, ch, 0,
                    nullptr, 0, residual ? c.drop_p : 0.f, c.drop_seed + 1));
@@ -190,7 +196,7 @@ int mlp_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_mlp_we
     Side side(c, acc);
     const float* dyb;
     PIO_TRY(branch_grad(c, dy, rows * ch, residual, &dyb, "pio_mlp_bwd"));
-    PIO_TRY(cast_colsum_f32(dyb, ch, dy16, ch, g->b2, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(cast_colsum_f32(dyb, ch, dy16, ch, g->b2, acc, rows, ch, c.rest(), c.rest_bytes(), c.st, c.dyn));
     PIO_TRY(side.fork());
     PIO_TRY(tc_dW(c, dy16, ch, s.g, ch, g->w2, rows, ch, ch, acc, side.stream()));
     PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->w2, ch, rows, ch, ch, nullptr, 0, dh1, ch, 2, s.h1, ch, 0));
@@ -198,8 +204,8 @@ int mlp_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_mlp_we
     PIO_TRY(side_colsum(c, side, dh1, ch, g->b1, acc, rows, ch));
     PIO_TRY(tc_dW(c, dh1, ch, s.h0, ch, g->w1, rows, ch, ch, acc, side.stream()));
     PIO_TRY(tc_dyW(c, dh1, ch, (const bf16*)w->w1, ch, rows, ch, ch, dh0, ch, nullptr, 0, 0, nullptr, 0, 0));
-    PIO_TRY(pio_layernorm_bwd(dh0, x, s.stats, w->ln_w, residual ? dy : nullptr, dx, g->ln_w, g->ln_b, acc, rows, ch,
-                              c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(layernorm_bwd(dh0, x, s.stats, w->ln_w, residual ? dy : nullptr, dx, g->ln_w, g->ln_b, acc, rows, ch,
+                          c.rest(), c.rest_bytes(), c.st, c.dyn));
     PIO_TRY(side.join());
     c.W.off = mark;
     return PIO_OK;
@@ -935,6 +941,361 @@ int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, 
     PIO_LAUNCH_CHECK();
     loss_finalize_kernel<<<1, 1024, 0, c.st>>>(row_loss, count, out3);
     PIO_LAUNCH_CHECK();
+    c.W.off = mark;
+    return PIO_OK;
+}
+
+
+// ---------------------------------------------------------------- decoder on the labelled rows only
+// PerceiverDecoder's cross_attention_layer (reference model.py:229-237: Residual(CrossAttention) then Residual(mlp))
+// for a DYNAMIC subset of the B*K query rows.  Every decoder query is independent of the others (its key / value
+// set is the N latents of its own sample), and in the masked-LM step only the positions that carry a label reach
+// the loss (an ignored position contributes exactly zero to the loss and to every gradient), so the decoder need
+// not touch the other ~85-90 % of the (sample, position) pairs at all.  The labelled pairs are compacted on the
+// device (label_compact; their count never reaches the host), and every kernel below is launched for the worst
+// case (all B*K rows) and clamps / leaves at the device-side count (Ctx::dyn), so the sequence replays from a
+// CUDA graph on any batch.  Row i of every array here is the pair idx[i] = b * l + pos.
+//   * the query row is the learned array's row `pos` (batch independent): gathered, never broadcast;
+//   * attention: one CTA per (sample, head) keeps that sample's K_h, V_h (N x dh, a few KB) in shared memory and
+//     walks the sample's rows (contiguous in the compaction order) one warp per row, fp32 arithmetic — 4*N*E flop
+//     per row, far too little for a tensor-core tile;
+//   * all products with weights are the tcgen05 GEMM with a device-side row count.
+struct DrSaved {
+    float *xq, *stats, *lse, *x1;
+    bf16 *hq, *q, *o16;
+    void* mlp;
+    size_t total;
+    DrSaved(void* p, int64_t rows, int e, int heads) {
+        ByteCarver k{(char*)p, 0};
+        xq = k.f32((size_t)rows * e);
+        stats = k.f32((size_t)rows * 2);
+        hq = k.b16((size_t)rows * e);
+        q = k.b16((size_t)rows * e);
+        o16 = k.b16((size_t)rows * e);
+        lse = k.f32((size_t)rows * heads);
+        x1 = k.f32((size_t)rows * e);
+        mlp = k.take(mlp_saved_bytes(rows, e));
+        total = k.off;
+    }
+};
+size_t decode_rows_saved_bytes(int64_t max_rows, int e, int heads) { return DrSaved(nullptr, max_rows, e, heads).total + 256; }
+size_t decode_rows_ws_bytes(int64_t max_rows, int e, int heads) {
+    return 3 * align_up((size_t)max_rows * e * 2, 256) + 3 * align_up((size_t)max_rows * e * 4, 256) + mlp_ws_bytes(max_rows, e) +
+           scratch_bytes(max_rows, e, e) + 4096;
+}
+bool decode_rows_supported(int n, int e, int heads) {
+    if (heads <= 0 || e % heads != 0) return false;
+    const int dh = e / heads;
+    // K_h, V_h as bf16 plus (backward) their fp32 gradients in one CTA's shared memory
+    return e % 8 == 0 && dh % 8 == 0 && dh <= 128 && n >= 1 && n <= 128 && (size_t)n * (dh + 2) * 2 * 2 + 2 * (size_t)n * dh * 4 + 8 * (size_t)(2 * n + 2 * dh) * 4 + 16 <= 160 * 1024;
+}
+
+__global__ void __launch_bounds__(256) dr_pad_labels_kernel(int64_t* __restrict__ labels_c, const int* __restrict__ count, int64_t rows,
+                                                             int64_t ignore) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)*count + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < rows; i += stride) labels_c[i] = ignore;
+}
+
+// idx (compact -> source row) and the labels of the compacted rows; entries past the count are `ignore`
+int label_compact(const int64_t* labels, int64_t rows, int64_t classes, int64_t ignore, int* idx, int64_t* labels_c, int* count,
+                  int* pos_scratch, int* block_counts, float* out3_scratch, cudaStream_t st) {
+    const unsigned cblocks = (unsigned)cdiv(rows, 1024);
+    LceIndex ix;
+    ix.count = count; ix.idx = idx; ix.pos = pos_scratch; ix.labels = labels_c;
+    lce_count_kernel<<<cblocks, 1024, 0, st>>>(labels, rows, classes, ignore, block_counts);
+    PIO_LAUNCH_CHECK();
+    lce_compact_kernel<<<cblocks, 1024, 0, st>>>(labels, rows, classes, ignore, block_counts, out3_scratch, ix);
+    PIO_LAUNCH_CHECK();
+    dr_pad_labels_kernel<<<(unsigned)std::min<int64_t>(cdiv(rows, 256), 1024), 256, 0, st>>>(labels_c, count, rows, ignore);
+    PIO_LAUNCH_CHECK();
+    return PIO_OK;
+}
+
+// xq[i] = queries[idx[i] % l] for i < count (warp per row)
+__global__ void __launch_bounds__(256) dr_gather_kernel(const float* __restrict__ queries, const int* __restrict__ idx,
+                                                         const int* __restrict__ count, float* __restrict__ xq, int l, int e) {
+    const int n = *count, lane = threadIdx.x & 31;
+    const int warps = gridDim.x * (blockDim.x >> 5);
+    for (int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < n; i += warps) {
+        const float* src = queries + (int64_t)(idx[i] % l) * e;
+        float* dst = xq + (int64_t)i * e;
+        for (int j = lane * 4; j < e; j += 128) *reinterpret_cast<float4*>(dst + j) = *reinterpret_cast<const float4*>(src + j);
+    }
+}
+// dqueries[idx[i] % l] += dxq[i] for i < count
+__global__ void __launch_bounds__(256) dr_scatter_add_kernel(const float* __restrict__ dxq, const int* __restrict__ idx,
+                                                              const int* __restrict__ count, float* __restrict__ dqueries, int l, int e) {
+    const int n = *count, lane = threadIdx.x & 31;
+    const int warps = gridDim.x * (blockDim.x >> 5);
+    for (int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < n; i += warps) {
+        const float* src = dxq + (int64_t)i * e;
+        float* dst = dqueries + (int64_t)(idx[i] % l) * e;
+        for (int j = lane; j < e; j += 32) atomicAdd(dst + j, src[j]);
+    }
+}
+
+__device__ __forceinline__ int dr_lower_bound(const int* __restrict__ idx, int n, int key) {
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (idx[mid] < key) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo;
+}
+
+// Shared-memory layout of one (sample, head): K as bf16 pairs with an odd row pitch (lane = key reads are conflict free),
+// V as bf16 pairs (lane = channel pair), per-warp q / dO (fp32, dh) and p / ds (fp32, n).
+struct DrSmem {
+    uint32_t *k, *v;
+    float *dk, *dv, *wbuf;
+    int kp;  // K row pitch in words
+};
+__device__ __forceinline__ DrSmem dr_carve(uint8_t* base, int n, int dh, bool grads) {
+    DrSmem s;
+    s.kp = dh / 2 + 1;
+    s.k = (uint32_t*)base;
+    s.v = s.k + (size_t)n * s.kp;
+    float* f = (float*)(s.v + (size_t)n * (dh / 2));
+    s.dk = s.dv = nullptr;
+    if (grads) {
+        s.dk = f;
+        s.dv = f + (size_t)n * dh;
+        f += 2 * (size_t)n * dh;
+    }
+    s.wbuf = f;  // [8 warps][2 * n + 2 * dh]
+    return s;
+}
+static size_t dr_smem_bytes(int n, int dh, bool grads) {
+    return (size_t)n * (dh / 2 + 1) * 4 + (size_t)n * (dh / 2) * 4 + (grads ? 2 * (size_t)n * dh * 4 : 0) + 8 * (size_t)(2 * n + 2 * dh) * 4 + 16;
+}
+__device__ __forceinline__ void dr_load_kv(const DrSmem& s, const bf16* __restrict__ kv, int b, int h, int n, int e, int dh) {
+    const int hw = dh / 2;
+    for (int t = threadIdx.x; t < n * hw; t += blockDim.x) {
+        const int key = t / hw, w = t - key * hw;
+        const uint32_t* row = reinterpret_cast<const uint32_t*>(kv + ((int64_t)b * n + key) * 2 * e + h * dh);
+        s.k[key * s.kp + w] = row[w];
+        s.v[key * hw + w] = reinterpret_cast<const uint32_t*>(kv + ((int64_t)b * n + key) * 2 * e + e + h * dh)[w];
+    }
+}
+__device__ __forceinline__ float2 bf2(uint32_t u) {
+    const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&u);
+    return make_float2(__low2float(h), __high2float(h));
+}
+
+// grid (heads, batch): o16[i, h*dh ..] and lse[i, h] for the rows i of sample b
+__global__ void __launch_bounds__(256) dr_attn_fwd_kernel(const bf16* __restrict__ q16, const bf16* __restrict__ kv, const int* __restrict__ idx,
+                                                           const int* __restrict__ count, bf16* __restrict__ o16, float* __restrict__ lse,
+                                                           int l, int n, int e, int heads, float scale, int64_t max_rows) {
+    extern __shared__ uint8_t dr_raw[];
+    const int h = blockIdx.x, b = blockIdx.y, dh = e / heads, hw = dh / 2;
+    const int cnt = *count;
+    const int lo = dr_lower_bound(idx, cnt, b * l), hi = dr_lower_bound(idx, cnt, (b + 1) * l);
+    if (h == 0 && b == 0) {  // rows between the count and the next multiple of 128: zero (operand padding of dWo = dY^T O)
+        const int64_t upto = min(max_rows, ((int64_t)cnt + 127) / 128 * 128);
+        for (int64_t t = (int64_t)cnt * e + threadIdx.x; t < upto * e; t += blockDim.x) o16[t] = __float2bfloat16(0.f);
+    }
+    if (lo >= hi) return;
+    const DrSmem s = dr_carve(dr_raw, n, dh, false);
+    dr_load_kv(s, kv, b, h, n, e, dh);
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    float* qs = s.wbuf + (size_t)wid * (2 * n + 2 * dh);
+    float* ps = qs + 2 * dh;
+    for (int i = lo + wid; i < hi; i += 8) {
+        const bf16* qrow = q16 + (int64_t)i * e + h * dh;
+        for (int d = lane; d < dh; d += 32) qs[d] = __bfloat162float(qrow[d]) * scale;
+        __syncwarp();
+        float mx = -INFINITY;
+        for (int key = lane; key < n; key += 32) {
+            float acc = 0.f;
+            const uint32_t* kr = s.k + key * s.kp;
+            for (int w = 0; w < hw; ++w) {
+                const float2 kk = bf2(kr[w]);
+                acc = fmaf(qs[2 * w], kk.x, fmaf(qs[2 * w + 1], kk.y, acc));
+            }
+            ps[key] = acc;
+            mx = fmaxf(mx, acc);
+        }
+        mx = warp_max(mx);
+        float sum = 0.f;
+        for (int key = lane; key < n; key += 32) {
+            const float pv = __expf(ps[key] - mx);
+            ps[key] = pv;
+            sum += pv;
+        }
+        sum = warp_sum(sum);
+        __syncwarp();
+        const float inv = 1.0f / sum;
+        for (int w = lane; w < hw; w += 32) {
+            float a0 = 0.f, a1 = 0.f;
+            for (int key = 0; key < n; ++key) {
+                const float2 vv = bf2(s.v[key * hw + w]);
+                a0 = fmaf(ps[key], vv.x, a0);
+                a1 = fmaf(ps[key], vv.y, a1);
+            }
+            __nv_bfloat162 o2 = __floats2bfloat162_rn(a0 * inv, a1 * inv);
+            reinterpret_cast<uint32_t*>(o16 + (int64_t)i * e + h * dh)[w] = *reinterpret_cast<uint32_t*>(&o2);
+        }
+        if (lane == 0) lse[(int64_t)i * heads + h] = mx + __logf(sum);
+        __syncwarp();
+    }
+}
+
+// grid (heads, batch): dq16 rows of sample b, and dK_h / dV_h of (b, h) as bf16 into dkv (B, N, 2E); P recomputed from lse
+__global__ void __launch_bounds__(256) dr_attn_bwd_kernel(const bf16* __restrict__ q16, const bf16* __restrict__ kv, const bf16* __restrict__ o16,
+                                                           const bf16* __restrict__ do16, const float* __restrict__ lse,
+                                                           const int* __restrict__ idx, const int* __restrict__ count,
+                                                           bf16* __restrict__ dq16, bf16* __restrict__ dkv, int l, int n, int e, int heads,
+                                                           float scale, int64_t max_rows) {
+    extern __shared__ uint8_t dr_raw[];
+    const int h = blockIdx.x, b = blockIdx.y, dh = e / heads, hw = dh / 2;
+    const int cnt = *count;
+    const int lo = dr_lower_bound(idx, cnt, b * l), hi = dr_lower_bound(idx, cnt, (b + 1) * l);
+    if (h == 0 && b == 0) {
+        const int64_t upto = min(max_rows, ((int64_t)cnt + 127) / 128 * 128);
+        for (int64_t t = (int64_t)cnt * e + threadIdx.x; t < upto * e; t += blockDim.x) dq16[t] = __float2bfloat16(0.f);
+    }
+    const DrSmem s = dr_carve(dr_raw, n, dh, true);
+    for (int t = threadIdx.x; t < 2 * n * dh; t += blockDim.x) s.dk[t] = 0.f;  // dk and dv are adjacent
+    if (lo < hi) dr_load_kv(s, kv, b, h, n, e, dh);
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    float* qs = s.wbuf + (size_t)wid * (2 * n + 2 * dh);  // q * scale
+    float* gs = qs + dh;                                   // dO
+    float* ps = qs + 2 * dh;                               // p
+    float* dss = ps + n;                                   // ds (gradient of the scaled score)
+    for (int i = lo + wid; i < hi; i += 8) {
+        const int64_t off = (int64_t)i * e + h * dh;
+        float delta = 0.f;
+        for (int d = lane; d < dh; d += 32) {
+            qs[d] = __bfloat162float(q16[off + d]) * scale;
+            const float g = __bfloat162float(do16[off + d]);
+            gs[d] = g;
+            delta = fmaf(g, __bfloat162float(o16[off + d]), delta);
+        }
+        delta = warp_sum(delta);
+        const float lse_i = lse[(int64_t)i * heads + h];
+        __syncwarp();
+        for (int key = lane; key < n; key += 32) {
+            float sc = 0.f, dp = 0.f;
+            const uint32_t* kr = s.k + key * s.kp;
+            const uint32_t* vr = s.v + key * hw;
+            for (int w = 0; w < hw; ++w) {
+                const float2 kk = bf2(kr[w]), vv = bf2(vr[w]);
+                sc = fmaf(qs[2 * w], kk.x, fmaf(qs[2 * w + 1], kk.y, sc));
+                dp = fmaf(gs[2 * w], vv.x, fmaf(gs[2 * w + 1], vv.y, dp));
+            }
+            const float pv = __expf(sc - lse_i);
+            ps[key] = pv;
+            dss[key] = pv * (dp - delta);
+        }
+        __syncwarp();
+        // dV[key] += p dO ; dK[key] += ds * scale * q (qs carries the scale): lane = channel, so the shared-memory
+        // atomics of a warp hit consecutive banks; other warps add to the same tile
+        for (int key = 0; key < n; ++key) {
+            const float pv = ps[key], ds = dss[key];
+            for (int d = lane; d < dh; d += 32) {
+                atomicAdd(&s.dv[key * dh + d], pv * gs[d]);
+                atomicAdd(&s.dk[key * dh + d], ds * qs[d]);
+            }
+        }
+        for (int w = lane; w < hw; w += 32) {  // dq = sum_key ds * scale * K[key]
+            float a0 = 0.f, a1 = 0.f;
+            for (int key = 0; key < n; ++key) {
+                const float2 kk = bf2(s.k[key * s.kp + w]);
+                const float dsk = dss[key] * scale;
+                a0 = fmaf(dsk, kk.x, a0);
+                a1 = fmaf(dsk, kk.y, a1);
+            }
+            __nv_bfloat162 o2 = __floats2bfloat162_rn(a0, a1);
+            reinterpret_cast<uint32_t*>(dq16 + off)[w] = *reinterpret_cast<uint32_t*>(&o2);
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < n * hw; t += blockDim.x) {
+        const int key = t / hw, w = t - key * hw;
+        __nv_bfloat162 k2 = __floats2bfloat162_rn(s.dk[key * dh + 2 * w], s.dk[key * dh + 2 * w + 1]);
+        __nv_bfloat162 v2 = __floats2bfloat162_rn(s.dv[key * dh + 2 * w], s.dv[key * dh + 2 * w + 1]);
+        bf16* row = dkv + ((int64_t)b * n + key) * 2 * e;
+        reinterpret_cast<uint32_t*>(row + h * dh)[w] = *reinterpret_cast<uint32_t*>(&k2);
+        reinterpret_cast<uint32_t*>(row + e + h * dh)[w] = *reinterpret_cast<uint32_t*>(&v2);
+    }
+}
+
+static int dr_configure(int n, int dh) {
+    static std::mutex mu;
+    static size_t configured[64] = {};
+    const size_t need = dr_smem_bytes(n, dh, true);
+    int dev = 0;
+    PIO_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev >= 0 && dev < 64 && configured[dev] < need) {
+        PIO_CUDA(cudaFuncSetAttribute(dr_attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
+        PIO_CUDA(cudaFuncSetAttribute(dr_attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
+        configured[dev] = need;
+    }
+    return PIO_OK;
+}
+
+int decode_rows_fwd(Ctx& c, const float* queries, const void* kv, const int* idx, float* y, const pio_attn_weights* aw,
+                    const pio_mlp_weights* mw, void* saved, int64_t max_rows, int l, int batch, int n, int e, int heads) {
+    const char* who = "pio_decode_rows_fwd";
+    PIO_CHECK_ARG(c.dyn != nullptr, "%s: needs the device-side row count", who);
+    PIO_CHECK_ARG(decode_rows_supported(n, e, heads), "%s: unsupported shape (n %d, e %d, heads %d)", who, n, e, heads);
+    PIO_CHECK_ARG(max_rows == (int64_t)batch * l && max_rows < (1ll << 31), "%s: max_rows must be batch * l", who);
+    DrSaved s(saved, max_rows, e, heads);
+    const int dh = e / heads;
+    PIO_TRY(dr_configure(n, dh));
+    const int row_blocks = (int)std::min<int64_t>(cdiv(max_rows, 8), (int64_t)num_sms() * 8);
+    dr_gather_kernel<<<row_blocks, 256, 0, c.st>>>(queries, idx, c.dyn, s.xq, l, e);
+    PIO_LAUNCH_CHECK();
+    PIO_TRY(layernorm_fwd_bf16(s.xq, aw->ln_w, aw->ln_b, s.hq, e, s.stats, max_rows, e, LN_EPS, c.st, c.dyn));
+    PIO_TRY(tc_xwT(c, s.hq, e, (const bf16*)aw->wq, e, max_rows, e, e, nullptr, 0, s.q, e, aw->bq, nullptr, 0, 0, nullptr, 0));
+    dr_attn_fwd_kernel<<<dim3((unsigned)heads, (unsigned)batch), 256, dr_smem_bytes(n, dh, false), c.st>>>(
+        s.q, (const bf16*)kv, idx, c.dyn, s.o16, s.lse, l, n, e, heads, 1.0f / sqrtf((float)dh), max_rows);
+    PIO_LAUNCH_CHECK();
+    PIO_TRY(tc_xwT(c, s.o16, e, (const bf16*)aw->wo, e, max_rows, e, e, s.x1, e, nullptr, 0, aw->bo, s.xq, e, 0, nullptr, 0));
+    PIO_TRY(mlp_fwd(c, s.x1, y, mw, s.mlp, max_rows, e, 1));
+    return PIO_OK;
+}
+
+int decode_rows_bwd(Ctx& c, const float* dy, const void* kv, const int* idx, float* dqueries, void* dkv, const pio_attn_weights* aw,
+                    const pio_mlp_weights* mw, const void* saved, const pio_attn_grads* ag, const pio_mlp_grads* mg, int acc,
+                    int64_t max_rows, int l, int batch, int n, int e, int heads) {
+    const char* who = "pio_decode_rows_bwd";
+    PIO_CHECK_ARG(c.dyn != nullptr && acc == 2, "%s: needs the device-side row count and atomic gradient accumulation", who);
+    PIO_CHECK_ARG(decode_rows_supported(n, e, heads), "%s: unsupported shape (n %d, e %d, heads %d)", who, n, e, heads);
+    DrSaved s((void*)saved, max_rows, e, heads);
+    const int dh = e / heads;
+    PIO_TRY(dr_configure(n, dh));
+    const size_t mark = c.W.off;
+    PIO_TAKE_BYTES(float, dx1, c, (size_t)max_rows * e * 4, who);
+    PIO_TAKE_BYTES(bf16, dy16, c, (size_t)max_rows * e * 2, who);
+    PIO_TAKE_BYTES(bf16, d_o16, c, (size_t)max_rows * e * 2, who);
+    PIO_TAKE_BYTES(bf16, dq16, c, (size_t)max_rows * e * 2, who);
+    PIO_TAKE_BYTES(float, dhq, c, (size_t)max_rows * e * 4, who);
+    PIO_TAKE_BYTES(float, dxq, c, (size_t)max_rows * e * 4, who);
+    PIO_TRY(mlp_bwd(c, dy, s.x1, dx1, mw, s.mlp, mg, acc, max_rows, e, 1));
+    Side side(c, acc);
+    PIO_TRY(cast_colsum_f32(dx1, e, dy16, e, ag->bo, acc, max_rows, e, c.rest(), c.rest_bytes(), c.st, c.dyn));
+    PIO_TRY(side.fork());
+    PIO_TRY(tc_dW(c, dy16, e, s.o16, e, ag->wo, max_rows, e, e, acc, side.stream()));
+    PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)aw->wo, e, max_rows, e, e, nullptr, 0, d_o16, e, 0, nullptr, 0, 0));
+    dr_attn_bwd_kernel<<<dim3((unsigned)heads, (unsigned)batch), 256, dr_smem_bytes(n, dh, true), c.st>>>(
+        s.q, (const bf16*)kv, s.o16, d_o16, s.lse, idx, c.dyn, dq16, (bf16*)dkv, l, n, e, heads, 1.0f / sqrtf((float)dh), max_rows);
+    PIO_LAUNCH_CHECK();
+    PIO_TRY(side.fork());
+    PIO_TRY(side_colsum(c, side, dq16, e, ag->bq, acc, max_rows, e));
+    PIO_TRY(tc_dW(c, dq16, e, s.hq, e, ag->wq, max_rows, e, e, acc, side.stream()));
+    PIO_TRY(tc_dyW(c, dq16, e, (const bf16*)aw->wq, e, max_rows, e, e, dhq, e, nullptr, 0, 0, nullptr, 0, 0));
+    PIO_TRY(layernorm_bwd(dhq, s.xq, s.stats, aw->ln_w, dx1, dxq, ag->ln_w, ag->ln_b, acc, max_rows, e, c.rest(), c.rest_bytes(), c.st,
+                          c.dyn));
+    const int row_blocks = (int)std::min<int64_t>(cdiv(max_rows, 8), (int64_t)num_sms() * 8);
+    dr_scatter_add_kernel<<<row_blocks, 256, 0, c.st>>>(dxq, idx, c.dyn, dqueries, l, e);
+    PIO_LAUNCH_CHECK();
+    PIO_TRY(side.join());
     c.W.off = mark;
     return PIO_OK;
 }

@@ -28,13 +28,18 @@ int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream
 int cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_src, int64_t ld_dst, cudaStream_t st);
 
 // bf16 helpers (pio_bf16_aux.cu)
+// (dyn_rows: optional DEVICE-side row count <= rows; rows between it and the next multiple of 128 of every bf16 output
+//  are zero-filled so they can serve as operand padding of a product over the row axis)
 int layernorm_fwd_bf16(const float* x, const float* w, const float* b, __nv_bfloat16* y, int64_t ldy, float* stats,
-                       int64_t rows, int c, float eps, cudaStream_t st);
+                       int64_t rows, int c, float eps, cudaStream_t st, const int* dyn_rows = nullptr);
+int layernorm_bwd(const float* dy, const float* x, const float* stats, const float* w, const float* dres, float* dx, float* dw,
+                  float* db, int accumulate, int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t st,
+                  const int* dyn_rows = nullptr);
 // dst16 (optional) = bf16(src); colsum (optional, c floats) (+)= column sums of src.  scratch: colsum_ws_bytes
 int cast_colsum_f32(const float* src, int64_t ld_src, __nv_bfloat16* dst16, int64_t ld_dst, float* colsum, int accumulate,
-                    int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t st);
+                    int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t st, const int* dyn_rows = nullptr);
 int colsum_bf16(const __nv_bfloat16* src, int64_t ld_src, float* colsum, int accumulate, int64_t rows, int c, void* ws,
-                size_t ws_bytes, cudaStream_t st);
+                size_t ws_bytes, cudaStream_t st, const int* dyn_rows = nullptr);
 size_t colsum_ws_bytes(int64_t rows, int c);
 
 constexpr float LN_EPS = 1e-5f;  // nn.LayerNorm default, used everywhere in the reference
@@ -45,6 +50,9 @@ struct Ctx {
     // dropout of the operator being run (0 = off): site seed+0 = attention probabilities, seed+1 = Residual
     float drop_p = 0.f;
     uint64_t drop_seed = 0;
+    // optional DEVICE-side row count of the operator's activations (<= the row count passed by the host): every kernel is
+    // launched for the host's worst case and leaves / clamps at the device count (the labelled-row decoder of the MLM step)
+    const int* dyn = nullptr;
     Ctx(void* ws, size_t n, pio_stream_t s) : st((cudaStream_t)s), W(ws, n) {}
     Ctx(void* ws, size_t n, pio_stream_t s, const pio_dropout* d) : st((cudaStream_t)s), W(ws, n) {
         if (d != nullptr && d->p > 0.f) {
@@ -133,6 +141,16 @@ size_t linear_ws_bytes(int64_t rows, int c_in, int64_t c_out);
 int linear_fwd(Ctx& c, const float* x, const float* w16, const float* b, float* y, int64_t rows, int c_in, int64_t c_out);
 int linear_bwd(Ctx& c, const float* dy, const float* x, const float* w16, float* dx, float* dw, float* db, int acc, int64_t rows,
                int c_in, int64_t c_out);
+size_t decode_rows_saved_bytes(int64_t max_rows, int e, int heads);
+size_t decode_rows_ws_bytes(int64_t max_rows, int e, int heads);
+bool decode_rows_supported(int n, int e, int heads);
+int label_compact(const int64_t* labels, int64_t rows, int64_t classes, int64_t ignore, int* idx, int64_t* labels_c, int* count,
+                  int* pos_scratch, int* block_counts, float* out3_scratch, cudaStream_t st);
+int decode_rows_fwd(Ctx& c, const float* queries, const void* kv, const int* idx, float* y, const pio_attn_weights* aw,
+                    const pio_mlp_weights* mw, void* saved, int64_t max_rows, int l, int batch, int n, int e, int heads);
+int decode_rows_bwd(Ctx& c, const float* dy, const void* kv, const int* idx, float* dqueries, void* dkv, const pio_attn_weights* aw,
+                    const pio_mlp_weights* mw, const void* saved, const pio_attn_grads* ag, const pio_mlp_grads* mg, int acc,
+                    int64_t max_rows, int l, int batch, int n, int e, int heads);
 size_t linear_ce_ws_bytes(int64_t rows, int c_in, int64_t classes);
 int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, const int64_t* labels, float* out3, float* dx,
                       float* dw, float* db, int64_t rows, int c_in, int64_t classes, int64_t ignore);

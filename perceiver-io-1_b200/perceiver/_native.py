@@ -130,6 +130,15 @@ _SIGNATURES = {
     "pio_latent_block_bwd": (c_int, [P, P, P, POINTER(AttnWeights), POINTER(MlpWeights), P, POINTER(AttnWeights),
                                      POINTER(MlpWeights), c_int, c_int, c_int, c_int, c_int, c_int, POINTER(Dropout), c_int, P,
                                      c_size_t, P]),
+    "pio_label_compact_ws_bytes": (c_size_t, [c_int64]),
+    "pio_label_compact": (c_int, [P, c_int64, c_int64, c_int64, P, P, P, P, c_size_t, P]),
+    "pio_decode_rows_supported": (c_int, [c_int, c_int, c_int]),
+    "pio_decode_rows_saved_bytes": (c_size_t, [c_int64, c_int, c_int]),
+    "pio_decode_rows_ws_bytes": (c_size_t, [c_int64, c_int, c_int]),
+    "pio_decode_rows_fwd": (c_int, [P, P, P, P, P, POINTER(AttnWeights), POINTER(MlpWeights), P, c_int64, c_int, c_int, c_int, c_int,
+                                    c_int, P, c_size_t, P]),
+    "pio_decode_rows_bwd": (c_int, [P, P, P, P, P, P, POINTER(AttnWeights), POINTER(MlpWeights), P, POINTER(AttnWeights),
+                                    POINTER(MlpWeights), c_int, c_int64, c_int, c_int, c_int, c_int, c_int, P, c_size_t, P]),
     "pio_linear_ws_bytes": (c_size_t, [c_int64, c_int, c_int64, c_int]),
     "pio_linear_fwd": (c_int, [P, P, P, P, c_int64, c_int, c_int64, c_int, P, c_size_t, P]),
     "pio_linear_ce_ws_bytes": (c_size_t, [c_int64, c_int, c_int64, c_int]),

@@ -844,6 +844,92 @@ class LatentBlockFn(torch.autograd.Function):
         return _out(dx, None, None, None, *grads)
 
 
+def label_compact(labels, classes, ignore_index=-100):
+    """Device-side compaction of the labelled positions of a masked-LM batch: -> (idx int32 (R,), labels_c int64 (R,),
+    count int32 (1,)) with R = labels.numel(); idx[i] = flat position of the i-th labelled pair (stable order),
+    labels_c[i] its label for i < count and ``ignore_index`` beyond.  The count stays on the device."""
+    labels = _c(labels, torch.int64)
+    rows = labels.numel()
+    dev = labels.device
+    idx = torch.empty(rows, dtype=torch.int32, device=dev)
+    labels_c = torch.empty(rows, dtype=torch.int64, device=dev)
+    count = torch.empty(1, dtype=torch.int32, device=dev)
+    L = N.lib()
+    ws = N.workspace(L.pio_label_compact_ws_bytes(rows), dev)
+    N.check(L.pio_label_compact(labels.data_ptr(), rows, int(classes), int(ignore_index), idx.data_ptr(), labels_c.data_ptr(),
+                                count.data_ptr(), ws.data_ptr(), ws.numel(), N.stream_ptr(dev)), "pio_label_compact")
+    return idx, labels_c, count
+
+
+def decode_rows_supported(n, e, heads):
+    return get_compute_mode() == N.MODE_BF16 and bool(N.lib().pio_decode_rows_supported(int(n), int(e), int(heads)))
+
+
+class DecodeRowsFn(torch.autograd.Function):
+    """PerceiverDecoder.cross_attention (reference model.py:203-206, :229-237) for the labelled (sample, position) pairs
+    only: -> (B*l, E) whose first ``count`` rows are the decoder outputs of the pairs ``idx`` (the rest is never read).
+    bf16 mode, dropout 0.  Inputs after ``l``: q_norm weight / bias, in_proj_bias, packed in_proj_weight or q_proj_weight,
+    out_proj weight / bias, heads, then the six tensors of the layer's mlp."""
+
+    @staticmethod
+    def forward(ctx, queries, kv, idx, count, l, ln_w, ln_b, bias, w_packed, w_q, wo, bo, heads, m_ln_w, m_ln_b, w1, b1, w2, b2):
+        queries, kv = _c(queries), _c(kv, torch.bfloat16)
+        ln_w, ln_b, bias, wo, bo = _c(ln_w), _c(ln_b), _c(bias), _c(wo), _c(bo)
+        w_packed = _c(w_packed) if w_packed is not None else None
+        w_q = _c(w_q) if w_q is not None else None
+        mlp_params = [_c(p) for p in (m_ln_w, m_ln_b, w1, b1, w2, b2)]
+        b, n, e2 = kv.shape
+        e = e2 // 2
+        max_rows = b * l
+        if idx.numel() != max_rows or queries.shape[1] != e or queries.shape[0] < l:
+            raise ValueError("DecodeRowsFn: idx / queries do not match the batch")
+        mode = N.MODE_BF16
+        L = N.lib()
+        dev = kv.device
+        mats = (_mat(w_packed, mode), _mat(w_q, mode), _mat(wo, mode))
+        wq, _, _, bq, _, _ = _mha_ptrs(mats[0], mats[1], None, None, bias, e)
+        aw = N.attn_struct(ln_w=ln_w, ln_b=ln_b, wq=wq, bq=bq, wo=mats[2], bo=bo)
+        mops = _mlp_operands(mlp_params, mode)
+        mw = N.mlp_struct(**dict(zip(N.MlpWeights._names, mops)))
+        saved = _saved(L.pio_decode_rows_saved_bytes(max_rows, e, heads), dev)
+        ws = N.workspace(L.pio_decode_rows_ws_bytes(max_rows, e, heads), dev)
+        y = torch.empty(max_rows, e, dtype=torch.float32, device=dev)
+        N.check(L.pio_decode_rows_fwd(queries.data_ptr(), kv.data_ptr(), idx.data_ptr(), count.data_ptr(), y.data_ptr(), byref(aw),
+                                      byref(mw), saved.data_ptr(), max_rows, l, b, n, e, heads, ws.data_ptr(), ws.numel(),
+                                      N.stream_ptr(dev)), "pio_decode_rows_fwd")
+        ctx.save_for_backward(queries, kv, idx, count, ln_w, ln_b, bias, w_packed, w_q, wo, bo, *mlp_params)
+        ctx.structs, ctx.keep = (aw, mw), (mats, mops)
+        ctx.saved_buf = saved
+        ctx.meta = (max_rows, l, b, n, e, heads)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        queries, kv, idx, count, ln_w, ln_b, bias, w_packed, w_q, wo, bo, *mlp_params = ctx.saved_tensors
+        max_rows, l, b, n, e, heads = ctx.meta
+        dy = _c(dy)
+        L = N.lib()
+        dev = kv.device
+        need = ctx.needs_input_grad
+        params = (queries, ln_w, ln_b, bias, w_packed, w_q, wo, bo, *mlp_params)
+        needs = (need[0],) + tuple(need[5:12]) + tuple(need[13:19])
+        grads, accf = _grads_like(params, N.MODE_BF16, needs)
+        dqueries, dln_w, dln_b, dbias, dwp, dwq, dwo, dbo, *mg = grads
+        dkv = torch.empty_like(kv)
+        gwq, _, _, gbq, _, _ = _mha_ptrs(dwp, dwq, None, None, dbias, e)
+        ag = N.attn_struct(ln_w=dln_w, ln_b=dln_b, wq=gwq, bq=gbq, wo=dwo, bo=dbo)
+        mgs = N.mlp_struct(**dict(zip(N.MlpWeights._names, mg)))
+        aw, mw = ctx.structs
+        ws = N.workspace(L.pio_decode_rows_ws_bytes(max_rows, e, heads), dev)
+        N.check(L.pio_decode_rows_bwd(dy.data_ptr(), kv.data_ptr(), idx.data_ptr(), count.data_ptr(), dqueries.data_ptr(),
+                                      dkv.data_ptr(), byref(aw), byref(mw), ctx.saved_buf.data_ptr(), byref(ag), byref(mgs), accf,
+                                      max_rows, l, b, n, e, heads, ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
+                "pio_decode_rows_bwd")
+        ctx.saved_buf = None
+        return _out(dqueries, dkv, None, None, None, dln_w, dln_b, dbias, dwp, dwq, dwo, dbo, None, *mg)
+
+
 class LinearFn(torch.autograd.Function):
     """nn.Linear of the output adapters (reference adapter.py:146-149)."""
 

@@ -296,10 +296,45 @@ class PerceiverMLM(nn.Module):
             if x_labels is None:
                 raise ValueError('return_loss=True needs labels: masking=True, or masking=False with labels=...')
             lin = self.decoder.output_adapter.linear
+            hidden_c = self._decode_labelled(x_latent, x_labels, l)
+            if hidden_c is not None:  # decoder evaluated for the labelled (sample, position) pairs only
+                hidden, labels_c = hidden_c
+                return F.linear_cross_entropy(hidden, lin.weight, lin.bias, labels_c), x_labels
             hidden = self.decoder.decode(x_latent, num_queries=l)
             return F.linear_cross_entropy(hidden, lin.weight, lin.bias, x_labels), x_labels
         x_logits = self.decoder(x_latent, pad_mask, num_queries=l)
         return x_logits, x_labels
+
+
+    def _decode_labelled(self, x_latent, labels, l):
+        """The training loss only reads the decoder at the positions that carry a label (an ignored position adds exactly
+        zero to the loss and to every gradient) and each decoder query is independent of the others (reference
+        model.py:229-237), so in bf16 mode the decoder layer runs on those ~10-15 % of the (sample, position) pairs only
+        (functional.DecodeRowsFn; compacted on the device, count never read by the host).  -> (rows, labels of the rows),
+        or None when the layer's shape / mode / dropout is outside what that operator covers."""
+        import os
+        dec = self.decoder
+        if not (torch.is_grad_enabled() and F.get_compute_mode() == F.N.MODE_BF16) or os.environ.get("PIO_NO_COMPACT_DECODE"):
+            return None
+        layer = dec.cross_attention
+        res_att, res_mlp = layer[0], layer[1]
+        if not (isinstance(res_att, Residual) and isinstance(res_att.module, CrossAttention) and isinstance(res_mlp.module, MLP)):
+            return None
+        if _active_p(res_att, res_att.dropout_p) > 0.0 or _active_p(res_mlp, res_mlp.dropout_p) > 0.0:
+            return None
+        b, *d = x_latent.shape
+        if tuple(d) != tuple(dec.latent_shape):
+            raise ValueError(f'Latent shape {tuple(d)} different from required shape {dec.latent_shape}')
+        ca = res_att.module
+        a = ca.attention.attention
+        if not F.decode_rows_supported(d[0], a.embed_dim, a.num_heads) or dec.output.shape[0] < l:
+            return None
+        kv = ca.project_kv(x_latent)
+        idx, labels_c, count = F.label_compact(labels, dec.output_adapter.linear.weight.shape[0])
+        w_packed, w_q, _, _ = a.packed()
+        hidden = F.DecodeRowsFn.apply(dec.output, kv, idx, count, l, ca.q_norm.weight, ca.q_norm.bias, a.in_proj_bias, w_packed, w_q,
+                                      a.out_proj.weight, a.out_proj.bias, a.num_heads, *res_mlp.module._params())
+        return hidden, labels_c
 
 
 class PerceiverIO(Sequential):
