@@ -137,16 +137,19 @@ __global__ void __launch_bounds__(256) colsum_partial_kernel(const TIn* __restri
     pdl_wait();
     const int col = blockIdx.x * 128 + (threadIdx.x & 127);
     const int sub = threadIdx.x >> 7;
-    const int64_t r0 = (int64_t)blockIdx.y * rows_per_chunk;
-    int64_t pad_to = 0;
-    if (dyn_rows != nullptr) {  // device-side row count; the bf16 copy is zero-filled up to the next multiple of 128 rows
+    if (dyn_rows != nullptr) {
+        // device-side row count: the live rows are re-divided among the chunks (with the host's split the few live rows of
+        // a mostly empty buffer all fell to the first chunks), and the bf16 copy is zero-filled from the count up to the
+        // next multiple of 128 rows (operand padding) by the first chunk
         const int64_t live = min(rows, (int64_t)*dyn_rows);
-        pad_to = min(rows, (live + 127) / 128 * 128);
+        const int64_t pad_to = min(rows, (live + 127) / 128 * 128);
         rows = live;
+        rows_per_chunk = max((int64_t)2, (live + gridDim.y - 1) / gridDim.y);
+        if (dst16 && blockIdx.y == 0 && col < pad_cols)
+            for (int64_t r = live + sub; r < pad_to; r += 2) dst16[r * ld_dst + col] = __float2bfloat16(0.f);
     }
+    const int64_t r0 = (int64_t)blockIdx.y * rows_per_chunk;
     const int64_t r1 = min(rows, r0 + rows_per_chunk);
-    if (dst16 && pad_to > rows && col < pad_cols)
-        for (int64_t r = max(rows, r0) + sub; r < min(pad_to, r0 + rows_per_chunk); r += 2) dst16[r * ld_dst + col] = __float2bfloat16(0.f);
     float acc = 0.f;
     if (col < c) {
         for (int64_t r = r0 + sub; r < r1; r += 2) {

@@ -963,6 +963,7 @@ int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, 
 struct DrSaved {
     float *xq, *stats, *lse, *x1;
     bf16 *hq, *q, *o16;
+    int* seg;  // [batch + 1] first compact row of every sample (at most rows + 1 entries)
     void* mlp;
     size_t total;
     DrSaved(void* p, int64_t rows, int e, int heads) {
@@ -974,6 +975,7 @@ struct DrSaved {
         o16 = k.b16((size_t)rows * e);
         lse = k.f32((size_t)rows * heads);
         x1 = k.f32((size_t)rows * e);
+        seg = (int*)k.take((size_t)(rows + 1) * 4);
         mlp = k.take(mlp_saved_bytes(rows, e));
         total = k.off;
     }
@@ -987,7 +989,8 @@ bool decode_rows_supported(int n, int e, int heads) {
     if (heads <= 0 || e % heads != 0) return false;
     const int dh = e / heads;
     // K_h, V_h as bf16 plus (backward) their fp32 gradients in one CTA's shared memory
-    return e % 8 == 0 && dh % 8 == 0 && dh <= 128 && n >= 1 && n <= 128 && (size_t)n * (dh + 2) * 2 * 2 + 2 * (size_t)n * dh * 4 + 8 * (size_t)(2 * n + 2 * dh) * 4 + 16 <= 160 * 1024;
+    // K_h, V_h (bf16) and the per-warp row buffers of one CTA in shared memory; keys / channels per warp / lane in registers
+    return e % 8 == 0 && dh % 8 == 0 && dh <= 128 && n >= 1 && n <= 128;
 }
 
 __global__ void __launch_bounds__(256) dr_pad_labels_kernel(int64_t* __restrict__ labels_c, const int* __restrict__ count, int64_t rows,
@@ -1043,39 +1046,39 @@ __device__ __forceinline__ int dr_lower_bound(const int* __restrict__ idx, int n
     }
     return lo;
 }
+// seg[b] = first compact row of sample b (b = 0 .. batch): one chain of dependent loads per sample here instead of two
+// per CTA in the attention kernels
+__global__ void __launch_bounds__(256) dr_segments_kernel(const int* __restrict__ idx, const int* __restrict__ count, int* __restrict__ seg,
+                                                           int batch, int l) {
+    const int cnt = *count;
+    for (int b = blockIdx.x * blockDim.x + threadIdx.x; b <= batch; b += gridDim.x * blockDim.x) seg[b] = dr_lower_bound(idx, cnt, b * l);
+}
 
-// Shared-memory layout of one (sample, head): K as bf16 pairs with an odd row pitch (lane = key reads are conflict free),
-// V as bf16 pairs (lane = channel pair), per-warp q / dO (fp32, dh) and p / ds (fp32, n).
+// Shared-memory layout of one (sample, head): K and V as bf16 pairs with an odd row pitch (reads with lane = key are
+// conflict free, reads with lane = channel pair are anyway), per-warp q / dO (fp32, dh) and p / ds (fp32, n).
 struct DrSmem {
     uint32_t *k, *v;
-    float *dk, *dv, *wbuf;
-    int kp;  // K row pitch in words
+    float* wbuf;
+    int kp;  // row pitch of K and V in words
 };
-__device__ __forceinline__ DrSmem dr_carve(uint8_t* base, int n, int dh, bool grads) {
+__device__ __forceinline__ DrSmem dr_carve(uint8_t* base, int n, int dh) {
     DrSmem s;
     s.kp = dh / 2 + 1;
     s.k = (uint32_t*)base;
     s.v = s.k + (size_t)n * s.kp;
-    float* f = (float*)(s.v + (size_t)n * (dh / 2));
-    s.dk = s.dv = nullptr;
-    if (grads) {
-        s.dk = f;
-        s.dv = f + (size_t)n * dh;
-        f += 2 * (size_t)n * dh;
-    }
-    s.wbuf = f;  // [8 warps][2 * n + 2 * dh]
+    s.wbuf = (float*)(s.v + (size_t)n * s.kp);  // [warps][2 * n + 2 * dh]
     return s;
 }
-static size_t dr_smem_bytes(int n, int dh, bool grads) {
-    return (size_t)n * (dh / 2 + 1) * 4 + (size_t)n * (dh / 2) * 4 + (grads ? 2 * (size_t)n * dh * 4 : 0) + 8 * (size_t)(2 * n + 2 * dh) * 4 + 16;
+static size_t dr_smem_bytes(int n, int dh, int warps) {
+    return 2 * (size_t)n * (dh / 2 + 1) * 4 + (size_t)warps * (2 * n + 2 * dh) * 4 + 16;
 }
 __device__ __forceinline__ void dr_load_kv(const DrSmem& s, const bf16* __restrict__ kv, int b, int h, int n, int e, int dh) {
     const int hw = dh / 2;
     for (int t = threadIdx.x; t < n * hw; t += blockDim.x) {
         const int key = t / hw, w = t - key * hw;
-        const uint32_t* row = reinterpret_cast<const uint32_t*>(kv + ((int64_t)b * n + key) * 2 * e + h * dh);
-        s.k[key * s.kp + w] = row[w];
-        s.v[key * hw + w] = reinterpret_cast<const uint32_t*>(kv + ((int64_t)b * n + key) * 2 * e + e + h * dh)[w];
+        const bf16* row = kv + ((int64_t)b * n + key) * 2 * e + h * dh;
+        s.k[key * s.kp + w] = reinterpret_cast<const uint32_t*>(row)[w];
+        s.v[key * s.kp + w] = reinterpret_cast<const uint32_t*>(row + e)[w];
     }
 }
 __device__ __forceinline__ float2 bf2(uint32_t u) {
@@ -1083,37 +1086,44 @@ __device__ __forceinline__ float2 bf2(uint32_t u) {
     return make_float2(__low2float(h), __high2float(h));
 }
 
-// grid (heads, batch): o16[i, h*dh ..] and lse[i, h] for the rows i of sample b
-__global__ void __launch_bounds__(256) dr_attn_fwd_kernel(const bf16* __restrict__ q16, const bf16* __restrict__ kv, const int* __restrict__ idx,
-                                                           const int* __restrict__ count, bf16* __restrict__ o16, float* __restrict__ lse,
-                                                           int l, int n, int e, int heads, float scale, int64_t max_rows) {
+constexpr int DR_FWD_WARPS = 8, DR_FWD_SPLIT = 2, DR_BWD_WARPS = 16;
+
+// grid (heads, batch, DR_FWD_SPLIT): o16[i, h*dh ..] and lse[i, h] for every DR_FWD_SPLIT-th batch of rows of sample b
+__global__ void __launch_bounds__(DR_FWD_WARPS * 32) dr_attn_fwd_kernel(const bf16* __restrict__ q16, const bf16* __restrict__ kv,
+                                                                         const int* __restrict__ seg, const int* __restrict__ count,
+                                                                         bf16* __restrict__ o16, float* __restrict__ lse, int l, int n, int e,
+                                                                         int heads, float scale, int64_t max_rows) {
     extern __shared__ uint8_t dr_raw[];
     const int h = blockIdx.x, b = blockIdx.y, dh = e / heads, hw = dh / 2;
     const int cnt = *count;
-    const int lo = dr_lower_bound(idx, cnt, b * l), hi = dr_lower_bound(idx, cnt, (b + 1) * l);
-    if (h == 0 && b == 0) {  // rows between the count and the next multiple of 128: zero (operand padding of dWo = dY^T O)
+    const int lo = seg[b], hi = seg[b + 1];
+    if (h == 0 && b == 0 && blockIdx.z == 0) {  // rows between the count and the next multiple of 128: zero (operand padding of dWo = dY^T O)
         const int64_t upto = min(max_rows, ((int64_t)cnt + 127) / 128 * 128);
         for (int64_t t = (int64_t)cnt * e + threadIdx.x; t < upto * e; t += blockDim.x) o16[t] = __float2bfloat16(0.f);
     }
-    if (lo >= hi) return;
-    const DrSmem s = dr_carve(dr_raw, n, dh, false);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int first = lo + blockIdx.z * DR_FWD_WARPS + wid;
+    if (lo + (int)blockIdx.z * DR_FWD_WARPS >= hi) return;
+    const DrSmem s = dr_carve(dr_raw, n, dh);
     dr_load_kv(s, kv, b, h, n, e, dh);
     __syncthreads();
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     float* qs = s.wbuf + (size_t)wid * (2 * n + 2 * dh);
     float* ps = qs + 2 * dh;
-    for (int i = lo + wid; i < hi; i += 8) {
+    for (int i = first; i < hi; i += DR_FWD_WARPS * DR_FWD_SPLIT) {
         const bf16* qrow = q16 + (int64_t)i * e + h * dh;
         for (int d = lane; d < dh; d += 32) qs[d] = __bfloat162float(qrow[d]) * scale;
         __syncwarp();
         float mx = -INFINITY;
         for (int key = lane; key < n; key += 32) {
-            float acc = 0.f;
+            float a0 = 0.f, a1 = 0.f;
             const uint32_t* kr = s.k + key * s.kp;
+#pragma unroll 4
             for (int w = 0; w < hw; ++w) {
                 const float2 kk = bf2(kr[w]);
-                acc = fmaf(qs[2 * w], kk.x, fmaf(qs[2 * w + 1], kk.y, acc));
+                a0 = fmaf(qs[2 * w], kk.x, a0);
+                a1 = fmaf(qs[2 * w + 1], kk.y, a1);
             }
+            const float acc = a0 + a1;
             ps[key] = acc;
             mx = fmaxf(mx, acc);
         }
@@ -1128,13 +1138,21 @@ __global__ void __launch_bounds__(256) dr_attn_fwd_kernel(const bf16* __restrict
         __syncwarp();
         const float inv = 1.0f / sum;
         for (int w = lane; w < hw; w += 32) {
-            float a0 = 0.f, a1 = 0.f;
-            for (int key = 0; key < n; ++key) {
-                const float2 vv = bf2(s.v[key * hw + w]);
-                a0 = fmaf(ps[key], vv.x, a0);
-                a1 = fmaf(ps[key], vv.y, a1);
+            float a0 = 0.f, a1 = 0.f, c0 = 0.f, c1 = 0.f;
+            int key = 0;
+            for (; key + 1 < n; key += 2) {
+                const float2 v0 = bf2(s.v[key * s.kp + w]), v1 = bf2(s.v[(key + 1) * s.kp + w]);
+                a0 = fmaf(ps[key], v0.x, a0);
+                a1 = fmaf(ps[key], v0.y, a1);
+                c0 = fmaf(ps[key + 1], v1.x, c0);
+                c1 = fmaf(ps[key + 1], v1.y, c1);
             }
-            __nv_bfloat162 o2 = __floats2bfloat162_rn(a0 * inv, a1 * inv);
+            if (key < n) {
+                const float2 v0 = bf2(s.v[key * s.kp + w]);
+                a0 = fmaf(ps[key], v0.x, a0);
+                a1 = fmaf(ps[key], v0.y, a1);
+            }
+            __nv_bfloat162 o2 = __floats2bfloat162_rn((a0 + c0) * inv, (a1 + c1) * inv);
             reinterpret_cast<uint32_t*>(o16 + (int64_t)i * e + h * dh)[w] = *reinterpret_cast<uint32_t*>(&o2);
         }
         if (lane == 0) lse[(int64_t)i * heads + h] = mx + __logf(sum);
@@ -1142,100 +1160,142 @@ __global__ void __launch_bounds__(256) dr_attn_fwd_kernel(const bf16* __restrict
     }
 }
 
-// grid (heads, batch): dq16 rows of sample b, and dK_h / dV_h of (b, h) as bf16 into dkv (B, N, 2E); P recomputed from lse
-__global__ void __launch_bounds__(256) dr_attn_bwd_kernel(const bf16* __restrict__ q16, const bf16* __restrict__ kv, const bf16* __restrict__ o16,
-                                                           const bf16* __restrict__ do16, const float* __restrict__ lse,
-                                                           const int* __restrict__ idx, const int* __restrict__ count,
-                                                           bf16* __restrict__ dq16, bf16* __restrict__ dkv, int l, int n, int e, int heads,
-                                                           float scale, int64_t max_rows) {
+// grid (heads, batch): dq16 rows of sample b, and dK_h / dV_h of (b, h) as bf16 into dkv (B, N, 2E); P recomputed from lse.
+// Rows go through in batches of sixteen (one per warp): phase A, warp = row, recomputes the row's probabilities and
+// score gradients into the warp's buffer and writes dq; phase B, warp = a slice of KPW keys, lane = CPL channels, adds
+// the batch's rank-1 terms into dK / dV accumulators held in REGISTERS for the whole kernel (no two warps own the same
+// key: no atomics, no shared-memory round trips — the first version did this with shared-memory atomics from the row
+// warps and took 450 us at the benchmark shape, a shared-memory read-modify-write version 297 us).
+template <int KPW, int CPL>
+__global__ void __launch_bounds__(DR_BWD_WARPS * 32) dr_attn_bwd_kernel(const bf16* __restrict__ q16, const bf16* __restrict__ kv,
+                                                                         const bf16* __restrict__ o16, const bf16* __restrict__ do16,
+                                                                         const float* __restrict__ lse, const int* __restrict__ seg,
+                                                                         const int* __restrict__ count, bf16* __restrict__ dq16,
+                                                                         bf16* __restrict__ dkv, int l, int n, int e, int heads, float scale,
+                                                                         int64_t max_rows) {
     extern __shared__ uint8_t dr_raw[];
     const int h = blockIdx.x, b = blockIdx.y, dh = e / heads, hw = dh / 2;
     const int cnt = *count;
-    const int lo = dr_lower_bound(idx, cnt, b * l), hi = dr_lower_bound(idx, cnt, (b + 1) * l);
+    const int lo = seg[b], hi = seg[b + 1];
     if (h == 0 && b == 0) {
         const int64_t upto = min(max_rows, ((int64_t)cnt + 127) / 128 * 128);
         for (int64_t t = (int64_t)cnt * e + threadIdx.x; t < upto * e; t += blockDim.x) dq16[t] = __float2bfloat16(0.f);
     }
-    const DrSmem s = dr_carve(dr_raw, n, dh, true);
-    for (int t = threadIdx.x; t < 2 * n * dh; t += blockDim.x) s.dk[t] = 0.f;  // dk and dv are adjacent
+    const DrSmem s = dr_carve(dr_raw, n, dh);
     if (lo < hi) dr_load_kv(s, kv, b, h, n, e, dh);
     __syncthreads();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    float* qs = s.wbuf + (size_t)wid * (2 * n + 2 * dh);  // q * scale
-    float* gs = qs + dh;                                   // dO
-    float* ps = qs + 2 * dh;                               // p
-    float* dss = ps + n;                                   // ds (gradient of the scaled score)
-    for (int i = lo + wid; i < hi; i += 8) {
-        const int64_t off = (int64_t)i * e + h * dh;
-        float delta = 0.f;
-        for (int d = lane; d < dh; d += 32) {
-            qs[d] = __bfloat162float(q16[off + d]) * scale;
-            const float g = __bfloat162float(do16[off + d]);
-            gs[d] = g;
-            delta = fmaf(g, __bfloat162float(o16[off + d]), delta);
-        }
-        delta = warp_sum(delta);
-        const float lse_i = lse[(int64_t)i * heads + h];
-        __syncwarp();
-        for (int key = lane; key < n; key += 32) {
-            float sc = 0.f, dp = 0.f;
-            const uint32_t* kr = s.k + key * s.kp;
-            const uint32_t* vr = s.v + key * hw;
-            for (int w = 0; w < hw; ++w) {
-                const float2 kk = bf2(kr[w]), vv = bf2(vr[w]);
-                sc = fmaf(qs[2 * w], kk.x, fmaf(qs[2 * w + 1], kk.y, sc));
-                dp = fmaf(gs[2 * w], vv.x, fmaf(gs[2 * w + 1], vv.y, dp));
-            }
-            const float pv = __expf(sc - lse_i);
-            ps[key] = pv;
-            dss[key] = pv * (dp - delta);
-        }
-        __syncwarp();
-        // dV[key] += p dO ; dK[key] += ds * scale * q (qs carries the scale): lane = channel, so the shared-memory
-        // atomics of a warp hit consecutive banks; other warps add to the same tile
-        for (int key = 0; key < n; ++key) {
-            const float pv = ps[key], ds = dss[key];
+    const int wstride = 2 * n + 2 * dh;
+    float* qs = s.wbuf + (size_t)wid * wstride;  // q * scale
+    float* gs = qs + dh;                          // dO
+    float* ps = qs + 2 * dh;                      // p
+    float* dss = ps + n;                          // ds (gradient of the scaled score)
+    const int k0 = wid * KPW;                     // keys [k0, k0 + KPW) belong to this warp in phase B
+    float dkr[KPW][CPL], dvr[KPW][CPL];
+#pragma unroll
+    for (int a = 0; a < KPW; ++a)
+#pragma unroll
+        for (int c = 0; c < CPL; ++c) dkr[a][c] = dvr[a][c] = 0.f;
+    for (int base = lo; base < hi; base += DR_BWD_WARPS) {
+        const int i = base + wid;
+        if (i < hi) {  // ---- phase A (warp-uniform)
+            const int64_t off = (int64_t)i * e + h * dh;
+            float delta = 0.f;
             for (int d = lane; d < dh; d += 32) {
-                atomicAdd(&s.dv[key * dh + d], pv * gs[d]);
-                atomicAdd(&s.dk[key * dh + d], ds * qs[d]);
+                qs[d] = __bfloat162float(q16[off + d]) * scale;
+                const float g = __bfloat162float(do16[off + d]);
+                gs[d] = g;
+                delta = fmaf(g, __bfloat162float(o16[off + d]), delta);
+            }
+            delta = warp_sum(delta);
+            const float lse_i = lse[(int64_t)i * heads + h];
+            __syncwarp();
+            for (int key = lane; key < n; key += 32) {
+                float sc = 0.f, dp = 0.f;
+                const uint32_t* kr = s.k + key * s.kp;
+                const uint32_t* vr = s.v + key * s.kp;
+#pragma unroll 4
+                for (int w = 0; w < hw; ++w) {
+                    const float2 kk = bf2(kr[w]), vv = bf2(vr[w]);
+                    sc = fmaf(qs[2 * w], kk.x, fmaf(qs[2 * w + 1], kk.y, sc));
+                    dp = fmaf(gs[2 * w], vv.x, fmaf(gs[2 * w + 1], vv.y, dp));
+                }
+                const float pv = __expf(sc - lse_i);
+                ps[key] = pv;
+                dss[key] = pv * (dp - delta);
+            }
+            __syncwarp();
+            for (int w = lane; w < hw; w += 32) {  // dq = sum_key ds * scale * K[key]
+                float a0 = 0.f, a1 = 0.f;
+                for (int key = 0; key < n; ++key) {
+                    const float2 kk = bf2(s.k[key * s.kp + w]);
+                    const float dsk = dss[key] * scale;
+                    a0 = fmaf(dsk, kk.x, a0);
+                    a1 = fmaf(dsk, kk.y, a1);
+                }
+                __nv_bfloat162 o2 = __floats2bfloat162_rn(a0, a1);
+                reinterpret_cast<uint32_t*>(dq16 + off)[w] = *reinterpret_cast<uint32_t*>(&o2);
             }
         }
-        for (int w = lane; w < hw; w += 32) {  // dq = sum_key ds * scale * K[key]
-            float a0 = 0.f, a1 = 0.f;
-            for (int key = 0; key < n; ++key) {
-                const float2 kk = bf2(s.k[key * s.kp + w]);
-                const float dsk = dss[key] * scale;
-                a0 = fmaf(dsk, kk.x, a0);
-                a1 = fmaf(dsk, kk.y, a1);
+        __syncthreads();
+        // ---- phase B: dV[key] += p dO ; dK[key] += ds * scale * q (qs carries the scale), for this warp's keys
+        const int nrows = min(DR_BWD_WARPS, hi - base);
+        for (int r = 0; r < nrows; ++r) {
+            const float* rq = s.wbuf + (size_t)r * wstride;
+            const float* rg = rq + dh;
+            const float* rp = rq + 2 * dh;
+            const float* rds = rp + n;
+            float qv[CPL], gv[CPL];
+#pragma unroll
+            for (int c = 0; c < CPL; ++c) {
+                const int d = lane + 32 * c;
+                qv[c] = d < dh ? rq[d] : 0.f;
+                gv[c] = d < dh ? rg[d] : 0.f;
             }
-            __nv_bfloat162 o2 = __floats2bfloat162_rn(a0, a1);
-            reinterpret_cast<uint32_t*>(dq16 + off)[w] = *reinterpret_cast<uint32_t*>(&o2);
+#pragma unroll
+            for (int a = 0; a < KPW; ++a) {
+                const int key = min(k0 + a, n - 1);  // (keys past n are never written out)
+                const float pv = rp[key], ds = rds[key];
+#pragma unroll
+                for (int c = 0; c < CPL; ++c) {
+                    dvr[a][c] = fmaf(pv, gv[c], dvr[a][c]);
+                    dkr[a][c] = fmaf(ds, qv[c], dkr[a][c]);
+                }
+            }
         }
-        __syncwarp();
+        __syncthreads();
     }
-    __syncthreads();
-    for (int t = threadIdx.x; t < n * hw; t += blockDim.x) {
-        const int key = t / hw, w = t - key * hw;
-        __nv_bfloat162 k2 = __floats2bfloat162_rn(s.dk[key * dh + 2 * w], s.dk[key * dh + 2 * w + 1]);
-        __nv_bfloat162 v2 = __floats2bfloat162_rn(s.dv[key * dh + 2 * w], s.dv[key * dh + 2 * w + 1]);
-        bf16* row = dkv + ((int64_t)b * n + key) * 2 * e;
-        reinterpret_cast<uint32_t*>(row + h * dh)[w] = *reinterpret_cast<uint32_t*>(&k2);
-        reinterpret_cast<uint32_t*>(row + e + h * dh)[w] = *reinterpret_cast<uint32_t*>(&v2);
+#pragma unroll
+    for (int a = 0; a < KPW; ++a) {
+        const int key = k0 + a;
+        if (key < n) {
+            bf16* row = dkv + ((int64_t)b * n + key) * 2 * e + h * dh;
+#pragma unroll
+            for (int c = 0; c < CPL; ++c) {
+                const int d = lane + 32 * c;
+                if (d < dh) {
+                    row[d] = __float2bfloat16(dkr[a][c]);
+                    row[e + d] = __float2bfloat16(dvr[a][c]);
+                }
+            }
+        }
     }
 }
 
+typedef void (*DrBwdKernel)(const bf16*, const bf16*, const bf16*, const bf16*, const float*, const int*, const int*, bf16*, bf16*, int, int,
+                            int, int, float, int64_t);
+static DrBwdKernel dr_bwd_pick(int n, int dh) {
+    const int kpw = n <= 2 * DR_BWD_WARPS ? 2 : (n <= 4 * DR_BWD_WARPS ? 4 : 8);
+    const int cpl = dh <= 32 ? 1 : (dh <= 64 ? 2 : 4);
+#define PIO_DR(K, C) if (kpw == K && cpl == C) return dr_attn_bwd_kernel<K, C>
+    PIO_DR(2, 1); PIO_DR(2, 2); PIO_DR(2, 4); PIO_DR(4, 1); PIO_DR(4, 2); PIO_DR(4, 4); PIO_DR(8, 1); PIO_DR(8, 2); PIO_DR(8, 4);
+#undef PIO_DR
+    return nullptr;
+}
 static int dr_configure(int n, int dh) {
-    static std::mutex mu;
-    static size_t configured[64] = {};
-    const size_t need = dr_smem_bytes(n, dh, true);
-    int dev = 0;
-    PIO_CUDA(cudaGetDevice(&dev));
-    std::lock_guard<std::mutex> lock(mu);
-    if (dev >= 0 && dev < 64 && configured[dev] < need) {
-        PIO_CUDA(cudaFuncSetAttribute(dr_attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
-        PIO_CUDA(cudaFuncSetAttribute(dr_attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
-        configured[dev] = need;
-    }
+    const size_t need_f = dr_smem_bytes(n, dh, DR_FWD_WARPS), need_b = dr_smem_bytes(n, dh, DR_BWD_WARPS);
+    if (need_f > 48 * 1024) PIO_CUDA(cudaFuncSetAttribute(dr_attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need_f));
+    if (need_b > 48 * 1024) PIO_CUDA(cudaFuncSetAttribute(dr_bwd_pick(n, dh), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need_b));
     return PIO_OK;
 }
 
@@ -1251,10 +1311,12 @@ int decode_rows_fwd(Ctx& c, const float* queries, const void* kv, const int* idx
     const int row_blocks = (int)std::min<int64_t>(cdiv(max_rows, 8), (int64_t)num_sms() * 8);
     dr_gather_kernel<<<row_blocks, 256, 0, c.st>>>(queries, idx, c.dyn, s.xq, l, e);
     PIO_LAUNCH_CHECK();
+    dr_segments_kernel<<<(unsigned)cdiv(batch + 1, 256), 256, 0, c.st>>>(idx, c.dyn, s.seg, batch, l);
+    PIO_LAUNCH_CHECK();
     PIO_TRY(layernorm_fwd_bf16(s.xq, aw->ln_w, aw->ln_b, s.hq, e, s.stats, max_rows, e, LN_EPS, c.st, c.dyn));
     PIO_TRY(tc_xwT(c, s.hq, e, (const bf16*)aw->wq, e, max_rows, e, e, nullptr, 0, s.q, e, aw->bq, nullptr, 0, 0, nullptr, 0));
-    dr_attn_fwd_kernel<<<dim3((unsigned)heads, (unsigned)batch), 256, dr_smem_bytes(n, dh, false), c.st>>>(
-        s.q, (const bf16*)kv, idx, c.dyn, s.o16, s.lse, l, n, e, heads, 1.0f / sqrtf((float)dh), max_rows);
+    dr_attn_fwd_kernel<<<dim3((unsigned)heads, (unsigned)batch, DR_FWD_SPLIT), DR_FWD_WARPS * 32, dr_smem_bytes(n, dh, DR_FWD_WARPS), c.st>>>(
+        s.q, (const bf16*)kv, s.seg, c.dyn, s.o16, s.lse, l, n, e, heads, 1.0f / sqrtf((float)dh), max_rows);
     PIO_LAUNCH_CHECK();
     PIO_TRY(tc_xwT(c, s.o16, e, (const bf16*)aw->wo, e, max_rows, e, e, s.x1, e, nullptr, 0, aw->bo, s.xq, e, 0, nullptr, 0));
     PIO_TRY(mlp_fwd(c, s.x1, y, mw, s.mlp, max_rows, e, 1));
@@ -1283,8 +1345,8 @@ int decode_rows_bwd(Ctx& c, const float* dy, const void* kv, const int* idx, flo
     PIO_TRY(side.fork());
     PIO_TRY(tc_dW(c, dy16, e, s.o16, e, ag->wo, max_rows, e, e, acc, side.stream()));
     PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)aw->wo, e, max_rows, e, e, nullptr, 0, d_o16, e, 0, nullptr, 0, 0));
-    dr_attn_bwd_kernel<<<dim3((unsigned)heads, (unsigned)batch), 256, dr_smem_bytes(n, dh, true), c.st>>>(
-        s.q, (const bf16*)kv, s.o16, d_o16, s.lse, idx, c.dyn, dq16, (bf16*)dkv, l, n, e, heads, 1.0f / sqrtf((float)dh), max_rows);
+    dr_bwd_pick(n, dh)<<<dim3((unsigned)heads, (unsigned)batch), DR_BWD_WARPS * 32, dr_smem_bytes(n, dh, DR_BWD_WARPS), c.st>>>(
+        s.q, (const bf16*)kv, s.o16, d_o16, s.lse, s.seg, c.dyn, dq16, (bf16*)dkv, l, n, e, heads, 1.0f / sqrtf((float)dh), max_rows);
     PIO_LAUNCH_CHECK();
     PIO_TRY(side.fork());
     PIO_TRY(side_colsum(c, side, dq16, e, ag->bq, acc, max_rows, e));
