@@ -525,6 +525,33 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 128 ? 1 : 2)
             }
             mbar_wait(sdp_full, (uint32_t)j & 1u);
             tc_fence_after();
+            if (T == 1) {
+                // One key tile holds the whole row (latent self-attention): delta = sum_k p_k dP_k from the probabilities that
+                // are recomputed below, so that sum_k dS_k = 0 to fp32 rounding.  (dO . O from a bf16 copy of O leaves a
+                // common-mode error along the mean key in dQ; with several key tiles the sum would need a pass of its own and
+                // the fp32 / bf16 output is used, above.)
+                float dsum = 0.f;
+#pragma unroll
+                for (int c0 = 0; c0 < BKV; c0 += 32) {
+                    uint32_t rs[32], rp[32];
+                    tmem_ld32(tmem_s + lane_off + (uint32_t)c0, rs);
+                    tmem_ld32(tmem_dp + lane_off + (uint32_t)c0, rp);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        float e = __uint_as_float(rs[i]) * p.scale_log2e - lse2;
+                        if (masked) e += bias[c0 + i];
+                        float dpi = __uint_as_float(rp[i]);
+                        if constexpr (DROP) {
+                            const uint64_t idx = (((uint64_t)b * p.heads + h) * p.n + (uint64_t)qi) * (uint64_t)p.m + (uint64_t)(j0 + c0 + i);
+                            dpi = drop_keep(p.drop, idx) ? dpi * p.drop.inv_keep : 0.f;
+                        }
+                        dsum = fmaf(fast_exp2(e), dpi, dsum);
+                    }
+                }
+                delta = dsum;
+                if (q_ok) p.delta[((int64_t)b * p.heads + h) * p.n + qi] = delta;
+            }
             if (j >= 2) mbar_wait(&dq_done[j & 1], (uint32_t)((j - 2) >> 1) & 1u);  // dQ(j-2) has consumed this dS buffer
             uint32_t dw[32];  // this row of dS as bf16 pairs
 #pragma unroll

@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(NCH <= 8 ? 512 : 256, NCH <= 16 ? 2 : 1) layer
     const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ stats,
     const float* __restrict__ w, const float* __restrict__ dres, float* __restrict__ dx,
     float* __restrict__ partial, int64_t rows, int c, float* __restrict__ atomic_dw = nullptr,
-    float* __restrict__ atomic_db = nullptr, const int* __restrict__ dyn_rows = nullptr) {
+    float* __restrict__ atomic_db = nullptr, const int* __restrict__ dyn_rows = nullptr, __nv_bfloat16* __restrict__ dx16 = nullptr) {
     extern __shared__ float s_acc[];  // [warps][2][c]
     pdl_trigger();
     pdl_wait();
@@ -365,7 +365,11 @@ __global__ void __launch_bounds__(NCH <= 8 ? 512 : 256, NCH <= 16 ? 2 : 1) layer
 #pragma unroll
             for (int i = 0; i < NCH; ++i) {
                 const int j = lane + 32 * i;
-                if (j < c) dx[r * c + j] = rstd * (d[i] - c1 - xh[i] * c2) + rs[i];
+                if (j < c) {
+                    const float o = rstd * (d[i] - c1 - xh[i] * c2) + rs[i];
+                    dx[r * c + j] = o;
+                    if (dx16 != nullptr) dx16[r * c + j] = __float2bfloat16(o);
+                }
             }
         }
     }
@@ -394,7 +398,7 @@ __global__ void __launch_bounds__(512, 2) layernorm_bwd_vec_kernel(
     const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ stats,
     const float* __restrict__ w, const float* __restrict__ dres, float* __restrict__ dx,
     float* __restrict__ partial, int64_t rows, float* __restrict__ atomic_dw, float* __restrict__ atomic_db,
-    const int* __restrict__ dyn_rows) {
+    const int* __restrict__ dyn_rows, __nv_bfloat16* __restrict__ dx16) {
     extern __shared__ float s_acc[];  // [warps][2][c]
     pdl_trigger();
     pdl_wait();
@@ -444,6 +448,13 @@ __global__ void __launch_bounds__(512, 2) layernorm_bwd_vec_kernel(
                 o.z = rstd * (d[i].z - c1 - xh[i].z * c2) + rs[i].z;
                 o.w = rstd * (d[i].w - c1 - xh[i].w * c2) + rs[i].w;
                 dxr[i * 32 + lane] = o;
+                if (dx16 != nullptr) {  // the same row as bf16: the next operator's dY operand (saves its cast pass)
+                    __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
+                    uint2 u;
+                    u.x = *reinterpret_cast<uint32_t*>(&lo);
+                    u.y = *reinterpret_cast<uint32_t*>(&hi);
+                    reinterpret_cast<uint2*>(dx16 + r * C)[i * 32 + lane] = u;
+                }
             }
         }
     }
@@ -800,21 +811,23 @@ size_t pio_layernorm_bwd_ws_bytes(int64_t rows, int c) {
 namespace pio {
 int layernorm_bwd(const float* dy, const float* x, const float* stats, const float* w, const float* dres, float* dx, float* dw,
                   float* db, int accumulate, int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t stream,
-                  const int* dyn_rows);
+                  const int* dyn_rows, __nv_bfloat16* dx16);
 }
 extern "C" {
 int pio_layernorm_bwd(const float* dy, const float* x, const float* stats, const float* w, const float* dres,
                       float* dx, float* dw, float* db, int accumulate, int64_t rows, int c, void* ws, size_t ws_bytes,
                       pio_stream_t stream) {
-    return pio::layernorm_bwd(dy, x, stats, w, dres, dx, dw, db, accumulate, rows, c, ws, ws_bytes, (cudaStream_t)stream, nullptr);
+    return pio::layernorm_bwd(dy, x, stats, w, dres, dx, dw, db, accumulate, rows, c, ws, ws_bytes, (cudaStream_t)stream, nullptr,
+                              nullptr);
 }
 }  // extern "C"
 
 namespace pio {
 int layernorm_bwd(const float* dy, const float* x, const float* stats, const float* w, const float* dres, float* dx, float* dw,
                   float* db, int accumulate, int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t stream,
-                  const int* dyn_rows) {
+                  const int* dyn_rows, __nv_bfloat16* dx16) {
     PIO_CHECK_ARG(dy && x && stats && w && dw && db && c > 0 && rows >= 0, "pio_layernorm_bwd: bad arguments");
+    PIO_CHECK_ARG(dx16 == nullptr || dx != nullptr, "pio_layernorm_bwd: the bf16 copy needs dx");
     PIO_CHECK_ARG(c <= 1024, "pio_layernorm_bwd: channels %d > 1024 unsupported", c);
     if (rows == 0) return PIO_OK;
     Workspace W(ws, ws_bytes);
@@ -834,9 +847,9 @@ int layernorm_bwd(const float* dy, const float* x, const float* stats, const flo
                         ((((uintptr_t)dy | (uintptr_t)x | (uintptr_t)w | (uintptr_t)dres | (uintptr_t)dx) & 15) == 0);
     if (vec_ok) {  // warps == 16 for these widths; smem = 16 * 2 * c * 4 <= 32 KB
         if (c == 128)
-            PIO_CUDA(launch_pdl(layernorm_bwd_vec_kernel<1>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, adw, adb, dyn_rows));
+            PIO_CUDA(launch_pdl(layernorm_bwd_vec_kernel<1>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, adw, adb, dyn_rows, dx16));
         else
-            PIO_CUDA(launch_pdl(layernorm_bwd_vec_kernel<2>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, adw, adb, dyn_rows));
+            PIO_CUDA(launch_pdl(layernorm_bwd_vec_kernel<2>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, adw, adb, dyn_rows, dx16));
         PIO_LAUNCH_CHECK();
         if (atomic) return PIO_OK;
         return reduce_partials(partial, blocks, (int64_t)2 * c, dw, c, db, c, accumulate, st);
@@ -847,7 +860,7 @@ int layernorm_bwd(const float* dy, const float* x, const float* stats, const flo
             PIO_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                           (int)smem));                                                          \
         PIO_CUDA(launch_pdl(layernorm_bwd_kernel<NCH>, dim3(blocks), dim3(32 * warps), smem, st, dy, x, stats, w, dres, dx, partial, rows, c, adw, \
-                            adb, dyn_rows));                                                                    \
+                            adb, dyn_rows, dx16));                                                              \
     } while (0)
     if (c <= 128) PIO_LN_BWD(4);
     else if (c <= 256) PIO_LN_BWD(8);

@@ -105,12 +105,39 @@ __device__ __forceinline__ void load4_f32(const float* a, float (&v)[4], bool ve
     }
 }
 
+// The global operand that some epilogue flavours read per output row (residual / running sum / saved GELU'): the loads of
+// one batch of BATCH row-iterations, issued together.
+constexpr int EPI_BATCH = 8;
+template <int BN, int KIND>
+__device__ __forceinline__ void epilogue_preload(const TcParams& p, int lane, int n0, int64_t gm0, int rows_here, int it0,
+                                                 float (&pre)[EPI_BATCH][4]) {
+    constexpr int LANES_PER_ROW = BN / 4;
+    constexpr int ROWS_PER_IT = 32 / LANES_PER_ROW;
+    const int col = (lane % LANES_PER_ROW) * 4;
+    const int rsub = lane / LANES_PER_ROW;
+    const int n = n0 + col;
+    const int valid = min(4, p.N - n);
+    const bool v32 = ((p.ldc32 & 3) == 0) && ((n & 3) == 0) && ((((uintptr_t)p.c32) & 15) == 0);
+    const bool vaux = ((p.ldaux & 3) == 0) && ((((uintptr_t)p.aux16) & 7) == 0);
+    const bool vres = ((p.ldr & 3) == 0) && ((((uintptr_t)p.residual) & 15) == 0);
+#pragma unroll
+    for (int u = 0; u < EPI_BATCH; ++u) {
+        const int rr = (it0 + u) * ROWS_PER_IT + rsub;
+        const bool ok = rr < rows_here && valid > 0;
+        const int64_t gm = gm0 + (ok ? rr : 0);
+        const int vv = ok ? valid : 0;
+        if (KIND == EPI_F32_RES) load4_f32(p.residual + gm * p.ldr + n, pre[u], vres, vv);
+        else if (KIND == EPI_F32_ACC) load4_f32(p.c32 + gm * p.ldc32 + n, pre[u], v32, vv);
+        else load4_b16(p.aux16 + gm * p.ldaux + n, pre[u], vaux, vv);
+    }
+}
+
 // One warp's 32 accumulator rows x BN columns, staged in shared memory (row pitch BN+4 floats).
 // Each lane owns 4 consecutive columns of a row, so every global access is a coalesced row
 // segment (16 B per lane when the leading dimensions allow it).
 template <int BN, int KIND>
 __device__ __forceinline__ void epilogue_rows(const TcParams& p, const float* stile, int lane, int n0, int64_t gm0,
-                                              int rows_here, int zsplit) {
+                                              int rows_here, int zsplit, const float (&early)[EPI_BATCH][4], bool use_early) {
     constexpr int PITCH = BN + 4;
     constexpr int LANES_PER_ROW = BN / 4;            // 32 (BN=128) or 16 (BN=64)
     constexpr int ROWS_PER_IT = 32 / LANES_PER_ROW;  // 1 or 2
@@ -134,21 +161,19 @@ __device__ __forceinline__ void epilogue_rows(const TcParams& p, const float* st
     // warps of a CTA had a single 512-byte request in flight each and the kernel ran at the speed of 32 serial
     // memory round trips (ncu: long-scoreboard 22 per issue, tensor pipe 4.6 % on the 32768 x 256 x 256 products).
     constexpr int ITERS = 32 / ROWS_PER_IT;
-    constexpr int BATCH = 8;
+    constexpr int BATCH = EPI_BATCH;
     constexpr bool PRELOAD = (KIND == EPI_F32_RES || KIND == EPI_F32_ACC || KIND == EPI_B16_DGELU);
 #pragma unroll 1
     for (int it0 = 0; it0 < ITERS; it0 += BATCH) {
         float pre[BATCH][4];
         if (PRELOAD) {
+            if (it0 == 0 && use_early) {  // the first batch was loaded before the accumulator was waited for
 #pragma unroll
-            for (int u = 0; u < BATCH; ++u) {
-                const int rr = (it0 + u) * ROWS_PER_IT + rsub;
-                const bool ok = rr < rows_here && valid > 0;
-                const int64_t gm = gm0 + (ok ? rr : 0);
-                const int vv = ok ? valid : 0;
-                if (KIND == EPI_F32_RES) load4_f32(p.residual + gm * p.ldr + n, pre[u], vres, vv);
-                else if (KIND == EPI_F32_ACC) load4_f32(p.c32 + gm * p.ldc32 + n, pre[u], v32, vv);
-                else load4_b16(p.aux16 + gm * p.ldaux + n, pre[u], vaux, vv);
+                for (int u = 0; u < BATCH; ++u)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) pre[u][j] = early[u][j];
+            } else {
+                epilogue_preload<BN, KIND>(p, lane, n0, gm0, rows_here, it0, pre);
             }
         }
 #pragma unroll
@@ -330,6 +355,21 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
         const int half = (warp - 2) >> 2;  // which half of the tile's columns this warp finishes
         constexpr int HN = BN / 2;
         constexpr int PITCH = HN + 4;
+        // Flavours that read a global operand per output row: the epilogue warps have nothing to do while the MMAs run,
+        // so the first batch of those loads (all of them for 64-wide tiles) is issued BEFORE waiting for the accumulator
+        // — the operand (a residual, the saved GELU' of the forward pass) usually comes from HBM, and that round trip
+        // used to sit between the last MMA and the first store (dX with GELU': 10.9 us against 5.5 us for a plain dX).
+        float early[EPI_BATCH][4];
+        bool have_early = false;
+        {
+            const int64_t gm0e = (int64_t)m0 + q * 32;
+            const int rows_e = (int)min((int64_t)32, (int64_t)m_eff - gm0e);
+            const int nhe = n0 + half * HN;
+            if constexpr (BN == 64) {  // (128-wide tiles: the 32 extra live registers across the accumulator copy would spill)
+                if (p.epi_kind == EPI_F32_RES) { epilogue_preload<HN, EPI_F32_RES>(p, lane, nhe, gm0e, rows_e, 0, early); have_early = true; }
+                else if (p.epi_kind == EPI_B16_DGELU) { epilogue_preload<HN, EPI_B16_DGELU>(p, lane, nhe, gm0e, rows_e, 0, early); have_early = true; }
+            }
+        }
         mbar_wait(tmem_full, 0);
         tc_fence_after();
         float* stile = reinterpret_cast<float*>(smem) + (half * 4 + q) * (32 * PITCH);
@@ -358,15 +398,15 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
         }
         const int nh = n0 + half * HN;
         switch (p.epi_kind) {
-            case EPI_F32: epilogue_rows<HN, EPI_F32>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
-            case EPI_F32_RES: epilogue_rows<HN, EPI_F32_RES>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
-            case EPI_F32_ACC: epilogue_rows<HN, EPI_F32_ACC>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
-            case EPI_B16: epilogue_rows<HN, EPI_B16>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
-            case EPI_B16_GELU: epilogue_rows<HN, EPI_B16_GELU>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
-            case EPI_B16_DGELU: epilogue_rows<HN, EPI_B16_DGELU>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
-            case EPI_PARTIAL: epilogue_rows<HN, EPI_PARTIAL>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
-            case EPI_F32_ATOMIC: epilogue_rows<HN, EPI_F32_ATOMIC>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
-            default: epilogue_rows<HN, EPI_GENERIC>(p, stile, lane, nh, gm0, rows_here, blockIdx.z); break;
+            case EPI_F32: epilogue_rows<HN, EPI_F32>(p, stile, lane, nh, gm0, rows_here, blockIdx.z, early, have_early); break;
+            case EPI_F32_RES: epilogue_rows<HN, EPI_F32_RES>(p, stile, lane, nh, gm0, rows_here, blockIdx.z, early, have_early); break;
+            case EPI_F32_ACC: epilogue_rows<HN, EPI_F32_ACC>(p, stile, lane, nh, gm0, rows_here, blockIdx.z, early, have_early); break;
+            case EPI_B16: epilogue_rows<HN, EPI_B16>(p, stile, lane, nh, gm0, rows_here, blockIdx.z, early, have_early); break;
+            case EPI_B16_GELU: epilogue_rows<HN, EPI_B16_GELU>(p, stile, lane, nh, gm0, rows_here, blockIdx.z, early, have_early); break;
+            case EPI_B16_DGELU: epilogue_rows<HN, EPI_B16_DGELU>(p, stile, lane, nh, gm0, rows_here, blockIdx.z, early, have_early); break;
+            case EPI_PARTIAL: epilogue_rows<HN, EPI_PARTIAL>(p, stile, lane, nh, gm0, rows_here, blockIdx.z, early, have_early); break;
+            case EPI_F32_ATOMIC: epilogue_rows<HN, EPI_F32_ATOMIC>(p, stile, lane, nh, gm0, rows_here, blockIdx.z, early, have_early); break;
+            default: epilogue_rows<HN, EPI_GENERIC>(p, stile, lane, nh, gm0, rows_here, blockIdx.z, early, have_early); break;
         }
         tc_fence_before();
     }
@@ -411,7 +451,10 @@ static void tc_choose(int64_t m, int64_t n, int64_t k, bool splittable, int* bn,
     const int64_t tiles = cdiv(m, TC_BM) * cdiv(n, *bn);
     const int num_kb = (int)cdiv(k, TC_BK);
     int s = 1;
-    static const int min_kb = getenv("PIO_TC_SPLIT_MIN_KB") ? atoi(getenv("PIO_TC_SPLIT_MIN_KB")) : 16;
+    // k-blocks per split: 8 (512 rows of the contraction).  Measured on the cfg2 step, where the weight-gradient
+    // products (256 x 256 outputs over 4096 rows, on the side stream) are the longer of the two backward chains:
+    // 16 -> 3.73 ms, 8 -> 3.61 ms, 4 -> 3.73 ms, 2 -> 3.74 ms (more, smaller CTAs start to take SMs from the main chain).
+    static const int min_kb = getenv("PIO_TC_SPLIT_MIN_KB") ? atoi(getenv("PIO_TC_SPLIT_MIN_KB")) : 8;
     if (splittable && num_kb >= 16 && tiles < sms) {
         s = (int)std::min<int64_t>(cdiv(sms, tiles), num_kb / min_kb);
         s = std::max(s, 1);

@@ -42,8 +42,9 @@ static int tc_gemm(Ctx& c, const pio_gemm_bf16_desc& d) { return gemm_bf16(&d, c
 // the end of the operator; the small, latency-bound kernels of the two chains then overlap on the GPU
 // (under stream capture the fork/join becomes two parallel branches of the graph).
 struct SideRes {
-    cudaStream_t stream = nullptr;
-    cudaEvent_t fork = nullptr, join = nullptr;
+    cudaStream_t stream = nullptr;   // weight-gradient GEMMs
+    cudaStream_t stream2 = nullptr;  // bias-gradient column sums (beside the GEMMs: one chain was the longer of the operator's two)
+    cudaEvent_t fork = nullptr, join = nullptr, join2 = nullptr;
 };
 static SideRes* side_res() {
     static SideRes res[64];
@@ -58,7 +59,9 @@ static SideRes* side_res() {
         cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
         (void)cs;
         if (cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking) != cudaSuccess) { r.stream = nullptr; return nullptr; }
-        if (cudaEventCreateWithFlags(&r.fork, cudaEventDisableTiming) != cudaSuccess ||
+        if (cudaStreamCreateWithFlags(&r.stream2, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&r.fork, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&r.join2, cudaEventDisableTiming) != cudaSuccess ||
             cudaEventCreateWithFlags(&r.join, cudaEventDisableTiming) != cudaSuccess) {
             r.stream = nullptr;
             return nullptr;
@@ -74,19 +77,23 @@ struct Side {
     Side(Ctx& ctx, int acc) : c(ctx), r(acc == 2 ? side_res() : nullptr) {}
     bool active() const { return r != nullptr; }
     cudaStream_t stream() const { return r ? r->stream : c.st; }
-    // everything enqueued on the main stream so far becomes visible to the side stream
+    cudaStream_t stream2() const { return r ? r->stream2 : c.st; }
+    // everything enqueued on the main stream so far becomes visible to the side streams
     int fork() {
         if (!r) return PIO_OK;
         PIO_CUDA(cudaEventRecord(r->fork, c.st));
         PIO_CUDA(cudaStreamWaitEvent(r->stream, r->fork, 0));
+        PIO_CUDA(cudaStreamWaitEvent(r->stream2, r->fork, 0));
         used = true;
         return PIO_OK;
     }
-    // the main stream waits for everything enqueued on the side stream
+    // the main stream waits for everything enqueued on the side streams
     int join() {
         if (!r || !used) return PIO_OK;
         PIO_CUDA(cudaEventRecord(r->join, r->stream));
         PIO_CUDA(cudaStreamWaitEvent(c.st, r->join, 0));
+        PIO_CUDA(cudaEventRecord(r->join2, r->stream2));
+        PIO_CUDA(cudaStreamWaitEvent(c.st, r->join2, 0));
         used = false;
         return PIO_OK;
     }
@@ -128,7 +135,7 @@ static int tc_dW(Ctx& c, const bf16* dy, int64_t lddy, const bf16* x, int64_t ld
     return gemm_bf16(&d, nullptr, 0, st);  // side stream: atomic accumulation, no scratch
 }
 static int side_colsum(Ctx& c, const Side& sd, const bf16* src, int64_t ld, float* out, int acc, int64_t rows, int cols) {
-    if (sd.active()) return colsum_bf16(src, ld, out, acc, rows, cols, nullptr, 0, sd.stream(), c.dyn);
+    if (sd.active()) return colsum_bf16(src, ld, out, acc, rows, cols, nullptr, 0, sd.stream2(), c.dyn);
     return colsum_bf16(src, ld, out, acc, rows, cols, c.rest(), c.rest_bytes(), c.st, c.dyn);
 }
 
@@ -186,18 +193,27 @@ int mlp_fwd(Ctx& c, const float* x, float* y, const pio_mlp_weights* w, void* sa
 }
 
 int mlp_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_mlp_weights* w, const void* saved,
-            const pio_mlp_grads* g, int acc, int64_t rows, int ch, int residual) {
+            const pio_mlp_grads* g, int acc, int64_t rows, int ch, int residual, const bf16* dy16_in, bf16* dx16_out) {
     PIO_TRY(need_mult8(ch, "channels", "pio_mlp_bwd"));
     MlpSaved s((void*)saved, rows, ch);
     const size_t mark = c.W.off;
-    PIO_TAKE_BYTES(bf16, dy16, c, (size_t)rows * ch * 2, "pio_mlp_bwd");
+    PIO_TAKE_BYTES(bf16, dy16_own, c, (size_t)rows * ch * 2, "pio_mlp_bwd");
     PIO_TAKE_BYTES(bf16, dh1, c, (size_t)rows * ch * 2, "pio_mlp_bwd");
     PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ch * 4, "pio_mlp_bwd");
     Side side(c, acc);
-    const float* dyb;
-    PIO_TRY(branch_grad(c, dy, rows * ch, residual, &dyb, "pio_mlp_bwd"));
-    PIO_TRY(cast_colsum_f32(dyb, ch, dy16, ch, g->b2, acc, rows, ch, c.rest(), c.rest_bytes(), c.st, c.dyn));
-    PIO_TRY(side.fork());
+    const bf16* dy16 = dy16_own;
+    if (dy16_in != nullptr && !(residual && c.drop_p > 0.f) && side.active()) {
+        // the producer of dy (the previous operator's LayerNorm backward) already wrote it as bf16: no cast pass on the
+        // critical chain, and the bias-gradient column sums move to the side stream with the weight gradient
+        dy16 = dy16_in;
+        PIO_TRY(side.fork());
+        PIO_TRY(side_colsum(c, side, dy16, ch, g->b2, acc, rows, ch));
+    } else {
+        const float* dyb;
+        PIO_TRY(branch_grad(c, dy, rows * ch, residual, &dyb, "pio_mlp_bwd"));
+        PIO_TRY(cast_colsum_f32(dyb, ch, dy16_own, ch, g->b2, acc, rows, ch, c.rest(), c.rest_bytes(), c.st, c.dyn));
+        PIO_TRY(side.fork());
+    }
     PIO_TRY(tc_dW(c, dy16, ch, s.g, ch, g->w2, rows, ch, ch, acc, side.stream()));
     PIO_TRY(tc_dyW(c, dy16, ch, (const bf16*)w->w2, ch, rows, ch, ch, nullptr, 0, dh1, ch, 2, s.h1, ch, 0));
     PIO_TRY(side.fork());
@@ -205,7 +221,7 @@ int mlp_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_mlp_we
     PIO_TRY(tc_dW(c, dh1, ch, s.h0, ch, g->w1, rows, ch, ch, acc, side.stream()));
     PIO_TRY(tc_dyW(c, dh1, ch, (const bf16*)w->w1, ch, rows, ch, ch, dh0, ch, nullptr, 0, 0, nullptr, 0, 0));
     PIO_TRY(layernorm_bwd(dh0, x, s.stats, w->ln_w, residual ? dy : nullptr, dx, g->ln_w, g->ln_b, acc, rows, ch,
-                          c.rest(), c.rest_bytes(), c.st, c.dyn));
+                          c.rest(), c.rest_bytes(), c.st, c.dyn, dx16_out));
     PIO_TRY(side.join());
     c.W.off = mark;
     return PIO_OK;
@@ -446,7 +462,8 @@ int self_attn_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* w, v
 }
 
 int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_attn_weights* w, const void* saved,
-                  const pio_attn_grads* g, int acc, int batch, int n, int ch, int heads, int residual) {
+                  const pio_attn_grads* g, int acc, int batch, int n, int ch, int heads, int residual, const bf16* dy16_in,
+                  bf16* dx16_out) {
     PIO_TRY(need_mult8(ch, "channels", "pio_self_attn_bwd"));
     PIO_TRY(check_packed_self(w, ch, "pio_self_attn_bwd"));
     PIO_CHECK_ARG(g->wk == g->wq + (size_t)ch * ch && g->wv == g->wq + 2 * (size_t)ch * ch && g->bk == g->bq + ch &&
@@ -455,16 +472,23 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
     SaSaved s((void*)saved, batch, n, ch, heads);
     const int64_t rows = (int64_t)batch * n;
     const size_t mark = c.W.off;
-    PIO_TAKE_BYTES(bf16, dy16, c, (size_t)rows * ch * 2, "pio_self_attn_bwd");
+    PIO_TAKE_BYTES(bf16, dy16_own, c, (size_t)rows * ch * 2, "pio_self_attn_bwd");
     PIO_TAKE_BYTES(bf16, dqkv16, c, (size_t)rows * 3 * ch * 2, "pio_self_attn_bwd");
     PIO_TAKE_BYTES(float, d_o, c, (size_t)rows * ch * 4, "pio_self_attn_bwd");
     PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ch * 4, "pio_self_attn_bwd");
     PIO_TAKE_BYTES(float, delta, c, (size_t)batch * heads * n * 4, "pio_self_attn_bwd");
     Side side(c, acc);
-    const float* dyb;
-    PIO_TRY(branch_grad(c, dy, rows * ch, residual, &dyb, "pio_self_attn_bwd"));
-    PIO_TRY(cast_colsum_f32(dyb, ch, dy16, ch, g->bo, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
-    PIO_TRY(side.fork());
+    const bf16* dy16 = dy16_own;
+    if (dy16_in != nullptr && !(residual && c.drop_p > 0.f) && side.active()) {  // see mlp_bwd
+        dy16 = dy16_in;
+        PIO_TRY(side.fork());
+        PIO_TRY(side_colsum(c, side, dy16, ch, g->bo, acc, rows, ch));
+    } else {
+        const float* dyb;
+        PIO_TRY(branch_grad(c, dy, rows * ch, residual, &dyb, "pio_self_attn_bwd"));
+        PIO_TRY(cast_colsum_f32(dyb, ch, dy16_own, ch, g->bo, acc, rows, ch, c.rest(), c.rest_bytes(), c.st));
+        PIO_TRY(side.fork());
+    }
     PIO_TRY(tc_dW(c, dy16, ch, s.o16, ch, g->wo, rows, ch, ch, acc, side.stream()));
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.qkv, 3 * ch, s.qkv + ch, s.qkv + 2 * ch, 3 * ch, nullptr, s.o, s.lse, batch, heads, n, n, ch);
@@ -486,8 +510,8 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
     PIO_TRY(side_colsum(c, side, dqkv16, 3 * ch, g->bq, acc, rows, 3 * ch));
     PIO_TRY(tc_dW(c, dqkv16, 3 * ch, s.h0, ch, g->wq, rows, 3 * ch, ch, acc, side.stream()));
     PIO_TRY(tc_dyW(c, dqkv16, 3 * ch, (const bf16*)w->wq, ch, rows, 3 * ch, ch, dh0, ch, nullptr, 0, 0, nullptr, 0, 0));
-    PIO_TRY(pio_layernorm_bwd(dh0, x, s.stats, w->ln_w, residual ? dy : nullptr, dx, g->ln_w, g->ln_b, acc, rows, ch, c.rest(),
-                              c.rest_bytes(), c.st));
+    PIO_TRY(layernorm_bwd(dh0, x, s.stats, w->ln_w, residual ? dy : nullptr, dx, g->ln_w, g->ln_b, acc, rows, ch, c.rest(),
+                          c.rest_bytes(), c.st, nullptr, dx16_out));
     PIO_TRY(side.join());
     c.W.off = mark;
     return PIO_OK;
@@ -511,7 +535,8 @@ size_t block_saved_bytes(int layers, int batch, int n, int ch, int heads) {
 }
 size_t block_ws_bytes(int batch, int n, int ch, int heads) {
     const size_t r = (size_t)batch * n;
-    return 2 * align_up(r * ch * 4, 256) + std::max(sa_ws_bytes(batch, n, ch, heads), mlp_ws_bytes(r, ch)) + 1024;
+    return 2 * align_up(r * ch * 4, 256) + 2 * align_up(r * ch * 2, 256) + std::max(sa_ws_bytes(batch, n, ch, heads), mlp_ws_bytes(r, ch)) +
+           1024;
 }
 
 int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,
@@ -569,18 +594,24 @@ int latent_block_bwd(Ctx& c, const float* dy, const float* x, float* dx, const p
     const int64_t rows = (int64_t)batch * n;
     PIO_TAKE_BYTES(float, dmid, c, (size_t)rows * ch * 4, "pio_latent_block_bwd");
     PIO_TAKE_BYTES(float, dcur, c, (size_t)rows * ch * 4, "pio_latent_block_bwd");
+    // each operator's LayerNorm backward also writes its dx as bf16, which the next operator takes as its dY operand
+    PIO_TAKE_BYTES(bf16, dmid16, c, (size_t)rows * ch * 2, "pio_latent_block_bwd");
+    PIO_TAKE_BYTES(bf16, dcur16, c, (size_t)rows * ch * 2, "pio_latent_block_bwd");
     const float* grad = dy;
+    const bf16* grad16 = nullptr;
     for (int s = layers - 1; s >= 0; --s) {
         const char* slab = (const char*)saved + (size_t)s * L.per_layer;
         const float* x_in = (s == 0) ? x : (const float*)((const char*)saved + (size_t)(s - 1) * L.per_layer + L.xnext);
         const uint64_t seed0 = c.drop_seed;
         c.drop_seed = seed0 + 4 * (uint64_t)s + 2;
-        PIO_TRY(mlp_bwd(c, grad, (const float*)(slab + L.xmid), dmid, &mlp[s], slab + L.mlp, &mlp_g[s], acc, rows, ch, 1));
+        PIO_TRY(mlp_bwd(c, grad, (const float*)(slab + L.xmid), dmid, &mlp[s], slab + L.mlp, &mlp_g[s], acc, rows, ch, 1, grad16, dmid16));
         float* out = (s == 0) ? dx : dcur;
         c.drop_seed = seed0 + 4 * (uint64_t)s;
-        PIO_TRY(self_attn_bwd(c, dmid, x_in, out, &attn[s], slab + L.sa, &attn_g[s], acc, batch, n, ch, heads, 1));
+        PIO_TRY(self_attn_bwd(c, dmid, x_in, out, &attn[s], slab + L.sa, &attn_g[s], acc, batch, n, ch, heads, 1, dmid16,
+                              s == 0 ? nullptr : dcur16));
         c.drop_seed = seed0;
         grad = out;
+        grad16 = (s == 0) ? nullptr : dcur16;
     }
     return PIO_OK;
 }
@@ -925,7 +956,7 @@ int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, 
             d.dyn_rows = count; d.dyn_offset = r0; d.dyn_axis = 1;
             PIO_TRY(gemm_bf16(&d, nullptr, 0, side.stream()));
         }
-        lce_colsum_kernel<<<dim3((unsigned)cdiv(cdiv(classes, 2), 128), (unsigned)cdiv(nr, 128)), 128, 0, side.stream()>>>(
+        lce_colsum_kernel<<<dim3((unsigned)cdiv(cdiv(classes, 2), 128), (unsigned)cdiv(nr, 128)), 128, 0, side.stream2()>>>(
             lg16, cop, db, count, r0, nr, classes);
         PIO_LAUNCH_CHECK();
         {  // dx (compacted) = dlogits W
@@ -990,7 +1021,7 @@ bool decode_rows_supported(int n, int e, int heads) {
     const int dh = e / heads;
     // K_h, V_h as bf16 plus (backward) their fp32 gradients in one CTA's shared memory
     // K_h, V_h (bf16) and the per-warp row buffers of one CTA in shared memory; keys / channels per warp / lane in registers
-    return e % 8 == 0 && dh % 8 == 0 && dh <= 128 && n >= 1 && n <= 128;
+    return e % 8 == 0 && dh % 8 == 0 && dh <= 128 && n >= 4 && n <= 128 && n % 4 == 0;
 }
 
 __global__ void __launch_bounds__(256) dr_pad_labels_kernel(int64_t* __restrict__ labels_c, const int* __restrict__ count, int64_t rows,
@@ -1054,8 +1085,10 @@ __global__ void __launch_bounds__(256) dr_segments_kernel(const int* __restrict_
     for (int b = blockIdx.x * blockDim.x + threadIdx.x; b <= batch; b += gridDim.x * blockDim.x) seg[b] = dr_lower_bound(idx, cnt, b * l);
 }
 
-// Shared-memory layout of one (sample, head): K and V as bf16 pairs with an odd row pitch (reads with lane = key are
-// conflict free, reads with lane = channel pair are anyway), per-warp q / dO (fp32, dh) and p / ds (fp32, n).
+// Shared-memory layout of one (sample, head): K and V as bf16 pairs with a row pitch of dh/2 + 4 words (16-byte
+// aligned, and 16-byte reads with lane = key are conflict free: eight lanes x four words cover the 32 banks), per-warp
+// q / dO (fp32, dh) and p / ds (fp32, n).  These kernels are bound by shared-memory instruction issue (a row's
+// scores are dh-long dot products against every key), hence the 16-byte operand reads everywhere.
 struct DrSmem {
     uint32_t *k, *v;
     float* wbuf;
@@ -1063,14 +1096,14 @@ struct DrSmem {
 };
 __device__ __forceinline__ DrSmem dr_carve(uint8_t* base, int n, int dh) {
     DrSmem s;
-    s.kp = dh / 2 + 1;
+    s.kp = dh / 2 + 4;
     s.k = (uint32_t*)base;
     s.v = s.k + (size_t)n * s.kp;
     s.wbuf = (float*)(s.v + (size_t)n * s.kp);  // [warps][2 * n + 2 * dh]
     return s;
 }
 static size_t dr_smem_bytes(int n, int dh, int warps) {
-    return 2 * (size_t)n * (dh / 2 + 1) * 4 + (size_t)warps * (2 * n + 2 * dh) * 4 + 16;
+    return 2 * (size_t)n * (dh / 2 + 4) * 4 + (size_t)warps * (2 * n + 2 * dh) * 4 + 16;
 }
 __device__ __forceinline__ void dr_load_kv(const DrSmem& s, const bf16* __restrict__ kv, int b, int h, int n, int e, int dh) {
     const int hw = dh / 2;
@@ -1084,6 +1117,34 @@ __device__ __forceinline__ void dr_load_kv(const DrSmem& s, const bf16* __restri
 __device__ __forceinline__ float2 bf2(uint32_t u) {
     const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&u);
     return make_float2(__low2float(h), __high2float(h));
+}
+// acc += sum over 8 channels of x[c] * k[c]: x = two float4 (shared memory, warp-uniform), k = eight bf16 (one 16-byte read)
+__device__ __forceinline__ float dot8(const float* x, const uint4& k, float acc) {
+    const float4 x0 = *reinterpret_cast<const float4*>(x), x1 = *reinterpret_cast<const float4*>(x + 4);
+    const float2 k0 = bf2(k.x), k1 = bf2(k.y), k2 = bf2(k.z), k3 = bf2(k.w);
+    acc = fmaf(x0.x, k0.x, acc); acc = fmaf(x0.y, k0.y, acc); acc = fmaf(x0.z, k1.x, acc); acc = fmaf(x0.w, k1.y, acc);
+    acc = fmaf(x1.x, k2.x, acc); acc = fmaf(x1.y, k2.y, acc); acc = fmaf(x1.z, k3.x, acc); acc = fmaf(x1.w, k3.y, acc);
+    return acc;
+}
+// (a0, a1) += sum over keys [0, n) of w[key] * tile[key][pair]: w in shared memory (fp32, 16-byte reads), tile rows of pitch kp words
+__device__ __forceinline__ void wsum_pairs(const float* w, const uint32_t* tile, int kp, int pair, int n, float& a0, float& a1) {
+    float c0 = 0.f, c1 = 0.f;
+    int key = 0;
+    for (; key + 3 < n; key += 4) {
+        const float4 ww = *reinterpret_cast<const float4*>(w + key);
+        const float2 v0 = bf2(tile[key * kp + pair]), v1 = bf2(tile[(key + 1) * kp + pair]);
+        const float2 v2 = bf2(tile[(key + 2) * kp + pair]), v3 = bf2(tile[(key + 3) * kp + pair]);
+        a0 = fmaf(ww.x, v0.x, a0); a1 = fmaf(ww.x, v0.y, a1);
+        c0 = fmaf(ww.y, v1.x, c0); c1 = fmaf(ww.y, v1.y, c1);
+        a0 = fmaf(ww.z, v2.x, a0); a1 = fmaf(ww.z, v2.y, a1);
+        c0 = fmaf(ww.w, v3.x, c0); c1 = fmaf(ww.w, v3.y, c1);
+    }
+    for (; key < n; ++key) {
+        const float2 v0 = bf2(tile[key * kp + pair]);
+        a0 = fmaf(w[key], v0.x, a0); a1 = fmaf(w[key], v0.y, a1);
+    }
+    a0 += c0;
+    a1 += c1;
 }
 
 constexpr int DR_FWD_WARPS = 8, DR_FWD_SPLIT = 2, DR_BWD_WARPS = 16;
@@ -1116,13 +1177,12 @@ __global__ void __launch_bounds__(DR_FWD_WARPS * 32) dr_attn_fwd_kernel(const bf
         float mx = -INFINITY;
         for (int key = lane; key < n; key += 32) {
             float a0 = 0.f, a1 = 0.f;
-            const uint32_t* kr = s.k + key * s.kp;
-#pragma unroll 4
-            for (int w = 0; w < hw; ++w) {
-                const float2 kk = bf2(kr[w]);
-                a0 = fmaf(qs[2 * w], kk.x, a0);
-                a1 = fmaf(qs[2 * w + 1], kk.y, a1);
+            const uint4* kr = reinterpret_cast<const uint4*>(s.k + key * s.kp);
+            for (int v = 0; v + 1 < dh / 8; v += 2) {
+                a0 = dot8(qs + 8 * v, kr[v], a0);
+                a1 = dot8(qs + 8 * v + 8, kr[v + 1], a1);
             }
+            if ((dh / 8) & 1) a0 = dot8(qs + dh - 8, kr[dh / 8 - 1], a0);
             const float acc = a0 + a1;
             ps[key] = acc;
             mx = fmaxf(mx, acc);
@@ -1138,21 +1198,9 @@ __global__ void __launch_bounds__(DR_FWD_WARPS * 32) dr_attn_fwd_kernel(const bf
         __syncwarp();
         const float inv = 1.0f / sum;
         for (int w = lane; w < hw; w += 32) {
-            float a0 = 0.f, a1 = 0.f, c0 = 0.f, c1 = 0.f;
-            int key = 0;
-            for (; key + 1 < n; key += 2) {
-                const float2 v0 = bf2(s.v[key * s.kp + w]), v1 = bf2(s.v[(key + 1) * s.kp + w]);
-                a0 = fmaf(ps[key], v0.x, a0);
-                a1 = fmaf(ps[key], v0.y, a1);
-                c0 = fmaf(ps[key + 1], v1.x, c0);
-                c1 = fmaf(ps[key + 1], v1.y, c1);
-            }
-            if (key < n) {
-                const float2 v0 = bf2(s.v[key * s.kp + w]);
-                a0 = fmaf(ps[key], v0.x, a0);
-                a1 = fmaf(ps[key], v0.y, a1);
-            }
-            __nv_bfloat162 o2 = __floats2bfloat162_rn((a0 + c0) * inv, (a1 + c1) * inv);
+            float a0 = 0.f, a1 = 0.f;
+            wsum_pairs(ps, s.v, s.kp, w, n, a0, a1);
+            __nv_bfloat162 o2 = __floats2bfloat162_rn(a0 * inv, a1 * inv);
             reinterpret_cast<uint32_t*>(o16 + (int64_t)i * e + h * dh)[w] = *reinterpret_cast<uint32_t*>(&o2);
         }
         if (lane == 0) lse[(int64_t)i * heads + h] = mx + __logf(sum);
@@ -1200,40 +1248,37 @@ __global__ void __launch_bounds__(DR_BWD_WARPS * 32) dr_attn_bwd_kernel(const bf
         const int i = base + wid;
         if (i < hi) {  // ---- phase A (warp-uniform)
             const int64_t off = (int64_t)i * e + h * dh;
-            float delta = 0.f;
             for (int d = lane; d < dh; d += 32) {
                 qs[d] = __bfloat162float(q16[off + d]) * scale;
-                const float g = __bfloat162float(do16[off + d]);
-                gs[d] = g;
-                delta = fmaf(g, __bfloat162float(o16[off + d]), delta);
+                gs[d] = __bfloat162float(do16[off + d]);
             }
-            delta = warp_sum(delta);
             const float lse_i = lse[(int64_t)i * heads + h];
             __syncwarp();
+            // The row term delta = dO . O is formed as sum_k p_k dP_k from the SAME recomputed probabilities that multiply
+            // it below: then sum_k dS_k = 0 holds to fp32 rounding.  With delta taken from the bf16 copy of O its rounding
+            // error e leaves sum_k dS_k = -e, a component of dq along the sample's mean key that is common to all rows and
+            // does not average out — it showed as an O(1) error of the decoder-query LayerNorm gradients.
+            float delta = 0.f;
             for (int key = lane; key < n; key += 32) {
                 float sc = 0.f, dp = 0.f;
-                const uint32_t* kr = s.k + key * s.kp;
-                const uint32_t* vr = s.v + key * s.kp;
-#pragma unroll 4
-                for (int w = 0; w < hw; ++w) {
-                    const float2 kk = bf2(kr[w]), vv = bf2(vr[w]);
-                    sc = fmaf(qs[2 * w], kk.x, fmaf(qs[2 * w + 1], kk.y, sc));
-                    dp = fmaf(gs[2 * w], vv.x, fmaf(gs[2 * w + 1], vv.y, dp));
+                const uint4* kr = reinterpret_cast<const uint4*>(s.k + key * s.kp);
+                const uint4* vr = reinterpret_cast<const uint4*>(s.v + key * s.kp);
+                for (int v = 0; v < dh / 8; ++v) {
+                    sc = dot8(qs + 8 * v, kr[v], sc);
+                    dp = dot8(gs + 8 * v, vr[v], dp);
                 }
                 const float pv = __expf(sc - lse_i);
                 ps[key] = pv;
-                dss[key] = pv * (dp - delta);
+                dss[key] = dp;
+                delta = fmaf(pv, dp, delta);
             }
+            delta = warp_sum(delta);
+            for (int key = lane; key < n; key += 32) dss[key] = ps[key] * (dss[key] - delta);
             __syncwarp();
-            for (int w = lane; w < hw; w += 32) {  // dq = sum_key ds * scale * K[key]
+            for (int w = lane; w < hw; w += 32) {  // dq = scale * sum_key ds * K[key]
                 float a0 = 0.f, a1 = 0.f;
-                for (int key = 0; key < n; ++key) {
-                    const float2 kk = bf2(s.k[key * s.kp + w]);
-                    const float dsk = dss[key] * scale;
-                    a0 = fmaf(dsk, kk.x, a0);
-                    a1 = fmaf(dsk, kk.y, a1);
-                }
-                __nv_bfloat162 o2 = __floats2bfloat162_rn(a0, a1);
+                wsum_pairs(dss, s.k, s.kp, w, n, a0, a1);
+                __nv_bfloat162 o2 = __floats2bfloat162_rn(a0 * scale, a1 * scale);
                 reinterpret_cast<uint32_t*>(dq16 + off)[w] = *reinterpret_cast<uint32_t*>(&o2);
             }
         }

@@ -34,7 +34,7 @@ int layernorm_fwd_bf16(const float* x, const float* w, const float* b, __nv_bflo
                        int64_t rows, int c, float eps, cudaStream_t st, const int* dyn_rows = nullptr);
 int layernorm_bwd(const float* dy, const float* x, const float* stats, const float* w, const float* dres, float* dx, float* dw,
                   float* db, int accumulate, int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t st,
-                  const int* dyn_rows = nullptr);
+                  const int* dyn_rows = nullptr, __nv_bfloat16* dx16 = nullptr);  // dx16: optional bf16 copy of dx
 // dst16 (optional) = bf16(src); colsum (optional, c floats) (+)= column sums of src.  scratch: colsum_ws_bytes
 int cast_colsum_f32(const float* src, int64_t ld_src, __nv_bfloat16* dst16, int64_t ld_dst, float* colsum, int accumulate,
                     int64_t rows, int c, void* ws, size_t ws_bytes, cudaStream_t st, const int* dyn_rows = nullptr);
@@ -110,8 +110,11 @@ namespace bf {
 size_t mlp_saved_bytes(int64_t rows, int ch);
 size_t mlp_ws_bytes(int64_t rows, int ch);
 int mlp_fwd(Ctx& c, const float* x, float* y, const pio_mlp_weights* w, void* saved, int64_t rows, int ch, int residual);
+// dy16_in: dy already as bf16 (skips the cast; the bias-gradient column sums then run on the side stream);
+// dx16_out: also write dx as bf16 (for the next operator's dy16_in)
 int mlp_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_mlp_weights* w, const void* saved,
-            const pio_mlp_grads* g, int acc, int64_t rows, int ch, int residual);
+            const pio_mlp_grads* g, int acc, int64_t rows, int ch, int residual, const __nv_bfloat16* dy16_in = nullptr,
+            __nv_bfloat16* dx16_out = nullptr);
 size_t kv_saved_bytes(int64_t rows, int ckv);
 size_t kv_ws_bytes(int64_t rows, int ckv, int e);
 int kv_project_fwd(Ctx& c, const float* x_kv, float* kv, const pio_attn_weights* w, void* saved, int64_t rows, int ckv, int e);
@@ -129,7 +132,8 @@ size_t sa_ws_bytes(int batch, int n, int ch, int heads);
 int self_attn_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* w, void* saved, int batch, int n, int ch, int heads,
                   int residual);
 int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_attn_weights* w, const void* saved,
-                  const pio_attn_grads* g, int acc, int batch, int n, int ch, int heads, int residual);
+                  const pio_attn_grads* g, int acc, int batch, int n, int ch, int heads, int residual,
+                  const __nv_bfloat16* dy16_in = nullptr, __nv_bfloat16* dx16_out = nullptr);
 size_t block_saved_bytes(int layers, int batch, int n, int ch, int heads);
 size_t block_ws_bytes(int batch, int n, int ch, int heads);
 int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,

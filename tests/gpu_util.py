@@ -40,15 +40,17 @@ def grad_table(got: dict, ref: dict, min_abs=1e-10):
 
 # bf16-mode per-tensor gradient bounds (max-abs error over the tensor's largest magnitude; note that this, like
 # rel_err above, is a tensor-scale metric, not an element-wise relative error).  The north-star tolerance 1e-2 holds
-# for the gradient as a whole (relative L2 over all parameters: measured 7.2e-3 at the benchmarked cfg2 batch 64).
+# for the gradient as a whole (relative L2 over all parameters: measured 7.0e-3 at the benchmarked cfg2 batch 64).
 # Per tensor, measured against the fp32 oracle on B200 (tests/test_gpu_train_step.py -s, cfg2 batch 64 and the small
-# config): every matrix <= 1.3e-2, every LayerNorm / bias vector <= 1.8e-2 — bounded here by 2e-2 and 3e-2 — with ONE
-# exception, the LayerNorm affine terms of the decoder queries (1.3e-1): sums over B*K rows of a softmax gradient whose
-# rows sum to zero, so the terms cancel almost exactly while the unbiased bf16 rounding noise of the operands does
-# not (a CPU run of the oracle with only the GEMM / attention operands rounded to bf16 already moves them by 2.5e-2;
-# the tensor-core attention additionally rounds P to bf16, as every flash-attention kernel does).
+# config): every matrix <= 1.3e-2, every LayerNorm / bias vector <= 2.2e-2, the LayerNorm affine terms of the decoder
+# queries <= 3.3e-2 — bounded here by 2e-2, 3e-2 and 5e-2.
+# (Round 1 held the decoder-query terms to 1e-1 and blamed cancellation.  The cause was the attention backward's row
+#  term delta = dO.O: taken from a rounded O it is inconsistent with the recomputed probabilities, sum_k dS_k is then
+#  -error instead of 0, and dQ gets a component along the sample's mean key that is common to all rows.  The kernels
+#  that see the whole key axis in one tile now form delta = sum_k p_k dP_k from the recomputed p — pio_attn_tc.cu dQ
+#  kernel for <= 64 keys, the labelled-row decoder kernel — and the error fell from 1.3e-1 to 2.5e-2.)
 BF16_GRAD_BOUNDS = [
-    ("decoder.cross_attention.0.module.q_norm.", 2e-1), ("1.cross_attention.0.module.q_norm.", 2e-1),
+    ("decoder.cross_attention.0.module.q_norm.", 5e-2), ("1.cross_attention.0.module.q_norm.", 5e-2),
     ("norm.", 3e-2), (".module.0.", 3e-2), ("bias", 3e-2), ("latent", 3e-2), ("output", 3e-2),
     ("", 2e-2),
 ]

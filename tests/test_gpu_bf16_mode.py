@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda"
 # Logits, loss and the gradient as a whole (all parameters concatenated, relative L2) keep the north-star bf16
 # tolerance of 1e-2.  Per tensor the bound comes from gpu_util.BF16_GRAD_BOUNDS (2e-2 for matrices, 3e-2 for
-# LayerNorm / bias vectors, 2e-1 for the decoder-query LayerNorm terms — each measured and justified there).  Only the
+# LayerNorm / bias vectors, 5e-2 for the decoder-query LayerNorm terms — each measured and justified there).  Only the
 # 8..16-channel golden fixtures keep a blanket 1e-1: with so few numbers per tensor a single bf16 rounding is a visible
 # fraction of the largest entry (vectors of fewer than 32 numbers are held to the whole-gradient criterion only).
 GRAD_TOL_TINY = 1e-1

@@ -152,7 +152,10 @@ def test_graphed_step_matches_eager_steps_and_the_oracle(cfg):
     final_e = {k: p.detach() for k, p in eager.named_parameters()}
     moved = _global_rel(final_e, init)
     assert moved > 1e-4
-    assert _global_rel(final_g, final_e) < 0.05 * moved, (_global_rel(final_g, final_e), moved)  # same trajectory
+    # same trajectory: the two runs differ only in the order of the atomic gradient sums, but AdamW normalises every element's
+    # update by its own gradient magnitude, so elements with a near-zero gradient can step differently: a tenth of the
+    # distance travelled bounds that; a wrong gradient or a stale weight shadow moves the runs apart by the full distance
+    assert _global_rel(final_g, final_e) < 0.1 * moved, (_global_rel(final_g, final_e), moved)
 
 
 def _oracle_step(sd, masked, pad, labels, layers, sa, heads):
