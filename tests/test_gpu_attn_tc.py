@@ -175,3 +175,36 @@ def test_flash_tc_backward_packed_qkv(N):
     assert_rel(dx16[..., :c].float(), dq_ref, 2e-2, "dq")
     assert_rel(dx16[..., c:2 * c].float(), dk_ref, 2e-2, "dk")
     assert_rel(dx16[..., 2 * c:].float(), dv_ref, 2e-2, "dv")
+
+
+@pytest.mark.parametrize("b,n,m,heads,dh", [(1, 256, 16384, 8, 64), (1, 1, 8192, 2, 64), (1, 128, 16384, 2, 128)])
+def test_flash_tc_forward_and_backward_at_long_key_axes(N, b, n, m, heads, dh):
+    """The north-star shape class (M >= 8192; BASELINE configs[3]: N 256, M 16384, 8 heads of 64) and the N = 1 decoder
+    query against fp64: the forward's lazy rescaling (the reference maximum may lag by 2^8) and the backward's tile-by-tile
+    accumulation in TMEM over 256 key tiles."""
+    torch.manual_seed(9)
+    e = heads * dh
+    q16 = torch.randn(b, n, e, device=DEV).to(torch.bfloat16)
+    kv16 = (torch.randn(b, m, 2 * e, device=DEV) * 1.5).to(torch.bfloat16)  # wider scores: the running maximum really moves
+    do16 = torch.randn(b, n, e, device=DEV).to(torch.bfloat16)
+    o_ref, lse_ref, dq_ref, dk_ref, dv_ref = _ref_grads(q16.double().cpu(), kv16[..., :e].double().cpu(), kv16[..., e:].double().cpu(),
+                                                        do16.double().cpu(), None, heads)
+    L = N.lib()
+    o = torch.empty(b, n, e, device=DEV)
+    lse = torch.empty(b, heads, n, device=DEV)
+    d = N.AttnDesc()
+    d.q, d.k, d.v, d.pad, d.o, d.lse = q16.data_ptr(), kv16.data_ptr(), kv16.data_ptr() + 2 * e, None, o.data_ptr(), lse.data_ptr()
+    d.q_bs, d.q_rs, d.k_bs, d.k_rs, d.v_bs, d.v_rs, d.o_bs, d.o_rs = n * e, e, m * 2 * e, 2 * e, m * 2 * e, 2 * e, n * e, e
+    d.batch, d.heads, d.n, d.m, d.dh, d.scale = b, heads, n, m, dh, dh ** -0.5
+    N.check(L.pio_attn_fwd(ctypes.byref(d), 1, N.stream_ptr()), "pio_attn_fwd")
+    dq16 = torch.full((b, n, e), float("nan"), device=DEV, dtype=torch.bfloat16)
+    dkv16 = torch.full((b, m, 2 * e), float("nan"), device=DEV, dtype=torch.bfloat16)
+    delta = torch.empty(b, heads, n, device=DEV)
+    N.check(L.pio_attn_bwd_bf16(ctypes.byref(d), do16.data_ptr(), dq16.data_ptr(), dkv16.data_ptr(), dkv16.data_ptr() + 2 * e,
+                                delta.data_ptr(), N.stream_ptr()), "pio_attn_bwd_bf16")
+    torch.cuda.synchronize()
+    assert_rel(o, o_ref, BF16_TOL, "o")
+    assert_rel(lse, lse_ref, 1e-4, "lse")
+    assert_rel(dq16.float(), dq_ref, 2e-2, "dq")
+    assert_rel(dkv16[..., :e].float(), dk_ref, 2e-2, "dk")
+    assert_rel(dkv16[..., e:].float(), dv_ref, 2e-2, "dv")

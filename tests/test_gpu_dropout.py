@@ -141,3 +141,31 @@ def test_bf16_mode_with_dropout_matches_fp32_mode_with_the_same_masks():
     num = sum(((grads["bf16"][k] - grads["fp32"][k]).double().norm() ** 2).item() for k in grads["fp32"])
     den = sum((grads["fp32"][k].double().norm() ** 2).item() for k in grads["fp32"])
     assert (num / den) ** 0.5 < 2e-2
+
+
+def test_masks_of_neighbouring_sites_are_uncorrelated():
+    """with hash(idx + seed) the mask of site seed + k was the mask of site seed shifted by k elements (the
+    Residual site is seed + 1, latent layer s uses seed + 4 s and + 2).  The site key is now mixed on its own before it
+    meets the element index: masks of neighbouring seeds must be uncorrelated at every small shift."""
+    import perceiver.functional as F
+    torch.manual_seed(0)
+    p, n, c = 0.5, 4096, 64
+    ps = [torch.ones(c, device=DEV), torch.zeros(c, device=DEV), torch.eye(c, device=DEV), torch.zeros(c, device=DEV),
+          torch.eye(c, device=DEV), torch.zeros(c, device=DEV)]
+    x = torch.randn(n, c, device=DEV) + 3.0
+
+    def mask(seed):
+        # Residual(mlp) with dropout: y - x is zero exactly where the branch output was dropped (site seed + 1)
+        y = F.MlpFn.apply(x, *ps, True, p, seed)
+        return ((y - x) != 0).float().reshape(-1)
+
+    base = 123456789
+    m0 = mask(base)
+    assert abs(m0.mean().item() - (1 - p)) < 0.01
+    for dseed in (1, 2, 3, 4, 8):
+        m1 = mask(base + dseed)
+        for shift in range(0, 9):
+            a = m0[: m0.numel() - 16]
+            b = m1[shift: shift + a.numel()]
+            corr = ((a - a.mean()) * (b - b.mean())).mean() / (a.std() * b.std())
+            assert abs(corr.item()) < 0.02, (dseed, shift, corr.item())
