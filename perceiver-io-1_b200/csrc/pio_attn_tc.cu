@@ -1,19 +1,22 @@
-// Flash-style attention forward on the 5th-gen tensor cores (PIO_MODE_BF16, head dim 64).
+// Flash-style attention on the 5th-gen tensor cores (PIO_MODE_BF16, head dim 32 / 64 / 128): forward, dQ and dK/dV.
 //
-// One CTA owns 128 query rows of one (batch, head) and streams the key/value axis in tiles of BKV keys:
-//   * Q, K and V tiles arrive by 3-D TMA (cp.async.bulk.tensor, 128-byte swizzle; the batch and row
-//     axes are separate tensor dimensions so rows past the end of a sample are zero-filled);
-//   * S = Q K^T is a tcgen05.mma (M=128, N=BKV, K=64) into TMEM; four softmax warps read it with
-//     tcgen05.ld (one query row per thread), apply scale, padding mask and the online-softmax update,
-//     and write P as bf16 straight into the swizzled K-major shared-memory layout the next MMA reads;
-//   * O_tile = P V is a second tcgen05.mma (V is consumed MN-major, exactly as TMA delivered it) into
-//     its own TMEM columns; the softmax threads fold it into their fp32 register accumulator with the
-//     running-max correction, so no N x M quantity ever exists outside the SM.
-// Small tiles (BKV = 64, 64 KB of shared memory, 128 TMEM columns) keep three CTAs resident per SM;
-// their phases interleave, which is what hides the TMA / MMA / MUFU latencies of this simple,
-// non-pipelined per-CTA schedule.
-// Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..5 = softmax.
+// Forward: one CTA owns 128 query rows of one (batch, head) and streams the key/value axis in tiles of 64 keys:
+//   * Q, K and V tiles arrive by 3-D TMA (cp.async.bulk.tensor, 128-byte swizzle; batch and row are separate tensor
+//     dimensions, so rows past the end of a sample are zero-filled), K/V through a 3-stage ring;
+//   * S = Q K^T is a tcgen05.mma (M=128, N=64) into one of two TMEM buffers; four softmax warps read it with tcgen05.ld
+//     (one query row per thread), apply scale, padding mask and the online softmax with ex2.approx against a LAZILY
+//     updated reference maximum (O and the running sum are rescaled only when the maximum grew by more than 2^8), and
+//     hand P to the P.V product as bf16 pairs THROUGH TENSOR MEMORY (tcgen05.st; the MMA takes its A operand from
+//     TMEM: no shared-memory round trip);
+//   * O += P V accumulates in TMEM across all key tiles (V is consumed MN-major, exactly as TMA delivered it); the
+//     schedule is software-pipelined: S(j+1) is issued before P(j) is awaited;
+//   * two CTAs per SM (one at dh = 128: 512 TMEM columns).
+// Backward (P recomputed from the saved log-sum-exp): a dQ kernel per 128 query rows and a dK/dV kernel per 128 key
+// rows on the transposed tile; dS / P^T / dS^T reach their products through tensor memory as well (see below).
+// Warp roles in all three: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..5 = softmax / math.
 #include <cuda.h>
+
+#include <atomic>
 #include <stdlib.h>
 
 #include "pio_ops_common.cuh"
@@ -838,11 +841,14 @@ static int launch_fwd(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const C
     constexpr int BKV = 64;
     constexpr int TC = HeadGeom<DH>::TILE_COLS;
     const size_t smem = (size_t)FA_BQ * TC * 2 + 6 * (size_t)BKV * TC * 2 + 2 * BKV * 4 + 128 + 1024;
-    static bool configured = false;  // per head size
-    if (!configured) {
+    static std::atomic<bool> configured[64];  // per head size
+    int dev_ = 0;
+    PIO_CUDA(cudaGetDevice(&dev_));  // the attribute is per function AND per device
+    dev_ = (dev_ >= 0 && dev_ < 64) ? dev_ : 0;
+    if (!configured[dev_].load()) {
         PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV, false, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         PIO_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel<BKV, true, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
+        configured[dev_].store(true);
     }
     if (p.drop.threshold != 0) PIO_CUDA(launch_pdl(attn_fwd_tc_kernel<BKV, true, DH>, grid, dim3(FA_THREADS), smem, st, tq, tk, tv, p));
     else PIO_CUDA(launch_pdl(attn_fwd_tc_kernel<BKV, false, DH>, grid, dim3(FA_THREADS), smem, st, tq, tk, tv, p));
@@ -854,11 +860,14 @@ static int launch_bwd_dq(dim3 grid, cudaStream_t st, const CUtensorMap& tq, cons
                          const CUtensorMap& tv, const FaBwdParams& p) {
     constexpr int TC = HeadGeom<DH>::TILE_COLS;
     const size_t smem = 2 * (size_t)FA_BQ * TC * 2 + 6 * (size_t)64 * TC * 2 + 2 * 64 * 4 + 128 + 1024;
-    static bool configured = false;
-    if (!configured) {
+    static std::atomic<bool> configured[64];
+    int dev_ = 0;
+    PIO_CUDA(cudaGetDevice(&dev_));  // the attribute is per function AND per device
+    dev_ = (dev_ >= 0 && dev_ < 64) ? dev_ : 0;
+    if (!configured[dev_].load()) {
         PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<false, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<true, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
+        configured[dev_].store(true);
     }
     if (p.drop.threshold != 0) PIO_CUDA(launch_pdl(attn_bwd_dq_tc_kernel<true, DH>, grid, dim3(FA_THREADS), smem, st, tq, tdo, tk, tv, p));
     else PIO_CUDA(launch_pdl(attn_bwd_dq_tc_kernel<false, DH>, grid, dim3(FA_THREADS), smem, st, tq, tdo, tk, tv, p));
@@ -870,11 +879,14 @@ static int launch_bwd_dkv(dim3 grid, cudaStream_t st, const CUtensorMap& tq, con
                           const CUtensorMap& tv, const FaBwdParams& p) {
     constexpr int TC = HeadGeom<DH>::TILE_COLS;
     const size_t smem = 2 * (size_t)128 * TC * 2 + 4 * (size_t)64 * TC * 2 + 4 * 64 * 4 + 128 + 1024;
-    static bool configured = false;
-    if (!configured) {
+    static std::atomic<bool> configured[64];
+    int dev_ = 0;
+    PIO_CUDA(cudaGetDevice(&dev_));  // the attribute is per function AND per device
+    dev_ = (dev_ >= 0 && dev_ < 64) ? dev_ : 0;
+    if (!configured[dev_].load()) {
         PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<false, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         PIO_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<true, DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
+        configured[dev_].store(true);
     }
     if (p.drop.threshold != 0) PIO_CUDA(launch_pdl(attn_bwd_dkv_tc_kernel<true, DH>, grid, dim3(FA_THREADS), smem, st, tq, tdo, tk, tv, p));
     else PIO_CUDA(launch_pdl(attn_bwd_dkv_tc_kernel<false, DH>, grid, dim3(FA_THREADS), smem, st, tq, tdo, tk, tv, p));

@@ -4,14 +4,18 @@
 //     shared-memory ring guarded by full/empty mbarriers;
 //   * one elected thread issues tcgen05.mma (kind::f16, M=128, N=BN, K=16) with the fp32
 //     accumulator tile in TMEM; tcgen05.commit releases ring slots and signals the epilogue;
-//   * four epilogue warps read the accumulator with tcgen05.ld (lane = row), apply
-//     bias / GELU / GELU' / residual and store fp32 and/or bf16.
+//   * eight epilogue warps (two per TMEM lane quadrant, half the tile's columns each) read the accumulator with
+//     tcgen05.ld (lane = row), stage it through shared memory and finish it with coalesced row segments:
+//     bias / GELU / GELU' / residual / accumulate / atomics, fp32 and/or bf16; operands the epilogue reads from
+//     global memory are requested before the accumulator is waited for (64-wide tiles).
 //
 // Either operand may be K-major (row = m|n, contiguous k: activations X, weights W for X W^T) or
 // MN-major (row = k, contiguous m|n: W for dY W, and dY / X for the weight gradient dY^T X), so
 // every product of the forward and backward pass reads its operands where they already lie.
-// Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..5 = epilogue.
+// Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..9 = epilogue.
 #include <cuda.h>
+
+#include <atomic>
 #include <stdlib.h>
 
 #include <mutex>
@@ -468,10 +472,13 @@ static void tc_choose(int64_t m, int64_t n, int64_t k, bool splittable, int* bn,
 template <int BN, bool A_MN, bool B_MN>
 static int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, dim3 grid, cudaStream_t st) {
     const size_t smem = (size_t)TC_STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + 1024 + 256;
-    static bool configured = false;  // per instantiation; attribute is sticky per function
-    if (!configured) {
+    static std::atomic<bool> configured[64];  // per instantiation; attribute is sticky per function
+    int dev_ = 0;
+    PIO_CUDA(cudaGetDevice(&dev_));  // the attribute is per function AND per device
+    dev_ = (dev_ >= 0 && dev_ < 64) ? dev_ : 0;
+    if (!configured[dev_].load()) {
         PIO_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
+        configured[dev_].store(true);
     }
     PIO_CUDA(launch_pdl(gemm_tc_kernel<BN, A_MN, B_MN>, grid, dim3(TC_THREADS), smem, st, ta, tb, p));
     count_launch();

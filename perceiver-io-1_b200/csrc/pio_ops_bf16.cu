@@ -5,7 +5,9 @@
 // biases stay fp32.  Saved activations that only feed GEMMs are kept in bf16.
 #include <stdlib.h>
 
+#include <map>
 #include <mutex>
+#include <utility>
 
 #include "pio_ops_common.cuh"
 
@@ -46,35 +48,43 @@ struct SideRes {
     cudaStream_t stream2 = nullptr;  // bias-gradient column sums (beside the GEMMs: one chain was the longer of the operator's two)
     cudaEvent_t fork = nullptr, join = nullptr, join2 = nullptr;
 };
-static SideRes* side_res() {
-    static SideRes res[64];
+// One set of side streams / events per (device, caller stream): two host threads (or two streams) running backward
+// operators on the same GPU must not share fork / join events — a second caller's record would overwrite the first's and
+// let side-stream kernels start before their producers.
+static SideRes* side_res(cudaStream_t caller) {
+    static std::map<std::pair<int, cudaStream_t>, SideRes*> table;
     static std::mutex mu;
     static const bool disabled = getenv("PIO_NO_SIDE_STREAM") != nullptr;
     if (disabled) return nullptr;
     int dev = -1;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) return nullptr;
     std::lock_guard<std::mutex> lock(mu);
-    SideRes& r = res[dev];
-    if (r.stream == nullptr) {
-        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
-        (void)cs;
-        if (cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking) != cudaSuccess) { r.stream = nullptr; return nullptr; }
-        if (cudaStreamCreateWithFlags(&r.stream2, cudaStreamNonBlocking) != cudaSuccess ||
-            cudaEventCreateWithFlags(&r.fork, cudaEventDisableTiming) != cudaSuccess ||
-            cudaEventCreateWithFlags(&r.join2, cudaEventDisableTiming) != cudaSuccess ||
-            cudaEventCreateWithFlags(&r.join, cudaEventDisableTiming) != cudaSuccess) {
-            r.stream = nullptr;
+    SideRes*& slot = table[std::make_pair(dev, caller)];
+    if (slot == nullptr) {
+        if (table.size() > 256) {  // (a caller that keeps making streams: stay on its own stream rather than leak)
+            table.erase(std::make_pair(dev, caller));
             return nullptr;
         }
+        SideRes* r = new SideRes();
+        if (cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaStreamCreateWithFlags(&r->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&r->fork, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&r->join2, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&r->join, cudaEventDisableTiming) != cudaSuccess) {
+            delete r;
+            table.erase(std::make_pair(dev, caller));
+            return nullptr;
+        }
+        slot = r;
     }
-    return &r;
+    return slot;
 }
 
 struct Side {
     Ctx& c;
     SideRes* r;
     bool used = false;
-    Side(Ctx& ctx, int acc) : c(ctx), r(acc == 2 ? side_res() : nullptr) {}
+    Side(Ctx& ctx, int acc) : c(ctx), r(acc == 2 ? side_res(ctx.st) : nullptr) {}
     bool active() const { return r != nullptr; }
     cudaStream_t stream() const { return r ? r->stream : c.st; }
     cudaStream_t stream2() const { return r ? r->stream2 : c.st; }

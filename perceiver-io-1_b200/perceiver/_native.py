@@ -179,6 +179,14 @@ def ptr(t):
 
 
 def stream_ptr(device=None):
+    """the caller's current stream on ``device``.  The library resolves per-device resources (side streams, the SM count,
+    function attributes, the no-allocation scratch array) for the CURRENT device, so the tensors' device must be the
+    current one: anything else is refused here, loudly, instead of pairing a stream with another device's resources."""
+    if device is not None:
+        idx = torch.device(device).index
+        if idx is not None and idx != torch.cuda.current_device():
+            raise RuntimeError(f"perceiver (B200-native): tensors live on cuda:{idx} but the current device is "
+                               f"cuda:{torch.cuda.current_device()}; wrap the call in `with torch.cuda.device({idx}):`")
     return torch.cuda.current_stream(device).cuda_stream
 
 

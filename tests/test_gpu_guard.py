@@ -5,6 +5,8 @@ import ctypes
 import pytest
 import torch
 
+from gpu_util import rel_err
+
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
 GAP = 4096
@@ -110,3 +112,56 @@ def test_adamw_and_flat_copy_stay_inside_their_tensors():
             ld = (s[1] + 7) // 8 * 8
             assert torch.equal(sh.view(s[0], ld)[:, :s[1]], p.view(s).to(torch.bfloat16))
             assert not sh.view(s[0], ld)[:, s[1]:].any()
+
+
+def test_two_threads_on_two_streams_run_backward_operators_concurrently():
+    """the side streams / fork-join events of the bf16 backward operators were one set per device, so
+    two host threads (or two streams) could overwrite each other's fork record.  They are now keyed by (device, caller
+    stream): two threads hammering pio_mlp_bwd (accumulate = 2, side-stream weight gradients) on their own streams must
+    each reproduce their single-threaded result."""
+    import threading
+    import perceiver
+    from perceiver import functional as F
+    perceiver.set_compute_mode("bf16")
+    try:
+        torch.manual_seed(0)
+        c, rows = 128, 2048
+
+        def make(seed):
+            g = torch.Generator(device=DEV).manual_seed(seed)
+            x = torch.randn(rows, c, device=DEV, generator=g)
+            ps = [torch.randn(s, device=DEV, generator=g) * 0.2 for s in [(c,), (c,), (c, c), (c,), (c, c), (c,)]]
+            dy = torch.randn(rows, c, device=DEV, generator=g)
+            return x, ps, dy
+
+        def run(x, ps, dy, iters, out):
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st):
+                for _ in range(iters):
+                    xin = x.clone().requires_grad_(True)
+                    pin = [p.clone().requires_grad_(True) for p in ps]
+                    y = F.MlpFn.apply(xin, *pin, True)
+                    y.backward(dy)
+                    out.append([xin.grad.clone()] + [p.grad.clone() for p in pin])
+            st.synchronize()
+
+        cases = [make(1), make(2)]
+        ref = []
+        for cs in cases:
+            o = []
+            run(*cs, 1, o)
+            ref.append(o[0])
+        outs = [[], []]
+        threads = [threading.Thread(target=run, args=(*cases[i], 25, outs[i])) for i in range(2)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        torch.cuda.synchronize()
+        for i in range(2):
+            assert len(outs[i]) == 25
+            for got in outs[i]:
+                for g, r in zip(got, ref[i]):
+                    assert rel_err(g, r) < 2e-3  # (atomics: summation order differs from run to run)
+    finally:
+        perceiver.set_compute_mode("fp32")
