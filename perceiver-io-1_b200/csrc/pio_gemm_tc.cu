@@ -282,6 +282,34 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
         if (m0 >= m_eff || blockIdx.z * p.kb_per_split >= num_kb) return;  // nothing to do: leave before any set-up
     }
 
+    const int kb_begin = blockIdx.z * p.kb_per_split;
+    const int kb_end = min(num_kb, kb_begin + p.kb_per_split);
+    const int nkb = kb_end - kb_begin;
+
+    // one k-block of both operands into ring stage i % TC_STAGES
+    auto load_kb = [&](int i) {
+        const int s = i % TC_STAGES;
+        const uint32_t ph = (uint32_t)(i / TC_STAGES) & 1u;
+        mbar_wait(&empty_bar[s], ph ^ 1u);
+        mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+        const int k0 = (kb_begin + i) * TC_BK;
+        uint8_t* a_dst = sA + s * A_STAGE;
+        uint8_t* b_dst = sB + s * B_STAGE;
+        if (!A_MN) {
+            tma_load_2d(a_dst, &tmA, k0, m0, &full_bar[s]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < TC_BM / 64; ++j) tma_load_2d(a_dst + j * 8192, &tmA, m0 + j * 64, k0, &full_bar[s]);
+        }
+        if (!B_MN) {
+            tma_load_2d(b_dst, &tmB, k0, n0, &full_bar[s]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) tma_load_2d(b_dst + j * 8192, &tmB, n0 + j * 64, k0, &full_bar[s]);
+        }
+    };
+    const int early_kb = min(nkb, TC_STAGES);
+
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmA);
         prefetch_tmap(&tmB);
@@ -291,6 +319,10 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
         }
         mbar_init(tmem_full, 1);
         fence_barrier_init();
+        // fill the ring before the TMEM allocation and the block barrier: the first loads' latency
+        // then overlaps the rest of the prologue (the operands come from earlier kernels, hence the wait)
+        pdl_wait();
+        for (int i = 0; i < early_kb; ++i) load_kb(i);
     }
     if (warp == 1) tmem_alloc(tmem_slot, BN);
     tc_fence_before();
@@ -299,33 +331,9 @@ __global__ void __launch_bounds__(TC_THREADS, 2)
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();  // prologue done; from here on the kernel reads / writes what earlier kernels produced
 
-    const int kb_begin = blockIdx.z * p.kb_per_split;
-    const int kb_end = min(num_kb, kb_begin + p.kb_per_split);
-    const int nkb = kb_end - kb_begin;
-
     if (warp == 0) {
         if (lane == 0) {
-            for (int i = 0; i < nkb; ++i) {
-                const int s = i % TC_STAGES;
-                const uint32_t ph = (uint32_t)(i / TC_STAGES) & 1u;
-                mbar_wait(&empty_bar[s], ph ^ 1u);
-                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-                const int k0 = (kb_begin + i) * TC_BK;
-                uint8_t* a_dst = sA + s * A_STAGE;
-                uint8_t* b_dst = sB + s * B_STAGE;
-                if (!A_MN) {
-                    tma_load_2d(a_dst, &tmA, k0, m0, &full_bar[s]);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < TC_BM / 64; ++j) tma_load_2d(a_dst + j * 8192, &tmA, m0 + j * 64, k0, &full_bar[s]);
-                }
-                if (!B_MN) {
-                    tma_load_2d(b_dst, &tmB, k0, n0, &full_bar[s]);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < BN / 64; ++j) tma_load_2d(b_dst + j * 8192, &tmB, n0 + j * 64, k0, &full_bar[s]);
-                }
-            }
+            for (int i = early_kb; i < nkb; ++i) load_kb(i);
         }
         __syncwarp();
     } else if (warp == 1) {

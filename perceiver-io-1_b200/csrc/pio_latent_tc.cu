@@ -43,16 +43,13 @@
 #include <cuda.h>
 #include <stdlib.h>
 
-#include "pio_ops_common.cuh"
-#include "pio_tc_common.cuh"
+#include "pio_latent_common.cuh"
 
 namespace pio {
 
 int make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows);
 
 namespace lb {
-
-using bf16 = __nv_bfloat16;
 
 constexpr int C = 256;
 constexpr int DH = 64;
@@ -121,115 +118,7 @@ __device__ int g_trace_n[2];
 #define LB_TRACE(who, tag) do { } while (0)
 #endif
 
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ float ex2(float x) {
-    float y;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-}
 __device__ __forceinline__ void bar_ew() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
-__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2) {
-    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"((uint64_t)map),
-                 "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
-                 : "memory");
-}
-__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-// 32 fp32 of row `row` (0..31) into a 32-row x 128-byte swizzled staging slice
-__device__ __forceinline__ void stage_row_f32(uint8_t* slice, int row, const float (&v)[32]) {
-    uint8_t* prow = slice + row * 128;
-#pragma unroll
-    for (int j = 0; j < 8; ++j)
-        *reinterpret_cast<float4*>(prow + ((j ^ (row & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-}
-
-__device__ __forceinline__ void ld_chunk(uint32_t taddr, float (&v)[32]) {
-    uint32_t r[32];
-    tmem_ld32(taddr, r);
-    tmem_ld_wait();
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-}
-__device__ __forceinline__ void st_chunk(uint32_t taddr, const float (&v)[32]) {
-    uint32_t r[32];
-#pragma unroll
-    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(v[i]);
-    tmem_st32(taddr, r);
-}
-
-// 32 fp32 -> bf16 into row `row`, 64-byte half `hh` of a 128-row x 128-byte swizzled (SW128, K-major) atom
-__device__ __forceinline__ void store_half_row_smem(uint8_t* atom, int row, int hh, const float (&v)[32]) {
-    uint8_t* prow = atom + row * 128;
-#pragma unroll
-    for (int piece = 0; piece < 4; ++piece) {
-        uint32_t w[4];
-#pragma unroll
-        for (int e2 = 0; e2 < 4; ++e2) {
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[piece * 8 + 2 * e2], v[piece * 8 + 2 * e2 + 1]);
-            w[e2] = *reinterpret_cast<uint32_t*>(&h2);
-        }
-        const int ci = hh * 4 + piece;
-        *reinterpret_cast<uint4*>(prow + ((ci ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
-    }
-}
-__device__ __forceinline__ void store32_bf16_global(bf16* dst, const float (&v)[32]) {
-#pragma unroll
-    for (int d = 0; d < 32; d += 8) {
-        uint32_t w[4];
-#pragma unroll
-        for (int e2 = 0; e2 < 4; ++e2) {
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[d + 2 * e2], v[d + 2 * e2 + 1]);
-            w[e2] = *reinterpret_cast<uint32_t*>(&h2);
-        }
-        *reinterpret_cast<uint4*>(dst + d) = make_uint4(w[0], w[1], w[2], w[3]);
-    }
-}
-__device__ __forceinline__ void store32_f32_global(float* dst, const float (&v)[32]) {
-#pragma unroll
-    for (int d = 0; d < 32; d += 4) *reinterpret_cast<float4*>(dst + d) = make_float4(v[d], v[d + 1], v[d + 2], v[d + 3]);
-}
-// v[i] += p[i], p in shared memory and warp-uniform (a broadcast read)
-__device__ __forceinline__ void add_vec32(float (&v)[32], const float* p) {
-#pragma unroll
-    for (int d = 0; d < 32; d += 4) {
-        const float4 t = *reinterpret_cast<const float4*>(p + d);
-        v[d] += t.x; v[d + 1] += t.y; v[d + 2] += t.z; v[d + 3] += t.w;
-    }
-}
-
-// running (count, mean, sum of squared deviations); chunks merge with Chan's update, so the statistics
-// are as robust as a two-pass LayerNorm although every value is seen once
-struct Stat {
-    float n, mean, m2;
-};
-__device__ __forceinline__ void stat_merge(Stat& a, float nb, float mean_b, float m2_b) {
-    const float nt = a.n + nb;
-    const float d = mean_b - a.mean;
-    const float f = nb / nt;
-    a.mean = fmaf(d, f, a.mean);
-    a.m2 = a.m2 + m2_b + d * d * a.n * f;
-    a.n = nt;
-}
-__device__ __forceinline__ void stat_chunk(Stat& a, const float (&v)[32]) {
-    float s = 0.f;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) s += v[i];
-    const float mean = s * (1.0f / 32.0f);
-    float m2 = 0.f;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) {
-        const float d = v[i] - mean;
-        m2 = fmaf(d, d, m2);
-    }
-    if (a.n == 0.f) {
-        a.n = 32.f; a.mean = mean; a.m2 = m2;
-    } else {
-        stat_merge(a, 32.f, mean, m2);
-    }
-}
 
 __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __grid_constant__ Params p) {
     extern __shared__ uint8_t smem_raw[];
@@ -724,31 +613,6 @@ __global__ void __launch_bounds__(THREADS, 1) latent_block_fwd_kernel(const __gr
 
 }  // namespace lb
 
-// (cols, rows, layers) tensor map with byte strides (pitch, layer_stride); box = box_cols x box_rows x 1, 128-byte swizzle
-static int make_out_map(CUtensorMap* map, bool f32, const void* base, int64_t cols, int64_t rows, int64_t nl, int64_t pitch,
-                        int64_t layer_stride, int box_cols, int box_rows) {
-    EncodeTiledFn fn = get_encode_fn();
-    if (!fn) {
-        set_error("cuTensorMapEncodeTiled entry point not available from the driver");
-        return PIO_ERR_CUDA;
-    }
-    PIO_CHECK_ARG((((uintptr_t)base) & 15) == 0 && pitch % 16 == 0 && layer_stride % 16 == 0 && layer_stride > 0,
-                  "latent_block_fwd_fused: saved-state tensor not 16-byte aligned (base %p pitch %lld layer stride %lld)", base,
-                  (long long)pitch, (long long)layer_stride);
-    cuuint64_t gdim[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)nl};
-    cuuint64_t gstr[2] = {(cuuint64_t)pitch, (cuuint64_t)layer_stride};
-    cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1u};
-    cuuint32_t estr[3] = {1u, 1u, 1u};
-    CUresult r = fn(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim,
-                    gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) {
-        set_error("cuTensorMapEncodeTiled (latent block output) failed with CUresult %d", (int)r);
-        return PIO_ERR_CUDA;
-    }
-    return PIO_OK;
-}
-
 #ifdef PIO_LB_TRACE
 extern "C" int pio_debug_lb_trace(long long* out, int max_pairs, int who, int reset) {
     int n = 0;
@@ -773,15 +637,21 @@ extern "C" int pio_debug_lb_trace(long long* out, int max_pairs, int who, int re
 // tile's element-wise work (~80 K warp instructions per layer) and its 1.5 MB of weight + saved-state traffic
 // per layer are then concentrated on a quarter of the SMs.  PIO_FUSED_LATENT_MIN_ROWS overrides the threshold
 // (0 = always), PIO_NO_FUSED_LATENT switches the kernel off; both are read per call (tests compare the two paths).
+bool latent_cluster_preferred(int64_t rows);
+int latent_block_fwd_cluster(const float* x, const LatentFusedLayer* layers, int nlayers, int batch, int n, cudaStream_t st);
+
 bool latent_fused_supported(int64_t rows, int n, int ch, int heads, float drop_p) {
     if (getenv("PIO_NO_FUSED_LATENT") != nullptr) return false;
+    if (!(ch == lb::C && heads == lb::H && (n == 32 || n == 64 || n == 128) && !(drop_p > 0.f))) return false;
+    if (latent_cluster_preferred(rows)) return true;  // the cluster kernel (pio_latent_cl.cu) wins at any tile count it takes
     int64_t min_rows = 56 * lb::ROWS;
     if (const char* e = getenv("PIO_FUSED_LATENT_MIN_ROWS")) min_rows = atoll(e);
-    return rows >= min_rows && ch == lb::C && heads == lb::H && (n == 32 || n == 64 || n == 128) && !(drop_p > 0.f);
+    return rows >= min_rows;
 }
 
 int latent_block_fwd_fused(const float* x, const LatentFusedLayer* layers, int nlayers, int batch, int n, cudaStream_t st) {
     PIO_CHECK_ARG(x && layers && nlayers >= 1 && nlayers <= PIO_LATENT_FUSED_MAX_LAYERS, "latent_block_fwd_fused: bad arguments");
+    if (latent_cluster_preferred((int64_t)batch * n)) return latent_block_fwd_cluster(x, layers, nlayers, batch, n, st);
     const int64_t rows = (int64_t)batch * n;
     if (rows == 0) return PIO_OK;
     lb::Params p{};
