@@ -21,16 +21,16 @@
 //     all four CTAs normalise with bit-identical (mean, rstd).
 //
 // Cross-CTA protocol (all mbarriers; no cluster-wide barrier inside the layer loop):
-//   gath_full (count 1 + 48 KB of transaction bytes): the local slice is written (thread 0 arrives after the
-//       element-wise warps' barrier) and the three remote slices have landed -> the MMA thread may issue.
+//   gath_full[j] (j = r: count 4, one arrival per TMEM lane quadrant; j != r: count 1 + 16 KB of transaction
+//       bytes): atom j of the operand is complete in this CTA -> the MMA thread may issue that k-block's products.
 //   gath_free (count 4): every CTA of the cluster, itself included, has seen the products that read the previous
 //       gather complete (thread 0 of each CTA arrives remotely after its mma_done wait) -> thread 0 may overwrite
 //       the peers' atoms with the next gather.
-//   stat_full (count 32 = 4 CTAs x 8 warps): all LayerNorm partials of this round have arrived.
+//   stat_full (count 1 + 8 KB of transaction bytes): all LayerNorm partials of this round have arrived (st.async).
 // A peer can never run a whole phase ahead on any of them: each gather needs every CTA's previous product.
 //
 // Warp roles: warps 0..7 element-wise (TMEM lane quadrant = warp & 3, column half = warp >> 2: a thread owns 32 of
-// its row's 64 local columns), warp 8 = TMA producer (weights, 3 x 32 KB ring), warp 9 = TMEM allocator + MMA
+// its row's 64 local columns), warp 8 = TMA producer (weights, 4 x 24 KB ring), warp 9 = TMEM allocator + MMA
 // issuer + TMA stores of the bf16 saved state straight out of the operand tiles.
 #include <cuda.h>
 #include <stdlib.h>
@@ -56,9 +56,10 @@ constexpr int ROWS = 128;
 constexpr int EW_WARPS = 8;
 constexpr int EW_THREADS = EW_WARPS * 32;
 constexpr int THREADS = EW_THREADS + 64;
-constexpr int STAGES = 3;
-constexpr int STAGE_BYTES = 32768;
-constexpr int QKV_STAGE_BYTES = 3 * 64 * 128;  // 64 rows each of Wq_r, Wk_r, Wv_r x one 64-column k-block
+constexpr int STAGES = 4;
+constexpr int STAGE_BYTES = 24576;
+constexpr int QKV_STAGE_BYTES = 3 * 64 * 128;  // 64 rows each of Wq_r, Wk_r, Wv_r x one 64-column k-block: a whole stage
+constexpr int HALF_SLICE_BYTES = 2 * 64 * 128;  // two 64 x 64 k-blocks of the CTA's rows of Wo / W1 / W2
 constexpr int ATOM = ROWS * 128;               // 16 KB: 128 rows x 64 bf16, 128-byte swizzle
 constexpr int TMEM_COLS = 512;
 // this CTA's slice of the layer's vectors, 64 floats each
@@ -66,7 +67,7 @@ enum Par : int { PAR_LN1_W = 0, PAR_LN1_B, PAR_BQ, PAR_BK, PAR_BV, PAR_BO, PAR_L
 constexpr int PAR_FLOATS = PAR_COUNT * 64;
 
 constexpr size_t SMEM_BYTES = 4 * ATOM + 3 * ATOM + STAGES * STAGE_BYTES + 8 * ROWS * sizeof(float2) + ROWS * sizeof(float) +
-                              PAR_FLOATS * sizeof(float) + 16 * sizeof(uint64_t) + 1024;
+                              2 * PAR_FLOATS * sizeof(float) + 24 * sizeof(uint64_t) + 1024;
 static_assert(SMEM_BYTES <= 232448, "cluster latent block kernel: more than 227 KB of shared memory");
 
 struct LayerPtrs {
@@ -105,24 +106,17 @@ __device__ __forceinline__ uint32_t mapa(uint32_t local, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(a) : "r"(local), "r"(rank));
     return a;
 }
-__device__ __forceinline__ void st_cluster_f32x2(uint32_t addr, float a, float b) {
-    asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
+// 8 bytes into a peer's shared memory, completing on the peer's mbarrier like a TMA write: the receiver learns of the
+// data through the barrier's transaction count, so neither side needs a fence (a release / acquire at cluster scope
+// compiles to MEMBAR.ALL.GPU / CCTL.IVALL, ~1 K cycles each: the first version spent a third of the layer in them)
+__device__ __forceinline__ void st_async_f32x2(uint32_t addr, float a, float b, uint32_t bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];" ::"r"(addr), "f"(a), "f"(b),
+                 "r"(bar)
+                 : "memory");
 }
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(addr) : "memory");
-}
-__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred P1;\n\t"
-        "WAIT_LOOP_CL:\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%0], %1;\n\t"
-        "@P1 bra DONE_CL;\n\t"
-        "bra WAIT_LOOP_CL;\n\t"
-        "DONE_CL:\n\t"
-        "}" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
+// arrive on a peer's mbarrier; relaxed: it orders no data, only tells the peer that products of this CTA have completed
+__device__ __forceinline__ void mbar_arrive_peer(uint32_t addr) {
+    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(addr) : "memory");
 }
 // 16-byte-granular copy from this CTA's shared memory into a peer's; the bytes complete on the peer's mbarrier
 __device__ __forceinline__ void bulk_copy_to_peer(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t bar_cluster) {
@@ -131,6 +125,26 @@ __device__ __forceinline__ void bulk_copy_to_peer(uint32_t dst_cluster, uint32_t
                  : "memory");
 }
 __device__ __forceinline__ void bar_ew() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+// Phase timeline for tuning (only in builds with -DPIO_LB_TRACE, tools/latent_trace.py --cluster): CTA 0's MMA thread
+// (who 0) and thread 0 of its element-wise warps (who 1) log (tag, clock64) pairs; tag = kind * 1000 + running index.
+#ifdef PIO_LB_TRACE
+__device__ long long gc_trace[2][2][8192];
+__device__ int gc_trace_n[2];
+#define CL_TRACE(who, tag)                                               \
+    do {                                                                 \
+        if (blockIdx.x == 0) {                                           \
+            const int _i = gc_trace_n[who];                              \
+            if (_i < 8192) {                                             \
+                gc_trace[who][0][_i] = (tag);                            \
+                gc_trace[who][1][_i] = clock64();                        \
+                gc_trace_n[who] = _i + 1;                                \
+            }                                                            \
+        }                                                                \
+    } while (0)
+#else
+#define CL_TRACE(who, tag) do { } while (0)
+#endif
 
 __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_block_fwd_cluster_kernel(const __grid_constant__ Params p) {
     extern __shared__ uint8_t smem_raw[];
@@ -141,19 +155,21 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
     uint8_t* sQ = sA + 4 * ATOM;         // Q_r | K_r | V_r tiles; sQ and sK double as staging of the fp32 residual copies,
     uint8_t* sK = sQ + ATOM;             // sV as the tile GELU' leaves from
     uint8_t* sV = sK + ATOM;
-    uint8_t* ring = sV + ATOM;           // [STAGES][32 KB] weight tiles
+    uint8_t* ring = sV + ATOM;           // [STAGES][24 KB] weight tiles
     float2* sStat = (float2*)(ring + STAGES * STAGE_BYTES);  // [8 partials = (CTA, column half)][128 rows] (mean, M2) over 32 columns
     float* sInv = (float*)(sStat + 8 * ROWS);                // 1 / softmax denominator of each row
     float* sPar = sInv + ROWS;
-    uint64_t* bars = (uint64_t*)(sPar + PAR_FLOATS);
+    uint64_t* bars = (uint64_t*)(sPar + 2 * PAR_FLOATS);
     uint64_t* full = bars;               // [STAGES]
     uint64_t* empty = bars + STAGES;     // [STAGES]
     uint64_t* mma_done = bars + 2 * STAGES;
     uint64_t* ew_done = bars + 2 * STAGES + 1;
-    uint64_t* gath_full = bars + 2 * STAGES + 2;
-    uint64_t* gath_free = bars + 2 * STAGES + 3;
-    uint64_t* stat_full = bars + 2 * STAGES + 4;
-    uint32_t* tmem_slot = (uint32_t*)(bars + 2 * STAGES + 5);
+    uint64_t* gath_full = bars + 2 * STAGES + 2;  // [R]: atom j of sA holds CTA j's part of the new operand
+    uint64_t* gath_free = bars + 2 * STAGES + 6;
+    uint64_t* stat_full = bars + 2 * STAGES + 7;
+    uint64_t* sa_free = bars + 2 * STAGES + 8;   // the TMA store out of the CTA's own atom of sA (and of sV) has read it
+    uint64_t* qkv_free = bars + 2 * STAGES + 9;  // the TMA stores out of sQ / sK / sV have read them
+    uint32_t* tmem_slot = (uint32_t*)(bars + 2 * STAGES + 10);
 
     pdl_trigger();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -167,9 +183,11 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
         }
         mbar_init(mma_done, 1);
         mbar_init(ew_done, EW_WARPS);
-        mbar_init(gath_full, 1);
+        for (int j = 0; j < R; ++j) mbar_init(&gath_full[j], j == r ? 4 : 1);
         mbar_init(gath_free, R);
-        mbar_init(stat_full, R * EW_WARPS);
+        mbar_init(stat_full, 1);
+        mbar_init(sa_free, 1);
+        mbar_init(qkv_free, 1);
         fence_barrier_init();
     }
     if (warp == EW_WARPS + 1) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -200,20 +218,23 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 if (l == 0) {
                     prefetch_tmap(mq); prefetch_tmap(&p.maps[l][1]); prefetch_tmap(&p.maps[l][2]); prefetch_tmap(&p.maps[l][3]);
                 }
-                for (int kb = 0; kb < 4; ++kb) {
+                // k-blocks in the order the atoms of the gathered operand arrive: the CTA's own, then r - 1, r - 2, r - 3
+                for (int i = 0; i < 4; ++i) {
+                    const int kb = (r + R - i) % R;
                     uint8_t* dst = acquire(QKV_STAGE_BYTES);
                     uint64_t* bar = &full[prod % STAGES];
 #pragma unroll
                     for (int j = 0; j < 3; ++j) tma_load_2d(dst + j * 8192, mq, kb * 64, j * C + r * DH, bar);
                     ++prod;
                 }
-                for (int w = 1; w < 4; ++w) {  // rows [64 r, 64 r + 64) of Wo, W1, W2: four 64 x 64 k-blocks each
-                    uint8_t* dst = acquire(STAGE_BYTES);
-                    uint64_t* bar = &full[prod % STAGES];
+                for (int w = 1; w < 4; ++w)  // rows [64 r, 64 r + 64) of Wo, W1, W2: four 64 x 64 k-blocks each, two per stage
+                    for (int hf = 0; hf < 2; ++hf) {
+                        uint8_t* dst = acquire(HALF_SLICE_BYTES);
+                        uint64_t* bar = &full[prod % STAGES];
 #pragma unroll
-                    for (int kb = 0; kb < 4; ++kb) tma_load_2d(dst + kb * 8192, &p.maps[l][w], kb * 64, r * DH, bar);
-                    ++prod;
-                }
+                        for (int kb = 0; kb < 2; ++kb) tma_load_2d(dst + kb * 8192, &p.maps[l][w], ((r + R - (hf * 2 + kb)) % R) * 64, r * DH, bar);
+                        ++prod;
+                    }
             }
         }
         __syncwarp();
@@ -229,15 +250,28 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             const int row0 = tile * ROWS;
             int cons = 0;
             uint32_t ew_phase = 0, g_phase = 0;
+            int tr = 0;
             auto wait_ew = [&]() {
+                CL_TRACE(0, 1000 + tr);
                 mbar_wait(ew_done, ew_phase);
                 ew_phase ^= 1u;
                 tc_fence_after();
+                CL_TRACE(0, 2000 + tr);
+                ++tr;
             };
-            auto wait_gather = [&]() {  // all four atoms of sA hold the new operand
-                mbar_wait(gath_full, g_phase);
-                g_phase ^= 1u;
+            // atom (r - j) mod 4 of the gathered operand has arrived (j = 0: the CTA's own, then in the order the peers send)
+            auto wait_atom = [&](int j) -> int {
+                const int a = (r + R - j) % R;
+                if (j == 0) CL_TRACE(0, 1000 + tr);
+                mbar_wait(&gath_full[a], g_phase);
                 tc_fence_after();
+                if (j == 0) CL_TRACE(0, 2000 + tr);
+                if (j == R - 1) {
+                    g_phase ^= 1u;
+                    CL_TRACE(0, 3000 + tr);
+                    ++tr;
+                }
+                return a;
             };
             auto ring_wait = [&]() -> uint32_t {
                 const int s = cons % STAGES;
@@ -249,34 +283,57 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 umma_commit(&empty[cons % STAGES]);
                 ++cons;
             };
-            // D[128 x 64] (+)= sA[128 x 256] W[64 r .. 64 r + 64, :]^T, the weight slice in one ring stage
-            auto slice_product = [&](uint32_t tmem_d, bool accumulate) {
-                const uint32_t b = ring_wait();
-#pragma unroll
-                for (int kb = 0; kb < 4; ++kb)
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        umma_bf16(tmem_d, make_smem_desc(a_addr + kb * ATOM + k * 32, 16, 1024),
-                                  make_smem_desc(b + kb * 8192 + k * 32, 16, 1024), idesc_64, (accumulate || kb > 0 || k > 0) ? 1u : 0u);
-                ring_release();
+            // the saved copy of the operand leaves the CTA's own atom by TMA; the element-wise warps may overwrite the atom
+            // once the store has read it (off the critical path: they first wait for the product just committed)
+            auto release_own_atom = [&]() {
+                lb::tma_store_wait_read();
+                lb::mbar_arrive(sa_free);
             };
             auto store_tile = [&](int which, const uint8_t* tile_ptr, int col0, int l) {  // one 128-row x 64-column bf16 atom
                 lb::tma_store_3d(&p.out[which], tile_ptr, col0, row0, l);
             };
+            // D[128 x 64] (+)= sA[128 x 256] W[64 r .. 64 r + 64, :]^T, k-block by k-block as the atoms of sA arrive (the
+            // producer loads the weight k-blocks in the same order, two per ring stage); `which` = where the CTA's own
+            // atom is saved, stored as soon as it is complete
+            auto slice_product = [&](uint32_t tmem_d, bool accumulate, int which, int l, bool with_h1) {
+                for (int hf = 0; hf < 2; ++hf) {
+                    uint32_t b = 0;
+#pragma unroll
+                    for (int kb = 0; kb < 2; ++kb) {
+                        const int j = hf * 2 + kb;
+                        const int a = wait_atom(j);
+                        if (j == 0) {
+                            store_tile(which, own_atom, r * DH, l);
+                            if (with_h1) store_tile(OM_MLP_H1, sV, r * DH, l);
+                            lb::tma_store_commit();
+                        }
+                        if (kb == 0) b = ring_wait();
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_bf16(tmem_d, make_smem_desc(a_addr + a * ATOM + k * 32, 16, 1024),
+                                      make_smem_desc(b + kb * 8192 + k * 32, 16, 1024), idesc_64, (accumulate || j > 0 || k > 0) ? 1u : 0u);
+                    }
+                    ring_release();
+                }
+                umma_commit(mma_done);
+                release_own_atom();
+            };
             for (int l = 0; l < p.layers; ++l) {
-                wait_gather();  // LayerNorm 1 output
-                store_tile(OM_SA_H0, own_atom, r * DH, l);
-                lb::tma_store_commit();
-                for (int kb = 0; kb < 4; ++kb) {  // [Q_r | K_r | V_r] = LN(x) [Wq_r; Wk_r; Wv_r]^T
+                for (int j = 0; j < R; ++j) {  // [Q_r | K_r | V_r] = LN(x) [Wq_r; Wk_r; Wv_r]^T
+                    const int a = wait_atom(j);
+                    if (j == 0) {
+                        store_tile(OM_SA_H0, own_atom, r * DH, l);
+                        lb::tma_store_commit();
+                    }
                     const uint32_t b = ring_wait();
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma_bf16(T_QKV, make_smem_desc(a_addr + kb * ATOM + k * 32, 16, 1024), make_smem_desc(b + k * 32, 16, 1024),
-                                  idesc_qkv, (kb > 0 || k > 0) ? 1u : 0u);
+                        umma_bf16(T_QKV, make_smem_desc(a_addr + a * ATOM + k * 32, 16, 1024), make_smem_desc(b + k * 32, 16, 1024),
+                                  idesc_qkv, (j > 0 || k > 0) ? 1u : 0u);
                     ring_release();
                 }
-                lb::tma_store_wait_read();  // the copy of the own atom has left it: once the products are done it may be overwritten
                 umma_commit(mma_done);
+                release_own_atom();
                 wait_ew();  // Q_r, K_r, V_r as bf16 in shared memory
                 store_tile(OM_QKV, sQ, r * DH, l);
                 store_tile(OM_QKV, sK, C + r * DH, l);
@@ -291,30 +348,13 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
 #pragma unroll
                 for (int t = 0; t < 8; ++t)  // O_r = P V_r
                     umma_bf16_ts(T_O, T_P + (uint32_t)t * 8, make_smem_desc(v_addr + t * 2048, ROWS * 128, 1024), idesc_pv, t > 0 ? 1u : 0u);
+                umma_commit(mma_done);
                 lb::tma_store_wait_read();  // Q, K, V have left their tiles (staging / GELU' use them next)
-                umma_commit(mma_done);
+                lb::mbar_arrive(qkv_free);
 
-                wait_gather();  // attention output of all four heads
-                store_tile(OM_O16, own_atom, r * DH, l);
-                lb::tma_store_commit();
-                slice_product(T_RES, true);  // x[:, slice] += O Wo[slice, :]^T
-                lb::tma_store_wait_read();
-                umma_commit(mma_done);
-
-                wait_gather();  // LayerNorm 2 output
-                store_tile(OM_MLP_H0, own_atom, r * DH, l);
-                lb::tma_store_commit();
-                slice_product(T_QKV, false);  // hidden[:, slice]
-                lb::tma_store_wait_read();
-                umma_commit(mma_done);
-
-                wait_gather();  // GELU output (and GELU' in sV)
-                store_tile(OM_MLP_G, own_atom, r * DH, l);
-                store_tile(OM_MLP_H1, sV, r * DH, l);
-                lb::tma_store_commit();
-                slice_product(T_RES, true);  // x[:, slice] += G W2[slice, :]^T
-                lb::tma_store_wait_read();
-                umma_commit(mma_done);
+                slice_product(T_RES, true, OM_O16, l, false);     // x[:, slice] += O Wo[slice, :]^T
+                slice_product(T_QKV, false, OM_MLP_H0, l, false);  // hidden[:, slice] = LN2(x) W1[slice, :]^T
+                slice_product(T_RES, true, OM_MLP_G, l, true);     // x[:, slice] += G W2[slice, :]^T
             }
             lb::tma_store_wait_all();
         }
@@ -335,20 +375,31 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
         uint8_t* own_atom = sA + r * ATOM;
         uint8_t* slice = sQ + warp * 4096;  // 32 rows x 128 bytes of fp32 staging, private to the warp
         const int slice_row0 = tile * ROWS + q * 32;
-        uint32_t mma_phase = 0, stat_phase = 0, free_phase = 0;
+        uint32_t mma_phase = 0, stat_phase = 0, free_phase = 0, sa_phase = 0, qkv_phase = 0;
         bool first_gather = true;
+        uint32_t peer_atom[R - 1], peer_bar[R - 1];  // the CTA's atom and its gath_full barrier in the three peers
+#pragma unroll
+        for (int d = 1; d < R; ++d) {
+            const uint32_t peer = (uint32_t)((r + d) % R);
+            peer_atom[d - 1] = mapa(smem_u32(own_atom), peer);
+            peer_bar[d - 1] = mapa(smem_u32(&gath_full[r]), peer);  // (a peer counts this CTA's bytes on its barrier number r)
+        }
 
+        int tr = 0;
         auto wait_mma = [&]() {
+            if (threadIdx.x == 0) CL_TRACE(1, 1000 + tr);
             mbar_wait(mma_done, mma_phase);
             mma_phase ^= 1u;
             tc_fence_after();
+            if (threadIdx.x == 0) CL_TRACE(1, 2000 + tr);
+            ++tr;
         };
         // this CTA has seen the products that read the current gather complete: tell every CTA of the cluster
         auto free_arrive = [&]() {
             if (threadIdx.x == 0) {
                 const uint32_t a = smem_u32(gath_free);
 #pragma unroll
-                for (int d = 0; d < R; ++d) mbar_arrive_cluster(mapa(a, (uint32_t)d));
+                for (int d = 0; d < R; ++d) mbar_arrive_peer(mapa(a, (uint32_t)d));
             }
         };
         auto signal = [&]() {  // everything this warp wrote (shared memory, tensor memory) is visible to the MMA thread
@@ -357,25 +408,36 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             __syncwarp();
             if (lane == 0) lb::mbar_arrive(ew_done);
         };
-        // the CTA's atom of the next A operand is complete in its own shared memory: copy it to the three peers
-        auto publish = [&]() {
+        // 32 values of this thread's row -> bf16 -> the CTA's atom of the next A operand in its own shared memory; the two
+        // warps of a TMEM lane quadrant then hold 32 complete rows (4 KB), which one of their threads copies into the
+        // three peers (cp.async.bulk shared::cta -> shared::cluster; the peers count the bytes on their gath_full[r]) before
+        // it arrives on the local gath_full[r].  (Sending every thread's 64 bytes with st.async as they are produced was
+        // slower: 25.0 instead of 18.7 us per layer.  Either way the 48 KB a CTA sends per gather leave at the ~20 bytes
+        // per clock of the SM-to-SM network, which is the floor of this design: four gathers = ~9 K cycles per layer.)
+        auto send_operand = [&](const float (&v)[32]) {
+            if (!first_gather) {
+                mbar_wait(sa_free, sa_phase);  // the saved copy of the previous operand has left the CTA's atom
+                sa_phase ^= 1u;
+                mbar_wait(gath_free, free_phase);  // every CTA of the cluster is done reading the previous operand
+                free_phase ^= 1u;
+            }
+            if (threadIdx.x == 0) {
+                CL_TRACE(1, 5000);
+#pragma unroll
+                for (int d = 1; d < R; ++d) mbar_expect_tx(&gath_full[(r + d) % R], ATOM);  // arrive + the 16 KB that peer sends
+            }
+            lb::store_half_row_smem(own_atom, row, cg, v);
             if (lane == 0) lb::tma_store_wait_read();  // (fp32 copies staged by this warp have left shared memory)
             tc_fence_before();
             fence_proxy_async();
-            bar_ew();
-            if (threadIdx.x == 0) {
-                if (!first_gather) {  // every CTA is done reading the previous operand
-                    mbar_wait_cluster(gath_free, free_phase);
-                    free_phase ^= 1u;
-                }
-                const uint32_t src = smem_u32(own_atom), bar = smem_u32(gath_full);
+            asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");  // the quadrant's two warps
+            if (cg == 0 && lane == 0) {
+                const uint32_t src = smem_u32(own_atom) + (uint32_t)q * 4096u;
 #pragma unroll
-                for (int d = 1; d < R; ++d) {
-                    const uint32_t peer = (uint32_t)((r + d) % R);
-                    bulk_copy_to_peer(mapa(src, peer), src, ATOM, mapa(bar, peer));
-                }
-                mbar_expect_tx(gath_full, (R - 1) * ATOM);  // arrive + the 48 KB the peers send
+                for (int d = 0; d < R - 1; ++d) bulk_copy_to_peer(peer_atom[d] + (uint32_t)q * 4096u, src, 4096u, peer_bar[d]);
+                lb::mbar_arrive(&gath_full[r]);
             }
+            if (threadIdx.x == 0) CL_TRACE(1, 5001);
             first_gather = false;
         };
         // 32 fp32 per row -> the warp's slice -> TMA store; an earlier store out of the slice must have read it
@@ -393,20 +455,19 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 lb::tma_store_commit();
             }
         };
-        // v = this thread's 32 channels of its row, st their statistics: exchange the partial statistics with the whole
-        // cluster, normalise in registers, write the bf16 row into the CTA's atom of sA and start the gather
-        auto ln_phase = [&](float (&v)[32], const Stat& st, const float* gamma, const float* beta, float* stats_out) {
-            const uint32_t mine = smem_u32(&sStat[(r * 2 + cg) * ROWS + row]);
+        // LayerNorm over the cluster: every thread sends the (mean, M2) of its 32 columns to all four CTAs ...
+        auto send_stats = [&](const Stat& st) {
+            const uint32_t mine = smem_u32(&sStat[(r * 2 + cg) * ROWS + row]), sbar = smem_u32(stat_full);
+            if (threadIdx.x == 0) mbar_expect_tx(stat_full, R * EW_THREADS * 8);  // 8 bytes from every element-wise thread of the cluster
 #pragma unroll
-            for (int d = 0; d < R; ++d) st_cluster_f32x2(mapa(mine, (uint32_t)d), st.mean, st.m2);
-            __syncwarp();
-            if (lane == 0) {
-                const uint32_t a = smem_u32(stat_full);
-#pragma unroll
-                for (int d = 0; d < R; ++d) mbar_arrive_cluster(mapa(a, (uint32_t)d));
-            }
-            mbar_wait_cluster(stat_full, stat_phase);
+            for (int d = 0; d < R; ++d) st_async_f32x2(mapa(mine, (uint32_t)d), st.mean, st.m2, mapa(sbar, (uint32_t)d));
+        };
+        // ... and, once all eight partials of its row are there, normalises its 32 values and sends them on as bf16
+        auto ln_finish = [&](float (&v)[32], const float* gamma, const float* beta, float* stats_out) {
+            if (threadIdx.x == 0) CL_TRACE(1, 4000);
+            mbar_wait(stat_full, stat_phase);
             stat_phase ^= 1u;
+            if (threadIdx.x == 0) CL_TRACE(1, 4001);
             Stat t{0.f, 0.f, 0.f};
 #pragma unroll
             for (int g = 0; g < 2 * R; ++g) {  // same order in every thread of every CTA: all agree bit for bit
@@ -429,11 +490,12 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 v[d + 2] = fmaf((v[d + 2] - mean) * rstd, g.z, b.z);
                 v[d + 3] = fmaf((v[d + 3] - mean) * rstd, g.w, b.w);
             }
-            lb::store_half_row_smem(own_atom, row, cg, v);
-            publish();
+            send_operand(v);
         };
 
-        // this CTA's 64-float slices of the layer's ten vectors: prefetched into registers, later into sPar
+        // this CTA's 64-float slices of the layer's ten vectors, double-buffered in shared memory: layer l + 1's are
+        // loaded into registers at the start of layer l and written to the other buffer in its Q/K/V phase (every
+        // thread has left layer l - 1 by then: the gather it waited for needed all of them)
         float pre[3];
         auto prefetch_params = [&](int l) {
             const LayerPtrs& Lp = p.layer[l];
@@ -443,11 +505,12 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 if (e < PAR_FLOATS) pre[k] = __ldg(Lp.par[e >> 6] + r * DH + (e & 63));
             }
         };
-        auto commit_params = [&]() {
+        auto commit_params = [&](int l) {
+            float* dst = sPar + (l & 1) * PAR_FLOATS;
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
                 const int e = k * EW_THREADS + (int)threadIdx.x;
-                if (e < PAR_FLOATS) sPar[e] = pre[k];
+                if (e < PAR_FLOATS) dst[e] = pre[k];
             }
         };
         prefetch_params(0);
@@ -466,25 +529,30 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] = 0.f;
         }
-        lb::st_chunk(T_RES + lane_off + (uint32_t)lcol, v);
         lb::stat_chunk(st, v);
+        send_stats(st);
+        lb::st_chunk(T_RES + lane_off + (uint32_t)lcol, v);
         tmem_st_wait();
-        commit_params();
+        commit_params(0);
         bar_ew();  // the parameters are in shared memory before anyone reads them
 
         for (int l = 0; l < p.layers; ++l) {
             const LayerPtrs& L = p.layer[l];
-            ln_phase(v, st, sPar + PAR_LN1_W * 64, sPar + PAR_LN1_B * 64, L.sa_stats);
+            const float* par = sPar + (l & 1) * PAR_FLOATS;
+            const bool last = (l + 1 == p.layers);
+            if (!last) prefetch_params(l + 1);
+            ln_finish(v, par + PAR_LN1_W * 64, par + PAR_LN1_B * 64, L.sa_stats);
 
             // ---- [Q_r | K_r | V_r] + bias -> bf16 operand tiles: six 32-column chunks, three per column half
             wait_mma();
             free_arrive();
+            if (!last) commit_params(l + 1);
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
                 const int chunk = cg * 3 + j;
                 float t[32];
                 lb::ld_chunk(T_QKV + lane_off + (uint32_t)(chunk * 32), t);
-                lb::add_vec32(t, sPar + PAR_BQ * 64 + chunk * 32);
+                lb::add_vec32(t, par + PAR_BQ * 64 + chunk * 32);
                 lb::store_half_row_smem(sQ + (chunk >> 1) * ATOM, row, chunk & 1, t);
             }
             signal();
@@ -541,21 +609,23 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 lb::ld_chunk(T_O + lane_off + (uint32_t)lcol, t);
 #pragma unroll
                 for (int i = 0; i < 32; ++i) t[i] *= inv_l;
-                lb::store_half_row_smem(own_atom, row, cg, t);
+                send_operand(t);
             }
-            publish();
 
             // ---- x_mid = x + attention + bo (back into the residual columns, fp32 copy out), LayerNorm 2
             wait_mma();
             free_arrive();
             st = Stat{0.f, 0.f, 0.f};
             lb::ld_chunk(T_RES + lane_off + (uint32_t)lcol, v);
-            lb::add_vec32(v, sPar + PAR_BO * 64 + lcol);
-            lb::st_chunk(T_RES + lane_off + (uint32_t)lcol, v);
-            stage_store_f32(OM_XMID, gcol, l, v);
+            lb::add_vec32(v, par + PAR_BO * 64 + lcol);
             lb::stat_chunk(st, v);
+            send_stats(st);  // first: the peers wait for these
+            lb::st_chunk(T_RES + lane_off + (uint32_t)lcol, v);
+            mbar_wait(qkv_free, qkv_phase);  // Q, K, V have left their tiles: sQ / sK are staging space, sV takes GELU'
+            qkv_phase ^= 1u;
+            stage_store_f32(OM_XMID, gcol, l, v);
             tmem_st_wait();
-            ln_phase(v, st, sPar + PAR_LN2_W * 64, sPar + PAR_LN2_B * 64, L.mlp_stats);
+            ln_finish(v, par + PAR_LN2_W * 64, par + PAR_LN2_B * 64, L.mlp_stats);
 
             // ---- GELU(hidden + b1) -> the CTA's atom of sA, GELU' -> sV; both leave by TMA
             wait_mma();
@@ -563,33 +633,26 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             {
                 float t[32], dg[32];
                 lb::ld_chunk(T_QKV + lane_off + (uint32_t)lcol, t);
-                lb::add_vec32(t, sPar + PAR_B1 * 64 + lcol);
+                lb::add_vec32(t, par + PAR_B1 * 64 + lcol);
 #pragma unroll
                 for (int i = 0; i < 32; ++i) gelu_erf_both(t[i], t[i], dg[i]);
-                lb::store_half_row_smem(own_atom, row, cg, t);
                 lb::store_half_row_smem(sV, row, cg, dg);
+                send_operand(t);
             }
-            publish();
 
             // ---- x_next = x_mid + mlp + b2: fp32 copy out; stays in the residual columns (and registers) for the next layer
             wait_mma();
             free_arrive();
-            const bool last = (l + 1 == p.layers);
-            if (!last) prefetch_params(l + 1);
             st = Stat{0.f, 0.f, 0.f};
             lb::ld_chunk(T_RES + lane_off + (uint32_t)lcol, v);
-            lb::add_vec32(v, sPar + PAR_B2 * 64 + lcol);
+            lb::add_vec32(v, par + PAR_B2 * 64 + lcol);
             if (!last) {
-                lb::st_chunk(T_RES + lane_off + (uint32_t)lcol, v);
                 lb::stat_chunk(st, v);
+                send_stats(st);
+                lb::st_chunk(T_RES + lane_off + (uint32_t)lcol, v);
             }
             stage_store_f32(last ? OM_Y : OM_XNEXT, gcol, last ? 0 : l, v);
-            if (!last) {
-                tmem_st_wait();
-                bar_ew();  // every warp is done with this layer's parameters
-                commit_params();
-                bar_ew();
-            }
+            if (!last) tmem_st_wait();
         }
         if (lane == 0) lb::tma_store_wait_all();
         __syncwarp();
@@ -604,6 +667,23 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
 }
 
 }  // namespace lbc
+
+#ifdef PIO_LB_TRACE
+extern "C" int pio_debug_lbc_trace(long long* out, int max_pairs, int who, int reset) {
+    int n = 0;
+    cudaMemcpyFromSymbol(&n, lbc::gc_trace_n, sizeof(int), who * sizeof(int));
+    n = std::min(n, max_pairs);
+    if (out && n > 0) {
+        cudaMemcpyFromSymbol(out, lbc::gc_trace, (size_t)n * 8, (size_t)(who * 2 + 0) * 8192 * 8);
+        cudaMemcpyFromSymbol(out + max_pairs, lbc::gc_trace, (size_t)n * 8, (size_t)(who * 2 + 1) * 8192 * 8);
+    }
+    if (reset) {
+        int z[2] = {0, 0};
+        cudaMemcpyToSymbol(lbc::gc_trace_n, z, sizeof(z));
+    }
+    return n;
+}
+#endif
 
 // Which fused kernel runs a block of `rows` latent rows.  The cluster kernel spends four SMs per 128-row tile and
 // takes about the same time per layer for any number of tiles up to one wave (the GPU places 33 clusters of four:
