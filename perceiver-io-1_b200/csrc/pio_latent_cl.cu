@@ -90,40 +90,8 @@ struct Params {
     float scale_log2e;
 };
 
-// ------------------------------------------------------------------ cluster PTX
-__device__ __forceinline__ uint32_t cluster_rank() {
-    uint32_t r;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-    return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-// the shared::cluster address of `local` (a shared::cta address of this CTA) in CTA `rank` of the cluster
-__device__ __forceinline__ uint32_t mapa(uint32_t local, uint32_t rank) {
-    uint32_t a;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(a) : "r"(local), "r"(rank));
-    return a;
-}
-// 8 bytes into a peer's shared memory, completing on the peer's mbarrier like a TMA write: the receiver learns of the
-// data through the barrier's transaction count, so neither side needs a fence (a release / acquire at cluster scope
-// compiles to MEMBAR.ALL.GPU / CCTL.IVALL, ~1 K cycles each: the first version spent a third of the layer in them)
-__device__ __forceinline__ void st_async_f32x2(uint32_t addr, float a, float b, uint32_t bar) {
-    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];" ::"r"(addr), "f"(a), "f"(b),
-                 "r"(bar)
-                 : "memory");
-}
-// arrive on a peer's mbarrier; relaxed: it orders no data, only tells the peer that products of this CTA have completed
-__device__ __forceinline__ void mbar_arrive_peer(uint32_t addr) {
-    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(addr) : "memory");
-}
-// 16-byte-granular copy from this CTA's shared memory into a peer's; the bytes complete on the peer's mbarrier
-__device__ __forceinline__ void bulk_copy_to_peer(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t bar_cluster) {
-    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_cluster),
-                 "r"(src_cta), "r"(bytes), "r"(bar_cluster)
-                 : "memory");
-}
+using namespace lb::cl;
+
 __device__ __forceinline__ void bar_ew() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 // Phase timeline for tuning (only in builds with -DPIO_LB_TRACE, tools/latent_trace.py --cluster): CTA 0's MMA thread

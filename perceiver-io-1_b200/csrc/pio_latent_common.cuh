@@ -121,6 +121,70 @@ __device__ __forceinline__ void stat_chunk(Stat& a, const float (&v)[32]) {
     }
 }
 
+// 32 bf16 of row `row`, 64-byte half `hh` of a 128-row x 128-byte swizzled atom -> fp32
+__device__ __forceinline__ void load_half_row_smem(const uint8_t* atom, int row, int hh, float (&v)[32]) {
+    const uint8_t* prow = atom + row * 128;
+#pragma unroll
+    for (int piece = 0; piece < 4; ++piece) {
+        const int ci = hh * 4 + piece;
+        const uint4 w = *reinterpret_cast<const uint4*>(prow + ((ci ^ (row & 7)) << 4));
+        const uint32_t u[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int e2 = 0; e2 < 4; ++e2) {
+            const __nv_bfloat162 h2 = *reinterpret_cast<const __nv_bfloat162*>(&u[e2]);
+            const float2 f = __bfloat1622float2(h2);
+            v[piece * 8 + 2 * e2] = f.x;
+            v[piece * 8 + 2 * e2 + 1] = f.y;
+        }
+    }
+}
+// 32 fp32 of row `row` of a 128-row x 128-byte swizzled box (TMA box of 32 fp32 columns)
+__device__ __forceinline__ void load_row_f32_smem(const uint8_t* box, int row, float (&v)[32]) {
+    const uint8_t* prow = box + row * 128;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const float4 t = *reinterpret_cast<const float4*>(prow + ((j ^ (row & 7)) << 4));
+        v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+    }
+}
+
+namespace cl {
+// ------------------------------------------------------------------ thread-block cluster PTX
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// the shared::cluster address of `local` (a shared::cta address of this CTA) in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa(uint32_t local, uint32_t rank) {
+    uint32_t a;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(a) : "r"(local), "r"(rank));
+    return a;
+}
+// 8 bytes into a peer's shared memory, completing on the peer's mbarrier like a TMA write: the receiver learns of the
+// data through the barrier's transaction count, so neither side needs a fence (a release / acquire at cluster scope
+// compiles to MEMBAR.ALL.GPU / CCTL.IVALL, ~1 K cycles each: the first version spent a third of the layer in them)
+__device__ __forceinline__ void st_async_f32x2(uint32_t addr, float a, float b, uint32_t bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];" ::"r"(addr), "f"(a), "f"(b),
+                 "r"(bar)
+                 : "memory");
+}
+// arrive on a peer's mbarrier; relaxed: it orders no data, only tells the peer that products of this CTA have completed
+__device__ __forceinline__ void mbar_arrive_peer(uint32_t addr) {
+    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(addr) : "memory");
+}
+// 16-byte-granular copy from this CTA's shared memory into a peer's; the bytes complete on the peer's mbarrier
+__device__ __forceinline__ void bulk_copy_to_peer(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t bar_cluster) {
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_cluster),
+                 "r"(src_cta), "r"(bytes), "r"(bar_cluster)
+                 : "memory");
+}
+}  // namespace cl
+
 }  // namespace lb
 
 // (cols, rows, layers) tensor map with byte strides (pitch, layer_stride); box = box_cols x box_rows x 1, 128-byte swizzle

@@ -546,7 +546,7 @@ size_t pio_latent_block_saved_bytes(int layers, int batch, int n, int c, int hea
 }
 size_t pio_latent_block_ws_bytes(int layers, int batch, int n, int c, int heads, int mode) {
     (void)layers;
-    if (mode == PIO_MODE_BF16) return bf::block_ws_bytes(batch, n, c, heads);
+    if (mode == PIO_MODE_BF16) return bf::block_ws_bytes(layers, batch, n, c, heads);
     const size_t r = (size_t)batch * n;
     return 2 * align_up(r * c * 4, 256) + std::max(self_attn_bwd_ws(batch, n, c, heads), mlp_bwd_ws(r, c)) + 1024;
 }

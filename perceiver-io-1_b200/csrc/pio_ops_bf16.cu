@@ -8,6 +8,7 @@
 #include <map>
 #include <mutex>
 #include <utility>
+#include <vector>
 
 #include "pio_ops_common.cuh"
 
@@ -543,10 +544,13 @@ struct BlockLayout {
 size_t block_saved_bytes(int layers, int batch, int n, int ch, int heads) {
     return (size_t)layers * BlockLayout(batch, n, ch, heads).per_layer + 256;
 }
-size_t block_ws_bytes(int batch, int n, int ch, int heads) {
+// bf16 gradient tensors the fused backward chain leaves per layer for the parameter-gradient kernels
+// (g, dH, g_mid, [dQ | dK | dV], dN2, dN1: eight [rows][C] tensors)
+static size_t block_bwd_layer_bytes(size_t r, int ch) { return 8 * align_up(r * ch * 2, 256); }
+size_t block_ws_bytes(int layers, int batch, int n, int ch, int heads) {
     const size_t r = (size_t)batch * n;
     return 2 * align_up(r * ch * 4, 256) + 2 * align_up(r * ch * 2, 256) + std::max(sa_ws_bytes(batch, n, ch, heads), mlp_ws_bytes(r, ch)) +
-           1024;
+           (size_t)layers * block_bwd_layer_bytes(r, ch) + 1024;
 }
 
 int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,
@@ -597,11 +601,82 @@ int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* a
     return PIO_OK;
 }
 
+// Backward of a block through the fused input-gradient chain (pio_latent_bwd_cl.cu: one launch per up to 8 layers),
+// followed by the parameter gradients of every layer on the side streams: four split-K weight-gradient GEMMs, four
+// bias column sums and the two LayerNorm parameter-gradient kernels per layer, all reading the bf16 tensors the chain
+// kernel left in the workspace.
+static int latent_block_bwd_fused(Ctx& c, Side& side, const float* dy, const float* x, float* dx, const pio_attn_weights* attn,
+                                  const pio_mlp_weights* mlp, const void* saved, const pio_attn_grads* attn_g,
+                                  const pio_mlp_grads* mlp_g, int layers, int batch, int n, int ch, int heads) {
+    BlockLayout L(batch, n, ch, heads);
+    const int64_t rows = (int64_t)batch * n;
+    const size_t mark = c.W.off;
+    const size_t one = align_up((size_t)rows * ch * 2, 256);
+    PIO_TAKE_BYTES(char, gbuf, c, (size_t)layers * block_bwd_layer_bytes(rows, ch), "pio_latent_block_bwd");
+    PIO_TAKE_BYTES(float, dcur, c, (size_t)rows * ch * 4, "pio_latent_block_bwd");
+    PIO_TAKE_BYTES(float, dcur2, c, (size_t)rows * ch * 4, "pio_latent_block_bwd");
+    std::vector<LatentBwdLayer> bl((size_t)layers);
+    for (int s = 0; s < layers; ++s) {
+        const char* slab = (const char*)saved + (size_t)s * L.per_layer;
+        SaSaved sa((void*)(slab + L.sa), batch, n, ch, heads);
+        MlpSaved ms((void*)(slab + L.mlp), rows, ch);
+        char* g = gbuf + (size_t)s * block_bwd_layer_bytes(rows, ch);
+        LatentBwdLayer& b = bl[(size_t)s];
+        b.w2 = mlp[s].w2; b.w1 = mlp[s].w1; b.wo = attn[s].wo; b.wqkv = attn[s].wq;
+        b.ln2_w = mlp[s].ln_w; b.ln1_w = attn[s].ln_w;
+        b.mlp_stats = ms.stats; b.sa_stats = sa.stats; b.lse = sa.lse;
+        b.mlp_h1 = ms.h1; b.xmid = (const float*)(slab + L.xmid); b.xnext = (const float*)(slab + L.xnext); b.qkv = sa.qkv;
+        b.gy16 = g; b.gh16 = g + one; b.gmid16 = g + 2 * one; b.gqkv16 = g + 3 * one; b.gn2 = g + 6 * one; b.gn1 = g + 7 * one;
+    }
+    // the chain, from the last layers to the first, up to 8 layers per launch
+    const float* grad = dy;
+    float* bufs[2] = {dcur, dcur2};
+    int flip = 0;
+    for (int hi = layers; hi > 0;) {
+        const int lo = std::max(0, hi - PIO_LATENT_FUSED_MAX_LAYERS);
+        const float* x_lo = (lo == 0) ? x : bl[(size_t)lo - 1].xnext;
+        float* out = (lo == 0) ? dx : bufs[flip];
+        PIO_TRY(latent_block_bwd_cluster(grad, x_lo, out, &bl[(size_t)lo], hi - lo, batch, n, c.st));
+        grad = out;
+        flip ^= 1;
+        hi = lo;
+    }
+    // parameter gradients
+    PIO_TRY(side.fork());
+    for (int s = layers - 1; s >= 0; --s) {
+        const char* slab = (const char*)saved + (size_t)s * L.per_layer;
+        SaSaved sa((void*)(slab + L.sa), batch, n, ch, heads);
+        MlpSaved ms((void*)(slab + L.mlp), rows, ch);
+        const LatentBwdLayer& b = bl[(size_t)s];
+        const float* x_in = (s == 0) ? x : bl[(size_t)s - 1].xnext;
+        const bf16 *gy = (const bf16*)b.gy16, *gh = (const bf16*)b.gh16, *gm = (const bf16*)b.gmid16, *gq = (const bf16*)b.gqkv16;
+        PIO_TRY(tc_dW(c, gy, ch, ms.g, ch, mlp_g[s].w2, rows, ch, ch, 2, side.stream()));
+        PIO_TRY(tc_dW(c, gh, ch, ms.h0, ch, mlp_g[s].w1, rows, ch, ch, 2, side.stream()));
+        PIO_TRY(tc_dW(c, gm, ch, sa.o16, ch, attn_g[s].wo, rows, ch, ch, 2, side.stream()));
+        PIO_TRY(tc_dW(c, gq, 3 * ch, sa.h0, ch, attn_g[s].wq, rows, 3 * ch, ch, 2, side.stream()));
+        PIO_TRY(side_colsum(c, side, gy, ch, mlp_g[s].b2, 2, rows, ch));
+        PIO_TRY(side_colsum(c, side, gh, ch, mlp_g[s].b1, 2, rows, ch));
+        PIO_TRY(side_colsum(c, side, gm, ch, attn_g[s].bo, 2, rows, ch));
+        PIO_TRY(side_colsum(c, side, gq, 3 * ch, attn_g[s].bq, 2, rows, 3 * ch));
+        PIO_TRY(ln_param_grads(b.gn2, b.xmid, b.mlp_stats, mlp_g[s].ln_w, mlp_g[s].ln_b, rows, ch, side.stream2()));
+        PIO_TRY(ln_param_grads(b.gn1, x_in, b.sa_stats, attn_g[s].ln_w, attn_g[s].ln_b, rows, ch, side.stream2()));
+    }
+    PIO_TRY(side.join());
+    c.W.off = mark;
+    return PIO_OK;
+}
+
 int latent_block_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_attn_weights* attn, const pio_mlp_weights* mlp,
                      const void* saved, const pio_attn_grads* attn_g, const pio_mlp_grads* mlp_g, int acc, int layers,
                      int batch, int n, int ch, int heads) {
     BlockLayout L(batch, n, ch, heads);
     const int64_t rows = (int64_t)batch * n;
+    if (acc == 2 && latent_bwd_cluster_supported(rows, n, ch, heads, c.drop_p)) {
+        bool packed = true;
+        for (int s = 0; s < layers; ++s) packed = packed && check_packed_self(&attn[s], ch, "pio_latent_block_bwd") == PIO_OK;
+        Side side(c, acc);
+        if (packed && side.active()) return latent_block_bwd_fused(c, side, dy, x, dx, attn, mlp, saved, attn_g, mlp_g, layers, batch, n, ch, heads);
+    }
     PIO_TAKE_BYTES(float, dmid, c, (size_t)rows * ch * 4, "pio_latent_block_bwd");
     PIO_TAKE_BYTES(float, dcur, c, (size_t)rows * ch * 4, "pio_latent_block_bwd");
     // each operator's LayerNorm backward also writes its dx as bf16, which the next operator takes as its dY operand

@@ -102,6 +102,23 @@ struct LatentFusedLayer {
     float* mlp_stats; void* mlp_h0; void* mlp_h1; void* mlp_g;
     float* xout;
 };
+// one layer of the fused backward input-gradient chain (pio_latent_bwd_cl.cu): weights (bf16 shadows), saved forward
+// state, and the bf16 gradient tensors the kernel leaves for the parameter-gradient kernels (all [rows][C] except
+// gqkv16 [rows][3C]; equally spaced over the layers, like the saved slabs)
+struct LatentBwdLayer {
+    const void *w2, *w1, *wo, *wqkv;
+    const float *ln2_w, *ln1_w;
+    const float *mlp_stats, *sa_stats, *lse;
+    const void* mlp_h1;
+    const float* xmid;
+    const float* xnext;  // the layer's output (the LayerNorm-1 input of the NEXT layer)
+    const void* qkv;
+    void *gy16, *gh16, *gmid16, *gqkv16, *gn2, *gn1;
+};
+bool latent_bwd_cluster_supported(int64_t rows, int n, int ch, int heads, float drop_p);
+int latent_block_bwd_cluster(const float* dy, const float* x, float* dx, const LatentBwdLayer* layers, int nlayers, int batch, int n,
+                             cudaStream_t st);
+int ln_param_grads(const void* dn16, const float* x, const float* stats, float* dgamma, float* dbeta, int64_t rows, int c, cudaStream_t st);
 bool latent_fused_supported(int64_t rows, int n, int ch, int heads, float drop_p);
 int latent_block_fwd_fused(const float* x, const LatentFusedLayer* layers, int nlayers, int batch, int n, cudaStream_t st);
 
@@ -135,7 +152,7 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
                   const pio_attn_grads* g, int acc, int batch, int n, int ch, int heads, int residual,
                   const __nv_bfloat16* dy16_in = nullptr, __nv_bfloat16* dx16_out = nullptr);
 size_t block_saved_bytes(int layers, int batch, int n, int ch, int heads);
-size_t block_ws_bytes(int batch, int n, int ch, int heads);
+size_t block_ws_bytes(int layers, int batch, int n, int ch, int heads);
 int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,
                      int layers, int batch, int n, int ch, int heads);
 int latent_block_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_attn_weights* attn, const pio_mlp_weights* mlp,
