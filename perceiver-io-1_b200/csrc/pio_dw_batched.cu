@@ -1,0 +1,213 @@
+// Batched weight-gradient products: dW_i[m_i x 256] += dY_i^T X_i (+ db_i[m_i] += column sums of dY_i) for a table of
+// problems that all contract over the same `rows`, in ONE launch.
+//
+// Reference: the weight / bias gradients of the Linear layers inside self_attention_layer (perceiver/model.py:20-26,
+// :102-116), which the reference leaves to autograd.  The fused backward chain of a latent block
+// (pio_latent_bwd_cl.cu) leaves dY and X of 4 products per layer in memory; launched one by one those 24 products of
+// a 6-layer block took 24 x ~11 us on a side stream (each is 0.5-1.6 GFLOP: set-up, a 64-block K loop on few CTAs
+// and an atomic epilogue), 2.5 x the chain kernel itself.  Here every (problem, 128-row tile of dW, K split) is one
+// CTA of one grid sized to a single wave:
+//   * both operands are read in place, MN-major (dY[rows][m] and X[rows][256] are row-major with the contraction
+//     index outermost), by TMA into a 4-stage ring of 16 KB + 32 KB;
+//   * tcgen05.mma M = 128, N = 256, fp32 accumulator in 256 TMEM columns; a second, N = 16 product of the same A tile
+//     with a tile of ones accumulates the tile's bias gradient (column sums of dY) in 16 more columns for free;
+//   * epilogue: accumulator rows staged through the idle ring so that a warp adds 512 contiguous bytes per
+//     instruction (red.global.add.v4.f32) into the gradient, which the caller has zero-filled or is accumulating into.
+#include <cuda.h>
+
+#include <atomic>
+
+#include "pio_ops_common.cuh"
+#include "pio_tc_common.cuh"
+
+namespace pio {
+
+int make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows);
+
+namespace dwb {
+
+constexpr int BM = 128, BN = 256, BK = 64;
+constexpr int STAGES = 4;
+constexpr int A_STAGE = BM * BK * 2;  // 16 KB: two boxes of 64 k-rows x 64 m
+constexpr int B_STAGE = BN * BK * 2;  // 32 KB: four boxes of 64 k-rows x 64 n
+constexpr int ONES_BYTES = 8192;
+constexpr int THREADS = 320;  // warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 2..9 epilogue
+constexpr int MAX_PROB = 32, MAX_TILES = 160;
+constexpr int PITCH = 128 + 4;  // floats per staged row (a warp finishes 128 columns)
+constexpr size_t SMEM_BYTES = STAGES * (A_STAGE + B_STAGE) + ONES_BYTES + 16 * sizeof(uint64_t) + 1024;
+static_assert(8 * 32 * PITCH * sizeof(float) <= STAGES * (A_STAGE + B_STAGE), "epilogue staging must fit in the ring");
+
+struct Problem {
+    CUtensorMap tmA, tmB;
+    float* dw;
+    float* db;
+    int m;
+    int pad;
+};
+struct Batch {
+    Problem prob[MAX_PROB];
+    unsigned char tile_prob[MAX_TILES];
+    unsigned char tile_m[MAX_TILES];
+    int num_kb, kb_per_split;
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+__global__ void __launch_bounds__(THREADS, 1) dw_batched_kernel(const __grid_constant__ Batch g) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + STAGES * A_STAGE;
+    uint8_t* sOnes = sB + STAGES * B_STAGE;
+    uint64_t* full_bar = (uint64_t*)(sOnes + ONES_BYTES);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full = empty_bar + STAGES;
+    uint32_t* tmem_slot = (uint32_t*)(tmem_full + 1);
+
+    pdl_trigger();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const Problem& P = g.prob[g.tile_prob[blockIdx.x]];
+    const int m0 = (int)g.tile_m[blockIdx.x] * BM;
+    const int kb_begin = blockIdx.y * g.kb_per_split;
+    const int kb_end = min(g.num_kb, kb_begin + g.kb_per_split);
+    const int nkb = kb_end - kb_begin;
+    if (nkb <= 0) return;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&P.tmA);
+        prefetch_tmap(&P.tmB);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(tmem_full, 1);
+        fence_barrier_init();
+    }
+    for (int i = threadIdx.x; i < ONES_BYTES / 4; i += THREADS) reinterpret_cast<uint32_t*>(sOnes)[i] = 0x3F803F80u;  // bf16 1.0 pairs
+    fence_proxy_async();
+    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % STAGES;
+                mbar_wait(&empty_bar[s], ((uint32_t)(i / STAGES) & 1u) ^ 1u);
+                mbar_expect_tx(&full_bar[s], A_STAGE + B_STAGE);
+                const int k0 = (kb_begin + i) * BK;
+#pragma unroll
+                for (int j = 0; j < BM / 64; ++j) tma_load_2d(sA + s * A_STAGE + j * 8192, &P.tmA, m0 + j * 64, k0, &full_bar[s]);
+#pragma unroll
+                for (int j = 0; j < BN / 64; ++j) tma_load_2d(sB + s * B_STAGE + j * 8192, &P.tmB, j * 64, k0, &full_bar[s]);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(BN, true, true);
+            const uint32_t idesc_b = make_idesc(16, true, true);
+            const uint32_t ones = smem_u32(sOnes);
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % STAGES;
+                mbar_wait(&full_bar[s], (uint32_t)(i / STAGES) & 1u);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(sA + s * A_STAGE), b_addr = smem_u32(sB + s * B_STAGE);
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                    const uint64_t da = make_smem_desc(a_addr + k * 2048, 8192, 1024);
+                    umma_bf16(tmem_base, da, make_smem_desc(b_addr + k * 2048, 8192, 1024), idesc, (i > 0 || k > 0) ? 1u : 0u);
+                    umma_bf16(tmem_base + BN, da, make_smem_desc(ones + k * 2048, 8192, 1024), idesc_b, (i > 0 || k > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(tmem_full);
+        }
+        __syncwarp();
+    } else {
+        const int q = warp & 3;            // TMEM lane quadrant: rows m0 + 32 q .. + 32 of dW
+        const int half = (warp - 2) >> 2;  // which 128 of the 256 columns
+        mbar_wait(tmem_full, 0);
+        tc_fence_after();
+        float* stile = reinterpret_cast<float*>(smem) + (half * 4 + q) * (32 * PITCH);
+        const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+#pragma unroll
+        for (int c0 = 0; c0 < 128; c0 += 32) {
+            uint32_t r[32];
+            tmem_ld32(tmem_base + lane_off + (uint32_t)(half * 128 + c0), r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<float4*>(stile + lane * PITCH + c0 + j) =
+                    make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+        }
+        if (half == 0 && P.db != nullptr) {  // the tile's bias gradient: every one of the 16 extra columns holds it
+            uint32_t r[32];
+            tmem_ld32(tmem_base + lane_off + (uint32_t)BN, r);
+            tmem_ld_wait();
+            const int m = m0 + q * 32 + lane;
+            if (m < P.m) atomicAdd(P.db + m, __uint_as_float(r[0]));
+        }
+        __syncwarp();
+        const int rows_here = min(32, P.m - (m0 + q * 32));
+        for (int rr = 0; rr < rows_here; ++rr) {
+            const float4 v = *reinterpret_cast<const float4*>(stile + rr * PITCH + lane * 4);
+            red_add_v4(P.dw + (int64_t)(m0 + q * 32 + rr) * BN + half * 128 + lane * 4, v.x, v.y, v.z, v.w);
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+}  // namespace dwb
+
+// items[i]: dw (m x 256, row-major, accumulated into), db (m, accumulated into; may be null), dy16 [rows][m] (pitch lddy),
+// x16 [rows][256] (pitch ldx)
+int dw_batched(const DwBatchItem* items, int count, int64_t rows, cudaStream_t st) {
+    using namespace dwb;
+    PIO_CHECK_ARG(items && count >= 1 && count <= MAX_PROB && rows > 0, "dw_batched: bad arguments (count %d)", count);
+    static_assert(sizeof(Batch) <= 32000, "dw_batched: the problem table must fit the kernel parameter space");
+    Batch g{};
+    int tiles = 0;
+    for (int i = 0; i < count; ++i) {
+        const DwBatchItem& it = items[i];
+        PIO_CHECK_ARG(it.dy16 && it.x16 && it.dw && it.m > 0 && it.m % 8 == 0 && it.n == BN && (((uintptr_t)it.dw) & 15) == 0,
+                      "dw_batched: item %d not supported (m %d n %d)", i, it.m, it.n);
+        PIO_TRY(make_tmap_bf16(&g.prob[i].tmA, it.dy16, rows, it.m, it.lddy, 64));
+        PIO_TRY(make_tmap_bf16(&g.prob[i].tmB, it.x16, rows, BN, it.ldx, 64));
+        g.prob[i].dw = it.dw;
+        g.prob[i].db = it.db;
+        g.prob[i].m = it.m;
+        for (int t = 0; t < (int)cdiv(it.m, BM); ++t) {
+            PIO_CHECK_ARG(tiles < MAX_TILES, "dw_batched: more than %d output tiles", MAX_TILES);
+            g.tile_prob[tiles] = (unsigned char)i;
+            g.tile_m[tiles] = (unsigned char)t;
+            ++tiles;
+        }
+    }
+    g.num_kb = (int)cdiv(rows, (int64_t)BK);
+    const int splits = std::max(1, std::min(g.num_kb, num_sms() / tiles));
+    g.kb_per_split = (int)cdiv(g.num_kb, splits);
+    const int used = (int)cdiv(g.num_kb, g.kb_per_split);
+    int dev = 0;
+    PIO_CUDA(cudaGetDevice(&dev));
+    static std::atomic<bool> configured[64];
+    if (dev >= 0 && dev < 64 && !configured[dev].load()) {
+        PIO_CUDA(cudaFuncSetAttribute(dw_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+        configured[dev].store(true);
+    }
+    PIO_CUDA(launch_pdl(dw_batched_kernel, dim3((unsigned)tiles, (unsigned)used), dim3(THREADS), SMEM_BYTES, st, g));
+    count_launch();
+    return PIO_OK;
+}
+
+}  // namespace pio

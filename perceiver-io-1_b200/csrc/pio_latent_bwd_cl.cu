@@ -644,22 +644,28 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
 
 }  // namespace lbb
 
-// dgamma += sum_rows dn * xhat, dbeta += sum_rows dn for a LayerNorm whose backward ran inside the fused kernel:
-// dn (bf16, the gradient of the normalised output before the affine scale), x (the LayerNorm input), (mean, rstd).
-// grid (C / 64, row chunks), 256 threads = 64 columns x 4 row phases; fp32 atomics into the (zero-filled) gradients.
-__global__ void __launch_bounds__(256) ln_param_grads_kernel(const __nv_bfloat16* __restrict__ dn, const float* __restrict__ x,
-                                                             const float* __restrict__ stats, float* __restrict__ dgamma,
-                                                             float* __restrict__ dbeta, int64_t rows, int c, int64_t rows_per_chunk) {
+// dgamma += sum_rows dn * xhat, dbeta += sum_rows dn for the LayerNorms whose backward ran inside the fused kernel, a
+// table of them per launch: dn (bf16, the gradient of the normalised output before the affine scale), x (the LayerNorm
+// input), (mean, rstd).  grid (C / 64, row chunks, items), 256 threads = 64 columns x 4 row phases; fp32 atomics into
+// the (zero-filled or running) gradients.
+struct LnGradTable {
+    LnGradItem item[PIO_LN_GRAD_MAX_ITEMS];
+};
+__global__ void __launch_bounds__(256) ln_param_grads_kernel(const __grid_constant__ LnGradTable tab, int64_t rows, int c,
+                                                             int64_t rows_per_chunk) {
     __shared__ float s_g[256], s_b[256];
     pdl_trigger();
     pdl_wait();
+    const LnGradItem& it = tab.item[blockIdx.z];
+    const __nv_bfloat16* __restrict__ dn = (const __nv_bfloat16*)it.dn16;
+    const float* __restrict__ x = it.x;
     const int col = blockIdx.x * 64 + (threadIdx.x & 63);
     const int sub = threadIdx.x >> 6;
     const int64_t r0 = (int64_t)blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
     float ag = 0.f, ab = 0.f;
     if (col < c)
         for (int64_t r = r0 + sub; r < r1; r += 4) {
-            const float2 ms = __ldg(reinterpret_cast<const float2*>(stats) + r);
+            const float2 ms = __ldg(reinterpret_cast<const float2*>(it.stats) + r);
             const float d = __bfloat162float(dn[r * c + col]);
             ag = fmaf(d, (x[r * c + col] - ms.x) * ms.y, ag);
             ab += d;
@@ -668,19 +674,23 @@ __global__ void __launch_bounds__(256) ln_param_grads_kernel(const __nv_bfloat16
     s_b[threadIdx.x] = ab;
     __syncthreads();
     if (sub == 0 && col < c) {
-        atomicAdd(dgamma + col, s_g[threadIdx.x] + s_g[threadIdx.x + 64] + s_g[threadIdx.x + 128] + s_g[threadIdx.x + 192]);
-        atomicAdd(dbeta + col, s_b[threadIdx.x] + s_b[threadIdx.x + 64] + s_b[threadIdx.x + 128] + s_b[threadIdx.x + 192]);
+        atomicAdd(it.dgamma + col, s_g[threadIdx.x] + s_g[threadIdx.x + 64] + s_g[threadIdx.x + 128] + s_g[threadIdx.x + 192]);
+        atomicAdd(it.dbeta + col, s_b[threadIdx.x] + s_b[threadIdx.x + 64] + s_b[threadIdx.x + 128] + s_b[threadIdx.x + 192]);
     }
 }
 
-int ln_param_grads(const void* dn16, const float* x, const float* stats, float* dgamma, float* dbeta, int64_t rows, int c, cudaStream_t st) {
-    PIO_CHECK_ARG(dn16 && x && stats && dgamma && dbeta && c > 0 && rows >= 0, "ln_param_grads: bad arguments");
+int ln_param_grads(const LnGradItem* items, int count, int64_t rows, int c, cudaStream_t st) {
+    PIO_CHECK_ARG(items && count >= 1 && count <= PIO_LN_GRAD_MAX_ITEMS && c > 0 && rows >= 0, "ln_param_grads: bad arguments");
     if (rows == 0) return PIO_OK;
+    LnGradTable tab{};
+    for (int i = 0; i < count; ++i) {
+        PIO_CHECK_ARG(items[i].dn16 && items[i].x && items[i].stats && items[i].dgamma && items[i].dbeta, "ln_param_grads: null pointer in item %d", i);
+        tab.item[i] = items[i];
+    }
     const int64_t col_blocks = cdiv(c, 64);
-    const int64_t chunks = std::max<int64_t>(1, std::min<int64_t>(cdiv(2 * (int64_t)num_sms(), col_blocks), cdiv(rows, 32)));
-    dim3 grid((unsigned)col_blocks, (unsigned)chunks);
-    PIO_CUDA(launch_pdl(ln_param_grads_kernel, grid, dim3(256), 0, st, (const __nv_bfloat16*)dn16, x, stats, dgamma, dbeta, rows, c,
-                        cdiv(rows, chunks)));
+    const int64_t chunks = std::max<int64_t>(1, std::min<int64_t>(cdiv(4 * (int64_t)num_sms(), col_blocks * count), cdiv(rows, 32)));
+    dim3 grid((unsigned)col_blocks, (unsigned)chunks, (unsigned)count);
+    PIO_CUDA(launch_pdl(ln_param_grads_kernel, grid, dim3(256), 0, st, tab, rows, c, cdiv(rows, chunks)));
     count_launch();
     return PIO_OK;
 }

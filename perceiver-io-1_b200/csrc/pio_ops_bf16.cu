@@ -641,25 +641,30 @@ static int latent_block_bwd_fused(Ctx& c, Side& side, const float* dy, const flo
         flip ^= 1;
         hi = lo;
     }
-    // parameter gradients
+    // parameter gradients: per (up to 8) layers one batched weight-gradient launch (bias gradients ride on it) and one
+    // launch for the LayerNorm parameter gradients, on the two side streams
     PIO_TRY(side.fork());
-    for (int s = layers - 1; s >= 0; --s) {
-        const char* slab = (const char*)saved + (size_t)s * L.per_layer;
-        SaSaved sa((void*)(slab + L.sa), batch, n, ch, heads);
-        MlpSaved ms((void*)(slab + L.mlp), rows, ch);
-        const LatentBwdLayer& b = bl[(size_t)s];
-        const float* x_in = (s == 0) ? x : bl[(size_t)s - 1].xnext;
-        const bf16 *gy = (const bf16*)b.gy16, *gh = (const bf16*)b.gh16, *gm = (const bf16*)b.gmid16, *gq = (const bf16*)b.gqkv16;
-        PIO_TRY(tc_dW(c, gy, ch, ms.g, ch, mlp_g[s].w2, rows, ch, ch, 2, side.stream()));
-        PIO_TRY(tc_dW(c, gh, ch, ms.h0, ch, mlp_g[s].w1, rows, ch, ch, 2, side.stream()));
-        PIO_TRY(tc_dW(c, gm, ch, sa.o16, ch, attn_g[s].wo, rows, ch, ch, 2, side.stream()));
-        PIO_TRY(tc_dW(c, gq, 3 * ch, sa.h0, ch, attn_g[s].wq, rows, 3 * ch, ch, 2, side.stream()));
-        PIO_TRY(side_colsum(c, side, gy, ch, mlp_g[s].b2, 2, rows, ch));
-        PIO_TRY(side_colsum(c, side, gh, ch, mlp_g[s].b1, 2, rows, ch));
-        PIO_TRY(side_colsum(c, side, gm, ch, attn_g[s].bo, 2, rows, ch));
-        PIO_TRY(side_colsum(c, side, gq, 3 * ch, attn_g[s].bq, 2, rows, 3 * ch));
-        PIO_TRY(ln_param_grads(b.gn2, b.xmid, b.mlp_stats, mlp_g[s].ln_w, mlp_g[s].ln_b, rows, ch, side.stream2()));
-        PIO_TRY(ln_param_grads(b.gn1, x_in, b.sa_stats, attn_g[s].ln_w, attn_g[s].ln_b, rows, ch, side.stream2()));
+    for (int hi = layers; hi > 0;) {
+        const int lo = std::max(0, hi - PIO_LATENT_FUSED_MAX_LAYERS);
+        DwBatchItem dwi[4 * PIO_LATENT_FUSED_MAX_LAYERS];
+        LnGradItem lni[2 * PIO_LATENT_FUSED_MAX_LAYERS];
+        int nd = 0, nl = 0;
+        for (int s = hi - 1; s >= lo; --s) {
+            const char* slab = (const char*)saved + (size_t)s * L.per_layer;
+            SaSaved sa((void*)(slab + L.sa), batch, n, ch, heads);
+            MlpSaved ms((void*)(slab + L.mlp), rows, ch);
+            const LatentBwdLayer& b = bl[(size_t)s];
+            const float* x_in = (s == 0) ? x : bl[(size_t)s - 1].xnext;
+            dwi[nd++] = DwBatchItem{b.gy16, ch, ch, ms.g, ch, ch, mlp_g[s].w2, mlp_g[s].b2};
+            dwi[nd++] = DwBatchItem{b.gh16, ch, ch, ms.h0, ch, ch, mlp_g[s].w1, mlp_g[s].b1};
+            dwi[nd++] = DwBatchItem{b.gmid16, ch, ch, sa.o16, ch, ch, attn_g[s].wo, attn_g[s].bo};
+            dwi[nd++] = DwBatchItem{b.gqkv16, 3 * ch, 3 * ch, sa.h0, ch, ch, attn_g[s].wq, attn_g[s].bq};
+            lni[nl++] = LnGradItem{b.gn2, b.xmid, b.mlp_stats, mlp_g[s].ln_w, mlp_g[s].ln_b};
+            lni[nl++] = LnGradItem{b.gn1, x_in, b.sa_stats, attn_g[s].ln_w, attn_g[s].ln_b};
+        }
+        PIO_TRY(dw_batched(dwi, nd, rows, side.stream()));
+        PIO_TRY(ln_param_grads(lni, nl, rows, ch, side.stream2()));
+        hi = lo;
     }
     PIO_TRY(side.join());
     c.W.off = mark;

@@ -118,7 +118,27 @@ struct LatentBwdLayer {
 bool latent_bwd_cluster_supported(int64_t rows, int n, int ch, int heads, float drop_p);
 int latent_block_bwd_cluster(const float* dy, const float* x, float* dx, const LatentBwdLayer* layers, int nlayers, int batch, int n,
                              cudaStream_t st);
-int ln_param_grads(const void* dn16, const float* x, const float* stats, float* dgamma, float* dbeta, int64_t rows, int c, cudaStream_t st);
+#define PIO_LN_GRAD_MAX_ITEMS 16
+struct LnGradItem {
+    const void* dn16;
+    const float* x;
+    const float* stats;
+    float* dgamma;
+    float* dbeta;
+};
+int ln_param_grads(const LnGradItem* items, int count, int64_t rows, int c, cudaStream_t st);
+// one launch for a table of weight-gradient products over the same rows (pio_dw_batched.cu)
+struct DwBatchItem {
+    const void* dy16;
+    int64_t lddy;
+    int m;
+    const void* x16;
+    int64_t ldx;
+    int n;  // 256
+    float* dw;
+    float* db;
+};
+int dw_batched(const DwBatchItem* items, int count, int64_t rows, cudaStream_t st);
 bool latent_fused_supported(int64_t rows, int n, int ch, int heads, float drop_p);
 int latent_block_fwd_fused(const float* x, const LatentFusedLayer* layers, int nlayers, int batch, int n, cudaStream_t st);
 
