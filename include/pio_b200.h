@@ -240,6 +240,36 @@ int pio_flat_copy_f32(float* flat, const pio_flat_tensor* tensors, const pio_ada
  * nn.CrossEntropyLoss, lightning.py:225-226).  Null pointers are allowed with a count of 0. */
 int pio_scale3_f32(float* a, int64_t na, float* b, int64_t nb, float* c, int64_t nc, const float* scale, pio_stream_t stream);
 
+/* Batched weight-gradient products of Linear layers that share their rows (reference: autograd through the nn.Linear /
+ * nn.MultiheadAttention projections of self_attention_layer, model.py:20-26, :102-116): for every item
+ *   dw (m x 256, row-major) += dy16^T x16,   db (m; nullable) += column sums of dy16
+ * with dy16 (rows x m, bf16, pitch lddy elements) and x16 (rows x 256, bf16, pitch ldx).  One launch for up to 32 items
+ * (at most 160 output tiles of 128 rows); n must be 256, m a multiple of 8, pitches multiples of 8, dw 16-byte aligned.
+ * The sums are added with fp32 atomics: the caller zero-fills dw / db or accumulates into running gradients. */
+typedef struct {
+    const void* dy16;
+    int64_t lddy;
+    int m;
+    const void* x16;
+    int64_t ldx;
+    int n;
+    float* dw;
+    float* db;
+} pio_dw_item;
+int pio_dw_batched(const pio_dw_item* items, int count, int64_t rows, pio_stream_t stream);
+
+/* LayerNorm parameter gradients for a table of up to 16 LayerNorms over the same (rows, c): dgamma += sum_rows dn * xhat,
+ * dbeta += sum_rows dn with xhat = (x - mean) * rstd, dn16 (rows x c, bf16) the gradient of the normalised output BEFORE
+ * the affine scale's backward, stats (rows x 2) = (mean, rstd); c a multiple of 4.  fp32 atomics into dgamma / dbeta. */
+typedef struct {
+    const void* dn16;
+    const float* x;
+    const float* stats;
+    float* dgamma;
+    float* dbeta;
+} pio_ln_grad_item;
+int pio_ln_param_grads(const pio_ln_grad_item* items, int count, int64_t rows, int c, pio_stream_t stream);
+
 /* Attention core of nn.MultiheadAttention as called at model.py:74 (dropout 0):
  * S = (q dh^-1/2) k^T, padded keys -> -inf, P = softmax(S), O = P v.  Flash-style: P is never
  * stored; lse (batch,heads,n) = logsumexp of the scaled scores, saved for the backward, which

@@ -89,6 +89,26 @@ struct Params {
 };
 
 __device__ __forceinline__ void bar_ew() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+// Phase timeline for tuning (only in builds with -DPIO_LB_TRACE, tools/latent_cluster_trace.py --bwd): CTA 0's MMA
+// thread (who 0) and thread 0 of its element-wise warps (who 1) log (tag, clock64) pairs.
+#ifdef PIO_LB_TRACE
+__device__ long long gb_trace[2][2][8192];
+__device__ int gb_trace_n[2];
+#define BW_TRACE(who, tag)                                               \
+    do {                                                                 \
+        if (blockIdx.x == 0) {                                           \
+            const int _i = gb_trace_n[who];                              \
+            if (_i < 8192) {                                             \
+                gb_trace[who][0][_i] = (tag);                            \
+                gb_trace[who][1][_i] = clock64();                        \
+                gb_trace_n[who] = _i + 1;                                \
+            }                                                            \
+        }                                                                \
+    } while (0)
+#else
+#define BW_TRACE(who, tag) do { } while (0)
+#endif
 __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
@@ -251,16 +271,26 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             const int row0 = tile * ROWS;
             int cons = 0;
             uint32_t ew_phase = 0, g_phase = 0, qkv_phase = 0;
+            int tr = 0;
             auto wait_ew = [&]() {
+                BW_TRACE(0, 1000 + tr);
                 mbar_wait(ew_done, ew_phase);
                 ew_phase ^= 1u;
                 tc_fence_after();
+                BW_TRACE(0, 2000 + tr);
+                ++tr;
             };
             auto wait_atom = [&](int j) -> int {
                 const int a = (r + R - j) % R;
+                if (j == 0) BW_TRACE(0, 1000 + tr);
                 mbar_wait(&gath_full[a], g_phase);
                 tc_fence_after();
-                if (j == R - 1) g_phase ^= 1u;
+                if (j == 0) BW_TRACE(0, 2000 + tr);
+                if (j == R - 1) {
+                    g_phase ^= 1u;
+                    BW_TRACE(0, 3000 + tr);
+                    ++tr;
+                }
                 return a;
             };
             auto ring_wait = [&]() -> uint32_t {
@@ -368,10 +398,14 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             peer_bar[d - 1] = mapa(smem_u32(&gath_full[r]), peer);
         }
 
+        int tr = 0;
         auto wait_mma = [&]() {
+            if (threadIdx.x == 0) BW_TRACE(1, 1000 + tr);
             mbar_wait(mma_done, mma_phase);
             mma_phase ^= 1u;
             tc_fence_after();
+            if (threadIdx.x == 0) BW_TRACE(1, 2000 + tr);
+            ++tr;
         };
         auto free_arrive = [&]() {  // this CTA is done with the current contents of sA: tell every CTA of the cluster
             if (threadIdx.x == 0) {
@@ -401,6 +435,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
         // the two warps of a TMEM lane quadrant have written their 32 rows (4 KB) of the tiles to send: one thread copies them
         // into the three peers' atom number r and arrives on the local gath_full[r]; src[d] = the tile for peer (r + 1 + d) % 4
         auto send_quadrant = [&](const uint8_t* s0, const uint8_t* s1, const uint8_t* s2) {
+            if (threadIdx.x == 0) BW_TRACE(1, 5000);
             tc_fence_before();
             fence_proxy_async();
             asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");
@@ -431,8 +466,10 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             for (int d = 0; d < R; ++d) st_async_f32x2(mapa(mine, (uint32_t)d), a, b, mapa(sbar, (uint32_t)d));
         };
         auto wait_sums = [&](float& a, float& b) {
+            if (threadIdx.x == 0) BW_TRACE(1, 4000);
             mbar_wait(stat_full, stat_phase);
             stat_phase ^= 1u;
+            if (threadIdx.x == 0) BW_TRACE(1, 4001);
             a = 0.f; b = 0.f;
 #pragma unroll
             for (int g = 0; g < 2 * R; ++g) {  // same order in every thread of every CTA
@@ -615,7 +652,9 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
 #pragma unroll
                 for (int d = 1; d < R; ++d) {
                     const int src = (r + R - d) % R;  // in the order the peers send
+                    if (threadIdx.x == 0 && d == 1) BW_TRACE(1, 6000);
                     mbar_wait(&gath_full[src], 1u);   // (four gathers per layer: the reduce-scatter is always an odd phase)
+                    if (threadIdx.x == 0 && d == R - 1) BW_TRACE(1, 6001);
                     float t[32];
                     lb::load_half_row_smem(sA + src * ATOM, row, cg, t);
 #pragma unroll
@@ -644,6 +683,23 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
 
 }  // namespace lbb
 
+#ifdef PIO_LB_TRACE
+extern "C" int pio_debug_lbb_trace(long long* out, int max_pairs, int who, int reset) {
+    int n = 0;
+    cudaMemcpyFromSymbol(&n, lbb::gb_trace_n, sizeof(int), who * sizeof(int));
+    n = std::min(n, max_pairs);
+    if (out && n > 0) {
+        cudaMemcpyFromSymbol(out, lbb::gb_trace, (size_t)n * 8, (size_t)(who * 2 + 0) * 8192 * 8);
+        cudaMemcpyFromSymbol(out + max_pairs, lbb::gb_trace, (size_t)n * 8, (size_t)(who * 2 + 1) * 8192 * 8);
+    }
+    if (reset) {
+        int z[2] = {0, 0};
+        cudaMemcpyToSymbol(lbb::gb_trace_n, z, sizeof(z));
+    }
+    return n;
+}
+#endif
+
 // dgamma += sum_rows dn * xhat, dbeta += sum_rows dn for the LayerNorms whose backward ran inside the fused kernel, a
 // table of them per launch: dn (bf16, the gradient of the normalised output before the affine scale), x (the LayerNorm
 // input), (mean, rstd).  grid (C / 64, row chunks, items), 256 threads = 64 columns x 4 row phases; fp32 atomics into
@@ -653,34 +709,66 @@ struct LnGradTable {
 };
 __global__ void __launch_bounds__(256) ln_param_grads_kernel(const __grid_constant__ LnGradTable tab, int64_t rows, int c,
                                                              int64_t rows_per_chunk) {
-    __shared__ float s_g[256], s_b[256];
+    // thread = 4 consecutive columns x one of 16 row phases: a warp reads two rows of the block's 64 columns per step
+    // (128 bytes of dn, 256 of x per row), four steps in flight
+    __shared__ float4 s_g[16][16], s_b[16][16];
     pdl_trigger();
     pdl_wait();
     const LnGradItem& it = tab.item[blockIdx.z];
     const __nv_bfloat16* __restrict__ dn = (const __nv_bfloat16*)it.dn16;
     const float* __restrict__ x = it.x;
-    const int col = blockIdx.x * 64 + (threadIdx.x & 63);
-    const int sub = threadIdx.x >> 6;
+    const float2* __restrict__ stats = reinterpret_cast<const float2*>(it.stats);
+    const int cq = threadIdx.x & 15, rp = threadIdx.x >> 4;
+    const int col = blockIdx.x * 64 + cq * 4;
     const int64_t r0 = (int64_t)blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
-    float ag = 0.f, ab = 0.f;
-    if (col < c)
-        for (int64_t r = r0 + sub; r < r1; r += 4) {
-            const float2 ms = __ldg(reinterpret_cast<const float2*>(it.stats) + r);
-            const float d = __bfloat162float(dn[r * c + col]);
-            ag = fmaf(d, (x[r * c + col] - ms.x) * ms.y, ag);
-            ab += d;
+    float ag[4] = {0.f, 0.f, 0.f, 0.f}, ab[4] = {0.f, 0.f, 0.f, 0.f};
+    if (col < c) {
+        for (int64_t rb = r0 + rp; rb < r1; rb += 64) {
+            uint2 d[4];
+            float4 xv[4];
+            float2 ms[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t r = rb + 16 * u;
+                if (r < r1) {
+                    d[u] = *reinterpret_cast<const uint2*>(dn + r * c + col);
+                    xv[u] = *reinterpret_cast<const float4*>(x + r * c + col);
+                    ms[u] = __ldg(stats + r);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (rb + 16 * u < r1) {
+                    const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&d[u].x));
+                    const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&d[u].y));
+                    const float dv[4] = {lo.x, lo.y, hi.x, hi.y};
+                    const float xs[4] = {xv[u].x, xv[u].y, xv[u].z, xv[u].w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        ag[j] = fmaf(dv[j], (xs[j] - ms[u].x) * ms[u].y, ag[j]);
+                        ab[j] += dv[j];
+                    }
+                }
+            }
         }
-    s_g[threadIdx.x] = ag;
-    s_b[threadIdx.x] = ab;
+    }
+    s_g[rp][cq] = make_float4(ag[0], ag[1], ag[2], ag[3]);
+    s_b[rp][cq] = make_float4(ab[0], ab[1], ab[2], ab[3]);
     __syncthreads();
-    if (sub == 0 && col < c) {
-        atomicAdd(it.dgamma + col, s_g[threadIdx.x] + s_g[threadIdx.x + 64] + s_g[threadIdx.x + 128] + s_g[threadIdx.x + 192]);
-        atomicAdd(it.dbeta + col, s_b[threadIdx.x] + s_b[threadIdx.x + 64] + s_b[threadIdx.x + 128] + s_b[threadIdx.x + 192]);
+    if (threadIdx.x < 128) {  // 64 columns x {dgamma, dbeta}
+        const int cc = threadIdx.x & 63;
+        const bool gamma = threadIdx.x < 64;
+        const float* src = reinterpret_cast<const float*>(gamma ? &s_g[0][0] : &s_b[0][0]);
+        float t = 0.f;
+#pragma unroll
+        for (int ph = 0; ph < 16; ++ph) t += src[ph * 64 + cc];
+        const int gc = blockIdx.x * 64 + cc;
+        if (gc < c) atomicAdd((gamma ? it.dgamma : it.dbeta) + gc, t);
     }
 }
 
 int ln_param_grads(const LnGradItem* items, int count, int64_t rows, int c, cudaStream_t st) {
-    PIO_CHECK_ARG(items && count >= 1 && count <= PIO_LN_GRAD_MAX_ITEMS && c > 0 && rows >= 0, "ln_param_grads: bad arguments");
+    PIO_CHECK_ARG(items && count >= 1 && count <= PIO_LN_GRAD_MAX_ITEMS && c > 0 && c % 4 == 0 && rows >= 0, "ln_param_grads: bad arguments");
     if (rows == 0) return PIO_OK;
     LnGradTable tab{};
     for (int i = 0; i < count; ++i) {
@@ -688,7 +776,7 @@ int ln_param_grads(const LnGradItem* items, int count, int64_t rows, int c, cuda
         tab.item[i] = items[i];
     }
     const int64_t col_blocks = cdiv(c, 64);
-    const int64_t chunks = std::max<int64_t>(1, std::min<int64_t>(cdiv(4 * (int64_t)num_sms(), col_blocks * count), cdiv(rows, 32)));
+    const int64_t chunks = std::max<int64_t>(1, std::min<int64_t>(cdiv(4 * (int64_t)num_sms(), col_blocks * count), cdiv(rows, 64)));
     dim3 grid((unsigned)col_blocks, (unsigned)chunks, (unsigned)count);
     PIO_CUDA(launch_pdl(ln_param_grads_kernel, grid, dim3(256), 0, st, tab, rows, c, cdiv(rows, chunks)));
     count_launch();

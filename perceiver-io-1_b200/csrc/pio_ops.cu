@@ -539,6 +539,16 @@ int pio_self_attn_bwd(const float* dy, const float* x, float* dx, const pio_attn
 }
 
 // ---- latent block
+int pio_dw_batched(const pio_dw_item* items, int count, int64_t rows, pio_stream_t stream) {
+    static_assert(sizeof(pio_dw_item) == sizeof(DwBatchItem), "pio_dw_item and DwBatchItem must have the same layout");
+    return dw_batched(reinterpret_cast<const DwBatchItem*>(items), count, rows, (cudaStream_t)stream);
+}
+
+int pio_ln_param_grads(const pio_ln_grad_item* items, int count, int64_t rows, int c, pio_stream_t stream) {
+    static_assert(sizeof(pio_ln_grad_item) == sizeof(LnGradItem), "pio_ln_grad_item and LnGradItem must have the same layout");
+    return ln_param_grads(reinterpret_cast<const LnGradItem*>(items), count, rows, c, (cudaStream_t)stream);
+}
+
 size_t pio_latent_block_saved_bytes(int layers, int batch, int n, int c, int heads, int mode) {
     if (mode == PIO_MODE_BF16) return bf::block_saved_bytes(layers, batch, n, c, heads);
     BlockLayout L(batch, n, c, heads);

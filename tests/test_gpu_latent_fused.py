@@ -1,7 +1,9 @@
 """The fused latent-block kernels (one launch per self_attention_block, reference model.py:36-44) against (a) the
 unfused bf16 operators they replace and (b) the fp32 oracle: the cluster kernel (pio_latent_cl.cu, four CTAs per
 128-row tile, the default up to 66 tiles) and the one-CTA-per-tile kernel (pio_latent_tc.cu).  The fused forward
-writes the same saved-for-backward state as the unfused one, so gradients through it check every saved tensor."""
+writes the same saved-for-backward state as the unfused one, so gradients through it check every saved tensor.  The
+backward runs through the fused input-gradient chain (pio_latent_bwd_cl.cu + the batched parameter-gradient kernels)
+or through the unfused operators."""
 import os
 
 import pytest
@@ -14,17 +16,19 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda"
 
 
-@pytest.fixture(autouse=True, params=["cluster", "single"])
+@pytest.fixture(autouse=True, params=["cluster", "single", "cluster-fwd-only"])
 def bf16_mode(request):
     import perceiver
     perceiver.set_compute_mode("bf16")
     os.environ.pop("PIO_NO_FUSED_LATENT", None)
-    os.environ["PIO_LATENT_CLUSTER"] = "1" if request.param == "cluster" else "0"  # (read per call)
+    os.environ["PIO_LATENT_CLUSTER"] = "0" if request.param == "single" else "1"  # (read per call)
+    os.environ["PIO_LATENT_BWD_CLUSTER"] = "1" if request.param == "cluster" else "0"
     os.environ["PIO_FUSED_LATENT_MIN_ROWS"] = "0"  # by default the one-CTA kernel only takes blocks of >= 56 row tiles
     yield
     os.environ.pop("PIO_NO_FUSED_LATENT", None)
     os.environ.pop("PIO_FUSED_LATENT_MIN_ROWS", None)
     os.environ.pop("PIO_LATENT_CLUSTER", None)
+    os.environ.pop("PIO_LATENT_BWD_CLUSTER", None)
     perceiver.set_compute_mode("fp32")
 
 
