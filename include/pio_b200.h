@@ -240,6 +240,16 @@ int pio_flat_copy_f32(float* flat, const pio_flat_tensor* tensors, const pio_ada
  * nn.CrossEntropyLoss, lightning.py:225-226).  Null pointers are allowed with a count of 0. */
 int pio_scale3_f32(float* a, int64_t na, float* b, int64_t nb, float* c, int64_t nc, const float* scale, pio_stream_t stream);
 
+/* Vocabulary logits of the text output adapter (reference adapter.py:101-109, nn.Linear) as the fused loss head forms
+ * them: c (m x n, bf16, pitch ldc >= n rounded up to 8) = a (m x k, bf16, pitch lda) w (n x k, bf16, pitch ldw)^T + bias
+ * (fp32, nullable), for the first *dyn_rows - dyn_off rows only when dyn_rows (DEVICE memory) is given; rows from there to
+ * the end of the last live 128-row tile are written as zeros, later rows are not touched.  Persistent kernel, one CTA per
+ * SM over the live tiles; k in {64, 128, 192, 256}, n >= 128, pitches multiples of 8.  Returns PIO_ERR_ARG for other
+ * shapes (pio_logits_bf16_supported tells beforehand). */
+int pio_logits_bf16_supported(int64_t m, int64_t n, int64_t k, int64_t lda, int64_t ldw, int64_t ldc);
+int pio_logits_bf16(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, void* c, int64_t ldc, int64_t m,
+                    int64_t n, int64_t k, const int32_t* dyn_rows, int dyn_off, pio_stream_t stream);
+
 /* Batched weight-gradient products of Linear layers that share their rows (reference: autograd through the nn.Linear /
  * nn.MultiheadAttention projections of self_attention_layer, model.py:20-26, :102-116): for every item
  *   dw (m x 256, row-major) += dy16^T x16,   db (m; nullable) += column sums of dy16

@@ -539,6 +539,15 @@ int pio_self_attn_bwd(const float* dy, const float* x, float* dx, const pio_attn
 }
 
 // ---- latent block
+int pio_logits_bf16_supported(int64_t m, int64_t n, int64_t k, int64_t lda, int64_t ldw, int64_t ldc) {
+    return logits_persistent_supported(m, n, k, lda, ldw, ldc) ? 1 : 0;
+}
+
+int pio_logits_bf16(const void* a, int64_t lda, const void* w, int64_t ldw, const float* bias, void* c, int64_t ldc, int64_t m,
+                    int64_t n, int64_t k, const int32_t* dyn_rows, int dyn_off, pio_stream_t stream) {
+    return logits_persistent(a, lda, w, ldw, bias, c, ldc, m, n, k, dyn_rows, dyn_off, (cudaStream_t)stream);
+}
+
 int pio_dw_batched(const pio_dw_item* items, int count, int64_t rows, pio_stream_t stream) {
     static_assert(sizeof(pio_dw_item) == sizeof(DwBatchItem), "pio_dw_item and DwBatchItem must have the same layout");
     return dw_batched(reinterpret_cast<const DwBatchItem*>(items), count, rows, (cudaStream_t)stream);

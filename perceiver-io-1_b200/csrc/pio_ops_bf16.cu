@@ -942,6 +942,90 @@ __global__ void __launch_bounds__(256) ce_chunk_kernel(bf16* __restrict__ lg, in
     }
 }
 
+// The same with the row held in registers between the passes (NV vectors of 8 logits per thread, classes <= 2048 NV):
+// one read and one write of the row instead of two reads and a write, all loads of a row in flight together, and the
+// block-wide reductions finished by every thread from shared memory instead of by thread 0 alone (the two-pass kernel
+// above spent 56 us on a 4352 x 10003 chunk that is resident in L2: it ran at the latency of its dependent passes).
+template <int NV>
+__global__ void __launch_bounds__(256) ce_chunk_reg_kernel(bf16* __restrict__ lg, int64_t ld, const int64_t* __restrict__ labels_c,
+                                                           const float* __restrict__ out3, const int* __restrict__ count, int64_t r0,
+                                                           int64_t nr, float* __restrict__ row_loss, int64_t classes) {
+    __shared__ float s_m[8], s_s[8];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int64_t live = max((int64_t)0, min(nr, (int64_t)*count - r0));
+    const int64_t upto = min(nr, (live + 63) / 64 * 64);
+    const float inv_n = 1.0f / out3[1];
+    const int nvec = (int)(ld >> 3);
+    for (int64_t r = blockIdx.x; r < upto; r += gridDim.x) {
+        uint4* zv = reinterpret_cast<uint4*>(lg + r * ld);
+        if (r >= live) {  // block-uniform
+            for (int j = threadIdx.x; j < nvec; j += blockDim.x) zv[j] = make_uint4(0u, 0u, 0u, 0u);
+            continue;
+        }
+        const int64_t y = labels_c[r0 + r];
+        float xy = 0.f;
+        if (threadIdx.x == 0) xy = __bfloat162float(lg[r * ld + y]);  // (before anyone overwrites the row)
+        uint4 u[NV];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int j = threadIdx.x + i * 256;
+            u[i] = j < nvec ? zv[j] : make_uint4(0u, 0u, 0u, 0u);
+        }
+        float m = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int64_t c0 = (int64_t)(threadIdx.x + i * 256) * 8;
+            const bf16* e = reinterpret_cast<const bf16*>(&u[i]);
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                if (c0 + k < classes) m = fmaxf(m, __bfloat162float(e[k]));
+        }
+        m = warp_max(m);
+        if (lane == 0) s_m[wid] = m;
+        __syncthreads();
+        float mm = s_m[0];
+#pragma unroll
+        for (int w = 1; w < 8; ++w) mm = fmaxf(mm, s_m[w]);
+        float ssum = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int64_t c0 = (int64_t)(threadIdx.x + i * 256) * 8;
+            const bf16* e = reinterpret_cast<const bf16*>(&u[i]);
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                if (c0 + k < classes) ssum += __expf(__bfloat162float(e[k]) - mm);
+        }
+        ssum = warp_sum(ssum);
+        if (lane == 0) s_s[wid] = ssum;
+        __syncthreads();
+        float tot = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) tot += s_s[w];
+        const float lse = mm + logf(tot);
+        if (threadIdx.x == 0) row_loss[r0 + r] = lse - xy;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int j = threadIdx.x + i * 256;
+            if (j < nvec) {
+                bf16* e = reinterpret_cast<bf16*>(&u[i]);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const int64_t col = (int64_t)j * 8 + k;
+                    float g = 0.f;
+                    if (col < classes) {
+                        g = __expf(__bfloat162float(e[k]) - lse);
+                        if (col == y) g -= 1.0f;
+                        g *= inv_n;
+                    }
+                    e[k] = __float2bfloat16(g);
+                }
+                zv[j] = u[i];
+            }
+        }
+        __syncthreads();  // s_m / s_s are rewritten for the next row
+    }
+}
+
 // db[j] += sum over the chunk's live rows of dl[r][j]: block = 128 rows x 256 columns (2 per thread), one atomic
 // per column per block.
 __global__ void __launch_bounds__(128) lce_colsum_kernel(const bf16* __restrict__ dl, int64_t ld, float* __restrict__ db,
@@ -985,8 +1069,18 @@ static int64_t lce_chunk_rows(int64_t classes) {
     return std::min<int64_t>(rows, 8192);
 }
 
+// Chunk schedule: the first chunk is L2-sized; an MLM batch labels ~15 % of its positions, so what follows is almost
+// always empty and every further chunk only costs launches of kernels that find nothing to do.  Later chunks are
+// therefore three times the previous one (32768 rows: 4352, 13056, 15360 instead of eight chunks); the logits buffer
+// has the size of the largest, of which only the live rows are ever written.
+static int64_t lce_max_chunk(int64_t rows, int64_t classes) {
+    int64_t most = 0;
+    for (int64_t r0 = 0, step = std::min(rows, lce_chunk_rows(classes)); r0 < rows; r0 += step, step *= 3) most = std::max(most, std::min(step, rows - r0));
+    return std::max<int64_t>(most, 1);
+}
+
 size_t linear_ce_ws_bytes(int64_t rows, int c_in, int64_t classes) {
-    const int64_t ch = std::min(rows, lce_chunk_rows(classes));
+    const int64_t ch = lce_max_chunk(rows, classes);
     return align_up((size_t)rows * pad8(c_in) * 2, 256) + align_up((size_t)ch * pad8(classes) * 2, 256) +
            align_up((size_t)rows * c_in * 4, 256) + 4 * align_up((size_t)rows * 8, 256) + 256 +
            align_up((size_t)cdiv(rows, 1024) * 4, 256) +
@@ -998,7 +1092,7 @@ int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, 
     const char* who = "pio_linear_ce_fwd_bwd";
     PIO_CHECK_ARG(rows < (1ll << 31), "%s: more than 2^31 rows", who);
     const int64_t cip = pad8(c_in), cop = pad8(classes);
-    const int64_t ch = std::min(rows, lce_chunk_rows(classes));
+    const int64_t ch0 = std::min(rows, lce_chunk_rows(classes)), ch = lce_max_chunk(rows, classes);
     const size_t mark = c.W.off;
     PIO_TAKE_BYTES(bf16, x16c, c, (size_t)rows * cip * 2, who);
     PIO_TAKE_BYTES(bf16, lg16, c, (size_t)ch * cop * 2, who);
@@ -1025,10 +1119,13 @@ int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, 
     PIO_CUDA(cudaMemsetAsync(dw, 0, (size_t)classes * c_in * sizeof(float), c.st));
     PIO_CUDA(cudaMemsetAsync(db, 0, (size_t)classes * sizeof(float), c.st));
     Side side(c, 2);
-    for (int64_t r0 = 0; r0 < rows; r0 += ch) {
-        const int64_t nr = std::min(ch, rows - r0);
+    for (int64_t r0 = 0, step = ch0; r0 < rows; r0 += step, step = std::min(3 * step, ch)) {
+        const int64_t nr = std::min(step, rows - r0);
         const bf16* xc = x16c + r0 * cip;
-        {  // logits (bf16) = x W^T + b for the live rows of this chunk
+        if (logits_persistent_supported(nr, classes, c_in, cip, cip, cop)) {
+            // logits (bf16) = x W^T + b for the live rows of this chunk: one CTA per SM over the live tiles only
+            PIO_TRY(logits_persistent(xc, cip, w16, cip, b, lg16, cop, nr, classes, c_in, count, (int)r0, c.st));
+        } else {
             pio_gemm_bf16_desc d{};
             d.a = xc; d.b = w16; d.m = nr; d.n = classes; d.k = c_in; d.lda = cip; d.ldb = cip; d.a_kmajor = 1; d.b_kmajor = 1;
             d.c16 = lg16; d.ldc16 = cop; d.bias = b;
@@ -1036,7 +1133,12 @@ int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, 
             PIO_TRY(tc_gemm(c, d));
         }
         const int blocks = (int)std::min<int64_t>(nr, (int64_t)num_sms() * 8);
-        ce_chunk_kernel<<<blocks, 256, 0, c.st>>>(lg16, cop, labels_c, out3, count, r0, nr, row_loss, classes);
+        if (cop <= 8 * 256 * 5)
+            ce_chunk_reg_kernel<5><<<blocks, 256, 0, c.st>>>(lg16, cop, labels_c, out3, count, r0, nr, row_loss, classes);
+        else if (cop <= 8 * 256 * 8)
+            ce_chunk_reg_kernel<8><<<blocks, 256, 0, c.st>>>(lg16, cop, labels_c, out3, count, r0, nr, row_loss, classes);
+        else
+            ce_chunk_kernel<<<blocks, 256, 0, c.st>>>(lg16, cop, labels_c, out3, count, r0, nr, row_loss, classes);
         PIO_LAUNCH_CHECK();
         PIO_TRY(side.fork());
         {  // dW += dlogits^T x   (contraction over the live rows)

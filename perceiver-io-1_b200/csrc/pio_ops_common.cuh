@@ -139,6 +139,10 @@ struct DwBatchItem {
     float* db;
 };
 int dw_batched(const DwBatchItem* items, int count, int64_t rows, cudaStream_t st);
+// persistent vocabulary-logits product (pio_logits_tc.cu)
+bool logits_persistent_supported(int64_t m, int64_t n, int64_t k, int64_t lda, int64_t ldb, int64_t ldc);
+int logits_persistent(const void* a, int64_t lda, const void* w, int64_t ldb, const float* bias, void* c, int64_t ldc, int64_t m,
+                      int64_t n, int64_t k, const int* dyn_rows, int dyn_off, cudaStream_t st);
 bool latent_fused_supported(int64_t rows, int n, int ch, int heads, float drop_p);
 int latent_block_fwd_fused(const float* x, const LatentFusedLayer* layers, int nlayers, int batch, int n, cudaStream_t st);
 

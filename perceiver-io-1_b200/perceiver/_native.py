@@ -96,6 +96,8 @@ _SIGNATURES = {
     "pio_adamw_tick": (c_int, [P, P]),
     "pio_flat_copy_f32": (c_int, [P, P, P, c_int, c_int, ctypes.c_float, P]),
     "pio_scale3_f32": (c_int, [P, c_int64, P, c_int64, P, c_int64, P, P]),
+    "pio_logits_bf16_supported": (c_int, [c_int64, c_int64, c_int64, c_int64, c_int64, c_int64]),
+    "pio_logits_bf16": (c_int, [P, c_int64, P, c_int64, P, P, c_int64, c_int64, c_int64, c_int64, P, c_int, P]),
     "pio_dw_batched": (c_int, [P, c_int, c_int64, P]),
     "pio_ln_param_grads": (c_int, [P, c_int, c_int64, c_int, P]),
     "pio_attn_fwd": (c_int, [POINTER(AttnDesc), c_int, P]),
