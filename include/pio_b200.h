@@ -240,6 +240,16 @@ int pio_flat_copy_f32(float* flat, const pio_flat_tensor* tensors, const pio_ada
  * nn.CrossEntropyLoss, lightning.py:225-226).  Null pointers are allowed with a count of 0. */
 int pio_scale3_f32(float* a, int64_t na, float* b, int64_t nb, float* c, int64_t nc, const float* scale, pio_stream_t stream);
 
+/* Deferred join of the side streams.  The bf16 backward operators run their parameter-gradient kernels on two side
+ * streams per (device, caller stream) and make the caller's stream wait for them before they return.  After
+ * pio_set_side_join_deferred(1) (per host thread) pio_latent_block_bwd returns WITHOUT that wait when all it has left
+ * on the side streams are parameter-gradient kernels, so they overlap with whatever the caller enqueues next; the
+ * caller must then call pio_side_join(stream) before anything on `stream` reads those gradients, and must keep the
+ * operator's workspace, saved buffer and inputs alive and unmodified until then.  Every other backward operator
+ * still joins before it returns (which also covers work deferred earlier on the same stream). */
+int pio_set_side_join_deferred(int on);
+int pio_side_join(pio_stream_t stream);
+
 /* Vocabulary logits of the text output adapter (reference adapter.py:101-109, nn.Linear) as the fused loss head forms
  * them: c (m x n, bf16, pitch ldc >= n rounded up to 8) = a (m x k, bf16, pitch lda) w (n x k, bf16, pitch ldw)^T + bias
  * (fp32, nullable), for the first *dyn_rows - dyn_off rows only when dyn_rows (DEVICE memory) is given; rows from there to

@@ -539,6 +539,13 @@ int pio_self_attn_bwd(const float* dy, const float* x, float* dx, const pio_attn
 }
 
 // ---- latent block
+int pio_set_side_join_deferred(int on) {
+    bf::set_side_join_deferred(on);
+    return PIO_OK;
+}
+
+int pio_side_join(pio_stream_t stream) { return bf::side_join((cudaStream_t)stream); }
+
 int pio_logits_bf16_supported(int64_t m, int64_t n, int64_t k, int64_t lda, int64_t ldw, int64_t ldc) {
     return logits_persistent_supported(m, n, k, lda, ldw, ldc) ? 1 : 0;
 }

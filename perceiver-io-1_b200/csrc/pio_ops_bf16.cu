@@ -110,6 +110,22 @@ struct Side {
     }
 };
 
+// Deferred join (pio_set_side_join_deferred / pio_side_join): an operator that only has parameter-gradient kernels
+// left on the side streams may return without making the caller's stream wait for them, so that they overlap with the
+// NEXT operator's kernels; the caller then joins (pio_side_join) before anything on its stream reads those gradients
+// or reuses the operator's workspace and saved buffers.  Per host thread; off unless the caller opts in.
+static thread_local int t_defer_side_join = 0;
+void set_side_join_deferred(int on) { t_defer_side_join = on ? 1 : 0; }
+int side_join(cudaStream_t st) {
+    SideRes* r = side_res(st);
+    if (!r) return PIO_OK;
+    PIO_CUDA(cudaEventRecord(r->join, r->stream));
+    PIO_CUDA(cudaStreamWaitEvent(st, r->join, 0));
+    PIO_CUDA(cudaEventRecord(r->join2, r->stream2));
+    PIO_CUDA(cudaStreamWaitEvent(st, r->join2, 0));
+    return PIO_OK;
+}
+
 // y = act(x16 W16^T + bias) (+ residual)
 static int tc_xwT(Ctx& c, const bf16* x, int64_t ldx, const bf16* w, int64_t ldw, int64_t rows, int64_t n, int64_t k,
                   float* c32, int64_t ldc32, bf16* c16, int64_t ldc16, const float* bias, const float* res, int64_t ldr,
@@ -666,7 +682,7 @@ static int latent_block_bwd_fused(Ctx& c, Side& side, const float* dy, const flo
         PIO_TRY(ln_param_grads(lni, nl, rows, ch, side.stream2()));
         hi = lo;
     }
-    PIO_TRY(side.join());
+    if (!t_defer_side_join) PIO_TRY(side.join());  // (deferred: the caller joins with pio_side_join)
     c.W.off = mark;
     return PIO_OK;
 }

@@ -175,6 +175,8 @@ int self_attn_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* w, v
 int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_attn_weights* w, const void* saved,
                   const pio_attn_grads* g, int acc, int batch, int n, int ch, int heads, int residual,
                   const __nv_bfloat16* dy16_in = nullptr, __nv_bfloat16* dx16_out = nullptr);
+void set_side_join_deferred(int on);
+int side_join(cudaStream_t st);
 size_t block_saved_bytes(int layers, int batch, int n, int ch, int heads);
 size_t block_ws_bytes(int layers, int batch, int n, int ch, int heads);
 int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,

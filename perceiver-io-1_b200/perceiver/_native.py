@@ -96,6 +96,8 @@ _SIGNATURES = {
     "pio_adamw_tick": (c_int, [P, P]),
     "pio_flat_copy_f32": (c_int, [P, P, P, c_int, c_int, ctypes.c_float, P]),
     "pio_scale3_f32": (c_int, [P, c_int64, P, c_int64, P, c_int64, P, P]),
+    "pio_set_side_join_deferred": (c_int, [c_int]),
+    "pio_side_join": (c_int, [P]),
     "pio_logits_bf16_supported": (c_int, [c_int64, c_int64, c_int64, c_int64, c_int64, c_int64]),
     "pio_logits_bf16": (c_int, [P, c_int64, P, c_int64, P, P, c_int64, c_int64, c_int64, c_int64, P, c_int, P]),
     "pio_dw_batched": (c_int, [P, c_int, c_int64, P]),
@@ -204,9 +206,11 @@ def require_cuda(*tensors):
 _ws = {}
 
 
-def workspace(nbytes: int, device):
+def workspace(nbytes: int, device, tag=None):
+    """scratch for one operator call; `tag`: a separate buffer (for scratch that outlives the call, see
+    functional.LatentBlockFn.backward)"""
     key = (device.index if device.index is not None else torch.cuda.current_device(),
-           torch.cuda.current_stream(device).cuda_stream)
+           torch.cuda.current_stream(device).cuda_stream, tag)
     buf = _ws.get(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(max(int(nbytes * 1.25), 1 << 20), dtype=torch.uint8, device=device)

@@ -5,6 +5,7 @@ autograd graph.  Saved-for-backward state is an opaque byte buffer whose layout 
 library knows (pio_*_saved_bytes).
 """
 import ctypes
+import os
 import threading
 import weakref
 from ctypes import byref
@@ -283,8 +284,49 @@ def _dst_address(p):
     return None if hit is None else hit[0]
 
 
+def _flush_deferred():
+    """An operator left parameter-gradient kernels running on the side streams (LatentBlockFn.backward): make the current
+    stream wait for them, release what they read, and only now tell the owners that those destinations are written."""
+    d = getattr(_PASS._tls, "deferred", None)
+    if not d:
+        return
+    _PASS._tls.deferred = None
+    for dev, entries, _keepalive in d:
+        N.check(N.lib().pio_side_join(N.stream_ptr(dev)), "pio_side_join")
+        for owner, k in entries:
+            owner._written(k)
+
+
+def _defer(dev, keepalive):
+    """Move this operator's write reports (and the buffers its side-stream kernels still read) to the deferred list.
+    False if nobody would flush them (not inside a backward pass): the caller must not defer then."""
+    if getattr(_PASS._tls, "deferred", None) is None:
+        _PASS._tls.deferred = []
+    t = _touched_list()
+    _PASS._tls.deferred.append((dev, list(t), keepalive))
+    t.clear()
+    _PASS._tls.just_deferred = True  # (the _after_op that ends THIS operator must not flush it again)
+    return True
+
+
+def _defer_probe():
+    """True inside a backward pass (where an end-of-pass callback can be queued): registers the flush once per pass."""
+    if getattr(_PASS._tls, "deferred", None) is not None:
+        return True
+    try:
+        torch.autograd.Variable._execution_engine.queue_callback(_flush_deferred)
+    except RuntimeError:
+        return False
+    _PASS._tls.deferred = []
+    return True
+
+
 def _after_op():
     """end of a backward operator: tell the owners which destinations are now written"""
+    if getattr(_PASS._tls, "just_deferred", False):
+        _PASS._tls.just_deferred = False
+        return
+    _flush_deferred()
     t = _touched_list()
     if t:
         done = list(t)
@@ -832,14 +874,32 @@ class LatentBlockFn(torch.autograd.Function):
         layers, b, n, c, heads, mode, drop = ctx.meta
         dy = _c(dy)
         L = N.lib()
-        grads, accf = _grads_like(params, mode, ctx.needs_input_grad[4:])
+        _flush_deferred()  # (an earlier block's deferred kernels read the workspace this call is about to reuse)
+        needs = ctx.needs_input_grad[4:]
+        grads, accf = _grads_like(params, mode, needs)
         dx = torch.empty_like(x)
         attn, mlp = ctx.wstructs
         attn_g, mlp_g, _ = LatentBlockFn._structs(grads, layers, c)
-        ws = N.workspace(L.pio_latent_block_ws_bytes(layers, b, n, c, heads, mode), x.device)
-        N.check(L.pio_latent_block_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), attn, mlp, ctx.saved_buf.data_ptr(), attn_g,
-                                       mlp_g, accf, layers, b, n, c, heads, _dref(drop), mode, ws.data_ptr(), ws.numel(),
-                                       N.stream_ptr(x.device)), "pio_latent_block_bwd")
+        # When every parameter gradient goes straight to a registered destination (FlatGradients), nothing reads them
+        # until the owner is told: the operator may then leave its parameter-gradient kernels running on the side streams
+        # while the next backward operator starts (pio_set_side_join_deferred).  Its scratch, the saved state and the
+        # inputs stay alive until the join.
+        defer = (mode == N.MODE_BF16 and accf == 2 and os.environ.get("PIO_NO_DEFERRED_JOIN") is None and
+                 all(_dst_address(p) is not None for p, need in zip(params, needs) if need and p is not None))
+        ws = N.workspace(L.pio_latent_block_ws_bytes(layers, b, n, c, heads, mode), x.device, "latent_bwd" if defer else None)
+        if defer:
+            defer = _defer_probe()
+        if defer:
+            L.pio_set_side_join_deferred(1)
+        try:
+            N.check(L.pio_latent_block_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), attn, mlp, ctx.saved_buf.data_ptr(), attn_g,
+                                           mlp_g, accf, layers, b, n, c, heads, _dref(drop), mode, ws.data_ptr(), ws.numel(),
+                                           N.stream_ptr(x.device)), "pio_latent_block_bwd")
+        finally:
+            if defer:
+                L.pio_set_side_join_deferred(0)
+        if defer:
+            _defer(x.device, (ws, ctx.saved_buf, x, dy, params, grads))
         ctx.saved_buf = None
         return _out(dx, None, None, None, *grads)
 
