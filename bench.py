@@ -268,86 +268,118 @@ def roofline_vocab_head(mode, pk, reps=10):
 
 
 def roofline_dominant_kernel(mode, pk, reps=20):
-    """The kernel with the largest time share inside the step: gemm_tc_kernel on the products of the 18 latent
-    self-attention layers and their MLPs, m x n x k = 4096 x 256 x 256 per product (B*N = 64*64 rows, C = 256) —
-    forward X W^T (+bias, bf16 out), backward dX = dY W (fp32 out) and dW = dY^T X (k = 4096, fp32 atomics), the three
-    flavours the step launches ~240 times.  Algorithmic work 2*m*n*k = 0.537 GFLOP per launch (SURVEY section 8d);
-    time = CUDA events on the launching stream around each launch with a 256 MB L2 flush between launches (`cold`),
-    and back to back without a flush (`warm`, the state inside the step, where the 2 MB operands stay in L2).
-    `share_of_step` is read from the committed timeline summary of the graph replay."""
-    import ctypes
+    """The kernel with the largest time share inside the step (profiles/r02_dominant_kernel.json, from the CUPTI timeline
+    of a graph replay): latent_block_bwd_cluster_kernel, the fused backward input-gradient chain of one latent block
+    (6 layers, 64 x 64 rows, C = 256, 4 heads), three launches per step; next to it the forward cluster kernel
+    (latent_block_fwd_cluster_kernel).  Algorithmic work per row and layer (SURVEY section 8d counts 2*m*n*k per
+    product): backward chain dG + dN2 + dO (3 x 2 C^2) + dN1 (2 C 3C) + attention (S, dP, dQ, dK, dV: 5 x 2 n dh H) =
+    950 272 FLOP; forward QKV (2 C 3C) + out-projection (2 C^2) + MLP (4 C^2) + attention (2 x 2 n dh H) = 851 968 FLOP.
+    Time = CUDA events on the launching stream around single launches through the C ABI (pio_latent_block_fwd /
+    pio_latent_block_bwd with the parameter-gradient kernels switched off), a 256 MB L2 flush before each (`cold`), and
+    back to back (`warm`, close to the in-step state)."""
     from perceiver import _native as N
+    from perceiver import functional as F
+    from perceiver.model import self_attention_block
     if mode != 1:
         return None
     dev = torch.device("cuda", torch.cuda.current_device())
     L = N.lib()
     st = N.stream_ptr(dev)
-    rows, c = CFG["batch"] * CFG["latent"][0], CFG["latent"][1]
+    batch, (n, c), layers, heads = CFG["batch"], CFG["latent"], CFG["sa"], CFG["heads"][1]
+    rows = batch * n
+    block = self_attention_block(layers, c, heads, 0.0).to(dev)
+    params = []
+    for layer in block:
+        params.extend(layer[0].module._params())
+        params.extend(layer[1].module._params())
+    params = [p.detach().contiguous() for p in params]
+    grads = [torch.zeros_like(p) for p in params]
+    x = torch.randn(batch, n, c, device=dev)
+    dy = torch.randn(batch, n, c, device=dev)
+    y = torch.empty_like(x)
+    dx = torch.empty_like(x)
+    attn, mlp, keep = F.LatentBlockFn._structs(params, layers, c, N.MODE_BF16)
+    attn_g, mlp_g, keep_g = F.LatentBlockFn._structs(grads, layers, c)
+    saved = torch.zeros(L.pio_latent_block_saved_bytes(layers, batch, n, c, heads, N.MODE_BF16), dtype=torch.uint8, device=dev)
+    ws = torch.empty(L.pio_latent_block_ws_bytes(layers, batch, n, c, heads, N.MODE_BF16), dtype=torch.uint8, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    x = torch.randn(rows, c, device=dev).to(torch.bfloat16)
-    w = (torch.randn(c, c, device=dev) * 0.05).to(torch.bfloat16)
-    dy = torch.randn(rows, c, device=dev).to(torch.bfloat16)
-    bias = torch.zeros(c, device=dev)
-    ws = torch.empty(16 << 20, dtype=torch.uint8, device=dev)
 
-    def desc(name):
-        d = N.GemmBf16Desc()
-        if name == "fwd":
-            out = torch.empty(rows, c, device=dev, dtype=torch.bfloat16)
-            d.a, d.b, d.m, d.n, d.k, d.lda, d.ldb, d.a_kmajor, d.b_kmajor = x.data_ptr(), w.data_ptr(), rows, c, c, c, c, 1, 1
-            d.c16, d.ldc16, d.bias = out.data_ptr(), c, bias.data_ptr()
-        elif name == "dX":
-            out = torch.empty(rows, c, device=dev)
-            d.a, d.b, d.m, d.n, d.k, d.lda, d.ldb, d.a_kmajor, d.b_kmajor = dy.data_ptr(), w.data_ptr(), rows, c, c, c, c, 1, 0
-            d.c32, d.ldc32 = out.data_ptr(), c
-        else:
-            out = torch.zeros(c, c, device=dev)
-            d.a, d.b, d.m, d.n, d.k, d.lda, d.ldb, d.a_kmajor, d.b_kmajor = dy.data_ptr(), x.data_ptr(), c, c, rows, c, c, 0, 0
-            d.c32, d.ldc32, d.accumulate = out.data_ptr(), c, 2
-        return d, out
+    def fwd():
+        N.check(L.pio_latent_block_fwd(x.data_ptr(), y.data_ptr(), attn, mlp, saved.data_ptr(), layers, batch, n, c, heads, None,
+                                       N.MODE_BF16, ws.data_ptr(), ws.numel(), st), "pio_latent_block_fwd")
 
-    cold, warm = {}, {}
-    for name in ("fwd", "dX", "dW"):
-        d, keep = desc(name)
-        ts = []
-        for i in range(reps + 3):
-            flush.zero_()
+    def bwd():
+        N.check(L.pio_latent_block_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), attn, mlp, saved.data_ptr(), attn_g, mlp_g, 2,
+                                       layers, batch, n, c, heads, None, N.MODE_BF16, ws.data_ptr(), ws.numel(), st),
+                "pio_latent_block_bwd")
+
+    old_env = os.environ.get("PIO_LATENT_BWD_CHAIN_ONLY")
+    os.environ["PIO_LATENT_BWD_CHAIN_ONLY"] = "1"
+    try:
+        c0 = L.pio_launch_count()
+        fwd()
+        one_fwd = L.pio_launch_count() - c0
+        c0 = L.pio_launch_count()
+        bwd()
+        one_bwd = L.pio_launch_count() - c0
+        torch.cuda.synchronize()
+        if one_fwd != 1 or one_bwd != 1:  # the fused kernels were not taken (shape / env): no single dominant launch to time
+            return {"kernel": "latent block cluster kernels", "unavailable": f"launches per call fwd {one_fwd} bwd {one_bwd}"}
+        cold, warm = {}, {}
+        for name, fn in (("bwd_chain", bwd), ("fwd", fwd)):
+            ts = []
+            for i in range(reps + 3):
+                flush.zero_()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                fn()
+                e1.record()
+                e1.synchronize()
+                if i >= 3:
+                    ts.append(e0.elapsed_time(e1))
+            cold[name] = sum(ts) / len(ts)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            for _ in range(3):
+                fn()
             e0.record()
-            N.check(L.pio_gemm_bf16(ctypes.byref(d), ws.data_ptr(), ws.numel(), st), "pio_gemm_bf16")
+            for _ in range(20):
+                fn()
             e1.record()
             e1.synchronize()
-            if i >= 3:
-                ts.append(e0.elapsed_time(e1))
-        cold[name] = sum(ts) / len(ts)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        for _ in range(3):
-            N.check(L.pio_gemm_bf16(ctypes.byref(d), ws.data_ptr(), ws.numel(), st), "pio_gemm_bf16")
-        e0.record()
-        for _ in range(50):
-            N.check(L.pio_gemm_bf16(ctypes.byref(d), ws.data_ptr(), ws.numel(), st), "pio_gemm_bf16")
-        e1.record()
-        e1.synchronize()
-        warm[name] = e0.elapsed_time(e1) / 50
-    flops_each = 2.0 * rows * c * c
-    achieved = flops_each * 3 / (sum(cold.values()) * 1e-3) / 1e12
-    achieved_warm = flops_each * 3 / (sum(warm.values()) * 1e-3) / 1e12
-    share, share_src = None, None
+            warm[name] = e0.elapsed_time(e1) / 20
+    finally:
+        if old_env is None:
+            os.environ.pop("PIO_LATENT_BWD_CHAIN_ONLY", None)
+        else:
+            os.environ["PIO_LATENT_BWD_CHAIN_ONLY"] = old_env
+    dh = c // heads
+    attn_unit = 2.0 * n * dh * heads
+    flops = {"bwd_chain": (3 * 2.0 * c * c + 2.0 * c * 3 * c + 5 * attn_unit) * rows * layers,
+             "fwd": (2.0 * c * 3 * c + 2.0 * c * c + 4.0 * c * c + 2 * attn_unit) * rows * layers}
+    achieved = flops["bwd_chain"] / (cold["bwd_chain"] * 1e-3) / 1e12
+    achieved_warm = flops["bwd_chain"] / (warm["bwd_chain"] * 1e-3) / 1e12
+    fwd_tf = flops["fwd"] / (warm["fwd"] * 1e-3) / 1e12
+    share, share_src, traffic = None, None, None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "r02_dominant_kernel.json")))
         share, share_src = tj.get("share_of_step"), tj.get("source")
         traffic = tj.get("dram_bytes_per_launch")
     except Exception:
-        traffic = None
-    return {"kernel": "gemm_tc_kernel (tcgen05 + TMA) at the latent-layer products 4096 x 256 x 256 (fwd / dX / dW)", "bound": "tensor",
-            "achieved": round(achieved, 2), "peak": pk["tflops"], "unit": "TFLOP/s", "frac": round(achieved / pk["tflops"], 5),
-            "traffic": traffic,
+        pass
+    return {"kernel": "latent_block_bwd_cluster_kernel (fused backward input-gradient chain of a 6-layer latent block, "
+                      "4-CTA clusters, tcgen05 + TMA + DSMEM), batch 64 x 64 latents x 256 channels",
+            "bound": "tensor", "achieved": round(achieved, 2), "peak": pk["tflops"], "unit": "TFLOP/s",
+            "frac": round(achieved / pk["tflops"], 5), "traffic": traffic,
             "achieved_warm_l2": round(achieved_warm, 2), "frac_warm_l2": round(achieved_warm / pk["tflops"], 5),
             "ms_per_launch": {k: round(t, 5) for k, t in cold.items()}, "ms_per_launch_warm_l2": {k: round(t, 5) for k, t in warm.items()},
-            "flops_per_launch": flops_each, "shape_mnk": [rows, c, c], "share_of_step": share, "share_source": share_src,
+            "flops_per_launch": flops["bwd_chain"], "share_of_step": share, "share_source": share_src,
             "peak_source": pk["source"] + " (burst)",
-            "note": "0.5 GFLOP per launch: launch / prologue / epilogue latency bound, nowhere near a roofline; the fused "
-                    "latent-block kernel (pio_latent_tc.cu) replaces these launches from 56 row tiles (batch 112) up"}
+            "forward_kernel": {"kernel": "latent_block_fwd_cluster_kernel", "flops_per_launch": flops["fwd"],
+                               "achieved_warm_l2": round(fwd_tf, 2), "frac_warm_l2": round(fwd_tf / pk["tflops"], 5)},
+            "note": "one launch = 6 layers x 32 row tiles on 128 SMs; the chain is a sequence of dependent phases per tile "
+                    "(4 operand exchanges over distributed shared memory per layer at ~20 B/clk per SM, thread = row "
+                    "element-wise phases, tcgen05 products of 128 x 64..256 x 64..256): latency and SM-to-SM bandwidth "
+                    "bound, not tensor-pipe bound — DESIGN.md section 3"}
 
 
 def reference_on_b200(steps=3, warmup=2):

@@ -68,12 +68,10 @@ struct LayerPtrs {
     const float* mlp_stats;  // (mean, rstd) per row
     const float* sa_stats;
     const float* lse;        // [sample][head][latent]
-    bf16* gn2;               // dN2, dN1 as bf16 [rows][C]
-    bf16* gn1;
 };
 
 enum InMap : int { IM_H1 = 0, IM_XMID, IM_XNEXT, IM_X, IM_QKV, IM_COUNT };
-enum OutMap : int { OM_GY = 0, OM_GH, OM_GMID, OM_GQKV, OM_COUNT };
+enum OutMap : int { OM_GY = 0, OM_GH, OM_GMID, OM_GQKV, OM_GN2, OM_GN1, OM_COUNT };
 
 struct Params {
     CUtensorMap w[PIO_LATENT_FUSED_MAX_LAYERS][4];  // W2, W1, Wo (256 x 256, boxes of 64 x 64), Wqkv (768 x 256, boxes of 64 columns x 16 rows)
@@ -106,8 +104,18 @@ __device__ int gb_trace_n[2];
             }                                                            \
         }                                                                \
     } while (0)
+__device__ unsigned long long gb_cta_time[4][1024];  // per CTA: kernel entry, after set-up, work done, exit (globaltimer, ns)
+#define BW_STAMP(i)                                                                        \
+    do {                                                                                   \
+        if (threadIdx.x == 0 && blockIdx.x < 1024) {                                       \
+            unsigned long long _t;                                                         \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_t));                         \
+            gb_cta_time[i][blockIdx.x] = _t;                                               \
+        }                                                                                  \
+    } while (0)
 #else
 #define BW_TRACE(who, tag) do { } while (0)
+#define BW_STAMP(i) do { } while (0)
 #endif
 __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
     asm volatile(
@@ -147,9 +155,12 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
     uint64_t* x_free = mma_done + 13;     // the element-wise warps have read sX
     uint64_t* q_free = mma_done + 14;     // the reduce-scatter's copies out of sQ / sK / sV have been received
     uint64_t* qs_free = mma_done + 15;    // the TMA stores of dQ / dK / dV have read sQ / sK / sV
-    uint32_t* tmem_slot = (uint32_t*)(mma_done + 16);
+    uint64_t* w2_full = mma_done + 16;    // the second half of the head's Wqkv rows has landed in sA (free after the dK / dV products)
+    uint64_t* sa_w_free = mma_done + 17;  // P | dS have been read: sA may take that half
+    uint32_t* tmem_slot = (uint32_t*)(mma_done + 18);
 
     pdl_trigger();
+    BW_STAMP(0);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int r = (int)cluster_rank();
     const int tile = blockIdx.x / R;
@@ -172,6 +183,8 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
         mbar_init(x_free, EW_WARPS);
         mbar_init(q_free, 1);
         mbar_init(qs_free, 1);
+        mbar_init(w2_full, 1);
+        mbar_init(sa_w_free, 1);
         fence_barrier_init();
     }
     if (warp == EW_WARPS + 1) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -187,6 +200,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
     const uint32_t T_S = tmem_base + 256;    // S (128 keys); later, with T_P, the 256-column partial of dN1
     const uint32_t T_P = tmem_base + 384;    // dP (128 keys)
     pdl_wait();
+    BW_STAMP(1);
 
     if (warp == EW_WARPS) {
         // ------------------------------------------------------------ TMA producer: weights
@@ -208,12 +222,22 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                         tma_load_2d(dst, &p.w[l][w], r * DH, a * 64, &full[prod % SLOTS]);
                         ++prod;
                     }
-                for (int kk = 0; kk < 12; ++kk) {  // Wqkv rows of head r (q, k, v), 16 at a time, all 256 columns
+                // Wqkv rows of head r (q, k, v), 16 at a time, all 256 columns (96 KB): the first six steps through the ring; the
+                // ring cannot hold the rest in flight (each refill is a ~2 K-cycle round trip: the product took 5.4 K cycles
+                // waiting for them), so the last six go to sA, which is idle from the dK / dV products to the reduce-scatter
+                for (int kk = 0; kk < 6; ++kk) {
                     uint8_t* dst = acquire();
                     const int row0 = (kk >> 2) * C + r * DH + (kk & 3) * 16;
 #pragma unroll
                     for (int j = 0; j < 4; ++j) tma_load_2d(dst + j * 2048, &p.w[l][3], j * 64, row0, &full[prod % SLOTS]);
                     ++prod;
+                }
+                mbar_wait(sa_w_free, (uint32_t)(p.layers - 1 - l) & 1u);
+                mbar_expect_tx(w2_full, 6 * SLOT_BYTES);
+                for (int kk = 6; kk < 12; ++kk) {
+                    const int row0 = (kk >> 2) * C + r * DH + (kk & 3) * 16;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) tma_load_2d(sA + (kk - 6) * SLOT_BYTES + j * 2048, &p.w[l][3], j * 64, row0, w2_full);
                 }
             }
         }
@@ -355,17 +379,24 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                               t > 0 ? 1u : 0u);
                 umma_commit(mma_done);
                 umma_commit(do_free);
+                umma_commit(sa_w_free);
                 wait_ew();  // dQ | dK | dV as bf16 in sQ | sK | sV
                 lb::tma_store_3d(&p.out[OM_GQKV], sQ, r * DH, row0, l);
                 lb::tma_store_3d(&p.out[OM_GQKV], sK, C + r * DH, row0, l);
                 lb::tma_store_3d(&p.out[OM_GQKV], sV, 2 * C + r * DH, row0, l);
                 lb::tma_store_commit();
-                for (int kk = 0; kk < 12; ++kk) {  // partial of dN1 (all 256 columns) = [dQ | dK | dV] Wqkv[rows of head r, :]
+                for (int kk = 0; kk < 6; ++kk) {  // partial of dN1 (all 256 columns) = [dQ | dK | dV] Wqkv[rows of head r, :]
                     const uint32_t b = ring_wait();
                     umma_bf16(T_S, make_smem_desc(q_addr + (kk >> 2) * ATOM + (kk & 3) * 32, 16, 1024), make_smem_desc(b, 2048, 1024), idesc_part,
                               kk > 0 ? 1u : 0u);
                     ring_release();
                 }
+                mbar_wait(w2_full, (uint32_t)(p.layers - 1 - l) & 1u);
+                tc_fence_after();
+#pragma unroll
+                for (int kk = 6; kk < 12; ++kk)
+                    umma_bf16(T_S, make_smem_desc(q_addr + (kk >> 2) * ATOM + (kk & 3) * 32, 16, 1024),
+                              make_smem_desc(a_addr + (kk - 6) * SLOT_BYTES, 2048, 1024), idesc_part, 1u);
                 umma_commit(mma_done);
                 lb::tma_store_wait_read();
                 lb::mbar_arrive(qs_free);
@@ -477,24 +508,57 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 a += o.x; b += o.y;
             }
         };
-        // LayerNorm backward of this thread's 32 columns: dn = gradient of the normalised output, xs = the LayerNorm input
-        // (fp32, in sX), stats = (mean, rstd) of the row; adds the result to the gradient stream in T_D and returns the new
-        // stream values in v.  dn is also stored as bf16 (dgamma / dbeta are formed from it by a kernel of their own).
-        auto ln_backward = [&](float (&dn)[32], const float* gamma, const float* stats, bf16* dn_out, float (&v)[32]) {
-            const float2 ms = row_ok ? __ldg(reinterpret_cast<const float2*>(stats) + grow) : make_float2(0.f, 0.f);
-            if (row_ok) lb::store32_bf16_global(dn_out + grow * C + gcol, dn);
-            float gm[32];
+        // LayerNorm backward of this thread's 32 columns: dn = gradient of the normalised output, the LayerNorm input (fp32)
+        // in sX, ms = (mean, rstd) of the row, gm = the affine scale (both loaded before the wait for the product: they
+        // come from L2); adds the result to the gradient stream in T_D and returns the new stream values in v.  dn also
+        // leaves as bf16 (dgamma / dbeta are formed from it by a kernel of their own): staged in the warp's own rows of
+        // sX once it has read them (thread = row is the wrong shape for global stores), stored by TMA; the buffer is
+        // released to the loader one phase later, when that store has read it (release_x).
+        bool x_pending = false;
+        auto release_x = [&]() {
+            if (x_pending) {
+                if (lane == 0) {
+                    lb::tma_store_wait_read();
+                    lb::mbar_arrive(x_free);
+                }
+                x_pending = false;
+            }
+        };
+        auto ln_prefetch = [&](const float* gamma, const float* stats, float (&gm)[32], float2& ms) {
+            ms = row_ok ? __ldg(reinterpret_cast<const float2*>(stats) + grow) : make_float2(0.f, 0.f);
 #pragma unroll
             for (int d = 0; d < 32; d += 4) {
                 const float4 t = __ldg(reinterpret_cast<const float4*>(gamma + gcol + d));
                 gm[d] = t.x; gm[d + 1] = t.y; gm[d + 2] = t.z; gm[d + 3] = t.w;
             }
+        };
+        auto ln_backward = [&](float (&dn)[32], const float (&gm)[32], const float2 ms, int which, int l, float (&v)[32]) {
             mbar_wait(x_full, x_phase);
             x_phase ^= 1u;
             float xh[32];
+            uint8_t* mine = sX + cg * ATOM + q * 4096;  // this warp's 32 rows of its 32-column box
             lb::load_row_f32_smem(sX + cg * ATOM, row, xh);
             __syncwarp();
-            if (lane == 0) lb::mbar_arrive(x_free);
+            {   // dn as bf16, packed 32 rows x 64 bytes, over the rows just read
+                uint8_t* prow = mine + lane * 64;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    uint32_t u[4];
+#pragma unroll
+                    for (int e2 = 0; e2 < 4; ++e2) {
+                        __nv_bfloat162 h2 = __floats2bfloat162_rn(dn[i * 8 + 2 * e2], dn[i * 8 + 2 * e2 + 1]);
+                        u[e2] = *reinterpret_cast<uint32_t*>(&h2);
+                    }
+                    *reinterpret_cast<uint4*>(prow + i * 16) = make_uint4(u[0], u[1], u[2], u[3]);
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    lb::tma_store_3d(&p.out[which], mine, gcol, tile * ROWS + q * 32, l);
+                    lb::tma_store_commit();
+                }
+                x_pending = true;
+            }
             float s1 = 0.f, s2 = 0.f;
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
@@ -538,6 +602,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
 
             // ---- dH = dG * gelu'(h) -> gather 2
             wait_mma();
+            release_x();  // (the previous layer's x rows served as staging for dN1)
             free_arrive();
             {
                 float t[32], h1[32];
@@ -551,12 +616,15 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             }
 
             // ---- g_mid = g + LayerNorm2-backward(dN2) -> tensor memory, gather 3
+            float gm[32];
+            float2 ms;
+            ln_prefetch(L.ln2_w, L.mlp_stats, gm, ms);
             wait_mma();
             free_arrive();
             {
                 float dn[32];
                 lb::ld_chunk(T_N + lane_off + (uint32_t)lcol, dn);
-                ln_backward(dn, L.ln2_w, L.mlp_stats, L.gn2, v);
+                ln_backward(dn, gm, ms, OM_GN2, l, v);
                 lb::st_chunk(T_D + lane_off + (uint32_t)lcol, v);
                 tmem_st_wait();
                 send_operand(v, true, false);
@@ -564,6 +632,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
 
             // ---- dO_r -> bf16 operand tile (over gelu')
             wait_mma();
+            release_x();  // (x_mid's rows served as staging for dN2: its store has long read them)
             {
                 float t[32];
                 lb::ld_chunk(T_O + lane_off + (uint32_t)lcol, t);
@@ -619,7 +688,6 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
 
             // ---- dQ | dK | dV -> bf16 tiles over Q | K | V: operand of the dN1 partial, saved for dWqkv
             wait_mma();
-            free_arrive();  // (sA = P | dS is free from here on: gather 3 counts as consumed only now)
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
                 const int chunk = cg * 3 + j;  // chunks 0, 1 = dQ (T_G), 2, 3 = dK (T_N), 4, 5 = dV (T_O): contiguous columns
@@ -630,7 +698,9 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             signal();
 
             // ---- reduce-scatter of the four dN1 partials, LayerNorm1-backward -> g for the next (earlier) layer
+            ln_prefetch(L.ln1_w, L.sa_stats, gm, ms);
             wait_mma();
+            free_arrive();  // sA (P | dS, then the second half of the Wqkv rows) is free from here on: gather 3 counts as consumed only now
             mbar_wait(qs_free, qs_phase);  // the saved copies of dQ | dK | dV have left their tiles: staging for the foreign slices
             qs_phase ^= 1u;
             wait_peers_free(false);
@@ -662,7 +732,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 }
                 bar_ew();       // every warp of the CTA has read the received slices:
                 free_arrive();  // the reduce-scatter counts as consumed
-                ln_backward(dn, L.ln1_w, L.sa_stats, L.gn1, v);
+                ln_backward(dn, gm, ms, OM_GN1, l, v);
                 if (l > 0) {
                     lb::st_chunk(T_D + lane_off + (uint32_t)lcol, v);
                     tmem_st_wait();
@@ -671,19 +741,28 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 }
             }
         }
+        if (lane == 0) lb::tma_store_wait_all();
+        __syncwarp();
         tc_fence_before();
     }
     __syncthreads();
+    BW_STAMP(2);
     cluster_sync_all();
     if (warp == EW_WARPS + 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, TMEM_COLS);
     }
+    BW_STAMP(3);
 }
 
 }  // namespace lbb
 
 #ifdef PIO_LB_TRACE
+extern "C" int pio_debug_lbb_cta_times(unsigned long long* out, int ctas) {
+    cudaMemcpyFromSymbol(out, lbb::gb_cta_time, sizeof(unsigned long long) * 4 * 1024);
+    return ctas;
+}
+
 extern "C" int pio_debug_lbb_trace(long long* out, int max_pairs, int who, int reset) {
     int n = 0;
     cudaMemcpyFromSymbol(&n, lbb::gb_trace_n, sizeof(int), who * sizeof(int));
@@ -806,7 +885,6 @@ int latent_block_bwd_cluster(const float* dy, const float* x, float* dx, const L
         PIO_TRY(make_tmap_bf16(&p.w[l][3], s.wqkv, 3 * C, C, C, 16));
         LayerPtrs& d = p.layer[l];
         d.ln2_w = s.ln2_w; d.ln1_w = s.ln1_w; d.mlp_stats = s.mlp_stats; d.sa_stats = s.sa_stats; d.lse = s.lse;
-        d.gn2 = (bf16*)s.gn2; d.gn1 = (bf16*)s.gn1;
     }
     const LatentBwdLayer& f0 = layers[0];
     const LatentBwdLayer& f1 = layers[nlayers > 1 ? 1 : 0];
@@ -827,6 +905,8 @@ int latent_block_bwd_cluster(const float* dy, const float* x, float* dx, const L
     PIO_TRY(make_out_map(&p.out[OM_GH], false, f0.gh16, C, rows, nlayers, C * 2, stride_of(f0.gh16, f1.gh16), 64, ROWS));
     PIO_TRY(make_out_map(&p.out[OM_GMID], false, f0.gmid16, C, rows, nlayers, C * 2, stride_of(f0.gmid16, f1.gmid16), 64, ROWS));
     PIO_TRY(make_out_map(&p.out[OM_GQKV], false, f0.gqkv16, 3 * C, rows, nlayers, 3 * C * 2, stride_of(f0.gqkv16, f1.gqkv16), 64, ROWS));
+    PIO_TRY(make_out_map(&p.out[OM_GN2], false, f0.gn2, C, rows, nlayers, C * 2, stride_of(f0.gn2, f1.gn2), 32, 32, false));
+    PIO_TRY(make_out_map(&p.out[OM_GN1], false, f0.gn1, C, rows, nlayers, C * 2, stride_of(f0.gn1, f1.gn1), 32, 32, false));
     p.dy = dy;
     p.dx = dx;
     p.layers = nlayers;

@@ -189,7 +189,7 @@ __device__ __forceinline__ void bulk_copy_to_peer(uint32_t dst_cluster, uint32_t
 
 // (cols, rows, layers) tensor map with byte strides (pitch, layer_stride); box = box_cols x box_rows x 1, 128-byte swizzle
 inline int make_out_map(CUtensorMap* map, bool f32, const void* base, int64_t cols, int64_t rows, int64_t nl, int64_t pitch,
-                        int64_t layer_stride, int box_cols, int box_rows) {
+                        int64_t layer_stride, int box_cols, int box_rows, bool swizzle = true) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) {
         set_error("cuTensorMapEncodeTiled entry point not available from the driver");
@@ -203,8 +203,8 @@ inline int make_out_map(CUtensorMap* map, bool f32, const void* base, int64_t co
     cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1u};
     cuuint32_t estr[3] = {1u, 1u, 1u};
     CUresult r = fn(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim,
-                    gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                    CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled (latent block output) failed with CUresult %d", (int)r);
         return PIO_ERR_CUDA;

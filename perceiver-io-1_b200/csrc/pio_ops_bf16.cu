@@ -657,6 +657,10 @@ static int latent_block_bwd_fused(Ctx& c, Side& side, const float* dy, const flo
         flip ^= 1;
         hi = lo;
     }
+    if (getenv("PIO_LATENT_BWD_CHAIN_ONLY") != nullptr) {  // measurement hook (bench.py times the chain kernel alone)
+        c.W.off = mark;
+        return PIO_OK;
+    }
     // parameter gradients: per (up to 8) layers one batched weight-gradient launch (bias gradients ride on it) and one
     // launch for the LayerNorm parameter gradients, on the two side streams
     PIO_TRY(side.fork());

@@ -49,6 +49,18 @@ def main():
         L.pio_debug_lbb_trace(None, 0, 0, 1)
         y.backward(dy)
         torch.cuda.synchronize()
+    L.pio_debug_lbb_cta_times.restype = ctypes.c_int
+    L.pio_debug_lbb_cta_times.argtypes = [ctypes.c_void_p, ctypes.c_int]
+    tb = (ctypes.c_ulonglong * (4 * 1024))()
+    L.pio_debug_lbb_cta_times(tb, 1024)
+    ctas = 4 * ((batch * n + 127) // 128)
+    st = [[tb[i * 1024 + c] for c in range(ctas)] for i in range(4)]
+    base = min(st[0])
+    names = ["kernel entry", "set-up done", "work done", "exit"]
+    print(f"per-CTA wall clock (ns since the first CTA entered), {ctas} CTAs:")
+    for i in range(4):
+        v = [x - base for x in st[i]]
+        print(f"  {names[i]:12s} min {min(v):7d}  median {sorted(v)[len(v) // 2]:7d}  max {max(v):7d}")
     MAXP = 8192
     ev = []
     for who in (0, 1):
