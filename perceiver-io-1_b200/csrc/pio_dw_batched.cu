@@ -49,12 +49,19 @@ struct Batch {
     unsigned char tile_prob[MAX_TILES];
     unsigned char tile_m[MAX_TILES];
     int num_kb, kb_per_split;
+    const int* dyn_rows;  // device-side count of live rows (the contraction then ends at its next multiple of 64), or null
+    int dyn_off;
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+// A_MN = true: the weight-gradient form above (A = dY^T, the contraction over rows, the device-side count bounds K).
+// A_MN = false: C (m x 256, fp32, accumulated into) += A (m x k, bf16, K-major) B (k x 256, bf16, row-major) split over K —
+// the loss head's dx = dlogits W (m = labelled rows of a chunk, k = vocabulary): 128 x 256 tiles so that A is read once,
+// K split to fill the GPU; the device-side count then bounds M (tiles past it exit).
+template <bool A_MN>
 __global__ void __launch_bounds__(THREADS, 1) dw_batched_kernel(const __grid_constant__ Batch g) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -70,8 +77,20 @@ __global__ void __launch_bounds__(THREADS, 1) dw_batched_kernel(const __grid_con
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const Problem& P = g.prob[g.tile_prob[blockIdx.x]];
     const int m0 = (int)g.tile_m[blockIdx.x] * BM;
-    const int kb_begin = blockIdx.y * g.kb_per_split;
-    const int kb_end = min(g.num_kb, kb_begin + g.kb_per_split);
+    int num_kb = g.num_kb, kb_per_split = g.kb_per_split, m_live = P.m;
+    if (g.dyn_rows != nullptr) {
+        pdl_wait();
+        const int live = max(0, __ldg(g.dyn_rows) - g.dyn_off);
+        if (A_MN) {  // (block-uniform) the live rows are re-divided among the K splits
+            num_kb = min(num_kb, (live + BK - 1) / BK);
+            kb_per_split = (num_kb + (int)gridDim.y - 1) / (int)gridDim.y;
+        } else {
+            m_live = min(m_live, live);
+            if (m0 >= m_live) return;
+        }
+    }
+    const int kb_begin = blockIdx.y * kb_per_split;
+    const int kb_end = min(num_kb, kb_begin + kb_per_split);
     const int nkb = kb_end - kb_begin;
     if (nkb <= 0) return;
 
@@ -101,8 +120,12 @@ __global__ void __launch_bounds__(THREADS, 1) dw_batched_kernel(const __grid_con
                 mbar_wait(&empty_bar[s], ((uint32_t)(i / STAGES) & 1u) ^ 1u);
                 mbar_expect_tx(&full_bar[s], A_STAGE + B_STAGE);
                 const int k0 = (kb_begin + i) * BK;
+                if (A_MN) {
 #pragma unroll
-                for (int j = 0; j < BM / 64; ++j) tma_load_2d(sA + s * A_STAGE + j * 8192, &P.tmA, m0 + j * 64, k0, &full_bar[s]);
+                    for (int j = 0; j < BM / 64; ++j) tma_load_2d(sA + s * A_STAGE + j * 8192, &P.tmA, m0 + j * 64, k0, &full_bar[s]);
+                } else {
+                    tma_load_2d(sA + s * A_STAGE, &P.tmA, k0, m0, &full_bar[s]);
+                }
 #pragma unroll
                 for (int j = 0; j < BN / 64; ++j) tma_load_2d(sB + s * B_STAGE + j * 8192, &P.tmB, j * 64, k0, &full_bar[s]);
             }
@@ -110,8 +133,8 @@ __global__ void __launch_bounds__(THREADS, 1) dw_batched_kernel(const __grid_con
         __syncwarp();
     } else if (warp == 1) {
         if (lane == 0) {
-            const uint32_t idesc = make_idesc(BN, true, true);
-            const uint32_t idesc_b = make_idesc(16, true, true);
+            const uint32_t idesc = make_idesc(BN, A_MN, true);
+            const uint32_t idesc_b = make_idesc(16, A_MN, true);
             const uint32_t ones = smem_u32(sOnes);
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % STAGES;
@@ -120,9 +143,10 @@ __global__ void __launch_bounds__(THREADS, 1) dw_batched_kernel(const __grid_con
                 const uint32_t a_addr = smem_u32(sA + s * A_STAGE), b_addr = smem_u32(sB + s * B_STAGE);
 #pragma unroll
                 for (int k = 0; k < BK / 16; ++k) {
-                    const uint64_t da = make_smem_desc(a_addr + k * 2048, 8192, 1024);
+                    const uint64_t da = A_MN ? make_smem_desc(a_addr + k * 2048, 8192, 1024) : make_smem_desc(a_addr + k * 32, 16, 1024);
                     umma_bf16(tmem_base, da, make_smem_desc(b_addr + k * 2048, 8192, 1024), idesc, (i > 0 || k > 0) ? 1u : 0u);
-                    umma_bf16(tmem_base + BN, da, make_smem_desc(ones + k * 2048, 8192, 1024), idesc_b, (i > 0 || k > 0) ? 1u : 0u);
+                    if (A_MN && P.db != nullptr)
+                        umma_bf16(tmem_base + BN, da, make_smem_desc(ones + k * 2048, 8192, 1024), idesc_b, (i > 0 || k > 0) ? 1u : 0u);
                 }
                 umma_commit(&empty_bar[s]);
             }
@@ -146,7 +170,7 @@ __global__ void __launch_bounds__(THREADS, 1) dw_batched_kernel(const __grid_con
                 *reinterpret_cast<float4*>(stile + lane * PITCH + c0 + j) =
                     make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
         }
-        if (half == 0 && P.db != nullptr) {  // the tile's bias gradient: every one of the 16 extra columns holds it
+        if (A_MN && half == 0 && P.db != nullptr) {  // the tile's bias gradient: every one of the 16 extra columns holds it
             uint32_t r[32];
             tmem_ld32(tmem_base + lane_off + (uint32_t)BN, r);
             tmem_ld_wait();
@@ -154,7 +178,7 @@ __global__ void __launch_bounds__(THREADS, 1) dw_batched_kernel(const __grid_con
             if (m < P.m) atomicAdd(P.db + m, __uint_as_float(r[0]));
         }
         __syncwarp();
-        const int rows_here = min(32, P.m - (m0 + q * 32));
+        const int rows_here = min(32, m_live - (m0 + q * 32));
         for (int rr = 0; rr < rows_here; ++rr) {
             const float4 v = *reinterpret_cast<const float4*>(stile + rr * PITCH + lane * 4);
             red_add_v4(P.dw + (int64_t)(m0 + q * 32 + rr) * BN + half * 128 + lane * 4, v.x, v.y, v.z, v.w);
@@ -171,8 +195,9 @@ __global__ void __launch_bounds__(THREADS, 1) dw_batched_kernel(const __grid_con
 }  // namespace dwb
 
 // items[i]: dw (m x 256, row-major, accumulated into), db (m, accumulated into; may be null), dy16 [rows][m] (pitch lddy),
-// x16 [rows][256] (pitch ldx)
-int dw_batched(const DwBatchItem* items, int count, int64_t rows, cudaStream_t st) {
+// x16 [rows][256] (pitch ldx).  dyn_rows (device memory, nullable): only the first *dyn_rows - dyn_off rows are live; both
+// operands must be zero from there to the next multiple of 64 rows.
+int dw_batched(const DwBatchItem* items, int count, int64_t rows, cudaStream_t st, const int* dyn_rows, int dyn_off) {
     using namespace dwb;
     PIO_CHECK_ARG(items && count >= 1 && count <= MAX_PROB && rows > 0, "dw_batched: bad arguments (count %d)", count);
     static_assert(sizeof(Batch) <= 32000, "dw_batched: the problem table must fit the kernel parameter space");
@@ -180,7 +205,7 @@ int dw_batched(const DwBatchItem* items, int count, int64_t rows, cudaStream_t s
     int tiles = 0;
     for (int i = 0; i < count; ++i) {
         const DwBatchItem& it = items[i];
-        PIO_CHECK_ARG(it.dy16 && it.x16 && it.dw && it.m > 0 && it.m % 8 == 0 && it.n == BN && (((uintptr_t)it.dw) & 15) == 0,
+        PIO_CHECK_ARG(it.dy16 && it.x16 && it.dw && it.m > 0 && it.n == BN && (((uintptr_t)it.dw) & 15) == 0,
                       "dw_batched: item %d not supported (m %d n %d)", i, it.m, it.n);
         PIO_TRY(make_tmap_bf16(&g.prob[i].tmA, it.dy16, rows, it.m, it.lddy, 64));
         PIO_TRY(make_tmap_bf16(&g.prob[i].tmB, it.x16, rows, BN, it.ldx, 64));
@@ -188,12 +213,14 @@ int dw_batched(const DwBatchItem* items, int count, int64_t rows, cudaStream_t s
         g.prob[i].db = it.db;
         g.prob[i].m = it.m;
         for (int t = 0; t < (int)cdiv(it.m, BM); ++t) {
-            PIO_CHECK_ARG(tiles < MAX_TILES, "dw_batched: more than %d output tiles", MAX_TILES);
+            PIO_CHECK_ARG(tiles < MAX_TILES && t < 256, "dw_batched: more than %d output tiles", MAX_TILES);
             g.tile_prob[tiles] = (unsigned char)i;
             g.tile_m[tiles] = (unsigned char)t;
             ++tiles;
         }
     }
+    g.dyn_rows = dyn_rows;
+    g.dyn_off = dyn_off;
     g.num_kb = (int)cdiv(rows, (int64_t)BK);
     const int splits = std::max(1, std::min(g.num_kb, num_sms() / tiles));
     g.kb_per_split = (int)cdiv(g.num_kb, splits);
@@ -202,10 +229,51 @@ int dw_batched(const DwBatchItem* items, int count, int64_t rows, cudaStream_t s
     PIO_CUDA(cudaGetDevice(&dev));
     static std::atomic<bool> configured[64];
     if (dev >= 0 && dev < 64 && !configured[dev].load()) {
-        PIO_CUDA(cudaFuncSetAttribute(dw_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+        PIO_CUDA(cudaFuncSetAttribute(dw_batched_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+        PIO_CUDA(cudaFuncSetAttribute(dw_batched_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
         configured[dev].store(true);
     }
-    PIO_CUDA(launch_pdl(dw_batched_kernel, dim3((unsigned)tiles, (unsigned)used), dim3(THREADS), SMEM_BYTES, st, g));
+    PIO_CUDA(launch_pdl(dw_batched_kernel<true>, dim3((unsigned)tiles, (unsigned)used), dim3(THREADS), SMEM_BYTES, st, g));
+    count_launch();
+    return PIO_OK;
+}
+
+// c32 (m x 256, fp32, row-major, ADDED into: zero-fill it first) += a16 (m x k, bf16, pitch lda) b16 (k x 256, bf16, pitch ldb),
+// split over K into one wave of 128 x 256 tiles; dyn_rows (device memory, nullable): only the first *dyn_rows - dyn_off rows
+// of a / c are live.
+bool xw_splitk_supported(int64_t m, int64_t n, int64_t k, int64_t lda, int64_t ldb) {
+    return n == dwb::BN && m > 0 && cdiv(m, (int64_t)dwb::BM) <= dwb::MAX_TILES && k > 0 && lda % 8 == 0 && ldb % 8 == 0;
+}
+int xw_splitk(const void* a16, int64_t lda, const void* b16, int64_t ldb, float* c32, int64_t m, int64_t k, cudaStream_t st,
+              const int* dyn_rows, int dyn_off) {
+    using namespace dwb;
+    PIO_CHECK_ARG(a16 && b16 && c32 && xw_splitk_supported(m, BN, k, lda, ldb) && (((uintptr_t)c32) & 15) == 0, "xw_splitk: bad arguments");
+    Batch g{};
+    PIO_TRY(make_tmap_bf16(&g.prob[0].tmA, a16, m, k, lda, BM));
+    PIO_TRY(make_tmap_bf16(&g.prob[0].tmB, b16, k, BN, ldb, 64));
+    g.prob[0].dw = c32;
+    g.prob[0].db = nullptr;
+    g.prob[0].m = (int)m;
+    const int tiles = (int)cdiv(m, (int64_t)BM);
+    for (int t = 0; t < tiles; ++t) {
+        g.tile_prob[t] = 0;
+        g.tile_m[t] = (unsigned char)t;
+    }
+    g.dyn_rows = dyn_rows;
+    g.dyn_off = dyn_off;
+    g.num_kb = (int)cdiv(k, (int64_t)BK);
+    const int splits = std::max(1, std::min(g.num_kb, num_sms() / tiles));
+    g.kb_per_split = (int)cdiv(g.num_kb, splits);
+    const int used = (int)cdiv(g.num_kb, g.kb_per_split);
+    int dev = 0;
+    PIO_CUDA(cudaGetDevice(&dev));
+    static std::atomic<bool> configured[64];
+    if (dev >= 0 && dev < 64 && !configured[dev].load()) {
+        PIO_CUDA(cudaFuncSetAttribute(dw_batched_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+        PIO_CUDA(cudaFuncSetAttribute(dw_batched_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+        configured[dev].store(true);
+    }
+    PIO_CUDA(launch_pdl(dw_batched_kernel<false>, dim3((unsigned)tiles, (unsigned)used), dim3(THREADS), SMEM_BYTES, st, g));
     count_launch();
     return PIO_OK;
 }

@@ -1161,17 +1161,27 @@ int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, 
             ce_chunk_kernel<<<blocks, 256, 0, c.st>>>(lg16, cop, labels_c, out3, count, r0, nr, row_loss, classes);
         PIO_LAUNCH_CHECK();
         PIO_TRY(side.fork());
-        {  // dW += dlogits^T x   (contraction over the live rows)
-            pio_gemm_bf16_desc d{};
-            d.a = lg16; d.b = xc; d.m = classes; d.n = c_in; d.k = nr; d.lda = cop; d.ldb = cip; d.a_kmajor = 0; d.b_kmajor = 0;
-            d.c32 = dw; d.ldc32 = c_in; d.accumulate = 2;
-            d.dyn_rows = count; d.dyn_offset = r0; d.dyn_axis = 1;
-            PIO_TRY(gemm_bf16(&d, nullptr, 0, side.stream()));
+        if (c_in == 256 && side.active() && cdiv(classes, 128) <= 160) {
+            // dW += dlogits^T x and db += column sums of dlogits over the live rows, one launch (pio_dw_batched.cu)
+            DwBatchItem it{lg16, cop, (int)classes, xc, cip, c_in, dw, db};
+            PIO_TRY(dw_batched(&it, 1, nr, side.stream(), count, (int)r0));
+        } else {
+            {  // dW += dlogits^T x   (contraction over the live rows)
+                pio_gemm_bf16_desc d{};
+                d.a = lg16; d.b = xc; d.m = classes; d.n = c_in; d.k = nr; d.lda = cop; d.ldb = cip; d.a_kmajor = 0; d.b_kmajor = 0;
+                d.c32 = dw; d.ldc32 = c_in; d.accumulate = 2;
+                d.dyn_rows = count; d.dyn_offset = r0; d.dyn_axis = 1;
+                PIO_TRY(gemm_bf16(&d, nullptr, 0, side.stream()));
+            }
+            lce_colsum_kernel<<<dim3((unsigned)cdiv(cdiv(classes, 2), 128), (unsigned)cdiv(nr, 128)), 128, 0, side.stream2()>>>(
+                lg16, cop, db, count, r0, nr, classes);
+            PIO_LAUNCH_CHECK();
         }
-        lce_colsum_kernel<<<dim3((unsigned)cdiv(cdiv(classes, 2), 128), (unsigned)cdiv(nr, 128)), 128, 0, side.stream2()>>>(
-            lg16, cop, db, count, r0, nr, classes);
-        PIO_LAUNCH_CHECK();
-        {  // dx (compacted) = dlogits W
+        if (xw_splitk_supported(nr, c_in, classes, cop, cip)) {
+            // dx (compacted) = dlogits W: 128 x 256 tiles so that dlogits is read once, split over the vocabulary
+            PIO_CUDA(cudaMemsetAsync(dxc + r0 * c_in, 0, (size_t)nr * c_in * sizeof(float), c.st));
+            PIO_TRY(xw_splitk(lg16, cop, w16, cip, dxc + r0 * c_in, nr, classes, c.st, count, (int)r0));
+        } else {  // dx (compacted) = dlogits W
             pio_gemm_bf16_desc d{};
             d.a = lg16; d.b = w16; d.m = nr; d.n = c_in; d.k = classes; d.lda = cop; d.ldb = cip; d.a_kmajor = 1; d.b_kmajor = 0;
             d.c32 = dxc + r0 * c_in; d.ldc32 = c_in;

@@ -138,7 +138,10 @@ struct DwBatchItem {
     float* dw;
     float* db;
 };
-int dw_batched(const DwBatchItem* items, int count, int64_t rows, cudaStream_t st);
+int dw_batched(const DwBatchItem* items, int count, int64_t rows, cudaStream_t st, const int* dyn_rows = nullptr, int dyn_off = 0);
+bool xw_splitk_supported(int64_t m, int64_t n, int64_t k, int64_t lda, int64_t ldb);
+int xw_splitk(const void* a16, int64_t lda, const void* b16, int64_t ldb, float* c32, int64_t m, int64_t k, cudaStream_t st,
+              const int* dyn_rows = nullptr, int dyn_off = 0);
 // persistent vocabulary-logits product (pio_logits_tc.cu)
 bool logits_persistent_supported(int64_t m, int64_t n, int64_t k, int64_t lda, int64_t ldb, int64_t ldc);
 int logits_persistent(const void* a, int64_t lda, const void* w, int64_t ldb, const float* bias, void* c, int64_t ldc, int64_t m,
