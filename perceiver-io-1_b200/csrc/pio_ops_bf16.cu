@@ -279,8 +279,13 @@ int kv_project_fwd(Ctx& c, const float* x_kv, float* kv, const pio_attn_weights*
     PIO_TRY(need_mult8(e, "embed dim", "pio_kv_project_fwd"));
     KvSaved s(saved, rows, ckv);
     const int64_t ckp = pad8(ckv);
-    PIO_TRY(layernorm_fwd_bf16(x_kv, w->kv_ln_w, w->kv_ln_b, s.h0, ckp, s.stats, rows, ckv, LN_EPS, c.st));
     bf16* kv16 = reinterpret_cast<bf16*>(kv);  // bf16 mode: the kv tensor is bf16 (B, M, 2E)
+    if (packed16(w->wk, w->wv, e, ckp) && w->bv == w->bk + e && c.dyn == nullptr && ln_linear_supported(rows, 2 * e, ckv, ckp, 2 * e, ckp)) {
+        // kv_norm + K/V in-projection in one persistent kernel (pio_logits_tc.cu): x_kv is read once, the normalised operand
+        // goes straight into the product's shared-memory tile (its bf16 copy and the statistics are still saved)
+        return ln_linear(x_kv, w->kv_ln_w, w->kv_ln_b, LN_EPS, w->wk, ckp, w->bk, kv16, 2 * e, s.h0, ckp, s.stats, rows, 2 * e, c.st);
+    }
+    PIO_TRY(layernorm_fwd_bf16(x_kv, w->kv_ln_w, w->kv_ln_b, s.h0, ckp, s.stats, rows, ckv, LN_EPS, c.st));
     if (packed16(w->wk, w->wv, e, ckp) && w->bv == w->bk + e) {
         PIO_TRY(tc_xwT(c, s.h0, ckp, (const bf16*)w->wk, ckp, rows, 2 * e, ckv, nullptr, 0, kv16, 2 * e, w->bk, nullptr, 0, 0,
                        nullptr, 0));
