@@ -1617,9 +1617,13 @@ int decode_rows_bwd(Ctx& c, const float* dy, const void* kv, const int* idx, flo
     PIO_TRY(side.fork());
     PIO_TRY(tc_dW(c, dy16, e, s.o16, e, ag->wo, max_rows, e, e, acc, side.stream()));
     PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)aw->wo, e, max_rows, e, e, nullptr, 0, d_o16, e, 0, nullptr, 0, 0));
-    dr_bwd_pick(n, dh)<<<dim3((unsigned)heads, (unsigned)batch), DR_BWD_WARPS * 32, dr_smem_bytes(n, dh, DR_BWD_WARPS), c.st>>>(
-        s.q, (const bf16*)kv, s.o16, d_o16, s.lse, s.seg, c.dyn, dq16, (bf16*)dkv, l, n, e, heads, 1.0f / sqrtf((float)dh), max_rows);
-    PIO_LAUNCH_CHECK();
+    if (dr_attn_bwd_tc_supported(n, e, heads)) {  // tcgen05 version (pio_dr_attn_tc.cu): head size 64, up to 128 keys
+        PIO_TRY(dr_attn_bwd_tc(s.q, kv, d_o16, s.lse, s.seg, c.dyn, dq16, dkv, batch, n, e, heads, max_rows, c.st));
+    } else {
+        dr_bwd_pick(n, dh)<<<dim3((unsigned)heads, (unsigned)batch), DR_BWD_WARPS * 32, dr_smem_bytes(n, dh, DR_BWD_WARPS), c.st>>>(
+            s.q, (const bf16*)kv, s.o16, d_o16, s.lse, s.seg, c.dyn, dq16, (bf16*)dkv, l, n, e, heads, 1.0f / sqrtf((float)dh), max_rows);
+        PIO_LAUNCH_CHECK();
+    }
     PIO_TRY(side.fork());
     PIO_TRY(side_colsum(c, side, dq16, e, ag->bq, acc, max_rows, e));
     PIO_TRY(tc_dW(c, dq16, e, s.hq, e, ag->wq, max_rows, e, e, acc, side.stream()));

@@ -146,6 +146,9 @@ int xw_splitk(const void* a16, int64_t lda, const void* b16, int64_t ldb, float*
 bool logits_persistent_supported(int64_t m, int64_t n, int64_t k, int64_t lda, int64_t ldb, int64_t ldc);
 int logits_persistent(const void* a, int64_t lda, const void* w, int64_t ldb, const float* bias, void* c, int64_t ldc, int64_t m,
                       int64_t n, int64_t k, const int* dyn_rows, int dyn_off, cudaStream_t st);
+bool dr_attn_bwd_tc_supported(int n, int e, int heads);
+int dr_attn_bwd_tc(const void* q16, const void* kv, const void* do16, const float* lse, const int* seg, const int* count, void* dq16,
+                   void* dkv, int batch, int n, int e, int heads, int64_t max_rows, cudaStream_t st);
 bool ln_linear_supported(int64_t m, int64_t n, int64_t k, int64_t ldw, int64_t ldc, int64_t ldh);
 int ln_linear(const float* x, const float* gamma, const float* beta, float eps, const void* w, int64_t ldw, const float* bias, void* c,
               int64_t ldc, void* h0, int64_t ldh, float* stats, int64_t m, int64_t n, cudaStream_t st);
