@@ -271,6 +271,193 @@ __global__ void __launch_bounds__(THREADS, 1)
     }
 }
 
+// Forward: o16[i, h] = softmax(q_i K_h^T / 8) V_h and lse[i, h] for the labelled rows, same CTA layout: S = Q K^T on tcgen05,
+// thread = row softmax (the two threads of a row split the keys and exchange maximum and sum through shared memory),
+// P as a bf16 K-major tile, O = P V with V read MN-major in place.
+struct FwdParams {
+    float* lse;
+    const int* seg;
+    const int* count;
+    bf16* o16;  // (max_rows, e)
+    int n, e, heads;
+    int64_t max_rows;
+    float scale_log2e;
+};
+
+__global__ void __launch_bounds__(THREADS, 1)
+    dr_attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const FwdParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* sQ = smem;
+    uint8_t* sK = sQ + ATOM;
+    uint8_t* sV = sK + ATOM;
+    uint8_t* sP = sV + ATOM;  // [128 rows][128 keys] bf16 as two 64-key atoms
+    float* sRed = (float*)(sP + 2 * ATOM);  // [2 column halves][128 rows]
+    uint64_t* bars = (uint64_t*)(sRed + 2 * ROWS);
+    uint64_t* kv_full = bars;
+    uint64_t* q_full = bars + 1;
+    uint64_t* q_free = bars + 2;
+    uint64_t* mma_done = bars + 3;
+    uint64_t* ew_done = bars + 4;
+    uint32_t* tmem_slot = (uint32_t*)(bars + 5);
+
+    pdl_trigger();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int h = blockIdx.x, b = blockIdx.y;
+    pdl_wait();
+    const int cnt = __ldg(p.count);
+    if (h == 0 && b == 0) {  // rows between the count and the next multiple of 128: zero (operand padding of dWo = dY^T O)
+        const int64_t upto = min(p.max_rows, ((int64_t)cnt + 127) / 128 * 128);
+        for (int64_t t = (int64_t)cnt * p.e + threadIdx.x; t < upto * p.e; t += blockDim.x) p.o16[t] = __float2bfloat16(0.f);
+    }
+    const int lo = __ldg(p.seg + b), hi = __ldg(p.seg + b + 1);
+    const int tiles = (hi - lo + ROWS - 1) / ROWS;
+    const int n = p.n;
+    if (tiles <= 0) return;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmQ);
+        prefetch_tmap(&tmKV);
+        mbar_init(kv_full, 1);
+        mbar_init(q_full, 1);
+        mbar_init(q_free, 1);
+        mbar_init(mma_done, 1);
+        mbar_init(ew_done, EW_WARPS);
+        fence_barrier_init();
+    }
+    if (warp == EW_WARPS + 1) tmem_alloc(tmem_slot, 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t T_S = tmem_base;        // S, 128 keys
+    const uint32_t T_O = tmem_base + 128;  // O, 64 columns
+
+    if (warp == EW_WARPS) {
+        if (lane == 0) {
+            mbar_expect_tx(kv_full, 2 * ATOM);
+            tma_load_3d(sK, &tmKV, h * DH, 0, b, kv_full);
+            tma_load_3d(sV, &tmKV, p.e + h * DH, 0, b, kv_full);
+            for (int t = 0; t < tiles; ++t) {
+                if (t > 0) mbar_wait(q_free, (uint32_t)(t - 1) & 1u);
+                mbar_expect_tx(q_full, ATOM);
+                tma_load_2d(sQ, &tmQ, h * DH, lo + t * ROWS, q_full);
+            }
+        }
+        __syncwarp();
+    } else if (warp == EW_WARPS + 1) {
+        if (lane == 0) {
+            const uint32_t idesc_s = make_idesc(128, false, false);
+            const uint32_t idesc_pv = make_idesc(DH, false, true);
+            const uint32_t q_addr = smem_u32(sQ), k_addr = smem_u32(sK), v_addr = smem_u32(sV), p_addr = smem_u32(sP);
+            uint32_t ew_phase = 0;
+            mbar_wait(kv_full, 0);
+            for (int t = 0; t < tiles; ++t) {
+                mbar_wait(q_full, (uint32_t)t & 1u);
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    umma_bf16(T_S, make_smem_desc(q_addr + k * 32, 16, 1024), make_smem_desc(k_addr + k * 32, 16, 1024), idesc_s, k > 0 ? 1u : 0u);
+                umma_commit(mma_done);
+                umma_commit(q_free);
+                mbar_wait(ew_done, ew_phase);  // P written
+                ew_phase ^= 1u;
+                tc_fence_after();
+#pragma unroll
+                for (int s = 0; s < 8; ++s)  // O = P V: 16 keys per step
+                    umma_bf16(T_O, make_smem_desc(p_addr + (s >> 2) * ATOM + (s & 3) * 32, 16, 1024), make_smem_desc(v_addr + s * 2048, 8192, 1024),
+                              idesc_pv, s > 0 ? 1u : 0u);
+                umma_commit(mma_done);
+                mbar_wait(ew_done, ew_phase);  // O drained (the next tile's products overwrite S and O)
+                ew_phase ^= 1u;
+            }
+        }
+        __syncwarp();
+    } else {
+        const int q = warp & 3, cg = warp >> 2;
+        const int row = q * 32 + lane;
+        const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+        uint32_t mma_phase = 0;
+        auto wait_mma = [&]() {
+            mbar_wait(mma_done, mma_phase);
+            mma_phase ^= 1u;
+            tc_fence_after();
+        };
+        auto signal = [&]() {
+            tc_fence_before();
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) lb::mbar_arrive(ew_done);
+        };
+        for (int t = 0; t < tiles; ++t) {
+            const int gi = lo + t * ROWS + row;
+            const bool row_ok = gi < hi;
+            wait_mma();
+            float inv_l;
+            {
+                float mx = -INFINITY;
+#pragma unroll
+                for (int cc = 0; cc < 2; ++cc) {
+                    const int key0 = (cg + 2 * cc) * 32;
+                    if (key0 < n) {
+                        float s[32];
+                        lb::ld_chunk(T_S + lane_off + (uint32_t)key0, s);
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (key0 + i < n) mx = fmaxf(mx, s[i]);
+                    }
+                }
+                sRed[cg * ROWS + row] = mx;
+                asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");
+                mx = fmaxf(sRed[row], sRed[ROWS + row]);
+                asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");
+                const float m2 = mx * p.scale_log2e;
+                float lsum = 0.f;
+#pragma unroll
+                for (int cc = 0; cc < 2; ++cc) {
+                    const int chunk = cg + 2 * cc;
+                    const int key0 = chunk * 32;
+                    float s[32];
+                    if (key0 < n) {
+                        lb::ld_chunk(T_S + lane_off + (uint32_t)key0, s);
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            s[i] = (key0 + i < n) ? lb::ex2(fmaf(s[i], p.scale_log2e, -m2)) : 0.f;
+                            lsum += s[i];
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) s[i] = 0.f;
+                    }
+                    lb::store_half_row_smem(sP + (chunk >> 1) * ATOM, row, chunk & 1, s);
+                }
+                sRed[cg * ROWS + row] = lsum;
+                asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");
+                lsum = sRed[row] + sRed[ROWS + row];
+                asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");
+                inv_l = 1.0f / lsum;
+                if (cg == 0 && row_ok) p.lse[(int64_t)gi * p.heads + h] = (m2 + log2f(lsum)) * 0.69314718055994530942f;
+            }
+            signal();
+            wait_mma();
+            {
+                float v[32];
+                lb::ld_chunk(T_O + lane_off + (uint32_t)(cg * 32), v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] *= inv_l;
+                if (row_ok) lb::store32_bf16_global(p.o16 + (int64_t)gi * p.e + h * DH + cg * 32, v);
+            }
+            signal();
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == EW_WARPS + 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 256);
+    }
+}
+
 }  // namespace drt
 
 bool dr_attn_bwd_tc_supported(int n, int e, int heads) {
@@ -303,6 +490,32 @@ int dr_attn_bwd_tc(const void* q16, const void* kv, const void* do16, const floa
         configured[dev].store(true);
     }
     PIO_CUDA(launch_pdl(dr_attn_bwd_tc_kernel, dim3((unsigned)heads, (unsigned)batch), dim3(THREADS), SMEM_BYTES, st, tq, tdo, tkv, p));
+    count_launch();
+    return PIO_OK;
+}
+
+int dr_attn_fwd_tc(const void* q16, const void* kv, const int* seg, const int* count, void* o16, float* lse, int batch, int n, int e,
+                   int heads, int64_t max_rows, cudaStream_t st) {
+    using namespace drt;
+    PIO_CHECK_ARG(q16 && kv && seg && count && o16 && lse && dr_attn_bwd_tc_supported(n, e, heads) && batch > 0 && batch <= 65535 &&
+                      heads <= 65535,
+                  "dr_attn_fwd_tc: unsupported arguments");
+    CUtensorMap tq, tkv;
+    PIO_TRY(make_tmap_bf16(&tq, q16, max_rows, e, e, ROWS));
+    PIO_TRY(make_out_map(&tkv, false, kv, 2 * (int64_t)e, n, batch, 2 * (int64_t)e * 2, (int64_t)n * 2 * e * 2, 64, ROWS));
+    FwdParams p{};
+    p.lse = lse; p.seg = seg; p.count = count; p.o16 = (bf16*)o16;
+    p.n = n; p.e = e; p.heads = heads; p.max_rows = max_rows;
+    p.scale_log2e = (1.0f / sqrtf((float)DH)) * 1.44269504088896340736f;
+    const size_t smem = 5 * ATOM + 2 * ROWS * sizeof(float) + 16 * sizeof(uint64_t) + 1024;
+    int dev = 0;
+    PIO_CUDA(cudaGetDevice(&dev));
+    static std::atomic<bool> configured[64];
+    if (dev >= 0 && dev < 64 && !configured[dev].load()) {
+        PIO_CUDA(cudaFuncSetAttribute(dr_attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[dev].store(true);
+    }
+    PIO_CUDA(launch_pdl(dr_attn_fwd_tc_kernel, dim3((unsigned)heads, (unsigned)batch), dim3(THREADS), smem, st, tq, tkv, p));
     count_launch();
     return PIO_OK;
 }

@@ -1587,9 +1587,13 @@ int decode_rows_fwd(Ctx& c, const float* queries, const void* kv, const int* idx
     PIO_LAUNCH_CHECK();
     PIO_TRY(layernorm_fwd_bf16(s.xq, aw->ln_w, aw->ln_b, s.hq, e, s.stats, max_rows, e, LN_EPS, c.st, c.dyn));
     PIO_TRY(tc_xwT(c, s.hq, e, (const bf16*)aw->wq, e, max_rows, e, e, nullptr, 0, s.q, e, aw->bq, nullptr, 0, 0, nullptr, 0));
-    dr_attn_fwd_kernel<<<dim3((unsigned)heads, (unsigned)batch, DR_FWD_SPLIT), DR_FWD_WARPS * 32, dr_smem_bytes(n, dh, DR_FWD_WARPS), c.st>>>(
-        s.q, (const bf16*)kv, s.seg, c.dyn, s.o16, s.lse, l, n, e, heads, 1.0f / sqrtf((float)dh), max_rows);
-    PIO_LAUNCH_CHECK();
+    if (dr_attn_bwd_tc_supported(n, e, heads)) {  // tcgen05 version (pio_dr_attn_tc.cu)
+        PIO_TRY(dr_attn_fwd_tc(s.q, kv, s.seg, c.dyn, s.o16, s.lse, batch, n, e, heads, max_rows, c.st));
+    } else {
+        dr_attn_fwd_kernel<<<dim3((unsigned)heads, (unsigned)batch, DR_FWD_SPLIT), DR_FWD_WARPS * 32, dr_smem_bytes(n, dh, DR_FWD_WARPS), c.st>>>(
+            s.q, (const bf16*)kv, s.seg, c.dyn, s.o16, s.lse, l, n, e, heads, 1.0f / sqrtf((float)dh), max_rows);
+        PIO_LAUNCH_CHECK();
+    }
     PIO_TRY(tc_xwT(c, s.o16, e, (const bf16*)aw->wo, e, max_rows, e, e, s.x1, e, nullptr, 0, aw->bo, s.xq, e, 0, nullptr, 0));
     PIO_TRY(mlp_fwd(c, s.x1, y, mw, s.mlp, max_rows, e, 1));
     return PIO_OK;

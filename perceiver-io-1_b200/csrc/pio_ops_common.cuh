@@ -149,6 +149,8 @@ int logits_persistent(const void* a, int64_t lda, const void* w, int64_t ldb, co
 bool dr_attn_bwd_tc_supported(int n, int e, int heads);
 int dr_attn_bwd_tc(const void* q16, const void* kv, const void* do16, const float* lse, const int* seg, const int* count, void* dq16,
                    void* dkv, int batch, int n, int e, int heads, int64_t max_rows, cudaStream_t st);
+int dr_attn_fwd_tc(const void* q16, const void* kv, const int* seg, const int* count, void* o16, float* lse, int batch, int n, int e,
+                   int heads, int64_t max_rows, cudaStream_t st);
 bool ln_linear_supported(int64_t m, int64_t n, int64_t k, int64_t ldw, int64_t ldc, int64_t ldh);
 int ln_linear(const float* x, const float* gamma, const float* beta, float eps, const void* w, int64_t ldw, const float* bias, void* c,
               int64_t ldc, void* h0, int64_t ldh, float* stats, int64_t m, int64_t n, cudaStream_t st);
