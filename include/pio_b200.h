@@ -240,6 +240,15 @@ int pio_flat_copy_f32(float* flat, const pio_flat_tensor* tensors, const pio_ada
  * nn.CrossEntropyLoss, lightning.py:225-226).  Null pointers are allowed with a count of 0. */
 int pio_scale3_f32(float* a, int64_t na, float* b, int64_t nb, float* c, int64_t nc, const float* scale, pio_stream_t stream);
 
+/* 1 if pio_latent_block_fwd / _bwd (bf16 mode, dropout 0) would run a block of `layers` layers on these shapes with the
+ * cluster kernels, one launch each way (C = 256, 4 heads, n in {32, 64, 128}, at most 8 layers and 66 row tiles; the
+ * environment switches PIO_NO_FUSED_LATENT / PIO_LATENT_CLUSTER / PIO_LATENT_BWD_CLUSTER are honoured).  A caller may then
+ * hand the Residual(mlp) of the cross-attention layer in front of the block (reference model.py:29-33, :36-44) to the
+ * same call as an MLP-ONLY FIRST LAYER: attn[0] all null pointers, mlp[0] that MLP's weights, layers = 1 + the block's.
+ * pio_latent_block_fwd / _bwd accept such a first layer in bf16 mode whether or not the cluster kernels take it (otherwise
+ * it runs as pio_mlp_fwd / _bwd would); the saved buffer is sized for `layers` layers as usual. */
+int pio_latent_block_cluster_ok(int layers, int batch, int n, int c, int heads);
+
 /* Deferred join of the side streams.  The bf16 backward operators run their parameter-gradient kernels on two side
  * streams per (device, caller stream) and make the caller's stream wait for them before they return.  After
  * pio_set_side_join_deferred(1) (per host thread) pio_latent_block_bwd returns WITHOUT that wait when all it has left

@@ -84,6 +84,7 @@ struct Params {
     int n;  // latents per sample: 32, 64 or 128
     int64_t total_rows;
     float scale_log2e, scale, log2e;
+    int first_mlp_only;  // layer 0 (processed last) has no attention half
 };
 
 __device__ __forceinline__ void bar_ew() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
@@ -215,7 +216,8 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             for (int l = p.layers - 1; l >= 0; --l) {
                 if (l == p.layers - 1)
                     for (int w = 0; w < 4; ++w) prefetch_tmap(&p.w[l][w]);
-                for (int w = 0; w < 3; ++w)  // W2, W1, Wo: k-blocks (output-feature rows) in the order the atoms of the operand arrive
+                const bool mlp_only = (l == 0 && p.first_mlp_only);
+                for (int w = 0; w < (mlp_only ? 2 : 3); ++w)  // W2, W1, Wo: k-blocks (output-feature rows) in the order the atoms of the operand arrive
                     for (int i = 0; i < R; ++i) {
                         const int a = (r + R - i) % R;
                         uint8_t* dst = acquire();
@@ -225,6 +227,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 // Wqkv rows of head r (q, k, v), 16 at a time, all 256 columns (96 KB): the first six steps through the ring; the
                 // ring cannot hold the rest in flight (each refill is a ~2 K-cycle round trip: the product took 5.4 K cycles
                 // waiting for them), so the last six go to sA, which is idle from the dK / dV products to the reduce-scatter
+                if (mlp_only) break;
                 for (int kk = 0; kk < 6; ++kk) {
                     uint8_t* dst = acquire();
                     const int row0 = (kk >> 2) * C + r * DH + (kk & 3) * 16;
@@ -263,6 +266,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 mbar_expect_tx(x_full, 2 * ATOM);
                 tma_load_3d(sX, &p.in[IM_XMID], r * DH, row0, l, x_full);
                 tma_load_3d(sX + ATOM, &p.in[IM_XMID], r * DH + 32, row0, l, x_full);
+                if (l == 0 && p.first_mlp_only) break;  // an MLP-only layer reads neither Q / K / V nor its own input
                 if (!first) {
                     mbar_wait(q_free, qf);
                     qf ^= 1u;
@@ -350,6 +354,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             for (int l = p.layers - 1; l >= 0; --l) {
                 gathered_product(T_G, OM_GY, l);    // dG[:, slice] = g W2[:, slice]
                 gathered_product(T_N, OM_GH, l);    // dN2[:, slice] = dH W1[:, slice]
+                if (l == 0 && p.first_mlp_only) break;
                 gathered_product(T_O, OM_GMID, l);  // dO_r = g_mid Wo[:, head r]
                 wait_ew();                          // dO_r as bf16 in sDO
                 mbar_wait(qkv_full, qkv_phase);     // Q_r, K_r, V_r have landed
@@ -625,6 +630,10 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 float dn[32];
                 lb::ld_chunk(T_N + lane_off + (uint32_t)lcol, dn);
                 ln_backward(dn, gm, ms, OM_GN2, l, v);
+                if (l == 0 && p.first_mlp_only) {  // an MLP-only first layer: this is the gradient of the block's input
+                    if (row_ok) lb::store32_f32_global(p.dx + grow * C + gcol, v);
+                    break;
+                }
                 lb::st_chunk(T_D + lane_off + (uint32_t)lcol, v);
                 tmem_st_wait();
                 send_operand(v, true, false);
@@ -877,12 +886,15 @@ int latent_block_bwd_cluster(const float* dy, const float* x, float* dx, const L
     if (rows == 0) return PIO_OK;
     using namespace lbb;
     Params p{};
+    const bool first_mlp_only = layers[0].wqkv == nullptr;
+    p.first_mlp_only = first_mlp_only ? 1 : 0;
     for (int l = 0; l < nlayers; ++l) {
         const LatentBwdLayer& s = layers[l];
+        PIO_CHECK_ARG(s.wqkv != nullptr || l == 0, "latent_block_bwd_cluster: only the first layer may be MLP-only");
         PIO_TRY(make_tmap_bf16(&p.w[l][0], s.w2, C, C, C, 64));
         PIO_TRY(make_tmap_bf16(&p.w[l][1], s.w1, C, C, C, 64));
-        PIO_TRY(make_tmap_bf16(&p.w[l][2], s.wo, C, C, C, 64));
-        PIO_TRY(make_tmap_bf16(&p.w[l][3], s.wqkv, 3 * C, C, C, 16));
+        PIO_TRY(make_tmap_bf16(&p.w[l][2], s.wo ? s.wo : s.w1, C, C, C, 64));
+        PIO_TRY(make_tmap_bf16(&p.w[l][3], s.wqkv ? s.wqkv : s.w1, s.wqkv ? 3 * C : C, C, C, 16));
         LayerPtrs& d = p.layer[l];
         d.ln2_w = s.ln2_w; d.ln1_w = s.ln1_w; d.mlp_stats = s.mlp_stats; d.sa_stats = s.sa_stats; d.lse = s.lse;
     }

@@ -88,6 +88,7 @@ struct Params {
     int n;  // latents per sample: 32, 64 or 128
     int64_t total_rows;
     float scale_log2e;
+    int first_mlp_only;  // layer 0 has no attention half (the MLP of the cross-attention layer in front of the block)
 };
 
 using namespace lb::cl;
@@ -186,8 +187,9 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 if (l == 0) {
                     prefetch_tmap(mq); prefetch_tmap(&p.maps[l][1]); prefetch_tmap(&p.maps[l][2]); prefetch_tmap(&p.maps[l][3]);
                 }
+                const bool mlp_only = (l == 0 && p.first_mlp_only);
                 // k-blocks in the order the atoms of the gathered operand arrive: the CTA's own, then r - 1, r - 2, r - 3
-                for (int i = 0; i < 4; ++i) {
+                for (int i = 0; i < 4 && !mlp_only; ++i) {
                     const int kb = (r + R - i) % R;
                     uint8_t* dst = acquire(QKV_STAGE_BYTES);
                     uint64_t* bar = &full[prod % STAGES];
@@ -195,7 +197,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                     for (int j = 0; j < 3; ++j) tma_load_2d(dst + j * 8192, mq, kb * 64, j * C + r * DH, bar);
                     ++prod;
                 }
-                for (int w = 1; w < 4; ++w)  // rows [64 r, 64 r + 64) of Wo, W1, W2: four 64 x 64 k-blocks each, two per stage
+                for (int w = mlp_only ? 2 : 1; w < 4; ++w)  // rows [64 r, 64 r + 64) of Wo, W1, W2: four 64 x 64 k-blocks each, two per stage
                     for (int hf = 0; hf < 2; ++hf) {
                         uint8_t* dst = acquire(HALF_SLICE_BYTES);
                         uint64_t* bar = &full[prod % STAGES];
@@ -287,6 +289,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 release_own_atom();
             };
             for (int l = 0; l < p.layers; ++l) {
+                if (!(l == 0 && p.first_mlp_only)) {
                 for (int j = 0; j < R; ++j) {  // [Q_r | K_r | V_r] = LN(x) [Wq_r; Wk_r; Wv_r]^T
                     const int a = wait_atom(j);
                     if (j == 0) {
@@ -321,6 +324,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 lb::mbar_arrive(qkv_free);
 
                 slice_product(T_RES, true, OM_O16, l, false);     // x[:, slice] += O Wo[slice, :]^T
+                }
                 slice_product(T_QKV, false, OM_MLP_H0, l, false);  // hidden[:, slice] = LN2(x) W1[slice, :]^T
                 slice_product(T_RES, true, OM_MLP_G, l, true);     // x[:, slice] += G W2[slice, :]^T
             }
@@ -509,6 +513,11 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             const float* par = sPar + (l & 1) * PAR_FLOATS;
             const bool last = (l + 1 == p.layers);
             if (!last) prefetch_params(l + 1);
+            const bool mlp_only = (l == 0 && p.first_mlp_only);
+            if (mlp_only) {
+                // the MLP of the cross-attention layer in front of the block: x is the attention half's output already
+                stage_store_f32(OM_XMID, gcol, l, v);  // (the backward pass reads the layer's x_mid)
+            } else {
             ln_finish(v, par + PAR_LN1_W * 64, par + PAR_LN1_B * 64, L.sa_stats);
 
             // ---- [Q_r | K_r | V_r] + bias -> bf16 operand tiles: six 32-column chunks, three per column half
@@ -593,11 +602,13 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             qkv_phase ^= 1u;
             stage_store_f32(OM_XMID, gcol, l, v);
             tmem_st_wait();
+            }
             ln_finish(v, par + PAR_LN2_W * 64, par + PAR_LN2_B * 64, L.mlp_stats);
 
             // ---- GELU(hidden + b1) -> the CTA's atom of sA, GELU' -> sV; both leave by TMA
             wait_mma();
             free_arrive();
+            if (mlp_only && !last) commit_params(l + 1);
             {
                 float t[32], dg[32];
                 lb::ld_chunk(T_QKV + lane_off + (uint32_t)lcol, t);
@@ -668,10 +679,12 @@ int latent_block_fwd_cluster(const float* x, const LatentFusedLayer* layers, int
     if (rows == 0) return PIO_OK;
     using namespace lbc;
     Params p{};
+    const bool first_mlp_only = layers[0].wqkv == nullptr;  // an MLP-only first layer (see latent_block_fwd in pio_ops_bf16.cu)
     for (int l = 0; l < nlayers; ++l) {
         const LatentFusedLayer& s = layers[l];
-        PIO_TRY(make_tmap_bf16(&p.maps[l][0], s.wqkv, 3 * C, C, C, 64));
-        PIO_TRY(make_tmap_bf16(&p.maps[l][1], s.wo, C, C, C, 64));
+        PIO_CHECK_ARG(s.wqkv != nullptr || l == 0, "latent_block_fwd_cluster: only the first layer may be MLP-only");
+        PIO_TRY(make_tmap_bf16(&p.maps[l][0], s.wqkv ? s.wqkv : s.w1, s.wqkv ? 3 * C : C, C, C, 64));
+        PIO_TRY(make_tmap_bf16(&p.maps[l][1], s.wo ? s.wo : s.w1, C, C, C, 64));
         PIO_TRY(make_tmap_bf16(&p.maps[l][2], s.w1, C, C, C, 64));
         PIO_TRY(make_tmap_bf16(&p.maps[l][3], s.w2, C, C, C, 64));
         LayerPtrs& d = p.layer[l];
@@ -679,6 +692,8 @@ int latent_block_fwd_cluster(const float* x, const LatentFusedLayer* layers, int
         d.par[PAR_BQ] = s.bqkv; d.par[PAR_BK] = s.bqkv + C; d.par[PAR_BV] = s.bqkv + 2 * C;
         d.par[PAR_BO] = s.bo; d.par[PAR_LN2_W] = s.ln2_w; d.par[PAR_LN2_B] = s.ln2_b;
         d.par[PAR_B1] = s.b1; d.par[PAR_B2] = s.b2;
+        if (l == 0 && first_mlp_only)
+            for (int k = 0; k < PAR_LN2_W; ++k) d.par[k] = s.ln2_w;  // (loaded with the rest, never used: any readable 256 floats)
         d.sa_stats = s.sa_stats; d.mlp_stats = s.mlp_stats; d.lse = s.lse;
     }
     const LatentFusedLayer& f0 = layers[0];
@@ -704,6 +719,7 @@ int latent_block_fwd_cluster(const float* x, const LatentFusedLayer* layers, int
     p.n = n;
     p.total_rows = rows;
     p.scale_log2e = (1.0f / sqrtf((float)DH)) * 1.44269504088896340736f;
+    p.first_mlp_only = first_mlp_only ? 1 : 0;
     int dev = 0;
     PIO_CUDA(cudaGetDevice(&dev));
     static std::atomic<bool> configured[64];

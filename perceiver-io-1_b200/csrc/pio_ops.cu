@@ -539,6 +539,14 @@ int pio_self_attn_bwd(const float* dy, const float* x, float* dx, const pio_attn
 }
 
 // ---- latent block
+int pio_latent_block_cluster_ok(int layers, int batch, int n, int c, int heads) {
+    const int64_t rows = (int64_t)batch * n;
+    return layers >= 1 && layers <= PIO_LATENT_FUSED_MAX_LAYERS && latent_fused_supported(rows, n, c, heads, 0.f) && latent_cluster_preferred(rows) &&
+                   latent_bwd_cluster_supported(rows, n, c, heads, 0.f)
+               ? 1
+               : 0;
+}
+
 int pio_set_side_join_deferred(int on) {
     bf::set_side_join_deferred(on);
     return PIO_OK;

@@ -574,17 +574,38 @@ size_t block_ws_bytes(int layers, int batch, int n, int ch, int heads) {
            (size_t)layers * block_bwd_layer_bytes(r, ch) + 1024;
 }
 
+static bool mlp_only_layer(const pio_attn_weights& a) { return a.wq == nullptr; }
+
 int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,
                      int layers, int batch, int n, int ch, int heads) {
     BlockLayout L(batch, n, ch, heads);
     const int64_t rows = (int64_t)batch * n;
     const float* cur = x;
-    if (latent_fused_supported(rows, n, ch, heads, c.drop_p)) {
-        // one persistent kernel per (up to 8) layers: pio_latent_tc.cu
-        bool packed = true;
-        for (int s = 0; s < layers; ++s) packed = packed && check_packed_self(&attn[s], ch, "pio_latent_block_fwd") == PIO_OK;
-        if (packed) {
-            for (int s0 = 0; s0 < layers; s0 += PIO_LATENT_FUSED_MAX_LAYERS) {
+    // An MLP-only first layer (attn[0].wq == null): the Residual(mlp) of the cross-attention layer in front of the block,
+    // handed over so that the fused kernels run it as half a layer.  Taken inside the cluster kernels when they run the
+    // whole block in one launch; otherwise as the MLP operator of its own, followed by the block.
+    const bool pre = mlp_only_layer(attn[0]);
+    bool packed = true;
+    for (int s = pre ? 1 : 0; s < layers; ++s) packed = packed && check_packed_self(&attn[s], ch, "pio_latent_block_fwd") == PIO_OK;
+    const bool fused = packed && latent_fused_supported(rows, n, ch, heads, c.drop_p);
+    int first = 0;
+    if (pre && !(fused && latent_cluster_preferred(rows) && layers <= PIO_LATENT_FUSED_MAX_LAYERS)) {
+        char* slab = (char*)saved;
+        float* out = (layers == 1) ? y : (float*)(slab + L.xnext);
+        const uint64_t seed0 = c.drop_seed;
+        c.drop_seed = seed0 + 2;
+        PIO_TRY(mlp_fwd(c, x, out, &mlp[0], slab + L.mlp, rows, ch, 1));
+        c.drop_seed = seed0;
+        // (the fused backward chain reads a layer's x_mid from its slab; for this layer that is the block's input)
+        PIO_CUDA(cudaMemcpyAsync(slab + L.xmid, x, (size_t)rows * ch * sizeof(float), cudaMemcpyDeviceToDevice, c.st));
+        cur = out;
+        first = 1;
+        if (layers == 1) return PIO_OK;
+    }
+    if (fused) {
+        // one persistent kernel per (up to 8) layers: pio_latent_cl.cu / pio_latent_tc.cu
+        {
+            for (int s0 = first; s0 < layers; s0 += PIO_LATENT_FUSED_MAX_LAYERS) {
                 const int cnt = std::min(PIO_LATENT_FUSED_MAX_LAYERS, layers - s0);
                 LatentFusedLayer fl[PIO_LATENT_FUSED_MAX_LAYERS];
                 for (int i = 0; i < cnt; ++i) {
@@ -607,7 +628,7 @@ int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* a
             return PIO_OK;
         }
     }
-    for (int s = 0; s < layers; ++s) {
+    for (int s = first; s < layers; ++s) {
         char* slab = (char*)saved + (size_t)s * L.per_layer;
         float* xmid = (float*)(slab + L.xmid);
         float* out = (s == layers - 1) ? y : (float*)(slab + L.xnext);
@@ -682,9 +703,10 @@ static int latent_block_bwd_fused(Ctx& c, Side& side, const float* dy, const flo
             const float* x_in = (s == 0) ? x : bl[(size_t)s - 1].xnext;
             dwi[nd++] = DwBatchItem{b.gy16, ch, ch, ms.g, ch, ch, mlp_g[s].w2, mlp_g[s].b2};
             dwi[nd++] = DwBatchItem{b.gh16, ch, ch, ms.h0, ch, ch, mlp_g[s].w1, mlp_g[s].b1};
+            lni[nl++] = LnGradItem{b.gn2, b.xmid, b.mlp_stats, mlp_g[s].ln_w, mlp_g[s].ln_b};
+            if (mlp_only_layer(attn[s])) continue;
             dwi[nd++] = DwBatchItem{b.gmid16, ch, ch, sa.o16, ch, ch, attn_g[s].wo, attn_g[s].bo};
             dwi[nd++] = DwBatchItem{b.gqkv16, 3 * ch, 3 * ch, sa.h0, ch, ch, attn_g[s].wq, attn_g[s].bq};
-            lni[nl++] = LnGradItem{b.gn2, b.xmid, b.mlp_stats, mlp_g[s].ln_w, mlp_g[s].ln_b};
             lni[nl++] = LnGradItem{b.gn1, x_in, b.sa_stats, attn_g[s].ln_w, attn_g[s].ln_b};
         }
         PIO_TRY(dw_batched(dwi, nd, rows, side.stream()));
@@ -701,9 +723,10 @@ int latent_block_bwd(Ctx& c, const float* dy, const float* x, float* dx, const p
                      int batch, int n, int ch, int heads) {
     BlockLayout L(batch, n, ch, heads);
     const int64_t rows = (int64_t)batch * n;
-    if (acc == 2 && latent_bwd_cluster_supported(rows, n, ch, heads, c.drop_p)) {
+    const bool pre = mlp_only_layer(attn[0]);
+    if (acc == 2 && latent_bwd_cluster_supported(rows, n, ch, heads, c.drop_p) && (!pre || layers <= PIO_LATENT_FUSED_MAX_LAYERS)) {
         bool packed = true;
-        for (int s = 0; s < layers; ++s) packed = packed && check_packed_self(&attn[s], ch, "pio_latent_block_bwd") == PIO_OK;
+        for (int s = pre ? 1 : 0; s < layers; ++s) packed = packed && check_packed_self(&attn[s], ch, "pio_latent_block_bwd") == PIO_OK;
         Side side(c, acc);
         if (packed && side.active()) return latent_block_bwd_fused(c, side, dy, x, dx, attn, mlp, saved, attn_g, mlp_g, layers, batch, n, ch, heads);
     }
@@ -718,6 +741,12 @@ int latent_block_bwd(Ctx& c, const float* dy, const float* x, float* dx, const p
         const char* slab = (const char*)saved + (size_t)s * L.per_layer;
         const float* x_in = (s == 0) ? x : (const float*)((const char*)saved + (size_t)(s - 1) * L.per_layer + L.xnext);
         const uint64_t seed0 = c.drop_seed;
+        if (s == 0 && pre) {  // the MLP-only first layer: its input is the block's input
+            c.drop_seed = seed0 + 2;
+            PIO_TRY(mlp_bwd(c, grad, x, dx, &mlp[0], slab + L.mlp, &mlp_g[0], acc, rows, ch, 1, grad16, nullptr));
+            c.drop_seed = seed0;
+            break;
+        }
         c.drop_seed = seed0 + 4 * (uint64_t)s + 2;
         PIO_TRY(mlp_bwd(c, grad, (const float*)(slab + L.xmid), dmid, &mlp[s], slab + L.mlp, &mlp_g[s], acc, rows, ch, 1, grad16, dmid16));
         float* out = (s == 0) ? dx : dcur;

@@ -154,6 +154,7 @@ int dr_attn_fwd_tc(const void* q16, const void* kv, const int* seg, const int* c
 bool ln_linear_supported(int64_t m, int64_t n, int64_t k, int64_t ldw, int64_t ldc, int64_t ldh);
 int ln_linear(const float* x, const float* gamma, const float* beta, float eps, const void* w, int64_t ldw, const float* bias, void* c,
               int64_t ldc, void* h0, int64_t ldh, float* stats, int64_t m, int64_t n, cudaStream_t st);
+bool latent_cluster_preferred(int64_t rows);
 bool latent_fused_supported(int64_t rows, int n, int ch, int heads, float drop_p);
 int latent_block_fwd_fused(const float* x, const LatentFusedLayer* layers, int nlayers, int batch, int n, cudaStream_t st);
 

@@ -96,6 +96,7 @@ _SIGNATURES = {
     "pio_adamw_tick": (c_int, [P, P]),
     "pio_flat_copy_f32": (c_int, [P, P, P, c_int, c_int, ctypes.c_float, P]),
     "pio_scale3_f32": (c_int, [P, c_int64, P, c_int64, P, c_int64, P, P]),
+    "pio_latent_block_cluster_ok": (c_int, [c_int, c_int, c_int, c_int, c_int]),
     "pio_set_side_join_deferred": (c_int, [c_int]),
     "pio_side_join": (c_int, [P]),
     "pio_logits_bf16_supported": (c_int, [c_int64, c_int64, c_int64, c_int64, c_int64, c_int64]),

@@ -834,10 +834,11 @@ class LatentBlockFn(torch.autograd.Function):
         keep = []
         for s in range(layers):
             p = params[s * _LAYER_PARAMS:(s + 1) * _LAYER_PARAMS]
-            fields = _sa_struct(*p[:6], c, mode)
-            keep.append(fields.pop("_keep"))
-            for k, v in fields.items():
-                setattr(attn[s], k, v if isinstance(v, int) or v is None else v.data_ptr())
+            if p[2] is not None:  # (an MLP-only first layer has no attention tensors: its struct stays all null)
+                fields = _sa_struct(*p[:6], c, mode)
+                keep.append(fields.pop("_keep"))
+                for k, v in fields.items():
+                    setattr(attn[s], k, v if isinstance(v, int) or v is None else v.data_ptr())
             ops = _mlp_operands(p[6:], mode)
             keep.append(ops)
             for k, v in zip(N.MlpWeights._names, ops):
@@ -847,7 +848,7 @@ class LatentBlockFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, heads, drop_p, drop_seed, *params):
         x = _c(x)
-        params = [_c(p) for p in params]
+        params = [None if p is None else _c(p) for p in params]
         layers = len(params) // _LAYER_PARAMS
         assert layers * _LAYER_PARAMS == len(params) and layers >= 1
         b, n, c = x.shape

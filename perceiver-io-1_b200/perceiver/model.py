@@ -150,10 +150,25 @@ def self_attention_layer(num_channels: int, num_heads: int, dropout: float):
 
 
 class SelfAttentionBlock(Sequential):
-    """S self-attention layers; forward hands all of them to one fused call."""
+    """S self-attention layers; forward hands all of them to one fused call.  ``pre``: the Residual(mlp) of the
+    cross-attention layer in front of the block (reference model.py:29-33), run by the same call as an MLP-only first
+    layer when the fused cluster kernels take the block (see `takes_pre_mlp`)."""
 
-    def forward(self, x):
+    def takes_pre_mlp(self, x, pre):
+        import os
+        if F.get_compute_mode() != F.N.MODE_BF16 or os.environ.get("PIO_NO_PRE_MLP") is not None or not x.is_cuda:
+            return False
+        if _active_p(self, self[0][0].dropout_p) or _active_p(pre, pre.dropout_p):
+            return False
+        b, n, c = x.shape
+        heads = self[0][0].module.attention.attention.num_heads
+        return bool(F.N.lib().pio_latent_block_cluster_ok(len(self) + 1, int(b), int(n), int(c), int(heads)))
+
+    def forward(self, x, pre=None):
         params = []
+        if pre is not None:
+            params.extend([None] * 6)
+            params.extend(pre.module._params())
         for layer in self:
             sa, ff = layer[0], layer[1]
             params.extend(sa.module._params())
@@ -201,6 +216,8 @@ class PerceiverEncoder(nn.Module):
     def _apply_layer(layer, x_latent, x, pad_mask, attn_mask, kv=None):
         cross, block = layer[0], layer[1]
         x_latent = cross[0](x_latent, x, pad_mask, attn_mask, kv=kv)
+        if isinstance(block, SelfAttentionBlock) and block.takes_pre_mlp(x_latent, cross[1]):
+            return block(x_latent, pre=cross[1])  # the cross-attention layer's MLP rides on the block's fused kernels
         x_latent = cross[1](x_latent)
         return block(x_latent)
 

@@ -93,3 +93,43 @@ def test_fused_block_matches_oracle(batch, n, layers):
     num = sum(((g[k].cpu().double() - sd[k].grad.double()) ** 2).sum().item() for k in g)
     den = sum((sd[k].grad.double() ** 2).sum().item() for k in g)
     assert (num / den) ** 0.5 < BF16_TOL, (num / den) ** 0.5
+
+
+@pytest.mark.parametrize("batch,n,layers", [(2, 64, 1), (5, 32, 3), (64, 64, 6), (3, 128, 7)])
+def test_pre_mlp_rides_on_the_block(batch, n, layers):
+    """Residual(mlp) of the cross-attention layer handed to the block's fused call as an MLP-only first layer
+    (reference model.py:29-33 followed by :36-44) against running it as an operator of its own."""
+    from perceiver import _native as N
+    from perceiver.model import Residual, mlp, self_attention_block
+    torch.manual_seed(11 * batch + n + layers)
+    block = self_attention_block(layers, 256, 4, 0.0).to(DEV)
+    pre = Residual(mlp(256), 0.0).to(DEV)
+    with torch.no_grad():
+        for mod in (block, pre):
+            for k, p in mod.named_parameters():
+                if p.dim() == 1:
+                    p.add_(torch.randn_like(p) * 0.1)
+    x = torch.randn(batch, n, 256, device=DEV)
+    dy = torch.randn(batch, n, 256, device=DEV)
+
+    def run(fused):
+        block.zero_grad(set_to_none=True)
+        pre.zero_grad(set_to_none=True)
+        xin = x.clone().requires_grad_(True)
+        c0 = N.lib().pio_launch_count()
+        y = block(xin, pre=pre) if fused else block(pre(xin))
+        y.backward(dy)
+        torch.cuda.synchronize()
+        launches = N.lib().pio_launch_count() - c0
+        grads = {"block." + k: p.grad.detach().clone() for k, p in block.named_parameters()}
+        grads.update({"pre." + k: p.grad.detach().clone() for k, p in pre.named_parameters()})
+        return y.detach(), xin.grad.detach(), grads, launches
+
+    y_f, dx_f, g_f, l_f = run(True)
+    y_u, dx_u, g_u, l_u = run(False)
+    if os.environ["PIO_LATENT_CLUSTER"] == "1" and os.environ["PIO_LATENT_BWD_CLUSTER"] == "1":
+        assert l_f < l_u, (l_f, l_u)  # the MLP's own launches are gone
+    assert_rel(y_f, y_u, 4e-3, "y")
+    assert_rel(dx_f, dx_u, 1e-2, "dx")
+    for k in g_u:
+        assert_rel(g_f[k], g_u[k], 1.5e-2, f"grad {k}")
