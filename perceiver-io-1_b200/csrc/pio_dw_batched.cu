@@ -51,6 +51,7 @@ struct Batch {
     int num_kb, kb_per_split;
     const int* dyn_rows;  // device-side count of live rows (the contraction then ends at its next multiple of 64), or null
     int dyn_off;
+    int store;  // A_MN = false with a single K split: the tile is stored, not added
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -75,8 +76,8 @@ __global__ void __launch_bounds__(THREADS, 1) dw_batched_kernel(const __grid_con
 
     pdl_trigger();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const Problem& P = g.prob[g.tile_prob[blockIdx.x]];
-    const int m0 = (int)g.tile_m[blockIdx.x] * BM;
+    const Problem& P = g.prob[A_MN ? g.tile_prob[blockIdx.x] : 0];
+    const int m0 = (A_MN ? (int)g.tile_m[blockIdx.x] : (int)blockIdx.x) * BM;  // (the single product of the A_MN = false form needs no tile table)
     int num_kb = g.num_kb, kb_per_split = g.kb_per_split, m_live = P.m;
     if (g.dyn_rows != nullptr) {
         pdl_wait();
@@ -181,7 +182,9 @@ __global__ void __launch_bounds__(THREADS, 1) dw_batched_kernel(const __grid_con
         const int rows_here = min(32, m_live - (m0 + q * 32));
         for (int rr = 0; rr < rows_here; ++rr) {
             const float4 v = *reinterpret_cast<const float4*>(stile + rr * PITCH + lane * 4);
-            red_add_v4(P.dw + (int64_t)(m0 + q * 32 + rr) * BN + half * 128 + lane * 4, v.x, v.y, v.z, v.w);
+            float* o = P.dw + (int64_t)(m0 + q * 32 + rr) * BN + half * 128 + lane * 4;
+            if (!A_MN && g.store) *reinterpret_cast<float4*>(o) = v;
+            else red_add_v4(o, v.x, v.y, v.z, v.w);
         }
         tc_fence_before();
     }
@@ -238,11 +241,16 @@ int dw_batched(const DwBatchItem* items, int count, int64_t rows, cudaStream_t s
     return PIO_OK;
 }
 
-// c32 (m x 256, fp32, row-major, ADDED into: zero-fill it first) += a16 (m x k, bf16, pitch lda) b16 (k x 256, bf16, pitch ldb),
-// split over K into one wave of 128 x 256 tiles; dyn_rows (device memory, nullable): only the first *dyn_rows - dyn_off rows
-// of a / c are live.
+// c32 (m x 256, fp32, row-major) (+)= a16 (m x k, bf16, pitch lda) b16 (k x 256, bf16, pitch ldb) in 128 x 256 tiles (a is read
+// once), split over K when there are fewer tiles than SMs; dyn_rows (device memory, nullable): only the first
+// *dyn_rows - dyn_off rows of a / c are live.  *stored = 1 when the tiles were stored (one K split: c32 need not be zeroed),
+// 0 when they were ADDED with atomics (the caller zero-fills c32 first; xw_splitk_stores tells beforehand).
 bool xw_splitk_supported(int64_t m, int64_t n, int64_t k, int64_t lda, int64_t ldb) {
-    return n == dwb::BN && m > 0 && cdiv(m, (int64_t)dwb::BM) <= dwb::MAX_TILES && k > 0 && lda % 8 == 0 && ldb % 8 == 0;
+    return n == dwb::BN && m > 0 && m < (1ll << 30) && k > 0 && lda % 8 == 0 && ldb % 8 == 0;
+}
+bool xw_splitk_stores(int64_t m, int64_t k) {
+    const int64_t tiles = cdiv(m, (int64_t)dwb::BM);
+    return std::max<int64_t>(1, std::min<int64_t>(cdiv(k, (int64_t)dwb::BK), num_sms() / tiles)) == 1;
 }
 int xw_splitk(const void* a16, int64_t lda, const void* b16, int64_t ldb, float* c32, int64_t m, int64_t k, cudaStream_t st,
               const int* dyn_rows, int dyn_off) {
@@ -255,14 +263,11 @@ int xw_splitk(const void* a16, int64_t lda, const void* b16, int64_t ldb, float*
     g.prob[0].db = nullptr;
     g.prob[0].m = (int)m;
     const int tiles = (int)cdiv(m, (int64_t)BM);
-    for (int t = 0; t < tiles; ++t) {
-        g.tile_prob[t] = 0;
-        g.tile_m[t] = (unsigned char)t;
-    }
     g.dyn_rows = dyn_rows;
     g.dyn_off = dyn_off;
     g.num_kb = (int)cdiv(k, (int64_t)BK);
     const int splits = std::max(1, std::min(g.num_kb, num_sms() / tiles));
+    g.store = splits == 1 ? 1 : 0;
     g.kb_per_split = (int)cdiv(g.num_kb, splits);
     const int used = (int)cdiv(g.num_kb, g.kb_per_split);
     int dev = 0;

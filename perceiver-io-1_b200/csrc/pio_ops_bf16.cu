@@ -307,6 +307,19 @@ int kv_project_bwd(Ctx& c, const float* dkv, const float* x_kv, float* dx_kv, co
     PIO_TAKE_BYTES(float, dh0, c, (size_t)rows * ckv * 4, "pio_kv_project_bwd");
     Side side(c, acc);
     PIO_TRY(side.fork());
+    const bool packed_g = g->bv == g->bk + e && g->wv == g->wk + (size_t)e * ckv;
+    if (packed_g && side.active() && ckv == 256 && packed16(w->wk, w->wv, e, ckp) && cdiv(2 * e, 128) <= 160) {
+        // dW (2E x C_kv) and its bias gradient in one batched launch (pio_dw_batched.cu), the input gradient as 128 x 256 tiles
+        DwBatchItem it{dkv16, 2 * e, 2 * e, s.h0, ckp, ckv, g->wk, g->bk};
+        PIO_TRY(dw_batched(&it, 1, rows, side.stream()));
+        if (!xw_splitk_stores(rows, 2 * e)) PIO_CUDA(cudaMemsetAsync(dh0, 0, (size_t)rows * ckv * sizeof(float), c.st));
+        PIO_TRY(xw_splitk(dkv16, 2 * e, w->wk, ckp, dh0, rows, 2 * e, c.st));
+        PIO_TRY(pio_layernorm_bwd(dh0, x_kv, s.stats, w->kv_ln_w, nullptr, dx_kv, g->kv_ln_w, g->kv_ln_b, acc, rows, ckv, c.rest(),
+                                  c.rest_bytes(), c.st));
+        PIO_TRY(side.join());
+        c.W.off = mark;
+        return PIO_OK;
+    }
     if (g->bv == g->bk + e) {
         PIO_TRY(side_colsum(c, side, dkv16, 2 * e, g->bk, acc, rows, 2 * e));
     } else {
@@ -1213,7 +1226,7 @@ int linear_ce_fwd_bwd(Ctx& c, const float* x, const float* w16, const float* b, 
         }
         if (xw_splitk_supported(nr, c_in, classes, cop, cip)) {
             // dx (compacted) = dlogits W: 128 x 256 tiles so that dlogits is read once, split over the vocabulary
-            PIO_CUDA(cudaMemsetAsync(dxc + r0 * c_in, 0, (size_t)nr * c_in * sizeof(float), c.st));
+            if (!xw_splitk_stores(nr, classes)) PIO_CUDA(cudaMemsetAsync(dxc + r0 * c_in, 0, (size_t)nr * c_in * sizeof(float), c.st));
             PIO_TRY(xw_splitk(lg16, cop, w16, cip, dxc + r0 * c_in, nr, classes, c.st, count, (int)r0));
         } else {  // dx (compacted) = dlogits W
             pio_gemm_bf16_desc d{};

@@ -140,6 +140,7 @@ struct DwBatchItem {
 };
 int dw_batched(const DwBatchItem* items, int count, int64_t rows, cudaStream_t st, const int* dyn_rows = nullptr, int dyn_off = 0);
 bool xw_splitk_supported(int64_t m, int64_t n, int64_t k, int64_t lda, int64_t ldb);
+bool xw_splitk_stores(int64_t m, int64_t k);
 int xw_splitk(const void* a16, int64_t lda, const void* b16, int64_t ldb, float* c32, int64_t m, int64_t k, cudaStream_t st,
               const int* dyn_rows = nullptr, int dyn_off = 0);
 // persistent vocabulary-logits product (pio_logits_tc.cu)
