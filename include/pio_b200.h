@@ -451,6 +451,30 @@ int pio_latent_block_bwd(const float* dy, const float* x, float* dx, const pio_a
                          int heads, const pio_dropout* drop, int mode, void* ws, size_t ws_bytes,
                          pio_stream_t stream);
 
+/* pio_latent_block_fwd / _bwd with a FIRST LAYER THAT HAS NO ATTENTION OF ITS OWN (bf16 mode): attn[0].wq == NULL.
+ *   attn[0] all null: layer 0 is only mlp[0] with its residual — the Residual(mlp) of the cross-attention layer in front
+ *     of the block (reference model.py:29-33).
+ *   attn[0].wo / .bo given: layer 0 first adds that cross-attention layer's out-projection and residual,
+ *     x += pre_o16 Wo^T + bo, where pre_o16 (rows x c, bf16) is the attention output (pio_cross_attend_fwd with
+ *     residual = 2 leaves it in its saved buffer at pio_cross_attend_o16_offset), then runs mlp[0].
+ * Backward: dx is the gradient of the block's input x; attn_g[0].wo / .bo receive the out-projection's gradients and
+ * pre_do16 (rows x c, bf16, written) the gradient of the attention output, to be handed to pio_cross_attend_bwd
+ * (residual = 2) as its `dy`.  Shapes the cluster kernels do not take run the same arithmetic with the per-operator
+ * kernels.  The plain entry points are these with pre_o16 = pre_do16 = NULL. */
+int pio_latent_block_fwd_pre(const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,
+                             int layers, int batch, int n, int c, int heads, const pio_dropout* drop, int mode, void* ws,
+                             size_t ws_bytes, pio_stream_t stream, const void* pre_o16);
+int pio_latent_block_bwd_pre(const float* dy, const float* x, float* dx, const pio_attn_weights* attn, const pio_mlp_weights* mlp,
+                             const void* saved, const pio_attn_grads* attn_g, const pio_mlp_grads* mlp_g, int accumulate,
+                             int layers, int batch, int n, int c, int heads, const pio_dropout* drop, int mode, void* ws,
+                             size_t ws_bytes, pio_stream_t stream, const void* pre_o16, void* pre_do16);
+/* Byte offset of the attention output (batch*n x e, bf16) inside the saved buffer of pio_cross_attend_fwd (bf16 mode).
+ * With residual = 2, pio_cross_attend_fwd stops after the attention (y is not written) and pio_cross_attend_bwd takes as
+ * `dy` the bf16 gradient of that attention output, leaves wo / bo gradients alone and returns in dx_q only the gradient
+ * that reaches x_q through q_norm and the Q projection. */
+size_t pio_cross_attend_o16_offset(int batch, int n, int e, int heads);
+
+
 /* nn.Linear of Classification/TextOutputAdapter, adapter.py:146-149: y = x W^T + b. */
 size_t pio_linear_ws_bytes(int64_t rows, int c_in, int64_t c_out, int mode);
 int pio_linear_fwd(const float* x, const float* w, const float* b, float* y, int64_t rows, int c_in,

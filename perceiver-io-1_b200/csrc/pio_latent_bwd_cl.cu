@@ -84,7 +84,8 @@ struct Params {
     int n;  // latents per sample: 32, 64 or 128
     int64_t total_rows;
     float scale_log2e, scale, log2e;
-    int first_mlp_only;  // layer 0 (processed last) has no attention half
+    int first_mlp_only;  // layer 0 (processed last) has no attention half of its own: 1 = MLP only, 2 = out-projection + MLP
+    bf16* pre_do16;      // mode 2: the gradient of the attention output (rows x 256), written
 };
 
 __device__ __forceinline__ void bar_ew() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
@@ -217,7 +218,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 if (l == p.layers - 1)
                     for (int w = 0; w < 4; ++w) prefetch_tmap(&p.w[l][w]);
                 const bool mlp_only = (l == 0 && p.first_mlp_only);
-                for (int w = 0; w < (mlp_only ? 2 : 3); ++w)  // W2, W1, Wo: k-blocks (output-feature rows) in the order the atoms of the operand arrive
+                for (int w = 0; w < ((mlp_only && p.first_mlp_only == 1) ? 2 : 3); ++w)  // W2, W1, Wo: k-blocks (output-feature rows) in the order the atoms of the operand arrive
                     for (int i = 0; i < R; ++i) {
                         const int a = (r + R - i) % R;
                         uint8_t* dst = acquire();
@@ -354,8 +355,9 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             for (int l = p.layers - 1; l >= 0; --l) {
                 gathered_product(T_G, OM_GY, l);    // dG[:, slice] = g W2[:, slice]
                 gathered_product(T_N, OM_GH, l);    // dN2[:, slice] = dH W1[:, slice]
-                if (l == 0 && p.first_mlp_only) break;
+                if (l == 0 && p.first_mlp_only == 1) break;
                 gathered_product(T_O, OM_GMID, l);  // dO_r = g_mid Wo[:, head r]
+                if (l == 0 && p.first_mlp_only == 2) break;
                 wait_ew();                          // dO_r as bf16 in sDO
                 mbar_wait(qkv_full, qkv_phase);     // Q_r, K_r, V_r have landed
                 qkv_phase ^= 1u;
@@ -630,8 +632,15 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 float dn[32];
                 lb::ld_chunk(T_N + lane_off + (uint32_t)lcol, dn);
                 ln_backward(dn, gm, ms, OM_GN2, l, v);
-                if (l == 0 && p.first_mlp_only) {  // an MLP-only first layer: this is the gradient of the block's input
+                if (l == 0 && p.first_mlp_only) {  // a first layer without attention of its own: this is the gradient of the block's input
                     if (row_ok) lb::store32_f32_global(p.dx + grow * C + gcol, v);
+                    if (p.first_mlp_only == 1) break;
+                    // mode 2: dO = g_mid Wo (the CTA's 64 columns = head r's) for the attention backward of the layer in front
+                    send_operand(v, true, false);
+                    wait_mma();
+                    float t[32];
+                    lb::ld_chunk(T_O + lane_off + (uint32_t)lcol, t);
+                    if (row_ok) lb::store32_bf16_global(p.pre_do16 + grow * C + gcol, t);
                     break;
                 }
                 lb::st_chunk(T_D + lane_off + (uint32_t)lcol, v);
@@ -886,8 +895,10 @@ int latent_block_bwd_cluster(const float* dy, const float* x, float* dx, const L
     if (rows == 0) return PIO_OK;
     using namespace lbb;
     Params p{};
-    const bool first_mlp_only = layers[0].wqkv == nullptr;
-    p.first_mlp_only = first_mlp_only ? 1 : 0;
+    const int first_mlp_only = layers[0].wqkv != nullptr ? 0 : (layers[0].wo != nullptr ? 2 : 1);
+    PIO_CHECK_ARG(first_mlp_only != 2 || layers[0].pre_do16 != nullptr, "latent_block_bwd_cluster: an out-projection first layer needs pre_do16");
+    p.first_mlp_only = first_mlp_only;
+    p.pre_do16 = (bf16*)layers[0].pre_do16;
     for (int l = 0; l < nlayers; ++l) {
         const LatentBwdLayer& s = layers[l];
         PIO_CHECK_ARG(s.wqkv != nullptr || l == 0, "latent_block_bwd_cluster: only the first layer may be MLP-only");

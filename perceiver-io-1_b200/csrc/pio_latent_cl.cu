@@ -88,7 +88,9 @@ struct Params {
     int n;  // latents per sample: 32, 64 or 128
     int64_t total_rows;
     float scale_log2e;
-    int first_mlp_only;  // layer 0 has no attention half (the MLP of the cross-attention layer in front of the block)
+    int first_mlp_only;  // layer 0 has no attention half of its own: 1 = only the MLP of the cross-attention layer in front of the block,
+                         // 2 = that layer's out-projection + residual (x += O Wo^T + bo, O given) and its MLP
+    CUtensorMap o_map;   // mode 2: the attention output O (rows x 256, bf16) as (columns, rows, 1)
 };
 
 using namespace lb::cl;
@@ -138,7 +140,8 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
     uint64_t* stat_full = bars + 2 * STAGES + 7;
     uint64_t* sa_free = bars + 2 * STAGES + 8;   // the TMA store out of the CTA's own atom of sA (and of sV) has read it
     uint64_t* qkv_free = bars + 2 * STAGES + 9;  // the TMA stores out of sQ / sK / sV have read them
-    uint32_t* tmem_slot = (uint32_t*)(bars + 2 * STAGES + 10);
+    uint64_t* o_full = bars + 2 * STAGES + 10;   // mode 2: the attention output tile has landed in sA
+    uint32_t* tmem_slot = (uint32_t*)(bars + 2 * STAGES + 11);
 
     pdl_trigger();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -157,6 +160,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
         mbar_init(stat_full, 1);
         mbar_init(sa_free, 1);
         mbar_init(qkv_free, 1);
+        mbar_init(o_full, 1);
         fence_barrier_init();
     }
     if (warp == EW_WARPS + 1) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -188,6 +192,12 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                     prefetch_tmap(mq); prefetch_tmap(&p.maps[l][1]); prefetch_tmap(&p.maps[l][2]); prefetch_tmap(&p.maps[l][3]);
                 }
                 const bool mlp_only = (l == 0 && p.first_mlp_only);
+                if (mlp_only && p.first_mlp_only == 2) {  // the attention output of the cross-attention layer: all four atoms from global memory
+                    prefetch_tmap(&p.o_map);
+                    mbar_expect_tx(o_full, 4 * ATOM);
+#pragma unroll
+                    for (int a = 0; a < 4; ++a) lb::tma_load_3d(sA + a * ATOM, &p.o_map, a * 64, tile * ROWS, 0, o_full);
+                }
                 // k-blocks in the order the atoms of the gathered operand arrive: the CTA's own, then r - 1, r - 2, r - 3
                 for (int i = 0; i < 4 && !mlp_only; ++i) {
                     const int kb = (r + R - i) % R;
@@ -197,7 +207,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                     for (int j = 0; j < 3; ++j) tma_load_2d(dst + j * 8192, mq, kb * 64, j * C + r * DH, bar);
                     ++prod;
                 }
-                for (int w = mlp_only ? 2 : 1; w < 4; ++w)  // rows [64 r, 64 r + 64) of Wo, W1, W2: four 64 x 64 k-blocks each, two per stage
+                for (int w = (mlp_only && p.first_mlp_only == 1) ? 2 : 1; w < 4; ++w)  // rows [64 r, 64 r + 64) of Wo, W1, W2: four 64 x 64 k-blocks each, two per stage
                     for (int hf = 0; hf < 2; ++hf) {
                         uint8_t* dst = acquire(HALF_SLICE_BYTES);
                         uint64_t* bar = &full[prod % STAGES];
@@ -324,6 +334,24 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 lb::mbar_arrive(qkv_free);
 
                 slice_product(T_RES, true, OM_O16, l, false);     // x[:, slice] += O Wo[slice, :]^T
+                } else if (p.first_mlp_only == 2) {
+                    // x[:, slice] += O Wo[slice, :]^T with O loaded by TMA (no gather); k-blocks in the order the producer loads Wo's
+                    mbar_wait(o_full, 0);
+                    wait_ew();  // the element-wise warps have put x into the residual columns
+                    for (int hf = 0; hf < 2; ++hf) {
+                        const uint32_t b = ring_wait();
+#pragma unroll
+                        for (int kb = 0; kb < 2; ++kb) {
+                            const int a = (r + R - (hf * 2 + kb)) % R;
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                umma_bf16(T_RES, make_smem_desc(a_addr + a * ATOM + k * 32, 16, 1024),
+                                          make_smem_desc(b + kb * 8192 + k * 32, 16, 1024), idesc_64, 1u);
+                        }
+                        ring_release();
+                    }
+                    umma_commit(mma_done);
+                    lb::mbar_arrive(sa_free);  // (nothing is stored out of sA here)
                 }
                 slice_product(T_QKV, false, OM_MLP_H0, l, false);  // hidden[:, slice] = LN2(x) W1[slice, :]^T
                 slice_product(T_RES, true, OM_MLP_G, l, true);     // x[:, slice] += G W2[slice, :]^T
@@ -501,12 +529,17 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] = 0.f;
         }
-        lb::stat_chunk(st, v);
-        send_stats(st);
+        if (p.first_mlp_only != 2) {  // (mode 2: the first LayerNorm sees x + O Wo^T + bo, formed below)
+            lb::stat_chunk(st, v);
+            send_stats(st);
+        } else {
+            first_gather = false;  // sA holds the attention output: the first gather waits until every CTA's out-projection has read it
+        }
         lb::st_chunk(T_RES + lane_off + (uint32_t)lcol, v);
         tmem_st_wait();
         commit_params(0);
         bar_ew();  // the parameters are in shared memory before anyone reads them
+        if (p.first_mlp_only == 2) signal();  // the out-projection accumulates into the residual columns just written
 
         for (int l = 0; l < p.layers; ++l) {
             const LayerPtrs& L = p.layer[l];
@@ -514,10 +547,11 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             const bool last = (l + 1 == p.layers);
             if (!last) prefetch_params(l + 1);
             const bool mlp_only = (l == 0 && p.first_mlp_only);
-            if (mlp_only) {
+            if (mlp_only && p.first_mlp_only == 1) {
                 // the MLP of the cross-attention layer in front of the block: x is the attention half's output already
                 stage_store_f32(OM_XMID, gcol, l, v);  // (the backward pass reads the layer's x_mid)
             } else {
+            if (!mlp_only) {
             ln_finish(v, par + PAR_LN1_W * 64, par + PAR_LN1_B * 64, L.sa_stats);
 
             // ---- [Q_r | K_r | V_r] + bias -> bf16 operand tiles: six 32-column chunks, three per column half
@@ -589,6 +623,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 send_operand(t);
             }
 
+            }  // (mode 2 starts here: the out-projection of the given attention output has accumulated into the residual columns)
             // ---- x_mid = x + attention + bo (back into the residual columns, fp32 copy out), LayerNorm 2
             wait_mma();
             free_arrive();
@@ -598,8 +633,10 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             lb::stat_chunk(st, v);
             send_stats(st);  // first: the peers wait for these
             lb::st_chunk(T_RES + lane_off + (uint32_t)lcol, v);
-            mbar_wait(qkv_free, qkv_phase);  // Q, K, V have left their tiles: sQ / sK are staging space, sV takes GELU'
-            qkv_phase ^= 1u;
+            if (!mlp_only) {
+                mbar_wait(qkv_free, qkv_phase);  // Q, K, V have left their tiles: sQ / sK are staging space, sV takes GELU'
+                qkv_phase ^= 1u;
+            }
             stage_store_f32(OM_XMID, gcol, l, v);
             tmem_st_wait();
             }
@@ -679,7 +716,11 @@ int latent_block_fwd_cluster(const float* x, const LatentFusedLayer* layers, int
     if (rows == 0) return PIO_OK;
     using namespace lbc;
     Params p{};
-    const bool first_mlp_only = layers[0].wqkv == nullptr;  // an MLP-only first layer (see latent_block_fwd in pio_ops_bf16.cu)
+    // a first layer without an attention half of its own (see latent_block_fwd in pio_ops_bf16.cu): 1 = MLP only, 2 = the
+    // out-projection of a given attention output (pre_o16) + residual, then the MLP
+    const int first_mlp_only = layers[0].wqkv != nullptr ? 0 : (layers[0].wo != nullptr ? 2 : 1);
+    PIO_CHECK_ARG(first_mlp_only != 2 || (layers[0].pre_o16 != nullptr && layers[0].bo != nullptr),
+                  "latent_block_fwd_cluster: an out-projection first layer needs the attention output and the bias");
     for (int l = 0; l < nlayers; ++l) {
         const LatentFusedLayer& s = layers[l];
         PIO_CHECK_ARG(s.wqkv != nullptr || l == 0, "latent_block_fwd_cluster: only the first layer may be MLP-only");
@@ -693,7 +734,8 @@ int latent_block_fwd_cluster(const float* x, const LatentFusedLayer* layers, int
         d.par[PAR_BO] = s.bo; d.par[PAR_LN2_W] = s.ln2_w; d.par[PAR_LN2_B] = s.ln2_b;
         d.par[PAR_B1] = s.b1; d.par[PAR_B2] = s.b2;
         if (l == 0 && first_mlp_only)
-            for (int k = 0; k < PAR_LN2_W; ++k) d.par[k] = s.ln2_w;  // (loaded with the rest, never used: any readable 256 floats)
+            for (int k = 0; k < PAR_LN2_W; ++k)
+                if (!(k == PAR_BO && first_mlp_only == 2)) d.par[k] = s.ln2_w;  // (loaded with the rest, never used: any readable 256 floats)
         d.sa_stats = s.sa_stats; d.mlp_stats = s.mlp_stats; d.lse = s.lse;
     }
     const LatentFusedLayer& f0 = layers[0];
@@ -719,7 +761,8 @@ int latent_block_fwd_cluster(const float* x, const LatentFusedLayer* layers, int
     p.n = n;
     p.total_rows = rows;
     p.scale_log2e = (1.0f / sqrtf((float)DH)) * 1.44269504088896340736f;
-    p.first_mlp_only = first_mlp_only ? 1 : 0;
+    p.first_mlp_only = first_mlp_only;
+    if (first_mlp_only == 2) PIO_TRY(make_out_map(&p.o_map, false, layers[0].pre_o16, C, rows, 1, C * 2, 256, 64, ROWS));
     int dev = 0;
     PIO_CUDA(cudaGetDevice(&dev));
     static std::atomic<bool> configured[64];

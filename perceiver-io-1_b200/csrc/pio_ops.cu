@@ -489,7 +489,8 @@ int pio_cross_attend_fwd(const float* x_q, const float* kv, const uint8_t* pad, 
                          void* saved, int batch, int n, int m, int e, int heads, int residual, const pio_dropout* drop,
                          int mode, void* ws, size_t ws_bytes, pio_stream_t stream) {
     PIO_TRY(check_mode(mode, "pio_cross_attend_fwd"));
-    PIO_CHECK_ARG(x_q && kv && y && w && saved && batch >= 0 && n >= 0 && m >= 0, "pio_cross_attend_fwd: bad arguments");
+    PIO_CHECK_ARG(x_q && kv && (y || residual == 2) && w && saved && batch >= 0 && n >= 0 && m >= 0, "pio_cross_attend_fwd: bad arguments");
+    PIO_CHECK_ARG(residual != 2 || mode == PIO_MODE_BF16, "pio_cross_attend_fwd: the deferred out-projection (residual = 2) needs PIO_MODE_BF16");
     PIO_TRY(check_heads(e, heads, "pio_cross_attend_fwd"));
     Ctx ctx(ws, ws_bytes, stream, drop);
     if (mode == PIO_MODE_BF16) return bf::cross_attend_fwd(ctx, x_q, kv, pad, y, w, saved, batch, n, m, e, heads, residual);
@@ -502,6 +503,7 @@ int pio_cross_attend_bwd(const float* dy, const float* x_q, const float* kv, con
                          size_t ws_bytes, pio_stream_t stream) {
     PIO_TRY(check_mode(mode, "pio_cross_attend_bwd"));
     PIO_CHECK_ARG(dy && x_q && kv && dx_q && dkv && w && saved && g, "pio_cross_attend_bwd: bad arguments");
+    PIO_CHECK_ARG(residual != 2 || mode == PIO_MODE_BF16, "pio_cross_attend_bwd: the deferred out-projection (residual = 2) needs PIO_MODE_BF16");
     PIO_TRY(check_heads(e, heads, "pio_cross_attend_bwd"));
     Ctx ctx(ws, ws_bytes, stream, drop);
     if (mode == PIO_MODE_BF16)
@@ -539,6 +541,8 @@ int pio_self_attn_bwd(const float* dy, const float* x, float* dx, const pio_attn
 }
 
 // ---- latent block
+size_t pio_cross_attend_o16_offset(int batch, int n, int e, int heads) { return bf::xa_o16_offset(batch, n, e, heads); }
+
 int pio_latent_block_cluster_ok(int layers, int batch, int n, int c, int heads) {
     const int64_t rows = (int64_t)batch * n;
     return layers >= 1 && layers <= PIO_LATENT_FUSED_MAX_LAYERS && latent_fused_supported(rows, n, c, heads, 0.f) && latent_cluster_preferred(rows) &&
@@ -588,11 +592,18 @@ size_t pio_latent_block_ws_bytes(int layers, int batch, int n, int c, int heads,
 int pio_latent_block_fwd(const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,
                          int layers, int batch, int n, int c, int heads, const pio_dropout* drop, int mode, void* ws,
                          size_t ws_bytes, pio_stream_t stream) {
+    return pio_latent_block_fwd_pre(x, y, attn, mlp, saved, layers, batch, n, c, heads, drop, mode, ws, ws_bytes, stream, nullptr);
+}
+
+int pio_latent_block_fwd_pre(const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,
+                             int layers, int batch, int n, int c, int heads, const pio_dropout* drop, int mode, void* ws,
+                             size_t ws_bytes, pio_stream_t stream, const void* pre_o16) {
     PIO_TRY(check_mode(mode, "pio_latent_block_fwd"));
     PIO_CHECK_ARG(x && y && attn && mlp && saved && layers >= 1 && batch >= 0 && n >= 0, "pio_latent_block_fwd: bad arguments");
     PIO_TRY(check_heads(c, heads, "pio_latent_block_fwd"));
     Ctx ctx(ws, ws_bytes, stream, drop);
-    if (mode == PIO_MODE_BF16) return bf::latent_block_fwd(ctx, x, y, attn, mlp, saved, layers, batch, n, c, heads);
+    if (mode == PIO_MODE_BF16) return bf::latent_block_fwd(ctx, x, y, attn, mlp, saved, layers, batch, n, c, heads, pre_o16);
+    PIO_CHECK_ARG(attn[0].wq != nullptr, "pio_latent_block_fwd: a first layer without attention weights needs PIO_MODE_BF16");
     BlockLayout L(batch, n, c, heads);
     const int64_t rows = (int64_t)batch * n;
     const float* cur = x;
@@ -615,12 +626,22 @@ int pio_latent_block_bwd(const float* dy, const float* x, float* dx, const pio_a
                          const void* saved, const pio_attn_grads* attn_g, const pio_mlp_grads* mlp_g, int accumulate,
                          int layers, int batch, int n, int c, int heads, const pio_dropout* drop, int mode, void* ws,
                          size_t ws_bytes, pio_stream_t stream) {
+    return pio_latent_block_bwd_pre(dy, x, dx, attn, mlp, saved, attn_g, mlp_g, accumulate, layers, batch, n, c, heads, drop, mode, ws,
+                                    ws_bytes, stream, nullptr, nullptr);
+}
+
+int pio_latent_block_bwd_pre(const float* dy, const float* x, float* dx, const pio_attn_weights* attn, const pio_mlp_weights* mlp,
+                             const void* saved, const pio_attn_grads* attn_g, const pio_mlp_grads* mlp_g, int accumulate,
+                             int layers, int batch, int n, int c, int heads, const pio_dropout* drop, int mode, void* ws,
+                             size_t ws_bytes, pio_stream_t stream, const void* pre_o16, void* pre_do16) {
     PIO_TRY(check_mode(mode, "pio_latent_block_bwd"));
     PIO_CHECK_ARG(dy && x && dx && attn && mlp && saved && attn_g && mlp_g && layers >= 1, "pio_latent_block_bwd: bad arguments");
     PIO_TRY(check_heads(c, heads, "pio_latent_block_bwd"));
     Ctx ctx(ws, ws_bytes, stream, drop);
     if (mode == PIO_MODE_BF16)
-        return bf::latent_block_bwd(ctx, dy, x, dx, attn, mlp, saved, attn_g, mlp_g, accumulate, layers, batch, n, c, heads);
+        return bf::latent_block_bwd(ctx, dy, x, dx, attn, mlp, saved, attn_g, mlp_g, accumulate, layers, batch, n, c, heads, pre_o16,
+                                    pre_do16);
+    PIO_CHECK_ARG(attn[0].wq != nullptr, "pio_latent_block_bwd: a first layer without attention weights needs PIO_MODE_BF16");
     BlockLayout L(batch, n, c, heads);
     const int64_t rows = (int64_t)batch * n;
     PIO_TAKE(dmid, ctx, (size_t)rows * c, "pio_latent_block_bwd");

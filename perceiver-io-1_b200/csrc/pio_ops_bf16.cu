@@ -388,6 +388,10 @@ struct XaSaved {
     }
 };
 size_t xa_saved_bytes(int batch, int n, int e, int heads) { return XaSaved(nullptr, batch, n, e, heads).total + 256; }
+size_t xa_o16_offset(int batch, int n, int e, int heads) {
+    char* const base = reinterpret_cast<char*>((uintptr_t)1 << 20);  // (any aligned non-null address: only the difference is used)
+    return (size_t)((char*)XaSaved(base, batch, n, e, heads).o16 - base);
+}
 size_t xa_ws_bytes(int batch, int n, int e, int heads) {
     const size_t r = (size_t)batch * n;
     return 2 * align_up(r * e * 2, 256) + 4 * align_up(r * e * 4, 256) + align_up((size_t)batch * heads * n * 4, 256) +
@@ -405,6 +409,7 @@ int cross_attend_fwd(Ctx& c, const float* x_q, const float* kv, const uint8_t* p
     pio_attn_desc a{};
     fill_attn(a, s.q, e, kv16, kv16 + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
     PIO_TRY(attention_fwd(a, s.o16, c.st, c.attn_drop()));
+    if (residual == 2) return PIO_OK;  // deferred out-projection: the caller takes the attention output (s.o16) from the saved buffer
     PIO_TRY(tc_xwT(c, s.o16, e, (const bf16*)w->wo, e, rows, e, e, y, e, nullptr, 0, w->bo, residual ? x_q : nullptr, e, 0,
                    nullptr, 0, residual ? c.drop_p : 0.f, c.drop_seed + 1));
     return PIO_OK;
@@ -423,16 +428,30 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
     PIO_TAKE_BYTES(float, dhq, c, (size_t)rows * e * 4, "pio_cross_attend_bwd");
     PIO_TAKE_BYTES(float, delta, c, (size_t)batch * heads * n * 4, "pio_cross_attend_bwd");
     Side side(c, acc);
-    const float* dyb;
-    PIO_TRY(branch_grad(c, dy, rows * e, residual, &dyb, "pio_cross_attend_bwd"));
-    PIO_TRY(cast_colsum_f32(dyb, e, dy16, e, g->bo, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
-    PIO_TRY(side.fork());
-    PIO_TRY(tc_dW(c, dy16, e, s.o16, e, g->wo, rows, e, e, acc, side.stream()));
     const bf16* kv16 = reinterpret_cast<const bf16*>(kv);
     bf16* dkv16 = reinterpret_cast<bf16*>(dkv);
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.q, e, kv16, kv16 + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
     const DropCfg adrop = c.attn_drop();
+    if (residual == 2) {
+        // deferred out-projection: `dy` IS the gradient of the attention output, bf16 (rows, e); the out-projection, its
+        // parameter gradients and the residual path belong to the caller (pio_latent_block_bwd_pre)
+        PIO_CHECK_ARG(attn_fwd_tc_supported(&b.fwd), "pio_cross_attend_bwd: the deferred out-projection needs the tensor-core attention kernels");
+        PIO_TRY(attn_bwd_tc(&b.fwd, reinterpret_cast<const bf16*>(dy), delta, dq16, dkv16, dkv16 + e, c.st, &adrop, s.o16));
+        PIO_TRY(side.fork());
+        PIO_TRY(side_colsum(c, side, dq16, e, g->bq, acc, rows, e));
+        PIO_TRY(tc_dW(c, dq16, e, s.hq, e, g->wq, rows, e, e, acc, side.stream()));
+        PIO_TRY(tc_dyW(c, dq16, e, (const bf16*)w->wq, e, rows, e, e, dhq, e, nullptr, 0, 0, nullptr, 0, 0));
+        PIO_TRY(pio_layernorm_bwd(dhq, x_q, s.stats, w->ln_w, nullptr, dx_q, g->ln_w, g->ln_b, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
+        PIO_TRY(side.join());
+        c.W.off = mark;
+        return PIO_OK;
+    }
+    const float* dyb;
+    PIO_TRY(branch_grad(c, dy, rows * e, residual, &dyb, "pio_cross_attend_bwd"));
+    PIO_TRY(cast_colsum_f32(dyb, e, dy16, e, g->bo, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
+    PIO_TRY(side.fork());
+    PIO_TRY(tc_dW(c, dy16, e, s.o16, e, g->wo, rows, e, e, acc, side.stream()));
     if (attn_fwd_tc_supported(&b.fwd)) {
         bf16* d_o16 = reinterpret_cast<bf16*>(d_o);  // the fp32 scratch is large enough for the bf16 tile
         PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)w->wo, e, rows, e, e, nullptr, 0, d_o16, e, 0, nullptr, 0, 0));
@@ -590,14 +609,18 @@ size_t block_ws_bytes(int layers, int batch, int n, int ch, int heads) {
 static bool mlp_only_layer(const pio_attn_weights& a) { return a.wq == nullptr; }
 
 int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,
-                     int layers, int batch, int n, int ch, int heads) {
+                     int layers, int batch, int n, int ch, int heads, const void* pre_o16) {
     BlockLayout L(batch, n, ch, heads);
     const int64_t rows = (int64_t)batch * n;
     const float* cur = x;
-    // An MLP-only first layer (attn[0].wq == null): the Residual(mlp) of the cross-attention layer in front of the block,
-    // handed over so that the fused kernels run it as half a layer.  Taken inside the cluster kernels when they run the
-    // whole block in one launch; otherwise as the MLP operator of its own, followed by the block.
+    // A first layer without an attention half of its own (attn[0].wq == null): the Residual(mlp) of the cross-attention
+    // layer in front of the block and, when attn[0].wo is given, that layer's out-projection + residual
+    // (x += pre_o16 Wo^T + bo with pre_o16 the attention output) before it — handed over so that the fused kernels run them
+    // as half a layer.  Taken inside the cluster kernels when they run the whole block in one launch; otherwise with the
+    // operators of their own, followed by the block.
     const bool pre = mlp_only_layer(attn[0]);
+    const bool pre_proj = pre && attn[0].wo != nullptr;
+    PIO_CHECK_ARG(!pre_proj || (pre_o16 != nullptr && attn[0].bo != nullptr), "pio_latent_block_fwd: an out-projection first layer needs the attention output");
     bool packed = true;
     for (int s = pre ? 1 : 0; s < layers; ++s) packed = packed && check_packed_self(&attn[s], ch, "pio_latent_block_fwd") == PIO_OK;
     const bool fused = packed && latent_fused_supported(rows, n, ch, heads, c.drop_p);
@@ -605,12 +628,18 @@ int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* a
     if (pre && !(fused && latent_cluster_preferred(rows) && layers <= PIO_LATENT_FUSED_MAX_LAYERS)) {
         char* slab = (char*)saved;
         float* out = (layers == 1) ? y : (float*)(slab + L.xnext);
+        float* xmid = (float*)(slab + L.xmid);
         const uint64_t seed0 = c.drop_seed;
+        if (pre_proj) {  // x_mid = x + O Wo^T + bo
+            PIO_TRY(tc_xwT(c, (const bf16*)pre_o16, ch, (const bf16*)attn[0].wo, ch, rows, ch, ch, xmid, ch, nullptr, 0, attn[0].bo, x, ch, 0,
+                           nullptr, 0));
+        } else {
+            // (the fused backward chain reads a layer's x_mid from its slab; for this layer that is the block's input)
+            PIO_CUDA(cudaMemcpyAsync(xmid, x, (size_t)rows * ch * sizeof(float), cudaMemcpyDeviceToDevice, c.st));
+        }
         c.drop_seed = seed0 + 2;
-        PIO_TRY(mlp_fwd(c, x, out, &mlp[0], slab + L.mlp, rows, ch, 1));
+        PIO_TRY(mlp_fwd(c, xmid, out, &mlp[0], slab + L.mlp, rows, ch, 1));
         c.drop_seed = seed0;
-        // (the fused backward chain reads a layer's x_mid from its slab; for this layer that is the block's input)
-        PIO_CUDA(cudaMemcpyAsync(slab + L.xmid, x, (size_t)rows * ch * sizeof(float), cudaMemcpyDeviceToDevice, c.st));
         cur = out;
         first = 1;
         if (layers == 1) return PIO_OK;
@@ -634,6 +663,7 @@ int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* a
                     f.xmid = (float*)(slab + L.xmid);
                     f.mlp_stats = ms.stats; f.mlp_h0 = ms.h0; f.mlp_h1 = ms.h1; f.mlp_g = ms.g;
                     f.xout = (s == layers - 1) ? y : (float*)(slab + L.xnext);
+                    f.pre_o16 = (s == 0) ? pre_o16 : nullptr;
                 }
                 PIO_TRY(latent_block_fwd_fused(cur, fl, cnt, batch, n, c.st));
                 cur = fl[cnt - 1].xout;
@@ -662,7 +692,8 @@ int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* a
 // kernel left in the workspace.
 static int latent_block_bwd_fused(Ctx& c, Side& side, const float* dy, const float* x, float* dx, const pio_attn_weights* attn,
                                   const pio_mlp_weights* mlp, const void* saved, const pio_attn_grads* attn_g,
-                                  const pio_mlp_grads* mlp_g, int layers, int batch, int n, int ch, int heads) {
+                                  const pio_mlp_grads* mlp_g, int layers, int batch, int n, int ch, int heads, const void* pre_o16,
+                                  void* pre_do16) {
     BlockLayout L(batch, n, ch, heads);
     const int64_t rows = (int64_t)batch * n;
     const size_t mark = c.W.off;
@@ -682,6 +713,7 @@ static int latent_block_bwd_fused(Ctx& c, Side& side, const float* dy, const flo
         b.mlp_stats = ms.stats; b.sa_stats = sa.stats; b.lse = sa.lse;
         b.mlp_h1 = ms.h1; b.xmid = (const float*)(slab + L.xmid); b.xnext = (const float*)(slab + L.xnext); b.qkv = sa.qkv;
         b.gy16 = g; b.gh16 = g + one; b.gmid16 = g + 2 * one; b.gqkv16 = g + 3 * one; b.gn2 = g + 6 * one; b.gn1 = g + 7 * one;
+        b.pre_do16 = (s == 0) ? pre_do16 : nullptr;
     }
     // the chain, from the last layers to the first, up to 8 layers per launch
     const float* grad = dy;
@@ -717,7 +749,10 @@ static int latent_block_bwd_fused(Ctx& c, Side& side, const float* dy, const flo
             dwi[nd++] = DwBatchItem{b.gy16, ch, ch, ms.g, ch, ch, mlp_g[s].w2, mlp_g[s].b2};
             dwi[nd++] = DwBatchItem{b.gh16, ch, ch, ms.h0, ch, ch, mlp_g[s].w1, mlp_g[s].b1};
             lni[nl++] = LnGradItem{b.gn2, b.xmid, b.mlp_stats, mlp_g[s].ln_w, mlp_g[s].ln_b};
-            if (mlp_only_layer(attn[s])) continue;
+            if (mlp_only_layer(attn[s])) {
+                if (attn[s].wo != nullptr) dwi[nd++] = DwBatchItem{b.gmid16, ch, ch, pre_o16, ch, ch, attn_g[s].wo, attn_g[s].bo};
+                continue;
+            }
             dwi[nd++] = DwBatchItem{b.gmid16, ch, ch, sa.o16, ch, ch, attn_g[s].wo, attn_g[s].bo};
             dwi[nd++] = DwBatchItem{b.gqkv16, 3 * ch, 3 * ch, sa.h0, ch, ch, attn_g[s].wq, attn_g[s].bq};
             lni[nl++] = LnGradItem{b.gn1, x_in, b.sa_stats, attn_g[s].ln_w, attn_g[s].ln_b};
@@ -733,7 +768,7 @@ static int latent_block_bwd_fused(Ctx& c, Side& side, const float* dy, const flo
 
 int latent_block_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_attn_weights* attn, const pio_mlp_weights* mlp,
                      const void* saved, const pio_attn_grads* attn_g, const pio_mlp_grads* mlp_g, int acc, int layers,
-                     int batch, int n, int ch, int heads) {
+                     int batch, int n, int ch, int heads, const void* pre_o16, void* pre_do16) {
     BlockLayout L(batch, n, ch, heads);
     const int64_t rows = (int64_t)batch * n;
     const bool pre = mlp_only_layer(attn[0]);
@@ -741,7 +776,8 @@ int latent_block_bwd(Ctx& c, const float* dy, const float* x, float* dx, const p
         bool packed = true;
         for (int s = pre ? 1 : 0; s < layers; ++s) packed = packed && check_packed_self(&attn[s], ch, "pio_latent_block_bwd") == PIO_OK;
         Side side(c, acc);
-        if (packed && side.active()) return latent_block_bwd_fused(c, side, dy, x, dx, attn, mlp, saved, attn_g, mlp_g, layers, batch, n, ch, heads);
+        if (packed && side.active())
+            return latent_block_bwd_fused(c, side, dy, x, dx, attn, mlp, saved, attn_g, mlp_g, layers, batch, n, ch, heads, pre_o16, pre_do16);
     }
     PIO_TAKE_BYTES(float, dmid, c, (size_t)rows * ch * 4, "pio_latent_block_bwd");
     PIO_TAKE_BYTES(float, dcur, c, (size_t)rows * ch * 4, "pio_latent_block_bwd");
@@ -754,9 +790,22 @@ int latent_block_bwd(Ctx& c, const float* dy, const float* x, float* dx, const p
         const char* slab = (const char*)saved + (size_t)s * L.per_layer;
         const float* x_in = (s == 0) ? x : (const float*)((const char*)saved + (size_t)(s - 1) * L.per_layer + L.xnext);
         const uint64_t seed0 = c.drop_seed;
-        if (s == 0 && pre) {  // the MLP-only first layer: its input is the block's input
+        if (s == 0 && pre) {  // the first layer without attention of its own
             c.drop_seed = seed0 + 2;
-            PIO_TRY(mlp_bwd(c, grad, x, dx, &mlp[0], slab + L.mlp, &mlp_g[0], acc, rows, ch, 1, grad16, nullptr));
+            if (attn[0].wo == nullptr) {  // MLP only: its input is the block's input
+                PIO_TRY(mlp_bwd(c, grad, x, dx, &mlp[0], slab + L.mlp, &mlp_g[0], acc, rows, ch, 1, grad16, nullptr));
+            } else {
+                // out-projection + MLP: the MLP's input is x_mid = x + O Wo^T + bo (in the slab); dx = g_mid, dO = g_mid Wo,
+                // dWo += g_mid^T O, dbo += column sums of g_mid
+                PIO_CHECK_ARG(pre_o16 != nullptr && pre_do16 != nullptr, "pio_latent_block_bwd: an out-projection first layer needs O and dO");
+                PIO_TRY(mlp_bwd(c, grad, (const float*)(slab + L.xmid), dx, &mlp[0], slab + L.mlp, &mlp_g[0], acc, rows, ch, 1, grad16, dmid16));
+                Side side(c, acc);
+                PIO_TRY(side.fork());
+                PIO_TRY(side_colsum(c, side, dmid16, ch, attn_g[0].bo, acc, rows, ch));
+                PIO_TRY(tc_dW(c, dmid16, ch, (const bf16*)pre_o16, ch, attn_g[0].wo, rows, ch, ch, acc, side.stream()));
+                PIO_TRY(tc_dyW(c, dmid16, ch, (const bf16*)attn[0].wo, ch, rows, ch, ch, nullptr, 0, (bf16*)pre_do16, ch, 0, nullptr, 0, 0));
+                PIO_TRY(side.join());
+            }
             c.drop_seed = seed0;
             break;
         }

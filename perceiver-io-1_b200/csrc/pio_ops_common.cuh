@@ -101,6 +101,7 @@ struct LatentFusedLayer {
     float* xmid;
     float* mlp_stats; void* mlp_h0; void* mlp_h1; void* mlp_g;
     float* xout;
+    const void* pre_o16;  // layer 0 as an out-projection + MLP first layer: the attention output (rows x C, bf16)
 };
 // one layer of the fused backward input-gradient chain (pio_latent_bwd_cl.cu): weights (bf16 shadows), saved forward
 // state, and the bf16 gradient tensors the kernel leaves for the parameter-gradient kernels (all [rows][C] except
@@ -114,6 +115,7 @@ struct LatentBwdLayer {
     const float* xnext;  // the layer's output (the LayerNorm-1 input of the NEXT layer)
     const void* qkv;
     void *gy16, *gh16, *gmid16, *gqkv16, *gn2, *gn1;
+    void* pre_do16;  // layer 0 as an out-projection + MLP first layer: the gradient of the attention output (rows x C, bf16), written
 };
 bool latent_bwd_cluster_supported(int64_t rows, int n, int ch, int heads, float drop_p);
 int latent_block_bwd_cluster(const float* dy, const float* x, float* dx, const LatentBwdLayer* layers, int nlayers, int batch, int n,
@@ -188,15 +190,16 @@ int self_attn_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* w, v
 int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_attn_weights* w, const void* saved,
                   const pio_attn_grads* g, int acc, int batch, int n, int ch, int heads, int residual,
                   const __nv_bfloat16* dy16_in = nullptr, __nv_bfloat16* dx16_out = nullptr);
+size_t xa_o16_offset(int batch, int n, int e, int heads);
 void set_side_join_deferred(int on);
 int side_join(cudaStream_t st);
 size_t block_saved_bytes(int layers, int batch, int n, int ch, int heads);
 size_t block_ws_bytes(int layers, int batch, int n, int ch, int heads);
 int latent_block_fwd(Ctx& c, const float* x, float* y, const pio_attn_weights* attn, const pio_mlp_weights* mlp, void* saved,
-                     int layers, int batch, int n, int ch, int heads);
+                     int layers, int batch, int n, int ch, int heads, const void* pre_o16 = nullptr);
 int latent_block_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_attn_weights* attn, const pio_mlp_weights* mlp,
                      const void* saved, const pio_attn_grads* attn_g, const pio_mlp_grads* mlp_g, int acc, int layers,
-                     int batch, int n, int ch, int heads);
+                     int batch, int n, int ch, int heads, const void* pre_o16 = nullptr, void* pre_do16 = nullptr);
 size_t linear_ws_bytes(int64_t rows, int c_in, int64_t c_out);
 int linear_fwd(Ctx& c, const float* x, const float* w16, const float* b, float* y, int64_t rows, int c_in, int64_t c_out);
 int linear_bwd(Ctx& c, const float* dy, const float* x, const float* w16, float* dx, float* dw, float* db, int acc, int64_t rows,

@@ -96,6 +96,12 @@ _SIGNATURES = {
     "pio_adamw_tick": (c_int, [P, P]),
     "pio_flat_copy_f32": (c_int, [P, P, P, c_int, c_int, ctypes.c_float, P]),
     "pio_scale3_f32": (c_int, [P, c_int64, P, c_int64, P, c_int64, P, P]),
+    "pio_latent_block_fwd_pre": (c_int, [P, P, POINTER(AttnWeights), POINTER(MlpWeights), P, c_int, c_int, c_int, c_int,
+                                     c_int, POINTER(Dropout), c_int, P, c_size_t, P, P]),
+    "pio_latent_block_bwd_pre": (c_int, [P, P, P, POINTER(AttnWeights), POINTER(MlpWeights), P, POINTER(AttnWeights),
+                                     POINTER(MlpWeights), c_int, c_int, c_int, c_int, c_int, c_int, POINTER(Dropout), c_int, P,
+                                     c_size_t, P, P, P]),
+    "pio_cross_attend_o16_offset": (c_size_t, [c_int, c_int, c_int, c_int]),
     "pio_latent_block_cluster_ok": (c_int, [c_int, c_int, c_int, c_int, c_int]),
     "pio_set_side_join_deferred": (c_int, [c_int]),
     "pio_side_join": (c_int, [P]),

@@ -700,13 +700,20 @@ class KVProjectFn(torch.autograd.Function):
 
 class CrossAttendFn(torch.autograd.Function):
     """Query side of Residual(CrossAttention) (reference model.py:77-99, :54-56): q_norm,
-    q in-projection, attention over the projected kv, out-projection, + x_q."""
+    q in-projection, attention over the projected kv, out-projection, + x_q.
+    ``residual=2`` (bf16 mode): stop after the attention and return its output (B, N, E) as bf16 — the out-projection,
+    its residual and their gradients then belong to the consumer (LatentBlockFn's first layer); ``wo`` / ``bo`` are None."""
 
     @staticmethod
     def forward(ctx, x_q, kv, pad, ln_w, ln_b, bias, w_packed, w_q, wo, bo, heads, residual, drop_p=0.0, drop_seed=0):
         mode = get_compute_mode()
         x_q, kv = _c(x_q), _c(kv, torch.float32 if mode == N.MODE_FP32 else torch.bfloat16)
-        ln_w, ln_b, bias, wo, bo = _c(ln_w), _c(ln_b), _c(bias), _c(wo), _c(bo)
+        ln_w, ln_b, bias = _c(ln_w), _c(ln_b), _c(bias)
+        deferred = int(residual) == 2
+        if deferred:
+            assert mode == N.MODE_BF16 and wo is None and bo is None
+        else:
+            wo, bo = _c(wo), _c(bo)
         w_packed = _c(w_packed) if w_packed is not None else None
         w_q = _c(w_q) if w_q is not None else None
         if pad is not None:
@@ -721,14 +728,17 @@ class CrossAttendFn(torch.autograd.Function):
         ctx.wstruct, ctx.keep = w, mats
         saved = _saved(L.pio_cross_attend_saved_bytes(b, n, m, e, heads, mode), x_q.device)
         ws = N.workspace(L.pio_cross_attend_ws_bytes(b, n, m, e, heads, mode), x_q.device)
-        y = torch.empty_like(x_q)
+        y = None if deferred else torch.empty_like(x_q)
         drop = _drop_struct(drop_p, drop_seed)
-        N.check(L.pio_cross_attend_fwd(x_q.data_ptr(), kv.data_ptr(), N.ptr(pad), y.data_ptr(), byref(w), saved.data_ptr(),
+        N.check(L.pio_cross_attend_fwd(x_q.data_ptr(), kv.data_ptr(), N.ptr(pad), N.ptr(y), byref(w), saved.data_ptr(),
                                        b, n, m, e, heads, int(residual), _dref(drop), mode, ws.data_ptr(), ws.numel(),
                                        N.stream_ptr(x_q.device)), "pio_cross_attend_fwd")
         ctx.save_for_backward(x_q, kv, pad, ln_w, ln_b, bias, w_packed, w_q, wo, bo)
         ctx.saved_buf = saved
         ctx.meta = (b, n, m, e, heads, int(residual), mode, drop)
+        if deferred:  # the attention output lives in the saved buffer
+            off = int(L.pio_cross_attend_o16_offset(b, n, e, heads))
+            return saved[off:off + b * n * e * 2].view(torch.bfloat16).view(b, n, e)
         return y
 
     @staticmethod
@@ -736,7 +746,7 @@ class CrossAttendFn(torch.autograd.Function):
     def backward(ctx, dy):
         x_q, kv, pad, ln_w, ln_b, bias, w_packed, w_q, wo, bo = ctx.saved_tensors
         b, n, m, e, heads, residual, mode, drop = ctx.meta
-        dy = _c(dy)
+        dy = _c(dy, torch.bfloat16 if residual == 2 else torch.float32)  # (deferred out-projection: the gradient of the attention output)
         L = N.lib()
         dev = x_q.device
         if mode == N.MODE_FP32:
@@ -834,11 +844,16 @@ class LatentBlockFn(torch.autograd.Function):
         keep = []
         for s in range(layers):
             p = params[s * _LAYER_PARAMS:(s + 1) * _LAYER_PARAMS]
-            if p[2] is not None:  # (an MLP-only first layer has no attention tensors: its struct stays all null)
+            if p[2] is not None:  # (a first layer without attention of its own has no in-projection: wq stays null)
                 fields = _sa_struct(*p[:6], c, mode)
                 keep.append(fields.pop("_keep"))
                 for k, v in fields.items():
                     setattr(attn[s], k, v if isinstance(v, int) or v is None else v.data_ptr())
+            elif p[4] is not None:  # ... but it may carry the out-projection of the cross-attention layer in front
+                wo_m = _mat(p[4], mode)
+                keep.append((wo_m,))
+                attn[s].wo = wo_m.data_ptr()
+                attn[s].bo = p[5].data_ptr()
             ops = _mlp_operands(p[6:], mode)
             keep.append(ops)
             for k, v in zip(N.MlpWeights._names, ops):
@@ -846,8 +861,9 @@ class LatentBlockFn(torch.autograd.Function):
         return attn, mlp, keep
 
     @staticmethod
-    def forward(ctx, x, heads, drop_p, drop_seed, *params):
+    def forward(ctx, x, o16, heads, drop_p, drop_seed, *params):
         x = _c(x)
+        o16 = None if o16 is None else _c(o16, torch.bfloat16)  # attention output whose out-projection the first layer applies
         params = [None if p is None else _c(p) for p in params]
         layers = len(params) // _LAYER_PARAMS
         assert layers * _LAYER_PARAMS == len(params) and layers >= 1
@@ -860,10 +876,10 @@ class LatentBlockFn(torch.autograd.Function):
         ws = N.workspace(L.pio_latent_block_ws_bytes(layers, b, n, c, heads, mode), x.device)
         y = torch.empty_like(x)
         drop = _drop_struct(drop_p, drop_seed)
-        N.check(L.pio_latent_block_fwd(x.data_ptr(), y.data_ptr(), attn, mlp, saved.data_ptr(), layers, b, n, c, heads,
-                                       _dref(drop), mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device)),
+        N.check(L.pio_latent_block_fwd_pre(x.data_ptr(), y.data_ptr(), attn, mlp, saved.data_ptr(), layers, b, n, c, heads,
+                                           _dref(drop), mode, ws.data_ptr(), ws.numel(), N.stream_ptr(x.device), N.ptr(o16)),
                 "pio_latent_block_fwd")
-        ctx.save_for_backward(x, *params)
+        ctx.save_for_backward(x, o16, *params)
         ctx.saved_buf = saved
         ctx.meta = (layers, b, n, c, heads, mode, drop)
         return y
@@ -871,12 +887,13 @@ class LatentBlockFn(torch.autograd.Function):
     @staticmethod
     @once_differentiable
     def backward(ctx, dy):
-        x, *params = ctx.saved_tensors
+        x, o16, *params = ctx.saved_tensors
         layers, b, n, c, heads, mode, drop = ctx.meta
         dy = _c(dy)
         L = N.lib()
         _flush_deferred()  # (an earlier block's deferred kernels read the workspace this call is about to reuse)
-        needs = ctx.needs_input_grad[4:]
+        needs = ctx.needs_input_grad[5:]
+        d_o16 = None if o16 is None else torch.empty_like(o16)
         grads, accf = _grads_like(params, mode, needs)
         dx = torch.empty_like(x)
         attn, mlp = ctx.wstructs
@@ -893,16 +910,16 @@ class LatentBlockFn(torch.autograd.Function):
         if defer:
             L.pio_set_side_join_deferred(1)
         try:
-            N.check(L.pio_latent_block_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), attn, mlp, ctx.saved_buf.data_ptr(), attn_g,
-                                           mlp_g, accf, layers, b, n, c, heads, _dref(drop), mode, ws.data_ptr(), ws.numel(),
-                                           N.stream_ptr(x.device)), "pio_latent_block_bwd")
+            N.check(L.pio_latent_block_bwd_pre(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), attn, mlp, ctx.saved_buf.data_ptr(), attn_g,
+                                               mlp_g, accf, layers, b, n, c, heads, _dref(drop), mode, ws.data_ptr(), ws.numel(),
+                                               N.stream_ptr(x.device), N.ptr(o16), N.ptr(d_o16)), "pio_latent_block_bwd")
         finally:
             if defer:
                 L.pio_set_side_join_deferred(0)
         if defer:
-            _defer(x.device, (ws, ctx.saved_buf, x, dy, params, grads))
+            _defer(x.device, (ws, ctx.saved_buf, x, o16, dy, params, grads))
         ctx.saved_buf = None
-        return _out(dx, None, None, None, *grads)
+        return _out(dx, d_o16, None, None, None, *grads)
 
 
 def label_compact(labels, classes, ignore_index=-100):

@@ -96,8 +96,10 @@ class CrossAttention(nn.Module):
             kv = self.project_kv(x_kv)
         w_packed, w_q, _, _ = a.packed()
         seed = F.next_dropout_seed() if p else 0
+        deferred = residual == 2  # (the consumer applies the out-projection: see SelfAttentionBlock.forward)
         return F.CrossAttendFn.apply(x_q, kv, pad_mask, self.q_norm.weight, self.q_norm.bias, a.in_proj_bias, w_packed,
-                                     w_q, a.out_proj.weight, a.out_proj.bias, a.num_heads, residual, p, seed)
+                                     w_q, None if deferred else a.out_proj.weight, None if deferred else a.out_proj.bias,
+                                     a.num_heads, residual, p, seed)
 
 
 class SelfAttention(nn.Module):
@@ -164,10 +166,16 @@ class SelfAttentionBlock(Sequential):
         heads = self[0][0].module.attention.attention.num_heads
         return bool(F.N.lib().pio_latent_block_cluster_ok(len(self) + 1, int(b), int(n), int(c), int(heads)))
 
-    def forward(self, x, pre=None):
+    def forward(self, x, pre=None, pre_attn=None, o16=None):
+        """``pre_attn`` / ``o16``: the CrossAttention in front and its attention output before the out-projection
+        (CrossAttendFn with residual=2): the first layer then also applies that out-projection and its residual."""
         params = []
         if pre is not None:
-            params.extend([None] * 6)
+            if pre_attn is not None:
+                a = pre_attn.attention.attention
+                params.extend([None, None, None, None, a.out_proj.weight, a.out_proj.bias])
+            else:
+                params.extend([None] * 6)
             params.extend(pre.module._params())
         for layer in self:
             sa, ff = layer[0], layer[1]
@@ -176,7 +184,7 @@ class SelfAttentionBlock(Sequential):
         heads = self[0][0].module.attention.attention.num_heads
         p = _active_p(self, self[0][0].dropout_p)
         seed = F.next_dropout_seed() if p else 0
-        return F.LatentBlockFn.apply(x, heads, p, seed, *params)
+        return F.LatentBlockFn.apply(x, o16, heads, p, seed, *params)
 
 
 def self_attention_block(num_layers: int, num_channels: int, num_heads: int, dropout: float):
@@ -215,11 +223,26 @@ class PerceiverEncoder(nn.Module):
     @staticmethod
     def _apply_layer(layer, x_latent, x, pad_mask, attn_mask, kv=None):
         cross, block = layer[0], layer[1]
+        if PerceiverEncoder._defer_out_proj(cross, block, x_latent):
+            ca = cross[0].module
+            o16 = ca(x_latent, x, pad_mask, attn_mask, kv=kv, residual=2, dropout_p=0.0)  # attention output, no out-projection
+            return block(x_latent, pre=cross[1], pre_attn=ca, o16=o16)
         x_latent = cross[0](x_latent, x, pad_mask, attn_mask, kv=kv)
         if isinstance(block, SelfAttentionBlock) and block.takes_pre_mlp(x_latent, cross[1]):
             return block(x_latent, pre=cross[1])  # the cross-attention layer's MLP rides on the block's fused kernels
         x_latent = cross[1](x_latent)
         return block(x_latent)
+
+    @staticmethod
+    def _defer_out_proj(cross, block, x_latent):
+        """The cross-attention layer's out-projection + residual can ride on the block's fused kernels too (tensor-core
+        attention head sizes, no dropout, the block takes the layer's MLP)."""
+        import os
+        ca = cross[0].module
+        a = ca.attention.attention
+        return (isinstance(block, SelfAttentionBlock) and os.environ.get("PIO_NO_PRE_PROJ") is None and
+                not _active_p(cross[0], cross[0].dropout_p) and (a.embed_dim // a.num_heads) in (32, 64, 128) and
+                block.takes_pre_mlp(x_latent, cross[1]))
 
     @_scoped
     def forward(self, x, pad_mask=None, attn_mask=None):

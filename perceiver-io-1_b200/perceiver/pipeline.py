@@ -101,7 +101,14 @@ class GraphedTrainStep:
             optimizer.zero_grad(set_to_none=True)
         self.graph = torch.cuda.CUDAGraph()
         before = N.lib().pio_launch_count()
-        with torch.cuda.graph(self.graph, capture_error_mode="thread_local" if self.world > 1 else "global"):
+        # The step is captured on a HIGH-priority stream: the library's side streams (parameter-gradient kernels) have the
+        # default, lowest priority, so when SMs free up the pending blocks of the main chain are placed first — after a
+        # latent block's backward chain the batched weight-gradient and LayerNorm-gradient kernels would otherwise keep
+        # the next operator's kernels waiting.
+        import os
+        prio = None if os.environ.get("PIO_NO_CAPTURE_PRIORITY") else -1
+        cap_stream = torch.cuda.Stream(dev, priority=prio) if prio is not None else torch.cuda.Stream(dev)
+        with torch.cuda.graph(self.graph, stream=cap_stream, capture_error_mode="thread_local" if self.world > 1 else "global"):
             self.loss = self._body()
         self.launches_per_replay = N.lib().pio_launch_count() - before  # kernels of this library inside one replay
 

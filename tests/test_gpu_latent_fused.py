@@ -133,3 +133,50 @@ def test_pre_mlp_rides_on_the_block(batch, n, layers):
     assert_rel(dx_f, dx_u, 1e-2, "dx")
     for k in g_u:
         assert_rel(g_f[k], g_u[k], 1.5e-2, f"grad {k}")
+
+
+@pytest.mark.parametrize("batch,n,m,layers,heads_x", [(2, 64, 96, 1, 4), (5, 32, 50, 2, 2), (64, 64, 512, 6, 4)])
+def test_cross_layer_out_projection_rides_on_the_block(batch, n, m, layers, heads_x):
+    """A whole encoder layer (cross_attention_layer + self_attention_block, reference model.py:29-44, :186-191) with the
+    cross-attention layer's out-projection, residual and MLP handed to the block's fused call, against the layer run
+    operator by operator."""
+    from perceiver.model import PerceiverEncoder, cross_attention_layer, self_attention_block
+    from perceiver.utils import Sequential
+    torch.manual_seed(7 * batch + n + m + layers)
+    layer = Sequential(cross_attention_layer(256, 256, heads_x, 0.0), self_attention_block(layers, 256, 4, 0.0)).to(DEV)
+    with torch.no_grad():
+        for k, p in layer.named_parameters():
+            if p.dim() == 1:
+                p.add_(torch.randn_like(p) * 0.1)
+    x_lat = torch.randn(batch, n, 256, device=DEV)
+    x_in = torch.randn(batch, m, 256, device=DEV)
+    pad = torch.zeros(batch, m, dtype=torch.bool, device=DEV)
+    pad[:, m - 5:] = True
+    dy = torch.randn(batch, n, 256, device=DEV)
+
+    def run(fused):
+        if fused:
+            os.environ.pop("PIO_NO_PRE_PROJ", None)
+            os.environ.pop("PIO_NO_PRE_MLP", None)
+        else:
+            os.environ["PIO_NO_PRE_PROJ"] = "1"
+            os.environ["PIO_NO_PRE_MLP"] = "1"
+        layer.zero_grad(set_to_none=True)
+        a = x_lat.clone().requires_grad_(True)
+        b = x_in.clone().requires_grad_(True)
+        y = PerceiverEncoder._apply_layer(layer, a, b, pad, None)
+        y.backward(dy)
+        torch.cuda.synchronize()
+        return y.detach(), a.grad.detach(), b.grad.detach(), {k: p.grad.detach().clone() for k, p in layer.named_parameters()}
+
+    try:
+        y_f, da_f, db_f, g_f = run(True)
+        y_u, da_u, db_u, g_u = run(False)
+    finally:
+        os.environ.pop("PIO_NO_PRE_PROJ", None)
+        os.environ.pop("PIO_NO_PRE_MLP", None)
+    assert_rel(y_f, y_u, 4e-3, "y")
+    assert_rel(da_f, da_u, 1e-2, "d latent")
+    assert_rel(db_f, db_u, 1.5e-2, "d input")
+    for k in g_u:
+        assert_rel(g_f[k], g_u[k], 1.5e-2, f"grad {k}")
