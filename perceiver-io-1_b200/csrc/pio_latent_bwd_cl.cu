@@ -23,8 +23,11 @@
 // bf16 (16 KB each) and adds the three it receives to its own fp32 slice.  LayerNorm backward needs two row sums over
 // all 256 channels: exchanged like the forward's statistics (st.async, 8 bytes per thread and peer).
 //
-// Left in global memory per layer for the parameter-gradient kernels: g (bf16; dW2 = g^T G, db2), dH (dW1, db1),
-// g_mid (dWo, dbo), [dQ | dK | dV] (dWqkv, dbqkv), dN2 and dN1 (bf16; LayerNorm dgamma / dbeta).
+// Left in global memory per layer for the batched weight-gradient kernel (pio_dw_batched.cu): g (bf16; dW2 = g^T G, db2),
+// dH (dW1, db1), g_mid (dWo, dbo), [dQ | dK | dV] (dWqkv, dbqkv).  The LayerNorm parameter gradients are formed here:
+// the column sums of dN and dN * xhat over a warp's 32 rows by a transposing shuffle butterfly, one atomic per lane
+// (a separate kernel over bf16 copies of dN took 36-60 us per block beside the attention backward of the next operator;
+// the sums cost ~0.8 K cycles per layer on the chain: step 1.902 -> 1.877 ms).
 //
 // Warp roles: warps 0..7 element-wise (TMEM lane quadrant = warp & 3, column half = warp >> 2), warp 8 = TMA producer
 // of the weights (6 x 8 KB ring), warp 9 = TMEM allocator + MMA issuer + TMA stores, warp 10 = TMA loads of the saved
@@ -68,6 +71,7 @@ struct LayerPtrs {
     const float* mlp_stats;  // (mean, rstd) per row
     const float* sa_stats;
     const float* lse;        // [sample][head][latent]
+    float *dln2_w, *dln2_b, *dln1_w, *dln1_b;  // LayerNorm parameter gradients (C each), added into with atomics
 };
 
 enum InMap : int { IM_H1 = 0, IM_XMID, IM_XNEXT, IM_X, IM_QKV, IM_COUNT };
@@ -521,16 +525,6 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
         // leaves as bf16 (dgamma / dbeta are formed from it by a kernel of their own): staged in the warp's own rows of
         // sX once it has read them (thread = row is the wrong shape for global stores), stored by TMA; the buffer is
         // released to the loader one phase later, when that store has read it (release_x).
-        bool x_pending = false;
-        auto release_x = [&]() {
-            if (x_pending) {
-                if (lane == 0) {
-                    lb::tma_store_wait_read();
-                    lb::mbar_arrive(x_free);
-                }
-                x_pending = false;
-            }
-        };
         auto ln_prefetch = [&](const float* gamma, const float* stats, float (&gm)[32], float2& ms) {
             ms = row_ok ? __ldg(reinterpret_cast<const float2*>(stats) + grow) : make_float2(0.f, 0.f);
 #pragma unroll
@@ -539,37 +533,43 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 gm[d] = t.x; gm[d + 1] = t.y; gm[d + 2] = t.z; gm[d + 3] = t.w;
             }
         };
-        auto ln_backward = [&](float (&dn)[32], const float (&gm)[32], const float2 ms, int which, int l, float (&v)[32]) {
+        // dgamma / dbeta: column sums over the warp's 32 rows by a transposing butterfly (31 shuffles: after the step with
+        // distance d a lane keeps the half of its columns selected by its bit d), lane j then adds column j's sum
+        auto col_sums_to = [&](float (&a)[32], float* dst) {
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) {
+                const bool up = (lane & off) != 0;
+#pragma unroll
+                for (int k = 0; k < off; ++k) {
+                    const float send = up ? a[k] : a[k + off];
+                    const float keep = up ? a[k + off] : a[k];
+                    a[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+                }
+            }
+            atomicAdd(dst + gcol + lane, a[0]);
+        };
+        auto ln_backward = [&](float (&dn)[32], const float (&gm)[32], const float2 ms, float* dgamma, float* dbeta, float (&v)[32]) {
             mbar_wait(x_full, x_phase);
             x_phase ^= 1u;
             float xh[32];
             uint8_t* mine = sX + cg * ATOM + q * 4096;  // this warp's 32 rows of its 32-column box
             lb::load_row_f32_smem(sX + cg * ATOM, row, xh);
             __syncwarp();
-            {   // dn as bf16, packed 32 rows x 64 bytes, over the rows just read
-                uint8_t* prow = mine + lane * 64;
+            if (lane == 0) lb::mbar_arrive(x_free);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    uint32_t u[4];
+            for (int i = 0; i < 32; ++i) xh[i] = (xh[i] - ms.x) * ms.y;
+            {
+                float t[32];
 #pragma unroll
-                    for (int e2 = 0; e2 < 4; ++e2) {
-                        __nv_bfloat162 h2 = __floats2bfloat162_rn(dn[i * 8 + 2 * e2], dn[i * 8 + 2 * e2 + 1]);
-                        u[e2] = *reinterpret_cast<uint32_t*>(&h2);
-                    }
-                    *reinterpret_cast<uint4*>(prow + i * 16) = make_uint4(u[0], u[1], u[2], u[3]);
-                }
-                fence_proxy_async();
-                __syncwarp();
-                if (lane == 0) {
-                    lb::tma_store_3d(&p.out[which], mine, gcol, tile * ROWS + q * 32, l);
-                    lb::tma_store_commit();
-                }
-                x_pending = true;
+                for (int i = 0; i < 32; ++i) t[i] = dn[i] * xh[i];
+                col_sums_to(t, dgamma);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) t[i] = dn[i];
+                col_sums_to(t, dbeta);
             }
             float s1 = 0.f, s2 = 0.f;
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
-                xh[i] = (xh[i] - ms.x) * ms.y;
                 dn[i] *= gm[i];
                 s1 += dn[i];
                 s2 = fmaf(dn[i], xh[i], s2);
@@ -609,7 +609,6 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
 
             // ---- dH = dG * gelu'(h) -> gather 2
             wait_mma();
-            release_x();  // (the previous layer's x rows served as staging for dN1)
             free_arrive();
             {
                 float t[32], h1[32];
@@ -631,7 +630,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
             {
                 float dn[32];
                 lb::ld_chunk(T_N + lane_off + (uint32_t)lcol, dn);
-                ln_backward(dn, gm, ms, OM_GN2, l, v);
+                ln_backward(dn, gm, ms, L.dln2_w, L.dln2_b, v);
                 if (l == 0 && p.first_mlp_only) {  // a first layer without attention of its own: this is the gradient of the block's input
                     if (row_ok) lb::store32_f32_global(p.dx + grow * C + gcol, v);
                     if (p.first_mlp_only == 1) break;
@@ -650,7 +649,6 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
 
             // ---- dO_r -> bf16 operand tile (over gelu')
             wait_mma();
-            release_x();  // (x_mid's rows served as staging for dN2: its store has long read them)
             {
                 float t[32];
                 lb::ld_chunk(T_O + lane_off + (uint32_t)lcol, t);
@@ -750,7 +748,7 @@ __global__ void __cluster_dims__(R, 1, 1) __launch_bounds__(THREADS, 1) latent_b
                 }
                 bar_ew();       // every warp of the CTA has read the received slices:
                 free_arrive();  // the reduce-scatter counts as consumed
-                ln_backward(dn, gm, ms, OM_GN1, l, v);
+                ln_backward(dn, gm, ms, L.dln1_w, L.dln1_b, v);
                 if (l > 0) {
                     lb::st_chunk(T_D + lane_off + (uint32_t)lcol, v);
                     tmem_st_wait();
@@ -908,6 +906,8 @@ int latent_block_bwd_cluster(const float* dy, const float* x, float* dx, const L
         PIO_TRY(make_tmap_bf16(&p.w[l][3], s.wqkv ? s.wqkv : s.w1, s.wqkv ? 3 * C : C, C, C, 16));
         LayerPtrs& d = p.layer[l];
         d.ln2_w = s.ln2_w; d.ln1_w = s.ln1_w; d.mlp_stats = s.mlp_stats; d.sa_stats = s.sa_stats; d.lse = s.lse;
+        d.dln2_w = s.dln2_w; d.dln2_b = s.dln2_b; d.dln1_w = s.dln1_w; d.dln1_b = s.dln1_b;
+        PIO_CHECK_ARG(d.dln2_w && d.dln2_b && (s.wqkv == nullptr || (d.dln1_w && d.dln1_b)), "latent_block_bwd_cluster: LayerNorm gradient destinations missing");
     }
     const LatentBwdLayer& f0 = layers[0];
     const LatentBwdLayer& f1 = layers[nlayers > 1 ? 1 : 0];
@@ -928,8 +928,6 @@ int latent_block_bwd_cluster(const float* dy, const float* x, float* dx, const L
     PIO_TRY(make_out_map(&p.out[OM_GH], false, f0.gh16, C, rows, nlayers, C * 2, stride_of(f0.gh16, f1.gh16), 64, ROWS));
     PIO_TRY(make_out_map(&p.out[OM_GMID], false, f0.gmid16, C, rows, nlayers, C * 2, stride_of(f0.gmid16, f1.gmid16), 64, ROWS));
     PIO_TRY(make_out_map(&p.out[OM_GQKV], false, f0.gqkv16, 3 * C, rows, nlayers, 3 * C * 2, stride_of(f0.gqkv16, f1.gqkv16), 64, ROWS));
-    PIO_TRY(make_out_map(&p.out[OM_GN2], false, f0.gn2, C, rows, nlayers, C * 2, stride_of(f0.gn2, f1.gn2), 32, 32, false));
-    PIO_TRY(make_out_map(&p.out[OM_GN1], false, f0.gn1, C, rows, nlayers, C * 2, stride_of(f0.gn1, f1.gn1), 32, 32, false));
     p.dy = dy;
     p.dx = dx;
     p.layers = nlayers;

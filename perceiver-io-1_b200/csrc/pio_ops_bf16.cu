@@ -714,6 +714,7 @@ static int latent_block_bwd_fused(Ctx& c, Side& side, const float* dy, const flo
         b.mlp_h1 = ms.h1; b.xmid = (const float*)(slab + L.xmid); b.xnext = (const float*)(slab + L.xnext); b.qkv = sa.qkv;
         b.gy16 = g; b.gh16 = g + one; b.gmid16 = g + 2 * one; b.gqkv16 = g + 3 * one; b.gn2 = g + 6 * one; b.gn1 = g + 7 * one;
         b.pre_do16 = (s == 0) ? pre_do16 : nullptr;
+        b.dln2_w = mlp_g[s].ln_w; b.dln2_b = mlp_g[s].ln_b; b.dln1_w = attn_g[s].ln_w; b.dln1_b = attn_g[s].ln_b;
     }
     // the chain, from the last layers to the first, up to 8 layers per launch
     const float* grad = dy;
@@ -738,27 +739,22 @@ static int latent_block_bwd_fused(Ctx& c, Side& side, const float* dy, const flo
     for (int hi = layers; hi > 0;) {
         const int lo = std::max(0, hi - PIO_LATENT_FUSED_MAX_LAYERS);
         DwBatchItem dwi[4 * PIO_LATENT_FUSED_MAX_LAYERS];
-        LnGradItem lni[2 * PIO_LATENT_FUSED_MAX_LAYERS];
-        int nd = 0, nl = 0;
+        int nd = 0;
         for (int s = hi - 1; s >= lo; --s) {
             const char* slab = (const char*)saved + (size_t)s * L.per_layer;
             SaSaved sa((void*)(slab + L.sa), batch, n, ch, heads);
             MlpSaved ms((void*)(slab + L.mlp), rows, ch);
             const LatentBwdLayer& b = bl[(size_t)s];
-            const float* x_in = (s == 0) ? x : bl[(size_t)s - 1].xnext;
             dwi[nd++] = DwBatchItem{b.gy16, ch, ch, ms.g, ch, ch, mlp_g[s].w2, mlp_g[s].b2};
             dwi[nd++] = DwBatchItem{b.gh16, ch, ch, ms.h0, ch, ch, mlp_g[s].w1, mlp_g[s].b1};
-            lni[nl++] = LnGradItem{b.gn2, b.xmid, b.mlp_stats, mlp_g[s].ln_w, mlp_g[s].ln_b};
             if (mlp_only_layer(attn[s])) {
                 if (attn[s].wo != nullptr) dwi[nd++] = DwBatchItem{b.gmid16, ch, ch, pre_o16, ch, ch, attn_g[s].wo, attn_g[s].bo};
                 continue;
             }
             dwi[nd++] = DwBatchItem{b.gmid16, ch, ch, sa.o16, ch, ch, attn_g[s].wo, attn_g[s].bo};
             dwi[nd++] = DwBatchItem{b.gqkv16, 3 * ch, 3 * ch, sa.h0, ch, ch, attn_g[s].wq, attn_g[s].bq};
-            lni[nl++] = LnGradItem{b.gn1, x_in, b.sa_stats, attn_g[s].ln_w, attn_g[s].ln_b};
         }
-        PIO_TRY(dw_batched(dwi, nd, rows, side.stream()));
-        PIO_TRY(ln_param_grads(lni, nl, rows, ch, side.stream2()));
+        PIO_TRY(dw_batched(dwi, nd, rows, side.stream()));  // (the LayerNorm parameter gradients were added by the chain kernel)
         hi = lo;
     }
     if (!t_defer_side_join) PIO_TRY(side.join());  // (deferred: the caller joins with pio_side_join)

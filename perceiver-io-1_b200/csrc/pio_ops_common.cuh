@@ -116,6 +116,7 @@ struct LatentBwdLayer {
     const void* qkv;
     void *gy16, *gh16, *gmid16, *gqkv16, *gn2, *gn1;
     void* pre_do16;  // layer 0 as an out-projection + MLP first layer: the gradient of the attention output (rows x C, bf16), written
+    float *dln2_w, *dln2_b, *dln1_w, *dln1_b;  // LayerNorm parameter gradients: added into by the chain kernel itself
 };
 bool latent_bwd_cluster_supported(int64_t rows, int n, int ch, int heads, float drop_p);
 int latent_block_bwd_cluster(const float* dy, const float* x, float* dx, const LatentBwdLayer* layers, int nlayers, int batch, int n,
