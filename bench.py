@@ -881,7 +881,7 @@ def main():
     ap.add_argument("--torch-optimizer", action="store_true", help="torch.optim.AdamW(fused=True) instead of perceiver.FusedAdamW")
     ap.add_argument("--flat-allreduce-after", action="store_true",
                     help="N > 1: previous scheme, one flat all-reduce after the captured graph instead of overlapped buckets")
-    ap.add_argument("--bucket-mb", type=int, default=24, help="gradient bucket size of the overlapped all-reduce")
+    ap.add_argument("--bucket-mb", type=int, default=16, help="gradient bucket size of the overlapped all-reduce")
     ap.add_argument("--timeline", default=None, help="with --profile-only: CSV of (stream, start_us, dur_us, kernel) of 2 more steps")
     ap.add_argument("--mode", default=os.environ.get("PIO_MODE", "bf16"), choices=["fp32", "bf16"])
     args = ap.parse_args()

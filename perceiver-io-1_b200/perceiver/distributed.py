@@ -118,7 +118,7 @@ class FlatGradients:
     still removes the per-operator gradient slabs and their zero-fill launches.
     Do not call ``zero_grad(set_to_none=True)`` afterwards: it would drop the views."""
 
-    def __init__(self, params, group: Optional[dist.ProcessGroup] = None, bucket_bytes: int = 24 << 20):
+    def __init__(self, params, group: Optional[dist.ProcessGroup] = None, bucket_bytes: int = 16 << 20):
         self.params = [p for p in params if p.requires_grad]
         if not self.params:
             raise ValueError("FlatGradients: no trainable parameters")

@@ -68,7 +68,7 @@ class GraphedTrainStep:
     Dropout seeds are launch arguments, so a replay repeats the captured masks: fine for timing, not for training with
     dropout > 0 (train those eagerly)."""
 
-    def __init__(self, params, optimizer, loss_fn, overlap_allreduce=True, bucket_bytes=24 << 20, warmup=3, before_warmup_step=None):
+    def __init__(self, params, optimizer, loss_fn, overlap_allreduce=True, bucket_bytes=16 << 20, warmup=3, before_warmup_step=None):
         import torch.distributed as dist
         from . import _native as N
         from .distributed import FlatGradients, average_gradients
@@ -152,7 +152,7 @@ class GraphedMLMStep(GraphedTrainStep):
       backward with every parameter gradient written in place into one flat buffer, the optimizer step, and for
       more than one rank the bucketed gradient all-reduce overlapped with the backward pass."""
 
-    def __init__(self, model, optimizer, ids, pad, overlap_allreduce=True, bucket_bytes=24 << 20, warmup=3):
+    def __init__(self, model, optimizer, ids, pad, overlap_allreduce=True, bucket_bytes=16 << 20, warmup=3):
         dev = next(model.parameters()).device
         self.model = model
         self.ids = torch.empty(ids.shape, dtype=torch.int64, device=dev)
