@@ -75,7 +75,7 @@ struct LayerPtrs {
 };
 
 enum InMap : int { IM_H1 = 0, IM_XMID, IM_XNEXT, IM_X, IM_QKV, IM_COUNT };
-enum OutMap : int { OM_GY = 0, OM_GH, OM_GMID, OM_GQKV, OM_GN2, OM_GN1, OM_COUNT };
+enum OutMap : int { OM_GY = 0, OM_GH, OM_GMID, OM_GQKV, OM_COUNT };
 
 struct Params {
     CUtensorMap w[PIO_LATENT_FUSED_MAX_LAYERS][4];  // W2, W1, Wo (256 x 256, boxes of 64 x 64), Wqkv (768 x 256, boxes of 64 columns x 16 rows)

@@ -597,9 +597,9 @@ struct BlockLayout {
 size_t block_saved_bytes(int layers, int batch, int n, int ch, int heads) {
     return (size_t)layers * BlockLayout(batch, n, ch, heads).per_layer + 256;
 }
-// bf16 gradient tensors the fused backward chain leaves per layer for the parameter-gradient kernels
-// (g, dH, g_mid, [dQ | dK | dV], dN2, dN1: eight [rows][C] tensors)
-static size_t block_bwd_layer_bytes(size_t r, int ch) { return 8 * align_up(r * ch * 2, 256); }
+// bf16 gradient tensors the fused backward chain leaves per layer for the batched weight-gradient kernel
+// (g, dH, g_mid, [dQ | dK | dV]: six [rows][C] tensors)
+static size_t block_bwd_layer_bytes(size_t r, int ch) { return 6 * align_up(r * ch * 2, 256); }
 size_t block_ws_bytes(int layers, int batch, int n, int ch, int heads) {
     const size_t r = (size_t)batch * n;
     return 2 * align_up(r * ch * 4, 256) + 2 * align_up(r * ch * 2, 256) + std::max(sa_ws_bytes(batch, n, ch, heads), mlp_ws_bytes(r, ch)) +
@@ -712,7 +712,7 @@ static int latent_block_bwd_fused(Ctx& c, Side& side, const float* dy, const flo
         b.ln2_w = mlp[s].ln_w; b.ln1_w = attn[s].ln_w;
         b.mlp_stats = ms.stats; b.sa_stats = sa.stats; b.lse = sa.lse;
         b.mlp_h1 = ms.h1; b.xmid = (const float*)(slab + L.xmid); b.xnext = (const float*)(slab + L.xnext); b.qkv = sa.qkv;
-        b.gy16 = g; b.gh16 = g + one; b.gmid16 = g + 2 * one; b.gqkv16 = g + 3 * one; b.gn2 = g + 6 * one; b.gn1 = g + 7 * one;
+        b.gy16 = g; b.gh16 = g + one; b.gmid16 = g + 2 * one; b.gqkv16 = g + 3 * one;
         b.pre_do16 = (s == 0) ? pre_do16 : nullptr;
         b.dln2_w = mlp_g[s].ln_w; b.dln2_b = mlp_g[s].ln_b; b.dln1_w = attn_g[s].ln_w; b.dln1_b = attn_g[s].ln_b;
     }

@@ -104,7 +104,7 @@ struct LatentFusedLayer {
     const void* pre_o16;  // layer 0 as an out-projection + MLP first layer: the attention output (rows x C, bf16)
 };
 // one layer of the fused backward input-gradient chain (pio_latent_bwd_cl.cu): weights (bf16 shadows), saved forward
-// state, and the bf16 gradient tensors the kernel leaves for the parameter-gradient kernels (all [rows][C] except
+// state, and the bf16 gradient tensors the kernel leaves for the batched weight-gradient kernel (all [rows][C] except
 // gqkv16 [rows][3C]; equally spaced over the layers, like the saved slabs)
 struct LatentBwdLayer {
     const void *w2, *w1, *wo, *wqkv;
@@ -114,7 +114,7 @@ struct LatentBwdLayer {
     const float* xmid;
     const float* xnext;  // the layer's output (the LayerNorm-1 input of the NEXT layer)
     const void* qkv;
-    void *gy16, *gh16, *gmid16, *gqkv16, *gn2, *gn1;
+    void *gy16, *gh16, *gmid16, *gqkv16;
     void* pre_do16;  // layer 0 as an out-projection + MLP first layer: the gradient of the attention output (rows x C, bf16), written
     float *dln2_w, *dln2_b, *dln1_w, *dln1_b;  // LayerNorm parameter gradients: added into by the chain kernel itself
 };
