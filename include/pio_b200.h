@@ -20,6 +20,9 @@
  *     partial sums + reduction pass), 2 = added to with fp32 atomics straight from the producing kernels
  *     (destinations must hold zeros or a running sum; no reduction passes; summation order, hence the last
  *     bits, vary run to run).  2 is honoured by the PIO_MODE_BF16 pipelines and treated as 1 elsewhere.
+ *     pio_kv_project_bwd and pio_cross_attend_bwd (PIO_MODE_BF16) also take, OR-ed in, PIO_ACC_DX and PIO_ACC_DKV:
+ *     the ACTIVATION gradient is added into what its buffer already holds instead of overwriting it (an input that a
+ *     second operator consumes too — the caller then has nothing left to sum).
  *   - `mode`: PIO_MODE_FP32 = fp32 FFMA arithmetic end to end (parity mode, rel 1e-4);
  *             PIO_MODE_BF16 = bf16 tcgen05 tensor-core contractions, fp32 accumulate/residual
  *             stream (performance mode, rel 1e-2).
@@ -408,7 +411,9 @@ size_t pio_kv_project_ws_bytes(int64_t rows, int c_kv, int e, int mode);
 int pio_kv_project_fwd(const float* x_kv, float* kv, const pio_attn_weights* w, void* saved,
                        int64_t rows, int c_kv, int e, int mode, void* ws, size_t ws_bytes,
                        pio_stream_t stream);
-/* dx_kv may be null (input needs no gradient, e.g. images). */
+/* dx_kv may be null (input needs no gradient, e.g. images).  accumulate | PIO_ACC_DX (bf16 mode): dx_kv += instead of =. */
+#define PIO_ACC_DX 4   /* the input gradient (dx_kv, dx_q) is added into its buffer */
+#define PIO_ACC_DKV 8  /* pio_cross_attend_bwd: the key/value gradient (bf16) is added into dkv */
 int pio_kv_project_bwd(const float* dkv, const float* x_kv, float* dx_kv, const pio_attn_weights* w,
                        const void* saved, const pio_attn_grads* g, int accumulate, int64_t rows,
                        int c_kv, int e, int mode, void* ws, size_t ws_bytes, pio_stream_t stream);
@@ -426,6 +431,9 @@ int pio_cross_attend_bwd(const float* dy, const float* x_q, const float* kv, con
                          const pio_attn_grads* g, int accumulate, int batch, int n, int m, int e,
                          int heads, int residual, const pio_dropout* drop, int mode, void* ws, size_t ws_bytes,
                          pio_stream_t stream);
+/* accumulate | PIO_ACC_DKV needs the tensor-core attention kernels (1 here: the shape has them); accumulate | PIO_ACC_DX
+ * needs residual = 2 (below), where dx_q carries no residual term of its own. */
+int pio_cross_attend_merges_dkv(int batch, int n, int m, int e, int heads);
 
 /* Residual(SelfAttention), model.py:102-116 + :54-56, one layer: y = out_proj(attn(qkv(LN(x)))) + x. */
 size_t pio_self_attn_saved_bytes(int batch, int n, int c, int heads, int mode);

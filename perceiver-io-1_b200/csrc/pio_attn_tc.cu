@@ -107,6 +107,21 @@ __device__ __forceinline__ void store_row64_bf16_global(__nv_bfloat16* dst, cons
     }
 }
 
+// v[0..32) += the 32 bf16 values at dst + c0
+__device__ __forceinline__ void add_row64_bf16_global(const __nv_bfloat16* dst, float (&v)[32], int c0) {
+#pragma unroll
+    for (int d = 0; d < 32; d += 8) {
+        const uint4 w = *reinterpret_cast<const uint4*>(dst + c0 + d);
+        const uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int e2 = 0; e2 < 4; ++e2) {
+            const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ws[e2]));
+            v[d + 2 * e2] += f.x;
+            v[d + 2 * e2 + 1] += f.y;
+        }
+    }
+}
+
 template <int BKV, bool DROP, int DH>
 __global__ void __launch_bounds__(FA_THREADS, DH == 128 ? 1 : 2)
     attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
@@ -370,6 +385,7 @@ struct FaBwdParams {
     int batch, heads, n, m;
     float scale, scale_log2e;
     DropCfg drop;
+    int dkv_add;             // dK / dV are added to what dk16 / dv16 hold (a second consumer of the same keys and values)
 };
 
 // dQ: CTA = 128 query rows of one (batch, head); streams key tiles of 64.
@@ -791,10 +807,14 @@ __global__ void __launch_bounds__(FA_THREADS, DH == 128 ? 1 : 2)
                 float v[32];
 #pragma unroll
                 for (int q = 0; q < 32; ++q) v[q] = __uint_as_float(rv[q]);
-                store_row64_bf16_global(p.dv16 + (int64_t)b * p.v_bs + (int64_t)key * p.v_rs + (int64_t)h * DH, v, c0);
+                __nv_bfloat16* dv_row = p.dv16 + (int64_t)b * p.v_bs + (int64_t)key * p.v_rs + (int64_t)h * DH;
+                if (p.dkv_add) add_row64_bf16_global(dv_row, v, c0);
+                store_row64_bf16_global(dv_row, v, c0);
 #pragma unroll
                 for (int q = 0; q < 32; ++q) v[q] = __uint_as_float(rk[q]);
-                store_row64_bf16_global(p.dk16 + (int64_t)b * p.k_bs + (int64_t)key * p.k_rs + (int64_t)h * DH, v, c0);
+                __nv_bfloat16* dk_row = p.dk16 + (int64_t)b * p.k_bs + (int64_t)key * p.k_rs + (int64_t)h * DH;
+                if (p.dkv_add) add_row64_bf16_global(dk_row, v, c0);
+                store_row64_bf16_global(dk_row, v, c0);
             }
         }
         tc_fence_before();
@@ -924,7 +944,7 @@ int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st, con
 
 // q, k, v, dO bf16; o fp32; lse fp32 -> dq16, dk16, dv16 (bf16, strides of q / k / v); delta scratch (batch, heads, n)
 int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta, __nv_bfloat16* dq16, __nv_bfloat16* dk16,
-                __nv_bfloat16* dv16, cudaStream_t st, const DropCfg* drop, const __nv_bfloat16* o16) {
+                __nv_bfloat16* dv16, cudaStream_t st, const DropCfg* drop, const __nv_bfloat16* o16, bool dkv_add) {
     PIO_CHECK_ARG(d && d->q && d->k && d->v && (d->o || o16) && d->lse && do16 && delta && dq16 && dk16 && dv16,
                   "attn_bwd_tc: null pointer");
     PIO_CHECK_ARG(attn_fwd_tc_supported(d), "attn_bwd_tc: unsupported shape (head dim %d)", d->dh);
@@ -939,6 +959,7 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
     p.scale = d->scale;
     p.scale_log2e = d->scale * 1.44269504088896340736f;
     p.drop = drop ? *drop : DropCfg{0, 0, 1.f};
+    p.dkv_add = dkv_add ? 1 : 0;
     {   // dQ + delta: 128-row query tiles, 64-row key tiles
         CUtensorMap tq, tdo, tk, tv;
         PIO_TRY(make_tmap3(&tq, d->q, cols, d->n, d->batch, d->q_rs, d->q_bs, FA_BQ));
@@ -976,5 +997,5 @@ extern "C" int pio_attn_bwd_bf16(const pio_attn_desc* fwd, const void* d_o16, vo
         return PIO_ERR_UNSUPPORTED;
     }
     return pio::attn_bwd_tc(fwd, (const __nv_bfloat16*)d_o16, delta, (__nv_bfloat16*)dq16, (__nv_bfloat16*)dk16,
-                            (__nv_bfloat16*)dv16, (cudaStream_t)stream, nullptr, nullptr);
+                            (__nv_bfloat16*)dv16, (cudaStream_t)stream, nullptr, nullptr, false);
 }

@@ -465,6 +465,8 @@ int pio_kv_project_bwd(const float* dkv, const float* x_kv, float* dx_kv, const 
     PIO_TRY(check_mode(mode, "pio_kv_project_bwd"));
     PIO_CHECK_ARG(dkv && x_kv && w && saved && g && rows >= 0 && c_kv > 0 && e > 0, "pio_kv_project_bwd: bad arguments");
     PIO_CHECK_ARG(g->kv_ln_w && g->kv_ln_b && g->wk && g->wv && g->bk && g->bv, "pio_kv_project_bwd: missing grads");
+    PIO_CHECK_ARG((accumulate & ~3) == 0 || (mode == PIO_MODE_BF16 && accumulate == (2 | PIO_ACC_DX) && dx_kv),
+                  "pio_kv_project_bwd: PIO_ACC_DX goes with PIO_MODE_BF16, accumulate = 2 and a dx_kv buffer");
     Ctx ctx(ws, ws_bytes, stream);
     if (mode == PIO_MODE_BF16) return bf::kv_project_bwd(ctx, dkv, x_kv, dx_kv, w, saved, g, accumulate, rows, c_kv, e);
     return kv_project_bwd(ctx, dkv, x_kv, dx_kv, w, saved, g, accumulate, rows, c_kv, e);
@@ -504,6 +506,9 @@ int pio_cross_attend_bwd(const float* dy, const float* x_q, const float* kv, con
     PIO_TRY(check_mode(mode, "pio_cross_attend_bwd"));
     PIO_CHECK_ARG(dy && x_q && kv && dx_q && dkv && w && saved && g, "pio_cross_attend_bwd: bad arguments");
     PIO_CHECK_ARG(residual != 2 || mode == PIO_MODE_BF16, "pio_cross_attend_bwd: the deferred out-projection (residual = 2) needs PIO_MODE_BF16");
+    PIO_CHECK_ARG((accumulate & ~3) == 0 || (mode == PIO_MODE_BF16 && (accumulate & ~(PIO_ACC_DX | PIO_ACC_DKV)) == 2),
+                  "pio_cross_attend_bwd: PIO_ACC_DX / PIO_ACC_DKV go with PIO_MODE_BF16 and accumulate = 2");
+    PIO_CHECK_ARG(!(accumulate & PIO_ACC_DX) || residual == 2, "pio_cross_attend_bwd: PIO_ACC_DX needs the deferred out-projection (residual = 2)");
     PIO_TRY(check_heads(e, heads, "pio_cross_attend_bwd"));
     Ctx ctx(ws, ws_bytes, stream, drop);
     if (mode == PIO_MODE_BF16)
@@ -542,6 +547,7 @@ int pio_self_attn_bwd(const float* dy, const float* x, float* dx, const pio_attn
 
 // ---- latent block
 size_t pio_cross_attend_o16_offset(int batch, int n, int e, int heads) { return bf::xa_o16_offset(batch, n, e, heads); }
+int pio_cross_attend_merges_dkv(int batch, int n, int m, int e, int heads) { return bf::xa_merges_dkv(batch, n, m, e, heads) ? 1 : 0; }
 
 int pio_latent_block_cluster_ok(int layers, int batch, int n, int c, int heads) {
     const int64_t rows = (int64_t)batch * n;

@@ -300,6 +300,10 @@ int kv_project_fwd(Ctx& c, const float* x_kv, float* kv, const pio_attn_weights*
 int kv_project_bwd(Ctx& c, const float* dkv, const float* x_kv, float* dx_kv, const pio_attn_weights* w, const void* saved,
                    const pio_attn_grads* g, int acc, int64_t rows, int ckv, int e) {
     PIO_TRY(need_mult8(e, "embed dim", "pio_kv_project_bwd"));
+    // PIO_ACC_DX: dx_kv already holds the other consumer's share; LayerNorm's backward adds it in as its residual term
+    // (every thread reads the elements it then writes, so the buffer may be both)
+    const float* dx_prev = (acc & PIO_ACC_DX) ? dx_kv : nullptr;
+    acc &= 3;
     KvSaved s((void*)saved, rows, ckv);
     const int64_t ckp = pad8(ckv);
     const size_t mark = c.W.off;
@@ -314,7 +318,7 @@ int kv_project_bwd(Ctx& c, const float* dkv, const float* x_kv, float* dx_kv, co
         PIO_TRY(dw_batched(&it, 1, rows, side.stream()));
         if (!xw_splitk_stores(rows, 2 * e)) PIO_CUDA(cudaMemsetAsync(dh0, 0, (size_t)rows * ckv * sizeof(float), c.st));
         PIO_TRY(xw_splitk(dkv16, 2 * e, w->wk, ckp, dh0, rows, 2 * e, c.st));
-        PIO_TRY(pio_layernorm_bwd(dh0, x_kv, s.stats, w->kv_ln_w, nullptr, dx_kv, g->kv_ln_w, g->kv_ln_b, acc, rows, ckv, c.rest(),
+        PIO_TRY(pio_layernorm_bwd(dh0, x_kv, s.stats, w->kv_ln_w, dx_prev, dx_kv, g->kv_ln_w, g->kv_ln_b, acc, rows, ckv, c.rest(),
                                   c.rest_bytes(), c.st));
         PIO_TRY(side.join());
         c.W.off = mark;
@@ -338,7 +342,7 @@ int kv_project_bwd(Ctx& c, const float* dkv, const float* x_kv, float* dx_kv, co
         PIO_TRY(tc_dyW(c, dkv16, 2 * e, (const bf16*)w->wk, ckp, rows, e, ckv, dh0, ckv, nullptr, 0, 0, nullptr, 0, 0));
         PIO_TRY(tc_dyW(c, dkv16 + e, 2 * e, (const bf16*)w->wv, ckp, rows, e, ckv, dh0, ckv, nullptr, 0, 0, nullptr, 0, 1));
     }
-    PIO_TRY(pio_layernorm_bwd(dh0, x_kv, s.stats, w->kv_ln_w, nullptr, dx_kv, g->kv_ln_w, g->kv_ln_b, acc, rows, ckv, c.rest(),
+    PIO_TRY(pio_layernorm_bwd(dh0, x_kv, s.stats, w->kv_ln_w, dx_prev, dx_kv, g->kv_ln_w, g->kv_ln_b, acc, rows, ckv, c.rest(),
                               c.rest_bytes(), c.st));
     PIO_TRY(side.join());
     c.W.off = mark;
@@ -392,6 +396,13 @@ size_t xa_o16_offset(int batch, int n, int e, int heads) {
     char* const base = reinterpret_cast<char*>((uintptr_t)1 << 20);  // (any aligned non-null address: only the difference is used)
     return (size_t)((char*)XaSaved(base, batch, n, e, heads).o16 - base);
 }
+bool xa_merges_dkv(int batch, int n, int m, int e, int heads) {  // the shapes whose backward runs on attn_bwd_tc
+    if (heads <= 0 || e % heads != 0 || e % 8 != 0) return false;
+    pio_attn_desc d{};
+    char* const base = reinterpret_cast<char*>((uintptr_t)1 << 20);
+    fill_attn(d, (const bf16*)base, e, (const bf16*)base, (const bf16*)base + e, 2 * e, nullptr, (float*)base, (float*)base, batch, heads, n, m, e);
+    return attn_fwd_tc_supported(&d);
+}
 size_t xa_ws_bytes(int batch, int n, int e, int heads) {
     const size_t r = (size_t)batch * n;
     return 2 * align_up(r * e * 2, 256) + 4 * align_up(r * e * 4, 256) + align_up((size_t)batch * heads * n * 4, 256) +
@@ -419,6 +430,8 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
                      const pio_attn_weights* w, const void* saved, const pio_attn_grads* g, int acc, int batch, int n, int m,
                      int e, int heads, int residual) {
     PIO_TRY(need_mult8(e, "embed dim", "pio_cross_attend_bwd"));
+    const bool dx_add = (acc & PIO_ACC_DX) != 0, dkv_add = (acc & PIO_ACC_DKV) != 0;  // see pio_b200.h
+    acc &= 3;
     XaSaved s((void*)saved, batch, n, e, heads);
     const int64_t rows = (int64_t)batch * n;
     const size_t mark = c.W.off;
@@ -433,16 +446,18 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
     pio_attn_bwd_desc b{};
     fill_attn(b.fwd, s.q, e, kv16, kv16 + e, 2 * e, pad, s.o, s.lse, batch, heads, n, m, e);
     const DropCfg adrop = c.attn_drop();
+    PIO_CHECK_ARG(!dkv_add || attn_fwd_tc_supported(&b.fwd), "pio_cross_attend_bwd: PIO_ACC_DKV needs the tensor-core attention kernels");
     if (residual == 2) {
         // deferred out-projection: `dy` IS the gradient of the attention output, bf16 (rows, e); the out-projection, its
         // parameter gradients and the residual path belong to the caller (pio_latent_block_bwd_pre)
         PIO_CHECK_ARG(attn_fwd_tc_supported(&b.fwd), "pio_cross_attend_bwd: the deferred out-projection needs the tensor-core attention kernels");
-        PIO_TRY(attn_bwd_tc(&b.fwd, reinterpret_cast<const bf16*>(dy), delta, dq16, dkv16, dkv16 + e, c.st, &adrop, s.o16));
+        PIO_TRY(attn_bwd_tc(&b.fwd, reinterpret_cast<const bf16*>(dy), delta, dq16, dkv16, dkv16 + e, c.st, &adrop, s.o16, dkv_add));
         PIO_TRY(side.fork());
         PIO_TRY(side_colsum(c, side, dq16, e, g->bq, acc, rows, e));
         PIO_TRY(tc_dW(c, dq16, e, s.hq, e, g->wq, rows, e, e, acc, side.stream()));
         PIO_TRY(tc_dyW(c, dq16, e, (const bf16*)w->wq, e, rows, e, e, dhq, e, nullptr, 0, 0, nullptr, 0, 0));
-        PIO_TRY(pio_layernorm_bwd(dhq, x_q, s.stats, w->ln_w, nullptr, dx_q, g->ln_w, g->ln_b, acc, rows, e, c.rest(), c.rest_bytes(), c.st));
+        PIO_TRY(pio_layernorm_bwd(dhq, x_q, s.stats, w->ln_w, dx_add ? dx_q : nullptr, dx_q, g->ln_w, g->ln_b, acc, rows, e, c.rest(),
+                                  c.rest_bytes(), c.st));
         PIO_TRY(side.join());
         c.W.off = mark;
         return PIO_OK;
@@ -455,7 +470,7 @@ int cross_attend_bwd(Ctx& c, const float* dy, const float* x_q, const float* kv,
     if (attn_fwd_tc_supported(&b.fwd)) {
         bf16* d_o16 = reinterpret_cast<bf16*>(d_o);  // the fp32 scratch is large enough for the bf16 tile
         PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)w->wo, e, rows, e, e, nullptr, 0, d_o16, e, 0, nullptr, 0, 0));
-        PIO_TRY(attn_bwd_tc(&b.fwd, d_o16, delta, dq16, dkv16, dkv16 + e, c.st, &adrop));
+        PIO_TRY(attn_bwd_tc(&b.fwd, d_o16, delta, dq16, dkv16, dkv16 + e, c.st, &adrop, nullptr, dkv_add));
     } else {
         PIO_TRY(tc_dyW(c, dy16, e, (const bf16*)w->wo, e, rows, e, e, d_o, e, nullptr, 0, 0, nullptr, 0, 0));
         b.d_o = d_o; b.delta = delta;

@@ -20,9 +20,11 @@ int attn_bwd_simt(const pio_attn_bwd_desc* d, cudaStream_t st, const AttnBf16Out
 bool attn_fwd_tc_supported(const pio_attn_desc* d);
 int attn_fwd_tc(const pio_attn_desc* d, __nv_bfloat16* o16, cudaStream_t st, const DropCfg* drop = nullptr);
 // tcgen05 backward: dO bf16 (strides of o), gradients bf16 with the strides of q / k / v
-// (o16 given: the row term delta = dO . O is formed from the bf16 copy of the output instead of d->o)
+// (o16 given: the row term delta = dO . O is formed from the bf16 copy of the output instead of d->o;
+//  dkv_add: dK and dV are added to what dk16 / dv16 hold — fp32 sum, one rounding)
 int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta, __nv_bfloat16* dq16, __nv_bfloat16* dk16,
-                __nv_bfloat16* dv16, cudaStream_t st, const DropCfg* drop = nullptr, const __nv_bfloat16* o16 = nullptr);
+                __nv_bfloat16* dv16, cudaStream_t st, const DropCfg* drop = nullptr, const __nv_bfloat16* o16 = nullptr,
+                bool dkv_add = false);
 
 int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream_t st);
 int cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_src, int64_t ld_dst, cudaStream_t st);
@@ -192,6 +194,7 @@ int self_attn_bwd(Ctx& c, const float* dy, const float* x, float* dx, const pio_
                   const pio_attn_grads* g, int acc, int batch, int n, int ch, int heads, int residual,
                   const __nv_bfloat16* dy16_in = nullptr, __nv_bfloat16* dx16_out = nullptr);
 size_t xa_o16_offset(int batch, int n, int e, int heads);
+bool xa_merges_dkv(int batch, int n, int m, int e, int heads);
 void set_side_join_deferred(int on);
 int side_join(cudaStream_t st);
 size_t block_saved_bytes(int layers, int batch, int n, int ch, int heads);

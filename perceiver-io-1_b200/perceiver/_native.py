@@ -16,6 +16,8 @@ LIB_PATH = os.environ.get("PIO_B200_LIB", os.path.join(_PKG_ROOT, "libpio_b200.s
 
 MODE_FP32 = 0
 MODE_BF16 = 1
+ACC_DX = 4   # PIO_ACC_DX: the activation gradient is added into its buffer
+ACC_DKV = 8  # PIO_ACC_DKV
 
 _lib = None
 _lock = threading.Lock()
@@ -102,6 +104,7 @@ _SIGNATURES = {
                                      POINTER(MlpWeights), c_int, c_int, c_int, c_int, c_int, c_int, POINTER(Dropout), c_int, P,
                                      c_size_t, P, P, P]),
     "pio_cross_attend_o16_offset": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "pio_cross_attend_merges_dkv": (c_int, [c_int, c_int, c_int, c_int, c_int]),
     "pio_latent_block_cluster_ok": (c_int, [c_int, c_int, c_int, c_int, c_int]),
     "pio_set_side_join_deferred": (c_int, [c_int]),
     "pio_side_join": (c_int, [P]),

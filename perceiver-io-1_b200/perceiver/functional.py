@@ -231,6 +231,7 @@ class _PassState:
         self.lock = threading.RLock()
         self.pending = {}  # (data_ptr, numel, device) of a parameter -> device address of its gradient buffer
         self.slabs = []    # keeps the memory behind those addresses alive for the pass
+        self.acts = {}     # activation with two consumers -> the gradient buffer its first backward returned (_act_pending)
         self._tls = threading.local()
 
     @property
@@ -352,6 +353,52 @@ def _forget_pending():
     with _PASS.lock:
         _PASS.pending.clear()
         _PASS.slabs.clear()
+        _PASS.acts.clear()
+
+
+# An ACTIVATION that two of these operators consume (the embedded input that both key/value projections read, the
+# projected kv that the two applications of the shared cross-attention layer read, the latent array that goes both into
+# the cross-attention and — as the residual — into the block behind it) gets the same treatment as a shared parameter:
+# the first backward that produces its gradient returns the buffer to autograd and publishes it here, the second adds its
+# contribution into that memory inside the kernel that computes it (PIO_ACC_DX / PIO_ACC_DKV) and reports None, so autograd
+# has nothing to sum — which was one full read-read-write pass over the activation per pair.
+#   * "Same activation" means the same autograd output (grad_fn and output number, both held by the entry), the same
+#     memory and the same shape; leaves and anything `_c` had to copy never match and take autograd's own summation.
+#   * The entry keeps the activation and its gradient alive until the end of the pass, so neither address can be
+#     handed to another tensor while a consumer may still look it up.
+#   * autograd stores the first gradient of an input as it is (no copy), which is what makes adding into it later
+#     the same as summing; bf16 mode only (the fp32 operators refuse the flags).
+_ACT_STATS = {"merged": 0}  # how many activation gradients were added in place (tests)
+
+
+def _act_key(x):
+    return (x.data_ptr(), tuple(x.shape), x.dtype, x.device)
+
+
+def _act_pending(x):
+    """the gradient buffer another operator of this backward pass already returned for activation ``x``, or None"""
+    if x.grad_fn is None or os.environ.get("PIO_NO_GRAD_MERGE") is not None:
+        return None
+    with _PASS.lock:
+        e = _PASS.acts.get(_act_key(x))
+    if e is not None and e[0] is x.grad_fn and e[1] == x.output_nr:
+        _ACT_STATS["merged"] += 1
+        return e[2]
+    return None
+
+
+def _act_publish(x, dx):
+    """first producer of ``x``'s gradient in this pass: later producers may add into ``dx`` (no-op outside a backward
+    pass, where nothing would clear the entry)"""
+    if x.grad_fn is None or dx is None or os.environ.get("PIO_NO_GRAD_MERGE") is not None:
+        return
+    with _PASS.lock:
+        if not _PASS.acts:
+            try:
+                torch.autograd.Variable._execution_engine.queue_callback(_forget_pending)
+            except RuntimeError:
+                return
+        _PASS.acts[_act_key(x)] = (x.grad_fn, x.output_nr, dx, x)
 
 
 def _grads_like(params, mode, needs=None):
@@ -686,15 +733,23 @@ class KVProjectFn(torch.autograd.Function):
         else:
             (dln_w, dln_b, dbias, dwp, dwk, dwv), accf = _grads_like((ln_w, ln_b, bias, w_packed, w_k, w_v), mode,
                                                                     ctx.needs_input_grad[1:7])
-        dx = torch.empty_like(x_kv) if ctx.needs_input_grad[0] else None
+        dx = merged = None
+        if ctx.needs_input_grad[0]:
+            merged = _act_pending(x_kv) if mode == N.MODE_BF16 else None  # the other key/value projection of the same input
+            dx = torch.empty_like(x_kv) if merged is None else merged
         _, gwk, gwv, _, gbk, gbv = _mha_ptrs(dwp, None, dwk, dwv, dbias, e)
         w = ctx.wstruct
         g = N.attn_struct(wk=gwk, wv=gwv, bk=gbk, bv=gbv, kv_ln_w=dln_w, kv_ln_b=dln_b)
         ws = N.workspace(L.pio_kv_project_ws_bytes(rows, ckv, e, mode), dev)
         N.check(L.pio_kv_project_bwd(dkv.data_ptr(), x_kv.data_ptr(), N.ptr(dx), byref(w), ctx.saved_buf.data_ptr(),
-                                     byref(g), accf, rows, ckv, e, mode, ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
+                                     byref(g), accf | (N.ACC_DX if merged is not None else 0), rows, ckv, e, mode,
+                                     ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
                 "pio_kv_project_bwd")
         ctx.saved_buf = None
+        if merged is not None:
+            dx = None
+        elif mode == N.MODE_BF16:
+            _act_publish(x_kv, dx)
         return _out(dx, dln_w, dln_b, dbias, dwp, dwk, dwv, None)
 
 
@@ -759,8 +814,12 @@ class CrossAttendFn(torch.autograd.Function):
         else:
             (dln_w, dln_b, dbias, dwp, dwq, dwo, dbo), accf = _grads_like((ln_w, ln_b, bias, w_packed, w_q, wo, bo), mode,
                                                                          ctx.needs_input_grad[3:10])
-        dx = torch.empty_like(x_q)
-        dkv = torch.empty_like(kv)
+        # x_q also feeds the block behind a deferred out-projection (its residual), kv the other application of a shared layer
+        dx_m = _act_pending(x_q) if residual == 2 else None
+        dkv_m = _act_pending(kv) if mode == N.MODE_BF16 and bool(L.pio_cross_attend_merges_dkv(b, n, m, e, heads)) else None
+        dx = torch.empty_like(x_q) if dx_m is None else dx_m
+        dkv = torch.empty_like(kv) if dkv_m is None else dkv_m
+        accf |= (N.ACC_DX if dx_m is not None else 0) | (N.ACC_DKV if dkv_m is not None else 0)
         gwq, _, _, gbq, _, _ = _mha_ptrs(dwp, dwq, None, None, dbias, e)
         w = ctx.wstruct
         g = N.attn_struct(ln_w=dln_w, ln_b=dln_b, wq=gwq, bq=gbq, wo=dwo, bo=dbo)
@@ -770,6 +829,14 @@ class CrossAttendFn(torch.autograd.Function):
                                        residual, _dref(drop), mode, ws.data_ptr(), ws.numel(), N.stream_ptr(dev)),
                 "pio_cross_attend_bwd")
         ctx.saved_buf = None
+        if dx_m is not None:
+            dx = None
+        elif residual == 2:
+            _act_publish(x_q, dx)
+        if dkv_m is not None:
+            dkv = None
+        elif mode == N.MODE_BF16:
+            _act_publish(kv, dkv)
         return _out(dx, dkv, None, dln_w, dln_b, dbias, dwp, dwq, dwo, dbo, None, None, None, None)
 
 
@@ -919,6 +986,8 @@ class LatentBlockFn(torch.autograd.Function):
         if defer:
             _defer(x.device, (ws, ctx.saved_buf, x, o16, dy, params, grads))
         ctx.saved_buf = None
+        if o16 is not None and mode == N.MODE_BF16:
+            _act_publish(x, dx)  # the cross-attention in front reads x too and adds its share into dx
         return _out(dx, d_o16, None, None, None, *grads)
 
 
