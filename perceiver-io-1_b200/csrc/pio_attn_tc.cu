@@ -949,6 +949,7 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
                   "attn_bwd_tc: null pointer");
     PIO_CHECK_ARG(attn_fwd_tc_supported(d), "attn_bwd_tc: unsupported shape (head dim %d)", d->dh);
     PIO_CHECK_ARG(d->heads <= 65535 && d->batch <= 65535, "attn_bwd_tc: batch/heads exceed grid limits");
+    if (xattn_bwd_tc_supported(d, drop)) return xattn_bwd_tc(d, do16, dq16, dk16, dv16, st, o16, dkv_add);  // (delta stays unused)
     const int64_t cols = (int64_t)d->heads * d->dh;
     FaBwdParams p{};
     p.pad = d->pad; p.o32 = d->o; p.o16 = o16; p.do16 = do16; p.lse = d->lse; p.delta = delta;

@@ -26,6 +26,12 @@ int attn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, float* delta,
                 __nv_bfloat16* dv16, cudaStream_t st, const DropCfg* drop = nullptr, const __nv_bfloat16* o16 = nullptr,
                 bool dkv_add = false);
 
+// every query of a sample in one 128-row tile (the latent array against the input), head size 64, no attention dropout:
+// one kernel, CTA = (sample, head), nothing recomputed (pio_xattn_tc.cu); attn_bwd_tc dispatches to it
+bool xattn_bwd_tc_supported(const pio_attn_desc* d, const DropCfg* drop);
+int xattn_bwd_tc(const pio_attn_desc* d, const __nv_bfloat16* do16, __nv_bfloat16* dq16, __nv_bfloat16* dk16, __nv_bfloat16* dv16,
+                 cudaStream_t st, const __nv_bfloat16* o16, bool dkv_add);
+
 int gemm_bf16(const pio_gemm_bf16_desc* d, void* ws, size_t ws_bytes, cudaStream_t st);
 int cast_bf16(const float* src, void* dst, int64_t rows, int cols, int64_t ld_src, int64_t ld_dst, cudaStream_t st);
 

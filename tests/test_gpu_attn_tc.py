@@ -114,10 +114,19 @@ def _ref_grads(q, k, v, do, pad, heads):
 @pytest.mark.parametrize("dh", [32, 64, 128])
 @pytest.mark.parametrize("b,n,m,heads,padded", [
     (2, 128, 64, 1, False), (2, 64, 512, 4, True), (2, 256, 1024, 2, False), (2, 70, 200, 2, True), (1, 1, 64, 1, False),
-    (2, 512, 64, 4, False), (1, 300, 1100, 2, True), (3, 64, 64, 4, False), (2, 256, 256, 4, False)])
-def test_flash_tc_backward(N, b, n, m, heads, padded, dh):
+    (2, 512, 64, 4, False), (1, 300, 1100, 2, True), (3, 64, 64, 4, False), (2, 256, 256, 4, False), (2, 100, 1100, 2, True),
+    (1, 128, 300, 3, False)])
+@pytest.mark.parametrize("one_tile_kernel", [True, False])
+def test_flash_tc_backward(N, b, n, m, heads, padded, dh, one_tile_kernel, monkeypatch):
     """dq, dk, dv of the tcgen05 backward against fp64 autograd over the same bf16-rounded q, k, v, dO.
-    The kernels round P, dS and the outputs to bf16, hence the bf16 tolerance.  Head sizes 64 and 128."""
+    The kernels round P, dS and the outputs to bf16, hence the bf16 tolerance.  Head sizes 64 and 128.
+    n <= 128 at head size 64 runs the (sample, head) kernel of pio_xattn_tc.cu unless switched off; everything else the
+    two general kernels."""
+    one_tile = n <= 128 and dh == 64
+    if not one_tile_kernel:
+        if not one_tile:
+            pytest.skip("same path as one_tile_kernel=True")
+        monkeypatch.setenv("PIO_NO_XATTN_TC", "1")
     torch.manual_seed(3)
     e = heads * dh
     q, kv, do = torch.randn(b, n, e), torch.randn(b, m, 2 * e), torch.randn(b, n, e)
@@ -145,7 +154,8 @@ def test_flash_tc_backward(N, b, n, m, heads, padded, dh):
     N.check(L.pio_attn_bwd_bf16(ctypes.byref(d), do16.data_ptr(), dq16.data_ptr(), dkv16.data_ptr(), dkv16.data_ptr() + 2 * e,
                                 delta.data_ptr(), N.stream_ptr()), "pio_attn_bwd_bf16")
     torch.cuda.synchronize()
-    assert_rel(delta, (o_ref * do16.double().cpu()).view(b, n, heads, dh).sum(-1).transpose(1, 2), 2e-2, "delta")
+    if not (one_tile and one_tile_kernel):  # (the one-tile kernel forms delta in registers)
+        assert_rel(delta, (o_ref * do16.double().cpu()).view(b, n, heads, dh).sum(-1).transpose(1, 2), 2e-2, "delta")
     assert_rel(dq16.float(), dq_ref, 2e-2, "dq")
     assert_rel(dkv16[..., :e].float(), dk_ref, 2e-2, "dk")
     assert_rel(dkv16[..., e:].float(), dv_ref, 2e-2, "dv")
