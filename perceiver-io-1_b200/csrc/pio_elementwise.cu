@@ -138,21 +138,30 @@ __global__ void text_embed_fwd_kernel(const int64_t* __restrict__ ids, const flo
 // small direct-mapped cache of embedding rows in shared memory (tag = id; a token whose slot is taken by
 // another id goes straight to global memory) and flushes the cache with one atomic per element at the end.
 constexpr int EMB_SLOTS = 16;
-__global__ void __launch_bounds__(256) text_embed_bwd_emb_kernel(const int64_t* __restrict__ ids, const float* __restrict__ dout,
-                                                                 float* __restrict__ demb, int64_t tokens, int c, int64_t vocab,
-                                                                 float scale, int slots) {
+constexpr int EMB_THREADS = 1024;  // 32 warps, one token each at a time: the kernel is a chain of dependent loads per token
+                                   // (id -> tag -> row), so it lives on how many rows are in flight (56 us with 8 warps)
+__global__ void __launch_bounds__(EMB_THREADS) text_embed_bwd_emb_kernel(const int64_t* __restrict__ ids, const float* __restrict__ dout,
+                                                                         float* __restrict__ demb, int64_t tokens, int c, int64_t vocab,
+                                                                         float scale, int slots) {
     extern __shared__ float s_cache[];  // [slots][c]
     __shared__ long long s_tag[EMB_SLOTS];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
     for (int i = threadIdx.x; i < slots * c; i += blockDim.x) s_cache[i] = 0.f;
     if (threadIdx.x < EMB_SLOTS) s_tag[threadIdx.x] = -1;
     __syncthreads();
+    const bool vec4 = (c & 3) == 0 && c <= 512 && ((((uintptr_t)dout) | ((uintptr_t)demb)) & 15) == 0;
     const int64_t per = (tokens + gridDim.x - 1) / gridDim.x;  // a contiguous run of tokens per block
     const int64_t t_end = min(tokens, (int64_t)(blockIdx.x + 1) * per);
     for (int64_t t = (int64_t)blockIdx.x * per + wid; t < t_end; t += nw) {
         int64_t id = ids[t];
         id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
         const float* g = dout + t * c;
+        float4 v[4];  // (vec4) the row, read before the slot is known: 16 bytes per lane and 128 channels
+        if (vec4) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (lane * 4 + 128 * k < c) v[k] = *reinterpret_cast<const float4*>(g + lane * 4 + 128 * k);
+        }
         int slot = -1;
         if (slots > 0) {
             // the lowest ids are the tokenizer's special tokens ([PAD], [UNK], [MASK], ...: reference tokenizer.py puts
@@ -165,11 +174,25 @@ __global__ void __launch_bounds__(256) text_embed_bwd_emb_kernel(const int64_t* 
             old = __shfl_sync(0xffffffffu, old, 0);
             if (old == -1 || old == id) slot = cand;
         }
-        if (slot >= 0) {
-            float* d = s_cache + (size_t)slot * c;
-            for (int j = lane; j < c; j += 32) atomicAdd(d + j, g[j] * scale);
+        if (vec4) {
+            float* d = (slot >= 0 ? s_cache + (size_t)slot * c : demb + id * c) + lane * 4;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (lane * 4 + 128 * k < c) {
+                    if (slot >= 0) {
+                        atomicAdd(d + 128 * k, v[k].x * scale);
+                        atomicAdd(d + 128 * k + 1, v[k].y * scale);
+                        atomicAdd(d + 128 * k + 2, v[k].z * scale);
+                        atomicAdd(d + 128 * k + 3, v[k].w * scale);
+                    } else {  // most tokens of a block are distinct ids and end up here: one 16-byte reduction per lane
+                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d + 128 * k), "f"(v[k].x * scale), "f"(v[k].y * scale),
+                                     "f"(v[k].z * scale), "f"(v[k].w * scale)
+                                     : "memory");
+                    }
+                }
+            }
         } else {
-            float* d = demb + id * c;
+            float* d = slot >= 0 ? s_cache + (size_t)slot * c : demb + id * c;
             for (int j = lane; j < c; j += 32) atomicAdd(d + j, g[j] * scale);
         }
     }
@@ -750,7 +773,7 @@ int pio_text_embed_bwd(const int64_t* ids, const float* dout, float* demb, float
         // blocks own >= 64 tokens each so the per-block cache has duplicates to absorb
         const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>(cdiv(tokens, 64), (int64_t)num_sms() * 2));
         const int slots = c <= 512 ? EMB_SLOTS : (c <= 2048 ? 4 : 0);
-        text_embed_bwd_emb_kernel<<<blocks, threads, (size_t)slots * c * sizeof(float), (cudaStream_t)stream>>>(
+        text_embed_bwd_emb_kernel<<<blocks, EMB_THREADS, (size_t)slots * c * sizeof(float), (cudaStream_t)stream>>>(
             ids, dout, demb, tokens, c, vocab, scale, slots);
         PIO_LAUNCH_CHECK();
     }
