@@ -82,6 +82,30 @@ __device__ __forceinline__ void store_half_row_packed(uint8_t* atom, int row, in
     }
 }
 
+// mbarrier wait with a watchdog: every wait in this kernel is for work that takes microseconds, so two seconds of spinning
+// can only be a protocol fault — trap (the launch fails with an error) instead of hanging the GPU
+__device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, P1;\n\t"
+        "}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void wait(uint64_t* bar, uint32_t parity) {
+    if (mbar_try(bar, parity)) return;
+    const long long t0 = clock64();
+    uint32_t spins = 0;
+    while (!mbar_try(bar, parity)) {
+        if ((++spins & 1023u) == 0 && clock64() - t0 > 4000000000ll) __trap();
+    }
+}
+
 __device__ __forceinline__ void pack32(const float (&v)[32], uint32_t (&w)[16]) {
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
@@ -180,7 +204,7 @@ __global__ void __launch_bounds__(THREADS, 1)
             lb::tma_load_3d(sDO, &tmDO, h * DH, 0, b, q_full);
             for (int j = 0; j < tiles; ++j) {
                 const int st = j % STAGES;
-                if (j >= STAGES) mbar_wait(kv_free + st, (uint32_t)(j / STAGES - 1) & 1u);
+                if (j >= STAGES) wait(kv_free + st, (uint32_t)(j / STAGES - 1) & 1u);
                 mbar_expect_tx(kv_full + st, 2 * ATOM);
                 lb::tma_load_3d(sK + st * ATOM, &tmK, h * DH, j * ROWS, b, kv_full + st);
                 lb::tma_load_3d(sV + st * ATOM, &tmV, h * DH, j * ROWS, b, kv_full + st);
@@ -196,7 +220,7 @@ __global__ void __launch_bounds__(THREADS, 1)
             const uint32_t pt_addr = smem_u32(sPT), dst_addr = smem_u32(sDST);
             auto issue_s = [&](int j) {  // S^T = K Q^T, dP^T = V dO^T of tile j
                 const uint32_t k_addr = smem_u32(sK + (j % STAGES) * ATOM), v_addr = smem_u32(sV + (j % STAGES) * ATOM);
-                mbar_wait(kv_full + j % STAGES, (uint32_t)(j / STAGES) & 1u);
+                wait(kv_full + j % STAGES, (uint32_t)(j / STAGES) & 1u);
                 tc_fence_after();
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
@@ -206,16 +230,16 @@ __global__ void __launch_bounds__(THREADS, 1)
                     umma_bf16(T_P, make_smem_desc(v_addr + k * 32, 16, 1024), make_smem_desc(do_addr + k * 32, 16, 1024), idesc_s, k > 0 ? 1u : 0u);
                 umma_commit(s_done);
             };
-            mbar_wait(q_full, 0);
+            wait(q_full, 0);
             issue_s(0);
             for (int j = 0; j < tiles; ++j) {
                 const uint32_t k_addr = smem_u32(sK + (j % STAGES) * ATOM);
                 if (j + 1 < tiles) {  // S^T, dP^T of the next tile go in FRONT of this tile's gradient products: they only need
-                    mbar_wait(s_free, (uint32_t)j & 1u);  // tile j's to have been read into registers, and the
+                    wait(s_free, (uint32_t)j & 1u);  // tile j's to have been read into registers, and the
                     issue_s(j + 1);                       // element-wise warps work on them while the products run
                 }
                 XT(8 * j + 5);
-                mbar_wait(ew_p, (uint32_t)j & 1u);  // P^T, dS^T of tile j written; dK, dV of tile j - 1 drained
+                wait(ew_p, (uint32_t)j & 1u);  // P^T, dS^T of tile j written; dK, dV of tile j - 1 drained
                 tc_fence_after();
                 XT(8 * j + 6);
                 for (int s = 0; s < qsteps; ++s)  // dK = dS^T Q: 16 queries per step
@@ -325,7 +349,7 @@ __global__ void __launch_bounds__(THREADS, 1)
         for (int j = 0; j < tiles; ++j) {
             uint32_t pw[CH][16], dw[CH][16];  // this thread's key against CH x 32 queries: probabilities and score gradients, bf16 pairs
             const bool key_ok = sOk[j * ROWS + row] != 0;
-            mbar_wait(s_done, (uint32_t)j & 1u);
+            wait(s_done, (uint32_t)j & 1u);
             tc_fence_after();
             if (threadIdx.x == 0) XT(8 * j);
 #pragma unroll
@@ -363,7 +387,7 @@ __global__ void __launch_bounds__(THREADS, 1)
             }
             if (threadIdx.x == 0) XT(8 * j + 1);
             if (j > 0) {  // the previous tile's gradient products have run: its dK, dV leave, and sPT / sDST may be rewritten
-                mbar_wait(g_done, (uint32_t)(j - 1) & 1u);
+                wait(g_done, (uint32_t)(j - 1) & 1u);
                 tc_fence_after();
                 if (threadIdx.x == 0) XT(8 * j + 2);
                 drain(j - 1);
@@ -380,7 +404,7 @@ __global__ void __launch_bounds__(THREADS, 1)
             signal(ew_p);
             if (threadIdx.x == 0) XT(8 * j + 4);
         }
-        mbar_wait(g_done, (uint32_t)(tiles - 1) & 1u);
+        wait(g_done, (uint32_t)(tiles - 1) & 1u);
         tc_fence_after();
         drain(tiles - 1);
         {   // dQ_h, accumulated over all tiles: lanes = queries
