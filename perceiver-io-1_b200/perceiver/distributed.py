@@ -128,6 +128,9 @@ class FlatGradients:
         self.flat = None
         self.handles = []
         self.fired = 0
+        # called as on_ready(bucket, handle) when a bucket's gradients are final on this rank and — more than one rank — its
+        # all-reduce has been issued (``handle``: wait on it from the stream that consumes the bucket; None with one rank)
+        self.on_ready = None
 
     # ------------------------------------------------------------------ profiling pass
     def profile(self):
@@ -212,21 +215,30 @@ class FlatGradients:
         if self.remaining[b] == 0:
             self._reduce(b)
 
+    def bucket_params(self, b):
+        """the parameters whose gradients live in bucket ``b``"""
+        from . import functional as F
+        return [p for p in self.params if self.bucket_of[F._pkey(p)] == b]
+
     def _reduce(self, b):
         self.fired |= 1 << b
         if self.world == 1:
+            if self.on_ready is not None:
+                self.on_ready(b, None)
             return
         view = self.views[b]
         nccl = dist.get_backend(self.group) == "nccl"
         op = dist.ReduceOp.AVG if nccl else dist.ReduceOp.SUM
         if self.comm is None:  # CPU tensors (gloo tests)
             self.handles.append(dist.all_reduce(view, op=op, group=self.group, async_op=True))
-            return
-        ev = torch.cuda.Event()
-        ev.record(torch.cuda.current_stream(view.device))  # everything the backward pass has enqueued so far
-        self.comm.wait_event(ev)
-        with torch.cuda.stream(self.comm):
-            self.handles.append(dist.all_reduce(view, op=op, group=self.group, async_op=True))
+        else:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(view.device))  # everything the backward pass has enqueued so far
+            self.comm.wait_event(ev)
+            with torch.cuda.stream(self.comm):
+                self.handles.append(dist.all_reduce(view, op=op, group=self.group, async_op=True))
+        if self.on_ready is not None:
+            self.on_ready(b, self.handles[-1])
 
     def step_end(self):
         """after loss.backward(): reduce what has not been reduced yet (buckets of parameters no operator reported),

@@ -92,10 +92,9 @@ class FusedAdamW(torch.optim.Optimizer):
         """Mirror ``param_groups`` (lr, betas, eps, weight_decay — e.g. after ``scheduler.step()``) into the device
         buffers the kernel reads.  ``step()`` does this itself; a step REPLAYED from a CUDA graph does not run any
         Python, so call this before ``graph.replay()`` whenever a scheduler changed the values."""
-        for gi, group in enumerate(self.param_groups):
-            plan = self._plans.get(gi)
-            if plan is None:
-                continue
+        for key, plan in self._plans.items():
+            gi = key[1] if isinstance(key, tuple) else key  # (subset key, group index) for step_params plans
+            group = self.param_groups[gi]
             hp = (float(group["lr"]), float(group["betas"][0]), float(group["betas"][1]), float(group["eps"]),
                   float(group["weight_decay"]))
             if hp != plan["hyper_host"]:
@@ -107,22 +106,38 @@ class FusedAdamW(torch.optim.Optimizer):
         super().load_state_dict(state_dict)
         self._plans = {}
 
+    def _launch(self, key, group, params):
+        L = N.lib()
+        plan = self._plan(key, group, params)
+        st = N.stream_ptr(params[0].device)
+        N.check(L.pio_adamw_step(plan["table"].data_ptr(), plan["chunks"].data_ptr(), plan["n_chunks"], plan["hyper"].data_ptr(), st),
+                "pio_adamw_step")
+        N.check(L.pio_adamw_tick(plan["hyper"].data_ptr(), st), "pio_adamw_tick")
+        for p in plan["shadowed"]:  # their bf16 shadows are current: the next training forward need not re-cast them
+            p._pio_fresh16 = True
+
     @torch.no_grad()
     def step(self, closure=None):
         loss = None
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
-        L = N.lib()
         for gi, group in enumerate(self.param_groups):
             params = [p for p in group["params"] if p.grad is not None]
-            if not params:
-                continue
-            plan = self._plan(gi, group, params)
-            st = N.stream_ptr(params[0].device)
-            N.check(L.pio_adamw_step(plan["table"].data_ptr(), plan["chunks"].data_ptr(), plan["n_chunks"], plan["hyper"].data_ptr(), st),
-                    "pio_adamw_step")
-            N.check(L.pio_adamw_tick(plan["hyper"].data_ptr(), st), "pio_adamw_tick")
-            for p in plan["shadowed"]:  # their bf16 shadows are current: the next training forward need not re-cast them
-                p._pio_fresh16 = True
+            if params:
+                self._launch(gi, group, params)
         return loss
+
+    @torch.no_grad()
+    def step_params(self, params, key):
+        """The same update for a SUBSET of the parameters, on the current stream: one launch per parameter group that
+        has members in ``params``.  ``key`` names the subset (its launch plan — chunk table, pointer table, device
+        step counter — is kept under it), so call it with the same subsets every step: `GraphedTrainStep` steps each
+        gradient bucket of `FlatGradients` as soon as the backward pass has completed (and all-reduced) it, instead of
+        one launch over everything after the pass.  Do not mix with ``step()`` on the same parameters within one run:
+        every plan counts its own steps."""
+        wanted = {id(p) for p in params}
+        for gi, group in enumerate(self.param_groups):
+            sub = [p for p in group["params"] if id(p) in wanted and p.grad is not None]
+            if sub:
+                self._launch((key, gi), group, sub)

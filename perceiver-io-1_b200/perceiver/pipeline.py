@@ -68,7 +68,8 @@ class GraphedTrainStep:
     Dropout seeds are launch arguments, so a replay repeats the captured masks: fine for timing, not for training with
     dropout > 0 (train those eagerly)."""
 
-    def __init__(self, params, optimizer, loss_fn, overlap_allreduce=True, bucket_bytes=16 << 20, warmup=3, before_warmup_step=None):
+    def __init__(self, params, optimizer, loss_fn, overlap_allreduce=True, bucket_bytes=16 << 20, warmup=3, before_warmup_step=None,
+                 bucketed_optimizer=None):
         import torch.distributed as dist
         from . import _native as N
         from .distributed import FlatGradients, average_gradients
@@ -79,6 +80,21 @@ class GraphedTrainStep:
         use_fg = overlap_allreduce or self.world == 1
         self.fg = FlatGradients(self.params, bucket_bytes=bucket_bytes) if use_fg else None
         self._average = average_gradients
+        # ``bucketed_optimizer`` (off unless asked for, or PIO_BUCKET_ADAMW=1): the optimizer steps each gradient bucket on its
+        # own lowest-priority stream as soon as the backward pass has completed it — and, with more than one rank, its
+        # all-reduce has finished — instead of one launch over all parameters after the pass, so that only the last
+        # bucket's update is left at the end of the step.  Measured at one rank on cfg2: 1.833 ms against 1.824 ms with the
+        # single launch — some stream keeps every SM busy for 98 % of the step, and AdamW's 30 bytes per parameter of HBM
+        # traffic slow the kernels they overlap by as much as they save at the end; kept for many-rank runs, where the
+        # update otherwise waits for the last all-reduce.
+        import os as _os
+        if bucketed_optimizer is None:
+            bucketed_optimizer = _os.environ.get("PIO_BUCKET_ADAMW") is not None
+        nccl_or_single = self.world == 1 or dist.get_backend() == "nccl"
+        self.bucketed_opt = bool(bucketed_optimizer) and self.fg is not None and hasattr(optimizer, "step_params") and nccl_or_single
+        self.opt_stream = torch.cuda.Stream(dev) if self.bucketed_opt else None
+        if self.bucketed_opt:
+            self.fg.on_ready = self._bucket_ready
         side = torch.cuda.Stream(dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
@@ -116,14 +132,32 @@ class GraphedTrainStep:
     def in_graph_optimizer(self):
         return self.fg is not None or self.world == 1
 
+    def _bucket_ready(self, b, handle):
+        if self.fg.flat is None or getattr(self, "_in_body", False) is False:
+            return  # (the profiling pass, or a backward pass outside the step)
+        cur = torch.cuda.current_stream(self.device)
+        ev = torch.cuda.Event()
+        ev.record(cur)  # the bucket's gradients are final — and nothing enqueued so far still reads its parameters' old values
+        self.opt_stream.wait_event(ev)
+        with torch.cuda.stream(self.opt_stream):
+            if handle is not None:
+                handle.wait()  # this stream waits for the bucket's all-reduce
+            self.opt.step_params(self.fg.bucket_params(b), ("bucket", b))
+
     def _body(self):
         if self.fg is not None:
             self.fg.step_begin()
-        loss = self.loss_fn()
-        loss.backward()
-        if self.fg is not None:
-            self.fg.step_end()
-        if self.in_graph_optimizer:
+        self._in_body = True
+        try:
+            loss = self.loss_fn()
+            loss.backward()
+            if self.fg is not None:
+                self.fg.step_end()
+        finally:
+            self._in_body = False
+        if self.bucketed_opt:
+            torch.cuda.current_stream(self.device).wait_stream(self.opt_stream)
+        elif self.in_graph_optimizer:
             self.opt.step()
         return loss
 
@@ -152,7 +186,7 @@ class GraphedMLMStep(GraphedTrainStep):
       backward with every parameter gradient written in place into one flat buffer, the optimizer step, and for
       more than one rank the bucketed gradient all-reduce overlapped with the backward pass."""
 
-    def __init__(self, model, optimizer, ids, pad, overlap_allreduce=True, bucket_bytes=16 << 20, warmup=3):
+    def __init__(self, model, optimizer, ids, pad, overlap_allreduce=True, bucket_bytes=16 << 20, warmup=3, bucketed_optimizer=None):
         dev = next(model.parameters()).device
         self.model = model
         self.ids = torch.empty(ids.shape, dtype=torch.int64, device=dev)
@@ -163,7 +197,7 @@ class GraphedMLMStep(GraphedTrainStep):
         def loss_fn():
             return model(self.ids, self.pad, masking=False, return_loss=True, labels=self.labels)[0]
         super().__init__(model.parameters(), optimizer, loss_fn, overlap_allreduce=overlap_allreduce, bucket_bytes=bucket_bytes,
-                         warmup=warmup, before_warmup_step=lambda: self._fill(ids, pad))
+                         warmup=warmup, before_warmup_step=lambda: self._fill(ids, pad), bucketed_optimizer=bucketed_optimizer)
 
     def _fill(self, ids, pad):
         if not self.prefetch.pending:

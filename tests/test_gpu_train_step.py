@@ -99,12 +99,13 @@ def test_flat_gradients_equal_the_per_operator_slabs_and_save_launches():
     fg.close()
 
 
-@pytest.mark.parametrize("cfg", ["small", "cfg2_b64"])
+@pytest.mark.parametrize("cfg", ["small", "cfg2_b64", "small_bucketed_adamw"])
 def test_graphed_step_matches_eager_steps_and_the_oracle(cfg):
     """3 optimizer steps: CUDA-graph replay (prefetched masking, flat gradients, AdamW in the graph) against the eager
     step on a copy of the model fed the same masked batches; step 1 loss and gradients against the fp32 oracle."""
     import perceiver
-    if cfg == "small":
+    bucketed = cfg.endswith("_bucketed_adamw")  # AdamW per gradient bucket from inside the backward pass (two buckets here)
+    if cfg.startswith("small"):
         vocab, seq, latent, layers, sa, heads, batch = 1003, 128, (32, 64), 3, 2, (2, 2, 2), 8
     else:  # BASELINE.json configs[1], the benchmarked workload
         vocab, seq, latent, layers, sa, heads, batch = 10003, 512, (64, 256), 3, 6, (4, 4, 4), 64
@@ -118,7 +119,9 @@ def test_graphed_step_matches_eager_steps_and_the_oracle(cfg):
     opt_e = perceiver.FusedAdamW(eager.parameters(), lr=lr)
     torch.manual_seed(11)
     init = {k: p.detach().clone() for k, p in model.named_parameters()}
-    gstep = perceiver.GraphedMLMStep(model, opt_g, ids_d, pad_d)
+    gstep = perceiver.GraphedMLMStep(model, opt_g, ids_d, pad_d, bucketed_optimizer=bucketed,
+                                     bucket_bytes=(256 << 10) if bucketed else (16 << 20))
+    assert gstep.bucketed_opt == bucketed and (not bucketed or len(gstep.fg.views) >= 2)
     # construction ran warm-up optimizer steps: back to the initial weights and optimizer state
     with torch.no_grad():
         for k, p in model.named_parameters():
