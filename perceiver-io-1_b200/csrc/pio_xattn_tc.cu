@@ -434,13 +434,18 @@ extern "C" int pio_debug_xat_trace(long long* out, int slots) {
 
 static bool aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 
-// all queries of a sample in one 128-row tile, head size 64, no attention dropout; rows of q / o / dO / dq contiguous
+// all queries of a sample in one 128-row tile, more than one key tile, head size 64, no attention dropout; rows of q / o /
+// dO / dq contiguous
 bool xattn_bwd_tc_supported(const pio_attn_desc* d, const DropCfg* drop) {
     const bool off = getenv("PIO_NO_XATTN_TC") != nullptr;
     if (off || d == nullptr) return false;
     if (drop != nullptr && drop->threshold != 0) return false;
     const int64_t cols = (int64_t)d->heads * d->dh;
-    return d->dh == xat::DH && d->n >= 1 && d->n <= xat::ROWS && d->m >= 1 && d->m <= xat::ROWS * xat::MAX_TILES && d->batch >= 1 &&
+    // keys that fit ONE tile stay with the general kernels: there the row term is formed as delta = sum_k p dP from the
+    // recomputed probabilities, which makes every row of dS sum to zero exactly — the decoder's query LayerNorm gradient
+    // (a sum of dQ over all rows, mostly cancelling) is 4x more accurate that way; over several key tiles delta = dO . O
+    // is the only one-pass form, here as there
+    return d->dh == xat::DH && d->n >= 1 && d->n <= xat::ROWS && d->m > xat::ROWS && d->m <= xat::ROWS * xat::MAX_TILES && d->batch >= 1 &&
            d->batch <= 65535 && d->heads <= 65535 && d->q_rs == cols && d->o_rs == cols && d->q_bs == (int64_t)d->n * cols &&
            d->o_bs == (int64_t)d->n * cols && d->k_rs % 8 == 0 && d->v_rs % 8 == 0 && d->k_bs % 8 == 0 && d->v_bs % 8 == 0 &&
            aligned16(d->q) && aligned16(d->k) && aligned16(d->v) && (d->o == nullptr || aligned16(d->o));

@@ -120,9 +120,9 @@ def _ref_grads(q, k, v, do, pad, heads):
 def test_flash_tc_backward(N, b, n, m, heads, padded, dh, one_tile_kernel, monkeypatch):
     """dq, dk, dv of the tcgen05 backward against fp64 autograd over the same bf16-rounded q, k, v, dO.
     The kernels round P, dS and the outputs to bf16, hence the bf16 tolerance.  Head sizes 64 and 128.
-    n <= 128 at head size 64 runs the (sample, head) kernel of pio_xattn_tc.cu unless switched off; everything else the
+    n <= 128 against more than 128 keys at head size 64 runs the (sample, head) kernel of pio_xattn_tc.cu unless switched off; everything else the
     two general kernels."""
-    one_tile = n <= 128 and dh == 64
+    one_tile = n <= 128 and m > 128 and dh == 64  # (keys that fit one tile stay with the general kernels)
     if not one_tile_kernel:
         if not one_tile:
             pytest.skip("same path as one_tile_kernel=True")
