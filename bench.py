@@ -804,10 +804,12 @@ def gpu_arm(args):
             xattn = cross_attention_core_tflops(mode, pk)
         except Exception as ex:  # side metric must never sink the headline line
             xattn = {"error": str(ex)[:200]}
-        try:
-            others = other_config_throughput(mode)
-        except Exception as ex:
-            others = {"error": str(ex)[:200]}
+        others = None
+        if world == 1:  # N = 1 only: its graphed steps (GraphedTrainStep) see the process group and would open all-reduces
+            try:        # that no other rank joins — rank 0 hung here in a full multi-rank run while the others sat at the last barrier
+                others = other_config_throughput(mode)
+            except Exception as ex:
+                others = {"error": str(ex)[:200]}
         sample_b = CFG["batch"]  # the same batch of 64 (same_config)
         cpu = cpu_reference_arm(steps=3, warmup=1, batch=sample_b) if world == 1 else None  # CPU baseline: N=1 only
         result = {
