@@ -368,6 +368,12 @@ def _forget_pending():
 #     handed to another tensor while a consumer may still look it up.
 #   * autograd stores the first gradient of an input as it is (no copy), which is what makes adding into it later
 #     the same as summing; bf16 mode only (the fp32 operators refuse the flags).
+#   * That holds while autograd's input buffer for the activation IS the published tensor.  A further consumer outside
+#     this protocol (a skip connection a user adds) makes autograd sum into another tensor as soon as its gradient
+#     arrives, and a share added to the published buffer after that would be lost.  So a later producer merges only
+#     while the engine still holds the published tensor — its reference count says so (this table's Python object + the
+#     engine's buffer = 2; autograd never adds in place into a tensor someone else holds, and a sum formed AFTER a merge
+#     contains it) — and otherwise returns its gradient the ordinary way.  Without `Tensor._use_count` nothing is merged.
 _ACT_STATS = {"merged": 0}  # how many activation gradients were added in place (tests)
 
 
@@ -382,8 +388,13 @@ def _act_pending(x):
     with _PASS.lock:
         e = _PASS.acts.get(_act_key(x))
     if e is not None and e[0] is x.grad_fn and e[1] == x.output_nr:
-        _ACT_STATS["merged"] += 1
-        return e[2]
+        try:
+            held = e[2]._use_count() >= 2  # (1: autograd has replaced its buffer by a sum with a foreign consumer's gradient)
+        except AttributeError:
+            held = False
+        if held:
+            _ACT_STATS["merged"] += 1
+            return e[2]
     return None
 
 

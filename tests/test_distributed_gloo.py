@@ -147,16 +147,29 @@ def _fg_worker(rank, world, port, out_dir):
     fired_inside = []
     orig = fg._reduce
     fg._reduce = lambda b: (fired_inside.append(b), orig(b))[1]
+    # the per-bucket consumer hook (GraphedTrainStep's optimizer-per-bucket): one call per bucket and step, with the handle
+    # of the bucket's all-reduce; after waiting on it the bucket holds the sum over the ranks
+    ready, sums = [], {}
+
+    def on_ready(b, handle):
+        handle.wait()
+        ready.append(b)
+        sums[b] = fg.views[b].clone()
+    fg.on_ready = on_ready
     results = []
     for step in range(2):  # twice: the per-step state resets
+        ready.clear()
         fg.step_begin()
         _fg_loss(params, x, y).backward()
         n_in_backward = len(fired_inside)
         fg.step_end()
         results.append(torch.cat([p.grad.reshape(-1) for p in params]).clone())
         fired_inside.clear()
+    hook_ok = (sorted(ready) == list(range(len(fg.views))) and
+               all(torch.allclose(sums[b] / world, fg.views[b]) for b in range(len(fg.views))) and
+               sorted(id(p) for b in range(len(fg.views)) for p in fg.bucket_params(b)) == sorted(id(p) for p in fg.params))
     torch.save({"g0": results[0], "g1": results[1], "buckets": len(fg.views), "fired_in_backward": n_in_backward,
-                "views": all(p.grad.data_ptr() >= fg.flat.data_ptr() for p in params)},
+                "views": all(p.grad.data_ptr() >= fg.flat.data_ptr() for p in params), "hook_ok": hook_ok},
                os.path.join(out_dir, f"fg{rank}.pt"))
     fg.close()
     dist.barrier()
@@ -170,6 +183,7 @@ def test_flat_gradients_two_rank_gloo_bucketed_mean_equals_full_batch_gradient(t
     got = [torch.load(tmp_path / f"fg{r}.pt") for r in range(world)]
     assert torch.equal(got[0]["g0"], got[1]["g0"]) and torch.equal(got[0]["g0"], got[0]["g1"])
     assert got[0]["views"] and got[0]["buckets"] >= 3
+    assert got[0]["hook_ok"] and got[1]["hook_ok"]
     assert got[0]["fired_in_backward"] >= 2  # buckets went out while the backward pass was still running
     # reference: one process, whole batch, plain autograd
     params = _fg_model()

@@ -164,3 +164,92 @@ def test_direct_calls_outside_a_backward_pass_share_nothing(fake):
     (g2,), _ = F._grads_like([w], N.MODE_BF16)
     assert isinstance(g1, torch.Tensor) and isinstance(g2, torch.Tensor) and g1.data_ptr() != g2.data_ptr()
     assert F._PASS.pending == {} and F._PASS.slabs == []
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Activation gradients with two consumers (functional._act_pending / _act_publish): the first backward publishes the
+# buffer it returns, the second adds into it and returns None.  CPU stand-ins for the CUDA operators follow the
+# protocol of KVProjectFn / CrossAttendFn / LatentBlockFn.backward.
+# ---------------------------------------------------------------------------------------------------------------
+class _Scale(torch.autograd.Function):
+    """y = k x with the activation-gradient protocol of the fused operators"""
+
+    @staticmethod
+    def forward(ctx, x, k):
+        ctx.save_for_backward(x)
+        ctx.k = k
+        return x * k
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        merged = F._act_pending(x)
+        if merged is not None:
+            merged.add_(dy * ctx.k)  # (the kernels add inside the producing kernel: PIO_ACC_DX / PIO_ACC_DKV)
+            return None, None
+        dx = dy * ctx.k
+        F._act_publish(x, dx)
+        return dx, None
+
+
+def test_second_consumer_of_an_activation_adds_into_the_first_gradient_buffer():
+    F._ACT_STATS["merged"] = 0
+    a = torch.randn(5, 3, requires_grad=True)
+    x = a.exp()                                  # a non-leaf: identified by (grad_fn, output number, address, shape)
+    y = _Scale.apply(x, 2.0).sum() + _Scale.apply(x, 3.0).sum()
+    y.backward()
+    assert F._ACT_STATS["merged"] == 1
+    assert not F._PASS.acts                      # released by the end-of-pass callback
+    torch.testing.assert_close(a.grad, a.detach().exp() * 5.0)
+    # a second pass starts from an empty table
+    a.grad = None
+    x = a.exp()
+    (_Scale.apply(x, 2.0).sum() + _Scale.apply(x, 3.0).sum() + _Scale.apply(x, 7.0).sum()).backward()
+    assert F._ACT_STATS["merged"] == 3
+    torch.testing.assert_close(a.grad, a.detach().exp() * 12.0)
+
+
+def test_a_consumer_outside_the_protocol_never_costs_a_share_of_the_gradient():
+    """autograd sums a foreign consumer's gradient with the published buffer into ANOTHER tensor; a share merged into
+    the published buffer after that would be lost, so a producer merges only while the engine still holds the buffer:
+    whichever order the engine runs the consumers in, the gradient is the full sum"""
+    for variant in range(6):
+        a = torch.randn(5, 3, requires_grad=True)
+        x = a.exp()
+        t = [_Scale.apply(x, 2.0).sum(), _Scale.apply(x, 3.0).sum()]
+        f = (x * 5.0).sum() if variant < 3 else _Scale.apply(x.clone(), 5.0).sum()  # an ordinary torch op on the same activation
+        y = (f + t[0] + t[1], t[0] + f + t[1], t[0] + t[1] + f)[variant % 3]
+        y.backward()
+        torch.testing.assert_close(a.grad, a.detach().exp() * 10.0)
+        assert not F._PASS.acts
+
+
+def test_leaves_and_direct_calls_are_never_merged(monkeypatch):
+    F._ACT_STATS["merged"] = 0
+    a = torch.randn(4, requires_grad=True)       # a leaf has no grad_fn to be identified by
+    (_Scale.apply(a, 2.0).sum() + _Scale.apply(a, 3.0).sum()).backward()
+    assert F._ACT_STATS["merged"] == 0
+    torch.testing.assert_close(a.grad, torch.full((4,), 5.0))
+    # outside a backward pass nothing can clear an entry, so nothing is published
+    x = a.exp()
+    F._act_publish(x, torch.zeros_like(x))
+    assert not F._PASS.acts
+    # the switch
+    monkeypatch.setenv("PIO_NO_GRAD_MERGE", "1")
+    a.grad = None
+    x = a.exp()
+    (_Scale.apply(x, 2.0).sum() + _Scale.apply(x, 3.0).sum()).backward()
+    assert F._ACT_STATS["merged"] == 0
+    torch.testing.assert_close(a.grad, a.detach().exp() * 5.0)
+
+
+def test_same_memory_other_autograd_output_is_not_merged():
+    """two views of one buffer are different autograd outputs: same address and shape, but not the same activation"""
+    F._ACT_STATS["merged"] = 0
+    a = torch.randn(6, requires_grad=True)
+    x = a.exp()
+    v1, v2 = x.view(6), x.view(6)                # same data_ptr, same shape, different grad_fn
+    (_Scale.apply(v1, 2.0).sum() + _Scale.apply(v2, 3.0).sum()).backward()
+    assert F._ACT_STATS["merged"] == 0
+    torch.testing.assert_close(a.grad, a.detach().exp() * 5.0)
