@@ -591,11 +591,13 @@ def gpu_arm(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     distributed = world > 1
+    # a rank stuck in a collective (or a kernel that never ends) would hold its GPU until the launcher's limit: every
+    # process ends itself instead, with the Python stacks of all threads on stderr (the whole default run takes well under
+    # a minute at one rank)
+    import faulthandler
+    faulthandler.dump_traceback_later(int(os.environ.get("PIO_BENCH_WATCHDOG_S", "600")), exit=True)
     if distributed:
-        import faulthandler
         import torch.distributed as dist
-        # a rank stuck in a collective would hold its GPU until the launcher's limit: every rank ends itself instead
-        faulthandler.dump_traceback_later(int(os.environ.get("PIO_BENCH_WATCHDOG_S", "600")), exit=True)
         # keep stdout to the one JSON line: NCCL writes its version banner (debug level VERSION, which sits BELOW
         # WARN) to stdout unless told where else to log
         # (and NCCL honours NCCL_DEBUG_FILE only above level VERSION)
