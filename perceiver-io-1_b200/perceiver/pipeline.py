@@ -66,7 +66,10 @@ class GraphedTrainStep:
     captured backward pass.  ``overlap_allreduce=False``: one flat all-reduce and the optimizer run eagerly after the
     graph (the previous scheme).  bf16 compute mode; the optimizer must be capturable (`perceiver.FusedAdamW`).
     Dropout seeds are launch arguments, so a replay repeats the captured masks: fine for timing, not for training with
-    dropout > 0 (train those eagerly)."""
+    dropout > 0 (train those eagerly).
+    With a process group of more than one rank, construction and every replay are COLLECTIVE: all ranks must build the
+    step and replay it the same number of times (a step built on one rank alone waits for the others in its first
+    all-reduce forever — bench.py's side measurements did exactly that once)."""
 
     def __init__(self, params, optimizer, loss_fn, overlap_allreduce=True, bucket_bytes=16 << 20, warmup=3, before_warmup_step=None,
                  bucketed_optimizer=None):
