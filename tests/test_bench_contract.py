@@ -47,3 +47,14 @@ def test_default_invocation_is_one_gpu_and_short():
     src = open(os.path.join(ROOT, "bench.py")).read()
     assert 'add_argument("--gpus", type=int, default=1)' in src
     assert 'add_argument("--steps", type=int, default=100)' in src
+
+
+def test_result_line_carries_every_key_of_the_contract():
+    tree = ast.parse(open(os.path.join(ROOT, "bench.py")).read())
+    want = {"metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
+            "dtype", "data", "config", "clocks", "e2e", "gpu_launches", "roofline", "cpu_baseline"}
+    for fn, extra in (("gpu_arm", set()), ("reference_arm", {"impl"})):
+        node = next(n for n in ast.walk(tree) if isinstance(n, ast.FunctionDef) and n.name == fn)
+        keysets = [{k.value for k in d.keys if isinstance(k, ast.Constant)} for d in ast.walk(node) if isinstance(d, ast.Dict)]
+        need = (want - {"clocks", "gpu_launches", "roofline"}) | extra if fn == "reference_arm" else want
+        assert any(need <= ks for ks in keysets), (fn, sorted(need - max(keysets, key=lambda ks: len(need & ks))))
